@@ -1,0 +1,37 @@
+#include "common.h"
+
+namespace b200 {
+
+char* error_buffer() {
+    static thread_local char buf[512] = {0};
+    return buf;
+}
+
+int fail(int code, const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(error_buffer(), 512, fmt, ap);
+    va_end(ap);
+    return code;
+}
+
+int sm_count_cached() {
+    static thread_local int cached_dev = -1;
+    static thread_local int cached_sms = 0;
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) return 148;
+    if (dev != cached_dev) {
+        int n = 0;
+        if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0)
+            n = 148;
+        cached_dev = dev;
+        cached_sms = n;
+    }
+    return cached_sms;
+}
+
+}  // namespace b200
+
+extern "C" const char* b200_last_error(void) { return b200::error_buffer(); }
+extern "C" int b200_version(void) { return 100; }
+extern "C" int b200_sm_count(void) { return b200::sm_count_cached(); }

@@ -1,0 +1,513 @@
+// Swap-AB stream-K tcgen05 GEMM for pipeline-stage linears (see b200_petals.h).
+//
+//   out[t, n] = epi( sum_k norm(x)[t, k] * W[n, k] )
+//
+// Layout of one CTA (192 threads, persistent over a contiguous k-block range):
+//   warp 0      weight loader   one lane; 16/32 KiB cp.async.bulk per k-block
+//   warp 1      MMA issuer      one lane; tcgen05.mma 128 x BN x 16, fp32 in TMEM
+//   warps 2..5  B producers     activations -> (norm) -> swizzled smem, then the
+//                               same warps drain TMEM and run the epilogue
+// The weight ring and the activation ring have independent depths, so the
+// HBM stream (weights) is never throttled by the L2-latency-bound B side.
+#include "common.h"
+#include "ptx.cuh"
+
+namespace b200 {
+
+constexpr int kTileM = 128;            // weight rows per tile (UMMA M)
+constexpr int kBK = 64;                // k elements per block = one 128 B swizzle row
+constexpr int kABytes = kTileM * 128;  // bytes of one packed weight block
+constexpr int kThreads = 192;
+constexpr int kEpiThreads = 128;
+
+template <int BN, int DUAL>
+struct GemmCfg {
+    static constexpr int kAPer = DUAL ? 2 : 1;
+    static constexpr int kStageA = kABytes * kAPer;
+    static constexpr int kStageB = BN * 128;
+    // ring depths (see DESIGN.md "GEMM shared-memory budget")
+    static constexpr int kSA = (BN == 16) ? (DUAL ? 3 : 6) : (BN == 256) ? (DUAL ? 3 : 6) : (DUAL ? 4 : 8);
+    static constexpr int kSB = (BN == 16) ? 6 : (BN == 32) ? 8 : (BN == 64) ? 6 : (BN == 128) ? 4 : 3;
+    static constexpr int kGroup = (BN == 16) ? 4 : (BN == 32) ? 2 : 1;  // k-blocks per producer batch
+    static constexpr int kTmemColsRaw = BN * kAPer;
+    static constexpr int kTmemCols = kTmemColsRaw <= 32 ? 32 : kTmemColsRaw <= 64 ? 64 : kTmemColsRaw <= 128 ? 128 : kTmemColsRaw <= 256 ? 256 : 512;
+    static constexpr int kMinBlocks = (BN == 16) ? 2 : 1;
+    static constexpr size_t kSmemData = (size_t)kSA * kStageA + (size_t)kSB * kStageB;
+    static constexpr size_t kSmemBytes = kSmemData + 1024 /*align*/ + 1024 /*barriers, stats*/;
+};
+
+struct GemmParams {
+    const uint8_t* __restrict__ w;
+    const uint16_t* __restrict__ x;
+    void* __restrict__ out;
+    const uint16_t* __restrict__ residual;
+    const uint16_t* __restrict__ bias;
+    const uint16_t* __restrict__ norm_w;
+    const uint16_t* __restrict__ norm_b;
+    float* __restrict__ scratch;
+    int* __restrict__ counters;
+    int T, N, K;
+    int ldx, ldo, ldr;
+    int n_tiles, t_tiles, kbpt;
+    long long Q;  // total k-blocks = n_tiles * t_tiles * kbpt
+    int epilogue, norm_mode;
+    float norm_eps;
+    int is_bf16, out_fp32;
+};
+
+__device__ __forceinline__ long long range_begin(const GemmParams& p, int c) {
+    return (long long)c * p.Q / (long long)gridDim.x;
+}
+
+__device__ __forceinline__ float gelu_tanh(float x) {
+    const float k0 = 0.7978845608028654f, k1 = 0.044715f;
+    return 0.5f * x * (1.0f + tanhf(k0 * (x + k1 * x * x * x)));
+}
+
+// Rounds through the 16-bit storage type so fused epilogues see the same values
+// the unfused torch sequence would have stored between ops.
+__device__ __forceinline__ float round16(float v, int is_bf16) {
+    return h16_to_float(float_to_h16(v, is_bf16), is_bf16);
+}
+
+template <int BN, int DUAL>
+__device__ __forceinline__ void epilogue_store_chunk(const GemmParams& p, int n_tile, int t_tile,
+                                                     int row, int chunk, const float (&vg)[16],
+                                                     const float (&vu)[16]) {
+    const int n = n_tile * kTileM + row;
+    if (n >= p.N) return;
+    const float b = p.bias ? h16_to_float(p.bias[n], p.is_bf16) : 0.0f;
+#pragma unroll
+    for (int j = 0; j < 16; ++j) {
+        const int t = t_tile * BN + chunk * 16 + j;
+        if (t >= p.T) break;
+        float v = vg[j] + b;
+        if (DUAL) {
+            const float g = round16(v, p.is_bf16);
+            const float u = round16(vu[j], p.is_bf16);
+            const float s = round16(g / (1.0f + __expf(-g)), p.is_bf16);
+            v = s * u;
+        } else if (p.epilogue == B200_EPI_GELU_TANH) {
+            v = gelu_tanh(round16(v, p.is_bf16));
+        }
+        if (p.residual) {
+            v = round16(v, p.is_bf16) + h16_to_float(p.residual[(size_t)t * p.ldr + n], p.is_bf16);
+        }
+        if (p.out_fp32) {
+            reinterpret_cast<float*>(p.out)[(size_t)t * p.ldo + n] = v;
+        } else {
+            reinterpret_cast<uint16_t*>(p.out)[(size_t)t * p.ldo + n] = float_to_h16(v, p.is_bf16);
+        }
+    }
+}
+
+template <int BN, int DUAL>
+__global__ void __launch_bounds__(kThreads, GemmCfg<BN, DUAL>::kMinBlocks)
+gemm_streamk_kernel(const GemmParams p) {
+    using Cfg = GemmCfg<BN, DUAL>;
+    constexpr int SA = Cfg::kSA, SB = Cfg::kSB, APER = Cfg::kAPer;
+
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint8_t* smem_a = smem;
+    uint8_t* smem_b = smem + (size_t)SA * Cfg::kStageA;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + Cfg::kSmemData);
+    uint64_t* a_full = bars;
+    uint64_t* a_empty = a_full + SA;
+    uint64_t* b_full = a_empty + SA;
+    uint64_t* b_empty = b_full + SB;
+    uint64_t* acc_full = b_empty + SB;
+    uint64_t* acc_empty = acc_full + 1;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + 1);
+    volatile int* fin_flag = reinterpret_cast<volatile int*>(tmem_slot + 1);  // [2]
+    float* stat_mean = reinterpret_cast<float*>(tmem_slot + 4);               // [32]
+    float* stat_rstd = stat_mean + 32;                                        // [32]
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+    const int cta = blockIdx.x;
+
+    if (threadIdx.x == 0) {
+        for (int i = 0; i < SA; ++i) { mbar_init(&a_full[i], 1); mbar_init(&a_empty[i], 1); }
+        for (int i = 0; i < SB; ++i) { mbar_init(&b_full[i], 4); mbar_init(&b_empty[i], 1); }
+        mbar_init(acc_full, 1);
+        mbar_init(acc_empty, 4);
+        fence_mbar_init();
+    }
+    if (warp == 1) tmem_alloc<Cfg::kTmemCols>(tmem_slot);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    const long long q_begin = range_begin(p, cta);
+    const long long q_end = range_begin(p, cta + 1);
+
+    if (warp == 0) {
+        // ------------------------------------------------ weight loader
+        if (lane == 0) {
+            // Weights never depend on the previous kernel: start streaming at once.
+            const uint64_t policy = l2_policy_evict_first();
+            uint32_t it = 0;
+            for (long long q = q_begin; q < q_end; ++q, ++it) {
+                const int u = (int)(q / p.kbpt);
+                const int kb = (int)(q - (long long)u * p.kbpt);
+                const int n_tile = u / p.t_tiles;
+                const int s = it % SA;
+                const uint32_t ph = (it / SA) & 1;
+                mbar_wait(&a_empty[s], ph ^ 1);
+                mbar_arrive_expect_tx(&a_full[s], Cfg::kStageA);
+                const uint8_t* src = p.w + ((size_t)n_tile * p.kbpt + kb) * Cfg::kStageA;
+                if (p.t_tiles == 1)
+                    bulk_g2s_hint(smem_a + (size_t)s * Cfg::kStageA, src, Cfg::kStageA, &a_full[s], policy);
+                else
+                    bulk_g2s(smem_a + (size_t)s * Cfg::kStageA, src, Cfg::kStageA, &a_full[s]);
+            }
+        }
+    } else if (warp == 1) {
+        // ------------------------------------------------ MMA issuer
+        if (lane == 0) {
+            const uint32_t idesc = umma_idesc(kTileM, BN, p.is_bf16, p.is_bf16, 0, 0);
+            uint32_t it = 0, part = 0;
+            long long q = q_begin;
+            while (q < q_end) {
+                const int u = (int)(q / p.kbpt);
+                const int kb0 = (int)(q - (long long)u * p.kbpt);
+                const long long rem = q_end - q;
+                const int kb1 = (rem < (long long)(p.kbpt - kb0)) ? kb0 + (int)rem : p.kbpt;
+                mbar_wait(acc_empty, (part & 1) ^ 1);
+                tc_fence_after();
+                for (int kb = kb0; kb < kb1; ++kb, ++it) {
+                    const int sa = it % SA, sb = it % SB;
+                    mbar_wait(&b_full[sb], (it / SB) & 1);
+                    mbar_wait(&a_full[sa], (it / SA) & 1);
+                    tc_fence_after();
+                    const uint32_t a_addr = smem_u32(smem_a + (size_t)sa * Cfg::kStageA);
+                    const uint32_t b_addr = smem_u32(smem_b + (size_t)sb * Cfg::kStageB);
+                    const uint64_t bdesc = umma_desc_kmajor_sw128(b_addr, 1024);
+#pragma unroll
+                    for (int a = 0; a < APER; ++a) {
+                        const uint64_t adesc = umma_desc_kmajor_sw128(a_addr + a * kABytes, 1024);
+#pragma unroll
+                        for (int k = 0; k < kBK / 16; ++k) {
+                            // +32 B per UMMA_K inside the 128 B swizzle row -> +2 in the address field
+                            umma_f16(tmem_base + a * BN, adesc + (uint64_t)(k * 2), bdesc + (uint64_t)(k * 2),
+                                     idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+                        }
+                    }
+                    umma_commit(&a_empty[sa]);
+                    umma_commit(&b_empty[sb]);
+                }
+                umma_commit(acc_full);
+                q += kb1 - kb0;
+                ++part;
+            }
+        }
+        __syncwarp();
+    } else {
+        // ------------------------------------------------ B producers + epilogue
+        const int e = threadIdx.x - 64;         // 0..127
+        const int lg = warp & 3;                // TMEM lane quarter this warp may read
+        const int row = lg * 32 + lane;         // accumulator row (weight row in tile)
+        const int ch = e & 7;                   // 16-byte chunk of the 128 B k-row
+        const int r0 = e >> 3;                  // first token row this thread stages
+
+        pdl_wait_prior_grid();  // activations come from the previous kernel
+
+        if (p.norm_mode != B200_NORM_NONE) {
+            // Per-token statistics (decode-size T only; host guarantees t_tiles == 1, BN <= 32).
+            const int pw = warp - 2;
+            for (int t = pw; t < BN; t += 4) {
+                float s1 = 0.f, s2 = 0.f;
+                if (t < p.T) {
+                    const uint16_t* xr = p.x + (size_t)t * p.ldx;
+                    for (int c = lane; c < p.K / 8; c += 32) {
+                        const uint4 v = ld_cg_v4(xr + c * 8);
+                        const uint32_t w4[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+                        for (int i = 0; i < 4; ++i) {
+                            const float a = h16_to_float((uint16_t)(w4[i] & 0xffff), p.is_bf16);
+                            const float b = h16_to_float((uint16_t)(w4[i] >> 16), p.is_bf16);
+                            s1 += a + b;
+                            s2 += a * a + b * b;
+                        }
+                    }
+                }
+                s1 = warp_sum(s1);
+                s2 = warp_sum(s2);
+                if (lane == 0) {
+                    const float inv = 1.0f / (float)p.K;
+                    if (p.norm_mode == B200_NORM_RMS) {
+                        stat_mean[t] = 0.f;
+                        stat_rstd[t] = rsqrtf(s2 * inv + p.norm_eps);
+                    } else {
+                        const float m = s1 * inv;
+                        const float var = fmaxf(s2 * inv - m * m, 0.f);
+                        stat_mean[t] = m;
+                        stat_rstd[t] = rsqrtf(var + p.norm_eps);
+                    }
+                }
+            }
+            named_bar_sync(1, kEpiThreads);
+        }
+
+        uint32_t it = 0, part = 0;
+        long long q = q_begin;
+        while (q < q_end) {
+            const int u = (int)(q / p.kbpt);
+            const int kb0 = (int)(q - (long long)u * p.kbpt);
+            const long long rem = q_end - q;
+            const int kb1 = (rem < (long long)(p.kbpt - kb0)) ? kb0 + (int)rem : p.kbpt;
+            const int n_tile = u / p.t_tiles;
+            const int t_tile = u - n_tile * p.t_tiles;
+
+            // ---- stage activations for k-blocks [kb0, kb1)
+            for (int kb = kb0; kb < kb1; kb += Cfg::kGroup) {
+                const int ng = (kb1 - kb < Cfg::kGroup) ? (kb1 - kb) : Cfg::kGroup;
+                uint4 v[Cfg::kGroup][BN / 16];
+                uint4 gw[Cfg::kGroup], gb[Cfg::kGroup];
+#pragma unroll
+                for (int g = 0; g < Cfg::kGroup; ++g) {
+                    if (g < ng) {
+                        const int kcol = (kb + g) * kBK + ch * 8;
+#pragma unroll
+                        for (int i = 0; i < BN / 16; ++i) {
+                            const int t = t_tile * BN + r0 + 16 * i;
+                            v[g][i] = (t < p.T) ? ld_cg_v4(p.x + (size_t)t * p.ldx + kcol) : make_uint4(0, 0, 0, 0);
+                        }
+                        if (p.norm_mode != B200_NORM_NONE) {
+                            gw[g] = ld_nc_v4(p.norm_w + kcol);
+                            gb[g] = p.norm_b ? ld_nc_v4(p.norm_b + kcol) : make_uint4(0, 0, 0, 0);
+                        }
+                    }
+                }
+#pragma unroll
+                for (int g = 0; g < Cfg::kGroup; ++g) {
+                    if (g < ng) {
+                        const uint32_t itg = it + g;
+                        const int sb = itg % SB;
+                        mbar_wait(&b_empty[sb], ((itg / SB) & 1) ^ 1);
+                        const uint32_t base = smem_u32(smem_b + (size_t)sb * Cfg::kStageB);
+#pragma unroll
+                        for (int i = 0; i < BN / 16; ++i) {
+                            const int r = r0 + 16 * i;
+                            uint4 val = v[g][i];
+                            if (p.norm_mode != B200_NORM_NONE) {
+                                const int t = t_tile * BN + r;
+                                if (t < p.T) {
+                                    const float mean = stat_mean[r], rstd = stat_rstd[r];
+                                    uint32_t xin[4] = {val.x, val.y, val.z, val.w};
+                                    const uint32_t win[4] = {gw[g].x, gw[g].y, gw[g].z, gw[g].w};
+                                    const uint32_t bin[4] = {gb[g].x, gb[g].y, gb[g].z, gb[g].w};
+#pragma unroll
+                                    for (int w = 0; w < 4; ++w) {
+                                        float x0 = h16_to_float((uint16_t)(xin[w] & 0xffff), p.is_bf16);
+                                        float x1 = h16_to_float((uint16_t)(xin[w] >> 16), p.is_bf16);
+                                        const float g0 = h16_to_float((uint16_t)(win[w] & 0xffff), p.is_bf16);
+                                        const float g1 = h16_to_float((uint16_t)(win[w] >> 16), p.is_bf16);
+                                        if (p.norm_mode == B200_NORM_RMS) {
+                                            // HF LlamaRMSNorm: weight * (x * rstd).to(dtype)
+                                            x0 = g0 * round16(x0 * rstd, p.is_bf16);
+                                            x1 = g1 * round16(x1 * rstd, p.is_bf16);
+                                        } else {
+                                            const float b0 = h16_to_float((uint16_t)(bin[w] & 0xffff), p.is_bf16);
+                                            const float b1 = h16_to_float((uint16_t)(bin[w] >> 16), p.is_bf16);
+                                            x0 = (x0 - mean) * rstd * g0 + b0;
+                                            x1 = (x1 - mean) * rstd * g1 + b1;
+                                        }
+                                        xin[w] = (uint32_t)float_to_h16(x0, p.is_bf16) |
+                                                 ((uint32_t)float_to_h16(x1, p.is_bf16) << 16);
+                                    }
+                                    val = make_uint4(xin[0], xin[1], xin[2], xin[3]);
+                                }
+                            }
+                            st_shared_v4(base + r * 128 + ((ch ^ (r & 7)) << 4), val);
+                        }
+                        fence_proxy_async_smem();
+                        __syncwarp();
+                        if (lane == 0) mbar_arrive(&b_full[sb]);
+                    }
+                }
+                it += ng;
+            }
+
+            // ---- drain the accumulator of this part
+            const bool full_tile = (kb0 == 0) && (kb1 == p.kbpt);
+            const int slot = (part == 0) ? 0 : 1;
+            float* my_partial = p.scratch + ((size_t)cta * 2 + slot) * (size_t)(APER * BN * kTileM);
+            mbar_wait(acc_full, part & 1);
+            tc_fence_after();
+#pragma unroll 1
+            for (int c = 0; c < BN / 16; ++c) {
+                uint32_t rg[16], ru[16];
+                const uint32_t taddr = tmem_base + ((uint32_t)(lg * 32) << 16) + c * 16;
+                tmem_ld16(taddr, rg);
+                if (DUAL) tmem_ld16(taddr + BN, ru);
+                tmem_ld_wait();
+                float vg[16], vu[16];
+#pragma unroll
+                for (int j = 0; j < 16; ++j) {
+                    vg[j] = __uint_as_float(rg[j]);
+                    vu[j] = DUAL ? __uint_as_float(ru[j]) : 0.f;
+                }
+                if (full_tile) {
+                    epilogue_store_chunk<BN, DUAL>(p, n_tile, t_tile, row, c, vg, vu);
+                } else {
+#pragma unroll
+                    for (int j = 0; j < 16; ++j) {
+                        my_partial[(size_t)(c * 16 + j) * kTileM + row] = vg[j];
+                        if (DUAL) my_partial[(size_t)(BN + c * 16 + j) * kTileM + row] = vu[j];
+                    }
+                }
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(acc_empty);
+
+            if (!full_tile) {
+                __threadfence();
+                named_bar_sync(1, kEpiThreads);
+                if (e == 0) {
+                    const int add = kb1 - kb0;
+                    const int old = atomicAdd(&p.counters[u], add);
+                    fin_flag[part & 1] = (old + add == p.kbpt) ? 1 : 0;
+                }
+                named_bar_sync(1, kEpiThreads);
+                if (fin_flag[part & 1]) {
+                    // Last contributor of tile u: sum all partials in CTA order (deterministic).
+                    __threadfence();
+                    const long long t_lo = (long long)u * p.kbpt, t_hi = t_lo + p.kbpt;
+                    int c_first = (int)((t_lo * (long long)gridDim.x) / p.Q);
+                    while (c_first + 1 < (int)gridDim.x && range_begin(p, c_first + 1) <= t_lo) ++c_first;
+                    while (c_first > 0 && range_begin(p, c_first) > t_lo) --c_first;
+#pragma unroll 1
+                    for (int c = 0; c < BN / 16; ++c) {
+                        float vg[16], vu[16];
+#pragma unroll
+                        for (int j = 0; j < 16; ++j) { vg[j] = 0.f; vu[j] = 0.f; }
+                        for (int cc = c_first; cc < (int)gridDim.x; ++cc) {
+                            const long long rb = range_begin(p, cc), re = range_begin(p, cc + 1);
+                            if (rb >= t_hi) break;
+                            if (re <= rb || re <= t_lo) continue;
+                            const int cslot = (rb >= t_lo) ? 0 : 1;
+                            const float* src = p.scratch + ((size_t)cc * 2 + cslot) * (size_t)(APER * BN * kTileM);
+#pragma unroll
+                            for (int j = 0; j < 16; ++j) {
+                                vg[j] += __ldcg(src + (size_t)(c * 16 + j) * kTileM + row);
+                                if (DUAL) vu[j] += __ldcg(src + (size_t)(BN + c * 16 + j) * kTileM + row);
+                            }
+                        }
+                        epilogue_store_chunk<BN, DUAL>(p, n_tile, t_tile, row, c, vg, vu);
+                    }
+                    if (e == 0) p.counters[u] = 0;  // leave the counters clean for the next launch
+                }
+            }
+            q += kb1 - kb0;
+            ++part;
+        }
+    }
+
+    pdl_launch_dependents();
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) tmem_dealloc<Cfg::kTmemCols>(tmem_base);
+}
+
+template <int BN, int DUAL>
+static int launch_gemm(const GemmParams& p, int grid, bool pdl, cudaStream_t stream) {
+    using Cfg = GemmCfg<BN, DUAL>;
+    static_assert(Cfg::kSmemBytes <= 227 * 1024, "shared memory budget exceeded");
+    static thread_local int configured_dev = -1;
+    int dev = 0;
+    B200_CUDA_CHECK(cudaGetDevice(&dev));
+    if (configured_dev != dev) {
+        B200_CUDA_CHECK(cudaFuncSetAttribute(gemm_streamk_kernel<BN, DUAL>,
+                                             cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             (int)Cfg::kSmemBytes));
+        configured_dev = dev;
+    }
+    B200_CUDA_CHECK(launch(gemm_streamk_kernel<BN, DUAL>, dim3(grid), dim3(kThreads), Cfg::kSmemBytes,
+                           stream, pdl, p));
+    return B200_OK;
+}
+
+static int pick_token_tile(int T) {
+    if (T <= 16) return 16;
+    if (T <= 32) return 32;
+    if (T <= 64) return 64;
+    if (T <= 128) return 128;
+    return 256;
+}
+
+}  // namespace b200
+
+using namespace b200;
+
+extern "C" int32_t b200_gemm_token_tile(int32_t T, int32_t dual) {
+    (void)dual;
+    return pick_token_tile(T);
+}
+
+extern "C" int64_t b200_gemm_scratch_bytes(int32_t max_tokens) {
+    const int bn = pick_token_tile(max_tokens);
+    // grid <= SM count; two partial slots per CTA; dual doubles the accumulator
+    return (int64_t)sm_count_cached() * 2 * 2 * bn * kTileM * (int64_t)sizeof(float);
+}
+
+extern "C" int b200_gemm(const b200_gemm_args* a, void* stream_) {
+    if (!a || !a->w_packed || !a->x || !a->out || !a->scratch || !a->counters)
+        return fail(B200_EINVAL, "b200_gemm: null pointer argument");
+    if (a->T <= 0 || a->N <= 0 || a->K <= 0 || (a->K % kBK) != 0)
+        return fail(B200_EINVAL, "b200_gemm: bad sizes T=%d N=%d K=%d (K must be a multiple of 64)", a->T, a->N, a->K);
+    if (a->n_tiles * kTileM < a->N)
+        return fail(B200_EINVAL, "b200_gemm: n_tiles=%d does not cover N=%d", a->n_tiles, a->N);
+    if ((a->ldx % 8) != 0 || (reinterpret_cast<uintptr_t>(a->x) & 15) != 0)
+        return fail(B200_EINVAL, "b200_gemm: x must be 16-byte aligned with ldx %% 8 == 0");
+    if (a->dual && a->epilogue != B200_EPI_SWIGLU)
+        return fail(B200_EINVAL, "b200_gemm: dual-packed weights require the SwiGLU epilogue");
+    if (!a->dual && a->epilogue == B200_EPI_SWIGLU)
+        return fail(B200_EINVAL, "b200_gemm: SwiGLU epilogue requires dual-packed weights");
+    const int bn = pick_token_tile(a->T);
+    const int t_tiles = (a->T + bn - 1) / bn;
+    if (a->norm_mode != B200_NORM_NONE) {
+        if (t_tiles != 1 || bn > 32)
+            return fail(B200_EINVAL, "b200_gemm: fused norm prologue supports T <= 32 (got %d)", a->T);
+        if (!a->norm_w) return fail(B200_EINVAL, "b200_gemm: norm_mode set without norm_w");
+    }
+    GemmParams p;
+    p.w = static_cast<const uint8_t*>(a->w_packed);
+    p.x = static_cast<const uint16_t*>(a->x);
+    p.out = a->out;
+    p.residual = static_cast<const uint16_t*>(a->residual);
+    p.bias = static_cast<const uint16_t*>(a->bias);
+    p.norm_w = static_cast<const uint16_t*>(a->norm_w);
+    p.norm_b = static_cast<const uint16_t*>(a->norm_b);
+    p.scratch = a->scratch;
+    p.counters = a->counters;
+    p.T = a->T; p.N = a->N; p.K = a->K;
+    p.ldx = a->ldx; p.ldo = a->ldo; p.ldr = a->ldr;
+    p.n_tiles = a->n_tiles; p.t_tiles = t_tiles; p.kbpt = a->K / kBK;
+    p.Q = (long long)a->n_tiles * t_tiles * p.kbpt;
+    p.epilogue = a->epilogue; p.norm_mode = a->norm_mode; p.norm_eps = a->norm_eps;
+    p.is_bf16 = (a->dtype == B200_BF16) ? 1 : 0;
+    p.out_fp32 = a->out_fp32;
+
+    int grid = a->grid > 0 ? a->grid : sm_count_cached();
+    if (grid > sm_count_cached()) grid = sm_count_cached();
+    if ((long long)grid > p.Q) grid = (int)p.Q;
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    const bool pdl = a->pdl != 0;
+#define B200_GEMM_CASE(BN_)                                                        \
+    case BN_:                                                                      \
+        return a->dual ? launch_gemm<BN_, 1>(p, grid, pdl, stream)                 \
+                       : launch_gemm<BN_, 0>(p, grid, pdl, stream);
+    switch (bn) {
+        B200_GEMM_CASE(16)
+        B200_GEMM_CASE(32)
+        B200_GEMM_CASE(64)
+        B200_GEMM_CASE(128)
+        B200_GEMM_CASE(256)
+    }
+#undef B200_GEMM_CASE
+    return fail(B200_EINVAL, "b200_gemm: unsupported token tile %d", bn);
+}

@@ -1,0 +1,112 @@
+"""Python front-end of the swap-AB stream-K tcgen05 GEMM (csrc/gemm.cu).
+
+``linear(x, w)`` computes ``epilogue(norm(x) @ W^T)`` for a packed weight with
+optional fused RMSNorm/LayerNorm prologue (decode-size inputs), bias,
+GELU-tanh / SwiGLU activation and residual add.  Replaces the reference's
+separate torch ops (petals/llama/block.py:88-90,151,208-238).
+"""
+from __future__ import annotations
+
+import ctypes
+from dataclasses import dataclass
+from typing import Optional
+
+import torch
+
+from . import native
+from .packing import PackedWeight
+
+EPI_NONE, EPI_GELU_TANH, EPI_SWIGLU = 0, 1, 2
+NORM_NONE, NORM_RMS, NORM_LAYER = 0, 1, 2
+MAX_FUSED_NORM_TOKENS = 32
+
+
+def dtype_code(dt: torch.dtype) -> int:
+    if dt == torch.float16:
+        return 0
+    if dt == torch.bfloat16:
+        return 1
+    raise ValueError(f"unsupported activation dtype {dt}")
+
+
+@dataclass
+class GemmWorkspace:
+    """Stream-K partial-tile scratch + per-tile arrival counters (kept zero)."""
+
+    scratch: torch.Tensor
+    counters: torch.Tensor
+    max_tokens: int
+
+    @classmethod
+    def create(cls, device, max_tokens: int = 16, max_units: int = 1 << 16) -> "GemmWorkspace":
+        with torch.cuda.device(device):
+            nbytes = native.lib().b200_gemm_scratch_bytes(int(max_tokens))
+        scratch = torch.empty(nbytes // 4, dtype=torch.float32, device=device)
+        counters = torch.zeros(max_units, dtype=torch.int32, device=device)
+        return cls(scratch, counters, max_tokens)
+
+
+_default_ws: dict = {}
+
+
+def default_workspace(device, tokens: int) -> GemmWorkspace:
+    key = (torch.device(device).index or 0)
+    ws = _default_ws.get(key)
+    if ws is None or ws.max_tokens < tokens:
+        ws = GemmWorkspace.create(device, max(tokens, 16))
+        _default_ws[key] = ws
+    return ws
+
+
+def linear(
+    x: torch.Tensor,
+    w: PackedWeight,
+    *,
+    out: Optional[torch.Tensor] = None,
+    residual: Optional[torch.Tensor] = None,
+    epilogue: int = EPI_NONE,
+    norm_mode: int = NORM_NONE,
+    norm_w: Optional[torch.Tensor] = None,
+    norm_b: Optional[torch.Tensor] = None,
+    norm_eps: float = 1e-5,
+    out_fp32: bool = False,
+    workspace: Optional[GemmWorkspace] = None,
+    pdl: bool = False,
+    grid: int = 0,
+) -> torch.Tensor:
+    """x: [T, K] (16-bit, last dim contiguous) -> [T, N]."""
+    assert x.dim() == 2 and x.stride(1) == 1 and x.is_cuda
+    T, K = x.shape
+    assert K == w.k_padded, f"activation width {K} != packed K {w.k_padded}"
+    if w.dual:
+        epilogue = EPI_SWIGLU
+    if out is None:
+        out = torch.empty((T, w.n), dtype=torch.float32 if out_fp32 else x.dtype, device=x.device)
+    ws = workspace or default_workspace(x.device, T)
+    assert w.n_tiles * ((T + 255) // 256 + 1) <= ws.counters.numel() or T <= 256
+    a = native.GemmArgs()
+    a.w_packed = w.data.data_ptr()
+    a.x = x.data_ptr()
+    a.out = out.data_ptr()
+    a.residual = residual.data_ptr() if residual is not None else None
+    a.bias = w.bias.data_ptr() if w.bias is not None else None
+    a.norm_w = norm_w.data_ptr() if norm_w is not None else None
+    a.norm_b = norm_b.data_ptr() if norm_b is not None else None
+    a.scratch = ws.scratch.data_ptr()
+    a.counters = ws.counters.data_ptr()
+    a.T, a.N, a.K = T, w.n, K
+    a.ldx = x.stride(0)
+    a.ldo = out.stride(0)
+    a.ldr = residual.stride(0) if residual is not None else 0
+    a.n_tiles = w.n_tiles
+    a.dual = 1 if w.dual else 0
+    a.epilogue = epilogue
+    a.norm_mode = norm_mode
+    a.norm_eps = norm_eps
+    a.dtype = dtype_code(x.dtype)
+    a.out_fp32 = 1 if out_fp32 else 0
+    a.grid = grid
+    a.pdl = 1 if pdl else 0
+    rc = native.lib().b200_gemm(ctypes.byref(a), native.current_stream_ptr())
+    native.check(rc, "b200_gemm")
+    return out

@@ -1,0 +1,97 @@
+"""Weight layout for the swap-AB tcgen05 GEMM (csrc/gemm.cu).
+
+A torch ``Linear`` weight ``W[N, K]`` (row = output feature, K contiguous) is
+re-tiled once at load time into the exact shared-memory image the UMMA
+descriptor expects, so that a k-block of a tile is ONE contiguous 16 KiB run in
+HBM and can be fetched with a single ``cp.async.bulk``:
+
+    packed[n_tile][k_block][a][128 rows][8 chunks][8 elems]      (16-bit elems)
+
+* ``n_tile``  — 128 output rows, ``k_block`` — 64 input features (128 bytes);
+* inside a block, row ``r`` keeps its 8 sixteen-byte chunks at position
+  ``chunk ^ (r % 8)`` — the hardware 128-byte swizzle (bank-conflict-free for
+  both the bulk copy and the tensor core reads);
+* ``a`` is 1, or 2 when two matrices are interleaved per tile (``gate``/``up``
+  for the fused SwiGLU epilogue: both accumulators of an output feature end up
+  in the same thread).
+
+N is zero-padded to a multiple of 128 and K to a multiple of 64.
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass
+from typing import Optional
+
+import torch
+
+TILE_N = 128
+BLOCK_K = 64
+
+
+@dataclass
+class PackedWeight:
+    data: torch.Tensor          # flat 16-bit tensor in the layout above
+    n: int                      # logical output features
+    k: int                      # logical input features
+    k_padded: int
+    n_tiles: int
+    dual: bool
+    bias: Optional[torch.Tensor] = None
+
+    @property
+    def kb_per_tile(self) -> int:
+        return self.k_padded // BLOCK_K
+
+    @property
+    def nbytes(self) -> int:
+        return self.data.numel() * self.data.element_size()
+
+
+def _tile(w: torch.Tensor) -> torch.Tensor:
+    """[N, K] -> [n_tiles, kb, 128, 64] swizzled; pads N and K."""
+    n, k = w.shape
+    n_pad = (n + TILE_N - 1) // TILE_N * TILE_N
+    k_pad = (k + BLOCK_K - 1) // BLOCK_K * BLOCK_K
+    if n_pad != n or k_pad != k:
+        wp = w.new_zeros((n_pad, k_pad))
+        wp[:n, :k] = w
+        w = wp
+    nt, kb = n_pad // TILE_N, k_pad // BLOCK_K
+    blk = w.view(nt, TILE_N, kb, 8, 8).permute(0, 2, 1, 3, 4)  # [nt, kb, 128, 8 chunks, 8]
+    r = torch.arange(TILE_N, device=w.device)
+    c = torch.arange(8, device=w.device)
+    src_chunk = c[None, :] ^ (r[:, None] % 8)                   # position p holds chunk p ^ (r%8)
+    blk = blk[:, :, r[:, None], src_chunk, :]                  # [nt, kb, 128, 8, 8]
+    return blk.contiguous().view(nt, kb, TILE_N, BLOCK_K)
+
+
+def pack_weight(w: torch.Tensor, bias: Optional[torch.Tensor] = None) -> PackedWeight:
+    """Pack one ``[N, K]`` weight (fp16/bf16)."""
+    assert w.dim() == 2 and w.dtype in (torch.float16, torch.bfloat16)
+    n, k = w.shape
+    t = _tile(w)
+    return PackedWeight(t.reshape(-1), n, k, t.shape[1] * BLOCK_K, t.shape[0], False,
+                        None if bias is None else bias.contiguous())
+
+
+def pack_dual(w_gate: torch.Tensor, w_up: torch.Tensor) -> PackedWeight:
+    """Interleave two same-shaped weights tile by tile (SwiGLU gate/up)."""
+    assert w_gate.shape == w_up.shape and w_gate.dtype == w_up.dtype
+    n, k = w_gate.shape
+    g, u = _tile(w_gate), _tile(w_up)
+    t = torch.stack((g, u), dim=2)                             # [nt, kb, 2, 128, 64]
+    return PackedWeight(t.contiguous().reshape(-1), n, k, g.shape[1] * BLOCK_K, g.shape[0], True)
+
+
+def unpack_weight(p: PackedWeight) -> torch.Tensor:
+    """Inverse of :func:`pack_weight` / :func:`pack_dual` (tests, re-sharding)."""
+    a = 2 if p.dual else 1
+    kb = p.kb_per_tile
+    t = p.data.view(p.n_tiles, kb, a, TILE_N, 8, 8)
+    r = torch.arange(TILE_N, device=t.device)
+    c = torch.arange(8, device=t.device)
+    src = c[None, :] ^ (r[:, None] % 8)
+    t = t[:, :, :, r[:, None], src, :]                         # swizzle is an involution
+    t = t.reshape(p.n_tiles, kb, a, TILE_N, BLOCK_K).permute(2, 0, 3, 1, 4)
+    full = t.reshape(a, p.n_tiles * TILE_N, kb * BLOCK_K)[:, : p.n, : p.k]
+    return full if p.dual else full[0]

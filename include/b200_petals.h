@@ -1,0 +1,90 @@
+/*
+ * b200_petals.h — C ABI of the sm_100a kernel library behind the pipeline stages.
+ *
+ * All entry points take raw device pointers and a CUDA stream (cudaStream_t cast
+ * to void*), launch asynchronously on that stream, allocate nothing unless the
+ * comment says so, and return 0 on success or a negative B200_E* code (the text
+ * of the last error is available from b200_last_error()).
+ *
+ * Reference citations (jwkim-skku Mini-Petals, paths relative to the reference
+ * root) name the torch op sequence each kernel replaces; the reference itself
+ * contains no native code.
+ */
+#ifndef B200_PETALS_H_
+#define B200_PETALS_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200_OK 0
+#define B200_EINVAL -1
+#define B200_ECUDA -2
+#define B200_ELIMIT -3
+
+/* element types of activations / weights */
+#define B200_F16 0
+#define B200_BF16 1
+
+const char* b200_last_error(void);
+int b200_version(void);
+/* Number of SMs of the current device (grid sizing for persistent kernels). */
+int b200_sm_count(void);
+
+/* ------------------------------------------------------------------ GEMM --
+ * out[T,N] = epilogue( norm(x)[T,K] . W[N,K]^T )      (W = torch Linear weight)
+ *
+ * Swap-AB tcgen05 kernel: the weight is the 128-row M operand, streamed once
+ * from HBM as pre-tiled, pre-swizzled 16 KiB blocks with bulk async copies;
+ * tokens are the N operand (16..256 per tile), accumulators live in TMEM.
+ * Work is split stream-K style over a persistent grid so that every SM streams
+ * the same number of weight bytes whatever N and K are; partial tiles meet in
+ * `scratch` and are summed in a fixed order (bit-reproducible).
+ *
+ * Replaces q/k/v_proj, o_proj, gate/up/down_proj, lm_head and their
+ * surrounding norm / activation / residual ops:
+ * petals/llama/block.py:88-90,151,208-213,227-238; src/llama_partition.py:466-470.
+ */
+#define B200_EPI_NONE 0
+#define B200_EPI_GELU_TANH 1 /* GPT-2 c_fc */
+#define B200_EPI_SWIGLU 2    /* requires dual-packed gate/up weight */
+
+#define B200_NORM_NONE 0
+#define B200_NORM_RMS 1
+#define B200_NORM_LAYER 2
+
+typedef struct b200_gemm_args {
+    const void* w_packed; /* b200_pack layout, see ops/packing.py */
+    const void* x;        /* [T, K] 16-bit, row stride ldx elements */
+    void* out;            /* [T, N] 16-bit (or fp32 when out_fp32), row stride ldo */
+    const void* residual; /* [T, N] 16-bit added after the epilogue, or NULL */
+    const void* bias;     /* [N] 16-bit, or NULL */
+    const void* norm_w;   /* [K] 16-bit norm gain (norm_mode != 0) */
+    const void* norm_b;   /* [K] 16-bit LayerNorm beta, or NULL */
+    float* scratch;       /* >= b200_gemm_scratch_bytes() bytes */
+    int32_t* counters;    /* >= n_tiles * t_tiles ints, all zero; left all zero */
+    int32_t T, N, K;      /* logical sizes; K is the packed (64-padded) K */
+    int32_t ldx, ldo, ldr;
+    int32_t n_tiles;      /* packed 128-row tiles (dual: pairs) */
+    int32_t dual;         /* 1 = gate/up interleaved per tile */
+    int32_t epilogue;
+    int32_t norm_mode;
+    float norm_eps;
+    int32_t dtype;        /* B200_F16 / B200_BF16 */
+    int32_t out_fp32;
+    int32_t grid;         /* 0 = one CTA per SM */
+    int32_t pdl;          /* 1 = launch with programmatic stream serialization */
+} b200_gemm_args;
+
+int b200_gemm(const b200_gemm_args* args, void* stream);
+/* Upper bound of the scratch needed by any b200_gemm call with T <= max_tokens. */
+int64_t b200_gemm_scratch_bytes(int32_t max_tokens);
+/* Token-tile width the kernel will pick for T tokens (16,32,64,128,256). */
+int32_t b200_gemm_token_tile(int32_t T, int32_t dual);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200_PETALS_H_ */

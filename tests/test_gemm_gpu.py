@@ -1,0 +1,128 @@
+"""tcgen05 stream-K GEMM vs a plain torch fp32 restatement of the same op."""
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+def _ref(x, w, bias=None, residual=None, epi="none", norm=None, up=None, dtype=torch.bfloat16):
+    xf = x.float()
+    if norm is not None:
+        mode, g, b, eps = norm
+        if mode == "rms":
+            var = xf.pow(2).mean(-1, keepdim=True)
+            xn = (xf * torch.rsqrt(var + eps)).to(dtype).float()
+            xf = (g.float() * xn).to(dtype).float()
+        else:
+            xf = torch.nn.functional.layer_norm(xf, (xf.shape[-1],), g.float(), b.float(), eps).to(dtype).float()
+    y = xf @ w.float().t()
+    if bias is not None:
+        y = y + bias.float()
+    if epi == "gelu":
+        y = torch.nn.functional.gelu(y.to(dtype).float(), approximate="tanh")
+    if epi == "swiglu":
+        u = (xf @ up.float().t()).to(dtype).float()
+        g_ = y.to(dtype).float()
+        y = torch.nn.functional.silu(g_).to(dtype).float() * u
+    if residual is not None:
+        y = y.to(dtype).float() + residual.float()
+    return y
+
+
+def _close(out, ref, dtype):
+    tol = 2e-2 if dtype == torch.bfloat16 else 4e-3
+    err = (out.float() - ref).abs().max().item()
+    scale = ref.abs().max().item() + 1e-6
+    assert err / scale < tol, f"rel err {err/scale:.4g} (abs {err:.4g}, scale {scale:.4g})"
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+@pytest.mark.parametrize("T,N,K", [(1, 256, 128), (1, 4096, 4096), (5, 1000, 512), (16, 512, 11008),
+                                   (20, 384, 256), (48, 256, 512), (100, 640, 1024), (300, 512, 768),
+                                   (1024, 1024, 512)])
+def test_gemm_plain(T, N, K, dtype):
+    from petals_b200.ops import gemm, packing
+
+    torch.manual_seed(T * 7 + N)
+    dev = "cuda"
+    x = (torch.randn(T, K, device=dev) * 0.5).to(dtype)
+    w = (torch.randn(N, K, device=dev) / K ** 0.5).to(dtype)
+    pw = packing.pack_weight(w)
+    out = gemm.linear(x, pw)
+    torch.cuda.synchronize()
+    _close(out, _ref(x, w, dtype=dtype), dtype)
+    # second launch re-uses the self-cleaning counters
+    out2 = gemm.linear(x, pw)
+    torch.cuda.synchronize()
+    assert torch.equal(out, out2), "stream-K result must be bit-reproducible"
+
+
+@pytest.mark.parametrize("T", [1, 7, 16, 130])
+def test_gemm_bias_residual_gelu(T):
+    from petals_b200.ops import gemm, packing
+
+    dtype = torch.float16
+    torch.manual_seed(3)
+    N, K = 3072, 768
+    x = (torch.randn(T, K, device="cuda") * 0.5).to(dtype)
+    w = (torch.randn(N, K, device="cuda") / K ** 0.5).to(dtype)
+    b = (torch.randn(N, device="cuda") * 0.1).to(dtype)
+    r = torch.randn(T, N, device="cuda").to(dtype)
+    pw = packing.pack_weight(w, b)
+    out = gemm.linear(x, pw, epilogue=gemm.EPI_GELU_TANH)
+    _close(out, _ref(x, w, bias=b, epi="gelu", dtype=dtype), dtype)
+    out = gemm.linear(x, pw, residual=r)
+    _close(out, _ref(x, w, bias=b, residual=r, dtype=dtype), dtype)
+
+
+@pytest.mark.parametrize("T", [1, 3, 16, 64, 200])
+def test_gemm_swiglu_dual(T):
+    from petals_b200.ops import gemm, packing
+
+    dtype = torch.bfloat16
+    torch.manual_seed(5)
+    N, K = 1408, 1024
+    x = (torch.randn(T, K, device="cuda") * 0.5).to(dtype)
+    wg = (torch.randn(N, K, device="cuda") / K ** 0.5).to(dtype)
+    wu = (torch.randn(N, K, device="cuda") / K ** 0.5).to(dtype)
+    pw = packing.pack_dual(wg, wu)
+    out = gemm.linear(x, pw)
+    _close(out, _ref(x, wg, epi="swiglu", up=wu, dtype=dtype), dtype)
+
+
+@pytest.mark.parametrize("mode", ["rms", "layer"])
+@pytest.mark.parametrize("T", [1, 4, 16, 29])
+def test_gemm_fused_norm(mode, T):
+    from petals_b200.ops import gemm, packing
+
+    dtype = torch.bfloat16
+    torch.manual_seed(11)
+    N, K = 768, 1024
+    x = (torch.randn(T, K, device="cuda") * 2 + 0.3).to(dtype)
+    w = (torch.randn(N, K, device="cuda") / K ** 0.5).to(dtype)
+    g = (1 + 0.1 * torch.randn(K, device="cuda")).to(dtype)
+    b = (0.1 * torch.randn(K, device="cuda")).to(dtype)
+    pw = packing.pack_weight(w)
+    if mode == "rms":
+        out = gemm.linear(x, pw, norm_mode=gemm.NORM_RMS, norm_w=g, norm_eps=1e-5)
+        ref = _ref(x, w, norm=("rms", g, None, 1e-5), dtype=dtype)
+    else:
+        out = gemm.linear(x, pw, norm_mode=gemm.NORM_LAYER, norm_w=g, norm_b=b, norm_eps=1e-5)
+        ref = _ref(x, w, norm=("layer", g, b, 1e-5), dtype=dtype)
+    _close(out, ref, dtype)
+
+
+def test_gemm_fp32_logits_and_small_grid():
+    from petals_b200.ops import gemm, packing
+
+    dtype = torch.bfloat16
+    torch.manual_seed(13)
+    N, K, T = 50257, 768, 2
+    x = torch.randn(T, K, device="cuda").to(dtype)
+    w = (torch.randn(N, K, device="cuda") / K ** 0.5).to(dtype)
+    pw = packing.pack_weight(w)
+    out = gemm.linear(x, pw, out_fp32=True)
+    assert out.dtype == torch.float32 and out.shape == (T, N)
+    _close(out, _ref(x, w, dtype=dtype), dtype)
+    out_small = gemm.linear(x, pw, out_fp32=True, grid=7)
+    _close(out_small, _ref(x, w, dtype=dtype), dtype)
