@@ -23,15 +23,24 @@ constexpr int kEpiThreads = 128;
 template <int BN, int DUAL>
 struct GemmCfg {
     static constexpr int kAPer = DUAL ? 2 : 1;
-    static constexpr int kStageA = kABytes * kAPer;
-    static constexpr int kStageB = BN * 128;
-    // ring depths (see DESIGN.md "GEMM shared-memory budget")
-    static constexpr int kSA = (BN == 16) ? (DUAL ? 3 : 6) : (BN == 256) ? (DUAL ? 3 : 6) : (DUAL ? 4 : 8);
-    static constexpr int kSB = (BN == 16) ? 6 : (BN == 32) ? 8 : (BN == 64) ? 6 : (BN == 128) ? 4 : 3;
-    static constexpr int kGroup = (BN == 16) ? 4 : (BN == 32) ? 2 : 1;  // k-blocks per producer batch
-    static constexpr int kTmemColsRaw = BN * kAPer;
+    static constexpr int kBlockA = kABytes * kAPer;       // weight bytes of one k-block
+    // One weight-ring stage = one 32 KiB bulk copy.  The single-thread loader and
+    // MMA loops pay ~100+ ns of barrier latency per stage, so stages must be big.
+    static constexpr int kKps = DUAL ? 1 : 2;              // k-blocks per weight stage
+    static constexpr int kStageA = kBlockA * kKps;         // 32768
+    static constexpr int kSA = (BN <= 16) ? 6 : (BN == 256) ? 3 : 4;
+    static constexpr int kGroup = (BN == 16) ? 4 : (BN == 32) ? 2 : 1;  // k-blocks per activation stage
+    static constexpr int kSubB = BN * 128;                 // one k-block of activations
+    static constexpr int kStageB = kSubB * kGroup;
+    static constexpr int kSB = (BN == 16) ? 3 : (BN == 32) ? 4 : (BN == 64) ? 6 : (BN == 128) ? 4 : 3;
+    static constexpr bool kPrefetch = BN <= 32;            // register double-buffering of the next B stage
+    // Back-to-back tcgen05.mma into ONE accumulator serialise on the tensor-pipe latency
+    // (~180 cycles each when N is tiny), so narrow tiles rotate the four k-steps of a
+    // k-block over independent accumulators that the epilogue adds up.
+    static constexpr int kNAcc = (BN <= 32) ? 4 : (BN == 64) ? 2 : 1;
+    static constexpr int kTmemColsRaw = BN * kAPer * kNAcc;
     static constexpr int kTmemCols = kTmemColsRaw <= 32 ? 32 : kTmemColsRaw <= 64 ? 64 : kTmemColsRaw <= 128 ? 128 : kTmemColsRaw <= 256 ? 256 : 512;
-    static constexpr int kMinBlocks = (BN == 16) ? 2 : 1;
+    static constexpr int kMinBlocks = 1;
     static constexpr size_t kSmemData = (size_t)kSA * kStageA + (size_t)kSB * kStageB;
     static constexpr size_t kSmemBytes = kSmemData + 1024 /*align*/ + 1024 /*barriers, stats*/;
 };
@@ -53,6 +62,7 @@ struct GemmParams {
     int epilogue, norm_mode;
     float norm_eps;
     int is_bf16, out_fp32;
+    int debug;  // experiment switches (scripts/exp_*.py): 1 = no MMA issue, 2 = no B stage waits
 };
 
 __device__ __forceinline__ long long range_begin(const GemmParams& p, int c) {
@@ -139,6 +149,10 @@ gemm_streamk_kernel(const GemmParams p) {
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    // Let the next kernel in the stream get resident now: its weight loader does not
+    // depend on our output and can fill its ring while we finish (it still waits for
+    // our completion before touching activations).
+    pdl_launch_dependents();
 
     const long long q_begin = range_begin(p, cta);
     const long long q_end = range_begin(p, cta + 1);
@@ -147,60 +161,87 @@ gemm_streamk_kernel(const GemmParams p) {
         // ------------------------------------------------ weight loader
         if (lane == 0) {
             // Weights never depend on the previous kernel: start streaming at once.
-            const uint64_t policy = l2_policy_evict_first();
-            uint32_t it = 0;
-            for (long long q = q_begin; q < q_end; ++q, ++it) {
-                const int u = (int)(q / p.kbpt);
-                const int kb = (int)(q - (long long)u * p.kbpt);
-                const int n_tile = u / p.t_tiles;
-                const int s = it % SA;
-                const uint32_t ph = (it / SA) & 1;
+            const uint64_t policy = (p.t_tiles == 1) ? l2_policy_evict_first() : l2_policy_evict_last();
+            // (u, kb) walk the global k-block index without divisions in the loop.
+            int u = (int)(q_begin / p.kbpt);
+            int kb = (int)(q_begin - (long long)u * p.kbpt);
+            int n_tile = u / p.t_tiles, t_tile = u - n_tile * p.t_tiles;
+            long long left = q_end - q_begin;
+            int s = 0;
+            uint32_t ph = 0;
+            const uint8_t* tile_base = p.w + (size_t)n_tile * p.kbpt * Cfg::kBlockA;
+            while (left > 0) {
+                int n = p.kbpt - kb;                          // stay inside this tile ...
+                if ((long long)n > left) n = (int)left;       // ... and inside our range
+                if (n > Cfg::kKps) n = Cfg::kKps;
                 mbar_wait(&a_empty[s], ph ^ 1);
-                mbar_arrive_expect_tx(&a_full[s], Cfg::kStageA);
-                const uint8_t* src = p.w + ((size_t)n_tile * p.kbpt + kb) * Cfg::kStageA;
-                if (p.t_tiles == 1)
-                    bulk_g2s_hint(smem_a + (size_t)s * Cfg::kStageA, src, Cfg::kStageA, &a_full[s], policy);
-                else
-                    bulk_g2s(smem_a + (size_t)s * Cfg::kStageA, src, Cfg::kStageA, &a_full[s]);
+                const uint32_t bytes = (uint32_t)n * Cfg::kBlockA;
+                mbar_arrive_expect_tx(&a_full[s], bytes);
+                bulk_g2s_hint(smem_a + (size_t)s * Cfg::kStageA, tile_base + (size_t)kb * Cfg::kBlockA, bytes,
+                              &a_full[s], policy);
+                if (++s == SA) { s = 0; ph ^= 1; }
+                left -= n;
+                kb += n;
+                if (kb == p.kbpt) {
+                    kb = 0;
+                    if (++t_tile == p.t_tiles) { t_tile = 0; ++n_tile; tile_base += (size_t)p.kbpt * Cfg::kBlockA; }
+                }
             }
         }
     } else if (warp == 1) {
         // ------------------------------------------------ MMA issuer
         if (lane == 0) {
             const uint32_t idesc = umma_idesc(kTileM, BN, p.is_bf16, p.is_bf16, 0, 0);
-            uint32_t it = 0, part = 0;
-            long long q = q_begin;
-            while (q < q_end) {
-                const int u = (int)(q / p.kbpt);
-                const int kb0 = (int)(q - (long long)u * p.kbpt);
-                const long long rem = q_end - q;
-                const int kb1 = (rem < (long long)(p.kbpt - kb0)) ? kb0 + (int)rem : p.kbpt;
-                mbar_wait(acc_empty, (part & 1) ^ 1);
+            int u = (int)(q_begin / p.kbpt);
+            int kb0 = (int)(q_begin - (long long)u * p.kbpt);
+            long long left = q_end - q_begin;
+            int sa = 0, sb = 0;
+            uint32_t pha = 0, phb = 0, php = 0;
+            const uint32_t a_base = smem_u32(smem_a), b_base = smem_u32(smem_b);
+            while (left > 0) {
+                int nk = p.kbpt - kb0;
+                if ((long long)nk > left) nk = (int)left;      // k-blocks of this part
+                mbar_wait(acc_empty, php ^ 1);
                 tc_fence_after();
-                for (int kb = kb0; kb < kb1; ++kb, ++it) {
-                    const int sa = it % SA, sb = it % SB;
-                    mbar_wait(&b_full[sb], (it / SB) & 1);
-                    mbar_wait(&a_full[sa], (it / SA) & 1);
-                    tc_fence_after();
-                    const uint32_t a_addr = smem_u32(smem_a + (size_t)sa * Cfg::kStageA);
-                    const uint32_t b_addr = smem_u32(smem_b + (size_t)sb * Cfg::kStageB);
-                    const uint64_t bdesc = umma_desc_kmajor_sw128(b_addr, 1024);
+                uint32_t acc = 0;
+                int done = 0, bofs = 0;
+                while (done < nk) {
+                    int na = nk - done;
+                    if (na > Cfg::kKps) na = Cfg::kKps;
+                    mbar_wait(&a_full[sa], pha);
+                    for (int j = 0; j < na; ++j) {
+                        if (bofs == 0 && !(p.debug & 2)) mbar_wait(&b_full[sb], phb);
+                        tc_fence_after();
+                        const uint64_t bdesc = umma_desc_kmajor_sw128(b_base + sb * Cfg::kStageB + bofs * Cfg::kSubB, 1024);
+                        if (!(p.debug & 1)) {
 #pragma unroll
-                    for (int a = 0; a < APER; ++a) {
-                        const uint64_t adesc = umma_desc_kmajor_sw128(a_addr + a * kABytes, 1024);
+                            for (int a = 0; a < APER; ++a) {
+                                const uint64_t adesc = umma_desc_kmajor_sw128(
+                                    a_base + sa * Cfg::kStageA + j * Cfg::kBlockA + a * kABytes, 1024);
 #pragma unroll
-                        for (int k = 0; k < kBK / 16; ++k) {
-                            // +32 B per UMMA_K inside the 128 B swizzle row -> +2 in the address field
-                            umma_f16(tmem_base + a * BN, adesc + (uint64_t)(k * 2), bdesc + (uint64_t)(k * 2),
-                                     idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+                                for (int k = 0; k < kBK / 16; ++k) {
+                                    // +32 B per UMMA_K inside the 128 B swizzle row -> +2 in the address field
+                                    umma_f16(tmem_base + (a * Cfg::kNAcc + (k % Cfg::kNAcc)) * BN, adesc + (uint64_t)(k * 2),
+                                             bdesc + (uint64_t)(k * 2), idesc, (k >= Cfg::kNAcc) ? 1u : acc);
+                                }
+                            }
+                        }
+                        acc = 1;
+                        ++bofs;
+                        if (bofs == Cfg::kGroup || done + j + 1 == nk) {
+                            if (!(p.debug & 2)) umma_commit(&b_empty[sb]);
+                            bofs = 0;
+                            if (++sb == SB) { sb = 0; phb ^= 1; }
                         }
                     }
                     umma_commit(&a_empty[sa]);
-                    umma_commit(&b_empty[sb]);
+                    if (++sa == SA) { sa = 0; pha ^= 1; }
+                    done += na;
                 }
                 umma_commit(acc_full);
-                q += kb1 - kb0;
-                ++part;
+                php ^= 1;
+                left -= nk;
+                kb0 = 0;   // every later part starts at the beginning of a tile
             }
         }
         __syncwarp();
@@ -251,7 +292,8 @@ gemm_streamk_kernel(const GemmParams p) {
             named_bar_sync(1, kEpiThreads);
         }
 
-        uint32_t it = 0, part = 0;
+        uint32_t part = 0, phb = 0;
+        int sb = 0;
         long long q = q_begin;
         while (q < q_end) {
             const int u = (int)(q / p.kbpt);
@@ -261,74 +303,89 @@ gemm_streamk_kernel(const GemmParams p) {
             const int n_tile = u / p.t_tiles;
             const int t_tile = u - n_tile * p.t_tiles;
 
-            // ---- stage activations for k-blocks [kb0, kb1)
-            for (int kb = kb0; kb < kb1; kb += Cfg::kGroup) {
-                const int ng = (kb1 - kb < Cfg::kGroup) ? (kb1 - kb) : Cfg::kGroup;
-                uint4 v[Cfg::kGroup][BN / 16];
-                uint4 gw[Cfg::kGroup], gb[Cfg::kGroup];
+            // ---- stage activations for k-blocks [kb0, kb1), kGroup k-blocks per B stage
+            {
+                constexpr int G = Cfg::kGroup, NI = BN / 16;
+                uint4 cur[G][NI], cgw[G], cgb[G];
+                uint4 nxt[Cfg::kPrefetch ? G : 1][Cfg::kPrefetch ? NI : 1], ngw[Cfg::kPrefetch ? G : 1], ngb[Cfg::kPrefetch ? G : 1];
+                auto load_stage = [&](int kb, auto& v, auto& gw, auto& gb) {
 #pragma unroll
-                for (int g = 0; g < Cfg::kGroup; ++g) {
-                    if (g < ng) {
-                        const int kcol = (kb + g) * kBK + ch * 8;
+                    for (int g = 0; g < G; ++g) {
+                        if (kb + g < kb1) {
+                            const int kcol = (kb + g) * kBK + ch * 8;
 #pragma unroll
-                        for (int i = 0; i < BN / 16; ++i) {
-                            const int t = t_tile * BN + r0 + 16 * i;
-                            v[g][i] = (t < p.T) ? ld_cg_v4(p.x + (size_t)t * p.ldx + kcol) : make_uint4(0, 0, 0, 0);
-                        }
-                        if (p.norm_mode != B200_NORM_NONE) {
-                            gw[g] = ld_nc_v4(p.norm_w + kcol);
-                            gb[g] = p.norm_b ? ld_nc_v4(p.norm_b + kcol) : make_uint4(0, 0, 0, 0);
-                        }
-                    }
-                }
-#pragma unroll
-                for (int g = 0; g < Cfg::kGroup; ++g) {
-                    if (g < ng) {
-                        const uint32_t itg = it + g;
-                        const int sb = itg % SB;
-                        mbar_wait(&b_empty[sb], ((itg / SB) & 1) ^ 1);
-                        const uint32_t base = smem_u32(smem_b + (size_t)sb * Cfg::kStageB);
-#pragma unroll
-                        for (int i = 0; i < BN / 16; ++i) {
-                            const int r = r0 + 16 * i;
-                            uint4 val = v[g][i];
-                            if (p.norm_mode != B200_NORM_NONE) {
-                                const int t = t_tile * BN + r;
-                                if (t < p.T) {
-                                    const float mean = stat_mean[r], rstd = stat_rstd[r];
-                                    uint32_t xin[4] = {val.x, val.y, val.z, val.w};
-                                    const uint32_t win[4] = {gw[g].x, gw[g].y, gw[g].z, gw[g].w};
-                                    const uint32_t bin[4] = {gb[g].x, gb[g].y, gb[g].z, gb[g].w};
-#pragma unroll
-                                    for (int w = 0; w < 4; ++w) {
-                                        float x0 = h16_to_float((uint16_t)(xin[w] & 0xffff), p.is_bf16);
-                                        float x1 = h16_to_float((uint16_t)(xin[w] >> 16), p.is_bf16);
-                                        const float g0 = h16_to_float((uint16_t)(win[w] & 0xffff), p.is_bf16);
-                                        const float g1 = h16_to_float((uint16_t)(win[w] >> 16), p.is_bf16);
-                                        if (p.norm_mode == B200_NORM_RMS) {
-                                            // HF LlamaRMSNorm: weight * (x * rstd).to(dtype)
-                                            x0 = g0 * round16(x0 * rstd, p.is_bf16);
-                                            x1 = g1 * round16(x1 * rstd, p.is_bf16);
-                                        } else {
-                                            const float b0 = h16_to_float((uint16_t)(bin[w] & 0xffff), p.is_bf16);
-                                            const float b1 = h16_to_float((uint16_t)(bin[w] >> 16), p.is_bf16);
-                                            x0 = (x0 - mean) * rstd * g0 + b0;
-                                            x1 = (x1 - mean) * rstd * g1 + b1;
-                                        }
-                                        xin[w] = (uint32_t)float_to_h16(x0, p.is_bf16) |
-                                                 ((uint32_t)float_to_h16(x1, p.is_bf16) << 16);
-                                    }
-                                    val = make_uint4(xin[0], xin[1], xin[2], xin[3]);
-                                }
+                            for (int i = 0; i < NI; ++i) {
+                                const int t = t_tile * BN + r0 + 16 * i;
+                                v[g][i] = (t < p.T) ? ld_cg_v4(p.x + (size_t)t * p.ldx + kcol) : make_uint4(0, 0, 0, 0);
                             }
-                            st_shared_v4(base + r * 128 + ((ch ^ (r & 7)) << 4), val);
+                            if (p.norm_mode != B200_NORM_NONE) {
+                                gw[g] = ld_nc_v4(p.norm_w + kcol);
+                                gb[g] = p.norm_b ? ld_nc_v4(p.norm_b + kcol) : make_uint4(0, 0, 0, 0);
+                            }
                         }
-                        fence_proxy_async_smem();
-                        __syncwarp();
-                        if (lane == 0) mbar_arrive(&b_full[sb]);
+                    }
+                };
+                if (!(p.debug & 2)) load_stage(kb0, cur, cgw, cgb);
+                for (int kb = kb0; kb < kb1 && !(p.debug & 2); kb += G) {
+                    if (Cfg::kPrefetch && kb + G < kb1) load_stage(kb + G, nxt, ngw, ngb);
+                    mbar_wait(&b_empty[sb], phb ^ 1);
+#pragma unroll
+                    for (int g = 0; g < G; ++g) {
+                        if (kb + g < kb1) {
+                            const uint32_t base = smem_u32(smem_b + (size_t)sb * Cfg::kStageB + (size_t)g * Cfg::kSubB);
+#pragma unroll
+                            for (int i = 0; i < NI; ++i) {
+                                const int r = r0 + 16 * i;
+                                uint4 val = cur[g][i];
+                                if (p.norm_mode != B200_NORM_NONE) {
+                                    const int t = t_tile * BN + r;
+                                    if (t < p.T) {
+                                        const float mean = stat_mean[r], rstd = stat_rstd[r];
+                                        uint32_t xin[4] = {val.x, val.y, val.z, val.w};
+                                        const uint32_t win[4] = {cgw[g].x, cgw[g].y, cgw[g].z, cgw[g].w};
+                                        const uint32_t bin[4] = {cgb[g].x, cgb[g].y, cgb[g].z, cgb[g].w};
+#pragma unroll
+                                        for (int w = 0; w < 4; ++w) {
+                                            float x0 = h16_to_float((uint16_t)(xin[w] & 0xffff), p.is_bf16);
+                                            float x1 = h16_to_float((uint16_t)(xin[w] >> 16), p.is_bf16);
+                                            const float g0 = h16_to_float((uint16_t)(win[w] & 0xffff), p.is_bf16);
+                                            const float g1 = h16_to_float((uint16_t)(win[w] >> 16), p.is_bf16);
+                                            if (p.norm_mode == B200_NORM_RMS) {
+                                                // HF LlamaRMSNorm: weight * (x * rstd).to(dtype)
+                                                x0 = g0 * round16(x0 * rstd, p.is_bf16);
+                                                x1 = g1 * round16(x1 * rstd, p.is_bf16);
+                                            } else {
+                                                const float b0 = h16_to_float((uint16_t)(bin[w] & 0xffff), p.is_bf16);
+                                                const float b1 = h16_to_float((uint16_t)(bin[w] >> 16), p.is_bf16);
+                                                x0 = (x0 - mean) * rstd * g0 + b0;
+                                                x1 = (x1 - mean) * rstd * g1 + b1;
+                                            }
+                                            xin[w] = (uint32_t)float_to_h16(x0, p.is_bf16) |
+                                                     ((uint32_t)float_to_h16(x1, p.is_bf16) << 16);
+                                        }
+                                        val = make_uint4(xin[0], xin[1], xin[2], xin[3]);
+                                    }
+                                }
+                                st_shared_v4(base + r * 128 + ((ch ^ (r & 7)) << 4), val);
+                            }
+                        }
+                    }
+                    fence_proxy_async_smem();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(&b_full[sb]);
+                    if (++sb == SB) { sb = 0; phb ^= 1; }
+                    if (Cfg::kPrefetch) {
+#pragma unroll
+                        for (int g = 0; g < G; ++g) {
+#pragma unroll
+                            for (int i = 0; i < NI; ++i) cur[g][i] = nxt[g][i];
+                            cgw[g] = ngw[g];
+                            cgb[g] = ngb[g];
+                        }
+                    } else if (kb + G < kb1) {
+                        load_stage(kb + G, cur, cgw, cgb);
                     }
                 }
-                it += ng;
             }
 
             // ---- drain the accumulator of this part
@@ -337,26 +394,35 @@ gemm_streamk_kernel(const GemmParams p) {
             float* my_partial = p.scratch + ((size_t)cta * 2 + slot) * (size_t)(APER * BN * kTileM);
             mbar_wait(acc_full, part & 1);
             tc_fence_after();
+            const int t_live = min(BN, p.T - t_tile * BN);  // token columns that exist in this tile
 #pragma unroll 1
-            for (int c = 0; c < BN / 16; ++c) {
+            for (int c = 0; c * 16 < t_live; ++c) {
+                const int ncol = min(16, t_live - c * 16);
                 uint32_t rg[16], ru[16];
                 const uint32_t taddr = tmem_base + ((uint32_t)(lg * 32) << 16) + c * 16;
-                tmem_ld16(taddr, rg);
-                if (DUAL) tmem_ld16(taddr + BN, ru);
-                tmem_ld_wait();
                 float vg[16], vu[16];
 #pragma unroll
-                for (int j = 0; j < 16; ++j) {
-                    vg[j] = __uint_as_float(rg[j]);
-                    vu[j] = DUAL ? __uint_as_float(ru[j]) : 0.f;
+                for (int j = 0; j < 16; ++j) { vg[j] = 0.f; vu[j] = 0.f; }
+#pragma unroll
+                for (int ac = 0; ac < Cfg::kNAcc; ++ac) {
+                    tmem_ld16(taddr + ac * BN, rg);
+                    if (DUAL) tmem_ld16(taddr + (Cfg::kNAcc + ac) * BN, ru);
+                    tmem_ld_wait();
+#pragma unroll
+                    for (int j = 0; j < 16; ++j) {
+                        vg[j] += __uint_as_float(rg[j]);
+                        if (DUAL) vu[j] += __uint_as_float(ru[j]);
+                    }
                 }
                 if (full_tile) {
                     epilogue_store_chunk<BN, DUAL>(p, n_tile, t_tile, row, c, vg, vu);
                 } else {
 #pragma unroll
                     for (int j = 0; j < 16; ++j) {
-                        my_partial[(size_t)(c * 16 + j) * kTileM + row] = vg[j];
-                        if (DUAL) my_partial[(size_t)(BN + c * 16 + j) * kTileM + row] = vu[j];
+                        if (j < ncol) {
+                            my_partial[(size_t)(c * 16 + j) * kTileM + row] = vg[j];
+                            if (DUAL) my_partial[(size_t)(BN + c * 16 + j) * kTileM + row] = vu[j];
+                        }
                     }
                 }
             }
@@ -381,10 +447,12 @@ gemm_streamk_kernel(const GemmParams p) {
                     while (c_first + 1 < (int)gridDim.x && range_begin(p, c_first + 1) <= t_lo) ++c_first;
                     while (c_first > 0 && range_begin(p, c_first) > t_lo) --c_first;
 #pragma unroll 1
-                    for (int c = 0; c < BN / 16; ++c) {
+                    for (int c = 0; c * 16 < t_live; ++c) {
+                        const int ncol = min(16, t_live - c * 16);
                         float vg[16], vu[16];
 #pragma unroll
                         for (int j = 0; j < 16; ++j) { vg[j] = 0.f; vu[j] = 0.f; }
+#pragma unroll 4
                         for (int cc = c_first; cc < (int)gridDim.x; ++cc) {
                             const long long rb = range_begin(p, cc), re = range_begin(p, cc + 1);
                             if (rb >= t_hi) break;
@@ -393,8 +461,10 @@ gemm_streamk_kernel(const GemmParams p) {
                             const float* src = p.scratch + ((size_t)cc * 2 + cslot) * (size_t)(APER * BN * kTileM);
 #pragma unroll
                             for (int j = 0; j < 16; ++j) {
-                                vg[j] += __ldcg(src + (size_t)(c * 16 + j) * kTileM + row);
-                                if (DUAL) vu[j] += __ldcg(src + (size_t)(BN + c * 16 + j) * kTileM + row);
+                                if (j < ncol) {
+                                    vg[j] += __ldcg(src + (size_t)(c * 16 + j) * kTileM + row);
+                                    if (DUAL) vu[j] += __ldcg(src + (size_t)(BN + c * 16 + j) * kTileM + row);
+                                }
                             }
                         }
                         epilogue_store_chunk<BN, DUAL>(p, n_tile, t_tile, row, c, vg, vu);
@@ -407,7 +477,6 @@ gemm_streamk_kernel(const GemmParams p) {
         }
     }
 
-    pdl_launch_dependents();
     tc_fence_before();
     __syncthreads();
     if (warp == 1) tmem_dealloc<Cfg::kTmemCols>(tmem_base);
@@ -491,6 +560,7 @@ extern "C" int b200_gemm(const b200_gemm_args* a, void* stream_) {
     p.epilogue = a->epilogue; p.norm_mode = a->norm_mode; p.norm_eps = a->norm_eps;
     p.is_bf16 = (a->dtype == B200_BF16) ? 1 : 0;
     p.out_fp32 = a->out_fp32;
+    p.debug = a->debug;
 
     int grid = a->grid > 0 ? a->grid : sm_count_cached();
     if (grid > sm_count_cached()) grid = sm_count_cached();

@@ -73,6 +73,7 @@ def linear(
     workspace: Optional[GemmWorkspace] = None,
     pdl: bool = False,
     grid: int = 0,
+    debug: int = 0,
 ) -> torch.Tensor:
     """x: [T, K] (16-bit, last dim contiguous) -> [T, N]."""
     assert x.dim() == 2 and x.stride(1) == 1 and x.is_cuda
@@ -107,6 +108,7 @@ def linear(
     a.out_fp32 = 1 if out_fp32 else 0
     a.grid = grid
     a.pdl = 1 if pdl else 0
+    a.debug = debug
     rc = native.lib().b200_gemm(ctypes.byref(a), native.current_stream_ptr())
     native.check(rc, "b200_gemm")
     return out

@@ -48,6 +48,7 @@ class GemmArgs(ctypes.Structure):
         ("out_fp32", ctypes.c_int32),
         ("grid", ctypes.c_int32),
         ("pdl", ctypes.c_int32),
+        ("debug", ctypes.c_int32),
     ]
 
 

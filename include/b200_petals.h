@@ -76,6 +76,7 @@ typedef struct b200_gemm_args {
     int32_t out_fp32;
     int32_t grid;         /* 0 = one CTA per SM */
     int32_t pdl;          /* 1 = launch with programmatic stream serialization */
+    int32_t debug;        /* 0 in production; experiment switches, see csrc/gemm.cu */
 } b200_gemm_args;
 
 int b200_gemm(const b200_gemm_args* args, void* stream);
