@@ -1,0 +1,486 @@
+// Session-KV attention kernels (see b200_petals.h):
+//   b200_attn_decode   RoPE + in-place KV append + split-KV (flash-decoding) attention,
+//                      one launch per layer for T independent sessions' new tokens.
+//   b200_rope_append   prefill/chunk: RoPE on q (in place) and k, k/v -> session cache.
+//   b200_attn_prefill  causal attention of a chunk against the session cache.
+// Decode attention is KV-bandwidth bound (one query per session), so it runs on the
+// CUDA cores with 16-byte loads; the tensor-core path is the prefill kernel's job.
+#include "common.h"
+#include "ptx.cuh"
+
+namespace b200 {
+
+struct AttnDecodeParams {
+    const uint16_t* __restrict__ qkv;
+    uint16_t* __restrict__ out;
+    const unsigned long long* __restrict__ kv_ptrs;  // [T][2]
+    const int* __restrict__ pos;                     // [T]
+    const float* __restrict__ inv_freq;              // [D/2] or null
+    float* __restrict__ scratch;                     // [T][n_heads][splits][D+2]
+    int* __restrict__ counters;                      // [T][n_kv]
+    int T, n_heads, n_kv, s_max, splits, ldqkv, ldo;
+    float scale;
+    int is_bf16;
+};
+
+constexpr int kAttnThreads = 128;
+constexpr int kMinRowsPerSplit = 64;
+
+__device__ __forceinline__ void unpack8(const uint4& v, float (&f)[8], int is_bf16) {
+    const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        f[2 * i] = h16_to_float((uint16_t)(w[i] & 0xffff), is_bf16);
+        f[2 * i + 1] = h16_to_float((uint16_t)(w[i] >> 16), is_bf16);
+    }
+}
+__device__ __forceinline__ uint4 pack8(const float (&f)[8], int is_bf16) {
+    uint32_t w[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+        w[i] = (uint32_t)float_to_h16(f[2 * i], is_bf16) | ((uint32_t)float_to_h16(f[2 * i + 1], is_bf16) << 16);
+    return make_uint4(w[0], w[1], w[2], w[3]);
+}
+
+// Rotates one head vector held as (lo = dims [c, c+8), hi = dims [c+D/2, c+D/2+8)).
+// HF convention: out = x*cos + rotate_half(x)*sin with cos/sin rounded to the model dtype.
+__device__ __forceinline__ void rope8(float (&lo)[8], float (&hi)[8], int c, int pos, const float* inv_freq,
+                                      int is_bf16) {
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        float sn, cs;
+        sincosf((float)pos * inv_freq[c + i], &sn, &cs);
+        cs = h16_to_float(float_to_h16(cs, is_bf16), is_bf16);
+        sn = h16_to_float(float_to_h16(sn, is_bf16), is_bf16);
+        const float a = lo[i], b = hi[i];
+        lo[i] = a * cs - b * sn;
+        hi[i] = b * cs + a * sn;
+    }
+}
+
+// One CTA = (token t, kv head g, split s).  LPR = D/8 lanes cooperate on one KV row.
+template <int D, int GROUP>
+__global__ void __launch_bounds__(kAttnThreads) attn_decode_kernel(const AttnDecodeParams p) {
+    constexpr int LPR = D / 8;          // lanes per row: 16 (D=128) or 8 (D=64)
+    constexpr int RPW = 32 / LPR;       // rows per warp per step: 2 or 4
+    constexpr int NW = kAttnThreads / 32;
+    __shared__ float s_q[GROUP][D];
+    __shared__ float s_m[NW][GROUP], s_l[NW][GROUP];
+    __shared__ float s_o[NW][GROUP][D];
+    __shared__ int s_last;
+
+    const int splits = p.splits;
+    int bid = blockIdx.x;
+    const int s = bid % splits; bid /= splits;
+    const int g = bid % p.n_kv;
+    const int t = bid / p.n_kv;
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+
+    pdl_wait_prior_grid();
+    pdl_launch_dependents();
+
+    const int pos = p.pos[t];
+    const int len = pos + 1;  // keys visible to the new token, itself included
+    int eff = (len + kMinRowsPerSplit - 1) / kMinRowsPerSplit;
+    if (eff > splits) eff = splits;
+    if (s >= eff) return;
+    const int chunk = (len + eff - 1) / eff;
+    const int r_begin = s * chunk;
+    const int r_end = min(len, r_begin + chunk);
+
+    uint16_t* kbase = reinterpret_cast<uint16_t*>(p.kv_ptrs[2 * t]) + (size_t)g * p.s_max * D;
+    uint16_t* vbase = reinterpret_cast<uint16_t*>(p.kv_ptrs[2 * t + 1]) + (size_t)g * p.s_max * D;
+    const uint16_t* row = p.qkv + (size_t)t * p.ldqkv;
+    const int q_off = g * GROUP * D;
+    const int k_off = p.n_heads * D + g * D;
+    const int v_off = (p.n_heads + p.n_kv) * D + g * D;
+
+    // ---- q (RoPE'd, pre-scaled) -> smem; new k/v -> cache (by the split that owns `pos`)
+    // D/2/8 threads per head vector, each owning dims [c, c+8) and [c+D/2, c+D/2+8).
+    constexpr int TPH = D / 16;
+    for (int item = tid; item < (GROUP + 1) * TPH; item += kAttnThreads) {
+        const int h = item / TPH, c = (item % TPH) * 8;
+        const bool is_k = (h == GROUP);
+        if (is_k && !(pos >= r_begin && pos < r_end)) continue;
+        const uint16_t* src = row + (is_k ? k_off : q_off + h * D);
+        float lo[8], hi[8];
+        unpack8(*reinterpret_cast<const uint4*>(src + c), lo, p.is_bf16);
+        unpack8(*reinterpret_cast<const uint4*>(src + c + D / 2), hi, p.is_bf16);
+        if (p.inv_freq) rope8(lo, hi, c, pos, p.inv_freq, p.is_bf16);
+        if (is_k) {
+            *reinterpret_cast<uint4*>(kbase + (size_t)pos * D + c) = pack8(lo, p.is_bf16);
+            *reinterpret_cast<uint4*>(kbase + (size_t)pos * D + c + D / 2) = pack8(hi, p.is_bf16);
+            // v is copied verbatim alongside
+            *reinterpret_cast<uint4*>(vbase + (size_t)pos * D + c) = *reinterpret_cast<const uint4*>(row + v_off + c);
+            *reinterpret_cast<uint4*>(vbase + (size_t)pos * D + c + D / 2) =
+                *reinterpret_cast<const uint4*>(row + v_off + c + D / 2);
+        } else {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                // round through the storage type like the unfused path (q is stored after RoPE)
+                s_q[h][c + i] = h16_to_float(float_to_h16(lo[i], p.is_bf16), p.is_bf16) * p.scale;
+                s_q[h][c + D / 2 + i] = h16_to_float(float_to_h16(hi[i], p.is_bf16), p.is_bf16) * p.scale;
+            }
+        }
+    }
+    __syncthreads();
+
+    // ---- online-softmax pass over this split's rows
+    const int sub = lane / LPR;         // which of the warp's RPW rows
+    const int dl = (lane % LPR) * 8;    // this lane's 8 dims
+    float q[GROUP][8], acc[GROUP][8], m[GROUP], l[GROUP];
+#pragma unroll
+    for (int h = 0; h < GROUP; ++h) {
+        m[h] = -INFINITY;
+        l[h] = 0.f;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) { q[h][i] = s_q[h][dl + i]; acc[h][i] = 0.f; }
+    }
+    constexpr int UNROLL = 4;
+    for (int r0 = r_begin + warp * RPW * UNROLL; r0 < r_end; r0 += NW * RPW * UNROLL) {
+        uint4 kraw[UNROLL], vraw[UNROLL];
+#pragma unroll
+        for (int j = 0; j < UNROLL; ++j) {
+            const int r = r0 + j * RPW + sub;
+            if (r < r_end) {
+                kraw[j] = *reinterpret_cast<const uint4*>(kbase + (size_t)r * D + dl);
+                vraw[j] = *reinterpret_cast<const uint4*>(vbase + (size_t)r * D + dl);
+            } else {
+                kraw[j] = make_uint4(0, 0, 0, 0);
+                vraw[j] = make_uint4(0, 0, 0, 0);
+            }
+        }
+#pragma unroll
+        for (int j = 0; j < UNROLL; ++j) {
+            const int r = r0 + j * RPW + sub;
+            const bool valid = r < r_end;
+            float kf[8], vf[8];
+            unpack8(kraw[j], kf, p.is_bf16);
+            unpack8(vraw[j], vf, p.is_bf16);
+#pragma unroll
+            for (int h = 0; h < GROUP; ++h) {
+                float sc = 0.f;
+#pragma unroll
+                for (int i = 0; i < 8; ++i) sc += q[h][i] * kf[i];
+#pragma unroll
+                for (int o = LPR / 2; o > 0; o >>= 1) sc += __shfl_xor_sync(0xffffffffu, sc, o);
+                if (valid) {
+                    const float mn = fmaxf(m[h], sc);
+                    const float corr = __expf(m[h] - mn);
+                    const float pr = __expf(sc - mn);
+                    l[h] = l[h] * corr + pr;
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) acc[h][i] = acc[h][i] * corr + pr * vf[i];
+                    m[h] = mn;
+                }
+            }
+        }
+    }
+    // ---- merge the RPW row-groups of a warp, then the warps, then the splits
+#pragma unroll
+    for (int h = 0; h < GROUP; ++h) {
+#pragma unroll
+        for (int o = LPR; o < 32; o <<= 1) {
+            const float m2 = __shfl_xor_sync(0xffffffffu, m[h], o);
+            const float l2 = __shfl_xor_sync(0xffffffffu, l[h], o);
+            const float mn = fmaxf(m[h], m2);
+            const float c1 = (m[h] == -INFINITY) ? 0.f : __expf(m[h] - mn);
+            const float c2 = (m2 == -INFINITY) ? 0.f : __expf(m2 - mn);
+            l[h] = l[h] * c1 + l2 * c2;
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                const float a2 = __shfl_xor_sync(0xffffffffu, acc[h][i], o);
+                acc[h][i] = acc[h][i] * c1 + a2 * c2;
+            }
+            m[h] = mn;
+        }
+        if (lane < LPR) {
+            if (lane == 0) { s_m[warp][h] = m[h]; s_l[warp][h] = l[h]; }
+#pragma unroll
+            for (int i = 0; i < 8; ++i) s_o[warp][h][dl + i] = acc[h][i];
+        }
+    }
+    __syncthreads();
+    // thread -> (head, dim) pairs
+    float* my_part = p.scratch + ((size_t)(t * p.n_heads + g * GROUP) * splits + s) * (D + 2);
+    for (int idx = tid; idx < GROUP * D; idx += kAttnThreads) {
+        const int h = idx / D, d = idx % D;
+        float mm = -INFINITY;
+#pragma unroll
+        for (int w = 0; w < NW; ++w) mm = fmaxf(mm, s_m[w][h]);
+        float ll = 0.f, oo = 0.f;
+#pragma unroll
+        for (int w = 0; w < NW; ++w) {
+            const float c = (s_m[w][h] == -INFINITY) ? 0.f : __expf(s_m[w][h] - mm);
+            ll += s_l[w][h] * c;
+            oo += s_o[w][h][d] * c;
+        }
+        if (eff == 1) {
+            p.out[(size_t)t * p.ldo + (g * GROUP + h) * D + d] = float_to_h16(oo / ll, p.is_bf16);
+        } else {
+            float* dst = my_part + (size_t)h * splits * (D + 2);
+            dst[d] = oo;
+            if (d == 0) { dst[D] = mm; dst[D + 1] = ll; }
+        }
+    }
+    if (eff == 1) return;
+    __threadfence();
+    __syncthreads();
+    if (tid == 0) {
+        const int old = atomicAdd(&p.counters[t * p.n_kv + g], 1);
+        s_last = (old + 1 == eff) ? 1 : 0;
+    }
+    __syncthreads();
+    if (!s_last) return;
+    __threadfence();
+    for (int idx = tid; idx < GROUP * D; idx += kAttnThreads) {
+        const int h = idx / D, d = idx % D;
+        const float* src = p.scratch + ((size_t)(t * p.n_heads + g * GROUP + h) * splits) * (D + 2);
+        float mm = -INFINITY;
+        for (int j = 0; j < eff; ++j) mm = fmaxf(mm, __ldcg(src + (size_t)j * (D + 2) + D));
+        float ll = 0.f, oo = 0.f;
+        for (int j = 0; j < eff; ++j) {
+            const float c = __expf(__ldcg(src + (size_t)j * (D + 2) + D) - mm);
+            ll += __ldcg(src + (size_t)j * (D + 2) + D + 1) * c;
+            oo += __ldcg(src + (size_t)j * (D + 2) + d) * c;
+        }
+        p.out[(size_t)t * p.ldo + (g * GROUP + h) * D + d] = float_to_h16(oo / ll, p.is_bf16);
+    }
+    if (tid == 0) p.counters[t * p.n_kv + g] = 0;
+}
+
+// ------------------------------------------------------------------ rope + append
+struct RopeAppendParams {
+    uint16_t* __restrict__ qkv;        // q rotated in place
+    uint16_t* __restrict__ kcache;     // [n_kv][s_max][D]
+    uint16_t* __restrict__ vcache;
+    const float* __restrict__ inv_freq;
+    int T, n_heads, n_kv, D, s_max, ldqkv, pos0, is_bf16;
+};
+
+__global__ void __launch_bounds__(128) rope_append_kernel(const RopeAppendParams p) {
+    pdl_wait_prior_grid();
+    pdl_launch_dependents();
+    const int D = p.D, tph = D / 16;
+    const int heads = p.n_heads + p.n_kv;
+    const long long total = (long long)p.T * heads * tph;
+    for (long long item = (long long)blockIdx.x * blockDim.x + threadIdx.x; item < total;
+         item += (long long)gridDim.x * blockDim.x) {
+        const int c = (int)(item % tph) * 8;
+        const int h = (int)((item / tph) % heads);
+        const int t = (int)(item / ((long long)tph * heads));
+        const int pos = p.pos0 + t;
+        uint16_t* src = p.qkv + (size_t)t * p.ldqkv + (size_t)h * D;
+        float lo[8], hi[8];
+        unpack8(*reinterpret_cast<const uint4*>(src + c), lo, p.is_bf16);
+        unpack8(*reinterpret_cast<const uint4*>(src + c + D / 2), hi, p.is_bf16);
+        if (p.inv_freq) rope8(lo, hi, c, pos, p.inv_freq, p.is_bf16);
+        if (h < p.n_heads) {
+            *reinterpret_cast<uint4*>(src + c) = pack8(lo, p.is_bf16);
+            *reinterpret_cast<uint4*>(src + c + D / 2) = pack8(hi, p.is_bf16);
+        } else {
+            const int g = h - p.n_heads;
+            uint16_t* kd = p.kcache + ((size_t)g * p.s_max + pos) * D;
+            uint16_t* vd = p.vcache + ((size_t)g * p.s_max + pos) * D;
+            const uint16_t* vs = p.qkv + (size_t)t * p.ldqkv + (size_t)(heads + g) * D;
+            *reinterpret_cast<uint4*>(kd + c) = pack8(lo, p.is_bf16);
+            *reinterpret_cast<uint4*>(kd + c + D / 2) = pack8(hi, p.is_bf16);
+            *reinterpret_cast<uint4*>(vd + c) = *reinterpret_cast<const uint4*>(vs + c);
+            *reinterpret_cast<uint4*>(vd + c + D / 2) = *reinterpret_cast<const uint4*>(vs + c + D / 2);
+        }
+    }
+}
+
+// ------------------------------------------------------------------ prefill (chunk vs cache)
+// CTA = (32 queries, one q head).  K/V tiles of 32 cached rows go through shared memory;
+// lane = key inside the tile for QK^T, lane = output dim for PV.  Scores never leave the SM.
+struct AttnPrefillParams {
+    const uint16_t* __restrict__ q;    // rotated q inside the qkv buffer, row stride ldq
+    uint16_t* __restrict__ out;        // [T, n_heads*D]
+    const uint16_t* __restrict__ kcache;
+    const uint16_t* __restrict__ vcache;
+    int T, n_heads, n_kv, s_max, ldq, ldo, pos0, is_bf16;
+    float scale;
+};
+
+template <int D>
+__global__ void __launch_bounds__(128) attn_prefill_kernel(const AttnPrefillParams p) {
+    constexpr int BQ = 32, BK = 32, NW = 4, QPW = BQ / NW;  // 8 queries per warp
+    constexpr int KS = D + 2;                               // padded row (halves): conflict-free column reads
+    __shared__ __align__(16) uint16_t s_k[BK * KS];
+    __shared__ __align__(16) uint16_t s_v[BK * D];
+    __shared__ float s_q[BQ][D];
+    __shared__ float s_p[NW][QPW][BK];
+
+    pdl_wait_prior_grid();
+    pdl_launch_dependents();
+    const int h = blockIdx.y, qb = blockIdx.x;
+    const int g = h / (p.n_heads / p.n_kv);
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int q0 = qb * BQ;
+    const uint16_t* kb = p.kcache + (size_t)g * p.s_max * D;
+    const uint16_t* vb = p.vcache + (size_t)g * p.s_max * D;
+
+    for (int i = tid; i < BQ * D; i += 128) {
+        const int r = i / D, d = i % D;
+        const int t = q0 + r;
+        s_q[r][d] = (t < p.T) ? h16_to_float(p.q[(size_t)t * p.ldq + (size_t)h * D + d], p.is_bf16) * p.scale : 0.f;
+    }
+    float m[QPW], l[QPW], acc[QPW][D / 32];
+#pragma unroll
+    for (int i = 0; i < QPW; ++i) {
+        m[i] = -INFINITY; l[i] = 0.f;
+#pragma unroll
+        for (int j = 0; j < D / 32; ++j) acc[i][j] = 0.f;
+    }
+    const int last_q = min(p.T, q0 + BQ) - 1;
+    const int kv_end = p.pos0 + last_q + 1;  // causal bound for the block
+    for (int k0 = 0; k0 < kv_end; k0 += BK) {
+        __syncthreads();
+        for (int i = tid; i < BK * D / 8; i += 128) {
+            const int r = i / (D / 8), c = (i % (D / 8)) * 8;
+            uint4 kv4 = make_uint4(0, 0, 0, 0), vv4 = make_uint4(0, 0, 0, 0);
+            if (k0 + r < kv_end) {
+                kv4 = *reinterpret_cast<const uint4*>(kb + (size_t)(k0 + r) * D + c);
+                vv4 = *reinterpret_cast<const uint4*>(vb + (size_t)(k0 + r) * D + c);
+            }
+            uint32_t* kd = reinterpret_cast<uint32_t*>(s_k + r * KS + c);  // KS*2 bytes = 4-byte aligned rows
+            kd[0] = kv4.x; kd[1] = kv4.y; kd[2] = kv4.z; kd[3] = kv4.w;
+            *reinterpret_cast<uint4*>(s_v + r * D + c) = vv4;
+        }
+        __syncthreads();
+        const int key = k0 + lane;
+#pragma unroll
+        for (int qi = 0; qi < QPW; ++qi) {
+            const int r = warp * QPW + qi;
+            const int t = q0 + r;
+            float sc = 0.f;
+            const uint32_t* krow = reinterpret_cast<const uint32_t*>(s_k + lane * KS);
+#pragma unroll 8
+            for (int d2 = 0; d2 < D / 2; ++d2) {
+                const uint32_t w = krow[d2];
+                sc += s_q[r][2 * d2] * h16_to_float((uint16_t)(w & 0xffff), p.is_bf16) +
+                      s_q[r][2 * d2 + 1] * h16_to_float((uint16_t)(w >> 16), p.is_bf16);
+            }
+            const bool ok = (t < p.T) && (key <= p.pos0 + t);
+            sc = ok ? sc : -INFINITY;
+            const float bm = warp_max(sc);
+            const float mn = fmaxf(m[qi], bm);
+            const float pr = (mn == -INFINITY) ? 0.f : __expf(sc - mn);
+            const float corr = (mn == -INFINITY) ? 1.f : __expf(m[qi] - mn);
+            l[qi] = l[qi] * corr + warp_sum(pr);
+#pragma unroll
+            for (int j = 0; j < D / 32; ++j) acc[qi][j] *= corr;
+            m[qi] = mn;
+            s_p[warp][qi][lane] = pr;
+        }
+        __syncwarp();
+#pragma unroll 4
+        for (int kk = 0; kk < BK; ++kk) {
+            float vv[D / 32];
+#pragma unroll
+            for (int j = 0; j < D / 32; ++j) vv[j] = h16_to_float(s_v[kk * D + j * 32 + lane], p.is_bf16);
+#pragma unroll
+            for (int qi = 0; qi < QPW; ++qi) {
+                const float pr = s_p[warp][qi][kk];
+#pragma unroll
+                for (int j = 0; j < D / 32; ++j) acc[qi][j] += pr * vv[j];
+            }
+        }
+        __syncwarp();
+    }
+#pragma unroll
+    for (int qi = 0; qi < QPW; ++qi) {
+        const int t = q0 + warp * QPW + qi;
+        if (t < p.T) {
+#pragma unroll
+            for (int j = 0; j < D / 32; ++j)
+                p.out[(size_t)t * p.ldo + (size_t)h * D + j * 32 + lane] = float_to_h16(acc[qi][j] / l[qi], p.is_bf16);
+        }
+    }
+}
+
+}  // namespace b200
+
+using namespace b200;
+
+extern "C" int64_t b200_attn_decode_scratch_bytes(int32_t T, int32_t n_heads, int32_t head_dim, int32_t splits) {
+    return (int64_t)T * n_heads * splits * (head_dim + 2) * (int64_t)sizeof(float);
+}
+
+extern "C" int b200_attn_decode(const b200_attn_decode_args* a, void* stream_) {
+    if (!a || !a->qkv || !a->out || !a->kv_ptrs || !a->pos || !a->scratch || !a->counters)
+        return fail(B200_EINVAL, "b200_attn_decode: null pointer argument");
+    if (a->n_kv_heads <= 0 || a->n_heads % a->n_kv_heads != 0)
+        return fail(B200_EINVAL, "b200_attn_decode: n_heads=%d not a multiple of n_kv_heads=%d", a->n_heads, a->n_kv_heads);
+    const int group = a->n_heads / a->n_kv_heads;
+    AttnDecodeParams p;
+    p.qkv = static_cast<const uint16_t*>(a->qkv);
+    p.out = static_cast<uint16_t*>(a->out);
+    p.kv_ptrs = reinterpret_cast<const unsigned long long*>(a->kv_ptrs);
+    p.pos = a->pos;
+    p.inv_freq = a->inv_freq;
+    p.scratch = a->scratch;
+    p.counters = a->counters;
+    p.T = a->T; p.n_heads = a->n_heads; p.n_kv = a->n_kv_heads; p.s_max = a->s_max;
+    p.splits = a->splits > 0 ? a->splits : 1;
+    p.ldqkv = a->ldqkv; p.ldo = a->ldo;
+    p.scale = a->scale;
+    p.is_bf16 = (a->dtype == B200_BF16) ? 1 : 0;
+    const dim3 grid((unsigned)(a->T * a->n_kv_heads * p.splits));
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    const bool pdl = a->pdl != 0;
+#define B200_ATTN_CASE(D_, G_)                                                                     \
+    if (a->head_dim == D_ && group == G_) {                                                        \
+        B200_CUDA_CHECK(launch(attn_decode_kernel<D_, G_>, grid, dim3(kAttnThreads), 0, stream, pdl, p)); \
+        return B200_OK;                                                                            \
+    }
+    B200_ATTN_CASE(128, 1) B200_ATTN_CASE(128, 2) B200_ATTN_CASE(128, 4) B200_ATTN_CASE(128, 8)
+    B200_ATTN_CASE(64, 1) B200_ATTN_CASE(64, 2) B200_ATTN_CASE(64, 4)
+#undef B200_ATTN_CASE
+    return fail(B200_EINVAL, "b200_attn_decode: unsupported head_dim=%d / group=%d", a->head_dim, group);
+}
+
+extern "C" int b200_rope_append(void* qkv, void* kcache, void* vcache, const float* inv_freq, int32_t T,
+                                int32_t n_heads, int32_t n_kv_heads, int32_t head_dim, int32_t s_max,
+                                int32_t ldqkv, int32_t pos0, int32_t dtype, int32_t pdl, void* stream_) {
+    if (!qkv || !kcache || !vcache) return fail(B200_EINVAL, "b200_rope_append: null pointer argument");
+    if (head_dim % 16 != 0) return fail(B200_EINVAL, "b200_rope_append: head_dim %d not a multiple of 16", head_dim);
+    if (pos0 + T > s_max) return fail(B200_ELIMIT, "b200_rope_append: %d+%d tokens exceed the cache capacity %d", pos0, T, s_max);
+    RopeAppendParams p;
+    p.qkv = static_cast<uint16_t*>(qkv);
+    p.kcache = static_cast<uint16_t*>(kcache);
+    p.vcache = static_cast<uint16_t*>(vcache);
+    p.inv_freq = inv_freq;
+    p.T = T; p.n_heads = n_heads; p.n_kv = n_kv_heads; p.D = head_dim; p.s_max = s_max; p.ldqkv = ldqkv;
+    p.pos0 = pos0; p.is_bf16 = (dtype == B200_BF16) ? 1 : 0;
+    const long long total = (long long)T * (n_heads + n_kv_heads) * (head_dim / 16);
+    int blocks = (int)((total + 127) / 128);
+    if (blocks > 148 * 8) blocks = 148 * 8;
+    B200_CUDA_CHECK(launch(rope_append_kernel, dim3(blocks), dim3(128), 0, static_cast<cudaStream_t>(stream_), pdl != 0, p));
+    return B200_OK;
+}
+
+extern "C" int b200_attn_prefill(const void* q, void* out, const void* kcache, const void* vcache, int32_t T,
+                                 int32_t n_heads, int32_t n_kv_heads, int32_t head_dim, int32_t s_max, int32_t ldq,
+                                 int32_t ldo, int32_t pos0, float scale, int32_t dtype, int32_t pdl, void* stream_) {
+    if (!q || !out || !kcache || !vcache) return fail(B200_EINVAL, "b200_attn_prefill: null pointer argument");
+    AttnPrefillParams p;
+    p.q = static_cast<const uint16_t*>(q);
+    p.out = static_cast<uint16_t*>(out);
+    p.kcache = static_cast<const uint16_t*>(kcache);
+    p.vcache = static_cast<const uint16_t*>(vcache);
+    p.T = T; p.n_heads = n_heads; p.n_kv = n_kv_heads; p.s_max = s_max; p.ldq = ldq; p.ldo = ldo; p.pos0 = pos0;
+    p.is_bf16 = (dtype == B200_BF16) ? 1 : 0;
+    p.scale = scale;
+    const dim3 grid((unsigned)((T + 31) / 32), (unsigned)n_heads);
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    if (head_dim == 128) {
+        B200_CUDA_CHECK(launch(attn_prefill_kernel<128>, grid, dim3(128), 0, stream, pdl != 0, p));
+    } else if (head_dim == 64) {
+        B200_CUDA_CHECK(launch(attn_prefill_kernel<64>, grid, dim3(128), 0, stream, pdl != 0, p));
+    } else {
+        return fail(B200_EINVAL, "b200_attn_prefill: unsupported head_dim=%d", head_dim);
+    }
+    return B200_OK;
+}

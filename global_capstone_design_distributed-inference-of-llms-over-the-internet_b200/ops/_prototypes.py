@@ -3,20 +3,36 @@ from __future__ import annotations
 
 import ctypes as C
 
+vp, i32, i64, f32 = C.c_void_p, C.c_int32, C.c_int64, C.c_float
 
-def _proto(L, name, argtypes, restype=C.c_int):
-    fn = getattr(L, name, None)
-    if fn is None:  # older build without this entry point
-        return
-    fn.argtypes = argtypes
-    fn.restype = restype
+
+class AttnDecodeArgs(C.Structure):
+    """Mirror of ``b200_attn_decode_args``."""
+
+    _fields_ = [
+        ("qkv", vp), ("out", vp), ("kv_ptrs", vp), ("pos", vp), ("inv_freq", vp), ("scratch", vp),
+        ("counters", vp),
+        ("T", i32), ("n_heads", i32), ("n_kv_heads", i32), ("head_dim", i32), ("s_max", i32),
+        ("splits", i32), ("ldqkv", i32), ("ldo", i32),
+        ("scale", f32), ("dtype", i32), ("pdl", i32),
+    ]
+
+
+PROTOTYPES = [
+    ("b200_attn_decode", [C.POINTER(AttnDecodeArgs), vp], C.c_int),
+    ("b200_attn_decode_scratch_bytes", [i32, i32, i32, i32], i64),
+    ("b200_rope_append", [vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, i32, i32, vp], C.c_int),
+    ("b200_attn_prefill", [vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, i32, f32, i32, i32, vp], C.c_int),
+    ("b200_embed", [vp, vp, i32, vp, vp, vp, i32, i32, i32, i32, i32, i32, vp], C.c_int),
+    ("b200_norm", [vp, vp, vp, vp, i32, i32, i32, i32, f32, i32, i32, i32, vp], C.c_int),
+    ("b200_argmax", [vp, i32, i32, i32, vp, vp, vp, vp, i32, i32, vp], C.c_int),
+]
 
 
 def register(L) -> None:
-    vp, i32, i64, f32 = C.c_void_p, C.c_int32, C.c_int64, C.c_float
-    # filled in as kernels are added (see include/b200_petals.h)
     for name, args, res in PROTOTYPES:
-        _proto(L, name, args, res)
-
-
-PROTOTYPES: list = []
+        fn = getattr(L, name, None)
+        if fn is None:  # older build without this entry point
+            continue
+        fn.argtypes = args
+        fn.restype = res

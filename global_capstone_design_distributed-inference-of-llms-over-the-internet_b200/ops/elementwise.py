@@ -1,0 +1,51 @@
+"""Python front-ends of csrc/elementwise.cu (embedding, norm, argmax)."""
+from __future__ import annotations
+
+from typing import Optional
+
+import torch
+
+from . import native
+from .gemm import dtype_code
+
+
+def embed(ids: torch.Tensor, wte: torch.Tensor, out: torch.Tensor, wpe: Optional[torch.Tensor] = None,
+          pos: Optional[torch.Tensor] = None, pos0: int = 0, pdl: bool = False):
+    assert ids.dtype == torch.int64 and ids.is_cuda
+    T, H = out.shape
+    rc = native.lib().b200_embed(ids.data_ptr(), pos.data_ptr() if pos is not None else None, pos0, wte.data_ptr(),
+                                 wpe.data_ptr() if wpe is not None else None, out.data_ptr(), T, H, wte.shape[0],
+                                 wpe.shape[0] if wpe is not None else 1 << 30, dtype_code(out.dtype),
+                                 1 if pdl else 0, native.current_stream_ptr())
+    native.check(rc, "b200_embed")
+    return out
+
+
+def norm(x: torch.Tensor, w: torch.Tensor, b: Optional[torch.Tensor], eps: float, layer_norm: bool,
+         out: Optional[torch.Tensor] = None, pdl: bool = False):
+    if out is None:
+        out = torch.empty_like(x)
+    T, H = x.shape
+    rc = native.lib().b200_norm(x.data_ptr(), w.data_ptr(), b.data_ptr() if b is not None else None, out.data_ptr(),
+                                T, H, x.stride(0), out.stride(0), eps, 1 if layer_norm else 0, dtype_code(x.dtype),
+                                1 if pdl else 0, native.current_stream_ptr())
+    native.check(rc, "b200_norm")
+    return out
+
+
+class ArgmaxWorkspace:
+    def __init__(self, device, max_tokens: int, chunks: int = 64):
+        self.chunks = chunks
+        self.part_val = torch.empty(max_tokens * chunks, dtype=torch.float32, device=device)
+        self.part_idx = torch.empty(max_tokens * chunks, dtype=torch.int32, device=device)
+        self.counters = torch.zeros(max_tokens, dtype=torch.int32, device=device)
+
+
+def argmax(logits: torch.Tensor, out_ids: torch.Tensor, ws: ArgmaxWorkspace, pdl: bool = False):
+    assert logits.dtype == torch.float32 and out_ids.dtype == torch.int64
+    T, V = logits.shape
+    rc = native.lib().b200_argmax(logits.data_ptr(), logits.stride(0), T, V, ws.part_val.data_ptr(),
+                                  ws.part_idx.data_ptr(), ws.counters.data_ptr(), out_ids.data_ptr(), ws.chunks,
+                                  1 if pdl else 0, native.current_stream_ptr())
+    native.check(rc, "b200_argmax")
+    return out_ids

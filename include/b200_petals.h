@@ -85,6 +85,55 @@ int64_t b200_gemm_scratch_bytes(int32_t max_tokens);
 /* Token-tile width the kernel will pick for T tokens (16,32,64,128,256). */
 int32_t b200_gemm_token_tile(int32_t T, int32_t dual);
 
+/* ------------------------------------------------------------- attention --
+ * Decode: for each of T independent sessions' new tokens, apply RoPE to q and k,
+ * append k/v to that session's pre-allocated cache in place (no torch.cat
+ * reallocation as in petals/llama/block.py:123-128), and attend over the cache
+ * with a split-KV online softmax (GQA heads of one kv head share the K/V
+ * stream; no repeat_kv copy, block.py:131-132).  Scores never touch HBM
+ * (block.py:134-141 materialises [nh,T,S] in fp32).
+ * kv_ptrs[t] = {K base, V base} of this layer for token t's session, each
+ * laid out [n_kv_heads][s_max][head_dim]; pos[t] = tokens already cached.
+ */
+typedef struct b200_attn_decode_args {
+    const void* qkv;        /* [T, (nh + 2 nkv) * d] : q | k | v, row stride ldqkv */
+    void* out;              /* [T, nh * d], row stride ldo */
+    const uint64_t* kv_ptrs;/* device [T][2] */
+    const int32_t* pos;     /* device [T] */
+    const float* inv_freq;  /* device [d/2] RoPE inverse frequencies, NULL = no RoPE (GPT-2) */
+    float* scratch;         /* >= b200_attn_decode_scratch_bytes() */
+    int32_t* counters;      /* T * n_kv_heads ints, zero on entry and on exit */
+    int32_t T, n_heads, n_kv_heads, head_dim, s_max, splits, ldqkv, ldo;
+    float scale;            /* 1/sqrt(d) */
+    int32_t dtype, pdl;
+} b200_attn_decode_args;
+int b200_attn_decode(const b200_attn_decode_args* args, void* stream);
+int64_t b200_attn_decode_scratch_bytes(int32_t T, int32_t n_heads, int32_t head_dim, int32_t splits);
+
+/* Prefill / chunk: rotate q in place, rotate k and store k, v into the session cache at
+ * positions [pos0, pos0 + T).  (HF rotary + cache append, block.py:96-128.) */
+int b200_rope_append(void* qkv, void* kcache, void* vcache, const float* inv_freq, int32_t T, int32_t n_heads,
+                     int32_t n_kv_heads, int32_t head_dim, int32_t s_max, int32_t ldqkv, int32_t pos0,
+                     int32_t dtype, int32_t pdl, void* stream);
+/* Causal attention of a T-token chunk (already appended) against cache rows [0, pos0 + T).
+ * The reference never builds the causal mask on its live path; this does. */
+int b200_attn_prefill(const void* q, void* out, const void* kcache, const void* vcache, int32_t T, int32_t n_heads,
+                      int32_t n_kv_heads, int32_t head_dim, int32_t s_max, int32_t ldq, int32_t ldo, int32_t pos0,
+                      float scale, int32_t dtype, int32_t pdl, void* stream);
+
+/* ----------------------------------------------------------- elementwise --
+ * Embedding gather (+ learned positions for GPT-2): src/llama_partition.py:107.
+ * ids are int64 on the device (the last stage writes them there). */
+int b200_embed(const void* ids, const void* pos, int32_t pos0, const void* wte, const void* wpe, void* out, int32_t T,
+               int32_t H, int32_t vocab, int32_t max_pos, int32_t dtype, int32_t pdl, void* stream);
+/* Standalone RMSNorm (layer_norm=0) / LayerNorm (1) for prefill-size inputs: block.py:208-213. */
+int b200_norm(const void* x, const void* w, const void* b, void* out, int32_t T, int32_t H, int32_t ldx, int32_t ldo,
+              float eps, int32_t layer_norm, int32_t dtype, int32_t pdl, void* stream);
+/* Greedy sampling: first index of the row maximum of fp32 logits (src/rpc_handler.py:331-335).
+ * part_val/part_idx: T*chunks scratch; counters: T ints kept zero. */
+int b200_argmax(const float* logits, int32_t ld, int32_t T, int32_t V, float* part_val, int32_t* part_idx,
+                int32_t* counters, void* out_ids, int32_t chunks, int32_t pdl, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
