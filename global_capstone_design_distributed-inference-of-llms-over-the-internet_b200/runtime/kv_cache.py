@@ -1,0 +1,122 @@
+"""Per-session KV cache: pre-allocated to ``max_length`` and appended in place.
+
+The reference keeps ``session_id -> tuple((k, v), ...)`` and grows every tensor
+with ``torch.cat`` on every token, never evicts and never enforces ``max_length``
+(src/rpc_handler.py:70,185,266; petals/llama/block.py:123-128).
+Here a session owns ``[n_layers, 2, n_kv, max_len, head_dim]`` from its first
+request; the manager enforces a token budget (upstream ``attn_cache_tokens``,
+petals/server/server.py:204-209), evicts idle sessions after a TTL, supports
+explicit close, and rollback to an earlier position (``start_from_position``,
+petals/server/block_functions.py:163-168).
+"""
+from __future__ import annotations
+
+import threading
+import time
+from dataclasses import dataclass, field
+from typing import Dict, Optional
+
+import torch
+
+
+class AllocationFailed(RuntimeError):
+    """Raised when the KV token budget cannot hold a new session (memory_cache.py:26)."""
+
+
+@dataclass
+class SessionKV:
+    session_id: str
+    data: torch.Tensor            # [n_layers, 2, n_kv, max_len, head_dim]
+    max_len: int
+    length: int = 0               # tokens cached so far
+    last_used: float = field(default_factory=time.monotonic)
+
+    @property
+    def n_layers(self) -> int:
+        return self.data.shape[0]
+
+    def k(self, layer: int) -> torch.Tensor:
+        return self.data[layer, 0]
+
+    def v(self, layer: int) -> torch.Tensor:
+        return self.data[layer, 1]
+
+    def rollback(self, position: int) -> None:
+        if not 0 <= position <= self.length:
+            raise ValueError(f"cannot roll session back to {position} (length {self.length})")
+        self.length = position
+
+    def touch(self) -> None:
+        self.last_used = time.monotonic()
+
+
+class KVCacheManager:
+    def __init__(self, n_layers: int, n_kv_heads: int, head_dim: int, dtype: torch.dtype, device,
+                 max_tokens: Optional[int] = None, default_max_length: int = 2048, session_ttl: float = 600.0):
+        self.n_layers, self.n_kv, self.head_dim = n_layers, n_kv_heads, head_dim
+        self.dtype, self.device = dtype, torch.device(device)
+        self.max_tokens = max_tokens              # None = unlimited
+        self.default_max_length = default_max_length
+        self.session_ttl = session_ttl
+        self.sessions: Dict[str, SessionKV] = {}
+        self._lock = threading.Lock()
+
+    # ---- accounting
+    @property
+    def tokens_used(self) -> int:
+        return sum(s.max_len for s in self.sessions.values())
+
+    @property
+    def tokens_left(self) -> Optional[int]:
+        return None if self.max_tokens is None else self.max_tokens - self.tokens_used
+
+    def bytes_per_token(self) -> int:
+        return 2 * self.n_layers * self.n_kv * self.head_dim * torch.empty((), dtype=self.dtype).element_size()
+
+    # ---- lifecycle
+    def get(self, session_id: str) -> Optional[SessionKV]:
+        s = self.sessions.get(session_id)
+        if s is not None:
+            s.touch()
+        return s
+
+    def allocate(self, session_id: str, max_length: Optional[int] = None) -> SessionKV:
+        max_length = int(max_length or self.default_max_length)
+        with self._lock:
+            self.evict_expired()
+            old = self.sessions.pop(session_id, None)
+            if old is not None and old.max_len >= max_length:
+                old.length = 0
+                old.touch()
+                self.sessions[session_id] = old
+                return old
+            if self.max_tokens is not None and self.tokens_used + max_length > self.max_tokens:
+                self._evict_lru_until(max_length)
+                if self.tokens_used + max_length > self.max_tokens:
+                    raise AllocationFailed(
+                        f"KV budget exhausted: need {max_length} tokens, {self.tokens_left} left of {self.max_tokens}")
+            data = torch.zeros((self.n_layers, 2, self.n_kv, max_length, self.head_dim), dtype=self.dtype,
+                               device=self.device)
+            s = SessionKV(session_id, data, max_length)
+            self.sessions[session_id] = s
+            return s
+
+    def close(self, session_id: str) -> bool:
+        with self._lock:
+            return self.sessions.pop(session_id, None) is not None
+
+    def evict_expired(self, now: Optional[float] = None) -> int:
+        now = time.monotonic() if now is None else now
+        dead = [k for k, s in self.sessions.items() if now - s.last_used > self.session_ttl]
+        for k in dead:
+            del self.sessions[k]
+        return len(dead)
+
+    def _evict_lru_until(self, need: int) -> None:
+        # only idle sessions (unused for > 10% of the TTL) are fair game
+        now = time.monotonic()
+        for k, s in sorted(self.sessions.items(), key=lambda kv: kv[1].last_used):
+            if self.tokens_used + need <= self.max_tokens:
+                break
+            if now - s.last_used > 0.1 * self.session_ttl:
+                del self.sessions[k]

@@ -1,0 +1,311 @@
+"""B200 execution of a layer span: packed weights + hand-written sm_100a kernels.
+
+One ``NativeSpan`` owns the decoder blocks ``[start, end)`` of a model on one GPU
+(optionally the embedding in front and the final norm + LM head + arg-max
+behind) and runs them with the kernels of ``csrc/``:
+
+decode (<= 32 tokens, one per session), per block — 5 launches:
+    qkv   = GEMM(norm-prologue(h), Wqkv) [+bias]          gemm.cu (tcgen05, stream-K)
+    attn  = RoPE + KV append + split-KV attention         attention.cu
+    h2    = GEMM(attn, Wo) [+bias] + h                    residual epilogue
+    act   = GEMM(norm-prologue(h2), Wgate|Wup) -> SwiGLU  (GPT-2: Wfc + bias -> GELU-tanh)
+    h     = GEMM(act, Wdown) [+bias] + h2
+  the whole step (all blocks, plus embedding / head / arg-max on the edge stages)
+  is captured once per batch size in a CUDA graph and replayed per token
+  (the reference graphs only RoPE and the two RMSNorms: petals/llama/cuda_graphs.py).
+
+prefill (a chunk of one session): standalone norm -> GEMM -> rope_append ->
+causal attention against the session cache -> GEMMs, chunked to ``max_chunk``.
+
+Replaces src/llama_partition.py:99-137,222-297,391-474 (Stage forward loops).
+"""
+from __future__ import annotations
+
+import math
+import os
+from typing import Dict, List, Optional, Sequence
+
+import torch
+
+from ..models.config import ModelConfig
+from ..ops import attention as A
+from ..ops import elementwise as E
+from ..ops import gemm as G
+from ..ops import packing
+from .kv_cache import SessionKV
+
+MAX_DECODE_BATCH = 32
+
+
+def _pdl_default() -> bool:
+    return os.environ.get("B200_PDL", "1") != "0"
+
+
+class NativeSpan:
+    def __init__(self, cfg: ModelConfig, weights: Dict[str, object], device, dtype: torch.dtype, *,
+                 kv_capacity: int = 2048, max_batch: int = 8, max_chunk: int = 512, attn_splits: int = 0,
+                 use_graphs: bool = True, pdl: Optional[bool] = None, free_source_weights: bool = True):
+        assert dtype in (torch.float16, torch.bfloat16), "native path runs fp16/bf16"
+        self.cfg, self.device, self.dtype = cfg, torch.device(device), dtype
+        self.kv_capacity, self.max_batch, self.max_chunk = kv_capacity, min(max_batch, MAX_DECODE_BATCH), max_chunk
+        self.use_graphs = use_graphs
+        self.pdl = _pdl_default() if pdl is None else pdl
+        self.has_embed = bool(weights.get("has_embed", False))
+        self.has_head = bool(weights.get("has_head", "lm_head" in weights))
+        c = cfg
+        with torch.cuda.device(self.device):
+            self.layers = []
+            for L in weights["layers"]:  # type: ignore[union-attr]
+                P = {"ln1_w": L["ln1_w"], "ln1_b": L.get("ln1_b"), "ln2_w": L["ln2_w"], "ln2_b": L.get("ln2_b"),
+                     "qkv": packing.pack_weight(L["qkv_w"], L.get("qkv_b")),
+                     "o": packing.pack_weight(L["o_w"], L.get("o_b")),
+                     "down": packing.pack_weight(L["down_w"], L.get("down_b"))}
+                if c.is_llama:
+                    P["mlp_in"] = packing.pack_dual(L["gate_w"], L["up_w"])
+                else:
+                    P["mlp_in"] = packing.pack_weight(L["fc_w"], L.get("fc_b"))
+                self.layers.append(P)
+                if free_source_weights:
+                    for k in ("qkv_w", "o_w", "down_w", "gate_w", "up_w", "fc_w"):
+                        L.pop(k, None)
+            self.embed_w = weights.get("embed") if self.has_embed else None
+            self.pos_embed_w = weights.get("pos_embed") if self.has_embed else None
+            if self.has_head:
+                self.final_norm_w = weights["final_norm_w"]
+                self.final_norm_b = weights.get("final_norm_b")
+                self.lm_head = packing.pack_weight(weights["lm_head"])  # type: ignore[arg-type]
+            self.inv_freq = (A.rope_inv_freq(c.head_dim, c.rope_theta, c.rope_scaling, self.device)
+                             if c.is_llama else None)
+            self.scale = 1.0 / math.sqrt(c.head_dim)
+            self.norm_mode = G.NORM_RMS if c.is_llama else G.NORM_LAYER
+            self.mlp_epi = G.EPI_SWIGLU if c.is_llama else G.EPI_GELU_TANH
+            nl = len(self.layers)
+            Tm = max(self.max_chunk, self.max_batch)
+            mk = lambda *s, dt=dtype: torch.empty(*s, dtype=dt, device=self.device)  # noqa: E731
+            self.h_a, self.h_b, self.xn = mk(Tm, c.hidden), mk(Tm, c.hidden), mk(Tm, c.hidden)
+            self.qkv = mk(Tm, c.qkv_size)
+            self.attn = mk(Tm, c.q_size)
+            self.act = mk(Tm, c.intermediate)
+            self.ids_in = torch.zeros(Tm, dtype=torch.int64, device=self.device)
+            self.ws = G.GemmWorkspace.create(self.device, Tm)
+            self.splits = attn_splits or max(1, min(16, kv_capacity // 256))
+            self.attn_ws = A.DecodeAttnWorkspace(self.device, self.max_batch, c.n_heads, c.n_kv_heads, c.head_dim,
+                                                 self.splits)
+            self.kv_ptrs = torch.zeros(max(nl, 1), self.max_batch, 2, dtype=torch.int64, device=self.device)
+            self.kv_ptrs_host = torch.zeros(max(nl, 1), self.max_batch, 2, dtype=torch.int64).pin_memory()
+            self.pos = torch.zeros(self.max_batch, dtype=torch.int32, device=self.device)
+            self.pos_host = torch.zeros(self.max_batch, dtype=torch.int32).pin_memory()
+            if self.has_head:
+                self.logits = mk(self.max_batch, c.vocab, dt=torch.float32)
+                self.ids_out = torch.zeros(self.max_batch, dtype=torch.int64, device=self.device)
+                self.argmax_ws = E.ArgmaxWorkspace(self.device, self.max_batch)
+        self._graphs: Dict[tuple, torch.cuda.CUDAGraph] = {}
+        self._ptr_key = None
+        self.kernel_launches = 0   # launches issued or replayed (bench bookkeeping)
+        self._launches_per_graph: Dict[tuple, int] = {}
+
+    # ------------------------------------------------------------------ pieces
+    @property
+    def n_layers(self) -> int:
+        return len(self.layers)
+
+    def weight_bytes(self) -> int:
+        n = sum(P[k].nbytes for P in self.layers for k in ("qkv", "o", "mlp_in", "down"))
+        if self.has_head:
+            n += self.lm_head.nbytes
+        return n
+
+    def _count(self, n: int = 1) -> None:
+        self.kernel_launches += n
+
+    def _decode_layers(self, T: int, h: torch.Tensor) -> torch.Tensor:
+        """h: [T, H] view of a static buffer; returns the buffer view holding the result."""
+        c, pdl = self.cfg, self.pdl
+        other = self.h_b if h.data_ptr() == self.h_a.data_ptr() else self.h_a
+        for li, P in enumerate(self.layers):
+            qkv, attn, act, h2 = self.qkv[:T], self.attn[:T], self.act[:T], other[:T]
+            G.linear(h, P["qkv"], out=qkv, norm_mode=self.norm_mode, norm_w=P["ln1_w"], norm_b=P["ln1_b"],
+                     norm_eps=c.norm_eps, workspace=self.ws, pdl=pdl)
+            A.attn_decode(qkv, attn, self.kv_ptrs[li], self.pos, self.inv_freq, self.attn_ws, c.n_heads,
+                          c.n_kv_heads, c.head_dim, self.kv_capacity, self.scale, pdl=pdl)
+            G.linear(attn, P["o"], out=h2, residual=h, workspace=self.ws, pdl=pdl)
+            G.linear(h2, P["mlp_in"], out=act, epilogue=self.mlp_epi, norm_mode=self.norm_mode, norm_w=P["ln2_w"],
+                     norm_b=P["ln2_b"], norm_eps=c.norm_eps, workspace=self.ws, pdl=pdl)
+            G.linear(act, P["down"], out=h, residual=h2, workspace=self.ws, pdl=pdl)
+            self._count(5)
+        return h
+
+    def _head(self, h_rows: torch.Tensor, greedy: bool) -> torch.Tensor:
+        """h_rows: [B<=32, H] -> logits [B, V] fp32 (and ids_out when greedy)."""
+        c = self.cfg
+        B = h_rows.shape[0]
+        logits = self.logits[:B]
+        G.linear(h_rows, self.lm_head, out=logits, norm_mode=self.norm_mode, norm_w=self.final_norm_w,
+                 norm_b=self.final_norm_b, norm_eps=c.norm_eps, out_fp32=True, workspace=self.ws, pdl=self.pdl)
+        self._count()
+        if greedy:
+            E.argmax(logits, self.ids_out[:B], self.argmax_ws, pdl=self.pdl)
+            self._count()
+        return logits
+
+    def _embed(self, T: int, pos0: int, use_pos_buffer: bool) -> torch.Tensor:
+        h = self.h_a[:T]
+        E.embed(self.ids_in[:T], self.embed_w, h, wpe=self.pos_embed_w,
+                pos=self.pos[:T] if use_pos_buffer else None, pos0=pos0, pdl=self.pdl)
+        self._count()
+        return h
+
+    # ------------------------------------------------------------------ decode
+    def _stage_ptrs(self, kvs: Sequence[SessionKV]) -> None:
+        key = tuple(id(k.data) for k in kvs)
+        if key != self._ptr_key:
+            B = len(kvs)
+            for b, kv in enumerate(kvs):
+                if kv.max_len != self.kv_capacity:
+                    raise ValueError(f"session capacity {kv.max_len} != engine kv_capacity {self.kv_capacity}")
+                base = kv.data.data_ptr()
+                per_layer = kv.data.stride(0) * kv.data.element_size()
+                half = kv.data.stride(1) * kv.data.element_size()
+                for li in range(self.n_layers):
+                    self.kv_ptrs_host[li, b, 0] = base + li * per_layer
+                    self.kv_ptrs_host[li, b, 1] = base + li * per_layer + half
+            self.kv_ptrs[:, :B].copy_(self.kv_ptrs_host[:, :B], non_blocking=True)
+            self._ptr_key = key
+        for b, kv in enumerate(kvs):
+            if kv.length + 1 > kv.max_len:
+                raise ValueError(f"session {kv.session_id}: max_length {kv.max_len} reached")
+            self.pos_host[b] = kv.length
+        self.pos[: len(kvs)].copy_(self.pos_host[: len(kvs)], non_blocking=True)
+
+    def _decode_body(self, B: int, from_ids: bool, greedy: bool):
+        h = self._embed(B, 0, True) if from_ids else self.h_a[:B]
+        h = self._decode_layers(B, h)
+        if self.has_head:
+            self._head(h, greedy)
+        return h
+
+    def decode(self, kvs: Sequence[SessionKV], h_in: Optional[torch.Tensor] = None,
+               ids: Optional[torch.Tensor] = None, greedy: bool = True):
+        """One token for each session in ``kvs``.
+
+        First stage: pass ``ids`` (int64 device tensor [B]) or leave ``ids_in`` pre-filled (e.g. by
+        the last stage's arg-max over NVLink).  Other stages: ``h_in`` [B, H].
+        Returns hidden states [B, H] (view of a static buffer) — or, on the last stage,
+        ``(logits [B, V] fp32, ids_out [B] int64)`` device views.
+        """
+        B = len(kvs)
+        assert 1 <= B <= self.max_batch
+        from_ids = self.embed_w is not None and h_in is None
+        self._stage_ptrs(kvs)
+        key = (B, from_ids, greedy)
+        g = None
+        if self.use_graphs:
+            g = self._graphs.get(key)
+            if g is None:
+                g = self._capture(key)   # runs the body once on whatever the buffers hold
+        if from_ids and ids is not None:
+            self.ids_in[:B].copy_(ids, non_blocking=True)
+        if not from_ids:
+            self.h_a[:B].copy_(h_in, non_blocking=True)
+        if g is not None:
+            g.replay()
+            self.kernel_launches += self._launches_per_graph[key]
+            out_h = self._graph_out[key]
+        else:
+            out_h = self._decode_body(B, from_ids, greedy)
+        for kv in kvs:
+            kv.length += 1
+            kv.touch()
+        if self.has_head:
+            return self.logits[:B], self.ids_out[:B]
+        return out_h
+
+    def _capture(self, key) -> torch.cuda.CUDAGraph:
+        B, from_ids, greedy = key
+        if not hasattr(self, "_graph_out"):
+            self._graph_out = {}
+        # warm-up outside capture (sets kernel attributes, loads modules)
+        before = self.kernel_launches
+        s = torch.cuda.Stream(device=self.device)
+        s.wait_stream(torch.cuda.current_stream(self.device))
+        with torch.cuda.stream(s):
+            self._decode_body(B, from_ids, greedy)
+        torch.cuda.current_stream(self.device).wait_stream(s)
+        torch.cuda.synchronize(self.device)
+        per = self.kernel_launches - before
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g, stream=s):
+            out_h = self._decode_body(B, from_ids, greedy)
+        self.kernel_launches = before  # warm-up + capture passes touched KV slot `pos` twice; harmless: same data
+        self._graphs[key] = g
+        self._graph_out[key] = out_h
+        self._launches_per_graph[key] = per
+        return g
+
+    # ------------------------------------------------------------------ prefill
+    def prefill(self, kv: SessionKV, h_in: Optional[torch.Tensor] = None, ids: Optional[torch.Tensor] = None,
+                pos0: Optional[int] = None, greedy: bool = True):
+        """Append T tokens of one session (chunked to ``max_chunk``).
+
+        Returns hidden [T, H] (new tensor) for non-last stages, else (logits [1,V], ids_out[1])
+        computed from the last position only.
+        """
+        c, pdl = self.cfg, self.pdl
+        pos0 = kv.length if pos0 is None else pos0
+        T = ids.shape[0] if h_in is None else h_in.shape[0]
+        if pos0 + T > kv.max_len:
+            raise ValueError(f"session {kv.session_id}: {pos0}+{T} tokens exceed max_length {kv.max_len}")
+        if kv.max_len != self.kv_capacity:
+            raise ValueError(f"session capacity {kv.max_len} != engine kv_capacity {self.kv_capacity}")
+        out = None if self.has_head else torch.empty(T, c.hidden, dtype=self.dtype, device=self.device)
+        last_h = None
+        for c0 in range(0, T, self.max_chunk):
+            n = min(self.max_chunk, T - c0)
+            p0 = pos0 + c0
+            if h_in is None:
+                self.ids_in[:n].copy_(ids[c0:c0 + n], non_blocking=True)
+                h = self._embed(n, p0, False)
+            else:
+                h = self.h_a[:n]
+                h.copy_(h_in[c0:c0 + n], non_blocking=True)
+            other = self.h_b
+            fused = n <= G.MAX_FUSED_NORM_TOKENS
+            ln = not c.is_llama
+            for li, P in enumerate(self.layers):
+                qkv, attn, act, h2 = self.qkv[:n], self.attn[:n], self.act[:n], other[:n]
+                if fused:
+                    G.linear(h, P["qkv"], out=qkv, norm_mode=self.norm_mode, norm_w=P["ln1_w"], norm_b=P["ln1_b"],
+                             norm_eps=c.norm_eps, workspace=self.ws, pdl=pdl)
+                else:
+                    E.norm(h, P["ln1_w"], P["ln1_b"], c.norm_eps, ln, out=self.xn[:n], pdl=pdl)
+                    G.linear(self.xn[:n], P["qkv"], out=qkv, workspace=self.ws, pdl=pdl)
+                A.rope_append(qkv, kv.k(li), kv.v(li), self.inv_freq, c.n_heads, c.n_kv_heads, c.head_dim,
+                              kv.max_len, p0, pdl=pdl)
+                A.attn_prefill(qkv, attn, kv.k(li), kv.v(li), c.n_heads, c.n_kv_heads, c.head_dim, kv.max_len, p0,
+                               self.scale, pdl=pdl)
+                G.linear(attn, P["o"], out=h2, residual=h, workspace=self.ws, pdl=pdl)
+                if fused:
+                    G.linear(h2, P["mlp_in"], out=act, epilogue=self.mlp_epi, norm_mode=self.norm_mode,
+                             norm_w=P["ln2_w"], norm_b=P["ln2_b"], norm_eps=c.norm_eps, workspace=self.ws, pdl=pdl)
+                else:
+                    E.norm(h2, P["ln2_w"], P["ln2_b"], c.norm_eps, ln, out=self.xn[:n], pdl=pdl)
+                    G.linear(self.xn[:n], P["mlp_in"], out=act, epilogue=self.mlp_epi, workspace=self.ws, pdl=pdl)
+                G.linear(act, P["down"], out=h, residual=h2, workspace=self.ws, pdl=pdl)
+                self._count(6 if fused else 8)
+            if out is not None:
+                out[c0:c0 + n].copy_(h, non_blocking=True)
+            last_h = h[n - 1:n]
+        kv.length = pos0 + T
+        kv.touch()
+        if self.has_head:
+            self._head(last_h, greedy)
+            return self.logits[:1], self.ids_out[:1]
+        return out
+
+    # ------------------------------------------------------------------ TorchSpan-compatible API
+    def forward(self, h: torch.Tensor, kv: SessionKV, pos0: Optional[int] = None) -> torch.Tensor:
+        """[T, H] -> [T, H] for one session (decode kernel path when T == 1)."""
+        assert not self.has_head
+        if h.shape[0] == 1 and (pos0 is None or pos0 == kv.length):
+            return self.decode([kv], h_in=h).clone()
+        return self.prefill(kv, h_in=h, pos0=pos0)
