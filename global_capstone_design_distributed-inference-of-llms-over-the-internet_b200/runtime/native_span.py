@@ -242,6 +242,62 @@ class NativeSpan:
         self._launches_per_graph[key] = per
         return g
 
+    # ------------------------------------------------------------------ device-resident greedy loop
+    def decode_loop(self, kvs: Sequence[SessionKV], first_ids: torch.Tensor, n_steps: int) -> torch.Tensor:
+        """Greedy-decode ``n_steps`` tokens for every session with no host round trip.
+
+        Only for a span that holds the whole model (embedding and head): the arg-max of
+        step i is copied to the embedding input of step i+1 and the positions advance on the
+        device, all inside one CUDA graph that is replayed ``n_steps`` times.
+        Returns the generated ids ``[n_steps, B]`` (device).
+        """
+        assert self.has_embed and self.has_head and self.embed_w is not None
+        B = len(kvs)
+        for kv in kvs:
+            if kv.length + n_steps > kv.max_len:
+                raise ValueError(f"session {kv.session_id}: {kv.length}+{n_steps} exceeds max_length {kv.max_len}")
+        self._stage_ptrs(kvs)
+        key = ("loop", B)
+        g = self._graphs.get(key)
+        if g is None:
+            if not hasattr(self, "hist"):
+                self.hist = torch.zeros(4096, self.max_batch, dtype=torch.int64, device=self.device)
+                self.step_idx = torch.zeros(1, dtype=torch.int64, device=self.device)
+
+            def body():
+                self._decode_body(B, True, True)
+                self.hist.index_copy_(0, self.step_idx, self.ids_out[:B].unsqueeze(0) if B == self.max_batch
+                                      else torch.nn.functional.pad(self.ids_out[:B], (0, self.max_batch - B)).unsqueeze(0))
+                self.ids_in[:B].copy_(self.ids_out[:B])
+                self.pos[:B].add_(1)
+                self.step_idx.add_(1)
+
+            before = self.kernel_launches
+            s = torch.cuda.Stream(device=self.device)
+            s.wait_stream(torch.cuda.current_stream(self.device))
+            with torch.cuda.stream(s):
+                body()
+            torch.cuda.current_stream(self.device).wait_stream(s)
+            torch.cuda.synchronize(self.device)
+            per = self.kernel_launches - before
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g, stream=s):
+                body()
+            self.kernel_launches = before
+            self._graphs[key] = g
+            self._launches_per_graph[key] = per
+            self._stage_ptrs(kvs)          # the warm-up advanced pos on the device: restore
+        assert n_steps <= self.hist.shape[0]
+        self.step_idx.zero_()
+        self.ids_in[:B].copy_(first_ids, non_blocking=True)
+        for _ in range(n_steps):
+            g.replay()
+        self.kernel_launches += n_steps * self._launches_per_graph[key]
+        for kv in kvs:
+            kv.length += n_steps
+            kv.touch()
+        return self.hist[:n_steps, :B]
+
     # ------------------------------------------------------------------ prefill
     def prefill(self, kv: SessionKV, h_in: Optional[torch.Tensor] = None, ids: Optional[torch.Tensor] = None,
                 pos0: Optional[int] = None, greedy: bool = True):
