@@ -581,3 +581,84 @@ extern "C" int b200_gemm(const b200_gemm_args* a, void* stream_) {
 #undef B200_GEMM_CASE
     return fail(B200_EINVAL, "b200_gemm: unsupported token tile %d", bn);
 }
+
+// ---------------------------------------------------------------------------------------------
+// b200_gemm_static_scratch: the same GEMM for hosts that may not allocate device memory.
+//
+// Who needs this: programs that give this library pointers but no allocator.  Typical cases are a C
+// plugin inside an inference server whose own pool already owns the whole device (a cudaMalloc from
+// here would fail or eat into a budget the host has promised to its sessions), and token loops with
+// a latency contract, where a device allocation can stall the GPU at an arbitrary point.  Such a
+// caller still passes x, the packed weight and out, but cannot provide the stream-K workspace that
+// b200_gemm expects in args->scratch / args->counters.
+//
+// What it does instead: the workspace lives in g_gemm_static_ws below, a fixed array that is part of
+// the loaded library image (every GPU that loads the library holds these ~5 MiB until the process
+// exits).  Layout: [kStaticCounterBytes of tile counters][kStaticScratchBytes of fp32 partial tiles].
+// The array name is only meaningful to device code; host code must translate it with
+// cudaGetSymbolAddress, which this function does once per device, with that device current, on the
+// first call made on that device.  That first call does the look-up (and may make the driver load the
+// module), so make it before any stream capture is begun on that device.
+//
+// Limits (checked, B200_ELIMIT with a message otherwise): T <= 16 tokens, at most 2048 output tiles,
+// at most 160 CTAs.  All calls on one device share the one array and it keeps whatever the last call
+// left in it: the counters this call needs are cleared on the stream before the launch, the partial
+// tiles need no clearing (they are written before they are read).  Two calls whose kernels overlap on
+// the GPU (different streams, or different threads/processes on the same device) race on the array;
+// keep calls to this entry point on one stream, or serialise them with events.
+namespace b200 {
+namespace {
+constexpr int kStaticMaxTokens = 16;
+constexpr int kStaticMaxCtas = 160;
+constexpr int kStaticMaxUnits = 2048;
+constexpr size_t kStaticCounterBytes = (size_t)kStaticMaxUnits * sizeof(int);                    // 8 KiB
+constexpr size_t kStaticScratchBytes = (size_t)kStaticMaxCtas * 2 /*slots*/ * 2 /*gate+up*/ *
+                                       kStaticMaxTokens * kTileM * sizeof(float);                // 5 MiB
+static __device__ __align__(256) unsigned char g_gemm_static_ws[kStaticCounterBytes + kStaticScratchBytes];
+
+constexpr int kMaxDevices = 64;
+void* g_static_ws_addr[kMaxDevices] = {nullptr};
+
+// Device address of g_gemm_static_ws on the CURRENT device (resolved once per device).
+int static_ws_for_current_device(void** out) {
+    int dev = 0;
+    B200_CUDA_CHECK(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= kMaxDevices) return fail(B200_ELIMIT, "b200_gemm_static_scratch: device index %d > %d", dev, kMaxDevices - 1);
+    void* p = __atomic_load_n(&g_static_ws_addr[dev], __ATOMIC_ACQUIRE);
+    if (p == nullptr) {
+        void* resolved = nullptr;
+        B200_CUDA_CHECK(cudaGetSymbolAddress(&resolved, g_gemm_static_ws));
+        if (resolved == nullptr) return fail(B200_ECUDA, "b200_gemm_static_scratch: symbol address is null");
+        // Concurrent first calls resolve the same address; last store wins harmlessly.
+        __atomic_store_n(&g_static_ws_addr[dev], resolved, __ATOMIC_RELEASE);
+        p = resolved;
+    }
+    *out = p;
+    return B200_OK;
+}
+}  // namespace
+}  // namespace b200
+
+extern "C" int b200_gemm_static_scratch(const b200_gemm_args* a, void* stream_) {
+    if (!a) return fail(B200_EINVAL, "b200_gemm_static_scratch: null args");
+    if (a->T > kStaticMaxTokens)
+        return fail(B200_ELIMIT, "b200_gemm_static_scratch: T=%d exceeds the built-in workspace limit of %d tokens "
+                                 "(use b200_gemm with a caller-owned workspace)", a->T, kStaticMaxTokens);
+    if (a->n_tiles > kStaticMaxUnits)
+        return fail(B200_ELIMIT, "b200_gemm_static_scratch: %d output tiles exceed the built-in limit of %d",
+                    a->n_tiles, kStaticMaxUnits);
+    if (sm_count_cached() > kStaticMaxCtas)
+        return fail(B200_ELIMIT, "b200_gemm_static_scratch: %d SMs exceed the %d CTAs the built-in workspace holds",
+                    sm_count_cached(), kStaticMaxCtas);
+    void* ws = nullptr;
+    const int rc = static_ws_for_current_device(&ws);
+    if (rc != B200_OK) return rc;
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    const int n_units = a->n_tiles > 0 ? a->n_tiles : 1;   // T <= 16 -> one token tile per output tile
+    // The counters must read zero when the kernel starts; whatever an earlier (possibly failed) call left is wiped.
+    B200_CUDA_CHECK(cudaMemsetAsync(ws, 0, (size_t)n_units * sizeof(int), stream));
+    b200_gemm_args local = *a;
+    local.counters = static_cast<int32_t*>(ws);
+    local.scratch = reinterpret_cast<float*>(static_cast<unsigned char*>(ws) + kStaticCounterBytes);
+    return b200_gemm(&local, stream_);
+}

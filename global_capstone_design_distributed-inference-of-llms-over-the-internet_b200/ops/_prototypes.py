@@ -19,6 +19,7 @@ class AttnDecodeArgs(C.Structure):
 
 
 PROTOTYPES = [
+    ("b200_gemm_static_scratch", [vp, vp], C.c_int),
     ("b200_attn_decode", [C.POINTER(AttnDecodeArgs), vp], C.c_int),
     ("b200_attn_decode_scratch_bytes", [i32, i32, i32, i32], i64),
     ("b200_rope_append", [vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, i32, i32, vp], C.c_int),

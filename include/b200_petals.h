@@ -85,6 +85,16 @@ int64_t b200_gemm_scratch_bytes(int32_t max_tokens);
 /* Token-tile width the kernel will pick for T tokens (16,32,64,128,256). */
 int32_t b200_gemm_token_tile(int32_t T, int32_t dual);
 
+/* b200_gemm for callers that cannot allocate device memory (no counterpart in the reference, which
+ * has no native code and lets torch allocate freely).  Same arguments and result as b200_gemm, but
+ * args->scratch and args->counters are ignored: the workspace is a fixed ~5 MiB array inside the
+ * library image, resolved per device on the first call made on that device (make that call before
+ * starting a stream capture).  Limits: T <= 16 tokens, <= 2048 output tiles, <= 160 CTAs; beyond
+ * them the call returns B200_ELIMIT.  Calls share the one array: keep them on one stream — kernels
+ * from two calls that overlap on the GPU race on it.  Performs no cudaMalloc/cudaFree. */
+#define B200_GEMM_STATIC_MAX_TOKENS 16
+int b200_gemm_static_scratch(const b200_gemm_args* args, void* stream);
+
 /* ------------------------------------------------------------- attention --
  * Decode: for each of T independent sessions' new tokens, apply RoPE to q and k,
  * append k/v to that session's pre-allocated cache in place (no torch.cat
