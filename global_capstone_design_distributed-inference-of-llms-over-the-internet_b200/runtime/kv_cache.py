@@ -30,6 +30,7 @@ class SessionKV:
     max_len: int
     length: int = 0               # tokens cached so far
     last_used: float = field(default_factory=time.monotonic)
+    limit: Optional[int] = None   # request-level max_length (<= max_len), enforced by the handler
 
     @property
     def n_layers(self) -> int:

@@ -1,0 +1,204 @@
+"""Stage objects: a layer span + its role (first / middle / last) behind one ``forward``.
+
+Mirrors the reference's three classes (src/llama_partition.py:76-474):
+
+    Stage0(full, end)                    embed + blocks [0, end)
+    StageSegment(full, start, end, ...)  blocks [start, end)
+    StageLast(full, start, ...)          blocks [start, L) + final norm + LM head
+
+``forward(x, position_ids, attention_mask, past_key_values, use_cache) -> (out, past)`` keeps
+the reference's argument list, with these deliberate differences: attention is always causal
+(``attention_mask`` is accepted and ignored — SURVEY B1), ``past_key_values`` is the session's
+pre-allocated :class:`SessionKV` (appended in place and returned as ``past``), and the last
+stage computes logits for the final position only (B9).  ``full`` is the :class:`StageWeights`
+returned by ``load_stage_model`` — only the requested span is ever read (the reference loads
+the whole model and prunes it).
+
+Execution back-end: NativeSpan (sm_100a kernels) for fp16/bf16 on a CUDA device, TorchSpan
+otherwise (CPU plumbing config, fp32).
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass
+from typing import Dict, Optional, Tuple
+
+import torch
+
+from ..models.config import ModelConfig, resolve_config
+from ..models.torch_ref import TorchSpan
+from ..weights.loader import load_span
+from .kv_cache import KVCacheManager, SessionKV
+
+
+@dataclass
+class StageWeights:
+    cfg: ModelConfig
+    weights: Dict[str, object]
+    role: str
+    start: int
+    end: int
+    device: torch.device
+    dtype: torch.dtype
+    use_cpu_offload: bool = False
+    model_name: str = ""
+
+    @property
+    def config(self) -> ModelConfig:   # reference code reads `.config`
+        return self.cfg
+
+
+def load_stage_weights(model_name: str, device, role: str, *, start: int = 0, end: Optional[int] = None,
+                       dtype: torch.dtype = torch.float16, use_cpu_offload: bool = False, seed: int = 0,
+                       families=("llama", "gpt2")) -> StageWeights:
+    cfg = resolve_config(model_name)
+    if cfg.family not in families:
+        raise ValueError(f"{model_name}: family {cfg.family!r} is not handled by this module ({families})")
+    role = {"stage0": "stage0", "segment": "segment", "last": "last"}.get(role)
+    if role is None:
+        raise ValueError("role must be one of stage0 / segment / last")
+    if role == "stage0":
+        start, end = 0, int(end if end is not None else cfg.n_layers)
+    elif role == "last":
+        start, end = int(start), cfg.n_layers
+    else:
+        start, end = int(start), int(end if end is not None else cfg.n_layers)
+    if role != "stage0" and start >= end:
+        raise ValueError(f"empty layer span [{start}, {end}) for {model_name} ({cfg.n_layers} layers)")
+    load_dev = torch.device("cpu") if use_cpu_offload else torch.device(device)
+    w = load_span(model_name, cfg, start, end, need_embed=(role == "stage0"), need_head=(role == "last"),
+                  dtype=dtype, device=load_dev, seed=seed)
+    return StageWeights(cfg, w, role, start, end, torch.device(device), dtype, use_cpu_offload, model_name)
+
+
+class _StageBase(torch.nn.Module):
+    role = "segment"
+
+    def __init__(self, full: StageWeights, start: int, end: int, gpu_device=None, keep_layers_on_gpu: int = 0,
+                 kv_capacity: int = 2048, max_batch: int = 8, backend: Optional[str] = None):
+        super().__init__()
+        if (start, end) != (full.start, full.end):
+            raise ValueError(f"stage span [{start},{end}) does not match loaded weights [{full.start},{full.end})")
+        self.cfg, self.start, self.end = full.cfg, start, end
+        self.config = full.cfg
+        self.device = torch.device(gpu_device) if gpu_device is not None else full.device
+        self.dtype = full.dtype
+        self.keep_layers_on_gpu = keep_layers_on_gpu
+        self.use_cpu_offload = full.use_cpu_offload
+        self.kv_capacity = kv_capacity
+        native_ok = self.device.type == "cuda" and self.dtype in (torch.float16, torch.bfloat16) \
+            and not full.use_cpu_offload
+        self.backend = backend or ("native" if native_ok else "torch")
+        if self.backend == "native":
+            from .native_span import NativeSpan
+
+            self.span = NativeSpan(self.cfg, full.weights, self.device, self.dtype, kv_capacity=kv_capacity,
+                                   max_batch=max_batch)
+        elif full.use_cpu_offload and self.device.type == "cuda":
+            from .offload import OffloadedSpan
+
+            self.span = OffloadedSpan(self.cfg, full.weights, self.device, self.dtype,
+                                      keep_layers_on_gpu=keep_layers_on_gpu)
+        else:
+            w = full.weights
+            if self.device != full.device or full.use_cpu_offload:
+                w = _to_device(w, self.device)
+            self.span = TorchSpan(self.cfg, w, self.device, self.dtype)
+
+    # ---- KV helpers (the handler owns the manager; tests may let the stage own one)
+    def new_kv_manager(self, **kw) -> KVCacheManager:
+        return KVCacheManager(self.end - self.start, self.cfg.n_kv_heads, self.cfg.head_dim, self.dtype,
+                              self.device, default_max_length=self.kv_capacity, **kw)
+
+    @staticmethod
+    def _pos0(position_ids, kv: SessionKV) -> int:
+        if position_ids is None:
+            return kv.length
+        return int(position_ids.reshape(-1)[0])
+
+    def _run_blocks(self, h: torch.Tensor, kv: SessionKV, pos0: int) -> torch.Tensor:
+        if pos0 != kv.length:
+            kv.rollback(pos0)                      # start_from_position semantics
+        return self.span.forward(h, kv, pos0)
+
+    def parameters(self, recurse: bool = True):   # reference probes next(stage.parameters()).dtype
+        yield torch.empty(0, dtype=self.dtype, device=self.device)
+
+
+def _to_device(w, device):
+    out = {}
+    for k, v in w.items():
+        if k == "layers":
+            out[k] = [{kk: vv.to(device) for kk, vv in L.items()} for L in v]
+        elif torch.is_tensor(v):
+            out[k] = v.to(device)
+        else:
+            out[k] = v
+    return out
+
+
+class Stage0(_StageBase):
+    role = "stage0"
+
+    def __init__(self, full: StageWeights, end: int, **kw):
+        super().__init__(full, 0, end, **kw)
+
+    @torch.inference_mode()
+    def forward(self, input_ids, position_ids=None, attention_mask=None, past_key_values: SessionKV = None,
+                use_cache: bool = True) -> Tuple[torch.Tensor, SessionKV]:
+        kv = past_key_values
+        ids = input_ids.reshape(-1).to(self.device)
+        pos0 = self._pos0(position_ids, kv)
+        if pos0 != kv.length:
+            kv.rollback(pos0)
+        if self.backend == "native":
+            if self.end == 0:
+                raise ValueError("native Stage0 needs at least one block")
+            if ids.numel() == 1:
+                h = self.span.decode([kv], ids=ids).clone()
+            else:
+                h = self.span.prefill(kv, ids=ids, pos0=pos0)
+        else:
+            h = self.span.embed(ids, pos0)
+            h = self.span.forward(h, kv, pos0) if self.end > 0 else h
+            if self.end == 0:
+                kv.length = pos0 + ids.numel()
+        return h.unsqueeze(0), kv
+
+
+class StageSegment(_StageBase):
+    role = "segment"
+
+    @torch.inference_mode()
+    def forward(self, hidden_states, position_ids=None, attention_mask=None, past_key_values: SessionKV = None,
+                use_cache: bool = True) -> Tuple[torch.Tensor, SessionKV]:
+        kv = past_key_values
+        h = hidden_states.reshape(-1, self.cfg.hidden).to(self.device, self.dtype)
+        h = self._run_blocks(h, kv, self._pos0(position_ids, kv))
+        return h.unsqueeze(0), kv
+
+
+class StageLast(_StageBase):
+    role = "last"
+
+    def __init__(self, full: StageWeights, start: int, **kw):
+        super().__init__(full, start, full.cfg.n_layers, **kw)
+
+    @torch.inference_mode()
+    def forward(self, hidden_states, position_ids=None, attention_mask=None, past_key_values: SessionKV = None,
+                use_cache: bool = True) -> Tuple[torch.Tensor, SessionKV]:
+        """-> (logits [1, 1, V] fp32 of the LAST position, kv)."""
+        kv = past_key_values
+        h = hidden_states.reshape(-1, self.cfg.hidden).to(self.device, self.dtype)
+        pos0 = self._pos0(position_ids, kv)
+        if pos0 != kv.length:
+            kv.rollback(pos0)
+        if self.backend == "native":
+            if h.shape[0] == 1:
+                logits, _ = self.span.decode([kv], h_in=h, greedy=True)
+            else:
+                logits, _ = self.span.prefill(kv, h_in=h, pos0=pos0)
+            logits = logits[:1].clone()
+        else:
+            h = self.span.forward(h, kv, pos0)
+            logits = self.span.head(h[-1:])
+        return logits.unsqueeze(0), kv

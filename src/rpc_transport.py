@@ -1,0 +1,322 @@
+"""Client side of the data plane: discover, route, call, journal, recover
+(reference: src/rpc_transport.py:45-863).
+
+``RpcTransport`` sends the client's hidden states through the server stages and returns the
+sampled token.  Two routing modes, as in the reference:
+
+* ``"stage"``  — fixed keys ``mini_petals:stage1..N``; any live peer under a key may serve it
+  (one of the 5 freshest is picked at random).
+* ``"module"`` — load-balanced: starting at ``start_block`` pick, per hop, the announced span
+  that covers the current block and reaches furthest (ties: higher throughput), until the
+  final stage.
+
+Fault tolerance: every tensor sent to a hop is journaled on the CPU; when a call fails the peer
+is excluded, a replacement is discovered, the journal is replayed into it to rebuild its KV
+cache and the call is retried (at most 3 attempts).  Fixes over the reference:
+the in-flight step is NOT part of the replay (the reference replays it and then sends it
+again, so the new server sees the token twice), and in module mode the whole route suffix is
+recomputed from the failed hop's first block and replayed end to end, so span boundaries stay
+aligned.  With ``push=True`` servers forward activations to the next hop themselves (chain
+topology; one client round trip per token instead of one per stage).
+"""
+from __future__ import annotations
+
+import logging
+import random
+import statistics
+import time
+from typing import Dict, List, Optional, Sequence, Tuple
+
+import torch
+
+from petals_b200.net.dht import DHT, parse_maddr
+from petals_b200.net.rpc import RpcClient, RpcError
+
+from .dht_utils import get_block_entries, get_stage_entries
+from .rpc_handler import HANDLER_PREFIX
+
+logger = logging.getLogger(__name__)
+
+MAX_ATTEMPTS = 3
+FRESHEST = 5
+
+
+class Hop:
+    """One server on the route: where it is and which journal feeds it."""
+
+    def __init__(self, key: str, entry: dict, final: bool, start_block: Optional[int] = None,
+                 end_block: Optional[int] = None):
+        self.key, self.entry, self.final = key, entry, final
+        self.peer_id = str(entry.get("peer_id"))
+        host, port, _ = parse_maddr((entry.get("p2p_maddrs") or [""])[0])
+        self.addr = (host, port)
+        self.start_block, self.end_block = start_block, end_block
+
+
+class RpcTransport:
+    def __init__(self, device=None, stage: int = 0, dht_initial_peers: Optional[Sequence[str]] = None,
+                 dht_port: int = 0, rpc_port: int = 0, temperature: float = 1.0, top_p: float = 0.92, top_k: int = 50,
+                 stage_keys: Optional[Sequence[str]] = None, routing: str = "stage", model_name: str = "default",
+                 total_blocks: int = 32, start_block: int = 0, request_timeout: float = 30.0,
+                 repetition_penalty: Optional[float] = None, dht: Optional[DHT] = None, push: bool = False):
+        self.device = device
+        self.temperature, self.top_p, self.top_k = temperature, top_p, top_k
+        self.repetition_penalty = repetition_penalty
+        self.stage_keys = list(stage_keys or [])
+        self.routing = routing
+        self.model_name, self.total_blocks, self.start_block = model_name, total_blocks, start_block
+        self.request_timeout = request_timeout
+        self.push = push
+        peers = [p for p in (dht_initial_peers or []) if p]
+        for p in peers:
+            if ":" in p and "/p2p/" not in p and not p.startswith("/"):
+                raise ValueError(f"initial peer {p!r} must be a full multiaddr (/ip4/../tcp/../p2p/..)")
+        self._own_dht = dht is None
+        self.dht = dht or DHT(start=True, initial_peers=peers, client_mode=True)
+        self.client = RpcClient()
+        self.failed_peers: Dict[str, set] = {}
+        self.session_routes: Dict[str, List[Hop]] = {}
+        # journal[session][hop key] = tensors sent to that hop, in order
+        self.client_cache: Dict[str, Dict[str, List[torch.Tensor]]] = {}
+        self.session_max_length: Dict[str, int] = {}
+        self.last_token: Optional[int] = None
+        self.hop_times: List[Tuple[str, float]] = []
+        self.last_prefill_total: Optional[float] = None
+        self.last_decode_total: Optional[float] = None
+        self.decode_totals: List[float] = []
+        self.recoveries = 0
+        logger.info("RpcTransport initialized")
+
+    # ------------------------------------------------------------------ discovery / routing
+    def _pick_stage_peer(self, key: str, exclude: set) -> Optional[dict]:
+        stage = int(key.rsplit("stage", 1)[-1])
+        entries = [e for e in get_stage_entries(self.dht, stage) if str(e.get("peer_id")) not in exclude
+                   and e.get("p2p_maddrs")]
+        if not entries:
+            return None
+        entries.sort(key=lambda e: e.get("timestamp", 0), reverse=True)
+        return random.choice(entries[:FRESHEST])
+
+    def _discover_stage(self, key: str, exclude: set, tries: int = 10, delay: float = 0.5) -> dict:
+        for _ in range(tries):
+            e = self._pick_stage_peer(key, exclude)
+            if e is not None:
+                return e
+            time.sleep(delay)
+        raise ConnectionError(f"no live peer under {key} (excluded {len(exclude)})")
+
+    def _module_route(self, from_block: int, exclude: set) -> List[Hop]:
+        hops: List[Hop] = []
+        b = from_block
+        while b < self.total_blocks:
+            cands = [e for e in get_block_entries(self.dht, b, self.model_name)
+                     if str(e.get("peer_id")) not in exclude and e.get("p2p_maddrs")
+                     and e.get("state", "online") != "offline"
+                     and e.get("start_block") is not None and int(e["start_block"]) <= b < int(e["end_block"])]
+            # a replacement must START at b: its cache holds nothing for blocks before b otherwise
+            aligned = [e for e in cands if int(e["start_block"]) == b]
+            if not aligned:
+                raise ConnectionError(f"no live server starts at block {b} of {self.model_name}")
+            best = max(aligned, key=lambda e: (int(e["end_block"]), float(e.get("throughput") or 0.0)))
+            end = int(best["end_block"])
+            hops.append(Hop(f"block_{b}", best, final=bool(best.get("final_stage")) or end >= self.total_blocks,
+                            start_block=b, end_block=end))
+            b = end
+        return hops
+
+    def _get_route(self, session_id: str) -> List[Hop]:
+        route = self.session_routes.get(session_id)
+        if route is None:
+            if self.routing == "module":
+                route = self._module_route(self.start_block, set())
+            else:
+                route = []
+                for i, key in enumerate(self.stage_keys):
+                    e = self._discover_stage(key, self.failed_peers.get(key, set()))
+                    route.append(Hop(key, e, final=(i == len(self.stage_keys) - 1)))
+            self.session_routes[session_id] = route
+        return route
+
+    # ------------------------------------------------------------------ calls
+    def _metadata(self, session_id: str, T: int, cur_len: int, is_prefill: bool, generated: Optional[Sequence[int]],
+                  is_replay: bool = False) -> dict:
+        md = {"session_id": session_id, "seq_len": int(T), "cur_len": int(cur_len), "is_prefill": bool(is_prefill),
+              "max_length": int(self.session_max_length.get(session_id, 0) or 0) or None,
+              "temperature": self.temperature, "top_p": self.top_p, "top_k": self.top_k}
+        if md["max_length"] is None:
+            del md["max_length"]
+        if generated is not None and not is_prefill:
+            md["generated_tokens"] = [int(t) for t in list(generated)[-50:]]
+        if is_replay:
+            md["is_replay"] = True
+        if self.repetition_penalty is not None:
+            md["repetition_penalty"] = float(self.repetition_penalty)
+        return md
+
+    def _call(self, hop: Hop, tensor: torch.Tensor, md: dict):
+        return self.client.call(hop.addr, f"{HANDLER_PREFIX}.rpc_forward", hop.key, [tensor], md,
+                                timeout=self.request_timeout)
+
+    def _journal(self, session_id: str, key: str) -> List[torch.Tensor]:
+        return self.client_cache.setdefault(session_id, {}).setdefault(key, [])
+
+    def _replay(self, session_id: str, hops: List[Hop], first_key: str) -> None:
+        """Rebuild the KV caches of ``hops`` (a route suffix) from the journal of its first hop."""
+        past = list(self._journal(session_id, first_key))
+        if not past:
+            return
+        logger.info("replaying %d journaled steps into %d hop(s)", len(past), len(hops))
+        for k in [h.key for h in hops[1:]]:
+            self.client_cache[session_id][k] = []        # re-recorded below
+        cur_len = 0
+        for i, t in enumerate(past):
+            T = t.shape[-2]
+            cur_len += T
+            x = t
+            for j, hop in enumerate(hops):
+                if hop.final:
+                    md = self._metadata(session_id, T, cur_len, i == 0, None, is_replay=True)
+                    md["temperature"] = 0.0              # the token of a replayed step is discarded
+                    self._call(hop, x, md)
+                    break
+                if j > 0:
+                    self._journal(session_id, hop.key).append(x.clone())
+                md = self._metadata(session_id, T, cur_len, i == 0, None, is_replay=True)
+                out, _ = self._call(hop, x, md)
+                x = out[0]
+
+    def _send(self, session_id: str, hidden: torch.Tensor, cur_len: int, is_prefill: bool,
+              generated: Optional[Sequence[int]]) -> int:
+        cur = hidden.detach().to("cpu")
+        T = cur.shape[-2]
+        route = self._get_route(session_id)
+        t_all = time.perf_counter()
+        i = 0
+        while i < len(route):
+            hop = route[i]
+            md = self._metadata(session_id, T, cur_len, is_prefill, generated)
+            if self.push and not hop.final:
+                md["route"] = [[h.addr[0], h.addr[1], h.key] for h in route[i + 1:]]
+            attempt = 0
+            while True:
+                t0 = time.perf_counter()
+                try:
+                    out, omd = self._call(hop, cur, md)
+                    break
+                except (TimeoutError, ConnectionError, RpcError, RuntimeError, ValueError) as e:
+                    attempt += 1
+                    logger.warning("hop %s (%s) failed: %s", hop.key, hop.peer_id[:12], e)
+                    if attempt >= MAX_ATTEMPTS:
+                        raise
+                    if self.push:
+                        # the error may come from any server down the chain: find the first dead one
+                        # and continue hop by hop from where the chain is known to be intact
+                        dead = self._find_dead_hop(route, i)
+                        self.push_fallbacks = getattr(self, "push_fallbacks", 0) + 1
+                        md.pop("route", None)
+                        if dead is not None and dead > i:
+                            # hops [i, dead) consumed the step already: rebuild them too by treating
+                            # hop i as the recovery point (replay is idempotent: prefill resets caches)
+                            self.failed_peers.setdefault(route[dead].key, set()).add(route[dead].peer_id)
+                            e2 = None
+                            if self.routing == "module":
+                                excl = set().union(*self.failed_peers.values())
+                                route = route[:i] + self._module_route(hop.start_block, excl)
+                            else:
+                                e2 = self._discover_stage(route[dead].key, self.failed_peers[route[dead].key], tries=5)
+                                route = route[:dead] + [Hop(route[dead].key, e2, route[dead].final)] + route[dead + 1:]
+                            self.session_routes[session_id] = route
+                            self._replay(session_id, route[i:], route[i].key)
+                            hop = route[i]
+                            self.recoveries += 1
+                            self.push = False          # finish this session hop by hop
+                            time.sleep(0.2)
+                            continue
+                    self.failed_peers.setdefault(hop.key, set()).add(hop.peer_id)
+                    logger.info("Marked peer %s as failed for %s", hop.peer_id[:12], hop.key)
+                    route, hop = self._recover(session_id, route, i)
+                    if self.push and not hop.final:
+                        md["route"] = [[h.addr[0], h.addr[1], h.key] for h in route[i + 1:]]
+                    time.sleep(0.2)
+            # journal only what the server has actually consumed
+            self._journal(session_id, hop.key).append(cur.clone())
+            self.hop_times.append((hop.key, time.perf_counter() - t0))
+            if "token_id" in omd or hop.final or (self.push and "token_id" in omd):
+                self.last_token = int(omd.get("token_id", out[0].reshape(-1)[0].item()))
+                break
+            cur = out[0]
+            i += 1
+        total = time.perf_counter() - t_all
+        if is_prefill:
+            self.last_prefill_total = total
+        else:
+            self.last_decode_total = total
+            self.decode_totals.append(total)
+        return self.last_token
+
+    def _find_dead_hop(self, route: List[Hop], i: int) -> Optional[int]:
+        for j in range(i, len(route)):
+            try:
+                self.client.call(route[j].addr, f"{HANDLER_PREFIX}.rpc_info", route[j].key, [], {}, timeout=2.0)
+            except Exception:  # noqa: BLE001
+                return j
+        return None
+
+    def _recover(self, session_id: str, route: List[Hop], i: int) -> Tuple[List[Hop], Hop]:
+        self.recoveries += 1
+        hop = route[i]
+        if self.routing == "module":
+            excl = set().union(*self.failed_peers.values()) if self.failed_peers else set()
+            suffix = self._module_route(hop.start_block, excl)
+            route = route[:i] + suffix
+            self.session_routes[session_id] = route
+            self._replay(session_id, suffix, suffix[0].key)
+        else:
+            e = self._discover_stage(hop.key, self.failed_peers.get(hop.key, set()), tries=5)
+            new = Hop(hop.key, e, hop.final)
+            route = route[:i] + [new] + route[i + 1:]
+            self.session_routes[session_id] = route
+            self._replay(session_id, [new] if not new.final else [new], new.key)
+        return route, route[i]
+
+    # ------------------------------------------------------------------ public API (reference names)
+    def send_prefill(self, L: int, hidden: torch.Tensor, session_id: str, max_length: int) -> None:
+        self.session_max_length[session_id] = int(max_length)
+        self._send(session_id, hidden, L, True, None)
+
+    def send_decode_step(self, cur_len: int, hidden: torch.Tensor, session_id: str, max_length: int,
+                         generated_tokens: Optional[Sequence[int]] = None) -> None:
+        self.session_max_length.setdefault(session_id, int(max_length))
+        self._send(session_id, hidden, cur_len, False, generated_tokens)
+
+    def recv_token(self) -> int:
+        if self.last_token is None:
+            raise RuntimeError("no token received yet")
+        return self.last_token
+
+    def close_session(self, session_id: str) -> None:
+        for hop in self.session_routes.pop(session_id, []):
+            try:
+                self.client.call(hop.addr, f"{HANDLER_PREFIX}.rpc_close_session", hop.key, [],
+                                 {"session_id": session_id}, timeout=5.0)
+            except Exception:  # noqa: BLE001 - best effort
+                pass
+        self.client_cache.pop(session_id, None)
+        self.session_max_length.pop(session_id, None)
+
+    def server_info(self, session_id: str) -> List[dict]:
+        return [self.client.call(h.addr, f"{HANDLER_PREFIX}.rpc_info", h.key, [], {}, timeout=5.0)[1]
+                for h in self._get_route(session_id)]
+
+    def latency_summary(self) -> Dict[str, float]:
+        d = self.decode_totals
+        if not d:
+            return {}
+        s = sorted(d)
+        return {"decode_p50_ms": statistics.median(s) * 1e3, "decode_p99_ms": s[min(len(s) - 1, int(0.99 * len(s)))] * 1e3,
+                "decode_mean_ms": sum(s) / len(s) * 1e3, "steps": len(s)}
+
+    def shutdown(self) -> None:
+        self.client.close()
+        if self._own_dht:
+            self.dht.shutdown()
