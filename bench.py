@@ -172,6 +172,8 @@ def run_b200(args):
         launches = int(t.item())
 
     # ---------------------------------------------------------------- end-to-end through the public API
+    eng.drain()
+    barrier()
     if eng.is_first:
         eng._tok_host[:S].copy_(eng._tok[:S])
         cur = [int(x) for x in eng._tok_host[:S]]

@@ -72,8 +72,15 @@ class PipelineEngine:
                                  default_max_length=kv_capacity)
         self.sessions: List[SessionKV] = []
         H = self.cfg.hidden
-        self._hid = torch.empty(max_sessions, H, dtype=dtype, device=self.device)
+        # per-slot staging buffers: [0] = received from the previous stage, [1] = sent to the next
+        self._hid = torch.empty(2, max_sessions, H, dtype=dtype, device=self.device)
         self._tok = torch.zeros(max_sessions, dtype=torch.int64, device=self.device)
+        self._tok_send = torch.zeros(max_sessions, dtype=torch.int64, device=self.device)
+        # Hidden states flow on the default group, token ids return on a second communicator:
+        # with one communicator the ring (last -> first) closes a cycle of in-order NCCL ops.
+        self.tok_group = dist.new_group() if self.world > 1 else None
+        self._send_work = [None] * max_sessions
+        self._tok_work = [None] * max_sessions
         self._tok_host = torch.zeros(max_sessions, dtype=torch.int64)
         if self.device.type == "cuda":
             self._tok_host = self._tok_host.pin_memory()
@@ -93,11 +100,16 @@ class PipelineEngine:
         self.sessions = []
 
     # ------------------------------------------------------------------ p2p helpers
-    def _send(self, t: torch.Tensor, dst: int) -> None:
-        dist.send(t, dst)
+    def _send(self, t: torch.Tensor, dst: int, group=None) -> None:
+        dist.send(t, dst, group=group)
 
-    def _recv(self, t: torch.Tensor, src: int) -> None:
-        dist.recv(t, src)
+    def _recv(self, t: torch.Tensor, src: int, group=None) -> None:
+        dist.recv(t, src, group=group)
+
+    @staticmethod
+    def _wait(work) -> None:
+        if work is not None:
+            work.wait()
 
     # ------------------------------------------------------------------ per-stage compute
     def _stage_prefill(self, kv: SessionKV, ids: Optional[torch.Tensor], h: Optional[torch.Tensor]):
@@ -145,12 +157,12 @@ class PipelineEngine:
         if self.is_last:
             tok.copy_(out[1].reshape(-1)[:1])
             if not self.is_first:
-                self._send(tok, 0)
+                self._send(tok, 0, self.tok_group)
         else:
             self._send(out.contiguous(), self.rank + 1)
         if self.is_first:
             if not self.is_last:
-                self._recv(tok, self.world - 1)
+                self._recv(tok, self.world - 1, self.tok_group)
             self.d2h_bytes += 8
             return int(tok.cpu()[0])
         return None
@@ -174,28 +186,47 @@ class PipelineEngine:
             out = self._stage_decode(kvs, self._tok[:S], None)
             self._tok[:S].copy_(out[1].reshape(-1)[:S])
         else:
+            # Asynchronous chain: sends never block the compute stream, receives are waited on right
+            # before use, and every slot j has its own staging buffers so a send may still be in
+            # flight while the next session is computed.
+            last = self.world - 1
             for j, si in enumerate(sess):
                 kv = [self.sessions[si]]
                 if self.is_first:
+                    self._wait(self._tok_work[j])                     # token of slot j from the previous round
+                    self._tok_work[j] = None
                     out = self._stage_decode(kv, self._tok[j:j + 1], None)
-                    self._send(out[:1].contiguous(), 1)
+                    self._wait(self._send_work[j])
+                    self._hid[1, j:j + 1].copy_(out[:1])
+                    self._send_work[j] = dist.isend(self._hid[1, j:j + 1], 1)
+                    self._tok_work[j] = dist.irecv(self._tok[j:j + 1], last, group=self.tok_group)
                 else:
-                    h = self._hid[j:j + 1]
-                    self._recv(h, self.rank - 1)
+                    h = self._hid[0, j:j + 1]
+                    dist.irecv(h, self.rank - 1).wait()
                     out = self._stage_decode(kv, None, h)
+                    self._wait(self._send_work[j])
                     if self.is_last:
-                        self._tok[j:j + 1].copy_(out[1].reshape(-1)[:1])
-                        self._send(self._tok[j:j + 1], 0)
+                        self._tok_send[j:j + 1].copy_(out[1].reshape(-1)[:1])
+                        self._send_work[j] = dist.isend(self._tok_send[j:j + 1], 0, group=self.tok_group)
                     else:
-                        self._send(out[:1].contiguous(), self.rank + 1)
-            if self.is_first:
+                        self._hid[1, j:j + 1].copy_(out[:1])
+                        self._send_work[j] = dist.isend(self._hid[1, j:j + 1], self.rank + 1)
+            if self.is_first and (to_host or tokens is not None):
                 for j in range(S):
-                    self._recv(self._tok[j:j + 1], self.world - 1)
+                    self._wait(self._tok_work[j])
+                    self._tok_work[j] = None
         if self.is_first and to_host:
             self._tok_host[:S].copy_(self._tok[:S])
             self.d2h_bytes += 8 * S
             return [int(x) for x in self._tok_host[:S]]
         return None
+
+    def drain(self) -> None:
+        """Wait for every outstanding p2p operation (call before reading staging buffers directly)."""
+        for lst in (self._send_work, self._tok_work):
+            for j, w in enumerate(lst):
+                self._wait(w)
+                lst[j] = None
 
     def generate(self, prompts: Sequence[torch.Tensor], max_new_tokens: int, eos_token_id: Optional[int] = None):
         """Greedy generation for a batch of prompts (one session each).  Returns, on rank 0,

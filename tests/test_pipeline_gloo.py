@@ -1,0 +1,65 @@
+"""PipelineEngine host logic with gloo on CPU (world size 2 and 3): the chain must reproduce
+the single-process result token for token."""
+import os
+import socket
+import sys
+
+import pytest
+import torch
+import torch.multiprocessing as mp
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _worker(rank, world, port, model, splits, q):
+    sys.path.insert(0, ROOT)
+    import torch.distributed as dist
+
+    from petals_b200.parallel.pipeline import PipelineEngine
+
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    torch.set_num_threads(1)
+    eng = PipelineEngine(model, splits, torch.float32, torch.device("cpu"), kv_capacity=64, max_sessions=4, seed=5)
+    g = torch.Generator().manual_seed(0)
+    prompts = [torch.randint(0, eng.cfg.vocab, (n,), generator=g) for n in (5, 9, 3)]
+    res = eng.generate(prompts, 6)
+    if rank == 0:
+        q.put(res[0])
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def _single(model):
+    sys.path.insert(0, ROOT)
+    from petals_b200.parallel.pipeline import PipelineEngine
+
+    eng = PipelineEngine(model, [], torch.float32, torch.device("cpu"), kv_capacity=64, max_sessions=4, seed=5)
+    g = torch.Generator().manual_seed(0)
+    prompts = [torch.randint(0, eng.cfg.vocab, (n,), generator=g) for n in (5, 9, 3)]
+    return eng.generate(prompts, 6)[0]
+
+
+@pytest.mark.parametrize("model,splits", [("tiny-llama-gqa", [2]), ("tiny-gpt2", [1, 3])])
+def test_chain_equals_single_process(model, splits):
+    ref = _single(model)
+    world = len(splits) + 1
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker, args=(r, world, port, model, splits, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    out = q.get(timeout=180)
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    assert out == ref
