@@ -92,9 +92,11 @@ class NativeSpan:
             self.attn_ws = A.DecodeAttnWorkspace(self.device, self.max_batch, c.n_heads, c.n_kv_heads, c.head_dim,
                                                  self.splits)
             self.kv_ptrs = torch.zeros(max(nl, 1), self.max_batch, 2, dtype=torch.int64, device=self.device)
-            self.kv_ptrs_host = torch.zeros(max(nl, 1), self.max_batch, 2, dtype=torch.int64).pin_memory()
             self.pos = torch.zeros(self.max_batch, dtype=torch.int32, device=self.device)
-            self.pos_host = torch.zeros(self.max_batch, dtype=torch.int32).pin_memory()
+            self._pos_ring = [(torch.zeros(self.max_batch, dtype=torch.int32).pin_memory(), torch.cuda.Event())
+                              for _ in range(8)]
+            self._pos_ring_idx = 0
+            self._ptr_tables: Dict[tuple, torch.Tensor] = {}
             if self.has_head:
                 self.logits = mk(self.max_batch, c.vocab, dt=torch.float32)
                 self.ids_out = torch.zeros(self.max_batch, dtype=torch.int64, device=self.device)
@@ -157,25 +159,44 @@ class NativeSpan:
 
     # ------------------------------------------------------------------ decode
     def _stage_ptrs(self, kvs: Sequence[SessionKV]) -> None:
-        key = tuple(id(k.data) for k in kvs)
+        """Point the static kv_ptrs / pos buffers (read by the captured graph) at these sessions.
+
+        Pointer tables are cached on the device per session tuple (keyed by the caches' device
+        addresses, which fully determine the table) and copied device-to-device; positions go
+        through a small ring of pinned staging buffers guarded by events, because a pinned buffer
+        must not be rewritten while an earlier asynchronous copy from it is still queued.
+        """
+        B = len(kvs)
+        key = tuple(kv.data.data_ptr() for kv in kvs)
         if key != self._ptr_key:
-            B = len(kvs)
-            for b, kv in enumerate(kvs):
-                if kv.max_len != self.kv_capacity:
-                    raise ValueError(f"session capacity {kv.max_len} != engine kv_capacity {self.kv_capacity}")
-                base = kv.data.data_ptr()
-                per_layer = kv.data.stride(0) * kv.data.element_size()
-                half = kv.data.stride(1) * kv.data.element_size()
-                for li in range(self.n_layers):
-                    self.kv_ptrs_host[li, b, 0] = base + li * per_layer
-                    self.kv_ptrs_host[li, b, 1] = base + li * per_layer + half
-            self.kv_ptrs[:, :B].copy_(self.kv_ptrs_host[:, :B], non_blocking=True)
+            tab = self._ptr_tables.get(key)
+            if tab is None:
+                host = torch.zeros(max(self.n_layers, 1), B, 2, dtype=torch.int64)
+                for b, kv in enumerate(kvs):
+                    if kv.max_len != self.kv_capacity:
+                        raise ValueError(f"session capacity {kv.max_len} != engine kv_capacity {self.kv_capacity}")
+                    base = kv.data.data_ptr()
+                    per_layer = kv.data.stride(0) * kv.data.element_size()
+                    half = kv.data.stride(1) * kv.data.element_size()
+                    for li in range(self.n_layers):
+                        host[li, b, 0] = base + li * per_layer
+                        host[li, b, 1] = base + li * per_layer + half
+                tab = host.to(self.device)
+                if len(self._ptr_tables) > 256:
+                    self._ptr_tables.clear()
+                self._ptr_tables[key] = tab
+            self.kv_ptrs[:, :B].copy_(tab)
             self._ptr_key = key
+        slot = self._pos_ring_idx
+        self._pos_ring_idx = (slot + 1) % len(self._pos_ring)
+        host, ev = self._pos_ring[slot]
+        ev.synchronize()
         for b, kv in enumerate(kvs):
             if kv.length + 1 > kv.max_len:
                 raise ValueError(f"session {kv.session_id}: max_length {kv.max_len} reached")
-            self.pos_host[b] = kv.length
-        self.pos[: len(kvs)].copy_(self.pos_host[: len(kvs)], non_blocking=True)
+            host[b] = kv.length
+        self.pos[:B].copy_(host[:B], non_blocking=True)
+        ev.record(torch.cuda.current_stream(self.device))
 
     def _decode_body(self, B: int, from_ids: bool, greedy: bool):
         h = self._embed(B, 0, True) if from_ids else self.h_a[:B]
