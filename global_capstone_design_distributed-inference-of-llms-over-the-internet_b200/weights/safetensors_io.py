@@ -14,6 +14,8 @@ import os
 import struct
 from typing import Dict, Iterable, List, Optional
 
+import warnings
+
 import torch
 
 _DTYPES = {
@@ -49,7 +51,9 @@ class SafetensorsFile:
         buf = memoryview(self._mm)[self._base + b: self._base + e]
         if e == b:
             return torch.empty(info["shape"], dtype=dt)
-        t = torch.frombuffer(buf, dtype=dt)
+        with warnings.catch_warnings():
+            warnings.simplefilter("ignore", UserWarning)   # read-only mmap view; nothing writes through it
+            t = torch.frombuffer(buf, dtype=dt)
         return t.view(info["shape"])
 
     def close(self):

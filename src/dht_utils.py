@@ -142,6 +142,9 @@ def update_server_throughput_on_dht(dht: DHT, peer_id, throughput: float, model_
 
 
 def announce_offline(dht: DHT, peer_id, block_indices: Sequence[int], model_name: str = "default", **kw) -> bool:
-    """Graceful shutdown announcement (upstream server.py:650); records lapse 5 s later."""
+    """Graceful shutdown announcement (upstream server.py:650).
+
+    A DHT record only yields to one with a LATER expiration, so the OFFLINE marker carries a full
+    TTL; readers skip OFFLINE entries, and the marker lapses on its own afterwards."""
     return register_blocks_on_dht(dht, peer_id, block_indices, model_name, state=ServerState.OFFLINE,
-                                  expiration_time=get_dht_time() + 5.0, **kw)
+                                  expiration_time=get_dht_time() + DEFAULT_TTL, **kw)

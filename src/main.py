@@ -208,6 +208,7 @@ def start_stage_server(args, device, stage_model, final_stage: bool, stage_index
                                      seed=getattr(args, "seed", None))
     stop = threading.Event()
     model_name = args.model
+    handler.on_die = lambda: (stop.set(), rpc.stop())   # scripted kill (tests / kill_stage.py --soft)
 
     def publish():
         exp = get_dht_time() + RECORD_TTL

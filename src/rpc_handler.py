@@ -62,6 +62,9 @@ class StageConnectionHandler:
         self.requests = 0
         self.started = time.time()
         self.fail_next = 0   # fault injection (tests): raise on the next N forwards
+        self.die_after: Optional[int] = None   # fault injection: "crash" while serving request number N
+        self.on_die = None                     # callable that tears the server down (set by the launcher)
+        self.die_guard = None                  # optional callable -> bool, consulted right before crashing
 
     # ------------------------------------------------------------------ registration
     def add_p2p_handlers(self, server: RpcServer) -> None:
@@ -108,6 +111,12 @@ class StageConnectionHandler:
         if self.fail_next > 0:
             self.fail_next -= 1
             raise RuntimeError("injected failure")
+        if self.die_after is not None and self.requests + 1 >= self.die_after and \
+                (self.die_guard is None or self.die_guard()):
+            self.die_after = None
+            if self.on_die is not None:
+                threading.Thread(target=self.on_die, daemon=True).start()
+            raise ConnectionError("injected crash")
         T = hidden_states.shape[-2] if hidden_states.dim() >= 2 else 1
         sid, kv = self._session_for(metadata, T)
         pos_ids = torch.arange(kv.length, kv.length + T, dtype=torch.long).unsqueeze(0)

@@ -103,6 +103,14 @@ class RpcTransport:
             if e is not None:
                 return e
             time.sleep(delay)
+        if exclude:
+            # every announced peer has failed at least once: failures may have been transient, so
+            # forgive them rather than giving up while live records are still being refreshed
+            logger.warning("all peers under %s are excluded; clearing the exclusion list", key)
+            exclude.clear()
+            e = self._pick_stage_peer(key, exclude)
+            if e is not None:
+                return e
         raise ConnectionError(f"no live peer under {key} (excluded {len(exclude)})")
 
     def _module_route(self, from_block: int, exclude: set) -> List[Hop]:
@@ -272,7 +280,7 @@ class RpcTransport:
             self.session_routes[session_id] = route
             self._replay(session_id, suffix, suffix[0].key)
         else:
-            e = self._discover_stage(hop.key, self.failed_peers.get(hop.key, set()), tries=5)
+            e = self._discover_stage(hop.key, self.failed_peers.setdefault(hop.key, set()), tries=2)
             new = Hop(hop.key, e, hop.final)
             route = route[:i] + [new] + route[i + 1:]
             self.session_routes[session_id] = route

@@ -1,0 +1,155 @@
+"""DHT TTL/sub-key semantics, RPC codec, KV manager, weights loader, task pool."""
+import json
+import os
+import time
+
+import pytest
+import torch
+
+
+def test_dht_ttl_subkeys_and_merge():
+    from petals_b200.net.dht import DHT, PeerID, get_dht_time, parse_maddr
+
+    a = DHT(start=True, host_maddrs=["/ip4/127.0.0.1/tcp/0"])
+    m = a.get_visible_maddrs()
+    host, port, pid = parse_maddr(m[0])
+    assert host == "127.0.0.1" and port > 0 and pid == str(a.peer_id)
+    b = DHT(start=True, initial_peers=m, client_mode=True)
+    now = get_dht_time()
+    assert b.store("k", {"v": 1}, now + 0.3, subkey="p1")
+    assert b.store("k", {"v": 2}, now + 10, subkey="p2")
+    assert not b.store("k", {"v": 0}, now - 1, subkey="p3")               # already expired
+    assert not a.store("k", {"v": 9}, now + 5, subkey="p2")               # older expiration loses
+    rec = a.get("k", latest=True)
+    assert {k: v.value["v"] for k, v in rec.value.items()} == {"p1": 1, "p2": 2}
+    time.sleep(0.35)
+    assert list(b.get("k").value) == ["p2"]                               # entries expire individually
+    assert a.store("plain", 5, now + 10) and b.get("plain").value == 5
+    assert a.get("missing") is None
+    p = PeerID.generate()
+    assert PeerID.from_base58(p.to_base58()) == p and hash(PeerID.from_base58(str(p))) == hash(p)
+    a.shutdown()
+    assert list(b.get("k").value) == ["p2"]                               # every node keeps what it stored itself
+    b.shutdown()
+
+
+def test_dht_registry_roundtrip():
+    from petals_b200.net.dht import DHT
+    from src import dht_utils as du
+    from src.load_balancing import ServerState, compute_spans, compute_throughputs
+
+    d = DHT(start=True, host_maddrs=["/ip4/127.0.0.1/tcp/0"])
+    assert du.get_module_key(3, "meta/llama") == "petals:module:meta/llama:block_3"
+    assert du.get_server_key("Qm1", "m") == "petals:server:m:Qm1"
+    du.register_blocks_on_dht(d, "peerA", range(8, 16), "m", ["/ip4/127.0.0.1/tcp/1/p2p/peerA"], 8, 16, 10.0)
+    du.register_blocks_on_dht(d, "peerB", range(8, 12), "m", ["/ip4/127.0.0.1/tcp/2/p2p/peerB"], 8, 12, 5.0)
+    du.register_server_on_dht(d, "peerA", 8, 16, 10.0, "m")
+    infos = du.get_remote_module_infos(d, "m", 16)
+    spans = compute_spans(infos)
+    assert (spans["peerA"].start, spans["peerA"].end) == (8, 16) and spans["peerB"].length == 4
+    assert compute_throughputs(spans, 16).tolist() == [0] * 8 + [15] * 4 + [10] * 4
+    assert du.update_server_throughput_on_dht(d, "peerA", 20.0, "m")
+    assert d.get(du.get_server_key("peerA", "m")).value["throughput"] == 20.0
+    du.announce_offline(d, "peerB", range(8, 12), "m")
+    infos = du.get_remote_module_infos(d, "m", 16)
+    assert "peerB" not in compute_spans(infos)                            # OFFLINE servers are ignored
+    du.register_stage_on_dht(d, 2, "peerA", ["/ip4/127.0.0.1/tcp/1/p2p/peerA"])
+    assert du.get_stage_entries(d, 2)[0]["stage"] == 2
+    d.shutdown()
+
+
+def test_kv_manager_budget_ttl_rollback():
+    from petals_b200.runtime.kv_cache import AllocationFailed, KVCacheManager
+
+    m = KVCacheManager(2, 2, 8, torch.float32, "cpu", max_tokens=100, session_ttl=0.2)
+    a = m.allocate("a", 40)
+    b = m.allocate("b", 40)
+    assert m.tokens_left == 20 and a.data.shape == (2, 2, 2, 40, 8)
+    with pytest.raises(AllocationFailed):
+        m.allocate("c", 40)
+    a.length = 10
+    a.rollback(4)
+    assert a.length == 4
+    with pytest.raises(ValueError):
+        a.rollback(9)
+    assert m.allocate("a", 30) is a and a.length == 0                      # re-prefill reuses the buffer
+    time.sleep(0.25)
+    assert m.evict_expired() == 2 and m.tokens_left == 100
+    c = m.allocate("c", 100)
+    assert m.close("c") and not m.close("c")
+    assert m.bytes_per_token() == 2 * 2 * 2 * 8 * 4
+
+
+def test_safetensors_roundtrip_and_span_selective_loading(tmp_path):
+    from petals_b200.models.config import PRESETS
+    from petals_b200.weights.loader import CheckpointSource, full_hf_state_dict, load_span
+    from petals_b200.weights.safetensors_io import SafetensorsFile, save_file
+
+    cfg = PRESETS["tiny-llama"]
+    sd = full_hf_state_dict(cfg, seed=2, dtype=torch.float16)
+    d = tmp_path / "ckpt"
+    d.mkdir()
+    # two shards + index: blocks 0-1 in shard A, the rest in shard B
+    a = {k: v for k, v in sd.items() if ".layers.0." in k or ".layers.1." in k or "embed" in k}
+    b = {k: v for k, v in sd.items() if k not in a}
+    save_file(a, str(d / "model-00001-of-00002.safetensors"))
+    save_file(b, str(d / "model-00002-of-00002.safetensors"), metadata={"format": "pt"})
+    wm = {k: "model-00001-of-00002.safetensors" for k in a}
+    wm.update({k: "model-00002-of-00002.safetensors" for k in b})
+    json.dump({"weight_map": wm}, open(d / "model.safetensors.index.json", "w"))
+    json.dump(cfg.to_hf_dict(), open(d / "config.json", "w"))
+    f = SafetensorsFile(str(d / "model-00002-of-00002.safetensors"))
+    assert f.metadata == {"format": "pt"} and torch.equal(f.get("model.norm.weight"), sd["model.norm.weight"])
+    src = CheckpointSource(str(d))
+    w = load_span(str(d), cfg, 0, 2, need_embed=True, need_head=False, dtype=torch.float16, device="cpu", src=src)
+    assert src.index.shards_opened == ["model-00001-of-00002.safetensors"]   # only the shard holding blocks 0-1
+    q = sd["model.layers.1.self_attn.q_proj.weight"]
+    assert torch.equal(w["layers"][1]["qkv_w"][: q.shape[0]], q)
+    # checkpoint == seeded random init of the same seed
+    from petals_b200.models.config import resolve_config
+
+    assert resolve_config(str(d)).hidden == cfg.hidden
+    w2 = load_span("tiny-llama", cfg, 2, 4, need_embed=False, need_head=True, dtype=torch.float16, device="cpu", seed=2)
+    w3 = load_span(str(d), cfg, 2, 4, need_embed=False, need_head=True, dtype=torch.float16, device="cpu")
+    assert torch.equal(w2["layers"][0]["down_w"], w3["layers"][0]["down_w"]) and torch.equal(w2["lm_head"], w3["lm_head"])
+
+
+def test_gpt2_conv1d_transpose_and_tied_head():
+    from petals_b200.models.config import PRESETS
+    from petals_b200.weights.loader import full_hf_state_dict, load_span
+
+    cfg = PRESETS["tiny-gpt2"]
+    sd = full_hf_state_dict(cfg, seed=1)
+    w = load_span("tiny-gpt2", cfg, 0, 1, need_embed=True, need_head=True, dtype=torch.float32, device="cpu", seed=1)
+    assert torch.equal(w["layers"][0]["qkv_w"], sd["h.0.attn.c_attn.weight"].t())
+    assert w["lm_head"] is w["embed"] and w["pos_embed"].shape == (cfg.max_positions, cfg.hidden)
+
+
+def test_task_pool_priorities():
+    from petals_b200.runtime.task_pool import PrioritizedTaskPool
+
+    pool = PrioritizedTaskPool("t", max_task_tokens=10)
+    order = []
+    gate = pool.submit(lambda: time.sleep(0.1))
+    f1 = pool.submit(lambda: order.append("fwd"), kind="forward")
+    f2 = pool.submit(lambda: order.append("inf"), kind="inference")
+    f1.result(2), f2.result(2), gate.result(2)
+    assert order == ["inf", "fwd"]                                         # inference (1.0) beats forward (2.0)
+    with pytest.raises(ValueError):
+        pool.submit(lambda: None, tokens=11)
+    bad = pool.submit(lambda: 1 / 0)
+    with pytest.raises(ZeroDivisionError):
+        bad.result(2)
+    pool.shutdown()
+
+
+def test_rope_llama3_scaling_matches_hf():
+    import transformers
+    from petals_b200.models.config import PRESETS
+    from petals_b200.ops.attention import rope_inv_freq
+
+    cfg = PRESETS["llama-3.1-8b"]
+    hf_cfg = transformers.LlamaConfig(**{k: v for k, v in cfg.to_hf_dict().items() if k not in ("model_type", "architectures")})
+    rot = transformers.models.llama.modeling_llama.LlamaRotaryEmbedding(hf_cfg)
+    ours = rope_inv_freq(cfg.head_dim, cfg.rope_theta, cfg.rope_scaling)
+    assert torch.allclose(ours, rot.inv_freq.float(), rtol=1e-5, atol=1e-9)

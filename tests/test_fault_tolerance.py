@@ -1,0 +1,105 @@
+"""Kill-a-stage rerouting with exact continuation (the reference's manual test_fault_tolerance.py
++ kill_stage.py, scripted).  Two replicas serve every stage; mid-generation the replica in use dies
+(server stopped => connection refused) or drops one request; the client must exclude it, replay the
+journal into the other replica — WITHOUT the in-flight step — and produce exactly the
+tokens of an undisturbed run."""
+import threading
+
+import pytest
+import torch
+
+from tests.test_cpu_pipeline import _args
+
+
+def _start(model, splits, cuts, stage, peers, seed=11):
+    from src.main import run_stage_server_fixed
+
+    return run_stage_server_fixed(_args(model, splits, stage, peers, seed=seed), torch.device("cpu"), cuts, block=False)
+
+
+@pytest.mark.parametrize("routing_push", [False, True])
+def test_stage_kill_and_replay_is_token_exact(routing_push):
+    from src.main import parse_splits, run_rank0
+
+    model, splits = "tiny-llama-gqa", "1,3"
+    cuts = parse_splits(splits)
+    dev = torch.device("cpu")
+    handles = []
+    try:
+        first = _start(model, splits, cuts, 1, "")
+        peers = first.dht.get_visible_maddrs()[0]
+        handles = [first, _start(model, splits, cuts, 2, peers), _start(model, splits, cuts, 1, peers),
+                   _start(model, splits, cuts, 2, peers)]
+        n_new = 10
+        ref, _ = run_rank0(_args(model, splits, 0, peers, seed=11, max_new_tokens=n_new), dev, cuts)
+
+        # whichever stage-2 replica the next run picks "crashes" while serving its 3rd request
+        finals = [h for h in handles if h.handler.final_stage]
+        fired = []
+        for h in finals:
+            h.handler.die_after = h.handler.requests + 3
+            h.handler.die_guard = lambda: (not fired) and (fired.append(1) or True)   # only one replica dies
+        out, stats = run_rank0(_args(model, splits, 0, peers, seed=11, max_new_tokens=n_new, push=routing_push,
+                                     request_timeout=5.0), dev, cuts)
+        killed = [h for h in finals if h.handler.die_after is None]
+        assert killed, "the fault was never injected"
+        assert stats["recoveries"] >= 1
+        assert out == ref, "continuation after recovery must be token-exact"
+    finally:
+        for h in handles:
+            try:
+                h.stop()
+            except Exception:
+                pass
+
+
+def test_dropped_request_is_retried_without_duplicate_token():
+    from src.main import parse_splits, run_rank0
+
+    model, splits = "tiny-gpt2", "2"
+    cuts = parse_splits(splits)
+    dev = torch.device("cpu")
+    h1 = _start(model, splits, cuts, 1, "")
+    peers = h1.dht.get_visible_maddrs()[0]
+    h2 = _start(model, splits, cuts, 1, peers)
+    try:
+        ref, _ = run_rank0(_args(model, splits, 0, peers, seed=11, max_new_tokens=8), dev, cuts)
+        h1.handler.fail_next = 1
+        h2.handler.fail_next = 1     # whichever replica is chosen fails once with a server-side error
+        out, stats = run_rank0(_args(model, splits, 0, peers, seed=11, max_new_tokens=8), dev, cuts)
+        assert out == ref and stats["recoveries"] >= 1
+    finally:
+        h1.stop()
+        h2.stop()
+
+
+def test_kv_length_mismatch_is_an_error_not_a_warning():
+    """The reference only warns when cur_len disagrees with the cached length (B4)."""
+    from petals_b200.net.rpc import RpcClient, RpcError
+    from src.main import parse_splits
+
+    model, splits = "tiny-gpt2", "2"
+    cuts = parse_splits(splits)
+    h = _start(model, splits, cuts, 1, "")
+    try:
+        c = RpcClient()
+        x = torch.randn(1, 4, 128)
+        md = {"session_id": "s", "seq_len": 4, "cur_len": 4, "is_prefill": True, "max_length": 32, "temperature": 0.0}
+        c.call(h.rpc.address, "StageConnectionHandler.rpc_forward", "k", [x], md)
+        bad = dict(md, is_prefill=False, seq_len=1, cur_len=9)
+        with pytest.raises(RpcError, match="KV length mismatch"):
+            c.call(h.rpc.address, "StageConnectionHandler.rpc_forward", "k", [x[:, :1]], bad)
+        ok = dict(md, is_prefill=False, seq_len=1, cur_len=5)
+        c.call(h.rpc.address, "StageConnectionHandler.rpc_forward", "k", [x[:, :1]], ok)
+        over = dict(md, is_prefill=True, seq_len=4, cur_len=4, max_length=3)
+        with pytest.raises(RpcError, match="max_length"):
+            c.call(h.rpc.address, "StageConnectionHandler.rpc_forward", "k", [x], over)
+        _, info = c.call(h.rpc.address, "StageConnectionHandler.rpc_info", "k", [], {})
+        assert info["sessions"] >= 1 and info["final_stage"] is True
+        _, r = c.call(h.rpc.address, "StageConnectionHandler.rpc_close_session", "k", [], {"session_id": "s"})
+        assert r["closed"] is True
+        with pytest.raises(RpcError, match="Missing past_key_values"):
+            c.call(h.rpc.address, "StageConnectionHandler.rpc_forward", "k", [x[:, :1]], ok)
+        c.close()
+    finally:
+        h.stop()
