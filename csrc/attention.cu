@@ -5,249 +5,9 @@
 //   b200_attn_prefill  causal attention of a chunk against the session cache.
 // Decode attention is KV-bandwidth bound (one query per session), so it runs on the
 // CUDA cores with 16-byte loads; the tensor-core path is the prefill kernel's job.
-#include "common.h"
-#include "ptx.cuh"
+#include "attn_core.cuh"
 
 namespace b200 {
-
-struct AttnDecodeParams {
-    const uint16_t* __restrict__ qkv;
-    uint16_t* __restrict__ out;
-    const unsigned long long* __restrict__ kv_ptrs;  // [T][2]
-    const int* __restrict__ pos;                     // [T]
-    const float* __restrict__ inv_freq;              // [D/2] or null
-    float* __restrict__ scratch;                     // [T][n_heads][splits][D+2]
-    int* __restrict__ counters;                      // [T][n_kv]
-    int T, n_heads, n_kv, s_max, splits, ldqkv, ldo;
-    float scale;
-    int is_bf16;
-};
-
-constexpr int kAttnThreads = 128;
-constexpr int kMinRowsPerSplit = 64;
-
-__device__ __forceinline__ void unpack8(const uint4& v, float (&f)[8], int is_bf16) {
-    const uint32_t w[4] = {v.x, v.y, v.z, v.w};
-#pragma unroll
-    for (int i = 0; i < 4; ++i) {
-        f[2 * i] = h16_to_float((uint16_t)(w[i] & 0xffff), is_bf16);
-        f[2 * i + 1] = h16_to_float((uint16_t)(w[i] >> 16), is_bf16);
-    }
-}
-__device__ __forceinline__ uint4 pack8(const float (&f)[8], int is_bf16) {
-    uint32_t w[4];
-#pragma unroll
-    for (int i = 0; i < 4; ++i)
-        w[i] = (uint32_t)float_to_h16(f[2 * i], is_bf16) | ((uint32_t)float_to_h16(f[2 * i + 1], is_bf16) << 16);
-    return make_uint4(w[0], w[1], w[2], w[3]);
-}
-
-// Rotates one head vector held as (lo = dims [c, c+8), hi = dims [c+D/2, c+D/2+8)).
-// HF convention: out = x*cos + rotate_half(x)*sin with cos/sin rounded to the model dtype.
-__device__ __forceinline__ void rope8(float (&lo)[8], float (&hi)[8], int c, int pos, const float* inv_freq,
-                                      int is_bf16) {
-#pragma unroll
-    for (int i = 0; i < 8; ++i) {
-        float sn, cs;
-        sincosf((float)pos * inv_freq[c + i], &sn, &cs);
-        cs = h16_to_float(float_to_h16(cs, is_bf16), is_bf16);
-        sn = h16_to_float(float_to_h16(sn, is_bf16), is_bf16);
-        const float a = lo[i], b = hi[i];
-        lo[i] = a * cs - b * sn;
-        hi[i] = b * cs + a * sn;
-    }
-}
-
-// One CTA = (token t, kv head g, split s).  LPR = D/8 lanes cooperate on one KV row.
-template <int D, int GROUP>
-__global__ void __launch_bounds__(kAttnThreads) attn_decode_kernel(const AttnDecodeParams p) {
-    constexpr int LPR = D / 8;          // lanes per row: 16 (D=128) or 8 (D=64)
-    constexpr int RPW = 32 / LPR;       // rows per warp per step: 2 or 4
-    constexpr int NW = kAttnThreads / 32;
-    __shared__ float s_q[GROUP][D];
-    __shared__ float s_m[NW][GROUP], s_l[NW][GROUP];
-    __shared__ float s_o[NW][GROUP][D];
-    __shared__ int s_last;
-
-    const int splits = p.splits;
-    int bid = blockIdx.x;
-    const int s = bid % splits; bid /= splits;
-    const int g = bid % p.n_kv;
-    const int t = bid / p.n_kv;
-    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-
-    pdl_wait_prior_grid();
-    pdl_launch_dependents();
-
-    const int pos = p.pos[t];
-    const int len = pos + 1;  // keys visible to the new token, itself included
-    int eff = (len + kMinRowsPerSplit - 1) / kMinRowsPerSplit;
-    if (eff > splits) eff = splits;
-    if (s >= eff) return;
-    const int chunk = (len + eff - 1) / eff;
-    const int r_begin = s * chunk;
-    const int r_end = min(len, r_begin + chunk);
-
-    uint16_t* kbase = reinterpret_cast<uint16_t*>(p.kv_ptrs[2 * t]) + (size_t)g * p.s_max * D;
-    uint16_t* vbase = reinterpret_cast<uint16_t*>(p.kv_ptrs[2 * t + 1]) + (size_t)g * p.s_max * D;
-    const uint16_t* row = p.qkv + (size_t)t * p.ldqkv;
-    const int q_off = g * GROUP * D;
-    const int k_off = p.n_heads * D + g * D;
-    const int v_off = (p.n_heads + p.n_kv) * D + g * D;
-
-    // ---- q (RoPE'd, pre-scaled) -> smem; new k/v -> cache (by the split that owns `pos`)
-    // D/2/8 threads per head vector, each owning dims [c, c+8) and [c+D/2, c+D/2+8).
-    constexpr int TPH = D / 16;
-    for (int item = tid; item < (GROUP + 1) * TPH; item += kAttnThreads) {
-        const int h = item / TPH, c = (item % TPH) * 8;
-        const bool is_k = (h == GROUP);
-        if (is_k && !(pos >= r_begin && pos < r_end)) continue;
-        const uint16_t* src = row + (is_k ? k_off : q_off + h * D);
-        float lo[8], hi[8];
-        unpack8(*reinterpret_cast<const uint4*>(src + c), lo, p.is_bf16);
-        unpack8(*reinterpret_cast<const uint4*>(src + c + D / 2), hi, p.is_bf16);
-        if (p.inv_freq) rope8(lo, hi, c, pos, p.inv_freq, p.is_bf16);
-        if (is_k) {
-            *reinterpret_cast<uint4*>(kbase + (size_t)pos * D + c) = pack8(lo, p.is_bf16);
-            *reinterpret_cast<uint4*>(kbase + (size_t)pos * D + c + D / 2) = pack8(hi, p.is_bf16);
-            // v is copied verbatim alongside
-            *reinterpret_cast<uint4*>(vbase + (size_t)pos * D + c) = *reinterpret_cast<const uint4*>(row + v_off + c);
-            *reinterpret_cast<uint4*>(vbase + (size_t)pos * D + c + D / 2) =
-                *reinterpret_cast<const uint4*>(row + v_off + c + D / 2);
-        } else {
-#pragma unroll
-            for (int i = 0; i < 8; ++i) {
-                // round through the storage type like the unfused path (q is stored after RoPE)
-                s_q[h][c + i] = h16_to_float(float_to_h16(lo[i], p.is_bf16), p.is_bf16) * p.scale;
-                s_q[h][c + D / 2 + i] = h16_to_float(float_to_h16(hi[i], p.is_bf16), p.is_bf16) * p.scale;
-            }
-        }
-    }
-    __syncthreads();
-
-    // ---- online-softmax pass over this split's rows
-    const int sub = lane / LPR;         // which of the warp's RPW rows
-    const int dl = (lane % LPR) * 8;    // this lane's 8 dims
-    float q[GROUP][8], acc[GROUP][8], m[GROUP], l[GROUP];
-#pragma unroll
-    for (int h = 0; h < GROUP; ++h) {
-        m[h] = -INFINITY;
-        l[h] = 0.f;
-#pragma unroll
-        for (int i = 0; i < 8; ++i) { q[h][i] = s_q[h][dl + i]; acc[h][i] = 0.f; }
-    }
-    constexpr int UNROLL = 4;
-    for (int r0 = r_begin + warp * RPW * UNROLL; r0 < r_end; r0 += NW * RPW * UNROLL) {
-        uint4 kraw[UNROLL], vraw[UNROLL];
-#pragma unroll
-        for (int j = 0; j < UNROLL; ++j) {
-            const int r = r0 + j * RPW + sub;
-            if (r < r_end) {
-                kraw[j] = *reinterpret_cast<const uint4*>(kbase + (size_t)r * D + dl);
-                vraw[j] = *reinterpret_cast<const uint4*>(vbase + (size_t)r * D + dl);
-            } else {
-                kraw[j] = make_uint4(0, 0, 0, 0);
-                vraw[j] = make_uint4(0, 0, 0, 0);
-            }
-        }
-#pragma unroll
-        for (int j = 0; j < UNROLL; ++j) {
-            const int r = r0 + j * RPW + sub;
-            const bool valid = r < r_end;
-            float kf[8], vf[8];
-            unpack8(kraw[j], kf, p.is_bf16);
-            unpack8(vraw[j], vf, p.is_bf16);
-#pragma unroll
-            for (int h = 0; h < GROUP; ++h) {
-                float sc = 0.f;
-#pragma unroll
-                for (int i = 0; i < 8; ++i) sc += q[h][i] * kf[i];
-#pragma unroll
-                for (int o = LPR / 2; o > 0; o >>= 1) sc += __shfl_xor_sync(0xffffffffu, sc, o);
-                if (valid) {
-                    const float mn = fmaxf(m[h], sc);
-                    const float corr = __expf(m[h] - mn);
-                    const float pr = __expf(sc - mn);
-                    l[h] = l[h] * corr + pr;
-#pragma unroll
-                    for (int i = 0; i < 8; ++i) acc[h][i] = acc[h][i] * corr + pr * vf[i];
-                    m[h] = mn;
-                }
-            }
-        }
-    }
-    // ---- merge the RPW row-groups of a warp, then the warps, then the splits
-#pragma unroll
-    for (int h = 0; h < GROUP; ++h) {
-#pragma unroll
-        for (int o = LPR; o < 32; o <<= 1) {
-            const float m2 = __shfl_xor_sync(0xffffffffu, m[h], o);
-            const float l2 = __shfl_xor_sync(0xffffffffu, l[h], o);
-            const float mn = fmaxf(m[h], m2);
-            const float c1 = (m[h] == -INFINITY) ? 0.f : __expf(m[h] - mn);
-            const float c2 = (m2 == -INFINITY) ? 0.f : __expf(m2 - mn);
-            l[h] = l[h] * c1 + l2 * c2;
-#pragma unroll
-            for (int i = 0; i < 8; ++i) {
-                const float a2 = __shfl_xor_sync(0xffffffffu, acc[h][i], o);
-                acc[h][i] = acc[h][i] * c1 + a2 * c2;
-            }
-            m[h] = mn;
-        }
-        if (lane < LPR) {
-            if (lane == 0) { s_m[warp][h] = m[h]; s_l[warp][h] = l[h]; }
-#pragma unroll
-            for (int i = 0; i < 8; ++i) s_o[warp][h][dl + i] = acc[h][i];
-        }
-    }
-    __syncthreads();
-    // thread -> (head, dim) pairs
-    float* my_part = p.scratch + ((size_t)(t * p.n_heads + g * GROUP) * splits + s) * (D + 2);
-    for (int idx = tid; idx < GROUP * D; idx += kAttnThreads) {
-        const int h = idx / D, d = idx % D;
-        float mm = -INFINITY;
-#pragma unroll
-        for (int w = 0; w < NW; ++w) mm = fmaxf(mm, s_m[w][h]);
-        float ll = 0.f, oo = 0.f;
-#pragma unroll
-        for (int w = 0; w < NW; ++w) {
-            const float c = (s_m[w][h] == -INFINITY) ? 0.f : __expf(s_m[w][h] - mm);
-            ll += s_l[w][h] * c;
-            oo += s_o[w][h][d] * c;
-        }
-        if (eff == 1) {
-            p.out[(size_t)t * p.ldo + (g * GROUP + h) * D + d] = float_to_h16(oo / ll, p.is_bf16);
-        } else {
-            float* dst = my_part + (size_t)h * splits * (D + 2);
-            dst[d] = oo;
-            if (d == 0) { dst[D] = mm; dst[D + 1] = ll; }
-        }
-    }
-    if (eff == 1) return;
-    __threadfence();
-    __syncthreads();
-    if (tid == 0) {
-        const int old = atomicAdd(&p.counters[t * p.n_kv + g], 1);
-        s_last = (old + 1 == eff) ? 1 : 0;
-    }
-    __syncthreads();
-    if (!s_last) return;
-    __threadfence();
-    for (int idx = tid; idx < GROUP * D; idx += kAttnThreads) {
-        const int h = idx / D, d = idx % D;
-        const float* src = p.scratch + ((size_t)(t * p.n_heads + g * GROUP + h) * splits) * (D + 2);
-        float mm = -INFINITY;
-        for (int j = 0; j < eff; ++j) mm = fmaxf(mm, __ldcg(src + (size_t)j * (D + 2) + D));
-        float ll = 0.f, oo = 0.f;
-        for (int j = 0; j < eff; ++j) {
-            const float c = __expf(__ldcg(src + (size_t)j * (D + 2) + D) - mm);
-            ll += __ldcg(src + (size_t)j * (D + 2) + D + 1) * c;
-            oo += __ldcg(src + (size_t)j * (D + 2) + d) * c;
-        }
-        p.out[(size_t)t * p.ldo + (g * GROUP + h) * D + d] = float_to_h16(oo / ll, p.is_bf16);
-    }
-    if (tid == 0) p.counters[t * p.n_kv + g] = 0;
-}
 
 // ------------------------------------------------------------------ rope + append
 struct RopeAppendParams {

@@ -9,107 +9,9 @@
 //                               same warps drain TMEM and run the epilogue
 // The weight ring and the activation ring have independent depths, so the
 // HBM stream (weights) is never throttled by the L2-latency-bound B side.
-#include "common.h"
-#include "ptx.cuh"
+#include "gemm_core.cuh"
 
 namespace b200 {
-
-constexpr int kTileM = 128;            // weight rows per tile (UMMA M)
-constexpr int kBK = 64;                // k elements per block = one 128 B swizzle row
-constexpr int kABytes = kTileM * 128;  // bytes of one packed weight block
-constexpr int kThreads = 192;
-constexpr int kEpiThreads = 128;
-
-template <int BN, int DUAL>
-struct GemmCfg {
-    static constexpr int kAPer = DUAL ? 2 : 1;
-    static constexpr int kBlockA = kABytes * kAPer;       // weight bytes of one k-block
-    // One weight-ring stage = one 32 KiB bulk copy.  The single-thread loader and
-    // MMA loops pay ~100+ ns of barrier latency per stage, so stages must be big.
-    static constexpr int kKps = DUAL ? 1 : 2;              // k-blocks per weight stage
-    static constexpr int kStageA = kBlockA * kKps;         // 32768
-    static constexpr int kSA = (BN <= 16) ? 6 : (BN == 256) ? 3 : 4;
-    static constexpr int kGroup = (BN == 16) ? 4 : (BN == 32) ? 2 : 1;  // k-blocks per activation stage
-    static constexpr int kSubB = BN * 128;                 // one k-block of activations
-    static constexpr int kStageB = kSubB * kGroup;
-    static constexpr int kSB = (BN == 16) ? 3 : (BN == 32) ? 4 : (BN == 64) ? 6 : (BN == 128) ? 4 : 3;
-    static constexpr bool kPrefetch = BN <= 32;            // register double-buffering of the next B stage
-    // Back-to-back tcgen05.mma into ONE accumulator serialise on the tensor-pipe latency
-    // (~180 cycles each when N is tiny), so narrow tiles rotate the four k-steps of a
-    // k-block over independent accumulators that the epilogue adds up.
-    static constexpr int kNAcc = (BN <= 32) ? 4 : (BN == 64) ? 2 : 1;
-    static constexpr int kTmemColsRaw = BN * kAPer * kNAcc;
-    static constexpr int kTmemCols = kTmemColsRaw <= 32 ? 32 : kTmemColsRaw <= 64 ? 64 : kTmemColsRaw <= 128 ? 128 : kTmemColsRaw <= 256 ? 256 : 512;
-    static constexpr int kMinBlocks = 1;
-    static constexpr size_t kSmemData = (size_t)kSA * kStageA + (size_t)kSB * kStageB;
-    static constexpr size_t kSmemBytes = kSmemData + 1024 /*align*/ + 1024 /*barriers, stats*/;
-};
-
-struct GemmParams {
-    const uint8_t* __restrict__ w;
-    const uint16_t* __restrict__ x;
-    void* __restrict__ out;
-    const uint16_t* __restrict__ residual;
-    const uint16_t* __restrict__ bias;
-    const uint16_t* __restrict__ norm_w;
-    const uint16_t* __restrict__ norm_b;
-    float* __restrict__ scratch;
-    int* __restrict__ counters;
-    int T, N, K;
-    int ldx, ldo, ldr;
-    int n_tiles, t_tiles, kbpt;
-    long long Q;  // total k-blocks = n_tiles * t_tiles * kbpt
-    int epilogue, norm_mode;
-    float norm_eps;
-    int is_bf16, out_fp32;
-    int debug;  // experiment switches (scripts/exp_*.py): 1 = no MMA issue, 2 = no B stage waits
-};
-
-__device__ __forceinline__ long long range_begin(const GemmParams& p, int c) {
-    return (long long)c * p.Q / (long long)gridDim.x;
-}
-
-__device__ __forceinline__ float gelu_tanh(float x) {
-    const float k0 = 0.7978845608028654f, k1 = 0.044715f;
-    return 0.5f * x * (1.0f + tanhf(k0 * (x + k1 * x * x * x)));
-}
-
-// Rounds through the 16-bit storage type so fused epilogues see the same values
-// the unfused torch sequence would have stored between ops.
-__device__ __forceinline__ float round16(float v, int is_bf16) {
-    return h16_to_float(float_to_h16(v, is_bf16), is_bf16);
-}
-
-template <int BN, int DUAL>
-__device__ __forceinline__ void epilogue_store_chunk(const GemmParams& p, int n_tile, int t_tile,
-                                                     int row, int chunk, const float (&vg)[16],
-                                                     const float (&vu)[16]) {
-    const int n = n_tile * kTileM + row;
-    if (n >= p.N) return;
-    const float b = p.bias ? h16_to_float(p.bias[n], p.is_bf16) : 0.0f;
-#pragma unroll
-    for (int j = 0; j < 16; ++j) {
-        const int t = t_tile * BN + chunk * 16 + j;
-        if (t >= p.T) break;
-        float v = vg[j] + b;
-        if (DUAL) {
-            const float g = round16(v, p.is_bf16);
-            const float u = round16(vu[j], p.is_bf16);
-            const float s = round16(g / (1.0f + __expf(-g)), p.is_bf16);
-            v = s * u;
-        } else if (p.epilogue == B200_EPI_GELU_TANH) {
-            v = gelu_tanh(round16(v, p.is_bf16));
-        }
-        if (p.residual) {
-            v = round16(v, p.is_bf16) + h16_to_float(p.residual[(size_t)t * p.ldr + n], p.is_bf16);
-        }
-        if (p.out_fp32) {
-            reinterpret_cast<float*>(p.out)[(size_t)t * p.ldo + n] = v;
-        } else {
-            reinterpret_cast<uint16_t*>(p.out)[(size_t)t * p.ldo + n] = float_to_h16(v, p.is_bf16);
-        }
-    }
-}
 
 template <int BN, int DUAL>
 __global__ void __launch_bounds__(kThreads, GemmCfg<BN, DUAL>::kMinBlocks)
@@ -159,7 +61,10 @@ gemm_streamk_kernel(const GemmParams p) {
 
     if (warp == 0) {
         // ------------------------------------------------ weight loader
-        if (lane == 0) {
+        // The whole warp walks the loop (warp-uniform control flow keeps addresses and barriers in
+        // uniform registers); one elected lane issues.  A lane-0-only loop makes ptxas wrap every
+        // bulk copy / MMA in a divergent "waterfall" and roughly halves the per-CTA streaming rate.
+        {
             // Weights never depend on the previous kernel: start streaming at once.
             const uint64_t policy = (p.t_tiles == 1) ? l2_policy_evict_first() : l2_policy_evict_last();
             // (u, kb) walk the global k-block index without divisions in the loop.
@@ -176,9 +81,12 @@ gemm_streamk_kernel(const GemmParams p) {
                 if (n > Cfg::kKps) n = Cfg::kKps;
                 mbar_wait(&a_empty[s], ph ^ 1);
                 const uint32_t bytes = (uint32_t)n * Cfg::kBlockA;
-                mbar_arrive_expect_tx(&a_full[s], bytes);
-                bulk_g2s_hint(smem_a + (size_t)s * Cfg::kStageA, tile_base + (size_t)kb * Cfg::kBlockA, bytes,
-                              &a_full[s], policy);
+                if (elect_one()) {
+                    mbar_arrive_expect_tx(&a_full[s], bytes);
+                    bulk_g2s_hint(smem_a + (size_t)s * Cfg::kStageA, tile_base + (size_t)kb * Cfg::kBlockA, bytes,
+                                  &a_full[s], policy);
+                }
+                __syncwarp();
                 if (++s == SA) { s = 0; ph ^= 1; }
                 left -= n;
                 kb += n;
@@ -189,8 +97,8 @@ gemm_streamk_kernel(const GemmParams p) {
             }
         }
     } else if (warp == 1) {
-        // ------------------------------------------------ MMA issuer
-        if (lane == 0) {
+        // ------------------------------------------------ MMA issuer (whole warp, one elected lane issues)
+        {
             const uint32_t idesc = umma_idesc(kTileM, BN, p.is_bf16, p.is_bf16, 0, 0);
             int u = (int)(q_begin / p.kbpt);
             int kb0 = (int)(q_begin - (long long)u * p.kbpt);
@@ -213,7 +121,7 @@ gemm_streamk_kernel(const GemmParams p) {
                         if (bofs == 0 && !(p.debug & 2)) mbar_wait(&b_full[sb], phb);
                         tc_fence_after();
                         const uint64_t bdesc = umma_desc_kmajor_sw128(b_base + sb * Cfg::kStageB + bofs * Cfg::kSubB, 1024);
-                        if (!(p.debug & 1)) {
+                        if (!(p.debug & 1) && elect_one()) {
 #pragma unroll
                             for (int a = 0; a < APER; ++a) {
                                 const uint64_t adesc = umma_desc_kmajor_sw128(
@@ -228,17 +136,21 @@ gemm_streamk_kernel(const GemmParams p) {
                         }
                         acc = 1;
                         ++bofs;
+                        __syncwarp();
                         if (bofs == Cfg::kGroup || done + j + 1 == nk) {
-                            if (!(p.debug & 2)) umma_commit(&b_empty[sb]);
+                            if (!(p.debug & 2) && elect_one()) umma_commit(&b_empty[sb]);
+                            __syncwarp();
                             bofs = 0;
                             if (++sb == SB) { sb = 0; phb ^= 1; }
                         }
                     }
-                    umma_commit(&a_empty[sa]);
+                    if (elect_one()) umma_commit(&a_empty[sa]);
+                    __syncwarp();
                     if (++sa == SA) { sa = 0; pha ^= 1; }
                     done += na;
                 }
-                umma_commit(acc_full);
+                if (elect_one()) umma_commit(acc_full);
+                __syncwarp();
                 php ^= 1;
                 left -= nk;
                 kb0 = 0;   // every later part starts at the beginning of a tile
@@ -564,6 +476,13 @@ extern "C" int b200_gemm(const b200_gemm_args* a, void* stream_) {
 
     int grid = a->grid > 0 ? a->grid : sm_count_cached();
     if (grid > sm_count_cached()) grid = sm_count_cached();
+    if (a->grid <= 0 && t_tiles == 1) {
+        // Few output tiles (o_proj, down_proj): give every tile the same whole number of CTAs so each
+        // CTA writes one partial and each tile has equally many contributors (measured 17.4 -> 14.1 us
+        // for 4096x4096 at 128 instead of 148 CTAs).
+        const int per_tile = grid / a->n_tiles;
+        if (per_tile >= 2) grid = per_tile * a->n_tiles;
+    }
     if ((long long)grid > p.Q) grid = (int)p.Q;
     cudaStream_t stream = static_cast<cudaStream_t>(stream_);
     const bool pdl = a->pdl != 0;

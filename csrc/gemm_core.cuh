@@ -1,0 +1,107 @@
+// Shared device-side pieces of the tcgen05 GEMM: tile configuration, kernel parameters and the
+// fused epilogue.  Used by the stand-alone stream-K kernel (gemm.cu) and by the persistent
+// multi-op decode kernel (decode_mega.cu).
+#pragma once
+#include "common.h"
+#include "ptx.cuh"
+
+namespace b200 {
+
+constexpr int kTileM = 128;            // weight rows per tile (UMMA M)
+constexpr int kBK = 64;                // k elements per block = one 128 B swizzle row
+constexpr int kABytes = kTileM * 128;  // bytes of one packed weight block
+constexpr int kThreads = 192;
+constexpr int kEpiThreads = 128;
+
+template <int BN, int DUAL>
+struct GemmCfg {
+    static constexpr int kAPer = DUAL ? 2 : 1;
+    static constexpr int kBlockA = kABytes * kAPer;       // weight bytes of one k-block
+    // One weight-ring stage = one 32 KiB bulk copy.  The single-thread loader and
+    // MMA loops pay ~100+ ns of barrier latency per stage, so stages must be big.
+    static constexpr int kKps = DUAL ? 1 : 2;              // k-blocks per weight stage
+    static constexpr int kStageA = kBlockA * kKps;         // 32768
+    static constexpr int kSA = (BN <= 16) ? 6 : (BN == 256) ? 3 : 4;
+    static constexpr int kGroup = (BN == 16) ? 4 : (BN == 32) ? 2 : 1;  // k-blocks per activation stage
+    static constexpr int kSubB = BN * 128;                 // one k-block of activations
+    static constexpr int kStageB = kSubB * kGroup;
+    static constexpr int kSB = (BN == 16) ? 3 : (BN == 32) ? 4 : (BN == 64) ? 6 : (BN == 128) ? 4 : 3;
+    static constexpr bool kPrefetch = BN <= 32;            // register double-buffering of the next B stage
+    // Back-to-back tcgen05.mma into ONE accumulator serialise on the tensor-pipe latency
+    // (~180 cycles each when N is tiny), so narrow tiles rotate the four k-steps of a
+    // k-block over independent accumulators that the epilogue adds up.
+    static constexpr int kNAcc = (BN <= 32) ? 4 : (BN == 64) ? 2 : 1;
+    static constexpr int kTmemColsRaw = BN * kAPer * kNAcc;
+    static constexpr int kTmemCols = kTmemColsRaw <= 32 ? 32 : kTmemColsRaw <= 64 ? 64 : kTmemColsRaw <= 128 ? 128 : kTmemColsRaw <= 256 ? 256 : 512;
+    static constexpr int kMinBlocks = 1;
+    static constexpr size_t kSmemData = (size_t)kSA * kStageA + (size_t)kSB * kStageB;
+    static constexpr size_t kSmemBytes = kSmemData + 1024 /*align*/ + 1024 /*barriers, stats*/;
+};
+
+struct GemmParams {
+    const uint8_t* __restrict__ w;
+    const uint16_t* __restrict__ x;
+    void* __restrict__ out;
+    const uint16_t* __restrict__ residual;
+    const uint16_t* __restrict__ bias;
+    const uint16_t* __restrict__ norm_w;
+    const uint16_t* __restrict__ norm_b;
+    float* __restrict__ scratch;
+    int* __restrict__ counters;
+    int T, N, K;
+    int ldx, ldo, ldr;
+    int n_tiles, t_tiles, kbpt;
+    long long Q;  // total k-blocks = n_tiles * t_tiles * kbpt
+    int epilogue, norm_mode;
+    float norm_eps;
+    int is_bf16, out_fp32;
+    int debug;  // experiment switches (scripts/exp_*.py): 1 = no MMA issue, 2 = no B stage waits
+};
+
+__device__ __forceinline__ long long range_begin(const GemmParams& p, int c) {
+    return (long long)c * p.Q / (long long)gridDim.x;
+}
+
+__device__ __forceinline__ float gelu_tanh(float x) {
+    const float k0 = 0.7978845608028654f, k1 = 0.044715f;
+    return 0.5f * x * (1.0f + tanhf(k0 * (x + k1 * x * x * x)));
+}
+
+// Rounds through the 16-bit storage type so fused epilogues see the same values
+// the unfused torch sequence would have stored between ops.
+__device__ __forceinline__ float round16(float v, int is_bf16) {
+    return h16_to_float(float_to_h16(v, is_bf16), is_bf16);
+}
+
+template <int BN, int DUAL>
+__device__ __forceinline__ void epilogue_store_chunk(const GemmParams& p, int n_tile, int t_tile,
+                                                     int row, int chunk, const float (&vg)[16],
+                                                     const float (&vu)[16]) {
+    const int n = n_tile * kTileM + row;
+    if (n >= p.N) return;
+    const float b = p.bias ? h16_to_float(p.bias[n], p.is_bf16) : 0.0f;
+#pragma unroll
+    for (int j = 0; j < 16; ++j) {
+        const int t = t_tile * BN + chunk * 16 + j;
+        if (t >= p.T) break;
+        float v = vg[j] + b;
+        if (DUAL) {
+            const float g = round16(v, p.is_bf16);
+            const float u = round16(vu[j], p.is_bf16);
+            const float s = round16(g / (1.0f + __expf(-g)), p.is_bf16);
+            v = s * u;
+        } else if (p.epilogue == B200_EPI_GELU_TANH) {
+            v = gelu_tanh(round16(v, p.is_bf16));
+        }
+        if (p.residual) {
+            v = round16(v, p.is_bf16) + h16_to_float(__ldcg(p.residual + (size_t)t * p.ldr + n), p.is_bf16);
+        }
+        if (p.out_fp32) {
+            reinterpret_cast<float*>(p.out)[(size_t)t * p.ldo + n] = v;
+        } else {
+            reinterpret_cast<uint16_t*>(p.out)[(size_t)t * p.ldo + n] = float_to_h16(v, p.is_bf16);
+        }
+    }
+}
+
+}  // namespace b200

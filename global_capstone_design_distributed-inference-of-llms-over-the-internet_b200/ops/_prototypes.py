@@ -18,7 +18,21 @@ class AttnDecodeArgs(C.Structure):
     ]
 
 
+def _mega_op_type():
+    from .native import GemmArgs
+
+    class MegaOp(C.Structure):
+        """Mirror of ``b200_mega_op``."""
+
+        _fields_ = [("type", i32), ("reserved", i32), ("gemm", GemmArgs), ("attn", AttnDecodeArgs)]
+
+    return MegaOp
+
+
 PROTOTYPES = [
+    ("b200_decode_mega_plan_bytes", [i32], i64),
+    ("b200_decode_mega_build", [vp, i32, vp], C.c_int),
+    ("b200_decode_mega_launch", [vp, i32, vp, i32, i32, vp], C.c_int),
     ("b200_gemm_static_scratch", [vp, vp], C.c_int),
     ("b200_attn_decode", [C.POINTER(AttnDecodeArgs), vp], C.c_int),
     ("b200_attn_decode_scratch_bytes", [i32, i32, i32, i32], i64),

@@ -41,6 +41,13 @@ class DecodeAttnWorkspace:
 
 def attn_decode(qkv, out, kv_ptrs, pos, inv_freq, ws: DecodeAttnWorkspace, n_heads, n_kv_heads, head_dim, s_max,
                 scale=None, pdl=False):
+    a = fill_decode_args(qkv, out, kv_ptrs, pos, inv_freq, ws, n_heads, n_kv_heads, head_dim, s_max, scale, pdl)
+    native.check(native.lib().b200_attn_decode(ctypes.byref(a), native.current_stream_ptr()), "b200_attn_decode")
+    return out
+
+
+def fill_decode_args(qkv, out, kv_ptrs, pos, inv_freq, ws, n_heads, n_kv_heads, head_dim, s_max, scale=None,
+                     pdl=False) -> AttnDecodeArgs:
     T = qkv.shape[0]
     assert T <= ws.max_tokens
     a = AttnDecodeArgs()
@@ -52,8 +59,7 @@ def attn_decode(qkv, out, kv_ptrs, pos, inv_freq, ws: DecodeAttnWorkspace, n_hea
     a.splits, a.ldqkv, a.ldo = ws.splits, qkv.stride(0), out.stride(0)
     a.scale = scale if scale is not None else head_dim ** -0.5
     a.dtype, a.pdl = dtype_code(qkv.dtype), 1 if pdl else 0
-    native.check(native.lib().b200_attn_decode(ctypes.byref(a), native.current_stream_ptr()), "b200_attn_decode")
-    return out
+    return a
 
 
 def rope_append(qkv, kcache, vcache, inv_freq, n_heads, n_kv_heads, head_dim, s_max, pos0, pdl=False):

@@ -76,6 +76,17 @@ def linear(
     debug: int = 0,
 ) -> torch.Tensor:
     """x: [T, K] (16-bit, last dim contiguous) -> [T, N]."""
+    a, out = fill_args(x, w, out=out, residual=residual, epilogue=epilogue, norm_mode=norm_mode, norm_w=norm_w,
+                       norm_b=norm_b, norm_eps=norm_eps, out_fp32=out_fp32, workspace=workspace, pdl=pdl, grid=grid,
+                       debug=debug)
+    rc = native.lib().b200_gemm(ctypes.byref(a), native.current_stream_ptr())
+    native.check(rc, "b200_gemm")
+    return out
+
+
+def fill_args(x, w, *, out=None, residual=None, epilogue=EPI_NONE, norm_mode=NORM_NONE, norm_w=None, norm_b=None,
+              norm_eps=1e-5, out_fp32=False, workspace=None, pdl=False, grid=0, debug=0):
+    """Builds the ``b200_gemm_args`` for one call (also used to describe ops of the persistent kernel)."""
     assert x.dim() == 2 and x.stride(1) == 1 and x.is_cuda
     T, K = x.shape
     assert K == w.k_padded, f"activation width {K} != packed K {w.k_padded}"
@@ -109,6 +120,4 @@ def linear(
     a.grid = grid
     a.pdl = 1 if pdl else 0
     a.debug = debug
-    rc = native.lib().b200_gemm(ctypes.byref(a), native.current_stream_ptr())
-    native.check(rc, "b200_gemm")
-    return out
+    return a, out

@@ -41,15 +41,29 @@ def _pdl_default() -> bool:
     return os.environ.get("B200_PDL", "1") != "0"
 
 
+def _mega_default() -> bool:
+    # The persistent multi-op decode kernel is functionally complete and tested, but its per-op
+    # latency chain (grid barrier + stream-K fix-up) currently costs more than the launch gaps it
+    # removes (203 vs 239 tok/s on Llama-2-7B); it stays opt-in until that is fixed.
+    return os.environ.get("B200_MEGA", "0") == "1"
+
+
+MEGA_MAX_TOKENS = 16
+
+
 class NativeSpan:
     def __init__(self, cfg: ModelConfig, weights: Dict[str, object], device, dtype: torch.dtype, *,
                  kv_capacity: int = 2048, max_batch: int = 8, max_chunk: int = 512, attn_splits: int = 0,
-                 use_graphs: bool = True, pdl: Optional[bool] = None, free_source_weights: bool = True):
+                 use_graphs: bool = True, pdl: Optional[bool] = None, free_source_weights: bool = True,
+                 use_mega: Optional[bool] = None, mega_grid: int = 0):
         assert dtype in (torch.float16, torch.bfloat16), "native path runs fp16/bf16"
         self.cfg, self.device, self.dtype = cfg, torch.device(device), dtype
         self.kv_capacity, self.max_batch, self.max_chunk = kv_capacity, min(max_batch, MAX_DECODE_BATCH), max_chunk
         self.use_graphs = use_graphs
         self.pdl = _pdl_default() if pdl is None else pdl
+        self.use_mega = _mega_default() if use_mega is None else use_mega
+        self.mega_grid = mega_grid      # 0 = all SMs; leave a few free when NCCL kernels run concurrently
+        self._mega_plans: Dict[tuple, tuple] = {}
         self.has_embed = bool(weights.get("has_embed", False))
         self.has_head = bool(weights.get("has_head", "lm_head" in weights))
         c = cfg
@@ -200,10 +214,74 @@ class NativeSpan:
 
     def _decode_body(self, B: int, from_ids: bool, greedy: bool):
         h = self._embed(B, 0, True) if from_ids else self.h_a[:B]
+        if self.use_mega and B <= MEGA_MAX_TOKENS:
+            return self._decode_mega(B, h, greedy)
         h = self._decode_layers(B, h)
         if self.has_head:
             self._head(h, greedy)
         return h
+
+    # ------------------------------------------------------------------ persistent decode kernel
+    def _mega_plan(self, B: int):
+        """Op list of one decode step (all blocks [+ LM head]) for the persistent kernel."""
+        plan = self._mega_plans.get(B)
+        if plan is not None:
+            return plan
+        from ..ops import native
+        from ..ops._prototypes import _mega_op_type
+
+        MegaOp = _mega_op_type()
+        c = self.cfg
+        ops = []
+
+        def gemm_op(x, w, **kw):
+            a, _ = G.fill_args(x, w, workspace=self.ws, **kw)
+            op = MegaOp()
+            op.type = 0
+            op.gemm = a
+            ops.append(op)
+
+        h, other = self.h_a[:B], self.h_b[:B]
+        qkv, attn, act = self.qkv[:B], self.attn[:B], self.act[:B]
+        for li, P in enumerate(self.layers):
+            gemm_op(h, P["qkv"], out=qkv, norm_mode=self.norm_mode, norm_w=P["ln1_w"], norm_b=P["ln1_b"],
+                    norm_eps=c.norm_eps)
+            op = MegaOp()
+            op.type = 1
+            op.attn = A.fill_decode_args(qkv, attn, self.kv_ptrs[li], self.pos, self.inv_freq, self.attn_ws, c.n_heads,
+                                         c.n_kv_heads, c.head_dim, self.kv_capacity, self.scale)
+            ops.append(op)
+            gemm_op(attn, P["o"], out=other, residual=h)
+            gemm_op(other, P["mlp_in"], out=act, epilogue=self.mlp_epi, norm_mode=self.norm_mode, norm_w=P["ln2_w"],
+                    norm_b=P["ln2_b"], norm_eps=c.norm_eps)
+            gemm_op(act, P["down"], out=h, residual=other)
+        if self.has_head:
+            gemm_op(h, self.lm_head, out=self.logits[:B], norm_mode=self.norm_mode, norm_w=self.final_norm_w,
+                    norm_b=self.final_norm_b, norm_eps=c.norm_eps, out_fp32=True)
+        n = len(ops)
+        arr = (MegaOp * n)(*ops)
+        L = native.lib()
+        dev_plan = torch.empty(L.b200_decode_mega_plan_bytes(n), dtype=torch.uint8, device=self.device)
+        with torch.cuda.device(self.device):
+            native.check(L.b200_decode_mega_build(arr, n, dev_plan.data_ptr()), "b200_decode_mega_build")
+        if not hasattr(self, "_mega_bar"):
+            self._mega_bar = torch.zeros(1, dtype=torch.int32, device=self.device)
+        plan = (dev_plan, n)
+        self._mega_plans[B] = plan
+        return plan
+
+    def _decode_mega(self, B: int, h: torch.Tensor, greedy: bool):
+        from ..ops import native
+
+        dev_plan, n = self._mega_plan(B)
+        rc = native.lib().b200_decode_mega_launch(dev_plan.data_ptr(), n, self._mega_bar.data_ptr(), self.mega_grid, 1,
+                                                  native.current_stream_ptr())
+        native.check(rc, "b200_decode_mega_launch")
+        self._count()
+        if self.has_head and greedy:
+            E.argmax(self.logits[:B], self.ids_out[:B], self.argmax_ws, pdl=False)
+            self._count()
+        return self.h_a[:B]
 
     def decode(self, kvs: Sequence[SessionKV], h_in: Optional[torch.Tensor] = None,
                ids: Optional[torch.Tensor] = None, greedy: bool = True):

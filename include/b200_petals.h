@@ -131,6 +131,30 @@ int b200_attn_prefill(const void* q, void* out, const void* kcache, const void* 
                       int32_t n_kv_heads, int32_t head_dim, int32_t s_max, int32_t ldq, int32_t ldo, int32_t pos0,
                       float scale, int32_t dtype, int32_t pdl, void* stream);
 
+/* -------------------------------------------------- persistent decode kernel --
+ * One cooperative launch runs a whole chain of decode ops (all blocks of a stage, plus the LM head):
+ * GEMM ops with the same semantics as b200_gemm (T <= 16) and attention ops with the semantics of
+ * b200_attn_decode.  Op i may read anything op i-1 wrote (a grid-wide barrier separates them); the
+ * weight loader runs ahead across op boundaries so HBM never idles.  Replaces the reference's
+ * per-op torch launches inside the layer loop (src/llama_partition.py:233-297) and its 3-op CUDA
+ * graphs (petals/llama/cuda_graphs.py).
+ *   b200_decode_mega_build   validates the op list and writes the device-side plan (synchronous
+ *                            copy into plan_device, which must hold b200_decode_mega_plan_bytes()).
+ *   b200_decode_mega_launch  zeroes *grid_barrier (one int, device) on the stream and launches;
+ *                            grid <= SM count (0 = all SMs); every CTA must be co-resident, so leave
+ *                            SMs free for concurrently running communication kernels if there are any.
+ */
+typedef struct b200_mega_op {
+    int32_t type; /* 0 = GEMM, 1 = attention */
+    int32_t reserved;
+    b200_gemm_args gemm;
+    b200_attn_decode_args attn;
+} b200_mega_op;
+int64_t b200_decode_mega_plan_bytes(int32_t n_ops);
+int b200_decode_mega_build(const b200_mega_op* ops, int32_t n_ops, void* plan_device);
+int b200_decode_mega_launch(const void* plan_device, int32_t n_ops, int32_t* grid_barrier, int32_t grid,
+                            int32_t cooperative, void* stream);
+
 /* ----------------------------------------------------------- elementwise --
  * Embedding gather (+ learned positions for GPT-2): src/llama_partition.py:107.
  * ids are int64 on the device (the last stage writes them there). */

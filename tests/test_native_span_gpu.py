@@ -51,6 +51,22 @@ def test_prefill_then_decode_matches_oracle(name, dtype, graphs):
     assert kn.length == L + 12
 
 
+def test_persistent_decode_kernel_matches_multi_kernel_path():
+    """The one-launch persistent decode kernel must be bit-identical to the per-op launches."""
+    cfg, ref, nat, mref, mnat = _build("tiny-llama-gqa", torch.bfloat16, use_mega=False)
+    _, _, nat2, _, mnat2 = _build("tiny-llama-gqa", torch.bfloat16, use_mega=True)
+    torch.manual_seed(2)
+    ids = torch.randint(0, cfg.vocab, (30,), device="cuda")
+    ka, kb = mnat.allocate("a", 256), mnat2.allocate("a", 256)
+    _, ta = nat.prefill(ka, ids=ids)
+    _, tb = nat2.prefill(kb, ids=ids)
+    assert torch.equal(ta, tb)
+    for _ in range(6):
+        la, ta = nat.decode([ka], ids=ta.clone())
+        lb, tb = nat2.decode([kb], ids=tb.clone())
+        assert torch.equal(la, lb) and torch.equal(ta, tb)
+
+
 def test_batched_decode_equals_single(monkeypatch):
     cfg, ref, nat, mref, mnat = _build("tiny-llama-gqa", torch.bfloat16)
     torch.manual_seed(1)
