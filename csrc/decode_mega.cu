@@ -96,6 +96,7 @@ decode_mega_kernel(const MegaOp* __restrict__ ops, int n_ops, int* __restrict__ 
     volatile int* fin_flag = reinterpret_cast<volatile int*>(tmem_slot + 1);  // [2]
     float* stat_mean = reinterpret_cast<float*>(tmem_slot + 4);               // [16]
     float* stat_rstd = stat_mean + 32;
+    float* stat_red = stat_rstd + 32;   // [4][32]
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int cta = blockIdx.x, G = gridDim.x;
@@ -258,7 +259,7 @@ decode_mega_kernel(const MegaOp* __restrict__ ops, int n_ops, int* __restrict__ 
                 const GemmParams p = ops[oi].g;
                 const int dual = ops[oi].dual;
                 const int aper = dual ? 2 : 1;
-                if (p.norm_mode != B200_NORM_NONE) {
+                if (p.norm_mode == B200_NORM_LAYER) {
                     const int pw = warp - 2;
                     for (int t = pw; t < kMegaBN; t += 4) {
                         float s1 = 0.f, s2 = 0.f;
@@ -295,6 +296,7 @@ decode_mega_kernel(const MegaOp* __restrict__ ops, int n_ops, int* __restrict__ 
                 const long long q_begin = mega_range_begin(p.Q, cta), q_end = mega_range_begin(p.Q, cta + 1);
                 long long q = q_begin;
                 int first_part = 1;
+                bool rms_ready = false;
                 while (q < q_end) {
                     const int u = (int)(q / p.kbpt);
                     const int kb0 = (int)(q - (long long)u * p.kbpt);
@@ -339,8 +341,8 @@ decode_mega_kernel(const MegaOp* __restrict__ ops, int n_ops, int* __restrict__ 
                                             const float g0 = h16_to_float((uint16_t)(win[w] & 0xffff), p.is_bf16);
                                             const float g1 = h16_to_float((uint16_t)(win[w] >> 16), p.is_bf16);
                                             if (p.norm_mode == B200_NORM_RMS) {
-                                                x0 = g0 * round16(x0 * rstd, p.is_bf16);
-                                                x1 = g1 * round16(x1 * rstd, p.is_bf16);
+                                                x0 = g0 * x0;   // 1/rms deferred to the epilogue
+                                                x1 = g1 * x1;
                                             } else {
                                                 const float b0 = h16_to_float((uint16_t)(bin[w] & 0xffff), p.is_bf16);
                                                 const float b1 = h16_to_float((uint16_t)(bin[w] >> 16), p.is_bf16);
@@ -364,6 +366,11 @@ decode_mega_kernel(const MegaOp* __restrict__ ops, int n_ops, int* __restrict__ 
                             for (int g = 0; g < kMegaGroup; ++g) { cur[g] = nxt[g]; cgw[g] = ngw[g]; cgb[g] = ngb[g]; }
                         }
                     }
+                    if (p.norm_mode == B200_NORM_RMS && !rms_ready) {
+                        rms_stats_128(p, min(kMegaBN, p.T), e, stat_red, stat_rstd);
+                        rms_ready = true;
+                    }
+                    const float* tok_scale = (p.norm_mode == B200_NORM_RMS) ? stat_rstd : nullptr;
                     // ---- drain the accumulators of this part
                     const bool full_tile = (kb0 == 0) && (kb1 == p.kbpt);
                     const int slot = first_part ? 0 : 1;
@@ -394,8 +401,8 @@ decode_mega_kernel(const MegaOp* __restrict__ ops, int n_ops, int* __restrict__ 
                     __syncwarp();
                     if (lane == 0) mbar_arrive(acc_empty);
                     if (full_tile) {
-                        if (dual) epilogue_store_chunk<kMegaBN, 1>(p, n_tile, 0, row, 0, vg, vu);
-                        else epilogue_store_chunk<kMegaBN, 0>(p, n_tile, 0, row, 0, vg, vu);
+                        if (dual) epilogue_store_chunk<kMegaBN, 1>(p, n_tile, 0, row, 0, vg, vu, tok_scale);
+                        else epilogue_store_chunk<kMegaBN, 0>(p, n_tile, 0, row, 0, vg, vu, tok_scale);
                     } else {
 #pragma unroll
                         for (int j = 0; j < 16; ++j) {
@@ -435,8 +442,8 @@ decode_mega_kernel(const MegaOp* __restrict__ ops, int n_ops, int* __restrict__ 
                                     }
                                 }
                             }
-                            if (dual) epilogue_store_chunk<kMegaBN, 1>(p, n_tile, 0, row, 0, vg, vu);
-                            else epilogue_store_chunk<kMegaBN, 0>(p, n_tile, 0, row, 0, vg, vu);
+                            if (dual) epilogue_store_chunk<kMegaBN, 1>(p, n_tile, 0, row, 0, vg, vu, tok_scale);
+                            else epilogue_store_chunk<kMegaBN, 0>(p, n_tile, 0, row, 0, vg, vu, tok_scale);
                             if (e == 0) p.counters[u] = 0;
                         }
                     }

@@ -34,6 +34,7 @@ gemm_streamk_kernel(const GemmParams p) {
     volatile int* fin_flag = reinterpret_cast<volatile int*>(tmem_slot + 1);  // [2]
     float* stat_mean = reinterpret_cast<float*>(tmem_slot + 4);               // [32]
     float* stat_rstd = stat_mean + 32;                                        // [32]
+    float* stat_red = stat_rstd + 32;                                         // [4][32]
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
@@ -167,8 +168,9 @@ gemm_streamk_kernel(const GemmParams p) {
 
         pdl_wait_prior_grid();  // activations come from the previous kernel
 
-        if (p.norm_mode != B200_NORM_NONE) {
+        if (p.norm_mode == B200_NORM_LAYER) {
             // Per-token statistics (decode-size T only; host guarantees t_tiles == 1, BN <= 32).
+            // RMSNorm needs no pre-pass: its 1/rms is applied in the epilogue (see rms_stats_128).
             const int pw = warp - 2;
             for (int t = pw; t < BN; t += 4) {
                 float s1 = 0.f, s2 = 0.f;
@@ -206,6 +208,7 @@ gemm_streamk_kernel(const GemmParams p) {
 
         uint32_t part = 0, phb = 0;
         int sb = 0;
+        bool rms_ready = false;
         long long q = q_begin;
         while (q < q_end) {
             const int u = (int)(q / p.kbpt);
@@ -264,8 +267,8 @@ gemm_streamk_kernel(const GemmParams p) {
                                             const float g1 = h16_to_float((uint16_t)(win[w] >> 16), p.is_bf16);
                                             if (p.norm_mode == B200_NORM_RMS) {
                                                 // HF LlamaRMSNorm: weight * (x * rstd).to(dtype)
-                                                x0 = g0 * round16(x0 * rstd, p.is_bf16);
-                                                x1 = g1 * round16(x1 * rstd, p.is_bf16);
+                                                x0 = g0 * x0;   // 1/rms deferred to the epilogue
+                                                x1 = g1 * x1;
                                             } else {
                                                 const float b0 = h16_to_float((uint16_t)(bin[w] & 0xffff), p.is_bf16);
                                                 const float b1 = h16_to_float((uint16_t)(bin[w] >> 16), p.is_bf16);
@@ -300,6 +303,12 @@ gemm_streamk_kernel(const GemmParams p) {
                 }
             }
 
+            // ---- deferred RMSNorm statistics: computed once, while the tensor core chews on the staged k-blocks
+            if (p.norm_mode == B200_NORM_RMS && !rms_ready) {
+                rms_stats_128(p, min(BN, p.T), e, stat_red, stat_rstd);
+                rms_ready = true;
+            }
+            const float* tok_scale = (p.norm_mode == B200_NORM_RMS) ? stat_rstd : nullptr;
             // ---- drain the accumulator of this part
             const bool full_tile = (kb0 == 0) && (kb1 == p.kbpt);
             const int slot = (part == 0) ? 0 : 1;
@@ -327,7 +336,7 @@ gemm_streamk_kernel(const GemmParams p) {
                     }
                 }
                 if (full_tile) {
-                    epilogue_store_chunk<BN, DUAL>(p, n_tile, t_tile, row, c, vg, vu);
+                    epilogue_store_chunk<BN, DUAL>(p, n_tile, t_tile, row, c, vg, vu, tok_scale);
                 } else {
 #pragma unroll
                     for (int j = 0; j < 16; ++j) {
@@ -379,7 +388,7 @@ gemm_streamk_kernel(const GemmParams p) {
                                 }
                             }
                         }
-                        epilogue_store_chunk<BN, DUAL>(p, n_tile, t_tile, row, c, vg, vu);
+                        epilogue_store_chunk<BN, DUAL>(p, n_tile, t_tile, row, c, vg, vu, tok_scale);
                     }
                     if (e == 0) p.counters[u] = 0;  // leave the counters clean for the next launch
                 }

@@ -67,6 +67,34 @@ __device__ __forceinline__ float gelu_tanh(float x) {
     return 0.5f * x * (1.0f + tanhf(k0 * (x + k1 * x * x * x)));
 }
 
+// Per-token 1/rms for the deferred RMSNorm: all 128 worker threads cooperate, result in rstd[0..T).
+// `red` is 4*32 floats of shared scratch; callers separate uses with their own barriers.
+__device__ __forceinline__ void rms_stats_128(const GemmParams& p, int T, int e, float* red, float* rstd) {
+    const int warp = e >> 5, lane = e & 31;
+    for (int t = 0; t < T; ++t) {
+        float s2 = 0.f;
+        const uint16_t* xr = p.x + (size_t)t * p.ldx;
+        for (int c = e; c < p.K / 8; c += 128) {
+            const uint4 v = ld_cg_v4(xr + c * 8);
+            const uint32_t w4[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const float a = h16_to_float((uint16_t)(w4[i] & 0xffff), p.is_bf16);
+                const float b = h16_to_float((uint16_t)(w4[i] >> 16), p.is_bf16);
+                s2 += a * a + b * b;
+            }
+        }
+        s2 = warp_sum(s2);
+        if (lane == 0) red[warp * 32 + t] = s2;
+    }
+    named_bar_sync(1, 128);
+    if (e < T) {
+        const float s = red[e] + red[32 + e] + red[64 + e] + red[96 + e];
+        rstd[e] = rsqrtf(s / (float)p.K + p.norm_eps);
+    }
+    named_bar_sync(1, 128);
+}
+
 // Rounds through the 16-bit storage type so fused epilogues see the same values
 // the unfused torch sequence would have stored between ops.
 __device__ __forceinline__ float round16(float v, int is_bf16) {
@@ -76,7 +104,7 @@ __device__ __forceinline__ float round16(float v, int is_bf16) {
 template <int BN, int DUAL>
 __device__ __forceinline__ void epilogue_store_chunk(const GemmParams& p, int n_tile, int t_tile,
                                                      int row, int chunk, const float (&vg)[16],
-                                                     const float (&vu)[16]) {
+                                                     const float (&vu)[16], const float* tok_scale = nullptr) {
     const int n = n_tile * kTileM + row;
     if (n >= p.N) return;
     const float b = p.bias ? h16_to_float(p.bias[n], p.is_bf16) : 0.0f;
@@ -84,10 +112,12 @@ __device__ __forceinline__ void epilogue_store_chunk(const GemmParams& p, int n_
     for (int j = 0; j < 16; ++j) {
         const int t = t_tile * BN + chunk * 16 + j;
         if (t >= p.T) break;
-        float v = vg[j] + b;
+        // deferred RMSNorm: the GEMM ran on x*g, the per-token 1/rms is applied here
+        const float ts = tok_scale ? tok_scale[chunk * 16 + j] : 1.0f;
+        float v = vg[j] * ts + b;
         if (DUAL) {
             const float g = round16(v, p.is_bf16);
-            const float u = round16(vu[j], p.is_bf16);
+            const float u = round16(vu[j] * ts, p.is_bf16);
             const float s = round16(g / (1.0f + __expf(-g)), p.is_bf16);
             v = s * u;
         } else if (p.epilogue == B200_EPI_GELU_TANH) {
