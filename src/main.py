@@ -210,6 +210,21 @@ def start_stage_server(args, device, stage_model, final_stage: bool, stage_index
     model_name = args.model
     handler.on_die = lambda: (stop.set(), rpc.stop())   # scripted kill (tests / kill_stage.py --soft)
 
+    def next_pings():
+        """RTTs to servers that start where this one ends (upstream ModuleAnnouncerThread, server.py:721-735)."""
+        if not lb_blocks:
+            return {}
+        from petals_b200.net.reachability import check_direct_reachability
+        from .dht_utils import get_block_entries
+
+        out = {}
+        for e in get_block_entries(dht, lb_blocks[-1] + 1, model_name)[:5]:
+            if e.get("p2p_maddrs") and str(e.get("peer_id")) != str(peer_id):
+                ok, rtt = check_direct_reachability(e["p2p_maddrs"][0], 1.0)
+                if ok:
+                    out[str(e["peer_id"])] = rtt
+        return out
+
     def publish():
         exp = get_dht_time() + RECORD_TTL
         if stage_index is not None:
@@ -221,9 +236,11 @@ def start_stage_server(args, device, stage_model, final_stage: bool, stage_index
             register_server_on_dht(dht, peer_id, lb_blocks[0], lb_blocks[-1] + 1, handler.throughput, model_name,
                                    server_address=maddrs[0], p2p_maddrs=maddrs, final_stage=final_stage,
                                    expiration_time=exp)
+            left = handler.kv.tokens_left
             register_blocks_on_dht(dht, peer_id, lb_blocks, model_name, p2p_maddrs=maddrs, start_block=lb_blocks[0],
                                    end_block=lb_blocks[-1] + 1, throughput=handler.throughput,
-                                   final_stage=final_stage, expiration_time=exp)
+                                   final_stage=final_stage, expiration_time=exp,
+                                   cache_tokens_left=-1 if left is None else left, next_pings=next_pings())
 
     def heartbeat():
         while not stop.wait(HEARTBEAT_PERIOD):

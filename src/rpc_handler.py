@@ -68,7 +68,7 @@ class StageConnectionHandler:
 
     # ------------------------------------------------------------------ registration
     def add_p2p_handlers(self, server: RpcServer) -> None:
-        for name in ("rpc_forward", "rpc_forward_stream", "rpc_info", "rpc_close_session", "rpc_push"):
+        for name in ("rpc_forward", "rpc_forward_stream", "rpc_info", "rpc_close_session", "rpc_push", "rpc_check"):
             server.add_handler(f"{HANDLER_PREFIX}.{name}", getattr(self, name))
 
     # ------------------------------------------------------------------ core
@@ -164,6 +164,13 @@ class StageConnectionHandler:
                     "cache_tokens_left": left if left is not None else -1, "kv_capacity": self.kv_capacity,
                     "throughput": self.throughput, "requests": self.requests, "queued": self.pool.queued,
                     "uptime_s": time.time() - self.started}
+
+    def rpc_check(self, uid: str, tensors, metadata: Dict):
+        """Dial-back probe for joining servers (upstream reachability.py rpc_check)."""
+        from petals_b200.net.reachability import check_direct_reachability
+
+        ok, rtt = check_direct_reachability(metadata["maddr"], float(metadata.get("timeout", 2.0)))
+        return [], {"reachable": ok, "rtt_s": rtt}
 
     def rpc_close_session(self, uid: str, tensors, metadata: Dict):
         return [], {"closed": self.kv.close(metadata.get("session_id", ""))}

@@ -153,3 +153,61 @@ def test_rope_llama3_scaling_matches_hf():
     rot = transformers.models.llama.modeling_llama.LlamaRotaryEmbedding(hf_cfg)
     ours = rope_inv_freq(cfg.head_dim, cfg.rope_theta, cfg.rope_scaling)
     assert torch.allclose(ours, rot.inv_freq.float(), rtol=1e-5, atol=1e-9)
+
+
+def test_memory_cache_blocks_until_freed_then_times_out():
+    import threading
+
+    from petals_b200.runtime.kv_cache import AllocationFailed
+    from petals_b200.runtime.memory_cache import MemoryCache, TensorDescriptor
+
+    d = TensorDescriptor((4, 256), torch.float32, torch.device("cpu"))          # 4 KiB
+    cache = MemoryCache(max_size_bytes=6000, alloc_timeout=0.2)
+    got = []
+    with cache.allocate_cache(d) as (h,):
+        assert cache.use_cache(h)[0].shape == (4, 256) and cache.bytes_left == 6000 - 4096
+        with pytest.raises(AllocationFailed):
+            with cache.allocate_cache(d):
+                pass
+
+        def waiter():
+            with cache.allocate_cache(d, timeout=5.0) as hs:
+                got.append(len(hs))
+
+        t = threading.Thread(target=waiter)
+        t.start()
+        time.sleep(0.1)
+        assert cache.enqueued_size_bytes == 4096
+    t.join(5)
+    assert got == [1] and cache.current_size_bytes == 0
+    with pytest.raises(AllocationFailed):
+        with cache.allocate_cache(TensorDescriptor((4096,), torch.float32, torch.device("cpu"))):
+            pass
+
+
+def test_block_sizing():
+    from petals_b200.models.config import PRESETS
+    from petals_b200.runtime import block_utils as bu
+
+    c7, c70 = PRESETS["llama-2-7b"], PRESETS["llama-2-70b"]
+    assert bu.get_block_size(c7, torch.float16) == 404_766_720             # 404.8 MB per Llama-2-7B block
+    assert bu.default_limits(c7) == (2048, 4096) and bu.default_limits(c70) == (8192, 16384)
+    n = bu.choose_num_blocks(c70, "cpu", torch.bfloat16, total_memory=180 << 30)
+    assert n == 80                                                          # 8 stages x 10 blocks fits easily per GPU
+    assert bu.choose_num_blocks(c70, "cpu", torch.bfloat16, total_memory=24 << 30) == 12   # (24-4) GiB / 1.78 GB
+    assert bu.get_block_size(c7, torch.float16, "fp8") < 0.51 * bu.get_block_size(c7, torch.float16)
+    assert bu.resolve_block_dtype(c7, "auto", "cpu") == torch.float32
+
+
+def test_reachability_probe():
+    from petals_b200.net.dht import DHT
+    from petals_b200.net.reachability import check_direct_reachability, validate_reachability
+
+    d = DHT(start=True, host_maddrs=["/ip4/127.0.0.1/tcp/0"])
+    m = d.get_visible_maddrs()[0]
+    ok, rtt = check_direct_reachability(m)
+    assert ok and rtt < 1.0
+    d.shutdown()
+    assert check_direct_reachability("/ip4/127.0.0.1/tcp/1")[0] is False
+    with pytest.raises(RuntimeError):
+        validate_reachability(["/ip4/127.0.0.1/tcp/1"], 0.5)
