@@ -44,6 +44,11 @@ REF = os.path.join(HERE, "_ref")
 
 
 # ----------------------------------------------------------------------------- hivemind stand-ins
+class _Tensor:   # runtime_pb2.Tensor stand-in: raw bytes + dtype + shape (hivemind's uncompressed codec)
+    def __init__(self, buffer, dtype, size):
+        self.buffer, self.dtype, self.size = buffer, dtype, size
+
+
 def _install_stubs():
     import torch
 
@@ -54,10 +59,6 @@ def _install_stubs():
 
         def to_base58(self):
             return str(self)
-
-    class _Tensor:   # runtime_pb2.Tensor stand-in: raw bytes + dtype + shape (hivemind's uncompressed codec)
-        def __init__(self, buffer, dtype, size):
-            self.buffer, self.dtype, self.size = buffer, dtype, size
 
     def serialize_torch_tensor(t, *a, **k):
         t = t.detach().contiguous()
