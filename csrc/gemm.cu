@@ -209,6 +209,7 @@ gemm_streamk_kernel(const GemmParams p) {
         uint32_t part = 0, phb = 0;
         int sb = 0;
         bool rms_ready = false;
+        const int tp_seq = (p.tp_world > 1) ? (__ldcv(p.tp_seq) + 1) : 0;
         long long q = q_begin;
         while (q < q_end) {
             const int u = (int)(q / p.kbpt);
@@ -336,6 +337,7 @@ gemm_streamk_kernel(const GemmParams p) {
                     }
                 }
                 if (full_tile) {
+                    if (p.tp_world > 1) tp_allreduce_tile(p, n_tile, row, ncol, e, tp_seq, vg);
                     epilogue_store_chunk<BN, DUAL>(p, n_tile, t_tile, row, c, vg, vu, tok_scale);
                 } else {
 #pragma unroll
@@ -388,6 +390,7 @@ gemm_streamk_kernel(const GemmParams p) {
                                 }
                             }
                         }
+                        if (p.tp_world > 1) tp_allreduce_tile(p, n_tile, row, ncol, e, tp_seq, vg);
                         epilogue_store_chunk<BN, DUAL>(p, n_tile, t_tile, row, c, vg, vu, tok_scale);
                     }
                     if (e == 0) p.counters[u] = 0;  // leave the counters clean for the next launch
@@ -401,6 +404,14 @@ gemm_streamk_kernel(const GemmParams p) {
     tc_fence_before();
     __syncthreads();
     if (warp == 1) tmem_dealloc<Cfg::kTmemCols>(tmem_base);
+    if (p.tp_world > 1 && threadIdx.x == 0) {
+        __threadfence();
+        if (atomicAdd(p.tp_exit, 1) == (int)gridDim.x - 1) {   // last CTA out: this launch is complete on this rank
+            *p.tp_exit = 0;
+            *p.tp_seq = *p.tp_seq + 1;
+            __threadfence();
+        }
+    }
 }
 
 template <int BN, int DUAL>
@@ -444,7 +455,23 @@ extern "C" int64_t b200_gemm_scratch_bytes(int32_t max_tokens) {
     return (int64_t)sm_count_cached() * 2 * 2 * bn * kTileM * (int64_t)sizeof(float);
 }
 
-extern "C" int b200_gemm(const b200_gemm_args* a, void* stream_) {
+static int gemm_impl(const b200_gemm_args* a, const b200_tp_args* tp, void* stream_);
+
+extern "C" int b200_gemm(const b200_gemm_args* a, void* stream_) { return gemm_impl(a, nullptr, stream_); }
+
+extern "C" int b200_gemm_allreduce(const b200_gemm_args* a, const b200_tp_args* tp, void* stream_) {
+    if (!tp || tp->world < 2 || tp->world > 8 || tp->rank < 0 || tp->rank >= tp->world)
+        return fail(B200_EINVAL, "b200_gemm_allreduce: bad tensor-parallel group (world %d)", tp ? tp->world : -1);
+    if (!a) return fail(B200_EINVAL, "b200_gemm_allreduce: null args");
+    if (a->T > 16 || a->dual || a->norm_mode != B200_NORM_NONE || a->epilogue != B200_EPI_NONE)
+        return fail(B200_ELIMIT, "b200_gemm_allreduce: supports row-parallel linears with T <= 16 (no norm / activation)");
+    if (a->N > tp->n_max || a->n_tiles > tp->tiles_max)
+        return fail(B200_ELIMIT, "b200_gemm_allreduce: N=%d / %d tiles exceed the workspace (%d / %d)", a->N, a->n_tiles,
+                    tp->n_max, tp->tiles_max);
+    return gemm_impl(a, tp, stream_);
+}
+
+static int gemm_impl(const b200_gemm_args* a, const b200_tp_args* tp, void* stream_) {
     if (!a || !a->w_packed || !a->x || !a->out || !a->scratch || !a->counters)
         return fail(B200_EINVAL, "b200_gemm: null pointer argument");
     if (a->T <= 0 || a->N <= 0 || a->K <= 0 || (a->K % kBK) != 0)
@@ -482,6 +509,16 @@ extern "C" int b200_gemm(const b200_gemm_args* a, void* stream_) {
     p.is_bf16 = (a->dtype == B200_BF16) ? 1 : 0;
     p.out_fp32 = a->out_fp32;
     p.debug = a->debug;
+    p.tp_world = 0;
+    if (tp) {
+        p.tp_world = tp->world; p.tp_rank = tp->rank; p.tp_n_max = tp->n_max; p.tp_tiles_max = tp->tiles_max;
+        for (int r = 0; r < tp->world; ++r) {
+            p.tp_stage[r] = static_cast<float*>(tp->stage[r]);
+            p.tp_flags[r] = static_cast<int*>(tp->flags[r]);
+        }
+        p.tp_seq = tp->seq;
+        p.tp_exit = tp->exit_counter;
+    }
 
     int grid = a->grid > 0 ? a->grid : sm_count_cached();
     if (grid > sm_count_cached()) grid = sm_count_cached();

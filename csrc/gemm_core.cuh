@@ -55,6 +55,12 @@ struct GemmParams {
     int epilogue, norm_mode;
     float norm_eps;
     int is_bf16, out_fp32;
+    // tensor-parallel all-reduce fused into the tile epilogue (tp_world <= 1: off)
+    int tp_world, tp_rank, tp_n_max, tp_tiles_max;
+    float* tp_stage[8];   // peer-mapped staging buffers: [2 parity][world][16 tokens][tp_n_max] fp32 on each rank
+    int* tp_flags[8];     // peer-mapped arrival flags:   [2 parity][world][tp_tiles_max]
+    int* tp_seq;          // local: number of fused launches completed on this workspace
+    int* tp_exit;         // local: CTAs that have left the current launch
     int debug;  // experiment switches (scripts/exp_*.py): 1 = no MMA issue, 2 = no B stage waits
 };
 
@@ -65,6 +71,57 @@ __device__ __forceinline__ long long range_begin(const GemmParams& p, int c) {
 __device__ __forceinline__ float gelu_tanh(float x) {
     const float k0 = 0.7978845608028654f, k1 = 0.044715f;
     return 0.5f * x * (1.0f + tanhf(k0 * (x + k1 * x * x * x)));
+}
+
+// ---- fused all-reduce of one finished 128-row tile across the tensor-parallel group ------------
+// Every rank holds a partial sum (its K shard) of the same output tile.  The finisher of the tile
+//   1. pushes its fp32 partial into EVERY rank's staging buffer with peer stores over NVLink and
+//      raises that rank's arrival flag (release, system scope) to the launch sequence number;
+//   2. waits until all ranks' flags for this tile carry the same number (acquire loads on local memory);
+//   3. adds the partials in rank order — every rank computes bit-identical sums — into vg.
+// Staging buffers and flags alternate between two halves by launch parity, so a rank that is one
+// launch ahead never overwrites data a slower peer is still reading (a rank cannot get two ahead:
+// finishing a launch requires every peer's pushes for it).
+__device__ __forceinline__ void tp_allreduce_tile(const GemmParams& p, int tile, int row, int ncol, int e, int seq,
+                                                  float (&vg)[16]) {
+    const int R = p.tp_world, me = p.tp_rank, par = seq & 1;
+    const size_t slot = (size_t)(par * R + me) * 16;
+    const int n = tile * kTileM + row;
+    for (int r = 0; r < R; ++r) {
+        float* dst = p.tp_stage[r] + slot * p.tp_n_max + n;
+#pragma unroll
+        for (int j = 0; j < 16; ++j)
+            if (j < ncol) __stcg(dst + (size_t)j * p.tp_n_max, vg[j]);
+    }
+    __threadfence_system();
+    named_bar_sync(1, 128);
+    if (e < R) {
+        int* f = p.tp_flags[e] + (size_t)(par * R + me) * p.tp_tiles_max + tile;
+        asm volatile("st.release.sys.global.s32 [%0], %1;\n" ::"l"(f), "r"(seq) : "memory");
+    }
+    if (e < R) {
+        const int* f = p.tp_flags[me] + (size_t)(par * R + e) * p.tp_tiles_max + tile;
+        long long t0 = clock64();
+        int v;
+        do {
+            asm volatile("ld.acquire.sys.global.s32 %0, [%1];\n" : "=r"(v) : "l"(f) : "memory");
+            if (v != seq && clock64() - t0 > 8000000000LL) {
+                printf("b200: tensor-parallel tile exchange timed out (rank %d waits for rank %d, tile %d, seq %d, flag %d)\n",
+                       me, e, tile, seq, v);
+                __trap();
+            }
+        } while (v != seq);
+    }
+    named_bar_sync(1, 128);
+    __threadfence_system();
+#pragma unroll
+    for (int j = 0; j < 16; ++j) vg[j] = 0.f;
+    for (int r = 0; r < R; ++r) {
+        const float* src = p.tp_stage[me] + (size_t)(par * R + r) * 16 * p.tp_n_max + n;
+#pragma unroll
+        for (int j = 0; j < 16; ++j)
+            if (j < ncol) vg[j] += __ldcv(src + (size_t)j * p.tp_n_max);
+    }
 }
 
 // Per-token 1/rms for the deferred RMSNorm: all 128 worker threads cooperate, result in rstd[0..T).

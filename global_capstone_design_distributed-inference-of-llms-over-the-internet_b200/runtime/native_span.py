@@ -134,6 +134,32 @@ class NativeSpan:
     def _count(self, n: int = 1) -> None:
         self.kernel_launches += n
 
+    tp = None          # TPWorkspace when this span is one shard of a tensor-parallel group
+    tp_mode = None     # "fused" | "nccl"
+    tp_group = None
+
+    def _row_parallel(self, x: torch.Tensor, w, out: torch.Tensor, residual: torch.Tensor) -> None:
+        """o_proj / down_proj: plain on one GPU, reduced across the group when tensor-parallel."""
+        if self.tp_mode is None:
+            G.linear(x, w, out=out, residual=residual, workspace=self.ws, pdl=self.pdl)
+        elif self.tp_mode == "fused" and x.shape[0] <= 16:
+            from ..parallel.tensor_parallel import linear_allreduce
+
+            linear_allreduce(x, w, self.tp, out=out, residual=residual, workspace=self.ws, pdl=self.pdl)
+        else:
+            # library baseline: GEMM without bias/residual, NCCL all-reduce, then the epilogue in torch
+            import torch.distributed as dist
+
+            bias, w.bias = w.bias, None
+            try:
+                G.linear(x, w, out=out, workspace=self.ws, pdl=False)
+            finally:
+                w.bias = bias
+            dist.all_reduce(out, group=self.tp_group)
+            if bias is not None:
+                out.add_(bias)
+            out.add_(residual)
+
     def _decode_layers(self, T: int, h: torch.Tensor) -> torch.Tensor:
         """h: [T, H] view of a static buffer; returns the buffer view holding the result."""
         c, pdl = self.cfg, self.pdl
@@ -144,10 +170,10 @@ class NativeSpan:
                      norm_eps=c.norm_eps, workspace=self.ws, pdl=pdl)
             A.attn_decode(qkv, attn, self.kv_ptrs[li], self.pos, self.inv_freq, self.attn_ws, c.n_heads,
                           c.n_kv_heads, c.head_dim, self.kv_capacity, self.scale, pdl=pdl)
-            G.linear(attn, P["o"], out=h2, residual=h, workspace=self.ws, pdl=pdl)
+            self._row_parallel(attn, P["o"], h2, h)
             G.linear(h2, P["mlp_in"], out=act, epilogue=self.mlp_epi, norm_mode=self.norm_mode, norm_w=P["ln2_w"],
                      norm_b=P["ln2_b"], norm_eps=c.norm_eps, workspace=self.ws, pdl=pdl)
-            G.linear(act, P["down"], out=h, residual=h2, workspace=self.ws, pdl=pdl)
+            self._row_parallel(act, P["down"], h, h2)
             self._count(5)
         return h
 
@@ -214,7 +240,7 @@ class NativeSpan:
 
     def _decode_body(self, B: int, from_ids: bool, greedy: bool):
         h = self._embed(B, 0, True) if from_ids else self.h_a[:B]
-        if self.use_mega and B <= MEGA_MAX_TOKENS:
+        if self.use_mega and B <= MEGA_MAX_TOKENS and self.tp_mode is None:
             return self._decode_mega(B, h, greedy)
         h = self._decode_layers(B, h)
         if self.has_head:
@@ -438,14 +464,14 @@ class NativeSpan:
                               kv.max_len, p0, pdl=pdl)
                 A.attn_prefill(qkv, attn, kv.k(li), kv.v(li), c.n_heads, c.n_kv_heads, c.head_dim, kv.max_len, p0,
                                self.scale, pdl=pdl)
-                G.linear(attn, P["o"], out=h2, residual=h, workspace=self.ws, pdl=pdl)
+                self._row_parallel(attn, P["o"], h2, h)
                 if fused:
                     G.linear(h2, P["mlp_in"], out=act, epilogue=self.mlp_epi, norm_mode=self.norm_mode,
                              norm_w=P["ln2_w"], norm_b=P["ln2_b"], norm_eps=c.norm_eps, workspace=self.ws, pdl=pdl)
                 else:
                     E.norm(h2, P["ln2_w"], P["ln2_b"], c.norm_eps, ln, out=self.xn[:n], pdl=pdl)
                     G.linear(self.xn[:n], P["mlp_in"], out=act, epilogue=self.mlp_epi, workspace=self.ws, pdl=pdl)
-                G.linear(act, P["down"], out=h, residual=h2, workspace=self.ws, pdl=pdl)
+                self._row_parallel(act, P["down"], h, h2)
                 self._count(6 if fused else 8)
             if out is not None:
                 out[c0:c0 + n].copy_(h, non_blocking=True)

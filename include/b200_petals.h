@@ -85,6 +85,26 @@ int64_t b200_gemm_scratch_bytes(int32_t max_tokens);
 /* Token-tile width the kernel will pick for T tokens (16,32,64,128,256). */
 int32_t b200_gemm_token_tile(int32_t T, int32_t dual);
 
+/* Row-parallel linear of a tensor-parallel span with the all-reduce fused into the tile epilogue
+ * (decode sizes, T <= 16): every rank runs this with its K shard of the weight; the CTA that finishes
+ * an output tile pushes its fp32 partial into every rank's staging buffer with peer stores over
+ * NVLink, waits for the other ranks' partials of the same tile (flags in local memory), adds them in
+ * rank order and applies bias / residual once.  All ranks end with bit-identical outputs; tiles are
+ * exchanged while other tiles are still in the tensor core.  The reference's dead TP path runs an
+ * NCCL all-reduce after each row-parallel linear (petals/server/backend.py:134-136 via tensor_parallel).
+ * stage[r] / flags[r] are rank r's buffers mapped into this process (e.g. torch symmetric memory):
+ *   stage: 2 * world * 16 * n_max floats,  flags: 2 * world * tiles_max ints (zeroed once),
+ *   seq / exit_counter: one int each, local, zeroed once.  All ranks must issue the same sequence of
+ *   b200_gemm_allreduce calls on a workspace. */
+typedef struct b200_tp_args {
+    int32_t world, rank, n_max, tiles_max;
+    void* stage[8];
+    void* flags[8];
+    int32_t* seq;
+    int32_t* exit_counter;
+} b200_tp_args;
+int b200_gemm_allreduce(const b200_gemm_args* args, const b200_tp_args* tp, void* stream);
+
 /* b200_gemm for callers that cannot allocate device memory (no counterpart in the reference, which
  * has no native code and lets torch allocate freely).  Same arguments and result as b200_gemm, but
  * args->scratch and args->counters are ignored: the workspace is a fixed ~5 MiB array inside the
