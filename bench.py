@@ -43,6 +43,8 @@ def parse_args():
     ap.add_argument("--dtype", default="fp16", choices=["fp16", "bf16"])
     ap.add_argument("--prompt-len", type=int, default=128)
     ap.add_argument("--sessions", type=int, default=0, help="in-flight sessions (default: one per stage)")
+    ap.add_argument("--weights", default="native", choices=["native", "fp8"],
+                    help="fp8 = opt-in e4m3 weights (NOT the headline configuration)")
     return ap.parse_args()
 
 
@@ -120,7 +122,7 @@ def run_b200(args):
     cap = L + 2 * (K + W) + 16
     cap = (cap + 255) // 256 * 256
     eng = PipelineEngine(args.model, even_splits(cfg.n_layers, world), dtype, dev, kv_capacity=cap,
-                         max_sessions=max(S, 1), max_chunk=256, seed=0)
+                         max_sessions=max(S, 1), max_chunk=256, seed=0, weight_format=args.weights)
     sess = eng.open_sessions(S)
     g = torch.Generator().manual_seed(1234)
     prompts = [torch.randint(0, cfg.vocab, (L,), generator=g) for _ in range(S)]
@@ -203,7 +205,8 @@ def run_b200(args):
             "metric": "decode tokens/sec (aggregate over in-flight sessions), Llama-2-7B N-stage pipeline",
             "value": round(tok_s, 2), "unit": "tokens/s", "n_gpus": world, "steps": K, "warmup": W,
             "ms_per_step": round(dev_ms / K, 4), "higher_is_better": True, "scaling": "weak",
-            "vs_baseline": None, "dtype": args.dtype, "data": "synthetic prompts, random-init weights",
+            "vs_baseline": None, "dtype": args.dtype if args.weights == "native" else f"{args.dtype} activations, fp8(e4m3) weights (opt-in)",
+            "data": "synthetic prompts, random-init weights",
             "impl": "b200",
             "config": {"model": args.model, "global_batch": S, "seq_len": L, "parallelism": f"pp{world}",
                        "sessions_in_flight": S, "batch_per_session": 1,

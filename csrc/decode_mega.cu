@@ -42,7 +42,7 @@ constexpr int kMegaSB = 3;
 constexpr int kMegaNAcc = 4;
 constexpr int kMegaTmemCols = 128;               // 16 cols x 2 matrices x 4 accumulators
 constexpr size_t kMegaSmemData = (size_t)kMegaSA * kMegaStageA + (size_t)kMegaSB * kMegaStageB;
-constexpr size_t kMegaSmemBytes = kMegaSmemData + 1024 + 1024;
+constexpr size_t kMegaSmemBytes = kMegaSmemData + 1024 + 2048;
 static_assert(sizeof(AttnDecodeSmem<128, 8>) <= (size_t)kMegaSB * kMegaStageB, "attention scratch must fit the B ring");
 
 __device__ __forceinline__ int ld_acquire_gpu(const int* p) {
@@ -490,6 +490,8 @@ extern "C" int b200_decode_mega_build(const b200_mega_op* ops, int32_t n_ops, vo
                 rc = fail(B200_EINVAL, "mega op %d: dual packing and SwiGLU epilogue must come together", i);
             else if (a.norm_mode != B200_NORM_NONE && !a.norm_w)
                 rc = fail(B200_EINVAL, "mega op %d: norm without weights", i);
+            else if (a.fp8)
+                rc = fail(B200_EINVAL, "mega op %d: fp8 weights are served by the per-op path", i);
             else if ((a.ldx % 8) != 0 || (reinterpret_cast<uintptr_t>(a.x) & 15) != 0)
                 rc = fail(B200_EINVAL, "mega op %d: misaligned activations", i);
             if (rc != B200_OK) break;

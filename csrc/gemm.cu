@@ -34,7 +34,7 @@ gemm_streamk_kernel(const GemmParams p) {
     volatile int* fin_flag = reinterpret_cast<volatile int*>(tmem_slot + 1);  // [2]
     float* stat_mean = reinterpret_cast<float*>(tmem_slot + 4);               // [32]
     float* stat_rstd = stat_mean + 32;                                        // [32]
-    float* stat_red = stat_rstd + 32;                                         // [4][32]
+    float* stat_red = stat_rstd + 32;                                         // [2][4][32]
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
@@ -100,7 +100,8 @@ gemm_streamk_kernel(const GemmParams p) {
     } else if (warp == 1) {
         // ------------------------------------------------ MMA issuer (whole warp, one elected lane issues)
         {
-            const uint32_t idesc = umma_idesc(kTileM, BN, p.is_bf16, p.is_bf16, 0, 0);
+            const uint32_t idesc = p.is_fp8 ? umma_idesc(kTileM, BN, 0, 0, 0, 0)   // e4m3 x e4m3
+                                            : umma_idesc(kTileM, BN, p.is_bf16, p.is_bf16, 0, 0);
             int u = (int)(q_begin / p.kbpt);
             int kb0 = (int)(q_begin - (long long)u * p.kbpt);
             long long left = q_end - q_begin;
@@ -130,8 +131,10 @@ gemm_streamk_kernel(const GemmParams p) {
 #pragma unroll
                                 for (int k = 0; k < kBK / 16; ++k) {
                                     // +32 B per UMMA_K inside the 128 B swizzle row -> +2 in the address field
-                                    umma_f16(tmem_base + (a * Cfg::kNAcc + (k % Cfg::kNAcc)) * BN, adesc + (uint64_t)(k * 2),
-                                             bdesc + (uint64_t)(k * 2), idesc, (k >= Cfg::kNAcc) ? 1u : acc);
+                                    const uint32_t d_tmem = tmem_base + (a * Cfg::kNAcc + (k % Cfg::kNAcc)) * BN;
+                                    const uint32_t accf = (k >= Cfg::kNAcc) ? 1u : acc;
+                                    if (p.is_fp8) umma_f8f6f4(d_tmem, adesc + (uint64_t)(k * 2), bdesc + (uint64_t)(k * 2), idesc, accf);
+                                    else umma_f16(d_tmem, adesc + (uint64_t)(k * 2), bdesc + (uint64_t)(k * 2), idesc, accf);
                                 }
                             }
                         }
@@ -206,9 +209,10 @@ gemm_streamk_kernel(const GemmParams p) {
             named_bar_sync(1, kEpiThreads);
         }
 
+        if (p.is_fp8) fp8_stats_128(p, min(BN, p.T), e, stat_red, stat_mean, stat_rstd);   // qmul, epilogue scale
         uint32_t part = 0, phb = 0;
         int sb = 0;
-        bool rms_ready = false;
+        bool rms_ready = p.is_fp8 != 0;   // fp8: the 1/rms is already folded into stat_rstd
         const int tp_seq = (p.tp_world > 1) ? (__ldcv(p.tp_seq) + 1) : 0;
         long long q = q_begin;
         while (q < q_end) {
@@ -228,6 +232,42 @@ gemm_streamk_kernel(const GemmParams p) {
 #pragma unroll
                     for (int g = 0; g < G; ++g) {
                         if (kb + g < kb1) {
+                            if (p.is_fp8) {
+                                // 128 elements per k-block; this thread quantises 16 of them (two 16-byte loads)
+                                const int kcol8 = (kb + g) * 128 + ch * 16;
+#pragma unroll
+                                for (int i = 0; i < NI; ++i) {
+                                    const int t = t_tile * BN + r0 + 16 * i;
+                                    uint4 lo = make_uint4(0, 0, 0, 0), hi = lo;
+                                    if (t < p.T) {
+                                        lo = ld_cg_v4(p.x + (size_t)t * p.ldx + kcol8);
+                                        hi = ld_cg_v4(p.x + (size_t)t * p.ldx + kcol8 + 8);
+                                    }
+                                    uint4 gl = make_uint4(0, 0, 0, 0), gh = gl;
+                                    if (p.norm_mode != B200_NORM_NONE) {
+                                        gl = ld_nc_v4(p.norm_w + kcol8);
+                                        gh = ld_nc_v4(p.norm_w + kcol8 + 8);
+                                    }
+                                    const float qm = (t < p.T) ? stat_mean[r0 + 16 * i] : 0.f;
+                                    const uint32_t xs[8] = {lo.x, lo.y, lo.z, lo.w, hi.x, hi.y, hi.z, hi.w};
+                                    const uint32_t gs[8] = {gl.x, gl.y, gl.z, gl.w, gh.x, gh.y, gh.z, gh.w};
+                                    float f[16];
+#pragma unroll
+                                    for (int w = 0; w < 8; ++w) {
+                                        float a = h16_to_float((uint16_t)(xs[w] & 0xffff), p.is_bf16);
+                                        float b = h16_to_float((uint16_t)(xs[w] >> 16), p.is_bf16);
+                                        if (p.norm_mode != B200_NORM_NONE) {
+                                            a *= h16_to_float((uint16_t)(gs[w] & 0xffff), p.is_bf16);
+                                            b *= h16_to_float((uint16_t)(gs[w] >> 16), p.is_bf16);
+                                        }
+                                        f[2 * w] = a * qm;
+                                        f[2 * w + 1] = b * qm;
+                                    }
+                                    v[g][i] = make_uint4(pack_e4m3x4(f[0], f[1], f[2], f[3]), pack_e4m3x4(f[4], f[5], f[6], f[7]),
+                                                         pack_e4m3x4(f[8], f[9], f[10], f[11]), pack_e4m3x4(f[12], f[13], f[14], f[15]));
+                                }
+                                continue;
+                            }
                             const int kcol = (kb + g) * kBK + ch * 8;
 #pragma unroll
                             for (int i = 0; i < NI; ++i) {
@@ -253,7 +293,7 @@ gemm_streamk_kernel(const GemmParams p) {
                             for (int i = 0; i < NI; ++i) {
                                 const int r = r0 + 16 * i;
                                 uint4 val = cur[g][i];
-                                if (p.norm_mode != B200_NORM_NONE) {
+                                if (p.norm_mode != B200_NORM_NONE && !p.is_fp8) {
                                     const int t = t_tile * BN + r;
                                     if (t < p.T) {
                                         const float mean = stat_mean[r], rstd = stat_rstd[r];
@@ -309,7 +349,7 @@ gemm_streamk_kernel(const GemmParams p) {
                 rms_stats_128(p, min(BN, p.T), e, stat_red, stat_rstd);
                 rms_ready = true;
             }
-            const float* tok_scale = (p.norm_mode == B200_NORM_RMS) ? stat_rstd : nullptr;
+            const float* tok_scale = (p.norm_mode == B200_NORM_RMS || p.is_fp8) ? stat_rstd : nullptr;
             // ---- drain the accumulator of this part
             const bool full_tile = (kb0 == 0) && (kb1 == p.kbpt);
             const int slot = (part == 0) ? 0 : 1;
@@ -486,6 +526,12 @@ static int gemm_impl(const b200_gemm_args* a, const b200_tp_args* tp, void* stre
         return fail(B200_EINVAL, "b200_gemm: SwiGLU epilogue requires dual-packed weights");
     const int bn = pick_token_tile(a->T);
     const int t_tiles = (a->T + bn - 1) / bn;
+    if (a->fp8) {
+        if (t_tiles != 1 || bn > 32) return fail(B200_ELIMIT, "b200_gemm: fp8 weights support T <= 32 per call (got %d)", a->T);
+        if (a->K % 128 != 0) return fail(B200_EINVAL, "b200_gemm: fp8 weights need K %% 128 == 0 (got %d)", a->K);
+        if (!a->w_scale) return fail(B200_EINVAL, "b200_gemm: fp8 weights need w_scale");
+        if (a->norm_mode == B200_NORM_LAYER) return fail(B200_EINVAL, "b200_gemm: fp8 + LayerNorm prologue is not supported");
+    }
     if (a->norm_mode != B200_NORM_NONE) {
         if (t_tiles != 1 || bn > 32)
             return fail(B200_EINVAL, "b200_gemm: fused norm prologue supports T <= 32 (got %d)", a->T);
@@ -503,7 +549,9 @@ static int gemm_impl(const b200_gemm_args* a, const b200_tp_args* tp, void* stre
     p.counters = a->counters;
     p.T = a->T; p.N = a->N; p.K = a->K;
     p.ldx = a->ldx; p.ldo = a->ldo; p.ldr = a->ldr;
-    p.n_tiles = a->n_tiles; p.t_tiles = t_tiles; p.kbpt = a->K / kBK;
+    p.n_tiles = a->n_tiles; p.t_tiles = t_tiles; p.kbpt = a->fp8 ? a->K / 128 : a->K / kBK;
+    p.is_fp8 = a->fp8 ? 1 : 0;
+    p.w_scale = a->fp8 ? a->w_scale : nullptr;
     p.Q = (long long)a->n_tiles * t_tiles * p.kbpt;
     p.epilogue = a->epilogue; p.norm_mode = a->norm_mode; p.norm_eps = a->norm_eps;
     p.is_bf16 = (a->dtype == B200_BF16) ? 1 : 0;

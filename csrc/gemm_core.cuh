@@ -2,6 +2,8 @@
 // fused epilogue.  Used by the stand-alone stream-K kernel (gemm.cu) and by the persistent
 // multi-op decode kernel (decode_mega.cu).
 #pragma once
+#include <cuda_fp8.h>
+
 #include "common.h"
 #include "ptx.cuh"
 
@@ -61,6 +63,8 @@ struct GemmParams {
     int* tp_flags[8];     // peer-mapped arrival flags:   [2 parity][world][tp_tiles_max]
     int* tp_seq;          // local: number of fused launches completed on this workspace
     int* tp_exit;         // local: CTAs that have left the current launch
+    int is_fp8;                       // e4m3 weights + on-the-fly e4m3 activations (kind::f8f6f4)
+    const float* __restrict__ w_scale;  // fp8: per-output-row dequantisation scale
     int debug;  // experiment switches (scripts/exp_*.py): 1 = no MMA issue, 2 = no B stage waits
 };
 
@@ -152,6 +156,53 @@ __device__ __forceinline__ void rms_stats_128(const GemmParams& p, int T, int e,
     named_bar_sync(1, 128);
 }
 
+// fp8 activations: per-token quantisation statistics in one pass over the row.
+//   qmul[t]  = 448 / max|x*g|                 (multiplier applied before the e4m3 conversion)
+//   scale[t] = max|x*g| / 448 * (RMSNorm ? 1/rms : 1)   (applied to the accumulator in the epilogue)
+__device__ __forceinline__ void fp8_stats_128(const GemmParams& p, int T, int e, float* red, float* qmul, float* scale) {
+    const int warp = e >> 5, lane = e & 31;
+    for (int t = 0; t < T; ++t) {
+        float s2 = 0.f, am = 0.f;
+        const uint16_t* xr = p.x + (size_t)t * p.ldx;
+        for (int c = e; c < p.K / 8; c += 128) {
+            const uint4 v = ld_cg_v4(xr + c * 8);
+            uint4 g4 = make_uint4(0, 0, 0, 0);
+            if (p.norm_mode != B200_NORM_NONE) g4 = ld_nc_v4(p.norm_w + c * 8);
+            const uint32_t w4[4] = {v.x, v.y, v.z, v.w};
+            const uint32_t gg[4] = {g4.x, g4.y, g4.z, g4.w};
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                float a = h16_to_float((uint16_t)(w4[i] & 0xffff), p.is_bf16);
+                float b = h16_to_float((uint16_t)(w4[i] >> 16), p.is_bf16);
+                s2 += a * a + b * b;
+                if (p.norm_mode != B200_NORM_NONE) {
+                    a *= h16_to_float((uint16_t)(gg[i] & 0xffff), p.is_bf16);
+                    b *= h16_to_float((uint16_t)(gg[i] >> 16), p.is_bf16);
+                }
+                am = fmaxf(am, fmaxf(fabsf(a), fabsf(b)));
+            }
+        }
+        s2 = warp_sum(s2);
+        am = warp_max(am);
+        if (lane == 0) { red[warp * 32 + t] = s2; red[128 + warp * 32 + t] = am; }
+    }
+    named_bar_sync(1, 128);
+    if (e < T) {
+        const float s = red[e] + red[32 + e] + red[64 + e] + red[96 + e];
+        const float am = fmaxf(fmaxf(fmaxf(red[128 + e], red[160 + e]), fmaxf(red[192 + e], red[224 + e])), 1e-20f);
+        const float rstd = (p.norm_mode == B200_NORM_RMS) ? rsqrtf(s / (float)p.K + p.norm_eps) : 1.0f;
+        qmul[e] = 448.0f / am;
+        scale[e] = am / 448.0f * rstd;
+    }
+    named_bar_sync(1, 128);
+}
+
+__device__ __forceinline__ uint32_t pack_e4m3x4(float a, float b, float c, float d) {
+    const uint32_t lo = __nv_cvt_float2_to_fp8x2(make_float2(a, b), __NV_SATFINITE, __NV_E4M3);
+    const uint32_t hi = __nv_cvt_float2_to_fp8x2(make_float2(c, d), __NV_SATFINITE, __NV_E4M3);
+    return lo | (hi << 16);
+}
+
 // Rounds through the 16-bit storage type so fused epilogues see the same values
 // the unfused torch sequence would have stored between ops.
 __device__ __forceinline__ float round16(float v, int is_bf16) {
@@ -165,16 +216,18 @@ __device__ __forceinline__ void epilogue_store_chunk(const GemmParams& p, int n_
     const int n = n_tile * kTileM + row;
     if (n >= p.N) return;
     const float b = p.bias ? h16_to_float(p.bias[n], p.is_bf16) : 0.0f;
+    const float ws_g = p.w_scale ? p.w_scale[n] : 1.0f;
+    const float ws_u = (DUAL && p.w_scale) ? p.w_scale[(size_t)p.n_tiles * kTileM + n] : 1.0f;
 #pragma unroll
     for (int j = 0; j < 16; ++j) {
         const int t = t_tile * BN + chunk * 16 + j;
         if (t >= p.T) break;
         // deferred RMSNorm: the GEMM ran on x*g, the per-token 1/rms is applied here
         const float ts = tok_scale ? tok_scale[chunk * 16 + j] : 1.0f;
-        float v = vg[j] * ts + b;
+        float v = vg[j] * ts * ws_g + b;
         if (DUAL) {
             const float g = round16(v, p.is_bf16);
-            const float u = round16(vu[j] * ts, p.is_bf16);
+            const float u = round16(vu[j] * ts * ws_u, p.is_bf16);
             const float s = round16(g / (1.0f + __expf(-g)), p.is_bf16);
             v = s * u;
         } else if (p.epilogue == B200_EPI_GELU_TANH) {

@@ -120,4 +120,6 @@ def fill_args(x, w, *, out=None, residual=None, epilogue=EPI_NONE, norm_mode=NOR
     a.grid = grid
     a.pdl = 1 if pdl else 0
     a.debug = debug
+    a.fp8 = 1 if w.fp8 else 0
+    a.w_scale = w.scale.data_ptr() if w.scale is not None else None
     return a, out

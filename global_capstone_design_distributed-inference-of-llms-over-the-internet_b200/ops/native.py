@@ -49,6 +49,8 @@ class GemmArgs(ctypes.Structure):
         ("grid", ctypes.c_int32),
         ("pdl", ctypes.c_int32),
         ("debug", ctypes.c_int32),
+        ("fp8", ctypes.c_int32),
+        ("w_scale", ctypes.c_void_p),
     ]
 
 

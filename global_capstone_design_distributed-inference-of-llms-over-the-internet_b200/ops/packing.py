@@ -37,10 +37,12 @@ class PackedWeight:
     n_tiles: int
     dual: bool
     bias: Optional[torch.Tensor] = None
+    fp8: bool = False
+    scale: Optional[torch.Tensor] = None   # fp8: fp32 [n_tiles*128] (dual: [2 * n_tiles*128], gate then up)
 
     @property
     def kb_per_tile(self) -> int:
-        return self.k_padded // BLOCK_K
+        return self.k_padded // (2 * BLOCK_K if self.fp8 else BLOCK_K)
 
     @property
     def nbytes(self) -> int:
@@ -95,3 +97,63 @@ def unpack_weight(p: PackedWeight) -> torch.Tensor:
     t = t.reshape(p.n_tiles, kb, a, TILE_N, BLOCK_K).permute(2, 0, 3, 1, 4)
     full = t.reshape(a, p.n_tiles * TILE_N, kb * BLOCK_K)[:, : p.n, : p.k]
     return full if p.dual else full[0]
+
+
+# ----------------------------------------------------------------------------- fp8 (opt-in)
+FP8_MAX = 448.0
+BLOCK_K8 = 128          # one 128-byte swizzle row holds 128 e4m3 elements
+
+
+def _quantize_rows(w: torch.Tensor):
+    amax = w.float().abs().amax(dim=1).clamp_min(1e-12)
+    scale = amax / FP8_MAX
+    q = (w.float() / scale[:, None]).to(torch.float8_e4m3fn)
+    return q, scale
+
+
+def _tile8(q: torch.Tensor) -> torch.Tensor:
+    """e4m3 [N, K] -> [n_tiles, kb, 128, 128] bytes, 16-byte chunks swizzled like the 16-bit layout."""
+    n, k = q.shape
+    n_pad = (n + TILE_N - 1) // TILE_N * TILE_N
+    k_pad = (k + BLOCK_K8 - 1) // BLOCK_K8 * BLOCK_K8
+    b = q.view(torch.uint8)
+    if n_pad != n or k_pad != k:
+        bp = b.new_zeros((n_pad, k_pad))
+        bp[:n, :k] = b
+        b = bp
+    nt, kb = n_pad // TILE_N, k_pad // BLOCK_K8
+    blk = b.view(nt, TILE_N, kb, 8, 16).permute(0, 2, 1, 3, 4)
+    r = torch.arange(TILE_N, device=q.device)
+    c = torch.arange(8, device=q.device)
+    src = c[None, :] ^ (r[:, None] % 8)
+    return blk[:, :, r[:, None], src, :].contiguous().view(nt, kb, TILE_N, BLOCK_K8)
+
+
+def pack_weight_fp8(w: torch.Tensor, bias: Optional[torch.Tensor] = None) -> PackedWeight:
+    """Per-output-row scaled e4m3 copy of ``w`` in the GEMM's tiled layout."""
+    n, k = w.shape
+    q, scale = _quantize_rows(w)
+    t = _tile8(q)
+    sc = torch.zeros(t.shape[0] * TILE_N, dtype=torch.float32, device=w.device)
+    sc[:n] = scale
+    return PackedWeight(t.reshape(-1), n, k, t.shape[1] * BLOCK_K8, t.shape[0], False,
+                        None if bias is None else bias.contiguous(), True, sc)
+
+
+def pack_dual_fp8(w_gate: torch.Tensor, w_up: torch.Tensor) -> PackedWeight:
+    n, k = w_gate.shape
+    qg, sg = _quantize_rows(w_gate)
+    qu, su = _quantize_rows(w_up)
+    g, u = _tile8(qg), _tile8(qu)
+    t = torch.stack((g, u), dim=2)
+    npad = g.shape[0] * TILE_N
+    sc = torch.zeros(2 * npad, dtype=torch.float32, device=w_gate.device)
+    sc[:n] = sg
+    sc[npad:npad + n] = su
+    return PackedWeight(t.contiguous().reshape(-1), n, k, g.shape[1] * BLOCK_K8, g.shape[0], True, None, True, sc)
+
+
+def dequantize_fp8(w: torch.Tensor) -> torch.Tensor:
+    """What the fp8 GEMM effectively multiplies by (tests): per-row quantise -> dequantise."""
+    q, scale = _quantize_rows(w)
+    return q.float() * scale[:, None]

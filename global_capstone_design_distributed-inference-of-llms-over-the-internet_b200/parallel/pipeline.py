@@ -38,7 +38,8 @@ def _dist_ready() -> bool:
 class PipelineEngine:
     def __init__(self, model: str, splits: Sequence[int] = (), dtype: torch.dtype = torch.float16, device=None, *,
                  backend: Optional[str] = None, kv_capacity: int = 2048, max_sessions: int = 8, max_chunk: int = 512,
-                 seed: int = 0, use_graphs: bool = True, cfg: Optional[ModelConfig] = None):
+                 seed: int = 0, use_graphs: bool = True, cfg: Optional[ModelConfig] = None,
+                 weight_format: str = "native"):
         self.cfg = cfg or resolve_config(model)
         self.rank = dist.get_rank() if _dist_ready() else 0
         self.world = dist.get_world_size() if _dist_ready() else 1
@@ -63,7 +64,8 @@ class PipelineEngine:
             from ..runtime.native_span import NativeSpan
 
             self.span = NativeSpan(self.cfg, w, self.device, dtype, kv_capacity=kv_capacity,
-                                   max_batch=max_sessions, max_chunk=max_chunk, use_graphs=use_graphs)
+                                   max_batch=max_sessions, max_chunk=max_chunk, use_graphs=use_graphs,
+                                   weight_format=weight_format)
         else:
             from ..models.torch_ref import TorchSpan
 

@@ -55,11 +55,21 @@ class NativeSpan:
     def __init__(self, cfg: ModelConfig, weights: Dict[str, object], device, dtype: torch.dtype, *,
                  kv_capacity: int = 2048, max_batch: int = 8, max_chunk: int = 512, attn_splits: int = 0,
                  use_graphs: bool = True, pdl: Optional[bool] = None, free_source_weights: bool = True,
-                 use_mega: Optional[bool] = None, mega_grid: int = 0):
+                 use_mega: Optional[bool] = None, mega_grid: int = 0, weight_format: str = "native"):
         assert dtype in (torch.float16, torch.bfloat16), "native path runs fp16/bf16"
         self.cfg, self.device, self.dtype = cfg, torch.device(device), dtype
         self.kv_capacity, self.max_batch, self.max_chunk = kv_capacity, min(max_batch, MAX_DECODE_BATCH), max_chunk
         self.use_graphs = use_graphs
+        if weight_format not in ("native", "fp8"):
+            raise ValueError("weight_format must be 'native' (fp16/bf16) or 'fp8'")
+        if weight_format == "fp8" and not cfg.is_llama:
+            raise ValueError("fp8 weights are implemented for RMSNorm (Llama-family) models")
+        self.weight_format = weight_format
+        fp8 = weight_format == "fp8"
+        if fp8:
+            self.max_chunk = max_chunk = min(max_chunk, G.MAX_FUSED_NORM_TOKENS)   # fp8 GEMM quantises <= 32 tokens per call
+        pack_w = packing.pack_weight_fp8 if fp8 else packing.pack_weight
+        pack_d = packing.pack_dual_fp8 if fp8 else packing.pack_dual
         self.pdl = _pdl_default() if pdl is None else pdl
         self.use_mega = _mega_default() if use_mega is None else use_mega
         self.mega_grid = mega_grid      # 0 = all SMs; leave a few free when NCCL kernels run concurrently
@@ -71,13 +81,13 @@ class NativeSpan:
             self.layers = []
             for L in weights["layers"]:  # type: ignore[union-attr]
                 P = {"ln1_w": L["ln1_w"], "ln1_b": L.get("ln1_b"), "ln2_w": L["ln2_w"], "ln2_b": L.get("ln2_b"),
-                     "qkv": packing.pack_weight(L["qkv_w"], L.get("qkv_b")),
-                     "o": packing.pack_weight(L["o_w"], L.get("o_b")),
-                     "down": packing.pack_weight(L["down_w"], L.get("down_b"))}
+                     "qkv": pack_w(L["qkv_w"], L.get("qkv_b")),
+                     "o": pack_w(L["o_w"], L.get("o_b")),
+                     "down": pack_w(L["down_w"], L.get("down_b"))}
                 if c.is_llama:
-                    P["mlp_in"] = packing.pack_dual(L["gate_w"], L["up_w"])
+                    P["mlp_in"] = pack_d(L["gate_w"], L["up_w"])
                 else:
-                    P["mlp_in"] = packing.pack_weight(L["fc_w"], L.get("fc_b"))
+                    P["mlp_in"] = pack_w(L["fc_w"], L.get("fc_b"))
                 self.layers.append(P)
                 if free_source_weights:
                     for k in ("qkv_w", "o_w", "down_w", "gate_w", "up_w", "fc_w"):
@@ -87,7 +97,7 @@ class NativeSpan:
             if self.has_head:
                 self.final_norm_w = weights["final_norm_w"]
                 self.final_norm_b = weights.get("final_norm_b")
-                self.lm_head = packing.pack_weight(weights["lm_head"])  # type: ignore[arg-type]
+                self.lm_head = pack_w(weights["lm_head"])  # type: ignore[arg-type]
             self.inv_freq = (A.rope_inv_freq(c.head_dim, c.rope_theta, c.rope_scaling, self.device)
                              if c.is_llama else None)
             self.scale = 1.0 / math.sqrt(c.head_dim)
@@ -240,7 +250,7 @@ class NativeSpan:
 
     def _decode_body(self, B: int, from_ids: bool, greedy: bool):
         h = self._embed(B, 0, True) if from_ids else self.h_a[:B]
-        if self.use_mega and B <= MEGA_MAX_TOKENS and self.tp_mode is None:
+        if self.use_mega and B <= MEGA_MAX_TOKENS and self.tp_mode is None and self.weight_format == "native":
             return self._decode_mega(B, h, greedy)
         h = self._decode_layers(B, h)
         if self.has_head:

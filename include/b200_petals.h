@@ -43,6 +43,11 @@ int b200_sm_count(void);
  * the same number of weight bytes whatever N and K are; partial tiles meet in
  * `scratch` and are summed in a fixed order (bit-reproducible).
  *
+ * Opt-in fp8 weights (fp8 = 1): e4m3 weights with one scale per output row, activations quantised
+ * per token on the fly, tcgen05.mma kind::f8f6f4, scales applied in the epilogue — half the weight
+ * bytes per token (stands in for the reference's dead bitsandbytes NF4/INT8 path,
+ * petals/server/server.py:88,189-191).
+ *
  * Replaces q/k/v_proj, o_proj, gate/up/down_proj, lm_head and their
  * surrounding norm / activation / residual ops:
  * petals/llama/block.py:88-90,151,208-213,227-238; src/llama_partition.py:466-470.
@@ -77,6 +82,8 @@ typedef struct b200_gemm_args {
     int32_t grid;         /* 0 = one CTA per SM */
     int32_t pdl;          /* 1 = launch with programmatic stream serialization */
     int32_t debug;        /* 0 in production; experiment switches, see csrc/gemm.cu */
+    int32_t fp8;          /* 1 = w_packed holds e4m3 weights (pack_weight_fp8), T <= 32, K % 128 == 0 */
+    const float* w_scale; /* fp8: per-output-row dequantisation scale, [n_tiles*128] (dual: gate rows then up rows) */
 } b200_gemm_args;
 
 int b200_gemm(const b200_gemm_args* args, void* stream);

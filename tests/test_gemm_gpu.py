@@ -126,3 +126,57 @@ def test_gemm_fp32_logits_and_small_grid():
     _close(out, _ref(x, w, dtype=dtype), dtype)
     out_small = gemm.linear(x, pw, out_fp32=True, grid=7)
     _close(out_small, _ref(x, w, dtype=dtype), dtype)
+
+
+def _fp8_emulate_act(xn):
+    """Per-token e4m3 round trip of already-normalised (minus 1/rms) activations."""
+    am = xn.abs().amax(-1, keepdim=True).clamp_min(1e-20)
+    q = (xn * (448.0 / am)).to(torch.float8_e4m3fn).float()
+    return q * (am / 448.0)
+
+
+@pytest.mark.parametrize("T", [1, 5, 16, 27])
+@pytest.mark.parametrize("norm", [False, True])
+def test_gemm_fp8_weights(T, norm):
+    from petals_b200.ops import gemm, packing
+
+    dtype = torch.bfloat16
+    torch.manual_seed(21 + T)
+    N, K = 1024, 2048
+    x = (torch.randn(T, K, device="cuda") * 1.5).to(dtype)
+    w = (torch.randn(N, K, device="cuda") / K ** 0.5).to(dtype)
+    g = (1 + 0.1 * torch.randn(K, device="cuda")).to(dtype)
+    res = torch.randn(T, N, device="cuda").to(dtype)
+    pw = packing.pack_weight_fp8(w)
+    assert pw.nbytes == N * K                                    # half the bytes of the 16-bit weight
+    xf = x.float()
+    if norm:
+        rstd = torch.rsqrt(xf.pow(2).mean(-1, keepdim=True) + 1e-5)
+        xa = _fp8_emulate_act(xf * g.float()) * rstd
+        out = gemm.linear(x, pw, norm_mode=gemm.NORM_RMS, norm_w=g, norm_eps=1e-5, residual=res)
+    else:
+        xa = _fp8_emulate_act(xf)
+        out = gemm.linear(x, pw, residual=res)
+    ref = (xa @ packing.dequantize_fp8(w).t()).to(dtype).float() + res.float()
+    _close(out, ref, dtype)
+    exact = ((xf * g.float() * rstd if norm else xf) @ w.float().t()) + res.float()
+    rel = (out.float() - exact).abs().max().item() / exact.abs().max().item()
+    assert rel < 0.06, f"fp8 quantisation error {rel:.3f} out of range"
+
+
+def test_gemm_fp8_swiglu_dual():
+    from petals_b200.ops import gemm, packing
+
+    dtype = torch.float16
+    torch.manual_seed(33)
+    N, K, T = 1408, 1024, 3
+    x = (torch.randn(T, K, device="cuda")).to(dtype)
+    wg = (torch.randn(N, K, device="cuda") / K ** 0.5).to(dtype)
+    wu = (torch.randn(N, K, device="cuda") / K ** 0.5).to(dtype)
+    pw = packing.pack_dual_fp8(wg, wu)
+    out = gemm.linear(x, pw)
+    xa = _fp8_emulate_act(x.float())
+    gq = (xa @ packing.dequantize_fp8(wg).t()).to(dtype).float()
+    uq = (xa @ packing.dequantize_fp8(wu).t()).to(dtype).float()
+    ref = torch.nn.functional.silu(gq).to(dtype).float() * uq
+    _close(out, ref, dtype)

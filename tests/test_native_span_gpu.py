@@ -85,3 +85,21 @@ def test_batched_decode_equals_single(monkeypatch):
         nat.prefill(kv, ids=p)
         l1, _ = nat.decode([kv], ids=ids[i:i + 1])
         assert torch.equal(l1[0], logits_b[i]), "batched decode must be bit-identical to single-session decode"
+
+
+def test_fp8_weight_span_tracks_the_oracle():
+    """Opt-in e4m3 weights: logits stay within quantisation error of the fp32 oracle."""
+    cfg, ref, nat, mref, mnat = _build("tiny-llama-gqa", torch.bfloat16, weight_format="fp8")
+    torch.manual_seed(4)
+    ids = torch.randint(0, cfg.vocab, (50,), device="cuda")
+    kr, kn = mref.allocate("a", 256), mnat.allocate("a", 256)
+    lr = ref.head(ref.forward(ref.embed(ids[:40], 0), kr)[-1:])
+    ln, _ = nat.prefill(kn, ids=ids[:40])                 # 40 tokens -> two <=32-token fp8 chunks
+    scale = lr.abs().max().item()
+    assert (ln - lr).abs().max().item() < 0.15 * scale
+    for t in range(40, 46):
+        lr = ref.head(ref.forward(ref.embed(ids[t:t + 1], t), kr))
+        ln, _ = nat.decode([kn], ids=ids[t:t + 1])
+        assert (ln - lr).abs().max().item() < 0.15 * scale
+    w16 = sum(P[k].nbytes for P in nat.layers for k in ("qkv", "o", "mlp_in", "down"))
+    assert w16 == cfg.n_layers * (cfg.qkv_size * cfg.hidden + cfg.hidden * cfg.q_size + 3 * cfg.hidden * cfg.intermediate)
