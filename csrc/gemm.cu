@@ -9,11 +9,13 @@
 //                               same warps drain TMEM and run the epilogue
 // The weight ring and the activation ring have independent depths, so the
 // HBM stream (weights) is never throttled by the L2-latency-bound B side.
+#include <stdlib.h>
+
 #include "gemm_core.cuh"
 
 namespace b200 {
 
-template <int BN, int DUAL>
+template <int BN, int DUAL, int FP8>
 __global__ void __launch_bounds__(kThreads, GemmCfg<BN, DUAL>::kMinBlocks)
 gemm_streamk_kernel(const GemmParams p) {
     using Cfg = GemmCfg<BN, DUAL>;
@@ -100,7 +102,7 @@ gemm_streamk_kernel(const GemmParams p) {
     } else if (warp == 1) {
         // ------------------------------------------------ MMA issuer (whole warp, one elected lane issues)
         {
-            const uint32_t idesc = p.is_fp8 ? umma_idesc(kTileM, BN, 0, 0, 0, 0)   // e4m3 x e4m3
+            const uint32_t idesc = FP8 ? umma_idesc(kTileM, BN, 0, 0, 0, 0)   // e4m3 x e4m3
                                             : umma_idesc(kTileM, BN, p.is_bf16, p.is_bf16, 0, 0);
             int u = (int)(q_begin / p.kbpt);
             int kb0 = (int)(q_begin - (long long)u * p.kbpt);
@@ -133,7 +135,7 @@ gemm_streamk_kernel(const GemmParams p) {
                                     // +32 B per UMMA_K inside the 128 B swizzle row -> +2 in the address field
                                     const uint32_t d_tmem = tmem_base + (a * Cfg::kNAcc + (k % Cfg::kNAcc)) * BN;
                                     const uint32_t accf = (k >= Cfg::kNAcc) ? 1u : acc;
-                                    if (p.is_fp8) umma_f8f6f4(d_tmem, adesc + (uint64_t)(k * 2), bdesc + (uint64_t)(k * 2), idesc, accf);
+                                    if (FP8) umma_f8f6f4(d_tmem, adesc + (uint64_t)(k * 2), bdesc + (uint64_t)(k * 2), idesc, accf);
                                     else umma_f16(d_tmem, adesc + (uint64_t)(k * 2), bdesc + (uint64_t)(k * 2), idesc, accf);
                                 }
                             }
@@ -209,10 +211,10 @@ gemm_streamk_kernel(const GemmParams p) {
             named_bar_sync(1, kEpiThreads);
         }
 
-        if (p.is_fp8) fp8_stats_128(p, min(BN, p.T), e, stat_red, stat_mean, stat_rstd);   // qmul, epilogue scale
+        if (FP8) fp8_stats_128(p, min(BN, p.T), e, stat_red, stat_mean, stat_rstd);   // qmul, epilogue scale
         uint32_t part = 0, phb = 0;
         int sb = 0;
-        bool rms_ready = p.is_fp8 != 0;   // fp8: the 1/rms is already folded into stat_rstd
+        bool rms_ready = (FP8 != 0);   // fp8: the 1/rms is already folded into stat_rstd
         const int tp_seq = (p.tp_world > 1) ? (__ldcv(p.tp_seq) + 1) : 0;
         long long q = q_begin;
         while (q < q_end) {
@@ -232,7 +234,7 @@ gemm_streamk_kernel(const GemmParams p) {
 #pragma unroll
                     for (int g = 0; g < G; ++g) {
                         if (kb + g < kb1) {
-                            if (p.is_fp8) {
+                            if (FP8) {
                                 // 128 elements per k-block; this thread quantises 16 of them (two 16-byte loads)
                                 const int kcol8 = (kb + g) * 128 + ch * 16;
 #pragma unroll
@@ -293,7 +295,7 @@ gemm_streamk_kernel(const GemmParams p) {
                             for (int i = 0; i < NI; ++i) {
                                 const int r = r0 + 16 * i;
                                 uint4 val = cur[g][i];
-                                if (p.norm_mode != B200_NORM_NONE && !p.is_fp8) {
+                                if (p.norm_mode != B200_NORM_NONE && !FP8) {
                                     const int t = t_tile * BN + r;
                                     if (t < p.T) {
                                         const float mean = stat_mean[r], rstd = stat_rstd[r];
@@ -349,7 +351,7 @@ gemm_streamk_kernel(const GemmParams p) {
                 rms_stats_128(p, min(BN, p.T), e, stat_red, stat_rstd);
                 rms_ready = true;
             }
-            const float* tok_scale = (p.norm_mode == B200_NORM_RMS || p.is_fp8) ? stat_rstd : nullptr;
+            const float* tok_scale = (p.norm_mode == B200_NORM_RMS || FP8) ? stat_rstd : nullptr;
             // ---- drain the accumulator of this part
             const bool full_tile = (kb0 == 0) && (kb1 == p.kbpt);
             const int slot = (part == 0) ? 0 : 1;
@@ -454,7 +456,7 @@ gemm_streamk_kernel(const GemmParams p) {
     }
 }
 
-template <int BN, int DUAL>
+template <int BN, int DUAL, int FP8 = 0>
 static int launch_gemm(const GemmParams& p, int grid, bool pdl, cudaStream_t stream) {
     using Cfg = GemmCfg<BN, DUAL>;
     static_assert(Cfg::kSmemBytes <= 227 * 1024, "shared memory budget exceeded");
@@ -462,12 +464,12 @@ static int launch_gemm(const GemmParams& p, int grid, bool pdl, cudaStream_t str
     int dev = 0;
     B200_CUDA_CHECK(cudaGetDevice(&dev));
     if (configured_dev != dev) {
-        B200_CUDA_CHECK(cudaFuncSetAttribute(gemm_streamk_kernel<BN, DUAL>,
+        B200_CUDA_CHECK(cudaFuncSetAttribute(gemm_streamk_kernel<BN, DUAL, FP8>,
                                              cudaFuncAttributeMaxDynamicSharedMemorySize,
                                              (int)Cfg::kSmemBytes));
         configured_dev = dev;
     }
-    B200_CUDA_CHECK(launch(gemm_streamk_kernel<BN, DUAL>, dim3(grid), dim3(kThreads), Cfg::kSmemBytes,
+    B200_CUDA_CHECK(launch(gemm_streamk_kernel<BN, DUAL, FP8>, dim3(grid), dim3(kThreads), Cfg::kSmemBytes,
                            stream, pdl, p));
     return B200_OK;
 }
@@ -492,7 +494,7 @@ extern "C" int32_t b200_gemm_token_tile(int32_t T, int32_t dual) {
 extern "C" int64_t b200_gemm_scratch_bytes(int32_t max_tokens) {
     const int bn = pick_token_tile(max_tokens);
     // grid <= SM count; two partial slots per CTA; dual doubles the accumulator
-    return (int64_t)sm_count_cached() * 2 * 2 * bn * kTileM * (int64_t)sizeof(float);
+    return (int64_t)sm_count_cached() * 2 /*CTAs per SM*/ * 2 * 2 * bn * kTileM * (int64_t)sizeof(float);
 }
 
 static int gemm_impl(const b200_gemm_args* a, const b200_tp_args* tp, void* stream_);
@@ -568,8 +570,13 @@ static int gemm_impl(const b200_gemm_args* a, const b200_tp_args* tp, void* stre
         p.tp_exit = tp->exit_counter;
     }
 
-    int grid = a->grid > 0 ? a->grid : sm_count_cached();
-    if (grid > sm_count_cached()) grid = sm_count_cached();
+    // The decode tile keeps two CTAs per SM resident (111 KiB of shared memory each): twice as many
+    // loader / MMA-issue threads per SM (measured 280 -> 297 tok/s on Llama-2-7B) and the next
+    // kernel's CTAs can start under PDL while this kernel drains.  B200_GEMM_CTAS_PER_SM=1 restores one.
+    static const int ctas_per_sm = [] { const char* e = getenv("B200_GEMM_CTAS_PER_SM"); return (e && atoi(e) == 1) ? 1 : 2; }();
+    const int max_grid = sm_count_cached() * ((bn == 16 && !a->fp8) ? ctas_per_sm : 1);
+    int grid = a->grid > 0 ? a->grid : max_grid;
+    if (grid > max_grid) grid = max_grid;
     if (a->grid <= 0 && t_tiles == 1) {
         // Few output tiles (o_proj, down_proj): give every tile the same whole number of CTAs so each
         // CTA writes one partial and each tile has equally many contributors (measured 17.4 -> 14.1 us
@@ -580,6 +587,10 @@ static int gemm_impl(const b200_gemm_args* a, const b200_tp_args* tp, void* stre
     if ((long long)grid > p.Q) grid = (int)p.Q;
     cudaStream_t stream = static_cast<cudaStream_t>(stream_);
     const bool pdl = a->pdl != 0;
+    if (a->fp8) {   // only the decode-size tiles are instantiated for e4m3 weights
+        if (bn == 16) return a->dual ? launch_gemm<16, 1, 1>(p, grid, pdl, stream) : launch_gemm<16, 0, 1>(p, grid, pdl, stream);
+        return a->dual ? launch_gemm<32, 1, 1>(p, grid, pdl, stream) : launch_gemm<32, 0, 1>(p, grid, pdl, stream);
+    }
 #define B200_GEMM_CASE(BN_)                                                        \
     case BN_:                                                                      \
         return a->dual ? launch_gemm<BN_, 1>(p, grid, pdl, stream)                 \
@@ -671,6 +682,7 @@ extern "C" int b200_gemm_static_scratch(const b200_gemm_args* a, void* stream_) 
     // The counters must read zero when the kernel starts; whatever an earlier (possibly failed) call left is wiped.
     B200_CUDA_CHECK(cudaMemsetAsync(ws, 0, (size_t)n_units * sizeof(int), stream));
     b200_gemm_args local = *a;
+    local.grid = sm_count_cached();   // one CTA per SM: the built-in workspace has slots for kStaticMaxCtas CTAs
     local.counters = static_cast<int32_t*>(ws);
     local.scratch = reinterpret_cast<float*>(static_cast<unsigned char*>(ws) + kStaticCounterBytes);
     return b200_gemm(&local, stream_);

@@ -7,6 +7,16 @@
 #include "common.h"
 #include "ptx.cuh"
 
+#ifndef B200_SA16
+#define B200_SA16 3        /* 32 KiB weight stages for the decode tile (BN = 16) */
+#endif
+#ifndef B200_GROUP16
+#define B200_GROUP16 2     /* k-blocks per activation stage for the decode tile */
+#endif
+#ifndef B200_MINBLK16
+#define B200_MINBLK16 2   /* CTAs per SM the decode tile is compiled for */
+#endif
+
 namespace b200 {
 
 constexpr int kTileM = 128;            // weight rows per tile (UMMA M)
@@ -23,8 +33,8 @@ struct GemmCfg {
     // MMA loops pay ~100+ ns of barrier latency per stage, so stages must be big.
     static constexpr int kKps = DUAL ? 1 : 2;              // k-blocks per weight stage
     static constexpr int kStageA = kBlockA * kKps;         // 32768
-    static constexpr int kSA = (BN <= 16) ? 6 : (BN == 256) ? 3 : 4;
-    static constexpr int kGroup = (BN == 16) ? 4 : (BN == 32) ? 2 : 1;  // k-blocks per activation stage
+    static constexpr int kSA = (BN <= 16) ? B200_SA16 : (BN == 256) ? 3 : 4;
+    static constexpr int kGroup = (BN == 16) ? B200_GROUP16 : (BN == 32) ? 2 : 1;  // k-blocks per activation stage
     static constexpr int kSubB = BN * 128;                 // one k-block of activations
     static constexpr int kStageB = kSubB * kGroup;
     static constexpr int kSB = (BN == 16) ? 3 : (BN == 32) ? 4 : (BN == 64) ? 6 : (BN == 128) ? 4 : 3;
@@ -35,7 +45,7 @@ struct GemmCfg {
     static constexpr int kNAcc = (BN <= 32) ? 4 : (BN == 64) ? 2 : 1;
     static constexpr int kTmemColsRaw = BN * kAPer * kNAcc;
     static constexpr int kTmemCols = kTmemColsRaw <= 32 ? 32 : kTmemColsRaw <= 64 ? 64 : kTmemColsRaw <= 128 ? 128 : kTmemColsRaw <= 256 ? 256 : 512;
-    static constexpr int kMinBlocks = 1;
+    static constexpr int kMinBlocks = (BN <= 16) ? B200_MINBLK16 : 1;
     static constexpr size_t kSmemData = (size_t)kSA * kStageA + (size_t)kSB * kStageB;
     static constexpr size_t kSmemBytes = kSmemData + 1024 /*align*/ + 1024 /*barriers, stats*/;
 };

@@ -13,7 +13,7 @@ import threading
 
 _LIB = None
 _LOCK = threading.Lock()
-LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "libb200petals.so")
+LIB_PATH = os.environ.get("B200_LIB") or os.path.join(os.path.dirname(os.path.abspath(__file__)), "libb200petals.so")
 
 
 class NativeError(RuntimeError):
