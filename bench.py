@@ -179,8 +179,11 @@ def run_b200(args):
     if eng.is_first:
         eng._tok_host[:S].copy_(eng._tok[:S])
         cur = [int(x) for x in eng._tok_host[:S]]
+    # streaming rounds: every session's token goes device -> host -> device each step, but a session's
+    # next step is issued as soon as ITS token is back (no barrier between rounds)
     for _ in range(3):
-        cur = eng.decode_round(cur)
+        r = eng.decode_round_streaming(cur)
+        cur = r if r else cur
     barrier()
     h2d0, d2h0 = eng.h2d_bytes, eng.d2h_bytes
     lat = []
@@ -189,10 +192,12 @@ def run_b200(args):
     e2.record()
     t_prev = time.perf_counter()
     for _ in range(K):
-        cur = eng.decode_round(cur)
+        r = eng.decode_round_streaming(cur)
+        cur = r if r else cur
         now = time.perf_counter()
         lat.append(now - t_prev)
         t_prev = now
+    eng.flush_streaming()
     e3.record()
     barrier()
     e2e_ms = max_over_ranks(e2.elapsed_time(e3))

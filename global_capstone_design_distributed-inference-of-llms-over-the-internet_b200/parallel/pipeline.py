@@ -223,6 +223,68 @@ class PipelineEngine:
             return [int(x) for x in self._tok_host[:S]]
         return None
 
+    def decode_round_streaming(self, tokens: Optional[Sequence[int]] = None, sessions: Optional[Sequence[int]] = None):
+        """Like :meth:`decode_round` with host-visible tokens, but without a barrier between rounds.
+
+        The first stage issues session j's next step as soon as session j's previous token has been
+        copied to the host (D2H) and back (H2D from pinned memory) — it does not wait for the other
+        sessions of the round, so the chain stays full across rounds.  ``tokens`` seeds the first call;
+        afterwards every call returns, on rank 0, the tokens produced by the PREVIOUS call (``None`` the
+        first time); call :meth:`flush_streaming` to collect the last ones.
+        """
+        sess = list(range(len(self.sessions))) if sessions is None else list(sessions)
+        S = len(sess)
+        if self.world == 1:
+            return self.decode_round(tokens, sessions)
+        last = self.world - 1
+        out = [None] * S
+        have_prev = getattr(self, "_streaming_live", False)
+        for j, si in enumerate(sess):
+            kv = [self.sessions[si]]
+            if self.is_first:
+                if have_prev:
+                    self._wait(self._tok_work[j])
+                    self._tok_work[j] = None
+                    self._tok_host[j:j + 1].copy_(self._tok[j:j + 1])       # D2H of session j's result (blocks on it only)
+                    self.d2h_bytes += 8
+                    out[j] = int(self._tok_host[j])
+                else:
+                    self._tok_host[j] = int(tokens[j])
+                self._tok[j:j + 1].copy_(self._tok_host[j:j + 1], non_blocking=True)   # H2D of the step's input
+                self.h2d_bytes += 8
+                o = self._stage_decode(kv, self._tok[j:j + 1], None)
+                self._wait(self._send_work[j])
+                self._hid[1, j:j + 1].copy_(o[:1])
+                self._send_work[j] = dist.isend(self._hid[1, j:j + 1], 1)
+                self._tok_work[j] = dist.irecv(self._tok[j:j + 1], last, group=self.tok_group)
+            else:
+                h = self._hid[0, j:j + 1]
+                dist.irecv(h, self.rank - 1).wait()
+                o = self._stage_decode(kv, None, h)
+                self._wait(self._send_work[j])
+                if self.is_last:
+                    self._tok_send[j:j + 1].copy_(o[1].reshape(-1)[:1])
+                    self._send_work[j] = dist.isend(self._tok_send[j:j + 1], 0, group=self.tok_group)
+                else:
+                    self._hid[1, j:j + 1].copy_(o[:1])
+                    self._send_work[j] = dist.isend(self._hid[1, j:j + 1], self.rank + 1)
+        self._streaming_live = True
+        return out if (self.is_first and have_prev) else None
+
+    def flush_streaming(self, sessions: Optional[Sequence[int]] = None):
+        """Collect the tokens of the last streaming round (rank 0) and leave streaming mode."""
+        S = len(self.sessions) if sessions is None else len(sessions)
+        out = None
+        if self.is_first and self.world > 1 and getattr(self, "_streaming_live", False):
+            for j in range(S):
+                self._wait(self._tok_work[j])
+                self._tok_work[j] = None
+            self._tok_host[:S].copy_(self._tok[:S])
+            self.d2h_bytes += 8 * S
+            out = [int(x) for x in self._tok_host[:S]]
+        self._streaming_live = False
+        return out
+
     def drain(self) -> None:
         """Wait for every outstanding p2p operation (call before reading staging buffers directly)."""
         for lst in (self._send_work, self._tok_work):
@@ -230,7 +292,8 @@ class PipelineEngine:
                 self._wait(w)
                 lst[j] = None
 
-    def generate(self, prompts: Sequence[torch.Tensor], max_new_tokens: int, eos_token_id: Optional[int] = None):
+    def generate(self, prompts: Sequence[torch.Tensor], max_new_tokens: int, eos_token_id: Optional[int] = None,
+                 streaming: bool = False):
         """Greedy generation for a batch of prompts (one session each).  Returns, on rank 0,
         ``(tokens per prompt, stats)`` with TTFT / decode timings like the reference client prints
         (src/main.py:213-225); None elsewhere."""
@@ -242,7 +305,17 @@ class PipelineEngine:
         outs = [[t] for t in first] if self.is_first else None
         cur = first
         t1 = time.perf_counter()
-        for _ in range(max_new_tokens - 1):
+        if streaming and self.world > 1:
+            for _ in range(max_new_tokens - 1):
+                got = self.decode_round_streaming(cur)
+                if self.is_first and got:
+                    for o, t in zip(outs, got):
+                        o.append(t)
+            got = self.flush_streaming()
+            if self.is_first and got:
+                for o, t in zip(outs, got):
+                    o.append(t)
+        for _ in range(0 if (streaming and self.world > 1) else max_new_tokens - 1):
             cur = self.decode_round(cur)
             if self.is_first:
                 for o, t in zip(outs, cur):

@@ -32,7 +32,9 @@ def _worker(rank, world, port, model, splits, q):
     g = torch.Generator().manual_seed(0)
     prompts = [torch.randint(0, eng.cfg.vocab, (n,), generator=g) for n in (5, 9, 3)]
     res = eng.generate(prompts, 6)
+    res2 = eng.generate(prompts, 6, streaming=True)
     if rank == 0:
+        assert res2[0] == res[0], "streaming rounds must produce the same tokens"
         q.put(res[0])
     dist.barrier()
     dist.destroy_process_group()
