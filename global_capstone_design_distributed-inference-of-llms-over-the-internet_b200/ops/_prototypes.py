@@ -38,6 +38,7 @@ PROTOTYPES = [
     ("b200_attn_decode_scratch_bytes", [i32, i32, i32, i32], i64),
     ("b200_rope_append", [vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, i32, i32, vp], C.c_int),
     ("b200_attn_prefill", [vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, i32, f32, i32, i32, vp], C.c_int),
+    ("b200_attn_prefill_tc", [vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, i32, f32, i32, i32, vp], C.c_int),
     ("b200_embed", [vp, vp, i32, vp, vp, vp, i32, i32, i32, i32, i32, i32, vp], C.c_int),
     ("b200_norm", [vp, vp, vp, vp, i32, i32, i32, i32, f32, i32, i32, i32, vp], C.c_int),
     ("b200_argmax", [vp, i32, i32, i32, vp, vp, vp, vp, i32, i32, vp], C.c_int),

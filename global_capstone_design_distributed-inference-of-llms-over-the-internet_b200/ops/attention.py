@@ -70,8 +70,20 @@ def rope_append(qkv, kcache, vcache, inv_freq, n_heads, n_kv_heads, head_dim, s_
     native.check(rc, "b200_rope_append")
 
 
-def attn_prefill(qkv, out, kcache, vcache, n_heads, n_kv_heads, head_dim, s_max, pos0, scale=None, pdl=False):
-    rc = native.lib().b200_attn_prefill(
+TC_PREFILL_MIN_TOKENS = 32
+
+
+def attn_prefill(qkv, out, kcache, vcache, n_heads, n_kv_heads, head_dim, s_max, pos0, scale=None, pdl=False,
+                 tensor_cores=None):
+    """Causal attention of a chunk against the session cache.  Chunks of >= 32 tokens run on the
+    tcgen05 kernel (csrc/attn_prefill_tc.cu); smaller ones on the CUDA-core kernel.  ``B200_PREFILL_TC=0``
+    forces the latter."""
+    import os
+
+    if tensor_cores is None:
+        tensor_cores = qkv.shape[0] >= TC_PREFILL_MIN_TOKENS and os.environ.get("B200_PREFILL_TC", "1") != "0"
+    fn = native.lib().b200_attn_prefill_tc if tensor_cores else native.lib().b200_attn_prefill
+    rc = fn(
         qkv.data_ptr(), out.data_ptr(), kcache.data_ptr(), vcache.data_ptr(), qkv.shape[0], n_heads, n_kv_heads,
         head_dim, s_max, qkv.stride(0), out.stride(0), pos0,
         scale if scale is not None else head_dim ** -0.5, dtype_code(qkv.dtype), 1 if pdl else 0,

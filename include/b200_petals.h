@@ -182,6 +182,12 @@ int b200_decode_mega_build(const b200_mega_op* ops, int32_t n_ops, void* plan_de
 int b200_decode_mega_launch(const void* plan_device, int32_t n_ops, int32_t* grid_barrier, int32_t grid,
                             int32_t cooperative, void* stream);
 
+/* Same contract on the tensor cores: 128-query x 128-key tiles, S = QK^T and O = PV by tcgen05.mma
+ * (V consumed in place as an MN-major operand), online softmax between them, accumulators in TMEM. */
+int b200_attn_prefill_tc(const void* q, void* out, const void* kcache, const void* vcache, int32_t T, int32_t n_heads,
+                         int32_t n_kv_heads, int32_t head_dim, int32_t s_max, int32_t ldq, int32_t ldo, int32_t pos0,
+                         float scale, int32_t dtype, int32_t pdl, void* stream);
+
 /* ----------------------------------------------------------- elementwise --
  * Embedding gather (+ learned positions for GPT-2): src/llama_partition.py:107.
  * ids are int64 on the device (the last stage writes them there). */

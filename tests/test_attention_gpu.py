@@ -89,13 +89,13 @@ def test_attn_decode(nh, nkv, D, rope, past, dtype):
 
 @pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
 @pytest.mark.parametrize("nh,nkv,D,rope", [(4, 4, 128, True), (8, 2, 128, True), (4, 4, 64, False)])
-@pytest.mark.parametrize("T,pos0", [(1, 0), (7, 0), (33, 0), (128, 0), (40, 100), (200, 17)])
+@pytest.mark.parametrize("T,pos0", [(1, 0), (7, 0), (33, 0), (128, 0), (40, 100), (200, 17), (300, 130), (256, 0)])
 def test_rope_append_and_prefill(nh, nkv, D, rope, T, pos0, dtype):
     from petals_b200.ops import attention as A
 
     torch.manual_seed(T + pos0)
     dev = "cuda"
-    s_max = 512
+    s_max = 1024
     inv = A.rope_inv_freq(D, 500000.0, device=dev) if rope else None
     qkv = torch.randn(T, (nh + 2 * nkv) * D, device=dev).to(dtype)
     kc = torch.zeros(nkv, s_max, D, device=dev, dtype=dtype)
