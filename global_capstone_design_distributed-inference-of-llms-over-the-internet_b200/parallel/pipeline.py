@@ -141,27 +141,49 @@ class PipelineEngine:
         return hcat
 
     # ------------------------------------------------------------------ public API
-    def prefill(self, session: int, prompt_ids: torch.Tensor) -> Optional[int]:
+    def prefill(self, session: int, prompt_ids: torch.Tensor, micro_batch: Optional[int] = None) -> Optional[int]:
         """Run a prompt through the chain; returns the first generated token on rank 0
-        (None on the other ranks).  ``prompt_ids``: 1-D int64, same on every rank."""
+        (None on the other ranks).  ``prompt_ids``: 1-D int64, same on every rank.
+
+        The prompt travels in micro-batches of ``micro_batch`` tokens (default: the engine's chunk
+        size): while stage s+1 works on chunk c, stage s already computes chunk c+1 and the
+        hand-off of chunk c rides NCCL in the background — upstream Petals chunks the prompt in time
+        only to bound the score matrix (petals/server/backend.py:129-152); here the chunks also fill
+        the pipeline."""
         kv = self.sessions[session]
         L = int(prompt_ids.shape[0])
+        mb = int(micro_batch or getattr(self.span, "max_chunk", 0) or 512)
+        chunks = [(c0, min(mb, L - c0)) for c0 in range(0, L, mb)]
         ids_dev = None
         if self.is_first:
             ids_dev = prompt_ids.to(self.device, non_blocking=True)
             self.h2d_bytes += L * 8
-        h = None
-        if not self.is_first:
-            h = torch.empty(L, self.cfg.hidden, dtype=self.dtype, device=self.device)
-            self._recv(h, self.rank - 1)
-        out = self._stage_prefill(kv, ids_dev, h)
+        H = self.cfg.hidden
         tok = self._tok[:1]
+        pending = []                       # keep send buffers alive until their isend completed
+        out = None
+        recv_next = None
+        if not self.is_first:
+            buf = torch.empty(chunks[0][1], H, dtype=self.dtype, device=self.device)
+            recv_next = (buf, dist.irecv(buf, self.rank - 1))
+        for ci, (c0, n) in enumerate(chunks):
+            h = None
+            if not self.is_first:
+                h, work = recv_next
+                work.wait()
+                if ci + 1 < len(chunks):   # post the next receive before computing this chunk
+                    nb = torch.empty(chunks[ci + 1][1], H, dtype=self.dtype, device=self.device)
+                    recv_next = (nb, dist.irecv(nb, self.rank - 1))
+            out = self._stage_prefill(kv, ids_dev[c0:c0 + n] if self.is_first else None, h)
+            if not self.is_last:
+                o = out.contiguous()
+                pending.append((o, dist.isend(o, self.rank + 1)))
+        for _, w in pending:
+            w.wait()
         if self.is_last:
             tok.copy_(out[1].reshape(-1)[:1])
             if not self.is_first:
                 self._send(tok, 0, self.tok_group)
-        else:
-            self._send(out.contiguous(), self.rank + 1)
         if self.is_first:
             if not self.is_last:
                 self._recv(tok, self.world - 1, self.tok_group)

@@ -32,6 +32,12 @@ def _worker(rank, world, port, model, splits, q):
     g = torch.Generator().manual_seed(0)
     prompts = [torch.randint(0, eng.cfg.vocab, (n,), generator=g) for n in (5, 9, 3)]
     res = eng.generate(prompts, 6)
+    # micro-batched prefill (3-token chunks flowing through the chain) must give the same first token
+    eng.close_sessions()
+    sid = eng.open_sessions(1)[0]
+    first = eng.prefill(sid, prompts[1], micro_batch=3)
+    if rank == 0:
+        assert first == res[0][1][0], "micro-batched prefill changed the result"
     res2 = eng.generate(prompts, 6, streaming=True)
     if rank == 0:
         assert res2[0] == res[0], "streaming rounds must produce the same tokens"
