@@ -29,7 +29,16 @@ def _mega_op_type():
     return MegaOp
 
 
+class SampleRow(C.Structure):
+    """Mirror of ``b200::SampleRow`` (csrc/sampling.cu)."""
+
+    _fields_ = [("temperature", f32), ("top_p", f32), ("penalty", f32), ("top_k", i32), ("n_recent", i32),
+                ("recent", i32 * 50)]
+
+
 PROTOTYPES = [
+    ("b200_sample_row_bytes", [], i32),
+    ("b200_sample", [vp, i32, i32, i32, vp, vp, vp, vp, i32, vp], C.c_int),
     ("b200_decode_mega_plan_bytes", [i32], i64),
     ("b200_decode_mega_build", [vp, i32, vp], C.c_int),
     ("b200_decode_mega_launch", [vp, i32, vp, i32, i32, vp], C.c_int),

@@ -201,6 +201,15 @@ int b200_norm(const void* x, const void* w, const void* b, void* out, int32_t T,
 int b200_argmax(const float* logits, int32_t ld, int32_t T, int32_t V, float* part_val, int32_t* part_idx,
                 int32_t* counters, void* out_ids, int32_t chunks, int32_t pdl, void* stream);
 
+/* Temperature / top-k / top-p / repetition-penalty sampling on the device with the reference's rules
+ * (src/rpc_handler.py:327-403), one CTA per row, no sort (radix descent over float bit patterns).
+ * rows: T records {float temperature, top_p, penalty; int32 top_k, n_recent; int32 recent[50]} on the
+ * device (b200_sample_row_bytes() each); uniforms: T floats in [0,1) (e.g. torch.rand on the device,
+ * philox); probs: T*V floats of scratch, holds the final un-normalised distribution on return. */
+int32_t b200_sample_row_bytes(void);
+int b200_sample(const float* logits, int32_t ld, int32_t T, int32_t V, const void* rows, const float* uniforms,
+                float* probs, void* out_ids, int32_t pdl, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -129,10 +129,22 @@ class StageConnectionHandler:
                 float(metadata.get("temperature", self._default_temperature)),
                 float(metadata.get("top_p", self._default_top_p)), int(metadata.get("top_k", self._default_top_k)),
                 float(metadata.get("repetition_penalty", 1.5)))
-            token = sample_token(logits, params, metadata.get("generated_tokens") or [],
-                                 generator=self._gen if logits.device.type == "cpu" else None)
+            generated = metadata.get("generated_tokens") or []
+            if logits.is_cuda and params.temperature > 0.0 and logits.dtype == torch.float32:
+                token = self._device_sample(logits, params, generated)          # csrc/sampling.cu
+            else:
+                token = sample_token(logits, params, generated,
+                                     generator=self._gen if logits.device.type == "cpu" else None)
             return [torch.tensor([[token]], dtype=torch.long)], {"token_id": token, "session_id": sid}
         return [out.detach().to("cpu")], {"session_id": sid}
+
+    def _device_sample(self, logits: torch.Tensor, params: SamplingParams, generated) -> int:
+        from petals_b200.ops.sampling import DeviceSampler
+
+        if getattr(self, "_dsampler", None) is None or self._dsampler.vocab != logits.shape[-1]:
+            self._dsampler = DeviceSampler(logits.device, 1, logits.shape[-1])
+        ids = self._dsampler.sample(logits.reshape(1, -1).contiguous(), params, [list(generated)])
+        return int(ids[0].item())
 
     def _submit(self, fn, *args, kind="inference", tokens=0):
         return self.pool.submit(fn, *args, kind=kind, tokens=tokens).result(timeout=self.request_timeout)
