@@ -102,6 +102,27 @@ class KVCacheManager:
             self.sessions[session_id] = s
             return s
 
+    def reorder(self, session_ids, hypo_ids) -> None:
+        """Beam-search bookkeeping: after the call, session ``session_ids[i]`` continues the hypothesis
+        that ``session_ids[hypo_ids[i]]`` held (upstream reorders cache rows by ``hypo_ids`` inside one
+        batched cache, petals/server/backend.py:154-158; sessions here are separate buffers, so the
+        surviving prefixes are copied, cached length included)."""
+        sess = [self.sessions[s] for s in session_ids]
+        src_idx = [int(h) for h in hypo_ids]
+        if len(src_idx) != len(sess) or any(not 0 <= h < len(sess) for h in src_idx):
+            raise ValueError("hypo_ids must index into session_ids")
+        need = {h for i, h in enumerate(src_idx) if h != i}
+        snap = {h: (sess[h].data[:, :, :, : sess[h].length].clone(), sess[h].length) for h in need}
+        for i, h in enumerate(src_idx):
+            if h == i:
+                continue
+            data, length = snap[h]
+            if length > sess[i].max_len:
+                raise ValueError("destination session is too small for the source hypothesis")
+            sess[i].data[:, :, :, :length].copy_(data)
+            sess[i].length = length
+            sess[i].touch()
+
     def close(self, session_id: str) -> bool:
         with self._lock:
             return self.sessions.pop(session_id, None) is not None

@@ -211,3 +211,19 @@ def test_reachability_probe():
     assert check_direct_reachability("/ip4/127.0.0.1/tcp/1")[0] is False
     with pytest.raises(RuntimeError):
         validate_reachability(["/ip4/127.0.0.1/tcp/1"], 0.5)
+
+
+def test_kv_reorder_by_hypo_ids():
+    from petals_b200.runtime.kv_cache import KVCacheManager
+
+    m = KVCacheManager(2, 1, 4, torch.float32, "cpu")
+    ss = [m.allocate(f"b{i}", 8) for i in range(3)]
+    for i, s in enumerate(ss):
+        s.data[:, :, :, : i + 2] = float(i + 1)
+        s.length = i + 2
+    m.reorder(["b0", "b1", "b2"], [2, 0, 0])          # a 3-cycle-free permutation with a duplicate source
+    assert ss[0].length == 4 and float(ss[0].data[0, 0, 0, 3, 0]) == 3.0
+    assert ss[1].length == 2 and float(ss[1].data[1, 1, 0, 1, 0]) == 1.0
+    assert ss[2].length == 2 and float(ss[2].data[0, 0, 0, 0, 0]) == 1.0
+    with pytest.raises(ValueError):
+        m.reorder(["b0", "b1"], [0, 5])
