@@ -32,6 +32,7 @@ from ..ops import attention as A
 from ..ops import elementwise as E
 from ..ops import gemm as G
 from ..ops import packing
+from ..utils.metrics import nvtx_range
 from .kv_cache import SessionKV
 
 MAX_DECODE_BATCH = 32
@@ -328,6 +329,10 @@ class NativeSpan:
         Returns hidden states [B, H] (view of a static buffer) — or, on the last stage,
         ``(logits [B, V] fp32, ids_out [B] int64)`` device views.
         """
+        with nvtx_range("b200.decode_step"):
+            return self._decode_impl(kvs, h_in, ids, greedy)
+
+    def _decode_impl(self, kvs, h_in, ids, greedy):
         B = len(kvs)
         assert 1 <= B <= self.max_batch
         from_ids = self.embed_w is not None and h_in is None

@@ -31,6 +31,7 @@ import torch
 
 from petals_b200.net.dht import DHT, parse_maddr
 from petals_b200.net.rpc import RpcClient, RpcError
+from petals_b200.utils import metrics
 
 from .dht_utils import get_block_entries, get_stage_entries
 from .rpc_handler import HANDLER_PREFIX
@@ -242,6 +243,7 @@ class RpcTransport:
                             continue
                     self.failed_peers.setdefault(hop.key, set()).add(hop.peer_id)
                     logger.info("Marked peer %s as failed for %s", hop.peer_id[:12], hop.key)
+                    metrics.emit("recovery", session=session_id, hop=hop.key, peer=hop.peer_id[:12], error=str(e)[:200])
                     route, hop = self._recover(session_id, route, i)
                     if self.push and not hop.final:
                         md["route"] = [[h.addr[0], h.addr[1], h.key] for h in route[i + 1:]]
@@ -249,6 +251,8 @@ class RpcTransport:
             # journal only what the server has actually consumed
             self._journal(session_id, hop.key).append(cur.clone())
             self.hop_times.append((hop.key, time.perf_counter() - t0))
+            metrics.emit("hop", session=session_id, hop=hop.key, peer=hop.peer_id[:12], seconds=self.hop_times[-1][1],
+                         tokens=int(T), prefill=bool(is_prefill))
             if "token_id" in omd or hop.final or (self.push and "token_id" in omd):
                 self.last_token = int(omd.get("token_id", out[0].reshape(-1)[0].item()))
                 break

@@ -227,3 +227,24 @@ def test_kv_reorder_by_hypo_ids():
     assert ss[2].length == 2 and float(ss[2].data[0, 0, 0, 0, 0]) == 1.0
     with pytest.raises(ValueError):
         m.reorder(["b0", "b1"], [0, 5])
+
+
+def test_metrics_jsonl_and_percentiles(tmp_path, monkeypatch):
+    import json as _json
+
+    from petals_b200.utils import metrics
+
+    f = tmp_path / "m.jsonl"
+    monkeypatch.setenv("PETALS_B200_METRICS", str(f))
+    monkeypatch.setattr(metrics, "_sink", None)
+    metrics.emit("hop", hop="block_8", seconds=0.0123)
+    metrics.emit("recovery", peer="Qm1")
+    lines = [_json.loads(x) for x in f.read_text().splitlines()]
+    assert [r["kind"] for r in lines] == ["hop", "recovery"] and lines[0]["hop"] == "block_8"
+    h = metrics.LatencyHistogram()
+    for ms in (1, 2, 3, 4, 100):
+        h.add(ms / 1e3)
+    s = h.summary()
+    assert s["n"] == 5 and s["p50"] == 3 and s["max"] == 100 and sum(h.counts) == 5
+    with metrics.nvtx_range("noop"):
+        pass
