@@ -1,0 +1,242 @@
+// Prefill-size GEMM (T >= 64): out[T,N] = epi(x[T,K] . W[N,K]^T) on tcgen05 with every operand
+// moved by the TMA engine and the epilogue overlapped with the next tile's main loop.
+//
+//   warp 0      producer: per k-block one cp.async.bulk of the pre-tiled weight block (16/32 KiB)
+//               and one cp.async.bulk.tensor.2d of the [BN tokens x 64] activation box (128B swizzle,
+//               rows past T are zero-filled by the TMA unit) on the same mbarrier
+//   warp 1      MMA issuer: 128 x BN x 16 tcgen05.mma into one of TWO TMEM accumulator buffers
+//   warps 2..5  epilogue: drain the other buffer (bias / GELU / SwiGLU / residual) while the tensor
+//               core already works on the next tile
+// Persistent grid, tiles assigned round-robin; tiles that share a weight block run on neighbouring
+// CTAs at the same time, so the weight block is read from HBM once and from L2 afterwards.
+// The decode-size kernel (gemm.cu) stages activations with the worker warps instead (fused norm,
+// fp8 quantisation) and splits K across CTAs; neither is needed once T fills the tile.
+#include <cuda.h>
+#include <string.h>
+
+#include "gemm_core.cuh"
+
+namespace b200 {
+
+template <int BN, int DUAL>
+struct PrefillCfg {
+    static constexpr int kAPer = DUAL ? 2 : 1;
+    static constexpr int kBytesA = kABytes * kAPer;          // weight bytes per k-block
+    static constexpr int kBytesB = BN * 128;                 // activation bytes per k-block
+    static constexpr int kStage = kBytesA + kBytesB;
+    static constexpr int kStages = (200 * 1024) / kStage;    // 4 for (256, single) and (128, dual)
+    static constexpr int kAccCols = BN * kAPer;              // TMEM columns of one accumulator buffer
+    static constexpr int kTmemCols = 2 * kAccCols <= 256 ? 256 : 512;
+    static constexpr size_t kSmemBytes = (size_t)kStages * kStage + 1024 + 1024;
+    static_assert(2 * kAccCols <= 512, "two accumulator buffers must fit TMEM");
+};
+
+__device__ __forceinline__ void tma_load_2d(void* smem_dst, const CUtensorMap* tmap, int c0, int c1, uint64_t* bar) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];\n" ::
+            "r"(smem_u32(smem_dst)),
+        "l"(tmap), "r"(c0), "r"(c1), "r"(smem_u32(bar))
+        : "memory");
+}
+
+template <int BN, int DUAL>
+__global__ void __launch_bounds__(kThreads, 1)
+gemm_prefill_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_x) {
+    using Cfg = PrefillCfg<BN, DUAL>;
+    constexpr int S = Cfg::kStages, APER = Cfg::kAPer;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + (size_t)S * Cfg::kStage);
+    uint64_t* full = bars;              // [S]
+    uint64_t* empty = bars + S;         // [S]
+    uint64_t* acc_full = empty + S;     // [2]
+    uint64_t* acc_empty = acc_full + 2; // [2]
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + 2);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (threadIdx.x == 0) {
+        for (int i = 0; i < S; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
+        for (int i = 0; i < 2; ++i) { mbar_init(&acc_full[i], 1); mbar_init(&acc_empty[i], 4); }
+        fence_mbar_init();
+        asm volatile("prefetch.tensormap [%0];\n" ::"l"(&tmap_x) : "memory");
+    }
+    if (warp == 1) tmem_alloc<Cfg::kTmemCols>(tmem_slot);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+    pdl_launch_dependents();
+
+    const int units = p.n_tiles * p.t_tiles;
+
+    if (warp == 0) {
+        // ------------------------------------------------------------ TMA producer
+        pdl_wait_prior_grid();   // activations come from the previous kernel
+        int s = 0;
+        uint32_t ph = 0;
+        for (int u = blockIdx.x; u < units; u += gridDim.x) {
+            const int n_tile = u / p.t_tiles, t_tile = u - n_tile * p.t_tiles;
+            const uint8_t* wt = p.w + (size_t)n_tile * p.kbpt * Cfg::kBytesA;
+            for (int kb = 0; kb < p.kbpt; ++kb) {
+                mbar_wait(&empty[s], ph ^ 1);
+                if (elect_one()) {
+                    uint8_t* st = smem + (size_t)s * Cfg::kStage;
+                    mbar_arrive_expect_tx(&full[s], Cfg::kStage);
+                    bulk_g2s(st, wt + (size_t)kb * Cfg::kBytesA, Cfg::kBytesA, &full[s]);
+                    tma_load_2d(st + Cfg::kBytesA, &tmap_x, kb * kBK, t_tile * BN, &full[s]);
+                }
+                __syncwarp();
+                if (++s == S) { s = 0; ph ^= 1; }
+            }
+        }
+    } else if (warp == 1) {
+        // ------------------------------------------------------------ MMA issuer
+        const uint32_t idesc = umma_idesc(kTileM, BN, p.is_bf16, p.is_bf16, 0, 0);
+        const uint32_t base = smem_u32(smem);
+        int s = 0;
+        uint32_t ph = 0, it = 0;
+        for (int u = blockIdx.x; u < units; u += gridDim.x, ++it) {
+            const int buf = it & 1;
+            mbar_wait(&acc_empty[buf], ((it >> 1) & 1) ^ 1);
+            tc_fence_after();
+            const uint32_t d0 = tmem_base + buf * Cfg::kAccCols;
+            for (int kb = 0; kb < p.kbpt; ++kb) {
+                mbar_wait(&full[s], ph);
+                tc_fence_after();
+                if (elect_one()) {
+                    const uint32_t a_addr = base + s * Cfg::kStage, b_addr = a_addr + Cfg::kBytesA;
+                    const uint64_t bdesc = umma_desc_kmajor_sw128(b_addr, 1024);
+#pragma unroll
+                    for (int a = 0; a < APER; ++a) {
+                        const uint64_t adesc = umma_desc_kmajor_sw128(a_addr + a * kABytes, 1024);
+#pragma unroll
+                        for (int k = 0; k < kBK / 16; ++k)
+                            umma_f16(d0 + a * BN, adesc + (uint64_t)(k * 2), bdesc + (uint64_t)(k * 2), idesc,
+                                     (kb > 0 || k > 0) ? 1u : 0u);
+                    }
+                    umma_commit(&empty[s]);
+                }
+                __syncwarp();
+                if (++s == S) { s = 0; ph ^= 1; }
+            }
+            if (elect_one()) umma_commit(&acc_full[buf]);
+            __syncwarp();
+        }
+    } else {
+        // ------------------------------------------------------------ epilogue warps
+        const int lg = warp & 3;
+        const int row = lg * 32 + lane;
+        uint32_t it = 0;
+        for (int u = blockIdx.x; u < units; u += gridDim.x, ++it) {
+            const int n_tile = u / p.t_tiles, t_tile = u - n_tile * p.t_tiles;
+            const int buf = it & 1;
+            mbar_wait(&acc_full[buf], (it >> 1) & 1);
+            tc_fence_after();
+            const int t_live = min(BN, p.T - t_tile * BN);
+            const uint32_t taddr0 = tmem_base + buf * Cfg::kAccCols + ((uint32_t)(lg * 32) << 16);
+#pragma unroll 1
+            for (int c = 0; c * 16 < t_live; ++c) {
+                uint32_t rg[16], ru[16];
+                tmem_ld16(taddr0 + c * 16, rg);
+                if (DUAL) tmem_ld16(taddr0 + BN + c * 16, ru);
+                tmem_ld_wait();
+                float vg[16], vu[16];
+#pragma unroll
+                for (int j = 0; j < 16; ++j) {
+                    vg[j] = __uint_as_float(rg[j]);
+                    vu[j] = DUAL ? __uint_as_float(ru[j]) : 0.f;
+                }
+                epilogue_store_chunk<BN, DUAL>(p, n_tile, t_tile, row, c, vg, vu, nullptr);
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&acc_empty[buf]);
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) tmem_dealloc<Cfg::kTmemCols>(tmem_base);
+}
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn encode_tiled_fn() {
+    static EncodeTiledFn fn = [] {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess ||
+            q != cudaDriverEntryPointSuccess)
+            p = nullptr;
+        return reinterpret_cast<EncodeTiledFn>(p);
+    }();
+    return fn;
+}
+
+template <int BN, int DUAL>
+static int launch_prefill(const GemmParams& p, const CUtensorMap& tmap, int grid, bool pdl, cudaStream_t stream) {
+    using Cfg = PrefillCfg<BN, DUAL>;
+    static_assert(Cfg::kSmemBytes <= 227 * 1024, "shared memory budget exceeded");
+    static thread_local int configured_dev = -1;
+    int dev = 0;
+    B200_CUDA_CHECK(cudaGetDevice(&dev));
+    if (configured_dev != dev) {
+        B200_CUDA_CHECK(cudaFuncSetAttribute(gemm_prefill_kernel<BN, DUAL>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             (int)Cfg::kSmemBytes));
+        configured_dev = dev;
+    }
+    B200_CUDA_CHECK(launch(gemm_prefill_kernel<BN, DUAL>, dim3(grid), dim3(kThreads), Cfg::kSmemBytes, stream, pdl, p, tmap));
+    return B200_OK;
+}
+
+}  // namespace b200
+
+using namespace b200;
+
+// Same argument struct as b200_gemm; valid for T >= 64, no norm prologue, 16-bit weights.
+extern "C" int b200_gemm_prefill(const b200_gemm_args* a, void* stream_) {
+    if (!a || !a->w_packed || !a->x || !a->out) return fail(B200_EINVAL, "b200_gemm_prefill: null pointer argument");
+    if (a->T <= 0 || a->N <= 0 || a->K <= 0 || (a->K % kBK) != 0)
+        return fail(B200_EINVAL, "b200_gemm_prefill: bad sizes T=%d N=%d K=%d", a->T, a->N, a->K);
+    if (a->norm_mode != B200_NORM_NONE || a->fp8)
+        return fail(B200_EINVAL, "b200_gemm_prefill: norm prologue / fp8 weights belong to b200_gemm");
+    if (a->n_tiles * kTileM < a->N) return fail(B200_EINVAL, "b200_gemm_prefill: n_tiles does not cover N");
+    if ((a->ldx % 8) != 0 || (reinterpret_cast<uintptr_t>(a->x) & 15) != 0)
+        return fail(B200_EINVAL, "b200_gemm_prefill: x must be 16-byte aligned with ldx %% 8 == 0");
+    if (a->dual && a->epilogue != B200_EPI_SWIGLU) return fail(B200_EINVAL, "b200_gemm_prefill: dual weights need SwiGLU");
+    EncodeTiledFn enc = encode_tiled_fn();
+    if (!enc) return fail(B200_ECUDA, "b200_gemm_prefill: cuTensorMapEncodeTiled is not available from the driver");
+    const int bn = a->dual ? 128 : 256;
+    GemmParams p;
+    memset(&p, 0, sizeof(p));
+    p.w = static_cast<const uint8_t*>(a->w_packed);
+    p.x = static_cast<const uint16_t*>(a->x);
+    p.out = a->out;
+    p.residual = static_cast<const uint16_t*>(a->residual);
+    p.bias = static_cast<const uint16_t*>(a->bias);
+    p.T = a->T; p.N = a->N; p.K = a->K;
+    p.ldx = a->ldx; p.ldo = a->ldo; p.ldr = a->ldr;
+    p.n_tiles = a->n_tiles; p.t_tiles = (a->T + bn - 1) / bn; p.kbpt = a->K / kBK;
+    p.epilogue = a->epilogue;
+    p.is_bf16 = (a->dtype == B200_BF16) ? 1 : 0;
+    p.out_fp32 = a->out_fp32;
+
+    CUtensorMap tmap;
+    const cuuint64_t dims[2] = {(cuuint64_t)a->K, (cuuint64_t)a->T};
+    const cuuint64_t strides[1] = {(cuuint64_t)a->ldx * 2};
+    const cuuint32_t box[2] = {(cuuint32_t)kBK, (cuuint32_t)bn};
+    const cuuint32_t estr[2] = {1, 1};
+    const CUresult r = enc(&tmap, p.is_bf16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2,
+                           const_cast<void*>(a->x), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                           CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return fail(B200_ECUDA, "b200_gemm_prefill: cuTensorMapEncodeTiled failed (%d)", (int)r);
+
+    const int units = p.n_tiles * p.t_tiles;
+    int grid = a->grid > 0 ? a->grid : sm_count_cached();
+    if (grid > sm_count_cached()) grid = sm_count_cached();
+    if (grid > units) grid = units;
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    return a->dual ? launch_prefill<128, 1>(p, tmap, grid, a->pdl != 0, stream)
+                   : launch_prefill<256, 0>(p, tmap, grid, a->pdl != 0, stream);
+}

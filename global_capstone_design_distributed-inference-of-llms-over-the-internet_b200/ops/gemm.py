@@ -79,9 +79,23 @@ def linear(
     a, out = fill_args(x, w, out=out, residual=residual, epilogue=epilogue, norm_mode=norm_mode, norm_w=norm_w,
                        norm_b=norm_b, norm_eps=norm_eps, out_fp32=out_fp32, workspace=workspace, pdl=pdl, grid=grid,
                        debug=debug)
+    if (x.shape[0] >= PREFILL_MIN_TOKENS and norm_mode == NORM_NONE and not w.fp8 and _prefill_kernel_enabled()):
+        # token-tile-filling inputs: TMA-fed kernel with the epilogue overlapped (csrc/gemm_prefill.cu)
+        rc = native.lib().b200_gemm_prefill(ctypes.byref(a), native.current_stream_ptr())
+        native.check(rc, "b200_gemm_prefill")
+        return out
     rc = native.lib().b200_gemm(ctypes.byref(a), native.current_stream_ptr())
     native.check(rc, "b200_gemm")
     return out
+
+
+PREFILL_MIN_TOKENS = 64
+
+
+def _prefill_kernel_enabled() -> bool:
+    import os
+
+    return os.environ.get("B200_PREFILL_GEMM", "1") != "0"
 
 
 def fill_args(x, w, *, out=None, residual=None, epilogue=EPI_NONE, norm_mode=NORM_NONE, norm_w=None, norm_b=None,

@@ -74,6 +74,8 @@ def lib() -> ctypes.CDLL:
             L.b200_sm_count.restype = ctypes.c_int
             L.b200_gemm.argtypes = [ctypes.POINTER(GemmArgs), ctypes.c_void_p]
             L.b200_gemm.restype = ctypes.c_int
+            L.b200_gemm_prefill.argtypes = [ctypes.POINTER(GemmArgs), ctypes.c_void_p]
+            L.b200_gemm_prefill.restype = ctypes.c_int
             L.b200_gemm_scratch_bytes.argtypes = [ctypes.c_int32]
             L.b200_gemm_scratch_bytes.restype = ctypes.c_int64
             L.b200_gemm_token_tile.argtypes = [ctypes.c_int32, ctypes.c_int32]

@@ -92,6 +92,11 @@ int64_t b200_gemm_scratch_bytes(int32_t max_tokens);
 /* Token-tile width the kernel will pick for T tokens (16,32,64,128,256). */
 int32_t b200_gemm_token_tile(int32_t T, int32_t dual);
 
+/* Prefill-size variant (T >= 64, no norm prologue, 16-bit weights; same argument struct, scratch and
+ * counters unused): weights by cp.async.bulk, activations by a 2-D TMA tensor map, two TMEM accumulator
+ * buffers so the epilogue of a tile overlaps the main loop of the next. */
+int b200_gemm_prefill(const b200_gemm_args* args, void* stream);
+
 /* Row-parallel linear of a tensor-parallel span with the all-reduce fused into the tile epilogue
  * (decode sizes, T <= 16): every rank runs this with its K shard of the weight; the CTA that finishes
  * an output tile pushes its fp32 partial into every rank's staging buffer with peer stores over
