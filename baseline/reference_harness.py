@@ -151,7 +151,11 @@ def _recv(sock):
     return pickle.loads(bytes(buf))
 
 
-def _serve(handler, port_holder, ready, stop, deserialize, msgpack_ser):
+def _serve(handler, port_holder, ready, stop, deserialize, msgpack_ser, device=None, done=None):
+    if device is not None:
+        import torch
+
+        torch.cuda.set_device(device)     # the current CUDA device is per host thread
     srv = socket.socket()
     srv.setsockopt(socket.SOL_SOCKET, socket.SO_REUSEADDR, 1)
     srv.bind(("127.0.0.1", port_holder[0]))
@@ -173,6 +177,8 @@ def _serve(handler, port_holder, ready, stop, deserialize, msgpack_ser):
                 _send(conn, (resp.tensors[0], resp.metadata))
         except (ConnectionError, OSError):
             conn.close()
+            if done is not None:
+                done.set()                # the client hung up: this stage's work is over
     srv.close()
 
 
@@ -245,12 +251,22 @@ def run(args) -> None:
         return h
 
     stop = threading.Event()
+    done = threading.Event()
     ports = [[0] for _ in range(n_stages)]
+
+    def watchdog():
+        # never leave the driver waiting on a wedged reference run
+        if not stop.wait(float(os.environ.get("REFERENCE_ARM_TIMEOUT", "420"))):
+            if rank == 0:
+                print(json.dumps({"impl": "reference", "unavailable": "reference harness timed out"}), flush=True)
+            os._exit(0)
+
+    threading.Thread(target=watchdog, daemon=True).start()
     threads = []
     if world == 1:
         h = make_server(1, dev)
         ready = threading.Event()
-        t = threading.Thread(target=_serve, args=(h, ports[1], ready, stop, deserialize, mser), daemon=True)
+        t = threading.Thread(target=_serve, args=(h, ports[1], ready, stop, deserialize, mser, dev, done), daemon=True)
         t.start(); ready.wait(30); threads.append(t)
         port_list = [0, ports[1][0]]
     else:
@@ -258,7 +274,7 @@ def run(args) -> None:
         if rank > 0:
             h = make_server(rank, dev)
             ready = threading.Event()
-            t = threading.Thread(target=_serve, args=(h, ports[rank], ready, stop, deserialize, mser), daemon=True)
+            t = threading.Thread(target=_serve, args=(h, ports[rank], ready, stop, deserialize, mser, dev, done), daemon=True)
             t.start(); ready.wait(30); threads.append(t)
         pt = torch.tensor([ports[rank][0] if rank > 0 else 0], device=dev, dtype=torch.int64)
         allp = [torch.zeros_like(pt) for _ in range(world)]
@@ -355,10 +371,10 @@ def run(args) -> None:
         }
         for s in socks:
             s.close()
-    if world > 1:
-        dist.barrier()
-    stop.set()
-    if rank == 0:
         print(json.dumps(result), flush=True)
-    if world > 1:
-        dist.destroy_process_group()
+    elif world > 1:
+        done.wait()          # serve until the client closes the connection (no collective while serving:
+                             # a blocking NCCL barrier here would starve the server thread)
+    stop.set()
+    sys.stdout.flush()
+    os._exit(0)              # skip process-group teardown: ranks finish at different times by design
