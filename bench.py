@@ -43,6 +43,8 @@ def parse_args():
     ap.add_argument("--dtype", default="fp16", choices=["fp16", "bf16"])
     ap.add_argument("--prompt-len", type=int, default=128)
     ap.add_argument("--sessions", type=int, default=0, help="in-flight sessions (default: one per stage)")
+    ap.add_argument("--group", type=int, default=1,
+                    help="sessions per micro-batch travelling through the chain together (serving-throughput mode)")
     ap.add_argument("--weights", default="native", choices=["native", "fp8"],
                     help="fp8 = opt-in e4m3 weights (NOT the headline configuration)")
     return ap.parse_args()
@@ -152,7 +154,7 @@ def run_b200(args):
             eng._tok[:S].copy_(native.ids_in[:S])
         else:
             for _ in range(n):
-                eng.decode_round(None, to_host=False)
+                eng.decode_round(None, to_host=False, group=args.group)
 
     device_steps(W)
     barrier()
@@ -214,7 +216,7 @@ def run_b200(args):
             "data": "synthetic prompts, random-init weights",
             "impl": "b200",
             "config": {"model": args.model, "global_batch": S, "seq_len": L, "parallelism": f"pp{world}",
-                       "sessions_in_flight": S, "batch_per_session": 1,
+                       "sessions_in_flight": S, "batch_per_session": 1, "sessions_per_micro_batch": args.group,
                        "l2": "every step streams all weights (13.5 GB >> 126 MB L2); no flush needed",
                        "p50_token_latency_ms": round(statistics.median(lat) * 1e3, 4),
                        "hbm_roofline_frac_measured": round(

@@ -192,7 +192,7 @@ class PipelineEngine:
         return None
 
     def decode_round(self, tokens: Optional[Sequence[int]] = None, sessions: Optional[Sequence[int]] = None,
-                     to_host: bool = True):
+                     to_host: bool = True, group: int = 1):
         """One new token for each listed session (default: all), one session per pipeline slot.
 
         ``tokens``: the previous token of every session (host ints, read on rank 0); when
@@ -211,30 +211,34 @@ class PipelineEngine:
             self._tok[:S].copy_(out[1].reshape(-1)[:S])
         else:
             # Asynchronous chain: sends never block the compute stream, receives are waited on right
-            # before use, and every slot j has its own staging buffers so a send may still be in
-            # flight while the next session is computed.
+            # before use, and every slot has its own staging buffers so a send may still be in
+            # flight while the next micro-batch is computed.  A micro-batch is `group` sessions that
+            # travel together as one [group, H] activation (one batched kernel sequence per stage).
             last = self.world - 1
-            for j, si in enumerate(sess):
-                kv = [self.sessions[si]]
+            g = max(1, int(group))
+            for j0 in range(0, S, g):
+                j1 = min(S, j0 + g)
+                kv = [self.sessions[si] for si in sess[j0:j1]]
+                slot = j0
                 if self.is_first:
-                    self._wait(self._tok_work[j])                     # token of slot j from the previous round
-                    self._tok_work[j] = None
-                    out = self._stage_decode(kv, self._tok[j:j + 1], None)
-                    self._wait(self._send_work[j])
-                    self._hid[1, j:j + 1].copy_(out[:1])
-                    self._send_work[j] = dist.isend(self._hid[1, j:j + 1], 1)
-                    self._tok_work[j] = dist.irecv(self._tok[j:j + 1], last, group=self.tok_group)
+                    self._wait(self._tok_work[slot])                  # tokens of this micro-batch from the previous round
+                    self._tok_work[slot] = None
+                    out = self._stage_decode(kv, self._tok[j0:j1], None)
+                    self._wait(self._send_work[slot])
+                    self._hid[1, j0:j1].copy_(out[: j1 - j0])
+                    self._send_work[slot] = dist.isend(self._hid[1, j0:j1], 1)
+                    self._tok_work[slot] = dist.irecv(self._tok[j0:j1], last, group=self.tok_group)
                 else:
-                    h = self._hid[0, j:j + 1]
+                    h = self._hid[0, j0:j1]
                     dist.irecv(h, self.rank - 1).wait()
                     out = self._stage_decode(kv, None, h)
-                    self._wait(self._send_work[j])
+                    self._wait(self._send_work[slot])
                     if self.is_last:
-                        self._tok_send[j:j + 1].copy_(out[1].reshape(-1)[:1])
-                        self._send_work[j] = dist.isend(self._tok_send[j:j + 1], 0, group=self.tok_group)
+                        self._tok_send[j0:j1].copy_(out[1].reshape(-1)[: j1 - j0])
+                        self._send_work[slot] = dist.isend(self._tok_send[j0:j1], 0, group=self.tok_group)
                     else:
-                        self._hid[1, j:j + 1].copy_(out[:1])
-                        self._send_work[j] = dist.isend(self._hid[1, j:j + 1], self.rank + 1)
+                        self._hid[1, j0:j1].copy_(out[: j1 - j0])
+                        self._send_work[slot] = dist.isend(self._hid[1, j0:j1], self.rank + 1)
             if self.is_first and (to_host or tokens is not None):
                 for j in range(S):
                     self._wait(self._tok_work[j])

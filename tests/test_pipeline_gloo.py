@@ -38,6 +38,18 @@ def _worker(rank, world, port, model, splits, q):
     first = eng.prefill(sid, prompts[1], micro_batch=3)
     if rank == 0:
         assert first == res[0][1][0], "micro-batched prefill changed the result"
+    # micro-batches of two sessions travelling together must not change any token
+    eng.close_sessions()
+    ids3 = eng.open_sessions(len(prompts))
+    cur = [eng.prefill(i, p) for i, p in zip(ids3, prompts)]
+    grouped = [[c] for c in cur] if rank == 0 else None
+    for _ in range(5):
+        cur = eng.decode_round(cur, group=2)
+        if rank == 0:
+            for o, tkn in zip(grouped, cur):
+                o.append(tkn)
+    if rank == 0:
+        assert grouped == res[0], "grouped micro-batches changed the tokens"
     res2 = eng.generate(prompts, 6, streaming=True)
     if rank == 0:
         assert res2[0] == res[0], "streaming rounds must produce the same tokens"
