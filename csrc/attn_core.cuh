@@ -222,15 +222,15 @@ __device__ __forceinline__ void attn_decode_body(const AttnDecodeParams& p, int 
         }
     }
     if (eff == 1) return;
-    __threadfence();
-    sync();
+    sync();   // orders every thread's partial stores before thread 0's release below
     if (tid == 0) {
-        const int old = atomicAdd(&p.counters[t * p.n_kv + g], 1);
+        int old;
+        asm volatile("atom.acq_rel.gpu.global.add.s32 %0, [%1], %2;\n"
+                     : "=r"(old) : "l"(&p.counters[t * p.n_kv + g]), "r"(1) : "memory");
         s_last = (old + 1 == eff) ? 1 : 0;
     }
     sync();
     if (!s_last) return;
-    __threadfence();
     for (int idx = tid; idx < GROUP * D; idx += kAttnThreads) {
         const int h = idx / D, d = idx % D;
         const float* src = p.scratch + ((size_t)(t * p.n_heads + g * GROUP + h) * splits) * (D + 2);
