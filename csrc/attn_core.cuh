@@ -19,7 +19,10 @@ struct AttnDecodeParams {
 };
 
 constexpr int kAttnThreads = 128;
-constexpr int kMinRowsPerSplit = 64;
+#ifndef B200_ATTN_MIN_ROWS
+#define B200_ATTN_MIN_ROWS 64
+#endif
+constexpr int kMinRowsPerSplit = B200_ATTN_MIN_ROWS;
 
 __device__ __forceinline__ void unpack8(const uint4& v, float (&f)[8], int is_bf16) {
     const uint32_t w[4] = {v.x, v.y, v.z, v.w};
