@@ -172,6 +172,7 @@ gemm_streamk_kernel(const GemmParams p) {
         const int r0 = e >> 3;                  // first token row this thread stages
 
         pdl_wait_prior_grid();  // activations come from the previous kernel
+        if (p.gather_world > 1) tp_gather_prologue(p, e);   // x = residual + sum of the TP partials of the previous linear
 
         if (p.norm_mode == B200_NORM_LAYER) {
             // Per-token statistics (decode-size T only; host guarantees t_tiles == 1, BN <= 32).
@@ -380,6 +381,7 @@ gemm_streamk_kernel(const GemmParams p) {
                 }
                 if (full_tile) {
                     if (p.tp_world > 1) tp_allreduce_tile(p, n_tile, row, ncol, e, tp_seq, vg);
+                    if (!(p.tp_world > 1 && p.tp_defer))
                     epilogue_store_chunk<BN, DUAL>(p, n_tile, t_tile, row, c, vg, vu, tok_scale);
                 } else {
 #pragma unroll
@@ -436,6 +438,7 @@ gemm_streamk_kernel(const GemmParams p) {
                             }
                         }
                         if (p.tp_world > 1) tp_allreduce_tile(p, n_tile, row, ncol, e, tp_seq, vg);
+                        if (!(p.tp_world > 1 && p.tp_defer))
                         epilogue_store_chunk<BN, DUAL>(p, n_tile, t_tile, row, c, vg, vu, tok_scale);
                     }
                     if (e == 0) p.counters[u] = 0;  // leave the counters clean for the next launch
@@ -500,7 +503,8 @@ extern "C" int64_t b200_gemm_scratch_bytes(int32_t max_tokens) {
     return (int64_t)sm_count_cached() * 2 /*CTAs per SM*/ * 2 * 2 * bn * kTileM * (int64_t)sizeof(float);
 }
 
-static int gemm_impl(const b200_gemm_args* a, const b200_tp_args* tp, void* stream_);
+static int gemm_impl(const b200_gemm_args* a, const b200_tp_args* tp, void* stream_, const b200_tp_args* gather = nullptr,
+                     const void* gather_residual = nullptr, const void* gather_bias = nullptr, int gather_ldr = 0);
 
 extern "C" int b200_gemm(const b200_gemm_args* a, void* stream_) { return gemm_impl(a, nullptr, stream_); }
 
@@ -516,7 +520,20 @@ extern "C" int b200_gemm_allreduce(const b200_gemm_args* a, const b200_tp_args* 
     return gemm_impl(a, tp, stream_);
 }
 
-static int gemm_impl(const b200_gemm_args* a, const b200_tp_args* tp, void* stream_) {
+// Consumer of a deferred b200_gemm_allreduce (tp->mode == 1): before staging, every CTA rebuilds
+// x[t, :] = residual[t, :] + bias + sum over ranks of the partial rows pushed by the producer, writes it to
+// a->x (so later kernels can use it as their residual) and then runs the normal GEMM on it.
+extern "C" int b200_gemm_gather(const b200_gemm_args* a, const b200_tp_args* tp, const void* residual, int32_t ldr,
+                                const void* bias, void* stream_) {
+    if (!a || !tp || !residual) return fail(B200_EINVAL, "b200_gemm_gather: null argument");
+    if (tp->world < 2 || tp->world > 8) return fail(B200_EINVAL, "b200_gemm_gather: bad world %d", tp->world);
+    if (a->T > 16 || a->K > tp->n_max || a->K % 512 != 0)
+        return fail(B200_ELIMIT, "b200_gemm_gather: T <= 16 and K a multiple of 512 within the workspace (T=%d K=%d)", a->T, a->K);
+    return gemm_impl(a, nullptr, stream_, tp, residual, bias, ldr);
+}
+
+static int gemm_impl(const b200_gemm_args* a, const b200_tp_args* tp, void* stream_, const b200_tp_args* gather,
+                     const void* gather_residual, const void* gather_bias, int gather_ldr) {
     if (!a || !a->w_packed || !a->x || !a->out || !a->scratch || !a->counters)
         return fail(B200_EINVAL, "b200_gemm: null pointer argument");
     if (a->T <= 0 || a->N <= 0 || a->K <= 0 || (a->K % kBK) != 0)
@@ -563,6 +580,7 @@ static int gemm_impl(const b200_gemm_args* a, const b200_tp_args* tp, void* stre
     p.out_fp32 = a->out_fp32;
     p.debug = a->debug;
     p.tp_world = 0;
+    p.tp_defer = 0;
     if (tp) {
         p.tp_world = tp->world; p.tp_rank = tp->rank; p.tp_n_max = tp->n_max; p.tp_tiles_max = tp->tiles_max;
         for (int r = 0; r < tp->world; ++r) {
@@ -571,6 +589,18 @@ static int gemm_impl(const b200_gemm_args* a, const b200_tp_args* tp, void* stre
         }
         p.tp_seq = tp->seq;
         p.tp_exit = tp->exit_counter;
+        p.tp_defer = tp->mode == 1 ? 1 : 0;
+    }
+    p.gather_world = 0;
+    if (gather) {
+        p.gather_world = gather->world; p.gather_rank = gather->rank;
+        p.gather_n_max = gather->n_max; p.gather_tiles_max = gather->tiles_max;
+        p.gather_stage = static_cast<const float*>(gather->stage[gather->rank]);
+        p.gather_flags = static_cast<const int*>(gather->flags[gather->rank]);
+        p.gather_seq = gather->seq;
+        p.gather_residual = static_cast<const uint16_t*>(gather_residual);
+        p.gather_bias = static_cast<const uint16_t*>(gather_bias);
+        p.gather_ldr = gather_ldr;
     }
 
     // The decode tile keeps two CTAs per SM resident (111 KiB of shared memory each): twice as many

@@ -73,6 +73,15 @@ struct GemmParams {
     int* tp_flags[8];     // peer-mapped arrival flags:   [2 parity][world][tp_tiles_max]
     int* tp_seq;          // local: number of fused launches completed on this workspace
     int* tp_exit;         // local: CTAs that have left the current launch
+    int tp_defer;         // 1: push partial tiles only; the CONSUMER kernel waits for them and adds them up
+    // consumer side ("gather" prologue): rebuild x = residual + bias + sum_r partial_r before staging it
+    int gather_world, gather_rank, gather_n_max, gather_tiles_max;
+    const float* gather_stage;        // this rank's staging buffer
+    const int* gather_flags;          // this rank's arrival flags
+    const int* gather_seq;            // launch number of the producer (read after it has completed)
+    const uint16_t* gather_residual;  // [T, K] 16-bit
+    const uint16_t* gather_bias;      // [K] 16-bit or null
+    int gather_ldr;
     int is_fp8;                       // e4m3 weights + on-the-fly e4m3 activations (kind::f8f6f4)
     const float* __restrict__ w_scale;  // fp8: per-output-row dequantisation scale
     int debug;  // experiment switches (scripts/exp_*.py): 1 = no MMA issue, 2 = no B stage waits
@@ -89,52 +98,91 @@ __device__ __forceinline__ float gelu_tanh(float x) {
 
 // ---- fused all-reduce of one finished 128-row tile across the tensor-parallel group ------------
 // Every rank holds a partial sum (its K shard) of the same output tile.  The finisher of the tile
-//   1. pushes its fp32 partial into EVERY rank's staging buffer with peer stores over NVLink and
-//      raises that rank's arrival flag (release, system scope) to the launch sequence number;
-//   2. waits until all ranks' flags for this tile carry the same number (acquire loads on local memory);
+//   1. pushes its fp32 partial into EVERY rank's staging buffer with peer stores over NVLink, each value
+//      paired with the launch sequence number in one 8-byte word (no fences, no separate flags);
+//   2. polls the other ranks' words of this tile in LOCAL memory until they carry the same number;
 //   3. adds the partials in rank order — every rank computes bit-identical sums — into vg.
 // Staging buffers and flags alternate between two halves by launch parity, so a rank that is one
 // launch ahead never overwrites data a slower peer is still reading (a rank cannot get two ahead:
 // finishing a launch requires every peer's pushes for it).
+__device__ __forceinline__ float round16(float v, int is_bf16);
+
+// "LL" exchange words (as in NCCL's low-latency protocol): a 4-byte value and the 4-byte launch sequence
+// number travel in ONE 8-byte store, so the receiver needs no fence and no separate flag — it polls the
+// word until the sequence number matches.  Sequence numbers never repeat for a slot.
+__device__ __forceinline__ void ll_store(uint2* dst, float v, int seq) {
+    asm volatile("st.volatile.global.v2.u32 [%0], {%1, %2};\n" ::"l"(dst), "r"(__float_as_uint(v)), "r"(seq) : "memory");
+}
+__device__ __forceinline__ float ll_load(const uint2* src, int seq) {
+    uint32_t a, b;
+    long long t0 = 0;
+    for (;;) {
+        asm volatile("ld.volatile.global.v2.u32 {%0, %1}, [%2];\n" : "=r"(a), "=r"(b) : "l"(src) : "memory");
+        if ((int)b == seq) break;
+        if (t0 == 0) t0 = clock64();
+        else if (clock64() - t0 > 8000000000LL) {
+            printf("b200: tensor-parallel exchange timed out (block %d thread %d, seq %d, saw %d)\n", blockIdx.x,
+                   threadIdx.x, seq, (int)b);
+            __trap();
+        }
+    }
+    return __uint_as_float(a);
+}
+
+// Consumer half of the deferred exchange (all-gather -> GEMM fusion): executed by the 128 worker threads
+// of EVERY CTA of the next GEMM before they stage activations.  Waits until all ranks' partial tiles of
+// the producer launch have landed in local memory, then writes x[t, :] = residual + bias + sum over
+// ranks (rank order) as 16-bit values.  All CTAs write identical values, so the redundancy is benign;
+// it costs two L2 round trips instead of an exposed NVLink round trip at the producer's tail.
+__device__ __forceinline__ void tp_gather_prologue(const GemmParams& p, int e) {
+    const int R = p.gather_world, seq = __ldcv(p.gather_seq), par = seq & 1;
+    const int H = p.K;
+    const uint2* stage = reinterpret_cast<const uint2*>(p.gather_stage);
+    uint16_t* x = const_cast<uint16_t*>(p.x);
+    for (int t = 0; t < p.T; ++t) {
+        for (int n = e * 2; n < H; n += 256) {
+            float a = 0.f, b = 0.f;
+            for (int r = 0; r < R; ++r) {
+                const uint2* src = stage + ((size_t)(par * R + r) * 16 + t) * p.gather_n_max + n;
+                a += ll_load(src, seq);
+                b += ll_load(src + 1, seq);
+            }
+            if (p.gather_bias) {
+                a += h16_to_float(p.gather_bias[n], p.is_bf16);
+                b += h16_to_float(p.gather_bias[n + 1], p.is_bf16);
+            }
+            const uint32_t rw = *reinterpret_cast<const uint32_t*>(p.gather_residual + (size_t)t * p.gather_ldr + n);
+            // same rounding sequence as the in-producer epilogue: round the linear's output, then add the residual
+            a = round16(a, p.is_bf16) + h16_to_float((uint16_t)(rw & 0xffff), p.is_bf16);
+            b = round16(b, p.is_bf16) + h16_to_float((uint16_t)(rw >> 16), p.is_bf16);
+            *reinterpret_cast<uint32_t*>(x + (size_t)t * p.ldx + n) =
+                (uint32_t)float_to_h16(a, p.is_bf16) | ((uint32_t)float_to_h16(b, p.is_bf16) << 16);
+        }
+    }
+    named_bar_sync(1, 128);
+}
+
 __device__ __forceinline__ void tp_allreduce_tile(const GemmParams& p, int tile, int row, int ncol, int e, int seq,
                                                   float (&vg)[16]) {
     const int R = p.tp_world, me = p.tp_rank, par = seq & 1;
     const size_t slot = (size_t)(par * R + me) * 16;
     const int n = tile * kTileM + row;
     for (int r = 0; r < R; ++r) {
-        float* dst = p.tp_stage[r] + slot * p.tp_n_max + n;
+        uint2* dst = reinterpret_cast<uint2*>(p.tp_stage[r]) + slot * p.tp_n_max + n;
 #pragma unroll
         for (int j = 0; j < 16; ++j)
-            if (j < ncol) __stcg(dst + (size_t)j * p.tp_n_max, vg[j]);
+            if (j < ncol) ll_store(dst + (size_t)j * p.tp_n_max, vg[j], seq);
     }
-    __threadfence_system();
-    named_bar_sync(1, 128);
-    if (e < R) {
-        int* f = p.tp_flags[e] + (size_t)(par * R + me) * p.tp_tiles_max + tile;
-        asm volatile("st.release.sys.global.s32 [%0], %1;\n" ::"l"(f), "r"(seq) : "memory");
-    }
-    if (e < R) {
-        const int* f = p.tp_flags[me] + (size_t)(par * R + e) * p.tp_tiles_max + tile;
-        long long t0 = clock64();
-        int v;
-        do {
-            asm volatile("ld.acquire.sys.global.s32 %0, [%1];\n" : "=r"(v) : "l"(f) : "memory");
-            if (v != seq && clock64() - t0 > 8000000000LL) {
-                printf("b200: tensor-parallel tile exchange timed out (rank %d waits for rank %d, tile %d, seq %d, flag %d)\n",
-                       me, e, tile, seq, v);
-                __trap();
-            }
-        } while (v != seq);
-    }
-    named_bar_sync(1, 128);
-    __threadfence_system();
+    if (p.tp_defer) return;   // the consumer kernel waits and adds (tp_gather_prologue)
+    const uint2* mine = reinterpret_cast<const uint2*>(p.tp_stage[me]);
+    float own[16];
 #pragma unroll
-    for (int j = 0; j < 16; ++j) vg[j] = 0.f;
+    for (int j = 0; j < 16; ++j) { own[j] = vg[j]; vg[j] = 0.f; }
     for (int r = 0; r < R; ++r) {
-        const float* src = p.tp_stage[me] + (size_t)(par * R + r) * 16 * p.tp_n_max + n;
+        const uint2* src = mine + (size_t)(par * R + r) * 16 * p.tp_n_max + n;
 #pragma unroll
         for (int j = 0; j < 16; ++j)
-            if (j < ncol) vg[j] += __ldcv(src + (size_t)j * p.tp_n_max);
+            if (j < ncol) vg[j] += (r == me) ? own[j] : ll_load(src + (size_t)j * p.tp_n_max, seq);
     }
 }
 

@@ -37,7 +37,7 @@ class TpArgs(ctypes.Structure):
 
     _fields_ = [("world", ctypes.c_int32), ("rank", ctypes.c_int32), ("n_max", ctypes.c_int32),
                 ("tiles_max", ctypes.c_int32), ("stage", ctypes.c_void_p * 8), ("flags", ctypes.c_void_p * 8),
-                ("seq", ctypes.c_void_p), ("exit_counter", ctypes.c_void_p)]
+                ("seq", ctypes.c_void_p), ("exit_counter", ctypes.c_void_p), ("mode", ctypes.c_int32)]
 
 
 class TPWorkspace:
@@ -50,7 +50,7 @@ class TPWorkspace:
         self.world, self.rank = dist.get_world_size(group), dist.get_rank(group)
         self.n_max = (n_max + 127) // 128 * 128
         self.tiles_max = self.n_max // 128
-        stage_floats = 2 * self.world * MAX_TP_TOKENS * self.n_max
+        stage_floats = 2 * 2 * self.world * MAX_TP_TOKENS * self.n_max   # (value, sequence number) pairs
         flag_ints = 2 * self.world * self.tiles_max
         self.stage = symm.empty(stage_floats, dtype=torch.float32, device=device)
         self.flags = symm.empty(flag_ints, dtype=torch.int32, device=device)
@@ -74,21 +74,49 @@ class TPWorkspace:
                                f"(stage {a.stage[self.rank]:#x} vs {self.stage.data_ptr():#x})")
         a.seq = self.local.data_ptr()
         a.exit_counter = self.local.data_ptr() + 4
+        a.mode = 0
         self.args = a
+        d = TpArgs()
+        ctypes.memmove(ctypes.byref(d), ctypes.byref(a), ctypes.sizeof(TpArgs))
+        d.mode = 1
+        self.args_defer = d          # producer pushes only; the next GEMM gathers (linear_gather)
         L = native.lib()
+        L.b200_gemm_gather.argtypes = [ctypes.POINTER(native.GemmArgs), ctypes.POINTER(TpArgs), ctypes.c_void_p,
+                                       ctypes.c_int32, ctypes.c_void_p, ctypes.c_void_p]
+        L.b200_gemm_gather.restype = ctypes.c_int
         L.b200_gemm_allreduce.argtypes = [ctypes.POINTER(native.GemmArgs), ctypes.POINTER(TpArgs), ctypes.c_void_p]
         L.b200_gemm_allreduce.restype = ctypes.c_int
 
 
 def linear_allreduce(x: torch.Tensor, w: PackedWeight, tp: TPWorkspace, *, out: torch.Tensor,
                      residual: Optional[torch.Tensor] = None, workspace: Optional[G.GemmWorkspace] = None,
-                     pdl: bool = False, add_bias: bool = True) -> torch.Tensor:
-    """out = sum_over_ranks(x_shard @ W_shard^T) [+ bias] [+ residual], identical on every rank."""
-    a, out = G.fill_args(x, w, out=out, residual=residual, workspace=workspace, pdl=pdl)
-    if not add_bias:
+                     pdl: bool = False, add_bias: bool = True, defer: bool = False) -> torch.Tensor:
+    """out = sum_over_ranks(x_shard @ W_shard^T) [+ bias] [+ residual], identical on every rank.
+
+    ``defer=True``: only push this rank's partial tiles; ``out`` is NOT written — the next GEMM must be
+    issued with :func:`linear_gather`, which waits for the partials, adds them (+ bias, + residual) into
+    its input buffer and multiplies."""
+    a, out = G.fill_args(x, w, out=out, residual=None if defer else residual, workspace=workspace, pdl=pdl)
+    if not add_bias or defer:
         a.bias = None
-    rc = native.lib().b200_gemm_allreduce(ctypes.byref(a), ctypes.byref(tp.args), native.current_stream_ptr())
+    tpa = tp.args_defer if defer else tp.args
+    rc = native.lib().b200_gemm_allreduce(ctypes.byref(a), ctypes.byref(tpa), native.current_stream_ptr())
     native.check(rc, "b200_gemm_allreduce")
+    return out
+
+
+def linear_gather(x_buf: torch.Tensor, w: PackedWeight, tp: TPWorkspace, *, residual: torch.Tensor,
+                  bias: Optional[torch.Tensor] = None, **linear_kw) -> torch.Tensor:
+    """GEMM whose input ``x_buf`` is first rebuilt as residual + bias + sum of the partial rows a deferred
+    :func:`linear_allreduce` pushed (all-gather -> GEMM in one kernel).  ``x_buf`` holds the reduced hidden
+    state afterwards.  Remaining keywords as :func:`petals_b200.ops.gemm.linear`."""
+    ws = linear_kw.pop("workspace", None)
+    pdl = linear_kw.pop("pdl", False)
+    out = linear_kw.pop("out", None)
+    a, out = G.fill_args(x_buf, w, out=out, workspace=ws, pdl=pdl, **linear_kw)
+    rc = native.lib().b200_gemm_gather(ctypes.byref(a), ctypes.byref(tp.args), residual.data_ptr(), residual.stride(0),
+                                       bias.data_ptr() if bias is not None else None, native.current_stream_ptr())
+    native.check(rc, "b200_gemm_gather")
     return out
 
 

@@ -175,6 +175,9 @@ class NativeSpan:
         """h: [T, H] view of a static buffer; returns the buffer view holding the result."""
         c, pdl = self.cfg, self.pdl
         other = self.h_b if h.data_ptr() == self.h_a.data_ptr() else self.h_a
+        deferred = self.tp_mode == "fused" and T <= 16 and getattr(self, "tp_defer", False)   # measured slower than the in-producer exchange
+        if deferred:
+            return self._decode_layers_tp_deferred(T, h, other)
         for li, P in enumerate(self.layers):
             qkv, attn, act, h2 = self.qkv[:T], self.attn[:T], self.act[:T], other[:T]
             G.linear(h, P["qkv"], out=qkv, norm_mode=self.norm_mode, norm_w=P["ln1_w"], norm_b=P["ln1_b"],
@@ -185,6 +188,39 @@ class NativeSpan:
             G.linear(h2, P["mlp_in"], out=act, epilogue=self.mlp_epi, norm_mode=self.norm_mode, norm_w=P["ln2_w"],
                      norm_b=P["ln2_b"], norm_eps=c.norm_eps, workspace=self.ws, pdl=pdl)
             self._row_parallel(act, P["down"], h, h2)
+            self._count(5)
+        return h
+
+    def _decode_layers_tp_deferred(self, T: int, h: torch.Tensor, other: torch.Tensor) -> torch.Tensor:
+        """Tensor-parallel decode with the exchange split across kernels: each row-parallel linear only
+        PUSHES its partial tiles to the peers; the following column-parallel linear waits for them and adds
+        them up while staging its input (all-gather -> GEMM), so the NVLink latency hides behind that
+        kernel's launch.  The last down_proj reduces in place (its consumer may be another stage)."""
+        from ..parallel.tensor_parallel import linear_allreduce, linear_gather
+
+        c, pdl, tp = self.cfg, self.pdl, self.tp
+        pending = None      # (residual buffer, bias) of a pushed-but-not-yet-reduced linear
+        n = len(self.layers)
+        for li, P in enumerate(self.layers):
+            qkv, attn, act, h2 = self.qkv[:T], self.attn[:T], self.act[:T], other[:T]
+            kw = dict(out=qkv, norm_mode=self.norm_mode, norm_w=P["ln1_w"], norm_b=P["ln1_b"], norm_eps=c.norm_eps,
+                      workspace=self.ws, pdl=pdl)
+            if pending is None:
+                G.linear(h, P["qkv"], **kw)
+            else:
+                linear_gather(h, P["qkv"], tp, residual=pending[0], bias=pending[1], **kw)
+            A.attn_decode(qkv, attn, self.kv_ptrs[li], self.pos, self.inv_freq, self.attn_ws, c.n_heads,
+                          c.n_kv_heads, c.head_dim, self.kv_capacity, self.scale, pdl=pdl)
+            linear_allreduce(attn, P["o"], tp, out=h2, workspace=self.ws, pdl=pdl, defer=True)
+            linear_gather(h2, P["mlp_in"], tp, residual=h, bias=P["o"].bias, out=act, epilogue=self.mlp_epi,
+                          norm_mode=self.norm_mode, norm_w=P["ln2_w"], norm_b=P["ln2_b"], norm_eps=c.norm_eps,
+                          workspace=self.ws, pdl=pdl)
+            if li + 1 < n:
+                linear_allreduce(act, P["down"], tp, out=h, workspace=self.ws, pdl=pdl, defer=True)
+                pending = (h2, P["down"].bias)
+            else:
+                linear_allreduce(act, P["down"], tp, out=h, residual=h2, workspace=self.ws, pdl=pdl)
+                pending = None
             self._count(5)
         return h
 

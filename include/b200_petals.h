@@ -114,8 +114,16 @@ typedef struct b200_tp_args {
     void* flags[8];
     int32_t* seq;
     int32_t* exit_counter;
+    int32_t mode;   /* 0: the producer waits and reduces (all-reduce in one kernel); 1: the producer only pushes
+                       its partial tiles and the next GEMM (b200_gemm_gather) waits for them and adds them up */
 } b200_tp_args;
 int b200_gemm_allreduce(const b200_gemm_args* args, const b200_tp_args* tp, void* stream);
+/* Consumer of a mode-1 producer ("all-gather -> GEMM"): every CTA first rebuilds
+ * x[t,:] = residual[t,:] + bias + sum over ranks of the pushed partial rows (rank order, bit-identical on
+ * all ranks), stores it to args->x, then runs b200_gemm on it.  The NVLink latency of the exchange hides
+ * behind the launch of this kernel instead of sitting at the producer's tail. */
+int b200_gemm_gather(const b200_gemm_args* args, const b200_tp_args* tp, const void* residual, int32_t ldr,
+                     const void* bias, void* stream);
 
 /* b200_gemm for callers that cannot allocate device memory (no counterpart in the reference, which
  * has no native code and lets torch allocate freely).  Same arguments and result as b200_gemm, but

@@ -21,10 +21,26 @@ for name, N, Kfull in (("o_proj", 4096, 4096), ("down", 4096, 11008)):
     out = torch.empty(1, N, device=dev, dtype=dt)
     def fused():
         for w in wts: linear_allreduce(x, w, tp, out=out, residual=res, workspace=ws)
+    gu = packing.pack_weight((torch.randn(256, N, device=dev) * 0.02).to(dt))   # a small consumer GEMM
+    out2 = torch.empty(1, 256, device=dev, dtype=dt); hbuf = torch.empty(1, N, device=dev, dtype=dt)
+    from petals_b200.parallel.tensor_parallel import linear_gather
+    def deferred():
+        for w in wts:
+            linear_allreduce(x, w, tp, out=out, workspace=ws, defer=True)
+            linear_gather(hbuf, gu, tp, residual=res, out=out2, workspace=ws)
+    def fused_plus_consumer():
+        for w in wts:
+            linear_allreduce(x, w, tp, out=hbuf, residual=res, workspace=ws)
+            gemm.linear(hbuf, gu, out=out2, workspace=ws)
+    def nccl_plus_consumer():
+        for w in wts:
+            gemm.linear(x, w, out=hbuf, workspace=ws); dist.all_reduce(hbuf); hbuf.add_(res)
+            gemm.linear(hbuf, gu, out=out2, workspace=ws)
     def nccl():
         for w in wts:
             gemm.linear(x, w, out=out, workspace=ws); dist.all_reduce(out); out.add_(res)
-    for label, fn in (("fused", fused), ("nccl", nccl)):
+    for label, fn in (("fused", fused), ("nccl", nccl), ("push+gather-gemm", deferred),
+                      ("fused+consumer-gemm", fused_plus_consumer), ("nccl+consumer-gemm", nccl_plus_consumer)):
         fn(); torch.cuda.synchronize(); dist.barrier()
         g = torch.cuda.CUDAGraph(); s = torch.cuda.Stream(); s.wait_stream(torch.cuda.current_stream())
         with torch.cuda.stream(s):

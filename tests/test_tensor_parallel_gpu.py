@@ -37,14 +37,15 @@ def _run(rank, world, port, q):
     dtype = torch.bfloat16
     res = {}
     ids = torch.randint(0, cfg.vocab, (40,), generator=torch.Generator().manual_seed(0)).to(dev)
-    for mode in ("single", "fused", "nccl"):
+    for mode in ("single", "fused", "fused-nodefer", "nccl"):
         w = load_span("tiny-llama-gqa", cfg, 0, cfg.n_layers, need_embed=True, need_head=True, dtype=dtype, device=dev, seed=9)
         if mode == "single":
             span = NativeSpan(cfg, w, dev, dtype, kv_capacity=256, max_batch=2, max_chunk=64, use_graphs=False)
             lc = cfg
         else:
-            span = make_tp_span(cfg, w, dev, dtype, dist.group.WORLD, mode=mode, kv_capacity=256, max_batch=2,
-                                max_chunk=64, use_graphs=(mode == "fused"))
+            span = make_tp_span(cfg, w, dev, dtype, dist.group.WORLD, mode=mode.split("-")[0], kv_capacity=256,
+                                max_batch=2, max_chunk=64, use_graphs=(mode == "fused"))
+            span.tp_defer = mode == "fused"
             lc = span.cfg
         kv = KVCacheManager(cfg.n_layers, lc.n_kv_heads, lc.head_dim, dtype, dev).allocate("s", 256)
         logits, tok = span.prefill(kv, ids=ids)
@@ -84,3 +85,4 @@ def test_tp2_fused_allreduce_matches_single_gpu_and_nccl():
     assert (res["fused"] - res["single"]).abs().max().item() < 0.05 * scale
     assert (res["nccl"] - res["single"]).abs().max().item() < 0.05 * scale
     assert (res["fused"] - res["nccl"]).abs().max().item() < 0.02 * scale
+    assert torch.equal(res["fused"], res["fused-nodefer"]), "deferred and in-producer reductions must agree bit for bit"
