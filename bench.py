@@ -43,6 +43,8 @@ def parse_args():
     ap.add_argument("--dtype", default="fp16", choices=["fp16", "bf16"])
     ap.add_argument("--prompt-len", type=int, default=128)
     ap.add_argument("--sessions", type=int, default=0, help="in-flight sessions (default: one per stage)")
+    ap.add_argument("--tp", type=int, default=1, help="tensor-parallel width of every stage (gpus = stages * tp)")
+    ap.add_argument("--tp-mode", default="fused", choices=["fused", "nccl"])
     ap.add_argument("--group", type=int, default=1,
                     help="sessions per micro-batch travelling through the chain together (serving-throughput mode)")
     ap.add_argument("--weights", default="native", choices=["native", "fp8"],
@@ -119,12 +121,14 @@ def run_b200(args):
     from petals_b200.models.config import resolve_config
 
     cfg = resolve_config(args.model)
-    S = args.sessions or world
+    stages = world // args.tp
+    S = args.sessions or stages
     K, W, L = args.steps, args.warmup, args.prompt_len
     cap = L + 2 * (K + W) + 16
     cap = (cap + 255) // 256 * 256
-    eng = PipelineEngine(args.model, even_splits(cfg.n_layers, world), dtype, dev, kv_capacity=cap,
-                         max_sessions=max(S, 1), max_chunk=256, seed=0, weight_format=args.weights)
+    eng = PipelineEngine(args.model, even_splits(cfg.n_layers, stages), dtype, dev, kv_capacity=cap,
+                         max_sessions=max(S, 1), max_chunk=256, seed=0, weight_format=args.weights, tp=args.tp,
+                         tp_mode=args.tp_mode)
     sess = eng.open_sessions(S)
     g = torch.Generator().manual_seed(1234)
     prompts = [torch.randint(0, cfg.vocab, (L,), generator=g) for _ in range(S)]
@@ -215,7 +219,7 @@ def run_b200(args):
             "vs_baseline": None, "dtype": args.dtype if args.weights == "native" else f"{args.dtype} activations, fp8(e4m3) weights (opt-in)",
             "data": "synthetic prompts, random-init weights",
             "impl": "b200",
-            "config": {"model": args.model, "global_batch": S, "seq_len": L, "parallelism": f"pp{world}",
+            "config": {"model": args.model, "global_batch": S, "seq_len": L, "parallelism": f"pp{stages}" + (f"tp{args.tp}({args.tp_mode})" if args.tp > 1 else ""),
                        "sessions_in_flight": S, "batch_per_session": 1, "sessions_per_micro_batch": args.group,
                        "l2": "every step streams all weights (13.5 GB >> 126 MB L2); no flush needed",
                        "p50_token_latency_ms": round(statistics.median(lat) * 1e3, 4),

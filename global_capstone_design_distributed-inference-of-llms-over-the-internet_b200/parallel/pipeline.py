@@ -39,13 +39,29 @@ class PipelineEngine:
     def __init__(self, model: str, splits: Sequence[int] = (), dtype: torch.dtype = torch.float16, device=None, *,
                  backend: Optional[str] = None, kv_capacity: int = 2048, max_sessions: int = 8, max_chunk: int = 512,
                  seed: int = 0, use_graphs: bool = True, cfg: Optional[ModelConfig] = None,
-                 weight_format: str = "native"):
+                 weight_format: str = "native", tp: int = 1, tp_mode: str = "fused"):
         self.cfg = cfg or resolve_config(model)
-        self.rank = dist.get_rank() if _dist_ready() else 0
-        self.world = dist.get_world_size() if _dist_ready() else 1
+        grank = dist.get_rank() if _dist_ready() else 0
+        gworld = dist.get_world_size() if _dist_ready() else 1
+        # Tensor-parallel spans: `tp` consecutive global ranks form one pipeline stage.  Every rank of a
+        # stage holds the same (replicated) hidden state, so stage s rank i simply talks to stage s+1 rank i.
+        self.tp = max(1, int(tp))
+        if gworld % self.tp:
+            raise ValueError(f"world size {gworld} is not a multiple of tp={self.tp}")
+        self.tp_rank = grank % self.tp
+        self.rank = grank // self.tp            # pipeline stage index
+        self.world = gworld // self.tp          # number of pipeline stages
+        self.grank, self.gworld = grank, gworld
+        self.tp_group = None
+        if self.tp > 1:
+            for st in range(self.world):       # every rank must create every group
+                g = dist.new_group(list(range(st * self.tp, (st + 1) * self.tp)))
+                if st == self.rank:
+                    self.tp_group = g
         bounds = [0] + [int(s) for s in splits] + [self.cfg.n_layers]
         if len(bounds) - 1 != self.world:
-            raise ValueError(f"{len(splits)} split points make {len(bounds) - 1} stages but world size is {self.world}")
+            raise ValueError(f"{len(splits)} split points make {len(bounds) - 1} stages but there are {self.world} "
+                             f"pipeline stages (world {gworld} / tp {self.tp})")
         if any(b >= e for b, e in zip(bounds, bounds[1:])):
             raise ValueError(f"empty stage in splits {list(splits)} for a {self.cfg.n_layers}-layer model")
         self.bounds = bounds
@@ -60,7 +76,13 @@ class PipelineEngine:
         self.max_sessions = max_sessions
         w = load_span(model, self.cfg, self.start, self.end, need_embed=self.is_first, need_head=self.is_last,
                       dtype=dtype, device=self.device, seed=seed)
-        if self.backend == "native":
+        if self.backend == "native" and self.tp > 1:
+            from .tensor_parallel import make_tp_span
+
+            self.span = make_tp_span(self.cfg, w, self.device, dtype, self.tp_group, mode=tp_mode,
+                                     kv_capacity=kv_capacity, max_batch=max_sessions, max_chunk=max_chunk,
+                                     use_graphs=use_graphs)
+        elif self.backend == "native":
             from ..runtime.native_span import NativeSpan
 
             self.span = NativeSpan(self.cfg, w, self.device, dtype, kv_capacity=kv_capacity,
@@ -70,8 +92,10 @@ class PipelineEngine:
             from ..models.torch_ref import TorchSpan
 
             self.span = TorchSpan(self.cfg, w, self.device, dtype)
-        self.kv = KVCacheManager(self.end - self.start, self.cfg.n_kv_heads, self.cfg.head_dim, dtype, self.device,
-                                 default_max_length=kv_capacity)
+        if self.tp > 1 and self.backend != "native":
+            raise ValueError("tensor-parallel spans need the native (CUDA) backend")
+        self.kv = KVCacheManager(self.end - self.start, self.cfg.n_kv_heads // self.tp, self.cfg.head_dim, dtype,
+                                 self.device, default_max_length=kv_capacity)
         self.sessions: List[SessionKV] = []
         H = self.cfg.hidden
         # per-slot staging buffers: [0] = received from the previous stage, [1] = sent to the next
@@ -102,11 +126,15 @@ class PipelineEngine:
         self.sessions = []
 
     # ------------------------------------------------------------------ p2p helpers
+    def _g(self, stage: int) -> int:
+        """Global rank of this rank's counterpart in pipeline stage ``stage``."""
+        return stage * self.tp + self.tp_rank
+
     def _send(self, t: torch.Tensor, dst: int, group=None) -> None:
-        dist.send(t, dst, group=group)
+        dist.send(t, self._g(dst), group=group)
 
     def _recv(self, t: torch.Tensor, src: int, group=None) -> None:
-        dist.recv(t, src, group=group)
+        dist.recv(t, self._g(src), group=group)
 
     @staticmethod
     def _wait(work) -> None:
@@ -165,7 +193,7 @@ class PipelineEngine:
         recv_next = None
         if not self.is_first:
             buf = torch.empty(chunks[0][1], H, dtype=self.dtype, device=self.device)
-            recv_next = (buf, dist.irecv(buf, self.rank - 1))
+            recv_next = (buf, dist.irecv(buf, self._g(self.rank - 1)))
         for ci, (c0, n) in enumerate(chunks):
             h = None
             if not self.is_first:
@@ -173,11 +201,11 @@ class PipelineEngine:
                 work.wait()
                 if ci + 1 < len(chunks):   # post the next receive before computing this chunk
                     nb = torch.empty(chunks[ci + 1][1], H, dtype=self.dtype, device=self.device)
-                    recv_next = (nb, dist.irecv(nb, self.rank - 1))
+                    recv_next = (nb, dist.irecv(nb, self._g(self.rank - 1)))
             out = self._stage_prefill(kv, ids_dev[c0:c0 + n] if self.is_first else None, h)
             if not self.is_last:
                 o = out.contiguous()
-                pending.append((o, dist.isend(o, self.rank + 1)))
+                pending.append((o, dist.isend(o, self._g(self.rank + 1))))
         for _, w in pending:
             w.wait()
         if self.is_last:
@@ -226,19 +254,19 @@ class PipelineEngine:
                     out = self._stage_decode(kv, self._tok[j0:j1], None)
                     self._wait(self._send_work[slot])
                     self._hid[1, j0:j1].copy_(out[: j1 - j0])
-                    self._send_work[slot] = dist.isend(self._hid[1, j0:j1], 1)
-                    self._tok_work[slot] = dist.irecv(self._tok[j0:j1], last, group=self.tok_group)
+                    self._send_work[slot] = dist.isend(self._hid[1, j0:j1], self._g(1))
+                    self._tok_work[slot] = dist.irecv(self._tok[j0:j1], self._g(last), group=self.tok_group)
                 else:
                     h = self._hid[0, j0:j1]
-                    dist.irecv(h, self.rank - 1).wait()
+                    dist.irecv(h, self._g(self.rank - 1)).wait()
                     out = self._stage_decode(kv, None, h)
                     self._wait(self._send_work[slot])
                     if self.is_last:
                         self._tok_send[j0:j1].copy_(out[1].reshape(-1)[: j1 - j0])
-                        self._send_work[slot] = dist.isend(self._tok_send[j0:j1], 0, group=self.tok_group)
+                        self._send_work[slot] = dist.isend(self._tok_send[j0:j1], self._g(0), group=self.tok_group)
                     else:
                         self._hid[1, j0:j1].copy_(out[: j1 - j0])
-                        self._send_work[slot] = dist.isend(self._hid[1, j0:j1], self.rank + 1)
+                        self._send_work[slot] = dist.isend(self._hid[1, j0:j1], self._g(self.rank + 1))
             if self.is_first and (to_host or tokens is not None):
                 for j in range(S):
                     self._wait(self._tok_work[j])
@@ -281,19 +309,19 @@ class PipelineEngine:
                 o = self._stage_decode(kv, self._tok[j:j + 1], None)
                 self._wait(self._send_work[j])
                 self._hid[1, j:j + 1].copy_(o[:1])
-                self._send_work[j] = dist.isend(self._hid[1, j:j + 1], 1)
-                self._tok_work[j] = dist.irecv(self._tok[j:j + 1], last, group=self.tok_group)
+                self._send_work[j] = dist.isend(self._hid[1, j:j + 1], self._g(1))
+                self._tok_work[j] = dist.irecv(self._tok[j:j + 1], self._g(last), group=self.tok_group)
             else:
                 h = self._hid[0, j:j + 1]
-                dist.irecv(h, self.rank - 1).wait()
+                dist.irecv(h, self._g(self.rank - 1)).wait()
                 o = self._stage_decode(kv, None, h)
                 self._wait(self._send_work[j])
                 if self.is_last:
                     self._tok_send[j:j + 1].copy_(o[1].reshape(-1)[:1])
-                    self._send_work[j] = dist.isend(self._tok_send[j:j + 1], 0, group=self.tok_group)
+                    self._send_work[j] = dist.isend(self._tok_send[j:j + 1], self._g(0), group=self.tok_group)
                 else:
                     self._hid[1, j:j + 1].copy_(o[:1])
-                    self._send_work[j] = dist.isend(self._hid[1, j:j + 1], self.rank + 1)
+                    self._send_work[j] = dist.isend(self._hid[1, j:j + 1], self._g(self.rank + 1))
         self._streaming_live = True
         return out if (self.is_first and have_prev) else None
 

@@ -167,6 +167,8 @@ def make_tp_span(cfg: ModelConfig, weights: Dict[str, object], device, dtype, gr
     w = dict(weights)
     w["layers"] = [shard_layer(cfg, L, rank, world) for L in weights["layers"]]  # type: ignore[index]
     local_cfg = shard_config(cfg, world)
+    if mode == "nccl":
+        span_kw["use_graphs"] = False   # NCCL collectives are issued eagerly between the kernels (baseline path)
     span = NativeSpan(local_cfg, w, device, dtype, **span_kw)
     span.full_hidden = cfg.hidden
     span.tp_mode = mode
