@@ -350,6 +350,39 @@ def run_stage_server(args, device, splits):
     return run_stage_server_fixed(args, device, splits)
 
 
+# --------------------------------------------------------------------------- in-box NCCL pipeline
+def run_inbox(args, device, splits):
+    """All stages inside one NVSwitch box: one process per GPU (torchrun), NCCL p2p chain.
+
+    ``--splits a,b`` with 3 x tp processes puts blocks [0,a) on stage 0, [a,b) on stage 1, [b,L) on stage 2
+    (the first stage also embeds, the last one samples); rank 0 prints what the reference client prints."""
+    import torch.distributed as dist
+
+    from petals_b200.parallel.pipeline import PipelineEngine
+
+    if not dist.is_initialized():
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        backend = "nccl" if device.type == "cuda" else "gloo"
+        kw = {"device_id": device} if backend == "nccl" else {}
+        dist.init_process_group(backend, **kw)
+    cfg = resolve_config(args.model)
+    tok = load_tokenizer(args.model, cfg)
+    ids = torch.tensor(tok.encode(args.prompt), dtype=torch.long)
+    cap = max(getattr(args, "kv_capacity", None) or 0, ((ids.numel() + args.max_new_tokens + 255) // 256) * 256)
+    eng = PipelineEngine(args.model, splits, args.dtype, device, kv_capacity=cap, max_sessions=1,
+                         seed=getattr(args, "seed", 0), tp=args.tp)
+    res = eng.generate([ids], args.max_new_tokens, eos_token_id=tok.eos_token_id)
+    if dist.get_rank() == 0:
+        outs, stats = res
+        print(f"\n{'=' * 80}\nPROMPT: {args.prompt}\nGENERATED: {tok.decode(outs[0])}\n{'=' * 80}\n")
+        logger.info("Decode completed in %.3fs", stats["decode_s"])
+        logger.info("Total time: %.3fs", stats["total_s"])
+        logger.info("TTFT (Time to First Token): %.3fs", stats["ttft_s"])
+        logger.info("Decode throughput: %.1f tok/s", stats["decode_tok_per_s"])
+    dist.barrier()
+    return res
+
+
 # --------------------------------------------------------------------------- CLI
 def build_parser() -> argparse.ArgumentParser:
     p = argparse.ArgumentParser(description="Mini Petals on B200: distributed pipeline inference")
@@ -382,6 +415,10 @@ def build_parser() -> argparse.ArgumentParser:
     p.add_argument("--seed", type=int, default=0, help="seed of the random-init weights when no checkpoint is local")
     p.add_argument("--kv_capacity", type=int, default=None, help="per-session KV capacity in tokens")
     p.add_argument("--push", action="store_true", help="servers forward activations to the next hop themselves")
+    p.add_argument("--inbox", action="store_true",
+                   help="in-box mode: launch with torchrun (one process per GPU); stages hand hidden states over "
+                        "NCCL p2p instead of TCP RPC; --splits gives the stage boundaries, --stage is ignored")
+    p.add_argument("--tp", type=int, default=1, help="--inbox: tensor-parallel width of every stage")
     return p
 
 
@@ -399,6 +436,8 @@ def main(argv=None):
         logger.info("CPU device: computing in fp32")
         args.dtype = torch.float32
     splits = parse_splits(args.splits)
+    if args.inbox:
+        return run_inbox(args, device, splits)
     if args.stage == 0:
         run_rank0(args, device, splits)
     else:
