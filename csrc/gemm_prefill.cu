@@ -207,7 +207,9 @@ extern "C" int b200_gemm_prefill(const b200_gemm_args* a, void* stream_) {
     if (a->dual && a->epilogue != B200_EPI_SWIGLU) return fail(B200_EINVAL, "b200_gemm_prefill: dual weights need SwiGLU");
     EncodeTiledFn enc = encode_tiled_fn();
     if (!enc) return fail(B200_ECUDA, "b200_gemm_prefill: cuTensorMapEncodeTiled is not available from the driver");
-    const int bn = a->dual ? 128 : 256;
+    // 128 x 256 tiles (128 x 128 x 2 matrices for SwiGLU); inputs of at most 128 tokens use the 128-wide
+    // tile so half of every MMA is not spent on zero-filled rows
+    const int bn = (a->dual || a->T <= 128) ? 128 : 256;
     GemmParams p;
     memset(&p, 0, sizeof(p));
     p.w = static_cast<const uint8_t*>(a->w_packed);
@@ -237,6 +239,7 @@ extern "C" int b200_gemm_prefill(const b200_gemm_args* a, void* stream_) {
     if (grid > sm_count_cached()) grid = sm_count_cached();
     if (grid > units) grid = units;
     cudaStream_t stream = static_cast<cudaStream_t>(stream_);
-    return a->dual ? launch_prefill<128, 1>(p, tmap, grid, a->pdl != 0, stream)
-                   : launch_prefill<256, 0>(p, tmap, grid, a->pdl != 0, stream);
+    if (a->dual) return launch_prefill<128, 1>(p, tmap, grid, a->pdl != 0, stream);
+    if (bn == 128) return launch_prefill<128, 0>(p, tmap, grid, a->pdl != 0, stream);
+    return launch_prefill<256, 0>(p, tmap, grid, a->pdl != 0, stream);
 }
