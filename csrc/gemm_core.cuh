@@ -214,6 +214,60 @@ __device__ __forceinline__ void rms_stats_128(const GemmParams& p, int T, int e,
     named_bar_sync(1, 128);
 }
 
+// Coalesced variant for tile-filling inputs: the warp's 32 rows x 16 token columns go through a 2 KiB
+// shared-memory transpose so that every global access is a 16-byte vector along n (one 64-byte segment per
+// token row per warp) instead of 2-byte accesses 2*ld bytes apart.  Same arithmetic as above.
+// Requirements (checked by the caller): 16-bit output, N, ldo, ldr multiples of 8.
+template <int BN, int DUAL>
+__device__ __forceinline__ void epilogue_store_chunk_vec(const GemmParams& p, int n_tile, int t_tile, int lane, int lg,
+                                                         int chunk, const float (&vg)[16], const float (&vu)[16],
+                                                         float* warp_smem /* [16][32] */) {
+    const int n_row = n_tile * kTileM + lg * 32 + lane;
+    const float b = (p.bias && n_row < p.N) ? h16_to_float(p.bias[n_row], p.is_bf16) : 0.0f;
+#pragma unroll
+    for (int j = 0; j < 16; ++j) {
+        float v = vg[j] + b;
+        if (DUAL) {
+            const float g = round16(v, p.is_bf16);
+            const float u = round16(vu[j], p.is_bf16);
+            const float s = round16(g / (1.0f + __expf(-g)), p.is_bf16);
+            v = s * u;
+        } else if (p.epilogue == B200_EPI_GELU_TANH) {
+            v = gelu_tanh(round16(v, p.is_bf16));
+        }
+        warp_smem[j * 32 + lane] = v;
+    }
+    __syncwarp();
+    const int q = lane & 3;                               // 8-wide n segment inside the warp's 32 rows
+    const int n0 = n_tile * kTileM + lg * 32 + q * 8;
+#pragma unroll
+    for (int i = 0; i < 2; ++i) {
+        const int j = (lane >> 2) + 8 * i;                 // token column inside the chunk
+        const int t = t_tile * BN + chunk * 16 + j;
+        if (t < p.T && n0 < p.N) {
+            const float4 lo = *reinterpret_cast<const float4*>(warp_smem + j * 32 + q * 8);
+            const float4 hi = *reinterpret_cast<const float4*>(warp_smem + j * 32 + q * 8 + 4);
+            float f[8] = {lo.x, lo.y, lo.z, lo.w, hi.x, hi.y, hi.z, hi.w};
+            if (p.residual) {
+                const uint4 r4 = ld_cg_v4(p.residual + (size_t)t * p.ldr + n0);
+                const uint32_t rw[4] = {r4.x, r4.y, r4.z, r4.w};
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    f[2 * k] = round16(f[2 * k], p.is_bf16) + h16_to_float((uint16_t)(rw[k] & 0xffff), p.is_bf16);
+                    f[2 * k + 1] = round16(f[2 * k + 1], p.is_bf16) + h16_to_float((uint16_t)(rw[k] >> 16), p.is_bf16);
+                }
+            }
+            uint32_t w[4];
+#pragma unroll
+            for (int k = 0; k < 4; ++k)
+                w[k] = (uint32_t)float_to_h16(f[2 * k], p.is_bf16) | ((uint32_t)float_to_h16(f[2 * k + 1], p.is_bf16) << 16);
+            *reinterpret_cast<uint4*>(reinterpret_cast<uint16_t*>(p.out) + (size_t)t * p.ldo + n0) =
+                make_uint4(w[0], w[1], w[2], w[3]);
+        }
+    }
+    __syncwarp();
+}
+
 // fp8 activations: per-token quantisation statistics in one pass over the row.
 //   qmul[t]  = 448 / max|x*g|                 (multiplier applied before the e4m3 conversion)
 //   scale[t] = max|x*g| / 448 * (RMSNorm ? 1/rms : 1)   (applied to the accumulator in the epilogue)

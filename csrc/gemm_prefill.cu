@@ -27,7 +27,7 @@ struct PrefillCfg {
     static constexpr int kStages = (200 * 1024) / kStage;    // 4 for (256, single) and (128, dual)
     static constexpr int kAccCols = BN * kAPer;              // TMEM columns of one accumulator buffer
     static constexpr int kTmemCols = 2 * kAccCols <= 256 ? 256 : 512;
-    static constexpr size_t kSmemBytes = (size_t)kStages * kStage + 1024 + 1024;
+    static constexpr size_t kSmemBytes = (size_t)kStages * kStage + 1024 + 1024 + 4 * 2048 /*epilogue transposes*/;
     static_assert(2 * kAccCols <= 512, "two accumulator buffers must fit TMEM");
 };
 
@@ -52,6 +52,7 @@ gemm_prefill_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap
     uint64_t* acc_full = empty + S;     // [2]
     uint64_t* acc_empty = acc_full + 2; // [2]
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + 2);
+    float* epi_smem = reinterpret_cast<float*>(smem + (size_t)S * Cfg::kStage + 1024);   // [4 warps][16][32]
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     if (threadIdx.x == 0) {
@@ -126,6 +127,8 @@ gemm_prefill_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap
         // ------------------------------------------------------------ epilogue warps
         const int lg = warp & 3;
         const int row = lg * 32 + lane;
+        const bool vec_ok = !p.out_fp32 && (p.N % 8 == 0) && (p.ldo % 8 == 0) && (!p.residual || p.ldr % 8 == 0);
+        float* my_smem = epi_smem + (warp - 2) * 512;
         uint32_t it = 0;
         for (int u = blockIdx.x; u < units; u += gridDim.x, ++it) {
             const int n_tile = u / p.t_tiles, t_tile = u - n_tile * p.t_tiles;
@@ -146,7 +149,8 @@ gemm_prefill_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap
                     vg[j] = __uint_as_float(rg[j]);
                     vu[j] = DUAL ? __uint_as_float(ru[j]) : 0.f;
                 }
-                epilogue_store_chunk<BN, DUAL>(p, n_tile, t_tile, row, c, vg, vu, nullptr);
+                if (vec_ok) epilogue_store_chunk_vec<BN, DUAL>(p, n_tile, t_tile, lane, lg, c, vg, vu, my_smem);
+                else epilogue_store_chunk<BN, DUAL>(p, n_tile, t_tile, row, c, vg, vu, nullptr);
             }
             tc_fence_before();
             __syncwarp();
