@@ -8,8 +8,22 @@
 //     O = O * corr + O_blk in registers
 // The T x S score matrix never exists in memory (the reference materialises [nh, T, S] in fp32:
 // petals/llama/block.py:134-141) and the causal mask is applied (the reference's live path has none).
-// v1 is not software-pipelined: loads, MMAs and softmax of a block run back to back.
+//
+// Two kernels live here:
+//   attn_prefill_tc_kernel   (v1)  one 128-query tile per CTA, loads / MMAs / softmax back to back
+//   attn_prefill_tc2_kernel  (v2)  the production path: warp-specialised and software-pipelined
+//       warp 8      TMA producer: Q tiles once, then K(0) V(0) K(1) V(1) ... through a 3-stage ring
+//                   (tensor maps bounded at the valid cache length: rows past it arrive as zeros)
+//       warp 9      MMA issuer: S_w(j+1) = Q_w K(j+1)^T is issued BEFORE O_w += P_w(j) V(j), so the tensor
+//                   core computes the next scores while the softmax warps work on the current ones
+//       warps 0-3   softmax group A (query tile 0), warps 4-7 softmax group B (query tile 1), registers moved
+//                   to them from the two worker warps' group with setmaxnreg: one thread per
+//                   query row reads its 128 scores from TMEM in one go, frees the S buffer at once, writes P
+//                   to shared memory; O accumulates in TMEM and is rescaled only when the running maximum
+//                   grew by more than 2^8 (exactness is restored by the final 1/l)
+//   K/V tiles are loaded once per 256 queries; CTAs are ordered heaviest-first (causal work is triangular).
 #include "attn_core.cuh"
+#include "tma_host.h"
 
 namespace b200 {
 
@@ -222,6 +236,316 @@ __global__ void __launch_bounds__(kPfThreads, 1) attn_prefill_tc_kernel(const At
     if (warp == 1) tmem_dealloc<256>(tmem_base);
 }
 
+
+// ---------------------------------------------------------------------------------------------- v2
+constexpr int kPf2Threads = 384;   // warps 0-3: softmax group A, 4-7: group B, 8: TMA, 9: MMA, 10-11: idle
+constexpr int kPf2Ring = 3;
+
+struct AttnPrefillTc2Params {
+    uint16_t* __restrict__ out;
+    int T, n_heads, n_kv, ldo, pos0, tiles_per_cta;
+    float scale_log2e;
+};
+
+__device__ __forceinline__ void tma_load_2d_attn(uint32_t smem_dst, const CUtensorMap* tmap, int c0, int c1, uint64_t* bar) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];\n" ::
+            "r"(smem_dst),
+        "l"(tmap), "r"(c0), "r"(c1), "r"(smem_u32(bar))
+        : "memory");
+}
+__device__ __forceinline__ void tma_load_3d_attn(uint32_t smem_dst, const CUtensorMap* tmap, int c0, int c1, int c2,
+                                                 uint64_t* bar) {
+    asm volatile(
+        "cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];\n" ::
+            "r"(smem_dst),
+        "l"(tmap), "r"(c0), "r"(c1), "r"(c2), "r"(smem_u32(bar))
+        : "memory");
+}
+
+struct RingPos {
+    int stage;
+    uint32_t par;
+    __device__ __forceinline__ void advance(int by) {
+        stage += by;
+        if (stage >= kPf2Ring) { stage -= kPf2Ring; par ^= 1; }
+    }
+};
+
+template <bool BF16>
+__device__ __forceinline__ uint32_t pack2(float a, float b) {
+    if (BF16) {
+        const __nv_bfloat162 v = __floats2bfloat162_rn(a, b);
+        return *reinterpret_cast<const uint32_t*>(&v);
+    }
+    const __half2 v = __floats2half2_rn(a, b);
+    return *reinterpret_cast<const uint32_t*>(&v);
+}
+
+template <int D, bool BF16>
+__global__ void __launch_bounds__(kPf2Threads, 1)
+attn_prefill_tc2_kernel(const AttnPrefillTc2Params p, const __grid_constant__ CUtensorMap tmap_q,
+                        const __grid_constant__ CUtensorMap tmap_k, const __grid_constant__ CUtensorMap tmap_v) {
+    constexpr int HALVES = D / 64;
+    constexpr int TILE = 128 * 128 * HALVES;       // bytes of a [128 x D] 16-bit tile
+    constexpr int P_BYTES = 128 * 128 * 2;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint8_t* s_q = smem;                           // [2][TILE]
+    uint8_t* s_ring = s_q + 2 * TILE;              // [3][TILE]
+    uint8_t* s_p = s_ring + kPf2Ring * TILE;       // [2][P_BYTES]
+    uint64_t* bars = reinterpret_cast<uint64_t*>(s_p + 2 * P_BYTES);
+    uint64_t* q_full = bars;                       // [1]
+    uint64_t* ring_full = bars + 1;                // [3]
+    uint64_t* ring_empty = bars + 4;               // [3]
+    uint64_t* s_full = bars + 7;                   // [2] scores of tile w are in TMEM
+    uint64_t* s_free = bars + 9;                   // [2] 128 arrivals: scores are in registers
+    uint64_t* p_ready = bars + 11;                 // [2] 128 arrivals: P_w is in shared memory, O_w is rescaled
+    uint64_t* o_full = bars + 13;                  // [2] O_w += P_w V has completed
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 15);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int h = blockIdx.x;
+    const int qb = (int)gridDim.y - 1 - (int)blockIdx.y;      // heaviest query blocks are scheduled first
+    const int q0 = qb * 128 * p.tiles_per_cta;
+    const int g = h / (p.n_heads / p.n_kv);
+
+    if (threadIdx.x == 0) {
+        mbar_init(q_full, 1);
+        for (int i = 0; i < kPf2Ring; ++i) { mbar_init(&ring_full[i], 1); mbar_init(&ring_empty[i], 1); }
+        for (int i = 0; i < 2; ++i) {
+            mbar_init(&s_full[i], 1); mbar_init(&s_free[i], 128); mbar_init(&p_ready[i], 128); mbar_init(&o_full[i], 1);
+        }
+        fence_mbar_init();
+        asm volatile("prefetch.tensormap [%0];\n" ::"l"(&tmap_q) : "memory");
+        asm volatile("prefetch.tensormap [%0];\n" ::"l"(&tmap_k) : "memory");
+        asm volatile("prefetch.tensormap [%0];\n" ::"l"(&tmap_v) : "memory");
+    }
+    if (warp == 9) tmem_alloc<512>(tmem_slot);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    pdl_wait_prior_grid();
+    pdl_launch_dependents();
+
+    // key blocks per query tile (causal): tile w sees keys [0, pos0 + last query of the tile]
+    int n_blk[2];
+#pragma unroll
+    for (int w = 0; w < 2; ++w) {
+        const int first = q0 + w * 128;
+        n_blk[w] = (w < p.tiles_per_cta && first < p.T) ? (p.pos0 + min(p.T, first + 128) + 127) / 128 : 0;
+    }
+    const int n_max = max(n_blk[0], n_blk[1]);
+
+    if (warp >= 8) {
+      // the whole worker warpgroup gives registers up with ONE instruction (setmaxnreg is warpgroup-aligned)
+      asm volatile("setmaxnreg.dec.sync.aligned.u32 72;\n");
+      if (warp == 8) {
+        // ------------------------------------------------------------ TMA producer
+        if (elect_one()) {
+            const int nq = n_blk[1] > 0 ? 2 : 1;
+            mbar_arrive_expect_tx(q_full, (uint32_t)(nq * TILE));
+            for (int w = 0; w < nq; ++w)
+                for (int hh = 0; hh < HALVES; ++hh)
+                    tma_load_2d_attn(smem_u32(s_q + w * TILE + hh * (128 * 128)), &tmap_q, h * D + hh * 64, q0 + w * 128, q_full);
+            RingPos r{0, 0};
+            for (int j = 0; j < n_max; ++j) {
+#pragma unroll
+                for (int kv = 0; kv < 2; ++kv) {
+                    mbar_wait(&ring_empty[r.stage], r.par ^ 1);
+                    mbar_arrive_expect_tx(&ring_full[r.stage], (uint32_t)TILE);
+                    for (int hh = 0; hh < HALVES; ++hh)
+                        tma_load_3d_attn(smem_u32(s_ring + r.stage * TILE + hh * (128 * 128)), kv == 0 ? &tmap_k : &tmap_v,
+                                         hh * 64, j * 128, g, &ring_full[r.stage]);
+                    r.advance(1);
+                }
+            }
+        }
+        __syncwarp();
+      } else if (warp == 9) {
+        // ------------------------------------------------------------ MMA issuer
+        const uint32_t idesc_s = umma_idesc(128, 128, BF16, BF16, 0, 0);
+        const uint32_t idesc_o = umma_idesc(128, D, BF16, BF16, 0, 1);   // B = V is MN-major
+        const uint32_t q_addr = smem_u32(s_q), ring_addr = smem_u32(s_ring), p_addr = smem_u32(s_p);
+        RingPos rk{0, 0}, rv{1, 0};   // K(j) is ring item 2j, V(j) is item 2j + 1
+        auto issue_s = [&](int w, int j, const RingPos& r) {
+            mbar_wait(&ring_full[r.stage], r.par);
+            if (j > 0) mbar_wait(&s_free[w], (uint32_t)(j - 1) & 1);
+            tc_fence_after();
+            if (elect_one()) {
+#pragma unroll
+                for (int ks = 0; ks < D / 16; ++ks) {
+                    const uint32_t off = (ks / 4) * (128 * 128) + (ks % 4) * 32;
+                    umma_f16(tmem_base + w * 128, umma_desc_kmajor_sw128(q_addr + w * TILE + off, 1024),
+                             umma_desc_kmajor_sw128(ring_addr + r.stage * TILE + off, 1024), idesc_s, ks > 0 ? 1u : 0u);
+                }
+                umma_commit(&s_full[w]);
+            }
+            __syncwarp();
+        };
+        auto issue_pv = [&](int w, int j, const RingPos& r) {
+            mbar_wait(&ring_full[r.stage], r.par);
+            mbar_wait(&p_ready[w], (uint32_t)j & 1);
+            tc_fence_after();
+            if (elect_one()) {
+#pragma unroll
+                for (int ks = 0; ks < 8; ++ks) {
+                    const uint32_t a_off = (ks / 4) * (128 * 128) + (ks % 4) * 32;   // P: K-major over keys
+                    const uint32_t b_off = ks * 2048;                                 // V: 16 key rows
+                    umma_f16(tmem_base + 256 + w * D, umma_desc_kmajor_sw128(p_addr + w * P_BYTES + a_off, 1024),
+                             umma_desc_mnmajor_sw128(ring_addr + r.stage * TILE + b_off, 128 * 128, 1024), idesc_o,
+                             (j > 0 || ks > 0) ? 1u : 0u);
+                }
+                umma_commit(&o_full[w]);
+            }
+            __syncwarp();
+        };
+        auto release = [&](const RingPos& r) {
+            if (elect_one()) umma_commit(&ring_empty[r.stage]);
+            __syncwarp();
+        };
+        mbar_wait(q_full, 0);
+        if (n_blk[0] > 0) issue_s(0, 0, rk);
+        if (n_blk[1] > 0) issue_s(1, 0, rk);
+        release(rk);
+        for (int j = 0; j < n_max; ++j) {
+            if (j + 1 < n_max) {
+                rk.advance(2);
+                if (j + 1 < n_blk[0]) issue_s(0, j + 1, rk);
+                if (j + 1 < n_blk[1]) issue_s(1, j + 1, rk);
+                release(rk);
+            }
+            if (j < n_blk[0]) issue_pv(0, j, rv);
+            if (j < n_blk[1]) issue_pv(1, j, rv);
+            release(rv);
+            rv.advance(2);
+        }
+      }
+    } else {
+        // ------------------------------------------------------------ softmax groups
+        asm volatile("setmaxnreg.inc.sync.aligned.u32 216;\n");
+        const int w = warp >> 2;                    // 0: query tile A, 1: query tile B
+        const int lg = warp & 3;                    // TMEM lane quarter this warp may touch
+        const int row = lg * 32 + lane;
+        const int t_row = q0 + w * 128 + row;
+        const int q_pos = p.pos0 + t_row;
+        const int nb = n_blk[w];
+        const uint32_t t_lane = (uint32_t)(lg * 32) << 16;
+        const uint32_t tmem_s = tmem_base + w * 128 + t_lane;
+        const uint32_t tmem_o = tmem_base + 256 + w * D + t_lane;
+        const uint32_t p_base = smem_u32(s_p + w * P_BYTES);
+        float m_used = -INFINITY, l_run = 0.f;
+        for (int j = 0; j < nb; ++j) {
+            const int k0 = j * 128;
+            mbar_wait(&s_full[w], (uint32_t)j & 1);
+            tc_fence_after();
+            float s[128];
+#pragma unroll
+            for (int c = 0; c < 8; ++c) {
+                uint32_t r[16];
+                tmem_ld16(tmem_s + c * 16, r);
+#pragma unroll
+                for (int i = 0; i < 16; ++i) s[c * 16 + i] = __uint_as_float(r[i]);
+            }
+            tmem_ld_wait();
+            tc_fence_before();
+            mbar_arrive(&s_free[w]);                // the next Q K^T may overwrite S now
+            if (k0 + 127 > p.pos0 + q0 + w * 128) { // the block crosses the diagonal of this tile
+                const int lim = q_pos - k0;
+#pragma unroll
+                for (int i = 0; i < 128; ++i) s[i] = (i <= lim) ? s[i] : -INFINITY;
+            }
+            float m_blk = s[0];
+#pragma unroll
+            for (int i = 1; i < 128; ++i) m_blk = fmaxf(m_blk, s[i]);
+            const float m_new = fmaxf(m_used, m_blk);
+            const bool need = (m_new - m_used) * p.scale_log2e > 8.0f;
+            const bool any = __any_sync(0xffffffffu, need);
+            if (j > 0) {                            // P_w and O_w are free once the previous P V has completed
+                mbar_wait(&o_full[w], (uint32_t)(j - 1) & 1);
+                tc_fence_after();
+            }
+            if (any) {
+                const float corr = need ? ex2_approx((m_used - m_new) * p.scale_log2e) : 1.0f;
+                if (need) { l_run *= corr; m_used = m_new; }
+                if (j > 0) {
+#pragma unroll
+                    for (int c = 0; c < D / 16; ++c) {
+                        uint32_t r[16];
+                        tmem_ld16(tmem_o + c * 16, r);
+                        tmem_ld_wait();
+#pragma unroll
+                        for (int i = 0; i < 16; ++i) r[i] = __float_as_uint(__uint_as_float(r[i]) * corr);
+                        tmem_st16(tmem_o + c * 16, r);
+                    }
+                    tmem_st_wait();
+                }
+            }
+            const float neg_m = -m_used * p.scale_log2e;
+            float l_blk = 0.f;
+#pragma unroll
+            for (int c = 0; c < 16; ++c) {          // 16 chunks of 8 keys = 16 bytes of P
+                uint32_t w4[4];
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    const float a = ex2_approx(fmaf(s[c * 8 + 2 * i], p.scale_log2e, neg_m));
+                    const float b = ex2_approx(fmaf(s[c * 8 + 2 * i + 1], p.scale_log2e, neg_m));
+                    l_blk += a + b;
+                    w4[i] = pack2<BF16>(a, b);
+                }
+                st_shared_v4(p_base + (c / 8) * (128 * 128) + row * 128 + (((c & 7) ^ (row & 7)) << 4),
+                             make_uint4(w4[0], w4[1], w4[2], w4[3]));
+            }
+            l_run += l_blk;
+            tc_fence_before();
+            fence_proxy_async_smem();
+            mbar_arrive(&p_ready[w]);
+        }
+        if (nb > 0) {
+            mbar_wait(&o_full[w], (uint32_t)(nb - 1) & 1);
+            tc_fence_after();
+            const float inv = 1.0f / l_run;
+            uint16_t* dst = p.out + (size_t)t_row * p.ldo + (size_t)h * D;
+#pragma unroll
+            for (int c = 0; c < D / 16; ++c) {
+                uint32_t r[16];
+                tmem_ld16(tmem_o + c * 16, r);
+                tmem_ld_wait();
+                if (t_row < p.T) {
+                    uint32_t w8[8];
+#pragma unroll
+                    for (int i = 0; i < 8; ++i)
+                        w8[i] = pack2<BF16>(__uint_as_float(r[2 * i]) * inv, __uint_as_float(r[2 * i + 1]) * inv);
+                    *reinterpret_cast<uint4*>(dst + c * 16) = make_uint4(w8[0], w8[1], w8[2], w8[3]);
+                    *reinterpret_cast<uint4*>(dst + c * 16 + 8) = make_uint4(w8[4], w8[5], w8[6], w8[7]);
+                }
+            }
+            tc_fence_before();
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 9) tmem_dealloc<512>(tmem_base);
+}
+
+template <int D, bool BF16>
+static int launch_tc2(const AttnPrefillTc2Params& p, const CUtensorMap& mq, const CUtensorMap& mk, const CUtensorMap& mv,
+                      dim3 grid, bool pdl, cudaStream_t stream) {
+    constexpr size_t smem = (size_t)(2 + kPf2Ring) * 128 * 128 * (D / 64) + 2 * 128 * 128 * 2 + 1024 + 256;
+    static_assert(smem <= 227 * 1024, "shared memory budget exceeded");
+    static thread_local int configured_dev = -1;
+    int dev = 0;
+    B200_CUDA_CHECK(cudaGetDevice(&dev));
+    if (configured_dev != dev) {
+        B200_CUDA_CHECK(cudaFuncSetAttribute(attn_prefill_tc2_kernel<D, BF16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        configured_dev = dev;
+    }
+    B200_CUDA_CHECK(launch(attn_prefill_tc2_kernel<D, BF16>, grid, dim3(kPf2Threads), smem, stream, pdl, p, mq, mk, mv));
+    return B200_OK;
+}
+
 }  // namespace b200
 
 using namespace b200;
@@ -233,6 +557,47 @@ extern "C" int b200_attn_prefill_tc(const void* q, void* out, const void* kcache
     if (head_dim != 128 && head_dim != 64) return fail(B200_EINVAL, "b200_attn_prefill_tc: unsupported head_dim=%d", head_dim);
     if (n_kv_heads <= 0 || n_heads % n_kv_heads) return fail(B200_EINVAL, "b200_attn_prefill_tc: bad head counts");
     if ((ldq % 8) || (ldo % 8)) return fail(B200_EINVAL, "b200_attn_prefill_tc: row strides must be multiples of 8 elements");
+    static const int version = [] { const char* e = getenv("B200_ATTN_PREFILL_V"); return e ? atoi(e) : 2; }();
+    if (version != 1 && (reinterpret_cast<uintptr_t>(q) & 15) == 0 && pos0 + T <= s_max) {
+        EncodeTiledFn enc = encode_tiled_fn();
+        if (!enc) return fail(B200_ECUDA, "b200_attn_prefill_tc: cuTensorMapEncodeTiled is not available from the driver");
+        const CUtensorMapDataType dt = (dtype == B200_BF16) ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16;
+        CUtensorMap mq, mk, mv;
+        const cuuint32_t estr[3] = {1, 1, 1};
+        {
+            const cuuint64_t dims[2] = {(cuuint64_t)n_heads * head_dim, (cuuint64_t)T};
+            const cuuint64_t strides[1] = {(cuuint64_t)ldq * 2};
+            const cuuint32_t box[2] = {64, 128};
+            const CUresult r = enc(&mq, dt, 2, const_cast<void*>(q), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                                   CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+            if (r != CUDA_SUCCESS) return fail(B200_ECUDA, "b200_attn_prefill_tc: tensor map for q failed (%d)", (int)r);
+        }
+        for (int i = 0; i < 2; ++i) {
+            // bounded at the valid length: rows the cache has not been written to arrive as zeros
+            const cuuint64_t dims[3] = {(cuuint64_t)head_dim, (cuuint64_t)(pos0 + T), (cuuint64_t)n_kv_heads};
+            const cuuint64_t strides[2] = {(cuuint64_t)head_dim * 2, (cuuint64_t)s_max * head_dim * 2};
+            const cuuint32_t box[3] = {64, 128, 1};
+            const CUresult r = enc(i == 0 ? &mk : &mv, dt, 3, const_cast<void*>(i == 0 ? kcache : vcache), dims, strides, box, estr,
+                                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+            if (r != CUDA_SUCCESS) return fail(B200_ECUDA, "b200_attn_prefill_tc: tensor map for k/v failed (%d)", (int)r);
+        }
+        static const int forced_tiles = [] { const char* e = getenv("B200_ATTN_PREFILL_TILES"); return e ? atoi(e) : 0; }();
+        AttnPrefillTc2Params p2;
+        p2.out = static_cast<uint16_t*>(out);
+        p2.T = T; p2.n_heads = n_heads; p2.n_kv = n_kv_heads; p2.ldo = ldo; p2.pos0 = pos0;
+        p2.scale_log2e = scale * 1.4426950408889634f;
+        // two query tiles per CTA share every K/V load; short prompts keep one tile per CTA to fill the SMs
+        const int pairs = (T + 255) / 256;
+        p2.tiles_per_cta = forced_tiles ? forced_tiles : ((pairs * n_heads * 4 >= sm_count_cached() * 3) ? 2 : 1);
+        const dim3 grid2((unsigned)n_heads, (unsigned)((T + 128 * p2.tiles_per_cta - 1) / (128 * p2.tiles_per_cta)));
+        cudaStream_t st = static_cast<cudaStream_t>(stream_);
+        if (head_dim == 128)
+            return dtype == B200_BF16 ? launch_tc2<128, true>(p2, mq, mk, mv, grid2, pdl != 0, st)
+                                      : launch_tc2<128, false>(p2, mq, mk, mv, grid2, pdl != 0, st);
+        return dtype == B200_BF16 ? launch_tc2<64, true>(p2, mq, mk, mv, grid2, pdl != 0, st)
+                                  : launch_tc2<64, false>(p2, mq, mk, mv, grid2, pdl != 0, st);
+    }
     AttnPrefillTcParams p;
     p.q = static_cast<const uint16_t*>(q);
     p.out = static_cast<uint16_t*>(out);

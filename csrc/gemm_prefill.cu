@@ -15,6 +15,7 @@
 #include <string.h>
 
 #include "gemm_core.cuh"
+#include "tma_host.h"
 
 namespace b200 {
 
@@ -160,22 +161,6 @@ gemm_prefill_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap
     tc_fence_before();
     __syncthreads();
     if (warp == 1) tmem_dealloc<Cfg::kTmemCols>(tmem_base);
-}
-
-typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
-                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
-                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
-
-static EncodeTiledFn encode_tiled_fn() {
-    static EncodeTiledFn fn = [] {
-        void* p = nullptr;
-        cudaDriverEntryPointQueryResult q;
-        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess ||
-            q != cudaDriverEntryPointSuccess)
-            p = nullptr;
-        return reinterpret_cast<EncodeTiledFn>(p);
-    }();
-    return fn;
 }
 
 template <int BN, int DUAL>

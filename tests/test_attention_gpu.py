@@ -129,6 +129,39 @@ def test_rope_append_and_prefill(nh, nkv, D, rope, T, pos0, dtype):
     assert torch.equal(vc[:, pos0:S], v.transpose(0, 1))
     assert (out.float() - ref).abs().max().item() < tol * max(1.0, ref.abs().max().item())
 
+@pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
+@pytest.mark.parametrize("nh,nkv,D,T,pos0,qscale", [(32, 8, 128, 1100, 77, 1.0), (64, 64, 64, 600, 0, 1.0),
+                                                    (8, 8, 128, 700, 300, 1.0), (32, 32, 128, 1024, 0, 6.0),
+                                                    (8, 2, 128, 130, 0, 6.0)])
+def test_prefill_attention_long(nh, nkv, D, T, pos0, qscale, dtype):
+    """Multi-block / two-tiles-per-CTA shapes of the pipelined tcgen05 kernel; the cache tail holds NaNs
+    (rows past the valid length must never reach the output) and large logits exercise the lazy rescale."""
+    from petals_b200.ops import attention as A
+
+    torch.manual_seed(nh + T)
+    dev = "cuda"
+    s_max = pos0 + T + 200
+    S = pos0 + T
+    qkv = torch.randn(T, (nh + 2 * nkv) * D, device=dev).to(dtype)
+    qkv[:, : nh * D] *= qscale
+    kc = torch.full((nkv, s_max, D), float("nan"), device=dev, dtype=dtype)
+    vc = torch.full((nkv, s_max, D), float("nan"), device=dev, dtype=dtype)
+    kc[:, :S] = torch.randn(nkv, S, D, device=dev).to(dtype)
+    vc[:, :S] = torch.randn(nkv, S, D, device=dev).to(dtype)
+    q = qkv[:, : nh * D].float().view(T, nh, D)
+    rep = nh // nkv
+    pos = torch.arange(pos0, S, device=dev)
+    sc = q.transpose(0, 1) @ kc[:, :S].float().repeat_interleave(rep, 0).transpose(1, 2) / math.sqrt(D)
+    mask = torch.arange(S, device=dev)[None, :] > pos[:, None]
+    sc = sc.masked_fill(mask[None], float("-inf"))
+    ref = (torch.softmax(sc, -1) @ vc[:, :S].float().repeat_interleave(rep, 0)).transpose(0, 1).reshape(T, nh * D)
+    out = torch.empty(T, nh * D, device=dev, dtype=dtype)
+    A.attn_prefill(qkv, out, kc, vc, nh, nkv, D, s_max, pos0)
+    torch.cuda.synchronize()
+    tol = 2e-2 if dtype == torch.bfloat16 else 4e-3
+    assert torch.isfinite(out.float()).all()
+    assert (out.float() - ref).abs().max().item() < tol * max(1.0, ref.abs().max().item())
+
 
 @pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
 def test_embed_norm_argmax(dtype):
