@@ -12,15 +12,16 @@
 // Two kernels live here:
 //   attn_prefill_tc_kernel   (v1)  one 128-query tile per CTA, loads / MMAs / softmax back to back
 //   attn_prefill_tc2_kernel  (v2)  the production path: warp-specialised and software-pipelined
-//       warp 8      TMA producer: Q tiles once, then K(0) V(0) K(1) V(1) ... through a 3-stage ring
+//       warp 8      TMA producer: Q tiles once, then K(0) V(0) K(1) V(1) ... through a 5-stage ring
 //                   (tensor maps bounded at the valid cache length: rows past it arrive as zeros)
-//       warp 9      MMA issuer: S_w(j+1) = Q_w K(j+1)^T is issued BEFORE O_w += P_w(j) V(j), so the tensor
-//                   core computes the next scores while the softmax warps work on the current ones
+//       warp 9      MMA issuer, ping-pong over the two query tiles: PV_A(j), S_A(j+1), PV_B(j), S_B(j+1) ...
+//                   while one group's softmax runs, the tensor core works for the other group
 //       warps 0-3   softmax group A (query tile 0), warps 4-7 softmax group B (query tile 1), registers moved
 //                   to them from the two worker warps' group with setmaxnreg: one thread per
-//                   query row reads its 128 scores from TMEM in one go, frees the S buffer at once, writes P
-//                   to shared memory; O accumulates in TMEM and is rescaled only when the running maximum
-//                   grew by more than 2^8 (exactness is restored by the final 1/l)
+//                   query row reads its 128 scores from TMEM in one go and writes the 16-bit P back over the
+//                   first half of the same TMEM columns (P is the tensor-memory A operand of the P V product,
+//                   it never touches shared memory); O accumulates in TMEM and is rescaled only when the
+//                   running maximum grew by more than 2^8 (exactness is restored by the final 1/l)
 //   K/V tiles are loaded once per 256 queries; CTAs are ordered heaviest-first (causal work is triangular).
 #include "attn_core.cuh"
 #include "tma_host.h"
@@ -239,7 +240,7 @@ __global__ void __launch_bounds__(kPfThreads, 1) attn_prefill_tc_kernel(const At
 
 // ---------------------------------------------------------------------------------------------- v2
 constexpr int kPf2Threads = 384;   // warps 0-3: softmax group A, 4-7: group B, 8: TMA, 9: MMA, 10-11: idle
-constexpr int kPf2Ring = 3;
+constexpr int kPf2Ring = 5;
 
 struct AttnPrefillTc2Params {
     uint16_t* __restrict__ out;
@@ -288,21 +289,18 @@ attn_prefill_tc2_kernel(const AttnPrefillTc2Params p, const __grid_constant__ CU
                         const __grid_constant__ CUtensorMap tmap_k, const __grid_constant__ CUtensorMap tmap_v) {
     constexpr int HALVES = D / 64;
     constexpr int TILE = 128 * 128 * HALVES;       // bytes of a [128 x D] 16-bit tile
-    constexpr int P_BYTES = 128 * 128 * 2;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     uint8_t* s_q = smem;                           // [2][TILE]
-    uint8_t* s_ring = s_q + 2 * TILE;              // [3][TILE]
-    uint8_t* s_p = s_ring + kPf2Ring * TILE;       // [2][P_BYTES]
-    uint64_t* bars = reinterpret_cast<uint64_t*>(s_p + 2 * P_BYTES);
+    uint8_t* s_ring = s_q + 2 * TILE;              // [kPf2Ring][TILE]
+    uint64_t* bars = reinterpret_cast<uint64_t*>(s_ring + kPf2Ring * TILE);
     uint64_t* q_full = bars;                       // [1]
-    uint64_t* ring_full = bars + 1;                // [3]
-    uint64_t* ring_empty = bars + 4;               // [3]
-    uint64_t* s_full = bars + 7;                   // [2] scores of tile w are in TMEM
-    uint64_t* s_free = bars + 9;                   // [2] 128 arrivals: scores are in registers
-    uint64_t* p_ready = bars + 11;                 // [2] 128 arrivals: P_w is in shared memory, O_w is rescaled
-    uint64_t* o_full = bars + 13;                  // [2] O_w += P_w V has completed
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 15);
+    uint64_t* ring_full = bars + 1;                // [kPf2Ring]
+    uint64_t* ring_empty = ring_full + kPf2Ring;   // [kPf2Ring]
+    uint64_t* s_full = ring_empty + kPf2Ring;      // [2] scores of tile w are in TMEM
+    uint64_t* p_ready = s_full + 2;                // [2] 128 arrivals: P_w is in TMEM, O_w is rescaled
+    uint64_t* o_full = p_ready + 2;                // [2] O_w += P_w V has completed
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(o_full + 2);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int h = blockIdx.x;
@@ -314,7 +312,7 @@ attn_prefill_tc2_kernel(const AttnPrefillTc2Params p, const __grid_constant__ CU
         mbar_init(q_full, 1);
         for (int i = 0; i < kPf2Ring; ++i) { mbar_init(&ring_full[i], 1); mbar_init(&ring_empty[i], 1); }
         for (int i = 0; i < 2; ++i) {
-            mbar_init(&s_full[i], 1); mbar_init(&s_free[i], 128); mbar_init(&p_ready[i], 128); mbar_init(&o_full[i], 1);
+            mbar_init(&s_full[i], 1); mbar_init(&p_ready[i], 128); mbar_init(&o_full[i], 1);
         }
         fence_mbar_init();
         asm volatile("prefetch.tensormap [%0];\n" ::"l"(&tmap_q) : "memory");
@@ -368,11 +366,12 @@ attn_prefill_tc2_kernel(const AttnPrefillTc2Params p, const __grid_constant__ CU
         // ------------------------------------------------------------ MMA issuer
         const uint32_t idesc_s = umma_idesc(128, 128, BF16, BF16, 0, 0);
         const uint32_t idesc_o = umma_idesc(128, D, BF16, BF16, 0, 1);   // B = V is MN-major
-        const uint32_t q_addr = smem_u32(s_q), ring_addr = smem_u32(s_ring), p_addr = smem_u32(s_p);
+        const uint32_t q_addr = smem_u32(s_q), ring_addr = smem_u32(s_ring);
         RingPos rk{0, 0}, rv{1, 0};   // K(j) is ring item 2j, V(j) is item 2j + 1
-        auto issue_s = [&](int w, int j, const RingPos& r) {
+        // S_w(j+1) overwrites the columns P_w(j) lives in: it is issued after P_w(j) V(j), and the tensor
+        // core executes in issue order.
+        auto issue_s = [&](int w, const RingPos& r) {
             mbar_wait(&ring_full[r.stage], r.par);
-            if (j > 0) mbar_wait(&s_free[w], (uint32_t)(j - 1) & 1);
             tc_fence_after();
             if (elect_one()) {
 #pragma unroll
@@ -392,11 +391,10 @@ attn_prefill_tc2_kernel(const AttnPrefillTc2Params p, const __grid_constant__ CU
             if (elect_one()) {
 #pragma unroll
                 for (int ks = 0; ks < 8; ++ks) {
-                    const uint32_t a_off = (ks / 4) * (128 * 128) + (ks % 4) * 32;   // P: K-major over keys
-                    const uint32_t b_off = ks * 2048;                                 // V: 16 key rows
-                    umma_f16(tmem_base + 256 + w * D, umma_desc_kmajor_sw128(p_addr + w * P_BYTES + a_off, 1024),
-                             umma_desc_mnmajor_sw128(ring_addr + r.stage * TILE + b_off, 128 * 128, 1024), idesc_o,
-                             (j > 0 || ks > 0) ? 1u : 0u);
+                    // A = P_w from tensor memory: 16 keys = 8 columns per k-step; B = V: 16 key rows = 2 KiB
+                    umma_f16_ts(tmem_base + 256 + w * D, tmem_base + w * 128 + ks * 8,
+                                umma_desc_mnmajor_sw128(ring_addr + r.stage * TILE + ks * 2048, 128 * 128, 1024), idesc_o,
+                                (j > 0 || ks > 0) ? 1u : 0u);
                 }
                 umma_commit(&o_full[w]);
             }
@@ -407,19 +405,18 @@ attn_prefill_tc2_kernel(const AttnPrefillTc2Params p, const __grid_constant__ CU
             __syncwarp();
         };
         mbar_wait(q_full, 0);
-        if (n_blk[0] > 0) issue_s(0, 0, rk);
-        if (n_blk[1] > 0) issue_s(1, 0, rk);
+        if (n_blk[0] > 0) issue_s(0, rk);
+        if (n_blk[1] > 0) issue_s(1, rk);
         release(rk);
         for (int j = 0; j < n_max; ++j) {
-            if (j + 1 < n_max) {
-                rk.advance(2);
-                if (j + 1 < n_blk[0]) issue_s(0, j + 1, rk);
-                if (j + 1 < n_blk[1]) issue_s(1, j + 1, rk);
-                release(rk);
-            }
+            const bool more = j + 1 < n_max;
+            if (more) rk.advance(2);
             if (j < n_blk[0]) issue_pv(0, j, rv);
+            if (j + 1 < n_blk[0]) issue_s(0, rk);
             if (j < n_blk[1]) issue_pv(1, j, rv);
+            if (j + 1 < n_blk[1]) issue_s(1, rk);
             release(rv);
+            if (more) release(rk);
             rv.advance(2);
         }
       }
@@ -435,7 +432,6 @@ attn_prefill_tc2_kernel(const AttnPrefillTc2Params p, const __grid_constant__ CU
         const uint32_t t_lane = (uint32_t)(lg * 32) << 16;
         const uint32_t tmem_s = tmem_base + w * 128 + t_lane;
         const uint32_t tmem_o = tmem_base + 256 + w * D + t_lane;
-        const uint32_t p_base = smem_u32(s_p + w * P_BYTES);
         float m_used = -INFINITY, l_run = 0.f;
         for (int j = 0; j < nb; ++j) {
             const int k0 = j * 128;
@@ -450,16 +446,18 @@ attn_prefill_tc2_kernel(const AttnPrefillTc2Params p, const __grid_constant__ CU
                 for (int i = 0; i < 16; ++i) s[c * 16 + i] = __uint_as_float(r[i]);
             }
             tmem_ld_wait();
-            tc_fence_before();
-            mbar_arrive(&s_free[w]);                // the next Q K^T may overwrite S now
             if (k0 + 127 > p.pos0 + q0 + w * 128) { // the block crosses the diagonal of this tile
                 const int lim = q_pos - k0;
 #pragma unroll
                 for (int i = 0; i < 128; ++i) s[i] = (i <= lim) ? s[i] : -INFINITY;
             }
-            float m_blk = s[0];
+            // eight independent chains: two warps per scheduler cannot hide a 127-deep dependent FMNMX chain
+            float mx[8];
 #pragma unroll
-            for (int i = 1; i < 128; ++i) m_blk = fmaxf(m_blk, s[i]);
+            for (int i = 0; i < 8; ++i) mx[i] = s[i];
+#pragma unroll
+            for (int i = 8; i < 128; ++i) mx[i & 7] = fmaxf(mx[i & 7], s[i]);
+            const float m_blk = fmaxf(fmaxf(fmaxf(mx[0], mx[1]), fmaxf(mx[2], mx[3])), fmaxf(fmaxf(mx[4], mx[5]), fmaxf(mx[6], mx[7])));
             const float m_new = fmaxf(m_used, m_blk);
             const bool need = (m_new - m_used) * p.scale_log2e > 8.0f;
             const bool any = __any_sync(0xffffffffu, need);
@@ -484,23 +482,22 @@ attn_prefill_tc2_kernel(const AttnPrefillTc2Params p, const __grid_constant__ CU
                 }
             }
             const float neg_m = -m_used * p.scale_log2e;
-            float l_blk = 0.f;
+            float ls[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
-            for (int c = 0; c < 16; ++c) {          // 16 chunks of 8 keys = 16 bytes of P
-                uint32_t w4[4];
+            for (int c = 0; c < 4; ++c) {           // 32 keys = 16 packed columns per tcgen05.st
+                uint32_t pk[16];
 #pragma unroll
-                for (int i = 0; i < 4; ++i) {
-                    const float a = ex2_approx(fmaf(s[c * 8 + 2 * i], p.scale_log2e, neg_m));
-                    const float b = ex2_approx(fmaf(s[c * 8 + 2 * i + 1], p.scale_log2e, neg_m));
-                    l_blk += a + b;
-                    w4[i] = pack2<BF16>(a, b);
+                for (int i = 0; i < 16; ++i) {
+                    const float a = ex2_approx(fmaf(s[c * 32 + 2 * i], p.scale_log2e, neg_m));
+                    const float b = ex2_approx(fmaf(s[c * 32 + 2 * i + 1], p.scale_log2e, neg_m));
+                    ls[i & 3] += a + b;
+                    pk[i] = pack2<BF16>(a, b);
                 }
-                st_shared_v4(p_base + (c / 8) * (128 * 128) + row * 128 + (((c & 7) ^ (row & 7)) << 4),
-                             make_uint4(w4[0], w4[1], w4[2], w4[3]));
+                tmem_st16(tmem_s + c * 16, pk);
             }
-            l_run += l_blk;
+            l_run += (ls[0] + ls[1]) + (ls[2] + ls[3]);
+            tmem_st_wait();
             tc_fence_before();
-            fence_proxy_async_smem();
             mbar_arrive(&p_ready[w]);
         }
         if (nb > 0) {
@@ -533,7 +530,7 @@ attn_prefill_tc2_kernel(const AttnPrefillTc2Params p, const __grid_constant__ CU
 template <int D, bool BF16>
 static int launch_tc2(const AttnPrefillTc2Params& p, const CUtensorMap& mq, const CUtensorMap& mk, const CUtensorMap& mv,
                       dim3 grid, bool pdl, cudaStream_t stream) {
-    constexpr size_t smem = (size_t)(2 + kPf2Ring) * 128 * 128 * (D / 64) + 2 * 128 * 128 * 2 + 1024 + 256;
+    constexpr size_t smem = (size_t)(2 + kPf2Ring) * 128 * 128 * (D / 64) + 1024 + 256;
     static_assert(smem <= 227 * 1024, "shared memory budget exceeded");
     static thread_local int configured_dev = -1;
     int dev = 0;
