@@ -98,6 +98,19 @@ gemm_streamk_kernel(const GemmParams p) {
                     if (++t_tile == p.t_tiles) { t_tile = 0; ++n_tile; tile_base += (size_t)p.kbpt * Cfg::kBlockA; }
                 }
             }
+            // Our own stream is issued; keep the HBM busy through the fix-up / epilogue and the next launch
+            // by pulling the head of the following kernels' weights into L2 (16 KiB pieces, CTA-interleaved).
+#pragma unroll
+            for (int r = 0; r < 2; ++r) {
+                constexpr long long kPiece = 16384;
+                const long long pieces = (p.pf_bytes[r] + kPiece - 1) / kPiece;
+                for (long long c = cta; c < pieces; c += gridDim.x) {
+                    const long long off = c * kPiece;
+                    const long long n = p.pf_bytes[r] - off < kPiece ? p.pf_bytes[r] - off : kPiece;
+                    if (elect_one()) bulk_prefetch_l2(p.pf_ptr[r] + off, (uint32_t)n);
+                    __syncwarp();
+                }
+            }
         }
     } else if (warp == 1) {
         // ------------------------------------------------ MMA issuer (whole warp, one elected lane issues)
@@ -579,6 +592,10 @@ static int gemm_impl(const b200_gemm_args* a, const b200_tp_args* tp, void* stre
     p.is_bf16 = (a->dtype == B200_BF16) ? 1 : 0;
     p.out_fp32 = a->out_fp32;
     p.debug = a->debug;
+    for (int r = 0; r < 2; ++r) {
+        p.pf_ptr[r] = static_cast<const uint8_t*>(a->prefetch[r]);
+        p.pf_bytes[r] = a->prefetch[r] ? (a->prefetch_bytes[r] & ~15LL) : 0;
+    }
     p.tp_world = 0;
     p.tp_defer = 0;
     if (tp) {

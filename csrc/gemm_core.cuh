@@ -84,6 +84,8 @@ struct GemmParams {
     int gather_ldr;
     int is_fp8;                       // e4m3 weights + on-the-fly e4m3 activations (kind::f8f6f4)
     const float* __restrict__ w_scale;  // fp8: per-output-row dequantisation scale
+    const uint8_t* pf_ptr[2];   // L2 warm-up ranges for the kernels that follow (see b200_gemm_args.prefetch)
+    long long pf_bytes[2];
     int debug;  // experiment switches (scripts/exp_*.py): 1 = no MMA issue, 2 = no B stage waits
 };
 

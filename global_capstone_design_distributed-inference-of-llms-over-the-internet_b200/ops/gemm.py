@@ -74,11 +74,12 @@ def linear(
     pdl: bool = False,
     grid: int = 0,
     debug: int = 0,
+    prefetch=None,
 ) -> torch.Tensor:
     """x: [T, K] (16-bit, last dim contiguous) -> [T, N]."""
     a, out = fill_args(x, w, out=out, residual=residual, epilogue=epilogue, norm_mode=norm_mode, norm_w=norm_w,
                        norm_b=norm_b, norm_eps=norm_eps, out_fp32=out_fp32, workspace=workspace, pdl=pdl, grid=grid,
-                       debug=debug)
+                       debug=debug, prefetch=prefetch)
     if (x.shape[0] >= PREFILL_MIN_TOKENS and norm_mode == NORM_NONE and not w.fp8 and _prefill_kernel_enabled()):
         # token-tile-filling inputs: TMA-fed kernel with the epilogue overlapped (csrc/gemm_prefill.cu)
         rc = native.lib().b200_gemm_prefill(ctypes.byref(a), native.current_stream_ptr())
@@ -99,7 +100,7 @@ def _prefill_kernel_enabled() -> bool:
 
 
 def fill_args(x, w, *, out=None, residual=None, epilogue=EPI_NONE, norm_mode=NORM_NONE, norm_w=None, norm_b=None,
-              norm_eps=1e-5, out_fp32=False, workspace=None, pdl=False, grid=0, debug=0):
+              norm_eps=1e-5, out_fp32=False, workspace=None, pdl=False, grid=0, debug=0, prefetch=None):
     """Builds the ``b200_gemm_args`` for one call (also used to describe ops of the persistent kernel)."""
     assert x.dim() == 2 and x.stride(1) == 1 and x.is_cuda
     T, K = x.shape
@@ -136,4 +137,11 @@ def fill_args(x, w, *, out=None, residual=None, epilogue=EPI_NONE, norm_mode=NOR
     a.debug = debug
     a.fp8 = 1 if w.fp8 else 0
     a.w_scale = w.scale.data_ptr() if w.scale is not None else None
+    # prefetch: up to two (PackedWeight | tensor, first_byte, n_bytes) ranges to warm the L2 with
+    for i, (t, off, nbytes) in enumerate(prefetch or ()):
+        data = t.data if hasattr(t, "n_tiles") else t
+        total = data.numel() * data.element_size()
+        off = min(off, total) & ~15
+        a.prefetch[i] = data.data_ptr() + off
+        a.prefetch_bytes[i] = max(0, min(nbytes, total - off))
     return a, out

@@ -51,6 +51,8 @@ class GemmArgs(ctypes.Structure):
         ("debug", ctypes.c_int32),
         ("fp8", ctypes.c_int32),
         ("w_scale", ctypes.c_void_p),
+        ("prefetch", ctypes.c_void_p * 2),
+        ("prefetch_bytes", ctypes.c_int64 * 2),
     ]
 
 

@@ -84,6 +84,13 @@ typedef struct b200_gemm_args {
     int32_t debug;        /* 0 in production; experiment switches, see csrc/gemm.cu */
     int32_t fp8;          /* 1 = w_packed holds e4m3 weights (pack_weight_fp8), T <= 32, K % 128 == 0 */
     const float* w_scale; /* fp8: per-output-row dequantisation scale, [n_tiles*128] (dual: gate rows then up rows) */
+    /* Optional L2 warm-up for the kernels that follow in the stream (b200_gemm only): once a CTA has issued
+     * its last weight load it asks the L2 for its share of up to two byte ranges (cp.async.bulk.prefetch.L2),
+     * typically the head of the next linear's packed weights, so the HBM keeps streaming through this
+     * kernel's fix-up / epilogue and the next kernel's launch.  NULL / 0 = none.  Ranges must be 16-byte
+     * aligned device memory that stays valid until the stream has passed this kernel. */
+    const void* prefetch[2];
+    int64_t prefetch_bytes[2];
 } b200_gemm_args;
 
 int b200_gemm(const b200_gemm_args* args, void* stream);
