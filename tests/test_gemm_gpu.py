@@ -180,3 +180,21 @@ def test_gemm_fp8_swiglu_dual():
     uq = (xa @ packing.dequantize_fp8(wu).t()).to(dtype).float()
     ref = torch.nn.functional.silu(gq).to(dtype).float() * uq
     _close(out, ref, dtype)
+
+
+def test_gemm_l2_prefetch_hint_changes_nothing():
+    """The optional L2 warm-up ranges are a pure hint: same bits out, odd sizes and offsets accepted."""
+    from petals_b200.ops import gemm, packing
+
+    dtype = torch.float16
+    torch.manual_seed(5)
+    x = (torch.randn(3, 1024, device="cuda") * 0.5).to(dtype)
+    w = (torch.randn(768, 1024, device="cuda") / 32).to(dtype)
+    nxt = packing.pack_weight((torch.randn(512, 1024, device="cuda") / 32).to(dtype))
+    pw = packing.pack_weight(w)
+    base = gemm.linear(x, pw)
+    hinted = gemm.linear(x, pw, prefetch=[(nxt, 0, nxt.nbytes), (nxt, 4096 + 24, 100_000)])
+    past_end = gemm.linear(x, pw, prefetch=[(nxt, nxt.nbytes - 32, 1 << 30)])
+    torch.cuda.synchronize()
+    assert torch.equal(base, hinted) and torch.equal(base, past_end)
+    _close(base, _ref(x, w, dtype=dtype), dtype)
