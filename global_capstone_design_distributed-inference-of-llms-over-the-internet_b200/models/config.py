@@ -133,6 +133,9 @@ PRESETS: Dict[str, ModelConfig] = {
     "tiny-llama": ModelConfig("llama", 4, 256, 2, 2, 128, 512, 1024, 1e-5, 10000.0, None, 512, False, "tiny-llama", 1, 2),
     "tiny-llama-gqa": ModelConfig("llama", 4, 512, 4, 2, 128, 768, 1024, 1e-5, 500000.0, None, 512, False,
                                   "tiny-llama-gqa", 1, 2),
+    # shardable 8 ways (heads, kv heads, 64-wide k-blocks of the MLP): tensor-parallel tests at world 4 / 8
+    "tiny-llama-tp8": ModelConfig("llama", 2, 1024, 8, 8, 128, 2048, 1024, 1e-5, 10000.0, None, 512, False,
+                                  "tiny-llama-tp8", 1, 2),
     "tiny-gpt2": ModelConfig("gpt2", 4, 128, 2, 2, 64, 512, 1000, 1e-5, max_positions=256, tie_embeddings=True,
                              name="tiny-gpt2", bos_token_id=999, eos_token_id=999),
 }

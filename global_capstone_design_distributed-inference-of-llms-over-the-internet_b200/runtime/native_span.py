@@ -125,7 +125,9 @@ class NativeSpan:
             self.h_a, self.h_b, self.xn = mk(Tm, c.hidden), mk(Tm, c.hidden), mk(Tm, c.hidden)
             self.qkv = mk(Tm, c.qkv_size)
             self.attn = mk(Tm, c.q_size)
-            self.act = mk(Tm, c.intermediate)
+            # width padded to the packed K of down_proj (64-wide k-blocks); the pad columns stay zero, which is what
+            # lets an intermediate size that is not a multiple of 64 (Llama-2-7B split 8 ways: 1376) through
+            self.act = torch.zeros(Tm, (c.intermediate + 63) // 64 * 64, dtype=dtype, device=self.device)
             self.ids_in = torch.zeros(Tm, dtype=torch.int64, device=self.device)
             self.ws = G.GemmWorkspace.create(self.device, Tm)
             self.splits = attn_splits or max(1, min(16, kv_capacity // 256))

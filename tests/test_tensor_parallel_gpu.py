@@ -1,4 +1,4 @@
-"""2-way tensor-parallel span: fused GEMM+all-reduce (peer memory) vs the NCCL baseline vs one GPU."""
+"""2/4/8-way tensor-parallel span: fused GEMM+all-reduce (peer memory) vs the NCCL baseline vs one GPU."""
 import os
 import socket
 import sys
@@ -19,7 +19,7 @@ def _free_port():
     return p
 
 
-def _run(rank, world, port, q):
+def _run(rank, world, port, q, preset="tiny-llama-gqa"):
     sys.path.insert(0, ROOT)
     import torch.distributed as dist
 
@@ -33,12 +33,12 @@ def _run(rank, world, port, q):
     torch.cuda.set_device(rank)
     dev = torch.device("cuda", rank)
     dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
-    cfg = PRESETS["tiny-llama-gqa"]
+    cfg = PRESETS[preset]
     dtype = torch.bfloat16
     res = {}
     ids = torch.randint(0, cfg.vocab, (40,), generator=torch.Generator().manual_seed(0)).to(dev)
     for mode in ("single", "fused", "fused-nodefer", "nccl"):
-        w = load_span("tiny-llama-gqa", cfg, 0, cfg.n_layers, need_embed=True, need_head=True, dtype=dtype, device=dev, seed=9)
+        w = load_span(preset, cfg, 0, cfg.n_layers, need_embed=True, need_head=True, dtype=dtype, device=dev, seed=9)
         if mode == "single":
             span = NativeSpan(cfg, w, dev, dtype, kv_capacity=256, max_batch=2, max_chunk=64, use_graphs=False)
             lc = cfg
@@ -68,12 +68,14 @@ def _run(rank, world, port, q):
     dist.destroy_process_group()
 
 
-@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs")
-def test_tp2_fused_allreduce_matches_single_gpu_and_nccl():
+@pytest.mark.parametrize("world,preset", [(2, "tiny-llama-gqa"), (4, "tiny-llama-tp8"), (8, "tiny-llama-tp8")])
+def test_tp_fused_allreduce_matches_single_gpu_and_nccl(world, preset):
+    if torch.cuda.device_count() < world:
+        pytest.skip(f"needs {world} GPUs")
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
     port = _free_port()
-    procs = [ctx.Process(target=_run, args=(r, 2, port, q)) for r in range(2)]
+    procs = [ctx.Process(target=_run, args=(r, world, port, q, preset)) for r in range(world)]
     for p in procs:
         p.start()
     res, same = q.get(timeout=300)
