@@ -230,6 +230,7 @@ gemm_streamk_kernel(const GemmParams p) {
         int sb = 0;
         bool rms_ready = (FP8 != 0);   // fp8: the 1/rms is already folded into stat_rstd
         const int tp_seq = (p.tp_world > 1) ? (__ldcv(p.tp_seq) + 1) : 0;
+        constexpr int ll_seq = 1;   // tag of a published word; the consumer clears the word again (tag 0) once it has read it
         long long q = q_begin;
         while (q < q_end) {
             const int u = (int)(q / p.kbpt);
@@ -396,6 +397,84 @@ gemm_streamk_kernel(const GemmParams p) {
                     if (p.tp_world > 1) tp_allreduce_tile(p, n_tile, row, ncol, e, tp_seq, vg);
                     if (!(p.tp_world > 1 && p.tp_defer))
                     epilogue_store_chunk<BN, DUAL>(p, n_tile, t_tile, row, c, vg, vu, tok_scale);
+                } else if (p.ll_words) {
+                    // ---- ticket-free fix-up (host guarantees T <= 4, one part per CTA, ll_parts CTAs per tile)
+                    constexpr int kLLStride = APER * 4 * kTileM;          // words per CTA
+                    const int P = p.ll_parts;
+                    const int first = u * P;                              // CTAs [first, first + P) share tile u
+                    if (cta != first + P - 1) {
+                        uint2* mine = reinterpret_cast<uint2*>(p.ll_words) + (size_t)cta * kLLStride + row;
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) {
+                            if (j < ncol) {
+                                ll_store(mine + j * kTileM, vg[j], ll_seq);
+                                if (DUAL) ll_store(mine + (4 + j) * kTileM, vu[j], ll_seq);
+                            }
+                        }
+                    } else {
+                        // last slice of the tile: sum p_0 + ... + p_{P-2} + own, in that order (same order as the
+                        // ticket path).  Words are polled eight at a time so the L2 round trips overlap.
+                        float sg[4] = {0.f, 0.f, 0.f, 0.f}, su[4] = {0.f, 0.f, 0.f, 0.f};
+                        const uint2* base = reinterpret_cast<const uint2*>(p.ll_words) + (size_t)first * kLLStride + row;
+                        const int lanes_k = APER * ncol;                  // (accumulator, column) pairs of this thread
+                        int k = 0, r = 0;                                 // walk (k, r) with r fastest
+                        const int total = lanes_k * (P - 1);
+                        for (int done = 0; done < total; done += 8) {
+                            const uint2* src[8];
+                            int kk[8];
+                            const int nb = min(8, total - done);
+#pragma unroll
+                            for (int i = 0; i < 8; ++i) {
+                                const int a = (k >= ncol) ? 1 : 0, j = k - a * ncol;
+                                src[i] = base + (size_t)r * kLLStride + (a * 4 + j) * kTileM;
+                                kk[i] = k;
+                                if (i < nb && ++r == P - 1) { r = 0; ++k; }
+                            }
+                            uint32_t val[8], tag[8];
+                            long long t0 = 0;
+                            for (;;) {
+                                bool ok = true;
+#pragma unroll
+                                for (int i = 0; i < 8; ++i)
+                                    if (i < nb)
+                                        asm volatile("ld.relaxed.gpu.global.v2.u32 {%0, %1}, [%2];\n"
+                                                     : "=r"(val[i]), "=r"(tag[i]) : "l"(src[i]) : "memory");
+#pragma unroll
+                                for (int i = 0; i < 8; ++i)
+                                    if (i < nb) ok = ok && ((int)tag[i] == ll_seq);
+                                if (ok) break;
+                                if (t0 == 0) t0 = clock64();
+                                else if (clock64() - t0 > 8000000000LL) {
+                                    printf("b200: stream-K partial exchange timed out (block %d thread %d seq %d)\n",
+                                           blockIdx.x, threadIdx.x, ll_seq);
+                                    __trap();
+                                }
+                            }
+#pragma unroll
+                            for (int i = 0; i < 8; ++i)   // leave the slot empty for the next launch (ordered by the kernel boundary)
+                                if (i < nb)
+                                    asm volatile("st.relaxed.gpu.global.v2.u32 [%0], {%1, %1};\n" ::"l"(src[i]), "r"(0) : "memory");
+#pragma unroll
+                            for (int i = 0; i < 8; ++i) {
+                                if (i < nb) {
+                                    const float v = __uint_as_float(val[i]);
+                                    const int a = (kk[i] >= ncol) ? 1 : 0, j = kk[i] - a * ncol;
+#pragma unroll
+                                    for (int jj = 0; jj < 4; ++jj) {
+                                        if (jj == j) { if (a) su[jj] += v; else sg[jj] += v; }
+                                    }
+                                }
+                            }
+                        }
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) {
+                            vg[j] = sg[j] + vg[j];
+                            if (DUAL) vu[j] = su[j] + vu[j];
+                        }
+                        if (p.tp_world > 1) tp_allreduce_tile(p, n_tile, row, ncol, e, tp_seq, vg);
+                        if (!(p.tp_world > 1 && p.tp_defer))
+                        epilogue_store_chunk<BN, DUAL>(p, n_tile, t_tile, row, c, vg, vu, tok_scale);
+                    }
                 } else {
 #pragma unroll
                     for (int j = 0; j < 16; ++j) {
@@ -410,7 +489,7 @@ gemm_streamk_kernel(const GemmParams p) {
             __syncwarp();
             if (lane == 0) mbar_arrive(acc_empty);
 
-            if (!full_tile) {
+            if (!full_tile && !p.ll_words) {
                 // Publish the partial with ONE acq_rel ticket: the CTA barrier orders every thread's
                 // partial stores before thread 0's release, and thread 0's acquire before every
                 // thread's reads (cumulativity), so no per-thread membar.gl is needed (~1 us per kernel).
@@ -509,6 +588,11 @@ extern "C" int32_t b200_gemm_token_tile(int32_t T, int32_t dual) {
     (void)dual;
     return pick_token_tile(T);
 }
+
+// ll_buf layout: [kLLHeaderBytes reserved][kLLMaxCtas x 8 KiB of (value, tag) words, all zero between launches]
+constexpr int kLLMaxCtas = 512;
+constexpr int kLLHeaderBytes = 256;
+extern "C" int64_t b200_gemm_ll_bytes(void) { return (int64_t)kLLHeaderBytes + (int64_t)kLLMaxCtas * 2 * 4 * kTileM * 8; }
 
 extern "C" int64_t b200_gemm_scratch_bytes(int32_t max_tokens) {
     const int bn = pick_token_tile(max_tokens);
@@ -635,6 +719,15 @@ static int gemm_impl(const b200_gemm_args* a, const b200_tp_args* tp, void* stre
         if (per_tile >= 2) grid = per_tile * a->n_tiles;
     }
     if ((long long)grid > p.Q) grid = (int)p.Q;
+    // Ticket-free fix-up: only when every tile is shared by the same whole number of CTAs with one part each.
+    p.ll_words = nullptr; p.ll_parts = 0;
+    if (a->ll_buf && bn == 16 && t_tiles == 1 && a->T <= 4 && grid % a->n_tiles == 0 && grid <= kLLMaxCtas) {
+        const int parts = grid / a->n_tiles;
+        if (parts >= 2 && p.kbpt >= parts) {
+            p.ll_words = reinterpret_cast<unsigned long long*>(static_cast<uint8_t*>(a->ll_buf) + kLLHeaderBytes);
+            p.ll_parts = parts;
+        }
+    }
     cudaStream_t stream = static_cast<cudaStream_t>(stream_);
     const bool pdl = a->pdl != 0;
     if (a->fp8) {   // only the decode-size tiles are instantiated for e4m3 weights

@@ -84,6 +84,11 @@ struct GemmParams {
     int gather_ldr;
     int is_fp8;                       // e4m3 weights + on-the-fly e4m3 activations (kind::f8f6f4)
     const float* __restrict__ w_scale;  // fp8: per-output-row dequantisation scale
+    // Fix-up of split tiles without tickets (decode, T <= 4): the grid gives every tile exactly `ll_parts` CTAs;
+    // the first ll_parts-1 of them publish their partial sums as (value, tag) 8-byte words and the last one
+    // polls for them and clears them again (no fence, no atomic, no counter) - see b200_gemm_args.ll_buf.
+    unsigned long long* ll_words;
+    int ll_parts;
     const uint8_t* pf_ptr[2];   // L2 warm-up ranges for the kernels that follow (see b200_gemm_args.prefetch)
     long long pf_bytes[2];
     int debug;  // experiment switches (scripts/exp_*.py): 1 = no MMA issue, 2 = no B stage waits

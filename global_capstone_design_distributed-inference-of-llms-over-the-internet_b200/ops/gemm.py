@@ -36,6 +36,7 @@ class GemmWorkspace:
     scratch: torch.Tensor
     counters: torch.Tensor
     max_tokens: int
+    ll: Optional[torch.Tensor] = None     # ticket-free fix-up words (b200_gemm_args.ll_buf), zeroed once
 
     @classmethod
     def create(cls, device, max_tokens: int = 16, max_units: int = 1 << 16) -> "GemmWorkspace":
@@ -43,7 +44,10 @@ class GemmWorkspace:
             nbytes = native.lib().b200_gemm_scratch_bytes(int(max_tokens))
         scratch = torch.empty(nbytes // 4, dtype=torch.float32, device=device)
         counters = torch.zeros(max_units, dtype=torch.int32, device=device)
-        return cls(scratch, counters, max_tokens)
+        ll = None
+        if _ll_fixup_enabled():
+            ll = torch.zeros(native.lib().b200_gemm_ll_bytes() // 8, dtype=torch.int64, device=device)
+        return cls(scratch, counters, max_tokens, ll)
 
 
 _default_ws: dict = {}
@@ -93,6 +97,12 @@ def linear(
 PREFILL_MIN_TOKENS = 64
 
 
+def _ll_fixup_enabled() -> bool:
+    import os
+
+    return os.environ.get("B200_GEMM_LL_FIXUP", "1") != "0"
+
+
 def _prefill_kernel_enabled() -> bool:
     import os
 
@@ -137,6 +147,7 @@ def fill_args(x, w, *, out=None, residual=None, epilogue=EPI_NONE, norm_mode=NOR
     a.debug = debug
     a.fp8 = 1 if w.fp8 else 0
     a.w_scale = w.scale.data_ptr() if w.scale is not None else None
+    a.ll_buf = ws.ll.data_ptr() if ws.ll is not None else None
     # prefetch: up to two (PackedWeight | tensor, first_byte, n_bytes) ranges to warm the L2 with
     for i, (t, off, nbytes) in enumerate(prefetch or ()):
         data = t.data if hasattr(t, "n_tiles") else t

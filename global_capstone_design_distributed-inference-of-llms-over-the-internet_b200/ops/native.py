@@ -53,6 +53,7 @@ class GemmArgs(ctypes.Structure):
         ("w_scale", ctypes.c_void_p),
         ("prefetch", ctypes.c_void_p * 2),
         ("prefetch_bytes", ctypes.c_int64 * 2),
+        ("ll_buf", ctypes.c_void_p),
     ]
 
 
@@ -80,6 +81,8 @@ def lib() -> ctypes.CDLL:
             L.b200_gemm_prefill.restype = ctypes.c_int
             L.b200_gemm_scratch_bytes.argtypes = [ctypes.c_int32]
             L.b200_gemm_scratch_bytes.restype = ctypes.c_int64
+            L.b200_gemm_ll_bytes.argtypes = []
+            L.b200_gemm_ll_bytes.restype = ctypes.c_int64
             L.b200_gemm_token_tile.argtypes = [ctypes.c_int32, ctypes.c_int32]
             L.b200_gemm_token_tile.restype = ctypes.c_int32
             _register_optional(L)
