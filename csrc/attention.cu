@@ -182,6 +182,7 @@ extern "C" int b200_attn_decode(const b200_attn_decode_args* a, void* stream_) {
     p.inv_freq = a->inv_freq;
     p.scratch = a->scratch;
     p.counters = a->counters;
+    p.ll = static_cast<unsigned long long*>(a->ll_scratch);
     p.T = a->T; p.n_heads = a->n_heads; p.n_kv = a->n_kv_heads; p.s_max = a->s_max;
     p.splits = a->splits > 0 ? a->splits : 1;
     p.ldqkv = a->ldqkv; p.ldo = a->ldo;

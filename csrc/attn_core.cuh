@@ -13,6 +13,7 @@ struct AttnDecodeParams {
     const float* __restrict__ inv_freq;              // [D/2] or null
     float* __restrict__ scratch;                     // [T][n_heads][splits][D+2]
     int* __restrict__ counters;                      // [T][n_kv]
+    unsigned long long* __restrict__ ll;             // optional [T][n_heads][splits][D+2] (value, tag) words, or null
     int T, n_heads, n_kv, s_max, splits, ldqkv, ldo;
     float scale;
     int is_bf16;
@@ -23,6 +24,17 @@ constexpr int kAttnThreads = 128;
 #define B200_ATTN_MIN_ROWS 64
 #endif
 constexpr int kMinRowsPerSplit = B200_ATTN_MIN_ROWS;
+
+// (value, tag) words of the ticket-free split merge: tag 1 = published, 0 = empty (cleared by the consumer).
+__device__ __forceinline__ void ll_word_store(uint2* dst, float v) {
+    asm volatile("st.relaxed.gpu.global.v2.u32 [%0], {%1, %2};\n" ::"l"(dst), "r"(__float_as_uint(v)), "r"(1u) : "memory");
+}
+__device__ __forceinline__ void ll_word_load(const uint2* src, uint32_t& v, uint32_t& tag) {
+    asm volatile("ld.relaxed.gpu.global.v2.u32 {%0, %1}, [%2];\n" : "=r"(v), "=r"(tag) : "l"(src) : "memory");
+}
+__device__ __forceinline__ void ll_word_clear(uint2* dst) {
+    asm volatile("st.relaxed.gpu.global.v2.u32 [%0], {%1, %1};\n" ::"l"(dst), "r"(0u) : "memory");
+}
 
 __device__ __forceinline__ void unpack8(const uint4& v, float (&f)[8], int is_bf16) {
     const uint32_t w[4] = {v.x, v.y, v.z, v.w};
@@ -218,6 +230,64 @@ __device__ __forceinline__ void attn_decode_body(const AttnDecodeParams& p, int 
         }
         if (eff == 1) {
             p.out[(size_t)t * p.ldo + (g * GROUP + h) * D + d] = float_to_h16(oo / ll, p.is_bf16);
+        } else if (p.ll) {
+            // ---- ticket-free merge: splits 0..eff-2 publish (value, tag) words, split eff-1 polls for them, merges
+            // in split order (same arithmetic as the ticket path) and clears the words again.
+            uint2* wbase = reinterpret_cast<uint2*>(p.ll) + ((size_t)(t * p.n_heads + g * GROUP + h) * splits) * (D + 2);
+            if (s != eff - 1) {
+                uint2* dst = wbase + (size_t)s * (D + 2);
+                ll_word_store(dst + d, oo);
+                if (d == 0) { ll_word_store(dst + D, mm); ll_word_store(dst + D + 1, ll); }
+            } else {
+                float pm[16], pl[16], po[16];   // splits <= 16
+                for (int j0 = 0; j0 < eff - 1; j0 += 4) {
+                    const int nb = min(4, eff - 1 - j0);
+                    uint32_t v[12], tg[12];
+                    long long t0 = 0;
+                    for (;;) {
+                        bool ok = true;
+#pragma unroll
+                        for (int i = 0; i < 4; ++i) {
+                            if (i < nb) {
+                                const uint2* src = wbase + (size_t)(j0 + i) * (D + 2);
+                                ll_word_load(src + d, v[3 * i], tg[3 * i]);
+                                ll_word_load(src + D, v[3 * i + 1], tg[3 * i + 1]);
+                                ll_word_load(src + D + 1, v[3 * i + 2], tg[3 * i + 2]);
+                            }
+                        }
+#pragma unroll
+                        for (int i = 0; i < 4; ++i)
+                            if (i < nb) ok = ok && tg[3 * i] == 1u && tg[3 * i + 1] == 1u && tg[3 * i + 2] == 1u;
+                        if (ok) break;
+                        if (t0 == 0) t0 = clock64();
+                        else if (clock64() - t0 > 8000000000LL) {
+                            printf("b200: split-KV merge timed out (block %d thread %d)\n", blockIdx.x, threadIdx.x);
+                            __trap();
+                        }
+                    }
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) {
+                        if (i < nb) {
+                            po[j0 + i] = __uint_as_float(v[3 * i]);
+                            pm[j0 + i] = __uint_as_float(v[3 * i + 1]);
+                            pl[j0 + i] = __uint_as_float(v[3 * i + 2]);
+                            ll_word_clear(wbase + (size_t)(j0 + i) * (D + 2) + d);
+                        }
+                    }
+                }
+                float gm = mm;
+                for (int j = 0; j < eff - 1; ++j) gm = fmaxf(gm, pm[j]);
+                float gl = 0.f, go = 0.f;
+                for (int j = 0; j < eff - 1; ++j) {
+                    const float cj = __expf(pm[j] - gm);
+                    gl += pl[j] * cj;
+                    go += po[j] * cj;
+                }
+                const float cs = __expf(mm - gm);
+                gl += ll * cs;
+                go += oo * cs;
+                p.out[(size_t)t * p.ldo + (g * GROUP + h) * D + d] = float_to_h16(go / gl, p.is_bf16);
+            }
         } else {
             float* dst = my_part + (size_t)h * splits * (D + 2);
             dst[d] = oo;
@@ -225,6 +295,17 @@ __device__ __forceinline__ void attn_decode_body(const AttnDecodeParams& p, int 
         }
     }
     if (eff == 1) return;
+    if (p.ll) {
+        if (s != eff - 1) return;
+        sync();   // every thread of the merging split has read the shared (m, l) words: clear them
+        for (int idx = tid; idx < GROUP * (eff - 1); idx += kAttnThreads) {
+            const int h = idx / (eff - 1), j = idx % (eff - 1);
+            uint2* w = reinterpret_cast<uint2*>(p.ll) + ((size_t)(t * p.n_heads + g * GROUP + h) * splits + j) * (D + 2);
+            ll_word_clear(w + D);
+            ll_word_clear(w + D + 1);
+        }
+        return;
+    }
     sync();   // orders every thread's partial stores before thread 0's release below
     if (tid == 0) {
         int old;

@@ -507,6 +507,8 @@ extern "C" int b200_decode_mega_build(const b200_mega_op* ops, int32_t n_ops, vo
             p.norm_b = static_cast<const uint16_t*>(a.norm_b);
             p.scratch = a.scratch;
             p.counters = a.counters;
+            p.ll_words = nullptr; p.ll_parts = 0;   // the persistent kernel keeps the ticket fix-up
+            p.pf_ptr[0] = p.pf_ptr[1] = nullptr; p.pf_bytes[0] = p.pf_bytes[1] = 0;
             p.T = a.T; p.N = a.N; p.K = a.K;
             p.ldx = a.ldx; p.ldo = a.ldo; p.ldr = a.ldr;
             p.n_tiles = a.n_tiles; p.t_tiles = 1; p.kbpt = a.K / kBK;
@@ -537,6 +539,7 @@ extern "C" int b200_decode_mega_build(const b200_mega_op* ops, int32_t n_ops, vo
             p.inv_freq = a.inv_freq;
             p.scratch = a.scratch;
             p.counters = a.counters;
+            p.ll = nullptr;   // the persistent kernel keeps the ticket merge
             p.T = a.T; p.n_heads = a.n_heads; p.n_kv = a.n_kv_heads; p.s_max = a.s_max;
             p.splits = a.splits > 0 ? a.splits : 1;
             p.ldqkv = a.ldqkv; p.ldo = a.ldo;

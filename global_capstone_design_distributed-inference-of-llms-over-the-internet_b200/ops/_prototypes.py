@@ -14,7 +14,7 @@ class AttnDecodeArgs(C.Structure):
         ("counters", vp),
         ("T", i32), ("n_heads", i32), ("n_kv_heads", i32), ("head_dim", i32), ("s_max", i32),
         ("splits", i32), ("ldqkv", i32), ("ldo", i32),
-        ("scale", f32), ("dtype", i32), ("pdl", i32),
+        ("scale", f32), ("dtype", i32), ("pdl", i32), ("ll_scratch", vp),
     ]
 
 

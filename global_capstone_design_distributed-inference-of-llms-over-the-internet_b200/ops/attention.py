@@ -2,6 +2,7 @@
 from __future__ import annotations
 
 import ctypes
+import os
 from typing import Optional
 
 import torch
@@ -35,6 +36,9 @@ class DecodeAttnWorkspace:
         nbytes = L.b200_attn_decode_scratch_bytes(max_tokens, n_heads, head_dim, splits)
         self.scratch = torch.empty(max(nbytes // 4, 1), dtype=torch.float32, device=device)
         self.counters = torch.zeros(max_tokens * n_kv_heads, dtype=torch.int32, device=device)
+        # (value, tag) words of the ticket-free split merge; B200_ATTN_LL_MERGE=0 falls back to the ticket path
+        self.ll = (torch.zeros(max(nbytes // 4, 1), dtype=torch.int64, device=device)
+                   if os.environ.get("B200_ATTN_LL_MERGE", "1") != "0" else None)
         self.splits = splits
         self.max_tokens = max_tokens
 
@@ -55,6 +59,7 @@ def fill_decode_args(qkv, out, kv_ptrs, pos, inv_freq, ws, n_heads, n_kv_heads, 
     a.kv_ptrs, a.pos = kv_ptrs.data_ptr(), pos.data_ptr()
     a.inv_freq = inv_freq.data_ptr() if inv_freq is not None else None
     a.scratch, a.counters = ws.scratch.data_ptr(), ws.counters.data_ptr()
+    a.ll_scratch = ws.ll.data_ptr() if getattr(ws, "ll", None) is not None else None
     a.T, a.n_heads, a.n_kv_heads, a.head_dim, a.s_max = T, n_heads, n_kv_heads, head_dim, s_max
     a.splits, a.ldqkv, a.ldo = ws.splits, qkv.stride(0), out.stride(0)
     a.scale = scale if scale is not None else head_dim ** -0.5

@@ -172,6 +172,11 @@ typedef struct b200_attn_decode_args {
     int32_t T, n_heads, n_kv_heads, head_dim, s_max, splits, ldqkv, ldo;
     float scale;            /* 1/sqrt(d) */
     int32_t dtype, pdl;
+    /* Optional: 2 * b200_attn_decode_scratch_bytes() bytes, zeroed ONCE by the caller, then owned by the library
+     * (one per stream).  The KV splits of a head then publish their partial (o, m, l) as (value, tag) 8-byte
+     * words and the last split polls, merges and clears them: no fence / atomic ticket in the merge.  Same
+     * arithmetic and order as the ticket path.  NULL = ticket path (scratch + counters). */
+    void* ll_scratch;
 } b200_attn_decode_args;
 int b200_attn_decode(const b200_attn_decode_args* args, void* stream);
 int64_t b200_attn_decode_scratch_bytes(int32_t T, int32_t n_heads, int32_t head_dim, int32_t splits);
