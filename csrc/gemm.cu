@@ -230,6 +230,7 @@ gemm_streamk_kernel(const GemmParams p) {
         int sb = 0;
         bool rms_ready = (FP8 != 0);   // fp8: the 1/rms is already folded into stat_rstd
         const int tp_seq = (p.tp_world > 1) ? (__ldcv(p.tp_seq) + 1) : 0;
+        bool tp_bumped = false;
         constexpr int ll_seq = 1;   // tag of a published word; the consumer clears the word again (tag 0) once it has read it
         long long q = q_begin;
         while (q < q_end) {
@@ -361,6 +362,18 @@ gemm_streamk_kernel(const GemmParams p) {
                 }
             }
 
+            // ---- tensor parallel: move the launch number on for the NEXT launch.  Done here, while the tensor core
+            // still works on the staged k-blocks, instead of at CTA exit (a fence + atomic round trip there delays
+            // the end of the kernel by 1.5-3 us).  Every thread of this CTA read the number before the barrier, the
+            // CTA's add comes after it, and only the last add of the grid writes - so no CTA can see the new value.
+            if (p.tp_world > 1 && !tp_bumped) {
+                tp_bumped = true;
+                named_bar_sync(1, kEpiThreads);
+                if (e == 0 && atomicAdd(p.tp_exit, 1) == (int)gridDim.x - 1) {
+                    *p.tp_exit = 0;
+                    *p.tp_seq = tp_seq;
+                }
+            }
             // ---- deferred RMSNorm statistics: computed once, while the tensor core chews on the staged k-blocks
             if (p.norm_mode == B200_NORM_RMS && !rms_ready) {
                 rms_stats_128(p, min(BN, p.T), e, stat_red, stat_rstd);
@@ -539,19 +552,18 @@ gemm_streamk_kernel(const GemmParams p) {
             q += kb1 - kb0;
             ++part;
         }
+        if (p.tp_world > 1 && !tp_bumped) {   // a CTA without work still counts
+            named_bar_sync(1, kEpiThreads);
+            if (e == 0 && atomicAdd(p.tp_exit, 1) == (int)gridDim.x - 1) {
+                *p.tp_exit = 0;
+                *p.tp_seq = tp_seq;
+            }
+        }
     }
 
     tc_fence_before();
     __syncthreads();
     if (warp == 1) tmem_dealloc<Cfg::kTmemCols>(tmem_base);
-    if (p.tp_world > 1 && threadIdx.x == 0) {
-        __threadfence();
-        if (atomicAdd(p.tp_exit, 1) == (int)gridDim.x - 1) {   // last CTA out: this launch is complete on this rank
-            *p.tp_exit = 0;
-            *p.tp_seq = *p.tp_seq + 1;
-            __threadfence();
-        }
-    }
 }
 
 template <int BN, int DUAL, int FP8 = 0>
