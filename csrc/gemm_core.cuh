@@ -196,22 +196,38 @@ __device__ __forceinline__ void tp_allreduce_tile(const GemmParams& p, int tile,
 // Per-token 1/rms for the deferred RMSNorm: all 128 worker threads cooperate, result in rstd[0..T).
 // `red` is 4*32 floats of shared scratch; callers separate uses with their own barriers.
 __device__ __forceinline__ void rms_stats_128(const GemmParams& p, int T, int e, float* red, float* rstd) {
+    // All 128 threads on one token after the other, two tokens in flight (their loads are independent).  The
+    // reduction tree of a token is the same for every T, so a token's 1/rms does not depend on how many sessions
+    // share the step.  Measured alternatives: eight tokens in flight spills registers into the GEMM main loops
+    // (T=1 chain 77 -> 87 us/layer); one warp per token needs 4+ dependent L2 round trips per token (77 -> 81.5).
     const int warp = e >> 5, lane = e & 31;
-    for (int t = 0; t < T; ++t) {
-        float s2 = 0.f;
-        const uint16_t* xr = p.x + (size_t)t * p.ldx;
+    for (int t0 = 0; t0 < T; t0 += 2) {
+        float sa = 0.f, sb = 0.f;
+        const bool two = t0 + 1 < T;
+        const uint16_t* xa = p.x + (size_t)t0 * p.ldx;
+        const uint16_t* xb = xa + (two ? p.ldx : 0);
         for (int c = e; c < p.K / 8; c += 128) {
-            const uint4 v = ld_cg_v4(xr + c * 8);
-            const uint32_t w4[4] = {v.x, v.y, v.z, v.w};
+            const uint4 va = ld_cg_v4(xa + c * 8);
+            uint4 vb = make_uint4(0, 0, 0, 0);
+            if (two) vb = ld_cg_v4(xb + c * 8);
+            const uint32_t wa[4] = {va.x, va.y, va.z, va.w};
+            const uint32_t wb[4] = {vb.x, vb.y, vb.z, vb.w};
 #pragma unroll
             for (int i = 0; i < 4; ++i) {
-                const float a = h16_to_float((uint16_t)(w4[i] & 0xffff), p.is_bf16);
-                const float b = h16_to_float((uint16_t)(w4[i] >> 16), p.is_bf16);
-                s2 += a * a + b * b;
+                const float a0 = h16_to_float((uint16_t)(wa[i] & 0xffff), p.is_bf16);
+                const float a1 = h16_to_float((uint16_t)(wa[i] >> 16), p.is_bf16);
+                sa += a0 * a0 + a1 * a1;
+                const float b0 = h16_to_float((uint16_t)(wb[i] & 0xffff), p.is_bf16);
+                const float b1 = h16_to_float((uint16_t)(wb[i] >> 16), p.is_bf16);
+                sb += b0 * b0 + b1 * b1;
             }
         }
-        s2 = warp_sum(s2);
-        if (lane == 0) red[warp * 32 + t] = s2;
+        sa = warp_sum(sa);
+        sb = warp_sum(sb);
+        if (lane == 0) {
+            red[warp * 32 + t0] = sa;
+            if (two) red[warp * 32 + t0 + 1] = sb;
+        }
     }
     named_bar_sync(1, 128);
     if (e < T) {
