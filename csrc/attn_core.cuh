@@ -54,18 +54,29 @@ __device__ __forceinline__ uint4 pack8(const float (&f)[8], int is_bf16) {
 
 // Rotates one head vector held as (lo = dims [c, c+8), hi = dims [c+D/2, c+D/2+8)).
 // HF convention: out = x*cos + rotate_half(x)*sin with cos/sin rounded to the model dtype.
-__device__ __forceinline__ void rope8(float (&lo)[8], float (&hi)[8], int c, int pos, const float* inv_freq,
-                                      int is_bf16) {
+__device__ __forceinline__ void rope_sincos8(int c, int pos, const float* inv_freq, int is_bf16, float (&sn)[8],
+                                             float (&cs)[8]) {
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
-        float sn, cs;
-        sincosf((float)pos * inv_freq[c + i], &sn, &cs);
-        cs = h16_to_float(float_to_h16(cs, is_bf16), is_bf16);
-        sn = h16_to_float(float_to_h16(sn, is_bf16), is_bf16);
-        const float a = lo[i], b = hi[i];
-        lo[i] = a * cs - b * sn;
-        hi[i] = b * cs + a * sn;
+        float s_, c_;
+        sincosf((float)pos * inv_freq[c + i], &s_, &c_);
+        cs[i] = h16_to_float(float_to_h16(c_, is_bf16), is_bf16);
+        sn[i] = h16_to_float(float_to_h16(s_, is_bf16), is_bf16);
     }
+}
+__device__ __forceinline__ void rope_apply8(float (&lo)[8], float (&hi)[8], const float (&sn)[8], const float (&cs)[8]) {
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        const float a = lo[i], b = hi[i];
+        lo[i] = a * cs[i] - b * sn[i];
+        hi[i] = b * cs[i] + a * sn[i];
+    }
+}
+__device__ __forceinline__ void rope8(float (&lo)[8], float (&hi)[8], int c, int pos, const float* inv_freq,
+                                      int is_bf16) {
+    float sn[8], cs[8];
+    rope_sincos8(c, pos, inv_freq, is_bf16, sn, cs);
+    rope_apply8(lo, hi, sn, cs);
 }
 
 // One CTA = (token t, kv head g, split s).  LPR = D/8 lanes cooperate on one KV row.
@@ -79,9 +90,13 @@ struct AttnDecodeSmem {
 
 // One work item = (token t, kv head g, split s), executed by kAttnThreads threads that share
 // `sm` and synchronise through `sync()` (a __syncthreads() or a named barrier).
-template <int D, int GROUP, typename Sync>
+// `before_qkv()` runs right before the first access to p.qkv (the only input the previous kernel produces):
+// the stand-alone kernel waits for the previous grid there, so everything above it - positions, cache
+// pointers, the RoPE sines and cosines, an L2 prefetch of this split's cache rows - overlaps that grid's tail.
+struct AttnNoHook { __device__ __forceinline__ void operator()() const {} };
+template <int D, int GROUP, typename Sync, typename Hook = AttnNoHook>
 __device__ __forceinline__ void attn_decode_body(const AttnDecodeParams& p, int t, int g, int s, int tid,
-                                                 AttnDecodeSmem<D, GROUP>& sm, Sync sync) {
+                                                 AttnDecodeSmem<D, GROUP>& sm, Sync sync, Hook before_qkv = Hook()) {
     constexpr int LPR = D / 8;          // lanes per row: 16 (D=128) or 8 (D=64)
     constexpr int RPW = 32 / LPR;       // rows per warp per step: 2 or 4
     constexpr int NW = kAttnThreads / 32;
@@ -112,6 +127,17 @@ __device__ __forceinline__ void attn_decode_body(const AttnDecodeParams& p, int 
     // ---- q (RoPE'd, pre-scaled) -> smem; new k/v -> cache (by the split that owns `pos`)
     // D/2/8 threads per head vector, each owning dims [c, c+8) and [c+D/2, c+D/2+8).
     constexpr int TPH = D / 16;
+    static_assert((GROUP + 1) * TPH <= kAttnThreads, "one RoPE item per thread");
+    float rs[8], rc[8];
+    if (p.inv_freq && tid < (GROUP + 1) * TPH) rope_sincos8((tid % TPH) * 8, pos, p.inv_freq, p.is_bf16, rs, rc);
+    if (tid == 0) {   // cache rows of earlier tokens do not depend on the previous kernel: start pulling them into L2
+        const int n_old = min(r_end, pos) - r_begin;
+        if (n_old > 0) {
+            bulk_prefetch_l2(kbase + (size_t)r_begin * D, (uint32_t)(n_old * D * 2));
+            bulk_prefetch_l2(vbase + (size_t)r_begin * D, (uint32_t)(n_old * D * 2));
+        }
+    }
+    before_qkv();
     for (int item = tid; item < (GROUP + 1) * TPH; item += kAttnThreads) {
         const int h = item / TPH, c = (item % TPH) * 8;
         const bool is_k = (h == GROUP);
@@ -120,7 +146,7 @@ __device__ __forceinline__ void attn_decode_body(const AttnDecodeParams& p, int 
         float lo[8], hi[8];
         unpack8(ld_cg_v4(src + c), lo, p.is_bf16);
         unpack8(ld_cg_v4(src + c + D / 2), hi, p.is_bf16);
-        if (p.inv_freq) rope8(lo, hi, c, pos, p.inv_freq, p.is_bf16);
+        if (p.inv_freq) rope_apply8(lo, hi, rs, rc);
         if (is_k) {
             *reinterpret_cast<uint4*>(kbase + (size_t)pos * D + c) = pack8(lo, p.is_bf16);
             *reinterpret_cast<uint4*>(kbase + (size_t)pos * D + c + D / 2) = pack8(hi, p.is_bf16);
@@ -339,9 +365,8 @@ __global__ void __launch_bounds__(kAttnThreads) attn_decode_kernel(const AttnDec
     const int s = bid % p.splits; bid /= p.splits;
     const int g = bid % p.n_kv;
     const int t = bid / p.n_kv;
-    pdl_wait_prior_grid();
     pdl_launch_dependents();
-    attn_decode_body<D, GROUP>(p, t, g, s, (int)threadIdx.x, sm, [] { __syncthreads(); });
+    attn_decode_body<D, GROUP>(p, t, g, s, (int)threadIdx.x, sm, [] { __syncthreads(); }, [] { pdl_wait_prior_grid(); });
 }
 
 }  // namespace b200
