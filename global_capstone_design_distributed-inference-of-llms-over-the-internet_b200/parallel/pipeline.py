@@ -105,6 +105,13 @@ class PipelineEngine:
         # Hidden states flow on the default group, token ids return on a second communicator:
         # with one communicator the ring (last -> first) closes a cycle of in-order NCCL ops.
         self.tok_group = dist.new_group() if self.world > 1 else None
+        # Links alternate between two more communicators: a middle stage then receives (link r-1) and sends
+        # (link r) on different NCCL streams - on one process group unbatched p2p ops are serialised with each
+        # other.  Receives are posted from an otherwise idle side stream, so the next micro-batch's receive does
+        # not queue behind the compute that is already enqueued on the main stream.
+        self.link_groups = [dist.new_group(), dist.new_group()] if self.world > 1 else [None, None]
+        self._recv_stream = torch.cuda.Stream(device=self.device) if (self.device.type == "cuda" and self.world > 1) else None
+        self._slot_done = [None] * max_sessions
         self._send_work = [None] * max_sessions
         self._tok_work = [None] * max_sessions
         self._tok_host = torch.zeros(max_sessions, dtype=torch.int64)
@@ -129,6 +136,26 @@ class PipelineEngine:
     def _g(self, stage: int) -> int:
         """Global rank of this rank's counterpart in pipeline stage ``stage``."""
         return stage * self.tp + self.tp_rank
+
+    def _link(self, src_stage: int):
+        """Communicator of the link src_stage -> src_stage + 1."""
+        return self.link_groups[src_stage % 2]
+
+    def _post_recv(self, buf: torch.Tensor, slot: int):
+        """Asynchronous receive of a micro-batch's hidden state from the previous stage."""
+        src = self.rank - 1
+        if self._recv_stream is None:
+            return dist.irecv(buf, self._g(src), group=self._link(src))
+        if self._slot_done[slot] is not None:      # the previous user of this staging slot has consumed it
+            self._recv_stream.wait_event(self._slot_done[slot])
+        with torch.cuda.stream(self._recv_stream):
+            return dist.irecv(buf, self._g(src), group=self._link(src))
+
+    def _mark_consumed(self, slot: int) -> None:
+        if self._recv_stream is not None:
+            ev = self._slot_done[slot] or torch.cuda.Event()
+            ev.record()
+            self._slot_done[slot] = ev
 
     def _send(self, t: torch.Tensor, dst: int, group=None) -> None:
         dist.send(t, self._g(dst), group=group)
@@ -244,7 +271,11 @@ class PipelineEngine:
             # travel together as one [group, H] activation (one batched kernel sequence per stage).
             last = self.world - 1
             g = max(1, int(group))
-            for j0 in range(0, S, g):
+            starts = list(range(0, S, g))
+            pending = None
+            if not self.is_first and starts:
+                pending = self._post_recv(self._hid[0, starts[0]:min(S, starts[0] + g)], starts[0])
+            for bi, j0 in enumerate(starts):
                 j1 = min(S, j0 + g)
                 kv = [self.sessions[si] for si in sess[j0:j1]]
                 slot = j0
@@ -254,19 +285,25 @@ class PipelineEngine:
                     out = self._stage_decode(kv, self._tok[j0:j1], None)
                     self._wait(self._send_work[slot])
                     self._hid[1, j0:j1].copy_(out[: j1 - j0])
-                    self._send_work[slot] = dist.isend(self._hid[1, j0:j1], self._g(1))
+                    self._send_work[slot] = dist.isend(self._hid[1, j0:j1], self._g(1), group=self._link(0))
                     self._tok_work[slot] = dist.irecv(self._tok[j0:j1], self._g(last), group=self.tok_group)
                 else:
                     h = self._hid[0, j0:j1]
-                    dist.irecv(h, self._g(self.rank - 1)).wait()
+                    work, pending = pending, None
+                    if bi + 1 < len(starts):                          # the next micro-batch's receive overlaps this one's compute
+                        n0 = starts[bi + 1]
+                        pending = self._post_recv(self._hid[0, n0:min(S, n0 + g)], n0)
+                    work.wait()
                     out = self._stage_decode(kv, None, h)
+                    self._mark_consumed(slot)
                     self._wait(self._send_work[slot])
                     if self.is_last:
                         self._tok_send[j0:j1].copy_(out[1].reshape(-1)[: j1 - j0])
                         self._send_work[slot] = dist.isend(self._tok_send[j0:j1], self._g(0), group=self.tok_group)
                     else:
                         self._hid[1, j0:j1].copy_(out[: j1 - j0])
-                        self._send_work[slot] = dist.isend(self._hid[1, j0:j1], self._g(self.rank + 1))
+                        self._send_work[slot] = dist.isend(self._hid[1, j0:j1], self._g(self.rank + 1),
+                                                           group=self._link(self.rank))
             if self.is_first and (to_host or tokens is not None):
                 for j in range(S):
                     self._wait(self._tok_work[j])
@@ -293,6 +330,9 @@ class PipelineEngine:
         last = self.world - 1
         out = [None] * S
         have_prev = getattr(self, "_streaming_live", False)
+        pending = None
+        if not self.is_first and S:
+            pending = self._post_recv(self._hid[0, 0:1], 0)
         for j, si in enumerate(sess):
             kv = [self.sessions[si]]
             if self.is_first:
@@ -309,19 +349,24 @@ class PipelineEngine:
                 o = self._stage_decode(kv, self._tok[j:j + 1], None)
                 self._wait(self._send_work[j])
                 self._hid[1, j:j + 1].copy_(o[:1])
-                self._send_work[j] = dist.isend(self._hid[1, j:j + 1], self._g(1))
+                self._send_work[j] = dist.isend(self._hid[1, j:j + 1], self._g(1), group=self._link(0))
                 self._tok_work[j] = dist.irecv(self._tok[j:j + 1], self._g(last), group=self.tok_group)
             else:
                 h = self._hid[0, j:j + 1]
-                dist.irecv(h, self._g(self.rank - 1)).wait()
+                work, pending = pending, None
+                if j + 1 < S:
+                    pending = self._post_recv(self._hid[0, j + 1:j + 2], j + 1)
+                work.wait()
                 o = self._stage_decode(kv, None, h)
+                self._mark_consumed(j)
                 self._wait(self._send_work[j])
                 if self.is_last:
                     self._tok_send[j:j + 1].copy_(o[1].reshape(-1)[:1])
                     self._send_work[j] = dist.isend(self._tok_send[j:j + 1], self._g(0), group=self.tok_group)
                 else:
                     self._hid[1, j:j + 1].copy_(o[:1])
-                    self._send_work[j] = dist.isend(self._hid[1, j:j + 1], self._g(self.rank + 1))
+                    self._send_work[j] = dist.isend(self._hid[1, j:j + 1], self._g(self.rank + 1),
+                                                    group=self._link(self.rank))
         self._streaming_live = True
         return out if (self.is_first and have_prev) else None
 
