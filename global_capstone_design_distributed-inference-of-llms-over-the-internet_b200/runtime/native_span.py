@@ -39,12 +39,13 @@ MAX_DECODE_BATCH = 32
 
 
 def _l2_prefetch_default():
-    """B200_L2_PREFETCH_MB="a,b,c,d" (MiB, see _decode_layers) switches the L2 warm-up on.
+    """B200_L2_PREFETCH_MB="a,b,c,d" (MiB, see _decode_layers); "0" switches the L2 warm-up off.
 
-    Off by default: measured on Llama-2-7B decode it changes nothing (296 tok/s off, 298 with 24,16,24,24,
-    282 with 64,48,64,64) - the decode GEMM is bound by how fast the SMs ingest weights, which an L2 hit does
-    not speed up, not by idle HBM time."""
-    v = os.environ.get("B200_L2_PREFETCH_MB", "0")
+    Measured on Llama-2-7B decode (1xB200, after the ticket-free fix-up): off 345.9 tok/s, "24,16,16,16" 350.4 /
+    351.6, "16,8,8,8" 348.8, "32,24,32,32" 347.2, "48,0,0,0" 344.3, "64,48,64,64" slower than off.  Small ranges
+    fill the HBM idle time around the kernel boundaries; large ones compete with the running kernel's own
+    stream.  (Before the fix-up change the same hint was neutral.)"""
+    v = os.environ.get("B200_L2_PREFETCH_MB", "24,16,16,16")
     if v.strip() in ("0", "", "off"):
         return None
     mb = [int(t) for t in v.split(",")]
