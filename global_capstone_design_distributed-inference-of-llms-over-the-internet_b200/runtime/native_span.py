@@ -131,7 +131,7 @@ class NativeSpan:
             self.act = torch.zeros(Tm, (c.intermediate + 63) // 64 * 64, dtype=dtype, device=self.device)
             self.ids_in = torch.zeros(Tm, dtype=torch.int64, device=self.device)
             self.ws = G.GemmWorkspace.create(self.device, Tm)
-            self.splits = attn_splits or max(1, min(16, kv_capacity // 256))
+            self.splits = attn_splits or int(os.environ.get("B200_ATTN_SPLITS", "0")) or max(1, min(16, kv_capacity // 64))
             self.attn_ws = A.DecodeAttnWorkspace(self.device, self.max_batch, c.n_heads, c.n_kv_heads, c.head_dim,
                                                  self.splits)
             self.kv_ptrs = torch.zeros(max(nl, 1), self.max_batch, 2, dtype=torch.int64, device=self.device)
