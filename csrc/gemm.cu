@@ -15,7 +15,10 @@
 
 namespace b200 {
 
-template <int BN, int DUAL, int FP8>
+// WIDE = 1: the ticket-free fix-up for 5..16 tokens (every CTA of a tile publishes its whole partial and then
+// reduces its own share of the tile's elements).  A separate instantiation so that its registers never weigh on
+// the batch-1 kernel.
+template <int BN, int DUAL, int FP8, int WIDE = 0>
 __global__ void __launch_bounds__(kThreads, GemmCfg<BN, DUAL>::kMinBlocks)
 gemm_streamk_kernel(const GemmParams p) {
     using Cfg = GemmCfg<BN, DUAL>;
@@ -410,6 +413,17 @@ gemm_streamk_kernel(const GemmParams p) {
                     if (p.tp_world > 1) tp_allreduce_tile(p, n_tile, row, ncol, e, tp_seq, vg);
                     if (!(p.tp_world > 1 && p.tp_defer))
                     epilogue_store_chunk<BN, DUAL>(p, n_tile, t_tile, row, c, vg, vu, tok_scale);
+                } else if (WIDE && p.ll_words) {
+                    // ---- wide ticket-free fix-up, part 1: publish the whole partial (reduced below, after the drain)
+                    constexpr int kLLStrideW = APER * 16 * kTileM;        // words per CTA
+                    uint2* mine = reinterpret_cast<uint2*>(p.ll_words) + (size_t)cta * kLLStrideW + row;
+#pragma unroll
+                    for (int j = 0; j < 16; ++j) {
+                        if (j < ncol) {
+                            ll_store(mine + j * kTileM, vg[j], 1);
+                            if (DUAL) ll_store(mine + (16 + j) * kTileM, vu[j], 1);
+                        }
+                    }
                 } else if (p.ll_words) {
                     // ---- ticket-free fix-up (host guarantees T <= 4, one part per CTA, ll_parts CTAs per tile)
                     constexpr int kLLStride = APER * 4 * kTileM;          // words per CTA
@@ -502,6 +516,60 @@ gemm_streamk_kernel(const GemmParams p) {
             __syncwarp();
             if (lane == 0) mbar_arrive(acc_empty);
 
+            if (WIDE && !full_tile && p.ll_words) {
+                // ---- wide fix-up, part 2: this CTA reduces its share of the tile's 128 x T elements (column-major
+                // index j * 128 + row): polls the P words of an element together, adds them in CTA order (the order
+                // of every other path), clears them, applies the epilogue for that single element.
+                constexpr int kLLStrideW = APER * 16 * kTileM;
+                const int P = p.ll_parts;
+                const int first = u * P;
+                const int E = kTileM * t_live;
+                const int per = (E + P - 1) / P;
+                const int e_lo = (cta - first) * per, e_hi = min(E, e_lo + per);
+                uint2* base = reinterpret_cast<uint2*>(p.ll_words) + (size_t)first * kLLStrideW;
+                for (int idx = e_lo + e; idx < e_hi; idx += kEpiThreads) {
+                    const int j = idx >> 7, r = idx & (kTileM - 1);
+                    uint2* w0 = base + j * kTileM + r;
+                    uint32_t vgw[9], tgw[9], vuw[9], tuw[9];
+                    long long t0 = 0;
+                    for (;;) {
+                        bool ok = true;
+#pragma unroll
+                        for (int c = 0; c < 9; ++c) {
+                            if (c < P) {
+                                asm volatile("ld.relaxed.gpu.global.v2.u32 {%0, %1}, [%2];\n"
+                                             : "=r"(vgw[c]), "=r"(tgw[c]) : "l"(w0 + (size_t)c * kLLStrideW) : "memory");
+                                if (DUAL)
+                                    asm volatile("ld.relaxed.gpu.global.v2.u32 {%0, %1}, [%2];\n"
+                                                 : "=r"(vuw[c]), "=r"(tuw[c])
+                                                 : "l"(w0 + (size_t)c * kLLStrideW + 16 * kTileM) : "memory");
+                            }
+                        }
+#pragma unroll
+                        for (int c = 0; c < 9; ++c)
+                            if (c < P) ok = ok && tgw[c] == 1u && (!DUAL || tuw[c] == 1u);
+                        if (ok) break;
+                        if (t0 == 0) t0 = clock64();
+                        else if (clock64() - t0 > 8000000000LL) {
+                            printf("b200: stream-K wide exchange timed out (block %d thread %d)\n", blockIdx.x, threadIdx.x);
+                            __trap();
+                        }
+                    }
+                    float sg = 0.f, su = 0.f;
+#pragma unroll
+                    for (int c = 0; c < 9; ++c) {
+                        if (c < P) {
+                            sg += __uint_as_float(vgw[c]);
+                            asm volatile("st.relaxed.gpu.global.v2.u32 [%0], {%1, %1};\n" ::"l"(w0 + (size_t)c * kLLStrideW), "r"(0) : "memory");
+                            if (DUAL) {
+                                su += __uint_as_float(vuw[c]);
+                                asm volatile("st.relaxed.gpu.global.v2.u32 [%0], {%1, %1};\n" ::"l"(w0 + (size_t)c * kLLStrideW + 16 * kTileM), "r"(0) : "memory");
+                            }
+                        }
+                    }
+                    epilogue_store_scalar<DUAL>(p, n_tile * kTileM + r, j, sg, su, tok_scale ? tok_scale[j] : 1.0f);
+                }
+            }
             if (!full_tile && !p.ll_words) {
                 // Publish the partial with ONE acq_rel ticket: the CTA barrier orders every thread's
                 // partial stores before thread 0's release, and thread 0's acquire before every
@@ -566,7 +634,7 @@ gemm_streamk_kernel(const GemmParams p) {
     if (warp == 1) tmem_dealloc<Cfg::kTmemCols>(tmem_base);
 }
 
-template <int BN, int DUAL, int FP8 = 0>
+template <int BN, int DUAL, int FP8 = 0, int WIDE = 0>
 static int launch_gemm(const GemmParams& p, int grid, bool pdl, cudaStream_t stream) {
     using Cfg = GemmCfg<BN, DUAL>;
     static_assert(Cfg::kSmemBytes <= 227 * 1024, "shared memory budget exceeded");
@@ -574,12 +642,12 @@ static int launch_gemm(const GemmParams& p, int grid, bool pdl, cudaStream_t str
     int dev = 0;
     B200_CUDA_CHECK(cudaGetDevice(&dev));
     if (configured_dev != dev) {
-        B200_CUDA_CHECK(cudaFuncSetAttribute(gemm_streamk_kernel<BN, DUAL, FP8>,
+        B200_CUDA_CHECK(cudaFuncSetAttribute(gemm_streamk_kernel<BN, DUAL, FP8, WIDE>,
                                              cudaFuncAttributeMaxDynamicSharedMemorySize,
                                              (int)Cfg::kSmemBytes));
         configured_dev = dev;
     }
-    B200_CUDA_CHECK(launch(gemm_streamk_kernel<BN, DUAL, FP8>, dim3(grid), dim3(kThreads), Cfg::kSmemBytes,
+    B200_CUDA_CHECK(launch(gemm_streamk_kernel<BN, DUAL, FP8, WIDE>, dim3(grid), dim3(kThreads), Cfg::kSmemBytes,
                            stream, pdl, p));
     return B200_OK;
 }
@@ -601,10 +669,10 @@ extern "C" int32_t b200_gemm_token_tile(int32_t T, int32_t dual) {
     return pick_token_tile(T);
 }
 
-// ll_buf layout: [kLLHeaderBytes reserved][kLLMaxCtas x 8 KiB of (value, tag) words, all zero between launches]
+// ll_buf layout: [kLLHeaderBytes reserved][kLLMaxCtas x 32 KiB of (value, tag) words, all zero between launches]
 constexpr int kLLMaxCtas = 512;
 constexpr int kLLHeaderBytes = 256;
-extern "C" int64_t b200_gemm_ll_bytes(void) { return (int64_t)kLLHeaderBytes + (int64_t)kLLMaxCtas * 2 * 4 * kTileM * 8; }
+extern "C" int64_t b200_gemm_ll_bytes(void) { return (int64_t)kLLHeaderBytes + (int64_t)kLLMaxCtas * 2 * 16 * kTileM * 8; }
 
 extern "C" int64_t b200_gemm_scratch_bytes(int32_t max_tokens) {
     const int bn = pick_token_tile(max_tokens);
@@ -733,9 +801,12 @@ static int gemm_impl(const b200_gemm_args* a, const b200_tp_args* tp, void* stre
     if ((long long)grid > p.Q) grid = (int)p.Q;
     // Ticket-free fix-up: only when every tile is shared by the same whole number of CTAs with one part each.
     p.ll_words = nullptr; p.ll_parts = 0;
-    if (a->ll_buf && bn == 16 && t_tiles == 1 && a->T <= 4 && grid % a->n_tiles == 0 && grid <= kLLMaxCtas) {
+    // T <= 4: the tile's last CTA collects; 5..16 tokens (no tensor parallelism, 16-bit weights): every CTA reduces a share.
+    static const int wide_min = [] { const char* e = getenv("B200_LL_WIDE_MIN"); return e ? atoi(e) : 5; }();
+    const bool ll_wide = a->T >= wide_min && a->T <= 16 && !tp && !gather && !a->fp8;
+    if (a->ll_buf && bn == 16 && t_tiles == 1 && (a->T <= 4 || ll_wide) && grid % a->n_tiles == 0 && grid <= kLLMaxCtas) {
         const int parts = grid / a->n_tiles;
-        if (parts >= 2 && p.kbpt >= parts) {
+        if (parts >= 2 && p.kbpt >= parts && (!ll_wide || parts <= 9)) {
             p.ll_words = reinterpret_cast<unsigned long long*>(static_cast<uint8_t*>(a->ll_buf) + kLLHeaderBytes);
             p.ll_parts = parts;
         }
@@ -746,6 +817,8 @@ static int gemm_impl(const b200_gemm_args* a, const b200_tp_args* tp, void* stre
         if (bn == 16) return a->dual ? launch_gemm<16, 1, 1>(p, grid, pdl, stream) : launch_gemm<16, 0, 1>(p, grid, pdl, stream);
         return a->dual ? launch_gemm<32, 1, 1>(p, grid, pdl, stream) : launch_gemm<32, 0, 1>(p, grid, pdl, stream);
     }
+    if (p.ll_words && ll_wide)
+        return a->dual ? launch_gemm<16, 1, 0, 1>(p, grid, pdl, stream) : launch_gemm<16, 0, 0, 1>(p, grid, pdl, stream);
 #define B200_GEMM_CASE(BN_)                                                        \
     case BN_:                                                                      \
         return a->dual ? launch_gemm<BN_, 1>(p, grid, pdl, stream)                 \

@@ -379,4 +379,26 @@ __device__ __forceinline__ void epilogue_store_chunk(const GemmParams& p, int n_
     }
 }
 
+// The same epilogue for ONE element (output feature n, token t): used by the wide ticket-free fix-up, where a thread
+// finishes elements of rows it did not accumulate.  Expression order as in epilogue_store_chunk (bit-identical).
+template <int DUAL>
+__device__ __forceinline__ void epilogue_store_scalar(const GemmParams& p, int n, int t, float g_sum, float u_sum, float ts) {
+    if (n >= p.N || t >= p.T) return;
+    const float b = p.bias ? h16_to_float(p.bias[n], p.is_bf16) : 0.0f;
+    const float ws_g = p.w_scale ? p.w_scale[n] : 1.0f;
+    const float ws_u = (DUAL && p.w_scale) ? p.w_scale[(size_t)p.n_tiles * kTileM + n] : 1.0f;
+    float v = g_sum * ts * ws_g + b;
+    if (DUAL) {
+        const float g = round16(v, p.is_bf16);
+        const float u = round16(u_sum * ts * ws_u, p.is_bf16);
+        const float s = round16(g / (1.0f + __expf(-g)), p.is_bf16);
+        v = s * u;
+    } else if (p.epilogue == B200_EPI_GELU_TANH) {
+        v = gelu_tanh(round16(v, p.is_bf16));
+    }
+    if (p.residual) v = round16(v, p.is_bf16) + h16_to_float(__ldcg(p.residual + (size_t)t * p.ldr + n), p.is_bf16);
+    if (p.out_fp32) reinterpret_cast<float*>(p.out)[(size_t)t * p.ldo + n] = v;
+    else reinterpret_cast<uint16_t*>(p.out)[(size_t)t * p.ldo + n] = float_to_h16(v, p.is_bf16);
+}
+
 }  // namespace b200

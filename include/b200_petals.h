@@ -91,7 +91,8 @@ typedef struct b200_gemm_args {
      * aligned device memory that stays valid until the stream has passed this kernel. */
     const void* prefetch[2];
     int64_t prefetch_bytes[2];
-    /* Optional ticket-free fix-up for batch-1..4 decode (b200_gemm / b200_gemm_allreduce / b200_gemm_gather):
+    /* Optional ticket-free fix-up for decode sizes (b200_gemm with T <= 16; b200_gemm_allreduce / b200_gemm_gather and
+     * fp8 weights with T <= 4):
      * b200_gemm_ll_bytes() bytes of device memory, zeroed ONCE by the caller and then owned by the library
      * (one buffer per stream of GEMM launches; it may be shared by all GEMMs of that stream).  When every
      * output tile is split over the same whole number of CTAs, the CTAs publish their partial sums as
