@@ -508,6 +508,7 @@ extern "C" int b200_decode_mega_build(const b200_mega_op* ops, int32_t n_ops, vo
             p.scratch = a.scratch;
             p.counters = a.counters;
             p.ll_words = nullptr; p.ll_parts = 0;   // the persistent kernel keeps the ticket fix-up
+            p.rstd_in = nullptr;
             p.pf_ptr[0] = p.pf_ptr[1] = nullptr; p.pf_bytes[0] = p.pf_bytes[1] = 0;
             p.T = a.T; p.N = a.N; p.K = a.K;
             p.ldx = a.ldx; p.ldo = a.ldo; p.ldr = a.ldr;

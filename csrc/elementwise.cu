@@ -188,6 +188,45 @@ extern "C" int b200_embed(const void* ids, const void* pos, int32_t pos0, const 
     return B200_OK;
 }
 
+namespace b200 {
+// Per-token 1/rms with exactly the reduction tree of rms_stats_128 (gemm_core.cuh): 128 threads per token, thread e
+// sums chunks e, e+128, ..., warp sums, then the four warp sums in warp order.  One block per token.
+__global__ void __launch_bounds__(128) rms_rstd_kernel(const uint16_t* __restrict__ x, int ldx, int K, float eps, int is_bf16,
+                                                       float* __restrict__ rstd) {
+    __shared__ float red[4];
+    pdl_wait_prior_grid();
+    pdl_launch_dependents();
+    const int e = threadIdx.x, t = blockIdx.x;
+    const uint16_t* xr = x + (size_t)t * ldx;
+    float s2 = 0.f;
+    for (int c = e; c < K / 8; c += 128) {
+        const uint4 v = ld_cg_v4(xr + c * 8);
+        const uint32_t w4[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const float a = h16_to_float((uint16_t)(w4[i] & 0xffff), is_bf16);
+            const float b = h16_to_float((uint16_t)(w4[i] >> 16), is_bf16);
+            s2 += a * a + b * b;
+        }
+    }
+    s2 = warp_sum(s2);
+    if ((e & 31) == 0) red[e >> 5] = s2;
+    __syncthreads();
+    if (e == 0) rstd[t] = rsqrtf((red[0] + red[1] + red[2] + red[3]) / (float)K + eps);
+}
+}  // namespace b200
+
+// rstd[t] = 1 / sqrt(mean(x[t]^2) + eps): feeds b200_gemm_args.rstd so that a many-token decode step computes the
+// RMSNorm statistics once instead of once per CTA of the following GEMM.
+extern "C" int b200_rms_rstd(const void* x, float* rstd, int32_t T, int32_t K, int32_t ldx, float eps, int32_t dtype,
+                             int32_t pdl, void* stream_) {
+    if (!x || !rstd) return fail(B200_EINVAL, "b200_rms_rstd: null pointer argument");
+    if (T <= 0 || K <= 0 || K % 8 != 0) return fail(B200_EINVAL, "b200_rms_rstd: bad sizes T=%d K=%d", T, K);
+    B200_CUDA_CHECK(launch(b200::rms_rstd_kernel, dim3(T), dim3(128), 0, static_cast<cudaStream_t>(stream_), pdl != 0,
+                           static_cast<const uint16_t*>(x), ldx, K, eps, dtype == B200_BF16 ? 1 : 0, rstd));
+    return B200_OK;
+}
+
 extern "C" int b200_norm(const void* x, const void* w, const void* b, void* out, int32_t T, int32_t H, int32_t ldx,
                          int32_t ldo, float eps, int32_t layer_norm, int32_t dtype, int32_t pdl, void* stream_) {
     if (!x || !w || !out) return fail(B200_EINVAL, "b200_norm: null pointer argument");

@@ -378,6 +378,11 @@ gemm_streamk_kernel(const GemmParams p) {
                 }
             }
             // ---- deferred RMSNorm statistics: computed once, while the tensor core chews on the staged k-blocks
+            if (p.norm_mode == B200_NORM_RMS && !rms_ready && p.rstd_in) {
+                if (e < min(BN, p.T)) stat_rstd[e] = __ldcg(p.rstd_in + e);
+                named_bar_sync(1, kEpiThreads);
+                rms_ready = true;
+            }
             if (p.norm_mode == B200_NORM_RMS && !rms_ready) {
                 rms_stats_128(p, min(BN, p.T), e, stat_red, stat_rstd);
                 rms_ready = true;
@@ -801,6 +806,7 @@ static int gemm_impl(const b200_gemm_args* a, const b200_tp_args* tp, void* stre
     if ((long long)grid > p.Q) grid = (int)p.Q;
     // Ticket-free fix-up: only when every tile is shared by the same whole number of CTAs with one part each.
     p.ll_words = nullptr; p.ll_parts = 0;
+    p.rstd_in = (a->norm_mode == B200_NORM_RMS && !a->fp8 && t_tiles == 1) ? a->rstd : nullptr;
     // One token (and T <= 4 with tensor parallelism or fp8 weights): the tile's last CTA collects.  2..16 tokens: every CTA
     // reduces a share (measured per-layer GEMM chain, T=2: 82.9 -> 78.1 us, T=4: 93.7 -> 82.5, T=16: 138 -> 108; T=1 equal).
     static const int wide_min = [] { const char* e = getenv("B200_LL_WIDE_MIN"); return e ? atoi(e) : 2; }();

@@ -89,6 +89,7 @@ struct GemmParams {
     // polls for them and clears them again (no fence, no atomic, no counter) - see b200_gemm_args.ll_buf.
     unsigned long long* ll_words;
     int ll_parts;
+    const float* rstd_in;       // precomputed per-token 1/rms (b200_rms_rstd) or null
     const uint8_t* pf_ptr[2];   // L2 warm-up ranges for the kernels that follow (see b200_gemm_args.prefetch)
     long long pf_bytes[2];
     int debug;  // experiment switches (scripts/exp_*.py): 1 = no MMA issue, 2 = no B stage waits

@@ -50,6 +50,7 @@ PROTOTYPES = [
     ("b200_attn_prefill_tc", [vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, i32, f32, i32, i32, vp], C.c_int),
     ("b200_embed", [vp, vp, i32, vp, vp, vp, i32, i32, i32, i32, i32, i32, vp], C.c_int),
     ("b200_norm", [vp, vp, vp, vp, i32, i32, i32, i32, f32, i32, i32, i32, vp], C.c_int),
+    ("b200_rms_rstd", [vp, vp, i32, i32, i32, f32, i32, i32, vp], C.c_int),
     ("b200_argmax", [vp, i32, i32, i32, vp, vp, vp, vp, i32, i32, vp], C.c_int),
 ]
 

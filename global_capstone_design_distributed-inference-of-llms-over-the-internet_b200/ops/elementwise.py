@@ -33,6 +33,16 @@ def norm(x: torch.Tensor, w: torch.Tensor, b: Optional[torch.Tensor], eps: float
     return out
 
 
+def rms_rstd(x: torch.Tensor, eps: float, out: torch.Tensor, pdl: bool = False) -> torch.Tensor:
+    """out[t] = 1/sqrt(mean(x[t]^2) + eps) (fp32), bit-identical to the statistics the GEMM would compute itself."""
+    T, K = x.shape
+    assert out.dtype == torch.float32 and out.numel() >= T
+    rc = native.lib().b200_rms_rstd(x.data_ptr(), out.data_ptr(), T, K, x.stride(0), eps, dtype_code(x.dtype),
+                                    1 if pdl else 0, native.current_stream_ptr())
+    native.check(rc, "b200_rms_rstd")
+    return out
+
+
 class ArgmaxWorkspace:
     def __init__(self, device, max_tokens: int, chunks: int = 64):
         self.chunks = chunks

@@ -79,11 +79,12 @@ def linear(
     grid: int = 0,
     debug: int = 0,
     prefetch=None,
+    rstd: Optional[torch.Tensor] = None,
 ) -> torch.Tensor:
     """x: [T, K] (16-bit, last dim contiguous) -> [T, N]."""
     a, out = fill_args(x, w, out=out, residual=residual, epilogue=epilogue, norm_mode=norm_mode, norm_w=norm_w,
                        norm_b=norm_b, norm_eps=norm_eps, out_fp32=out_fp32, workspace=workspace, pdl=pdl, grid=grid,
-                       debug=debug, prefetch=prefetch)
+                       debug=debug, prefetch=prefetch, rstd=rstd)
     if (x.shape[0] >= PREFILL_MIN_TOKENS and norm_mode == NORM_NONE and not w.fp8 and _prefill_kernel_enabled()):
         # token-tile-filling inputs: TMA-fed kernel with the epilogue overlapped (csrc/gemm_prefill.cu)
         rc = native.lib().b200_gemm_prefill(ctypes.byref(a), native.current_stream_ptr())
@@ -110,7 +111,7 @@ def _prefill_kernel_enabled() -> bool:
 
 
 def fill_args(x, w, *, out=None, residual=None, epilogue=EPI_NONE, norm_mode=NORM_NONE, norm_w=None, norm_b=None,
-              norm_eps=1e-5, out_fp32=False, workspace=None, pdl=False, grid=0, debug=0, prefetch=None):
+              norm_eps=1e-5, out_fp32=False, workspace=None, pdl=False, grid=0, debug=0, prefetch=None, rstd=None):
     """Builds the ``b200_gemm_args`` for one call (also used to describe ops of the persistent kernel)."""
     assert x.dim() == 2 and x.stride(1) == 1 and x.is_cuda
     T, K = x.shape
@@ -148,6 +149,7 @@ def fill_args(x, w, *, out=None, residual=None, epilogue=EPI_NONE, norm_mode=NOR
     a.fp8 = 1 if w.fp8 else 0
     a.w_scale = w.scale.data_ptr() if w.scale is not None else None
     a.ll_buf = ws.ll.data_ptr() if ws.ll is not None else None
+    a.rstd = rstd.data_ptr() if rstd is not None else None
     # prefetch: up to two (PackedWeight | tensor, first_byte, n_bytes) ranges to warm the L2 with
     for i, (t, off, nbytes) in enumerate(prefetch or ()):
         data = t.data if hasattr(t, "n_tiles") else t

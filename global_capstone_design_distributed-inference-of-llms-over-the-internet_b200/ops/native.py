@@ -54,6 +54,7 @@ class GemmArgs(ctypes.Structure):
         ("prefetch", ctypes.c_void_p * 2),
         ("prefetch_bytes", ctypes.c_int64 * 2),
         ("ll_buf", ctypes.c_void_p),
+        ("rstd", ctypes.c_void_p),
     ]
 
 

@@ -38,6 +38,9 @@ from .kv_cache import SessionKV
 MAX_DECODE_BATCH = 32
 
 
+RSTD_KERNEL_MIN_TOKENS = int(os.environ.get("B200_RSTD_KERNEL_MIN_TOKENS", "8"))
+
+
 def _l2_prefetch_default():
     """B200_L2_PREFETCH_MB="a,b,c,d" (MiB, see _decode_layers); "0" switches the L2 warm-up off.
 
@@ -130,6 +133,7 @@ class NativeSpan:
             # lets an intermediate size that is not a multiple of 64 (Llama-2-7B split 8 ways: 1376) through
             self.act = torch.zeros(Tm, (c.intermediate + 63) // 64 * 64, dtype=dtype, device=self.device)
             self.ids_in = torch.zeros(Tm, dtype=torch.int64, device=self.device)
+            self.rstd = torch.zeros(max(Tm, 32), dtype=torch.float32, device=self.device)
             self.ws = G.GemmWorkspace.create(self.device, Tm)
             self.splits = attn_splits or int(os.environ.get("B200_ATTN_SPLITS", "0")) or max(1, min(16, kv_capacity // 64))
             self.attn_ws = A.DecodeAttnWorkspace(self.device, self.max_batch, c.n_heads, c.n_kv_heads, c.head_dim,
@@ -212,13 +216,22 @@ class NativeSpan:
                 pf[1] = [(P["mlp_in"], mb[0] * M, mb[1] * M)]
                 pf[2] = [(P["down"], 0, mb[2] * M)]
                 pf[3] = [(nxt, 0, mb[3] * M)] if nxt is not None else None
+            # Many sessions per step: the RMSNorm statistics are computed once by a one-block-per-token kernel
+            # instead of once per CTA of the GEMM (~1 us per token pair there); same bits either way.
+            rs = None
+            if c.is_llama and T >= RSTD_KERNEL_MIN_TOKENS:
+                rs = E.rms_rstd(h, c.norm_eps, self.rstd, pdl=pdl)
+                self._count()
             G.linear(h, P["qkv"], out=qkv, norm_mode=self.norm_mode, norm_w=P["ln1_w"], norm_b=P["ln1_b"],
-                     norm_eps=c.norm_eps, workspace=self.ws, pdl=pdl, prefetch=pf[0])
+                     norm_eps=c.norm_eps, workspace=self.ws, pdl=pdl, prefetch=pf[0], rstd=rs)
             A.attn_decode(qkv, attn, self.kv_ptrs[li], self.pos, self.inv_freq, self.attn_ws, c.n_heads,
                           c.n_kv_heads, c.head_dim, self.kv_capacity, self.scale, pdl=pdl)
             self._row_parallel(attn, P["o"], h2, h, prefetch=pf[1])
+            if rs is not None:
+                rs = E.rms_rstd(h2, c.norm_eps, self.rstd, pdl=pdl)
+                self._count()
             G.linear(h2, P["mlp_in"], out=act, epilogue=self.mlp_epi, norm_mode=self.norm_mode, norm_w=P["ln2_w"],
-                     norm_b=P["ln2_b"], norm_eps=c.norm_eps, workspace=self.ws, pdl=pdl, prefetch=pf[2])
+                     norm_b=P["ln2_b"], norm_eps=c.norm_eps, workspace=self.ws, pdl=pdl, prefetch=pf[2], rstd=rs)
             self._row_parallel(act, P["down"], h, h2, prefetch=pf[3])
             self._count(5)
         return h

@@ -101,6 +101,9 @@ typedef struct b200_gemm_args {
      * tile reduces a share of its elements).  Same summation
      * order as the ticket path, i.e. bit-identical results.  NULL = ticket path. */
     void* ll_buf;
+    /* Optional with norm_mode == B200_NORM_RMS: per-token 1/rms computed beforehand (b200_rms_rstd, same bits as the
+     * in-kernel statistics); the kernel then skips its own statistics pass.  Pays off from ~8 tokens per step. */
+    const float* rstd;
 } b200_gemm_args;
 
 int b200_gemm(const b200_gemm_args* args, void* stream);
@@ -230,6 +233,9 @@ int b200_attn_prefill_tc(const void* q, void* out, const void* kcache, const voi
 int b200_embed(const void* ids, const void* pos, int32_t pos0, const void* wte, const void* wpe, void* out, int32_t T,
                int32_t H, int32_t vocab, int32_t max_pos, int32_t dtype, int32_t pdl, void* stream);
 /* Standalone RMSNorm (layer_norm=0) / LayerNorm (1) for prefill-size inputs: block.py:208-213. */
+/* rstd[t] = 1/sqrt(mean(x[t]^2) + eps), one block per token; see b200_gemm_args.rstd. */
+int b200_rms_rstd(const void* x, float* rstd, int32_t T, int32_t K, int32_t ldx, float eps, int32_t dtype, int32_t pdl,
+                  void* stream);
 int b200_norm(const void* x, const void* w, const void* b, void* out, int32_t T, int32_t H, int32_t ldx, int32_t ldo,
               float eps, int32_t layer_norm, int32_t dtype, int32_t pdl, void* stream);
 /* Greedy sampling: first index of the row maximum of fp32 logits (src/rpc_handler.py:331-335).
