@@ -198,3 +198,55 @@ def test_gemm_l2_prefetch_hint_changes_nothing():
     torch.cuda.synchronize()
     assert torch.equal(base, hinted) and torch.equal(base, past_end)
     _close(base, _ref(x, w, dtype=dtype), dtype)
+
+
+@pytest.mark.parametrize("T", [1, 2, 4, 5, 16])
+@pytest.mark.parametrize("shape", [(4096, 4096, False), (1408, 4096, True), (512, 11008, False)])
+def test_gemm_ticket_free_fixup_matches_ticket_path_bit_for_bit(T, shape):
+    """(value, tag) word exchange (T = 1: the tile's last CTA collects; 2..16: every CTA reduces a share) vs the
+    scratch + ticket path: same summation order, so the same bits; the word buffer is left all zero."""
+    from petals_b200.ops import gemm, packing
+
+    N, K, dual = shape
+    dtype = torch.bfloat16
+    torch.manual_seed(T + N)
+    x = (torch.randn(T, K, device="cuda") * 0.5).to(dtype)
+    res = torch.randn(T, N, device="cuda").to(dtype)
+    g = (1 + 0.1 * torch.randn(K, device="cuda")).to(dtype)
+    if dual:
+        pw = packing.pack_dual((torch.randn(N, K, device="cuda") / K ** 0.5).to(dtype),
+                               (torch.randn(N, K, device="cuda") / K ** 0.5).to(dtype))
+        kw = dict(norm_mode=gemm.NORM_RMS, norm_w=g)
+    else:
+        pw = packing.pack_weight((torch.randn(N, K, device="cuda") / K ** 0.5).to(dtype))
+        kw = dict(residual=res)
+    ws_ll = gemm.GemmWorkspace.create("cuda", 16)
+    assert ws_ll.ll is not None
+    ws_ticket = gemm.GemmWorkspace.create("cuda", 16)
+    ws_ticket.ll = None
+    a = gemm.linear(x, pw, workspace=ws_ll, **kw)
+    b = gemm.linear(x, pw, workspace=ws_ticket, **kw)
+    a2 = gemm.linear(x, pw, workspace=ws_ll, **kw)
+    torch.cuda.synchronize()
+    assert torch.equal(a, b) and torch.equal(a, a2)
+    assert int(ws_ll.ll.abs().sum()) == 0 and int(ws_ticket.counters.abs().sum()) == 0
+
+
+@pytest.mark.parametrize("T", [1, 8, 16])
+def test_rms_rstd_kernel_matches_in_kernel_statistics(T):
+    from petals_b200.ops import elementwise as E, gemm, packing
+
+    dtype = torch.float16
+    torch.manual_seed(T)
+    K, N = 4096, 768
+    x = (torch.randn(T, K, device="cuda") * 1.7 + 0.2).to(dtype)
+    g = (1 + 0.1 * torch.randn(K, device="cuda")).to(dtype)
+    pw = packing.pack_weight((torch.randn(N, K, device="cuda") / K ** 0.5).to(dtype))
+    rstd = torch.zeros(32, device="cuda", dtype=torch.float32)
+    E.rms_rstd(x, 1e-5, rstd)
+    ref = torch.rsqrt(x.float().pow(2).mean(-1) + 1e-5)
+    assert (rstd[:T] - ref).abs().max().item() < 1e-5 * ref.abs().max().item() + 1e-7
+    a = gemm.linear(x, pw, norm_mode=gemm.NORM_RMS, norm_w=g)
+    b = gemm.linear(x, pw, norm_mode=gemm.NORM_RMS, norm_w=g, rstd=rstd)
+    torch.cuda.synchronize()
+    assert torch.equal(a, b)
