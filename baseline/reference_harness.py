@@ -210,6 +210,10 @@ def run(args) -> None:
     import torch.distributed as dist
 
     if not os.path.isdir(os.path.join(REF, "src")):
+        import subprocess
+
+        subprocess.run([sys.executable, os.path.join(HERE, "install_reference.py")], check=False, capture_output=True)
+    if not os.path.isdir(os.path.join(REF, "src")):
         raise RuntimeError("baseline/_ref is empty: run `python baseline/install_reference.py` first")
     serialize, deserialize, mser = _install_stubs()
     sys.path.insert(0, REF)
