@@ -256,10 +256,26 @@ class PipelineEngine:
         """
         sess = list(range(len(self.sessions))) if sessions is None else list(sessions)
         S = len(sess)
+        if self.world == 1 and tokens is not None and to_host and self.backend == "native":
+            # Single-GPU host loop, the latency path: the pinned token buffer is copied straight into the captured
+            # graph's input and the result straight out of its output - no device-to-device staging in between.
+            kvs = [self.sessions[i] for i in sess]
+            for j, t in enumerate(tokens):
+                self._tok_host[j] = int(t)
+            self.span.ids_in[:S].copy_(self._tok_host[:S], non_blocking=True)
+            self.h2d_bytes += 8 * S
+            out = self.span.decode(kvs, ids=None)
+            self._tok_host[:S].copy_(out[1].reshape(-1)[:S])          # blocking D2H
+            self.d2h_bytes += 8 * S
+            self._tok_stale = True                                    # the device copy is refreshed on demand
+            return [int(x) for x in self._tok_host[:S]]
         if self.is_first and tokens is not None:
             self._tok_host[:S] = torch.as_tensor(list(tokens), dtype=torch.int64)
             self._tok[:S].copy_(self._tok_host[:S], non_blocking=True)
             self.h2d_bytes += 8 * S
+        elif self.is_first and getattr(self, "_tok_stale", False):
+            self._tok[:S].copy_(self._tok_host[:S], non_blocking=True)
+        self._tok_stale = False
         if self.world == 1:
             kvs = [self.sessions[i] for i in sess]
             out = self._stage_decode(kvs, self._tok[:S], None)
