@@ -85,7 +85,7 @@ def linear(
     a, out = fill_args(x, w, out=out, residual=residual, epilogue=epilogue, norm_mode=norm_mode, norm_w=norm_w,
                        norm_b=norm_b, norm_eps=norm_eps, out_fp32=out_fp32, workspace=workspace, pdl=pdl, grid=grid,
                        debug=debug, prefetch=prefetch, rstd=rstd)
-    if (x.shape[0] >= PREFILL_MIN_TOKENS and norm_mode == NORM_NONE and not w.fp8 and _prefill_kernel_enabled()):
+    if uses_prefill_kernel(x.shape[0], w, norm_mode):
         # token-tile-filling inputs: TMA-fed kernel with the epilogue overlapped (csrc/gemm_prefill.cu)
         rc = native.lib().b200_gemm_prefill(ctypes.byref(a), native.current_stream_ptr())
         native.check(rc, "b200_gemm_prefill")
@@ -96,6 +96,11 @@ def linear(
 
 
 PREFILL_MIN_TOKENS = 64
+
+
+def uses_prefill_kernel(T: int, w: PackedWeight, norm_mode: int = NORM_NONE) -> bool:
+    """The routing rule of :func:`linear` (callers that cache argument structs launch the kernel themselves)."""
+    return T >= PREFILL_MIN_TOKENS and norm_mode == NORM_NONE and not w.fp8 and _prefill_kernel_enabled()
 
 
 def _ll_fixup_enabled() -> bool:
