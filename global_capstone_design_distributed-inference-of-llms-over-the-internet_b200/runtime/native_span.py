@@ -593,9 +593,10 @@ class NativeSpan:
         """Argument structs of every launch of an n-token chunk, built once per chunk length.
 
         A prefill chunk is 8 launches per block; building their arguments through the generic wrappers costs
-        ~15 us of Python each, more than the kernels take for short prompts (a 128-token prompt on Llama-2-7B
-        was 5.8 ms, of which ~2.5 ms GPU).  Only the cache pointers, the start position and the stream change
-        from call to call, so everything else is kept as ready ctypes arguments."""
+        ~15 us of Python each.  Only the cache pointers, the start position and the stream change from call to
+        call, so everything else is kept as ready ctypes arguments.  Measured on Llama-2-7B: 2048-token prompt
+        29.2 -> 27.6 ms, 4096 tokens 60.7 -> 58.5 ms; a 128-token prompt stays at 5.8 ms (GPU-bound: at 128 tokens
+        each GEMM has only 32-96 output tiles for 148 SMs and the prefill kernel does not split K)."""
         plan = self._prefill_plans.get(n)
         if plan is not None:
             return plan
