@@ -807,9 +807,10 @@ static int gemm_impl(const b200_gemm_args* a, const b200_tp_args* tp, void* stre
     // Ticket-free fix-up: only when every tile is shared by the same whole number of CTAs with one part each.
     p.ll_words = nullptr; p.ll_parts = 0;
     p.rstd_in = (a->norm_mode == B200_NORM_RMS && !a->fp8 && t_tiles == 1) ? a->rstd : nullptr;
-    // One token (and T <= 4 with tensor parallelism or fp8 weights): the tile's last CTA collects.  2..16 tokens: every CTA
-    // reduces a share (measured per-layer GEMM chain, T=2: 82.9 -> 78.1 us, T=4: 93.7 -> 82.5, T=16: 138 -> 108; T=1 equal).
-    static const int wide_min = [] { const char* e = getenv("B200_LL_WIDE_MIN"); return e ? atoi(e) : 2; }();
+    // 1..16 tokens: every CTA of a tile reduces a share of its elements (measured per-layer GEMM chain, T=2: 82.9 -> 78.1 us,
+    // T=4: 93.7 -> 82.5, T=16: 138 -> 108; T=1: 359.1 -> 362.2 tok/s end of the decode bench).  With tensor parallelism or
+    // fp8 weights (T <= 4) the tile's last CTA collects.
+    static const int wide_min = [] { const char* e = getenv("B200_LL_WIDE_MIN"); return e ? atoi(e) : 1; }();
     const bool ll_wide = a->T >= wide_min && a->T <= 16 && !tp && !gather && !a->fp8;
     if (a->ll_buf && bn == 16 && t_tiles == 1 && (a->T <= 4 || ll_wide) && grid % a->n_tiles == 0 && grid <= kLLMaxCtas) {
         const int parts = grid / a->n_tiles;
