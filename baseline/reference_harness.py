@@ -357,7 +357,8 @@ def run(args) -> None:
         H = cfg.hidden
         esz = 2
         result = {
-            "metric": "decode tokens/sec (aggregate over in-flight sessions), Llama-2-7B N-stage pipeline",
+            "metric": "decode tokens/sec (aggregate over in-flight sessions), "
+                      + ("Llama-2-7B" if args.model == "llama-2-7b" else args.model) + " N-stage pipeline",
             "value": round(K / (ms / 1e3), 2), "unit": "tokens/s", "n_gpus": world, "steps": K, "warmup": W,
             "ms_per_step": round(ms / K, 4), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": args.dtype, "data": "synthetic prompts, random-init weights", "impl": "reference",

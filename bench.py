@@ -213,7 +213,8 @@ def run_b200(args):
         e2e_tok_s = S * K / (e2e_ms / 1e3)
         wbytes = cfg.layer_bytes(2) * cfg.n_layers + cfg.vocab * cfg.hidden * 2
         out = {
-            "metric": "decode tokens/sec (aggregate over in-flight sessions), Llama-2-7B N-stage pipeline",
+            "metric": "decode tokens/sec (aggregate over in-flight sessions), "
+                      + ("Llama-2-7B" if args.model == "llama-2-7b" else args.model) + " N-stage pipeline",
             "value": round(tok_s, 2), "unit": "tokens/s", "n_gpus": world, "steps": K, "warmup": W,
             "ms_per_step": round(dev_ms / K, 4), "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": args.dtype if args.weights == "native" else f"{args.dtype} activations, fp8(e4m3) weights (opt-in)",
