@@ -265,6 +265,7 @@ class PipelineEngine:
             self.span.ids_in[:S].copy_(self._tok_host[:S], non_blocking=True)
             self.h2d_bytes += 8 * S
             out = self.span.decode(kvs, ids=None)
+            self.span.prestage(kvs)                                   # next step's positions, off the critical path
             self._tok_host[:S].copy_(out[1].reshape(-1)[:S])          # blocking D2H
             self.d2h_bytes += 8 * S
             self._tok_stale = True                                    # the device copy is refreshed on demand

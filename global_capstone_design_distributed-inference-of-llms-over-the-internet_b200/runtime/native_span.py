@@ -333,6 +333,12 @@ class NativeSpan:
         self.pos[:B].copy_(host[:B], non_blocking=True)
         ev.record(torch.cuda.current_stream(self.device))
 
+    def prestage(self, kvs: Sequence[SessionKV]) -> None:
+        """Queue the NEXT step's positions / cache pointers behind the step that was just launched, so a host loop
+        that now blocks on the token does not pay for this staging between two steps."""
+        self._stage_ptrs(kvs)
+        self._prestaged = tuple((kv.data.data_ptr(), kv.length) for kv in kvs)
+
     def _decode_body(self, B: int, from_ids: bool, greedy: bool):
         h = self._embed(B, 0, True) if from_ids else self.h_a[:B]
         if self.use_mega and B <= MEGA_MAX_TOKENS and self.tp_mode is None and self.weight_format == "native":
@@ -420,7 +426,10 @@ class NativeSpan:
         B = len(kvs)
         assert 1 <= B <= self.max_batch
         from_ids = self.embed_w is not None and h_in is None
-        self._stage_ptrs(kvs)
+        staged = getattr(self, "_prestaged", None)
+        self._prestaged = None
+        if staged is None or staged != tuple((kv.data.data_ptr(), kv.length) for kv in kvs):
+            self._stage_ptrs(kvs)
         key = (B, from_ids, greedy)
         g = None
         if self.use_graphs:
@@ -476,6 +485,7 @@ class NativeSpan:
         Returns the generated ids ``[n_steps, B]`` (device).
         """
         assert self.has_embed and self.has_head and self.embed_w is not None
+        self._prestaged = None
         B = len(kvs)
         for kv in kvs:
             if kv.length + n_steps > kv.max_len:
@@ -531,6 +541,7 @@ class NativeSpan:
         computed from the last position only.
         """
         c, pdl = self.cfg, self.pdl
+        self._prestaged = None
         pos0 = kv.length if pos0 is None else pos0
         T = ids.shape[0] if h_in is None else h_in.shape[0]
         if pos0 + T > kv.max_len:
