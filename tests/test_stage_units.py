@@ -92,3 +92,24 @@ def test_throughput_estimate_and_cache(tmp_path, monkeypatch):
     # compute-bound case: min(compute, network)
     monkeypatch.setattr(tm, "measure_compute_throughput", lambda *a, **k: 12.5)
     assert tm.get_server_throughput(Stage(), "cpu", torch.float16, network_bandwidth_mbps=100.0) == 12.5
+
+
+def test_cache_and_position_helpers():
+    """src/utils.py keeps the reference's helper names (there: HF Cache <-> legacy tuples, src/utils.py:5-64)."""
+    from petals_b200.runtime.kv_cache import KVCacheManager
+    from src import utils
+
+    assert utils.extract_kv_tuple(None) is None and utils.past_length(None) == 0
+    assert utils.default_position_ids(None, 3).tolist() == [[0, 1, 2]]
+    kv = KVCacheManager(2, 2, 8, torch.float32, "cpu").allocate("s", 16)
+    kv.data.normal_()
+    kv.length = 5
+    k, v = utils.extract_kv_tuple(kv, layer=1)
+    assert k.shape == v.shape == (2, 5, 8)
+    assert torch.equal(k, kv.data[1, 0, :, :5]) and torch.equal(v, kv.data[1, 1, :, :5])
+    assert utils.past_length(kv) == 5 and utils.default_position_ids(kv, 2).tolist() == [[5, 6]]
+    assert utils.normalize_cache(kv) is kv
+    kv.rollback(3)
+    assert utils.past_length(kv) == 3
+    with pytest.raises(ValueError):
+        kv.rollback(9)
