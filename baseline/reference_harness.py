@@ -21,8 +21,14 @@ What is the reference's and what is not
 
 N GPUs: rank 0 is the client (embedding + first 32/N blocks), ranks 1..N-1 are server stages
 (the last one samples); N = 1 runs the client half and one last-stage server thread on the same GPU
-(the reference cannot run without at least one server stage).  One session, batch 1 — the
-reference has no way to keep several sessions in flight.
+(the reference cannot run without at least one server stage).
+
+Sessions: like the other arm, ``--sessions`` (default: one per GPU) independent batch-1 client sessions run
+concurrently, each with its own session id, its own sockets to every stage and its own client-side KV; a
+stage server accepts all of them and serialises ``_run_forward`` calls the way the reference's single event
+loop does, so while session A is on stage 2 session B can be on stage 1.  The client half (``Stage0``) is
+one module on rank 0's GPU shared by the session threads under a lock (the reference would start one client
+process per session, each with its own copy of those blocks on that GPU).
 """
 from __future__ import annotations
 
@@ -159,26 +165,43 @@ def _serve(handler, port_holder, ready, stop, deserialize, msgpack_ser, device=N
     srv = socket.socket()
     srv.setsockopt(socket.SOL_SOCKET, socket.SO_REUSEADDR, 1)
     srv.bind(("127.0.0.1", port_holder[0]))
-    srv.listen(4)
+    srv.listen(64)
     port_holder[0] = srv.getsockname()[1]
     ready.set()
     srv.settimeout(0.5)
+    fwd_lock = threading.Lock()           # one _run_forward at a time, like the reference's event loop
+    state = {"open": 0, "seen": 0}
+    state_lock = threading.Lock()
+
+    def connection(conn):
+        if device is not None:
+            import torch
+
+            torch.cuda.set_device(device)
+        try:
+            while True:
+                tensor_msg, metadata = _recv(conn)
+                hidden = deserialize(tensor_msg)
+                with fwd_lock:
+                    resp = handler._run_forward(hidden, msgpack_ser.loads(metadata))      # <- reference code
+                _send(conn, (resp.tensors[0], resp.metadata))
+        except (ConnectionError, OSError):
+            conn.close()
+        with state_lock:
+            state["open"] -= 1
+            if state["open"] == 0 and done is not None:
+                done.set()                # every client hung up: this stage's work is over
+
     while not stop.is_set():
         try:
             conn, _ = srv.accept()
         except socket.timeout:
             continue
         conn.setsockopt(socket.IPPROTO_TCP, socket.TCP_NODELAY, 1)
-        try:
-            while True:
-                tensor_msg, metadata = _recv(conn)
-                hidden = deserialize(tensor_msg)
-                resp = handler._run_forward(hidden, msgpack_ser.loads(metadata))      # <- reference code
-                _send(conn, (resp.tensors[0], resp.metadata))
-        except (ConnectionError, OSError):
-            conn.close()
-            if done is not None:
-                done.set()                # the client hung up: this stage's work is over
+        with state_lock:
+            state["open"] += 1
+            state["seen"] += 1
+        threading.Thread(target=connection, args=(conn,), daemon=True).start()
     srv.close()
 
 
@@ -287,95 +310,148 @@ def run(args) -> None:
 
     result = None
     if rank == 0:
+        import hashlib
+
         full0, c0 = _hf_span(hf_dict, bounds[1], dev, dtype, True, False)
         s0 = lp.Stage0(full0, bounds[1]).to(dev)
         _shim(s0, c0)
-        socks = []
-        for si in range(1, n_stages):
-            s = socket.create_connection(("127.0.0.1", port_list[si]))
-            s.setsockopt(socket.IPPROTO_TCP, socket.TCP_NODELAY, 1)
-            socks.append(s)
+        S = args.sessions or world
+        s0_lock = threading.Lock()
         g = torch.Generator().manual_seed(1234)
-        prompt_host = torch.randint(0, cfg.vocab, (1, P), generator=g).pin_memory()
-        session = "bench-session"
-        generated = []
+        max_len = max(P + 2 * (K + W) + 16, 2048 + 64)
 
-        def hops(hidden, md):
-            cur = hidden.cpu()                                             # reference: rpc_transport.py:724
-            for sock in socks:
-                _send(sock, (serialize(cur), mser.dumps(md)))
-                tensor_msg, rmd = _recv(sock)
-                out = deserialize(tensor_msg)
-                rmd = mser.loads(rmd)
-                if "token_id" in rmd:
-                    return int(rmd["token_id"])
-                cur = out
-            raise RuntimeError("no token returned")
+        class Session:
+            def __init__(self, i, prompt_len):
+                self.sid = f"bench-session-{i}"
+                self.socks = []
+                for si in range(1, n_stages):
+                    sk = socket.create_connection(("127.0.0.1", port_list[si]))
+                    sk.setsockopt(socket.IPPROTO_TCP, socket.TCP_NODELAY, 1)
+                    self.socks.append(sk)
+                self.prompt = torch.randint(0, cfg.vocab, (1, prompt_len), generator=g).pin_memory()
+                self.generated = []
+                self.tok_host = torch.zeros(1, 1, dtype=torch.long).pin_memory()
+                self.lat = []
+
+            def hops(self, hidden, md):
+                cur = hidden.cpu()                                             # reference: rpc_transport.py:724
+                for sock in self.socks:
+                    _send(sock, (serialize(cur), mser.dumps(md)))
+                    tensor_msg, rmd = _recv(sock)
+                    out = deserialize(tensor_msg)
+                    rmd = mser.loads(rmd)
+                    if "token_id" in rmd:
+                        return int(rmd["token_id"])
+                    cur = out
+                raise RuntimeError("no token returned")
+
+            def prefill(self):
+                Pn = self.prompt.shape[1]
+                with s0_lock:
+                    ids = self.prompt.to(dev, non_blocking=True)
+                    pos = torch.arange(Pn, device=dev).unsqueeze(0)
+                    hidden, self.past0 = s0(ids, pos, None, None, use_cache=True)
+                md = dict(session_id=self.sid, seq_len=Pn, cur_len=Pn, is_prefill=True, max_length=max_len,
+                          temperature=0.0, top_p=0.92, top_k=50)
+                self.nxt = self.hops(hidden, md)
+                self.generated.append(self.nxt)
+                self.cur_len = Pn + 1
+
+            def step(self):
+                with s0_lock:
+                    self.tok_host[0, 0] = self.nxt
+                    new = self.tok_host.to(dev, non_blocking=True)               # H2D of the step's input
+                    past_len = self.past0[0][0].shape[-2]
+                    pos = torch.tensor([[past_len]], device=dev, dtype=torch.long)
+                    hidden, self.past0 = s0(new, pos, None, self.past0, use_cache=True)
+                md = dict(session_id=self.sid, seq_len=1, cur_len=self.cur_len, is_prefill=False, max_length=max_len,
+                          temperature=0.0, top_p=0.92, top_k=50, generated_tokens=self.generated[-50:])
+                self.nxt = self.hops(hidden, md)                                 # D2H of hidden + token back
+                self.generated.append(self.nxt)
+                self.cur_len += 1
+
+            def close(self):
+                for sk in self.socks:
+                    sk.close()
+
+        def run_steps(sessions, n, record):
+            def work(se):
+                torch.cuda.set_device(dev)
+                with torch.inference_mode():
+                    t_prev = time.perf_counter()
+                    for _ in range(n):
+                        se.step()
+                        now = time.perf_counter()
+                        if record:
+                            se.lat.append(now - t_prev)
+                        t_prev = now
+            if len(sessions) == 1:
+                work(sessions[0])
+                return
+            ts = [threading.Thread(target=work, args=(se,)) for se in sessions]
+            for t in ts:
+                t.start()
+            for t in ts:
+                t.join()
 
         with torch.inference_mode():
-            ids = prompt_host.to(dev, non_blocking=True)
-            pos = torch.arange(P, device=dev).unsqueeze(0)
-            hidden, past0 = s0(ids, pos, None, None, use_cache=True)
-            md = dict(session_id=session, seq_len=P, cur_len=P, is_prefill=True, max_length=P + K + W + 8,
-                      temperature=0.0, top_p=0.92, top_k=50)
-            nxt = hops(hidden, md)
-            generated.append(nxt)
-            cur_len = P + 1
-            tok_host = torch.zeros(1, 1, dtype=torch.long).pin_memory()
-
-            def step():
-                nonlocal nxt, past0, cur_len
-                tok_host[0, 0] = nxt
-                new = tok_host.to(dev, non_blocking=True)                    # H2D of the step's input
-                past_len = past0[0][0].shape[-2]
-                pos = torch.tensor([[past_len]], device=dev, dtype=torch.long)
-                hidden, past0 = s0(new, pos, None, past0, use_cache=True)
-                md = dict(session_id=session, seq_len=1, cur_len=cur_len, is_prefill=False, max_length=P + K + W + 8,
-                          temperature=0.0, top_p=0.92, top_k=50, generated_tokens=generated[-50:])
-                nxt = hops(hidden, md)                                      # D2H of hidden + token back
-                generated.append(nxt)
-                cur_len += 1
-
-            for _ in range(W):
-                step()
+            sessions = [Session(i, P) for i in range(S)]
+            for se in sessions:
+                se.prefill()
+            run_steps(sessions, W, False)
             torch.cuda.synchronize()
             sampler = ClockSampler(local)
             sampler.start()
-            lat = []
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             e0.record()
-            t_prev = time.perf_counter()
-            for _ in range(K):
-                step()
-                now = time.perf_counter()
-                lat.append(now - t_prev)
-                t_prev = now
+            run_steps(sessions, K, True)
             e1.record()
             torch.cuda.synchronize()
             ms = e0.elapsed_time(e1)
             clocks = sampler.stop()
+            # time to first token: a fresh session's prompt through Stage0 and every server stage, token back on the host
+            ttft = {}
+            for plen in (128, 2048):
+                try:
+                    times = []
+                    for rep in range(3):
+                        se = Session(1000 + plen * 10 + rep, plen)
+                        torch.cuda.synchronize()
+                        t0 = time.perf_counter()
+                        se.prefill()
+                        times.append((time.perf_counter() - t0) * 1e3)
+                        se.close()
+                    ttft[str(plen)] = round(statistics.median(times[1:]), 3)
+                except Exception as e:  # noqa: BLE001  (the decode line must survive a failing prompt length)
+                    ttft[str(plen)] = f"failed: {type(e).__name__}: {e}"[:120]
         H = cfg.hidden
         esz = 2
+        lat0 = sessions[0].lat
+        sha = hashlib.sha256(",".join(str(t) for t in sessions[0].generated[-K:]).encode()).hexdigest()[:16]
         result = {
             "metric": "decode tokens/sec (aggregate over in-flight sessions), "
                       + ("Llama-2-7B" if args.model == "llama-2-7b" else args.model) + " N-stage pipeline",
-            "value": round(K / (ms / 1e3), 2), "unit": "tokens/s", "n_gpus": world, "steps": K, "warmup": W,
+            "value": round(S * K / (ms / 1e3), 2), "unit": "tokens/s", "n_gpus": world, "steps": K, "warmup": W,
             "ms_per_step": round(ms / K, 4), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": args.dtype, "data": "synthetic prompts, random-init weights", "impl": "reference",
-            "config": {"model": args.model, "global_batch": 1, "seq_len": P, "parallelism": f"pp{n_stages}",
-                       "sessions_in_flight": 1, "keep_layers_on_gpu": "span (best case, resident weights)",
+            "config": {"model": args.model, "global_batch": S, "seq_len": P, "parallelism": f"pp{n_stages}",
+                       "sessions_in_flight": S, "batch_per_session": 1,
+                       "keep_layers_on_gpu": "span (best case, resident weights)",
                        "transport": "loopback TCP stand-in for hivemind/libp2p (not installable offline)",
-                       "p50_token_latency_ms": round(statistics.median(lat) * 1e3, 4),
+                       "p50_token_latency_ms": round(statistics.median(lat0) * 1e3, 4),
+                       "single_session_tokens_per_s": round(1.0 / statistics.median(lat0), 2),
+                       "ttft_ms": ttft, "tokens_sha": sha,
                        "note": "reference Stage*/OptimizedLlamaDecoderLayer/_run_forward/_sample_token run unmodified "
                                "from baseline/_ref; N=1 runs client half + one last-stage server on the same GPU"},
             "clocks": clocks,
-            "e2e": {"value": round(K / (ms / 1e3), 2), "unit": "tokens/s", "h2d_bytes_per_step": 8 + (n_stages - 1) * H * esz,
-                    "d2h_bytes_per_step": (n_stages - 1) * H * esz + 8, "ms_per_step": round(ms / K, 4),
+            "e2e": {"value": round(S * K / (ms / 1e3), 2), "unit": "tokens/s",
+                    "h2d_bytes_per_step": S * (8 + (n_stages - 1) * H * esz),
+                    "d2h_bytes_per_step": S * ((n_stages - 1) * H * esz + 8), "ms_per_step": round(ms / K, 4),
                     "note": "the reference has no device-only loop: value == e2e"},
             "gpu_launches": 0,
         }
-        for s in socks:
-            s.close()
+        for se in sessions:
+            se.close()
         print(json.dumps(result), flush=True)
     elif world > 1:
         done.wait()          # serve until the client closes the connection (no collective while serving:

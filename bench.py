@@ -49,7 +49,21 @@ def parse_args():
                     help="sessions per micro-batch travelling through the chain together (serving-throughput mode)")
     ap.add_argument("--weights", default="native", choices=["native", "fp8"],
                     help="fp8 = opt-in e4m3 weights (NOT the headline configuration)")
+    ap.add_argument("--hop", default=None, choices=["p2p", "nccl"],
+                    help="decode hop between stages: in-graph peer stores (default) or host-issued NCCL send/recv")
+    ap.add_argument("--head-split", type=int, default=None, help="1/0: shard the LM head over the last and first stage")
+    ap.add_argument("--no-ttft", action="store_true", help="skip the time-to-first-token measurement")
     return ap.parse_args()
+
+
+def measured_peaks():
+    """Roofline denominators measured by the driver on this pool (fallback: the profiling recipe's figures)."""
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            d = json.load(f)
+        return float(d["hbm_gbs"]), "measured"
+    except Exception:  # noqa: BLE001
+        return 6650.0, "fallback"
 
 
 class ClockSampler:
@@ -125,10 +139,14 @@ def run_b200(args):
     S = args.sessions or stages
     K, W, L = args.steps, args.warmup, args.prompt_len
     cap = L + 2 * (K + W) + 16
+    ttft_lens = [] if args.no_ttft else [128, 2048]
+    if ttft_lens:
+        cap = max(cap, max(ttft_lens) + 64)
     cap = (cap + 255) // 256 * 256
     eng = PipelineEngine(args.model, even_splits(cfg.n_layers, stages), dtype, dev, kv_capacity=cap,
-                         max_sessions=max(S, 1), max_chunk=256, seed=0, weight_format=args.weights, tp=args.tp,
-                         tp_mode=args.tp_mode)
+                         max_sessions=max(S, 1), max_chunk=512, seed=0, weight_format=args.weights, tp=args.tp,
+                         tp_mode=args.tp_mode, hop=args.hop,
+                         head_split=None if args.head_split is None else bool(args.head_split))
     sess = eng.open_sessions(S)
     g = torch.Generator().manual_seed(1234)
     prompts = [torch.randint(0, cfg.vocab, (L,), generator=g) for _ in range(S)]
@@ -193,6 +211,7 @@ def run_b200(args):
     barrier()
     h2d0, d2h0 = eng.h2d_bytes, eng.d2h_bytes
     lat = []
+    toks0 = []                    # session 0's tokens of the end-to-end phase (checksum: must not depend on N)
     e2, e3 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
     e2.record()
@@ -200,15 +219,38 @@ def run_b200(args):
     for _ in range(K):
         r = eng.decode_round_streaming(cur)
         cur = r if r else cur
+        if r:
+            toks0.append(int(r[0]))
         now = time.perf_counter()
         lat.append(now - t_prev)
         t_prev = now
-    eng.flush_streaming()
+    r = eng.flush_streaming()
+    if r:
+        toks0.append(int(r[0]))
     e3.record()
     barrier()
     e2e_ms = max_over_ranks(e2.elapsed_time(e3))
     clocks = sampler.stop() if rank == 0 else None
+
+    # ---------------------------------------------------------------- time to first token (public prefill API)
+    ttft = {}
+    if ttft_lens:
+        extra = eng.open_sessions(1)[0]
+        gt = torch.Generator().manual_seed(4321)
+        for plen in ttft_lens:
+            prompt = torch.randint(0, cfg.vocab, (plen,), generator=gt).pin_memory()
+            times = []
+            for _ in range(4):
+                eng.sessions[extra].length = 0
+                barrier()
+                t0 = time.perf_counter()
+                eng.prefill(extra, prompt)          # H2D of the prompt ... D2H of the first token (rank 0)
+                times.append((time.perf_counter() - t0) * 1e3)
+            ttft[str(plen)] = round(statistics.median(times[1:]), 3)
     if rank == 0:
+        import hashlib
+
+        hbm_gbs, peak_src = measured_peaks()
         tok_s = S * K / (dev_ms / 1e3)
         e2e_tok_s = S * K / (e2e_ms / 1e3)
         wbytes = cfg.layer_bytes(2) * cfg.n_layers + cfg.vocab * cfg.hidden * 2
@@ -224,8 +266,12 @@ def run_b200(args):
                        "sessions_in_flight": S, "batch_per_session": 1, "sessions_per_micro_batch": args.group,
                        "l2": "every step streams all weights (13.5 GB >> 126 MB L2); no flush needed",
                        "p50_token_latency_ms": round(statistics.median(lat) * 1e3, 4),
-                       "hbm_roofline_frac_measured": round(
-                           (S * wbytes / world) / (dev_ms / K / 1e3) / 6551e9, 3)},
+                       "single_session_tokens_per_s": round(1.0 / statistics.median(lat), 2),
+                       "hop": eng.hop, "head_split": eng.head_split,
+                       "ttft_ms": ttft,
+                       "tokens_sha": hashlib.sha256(",".join(str(t) for t in toks0[-K:]).encode()).hexdigest()[:16],
+                       f"hbm_roofline_frac_of_{peak_src}": round(
+                           (S * wbytes / world) / (dev_ms / K / 1e3) / (hbm_gbs * 1e9), 3)},
             "clocks": clocks,
             "e2e": {"value": round(e2e_tok_s, 2), "unit": "tokens/s",
                     "h2d_bytes_per_step": (eng.h2d_bytes - h2d0) // K, "d2h_bytes_per_step": (eng.d2h_bytes - d2h0) // K,

@@ -114,9 +114,13 @@ __global__ void __launch_bounds__(256) norm_kernel(const uint16_t* __restrict__ 
 // ------------------------------------------------------------------ argmax
 // logits fp32 [T, V] -> ids[t] = first index of the row maximum (torch.argmax tie rule).
 // Stage 1: grid (chunks, T) partial (max, idx); the last CTA of a row reduces the partials.
+// Vocabulary shards: indices are reported with idx_offset added; init_pair[t] = {value bits, index} is a candidate from
+// another shard (same tie rule: the lower index wins), out_pair[t] receives the winner.
 __global__ void __launch_bounds__(256) argmax_kernel(const float* __restrict__ logits, int ld, int V,
                                                     float* __restrict__ part_val, int* __restrict__ part_idx,
-                                                    int* __restrict__ counters, long long* __restrict__ out_ids) {
+                                                    int* __restrict__ counters, long long* __restrict__ out_ids,
+                                                    int idx_offset, const uint32_t* __restrict__ init_pair,
+                                                    uint32_t* __restrict__ out_pair) {
     __shared__ float s_v[8];
     __shared__ int s_i[8];
     __shared__ int s_last;
@@ -166,7 +170,14 @@ __global__ void __launch_bounds__(256) argmax_kernel(const float* __restrict__ l
         }
         reduce_pair(best, bidx);
         if (threadIdx.x == 0) {
-            out_ids[t] = (bidx == 0x7fffffff) ? 0 : bidx;
+            if (bidx != 0x7fffffff) bidx += idx_offset;
+            if (init_pair) {
+                const float v2 = __uint_as_float(__ldcg(init_pair + 2 * t));
+                const int i2 = (int)__ldcg(init_pair + 2 * t + 1);
+                if (v2 > best || (v2 == best && i2 < bidx)) { best = v2; bidx = i2; }
+            }
+            if (out_ids) out_ids[t] = (bidx == 0x7fffffff) ? 0 : bidx;
+            if (out_pair) { out_pair[2 * t] = __float_as_uint(best); out_pair[2 * t + 1] = (uint32_t)bidx; }
             counters[t] = 0;
         }
     }
@@ -250,12 +261,22 @@ extern "C" int b200_norm(const void* x, const void* w, const void* b, void* out,
     return B200_OK;
 }
 
-extern "C" int b200_argmax(const float* logits, int32_t ld, int32_t T, int32_t V, float* part_val, int32_t* part_idx,
-                           int32_t* counters, void* out_ids, int32_t chunks, int32_t pdl, void* stream_) {
-    if (!logits || !part_val || !part_idx || !counters || !out_ids)
+extern "C" int b200_argmax_partial(const float* logits, int32_t ld, int32_t T, int32_t V, float* part_val,
+                                   int32_t* part_idx, int32_t* counters, void* out_ids, int32_t chunks,
+                                   int32_t idx_offset, const void* init_pair, void* out_pair, int32_t pdl,
+                                   void* stream_) {
+    if (!logits || !part_val || !part_idx || !counters || (!out_ids && !out_pair))
         return fail(B200_EINVAL, "b200_argmax: null pointer argument");
     if (chunks <= 0 || chunks > 1024) return fail(B200_EINVAL, "b200_argmax: chunks=%d out of range", chunks);
     B200_CUDA_CHECK(launch(argmax_kernel, dim3(chunks, T), dim3(256), 0, static_cast<cudaStream_t>(stream_), pdl != 0,
-                           logits, ld, V, part_val, part_idx, counters, static_cast<long long*>(out_ids)));
+                           logits, ld, V, part_val, part_idx, counters, static_cast<long long*>(out_ids), idx_offset,
+                           static_cast<const uint32_t*>(init_pair), static_cast<uint32_t*>(out_pair)));
     return B200_OK;
+}
+
+extern "C" int b200_argmax(const float* logits, int32_t ld, int32_t T, int32_t V, float* part_val, int32_t* part_idx,
+                           int32_t* counters, void* out_ids, int32_t chunks, int32_t pdl, void* stream_) {
+    if (!out_ids) return fail(B200_EINVAL, "b200_argmax: null pointer argument");
+    return b200_argmax_partial(logits, ld, T, V, part_val, part_idx, counters, out_ids, chunks, 0, nullptr, nullptr, pdl,
+                               stream_);
 }

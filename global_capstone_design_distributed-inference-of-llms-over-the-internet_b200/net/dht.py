@@ -11,11 +11,17 @@ re-provides the part of the API the framework consumes:
     dht.get_visible_maddrs(), dht.peer_id, dht.shutdown(), get_dht_time()
 
 Records with sub-keys merge into a dict ``subkey -> ValueWithExpiration`` whose entries
-expire individually (what replica announcement relies on).  A node started without
-``initial_peers`` is a bootstrap node and serves its table over TCP; a node with
-``initial_peers`` keeps its own table too, forwards stores to every reachable peer and
-merges gets (newest expiration wins), so the registry survives as long as one
-bootstrap peer is alive.  Multiaddrs look like ``/ip4/127.0.0.1/tcp/8000/p2p/<peer_id>``.
+expire individually (what replica announcement relies on).  Every non-client node serves its
+table over TCP.  Nodes learn of each other transitively: each request carries the sender's
+listen address and each answer the answering node's peer list, so a node bootstrapped from
+one peer soon knows every node that peer knows (and they know it).  Stores are replicated to
+every known peer and gets are merged over all of them (newest expiration wins); a peer that
+stops answering is skipped for a few seconds instead of being dialled on every call.  The
+registry therefore outlives its bootstrap node: servers keep re-announcing to each other and a
+client that has talked to the swarm once keeps finding them (hivemind's Kademlia gives the
+reference the same property, src/main.py:304-312).  Swarms here are a handful of nodes, so
+"k closest" replication is simply "all known peers".
+Multiaddrs look like ``/ip4/127.0.0.1/tcp/8000/p2p/<peer_id>``.
 """
 from __future__ import annotations
 
@@ -168,17 +174,21 @@ def _recv_msg(sock: socket.socket):
 class _Handler(socketserver.BaseRequestHandler):
     def handle(self):
         table: _Table = self.server.table  # type: ignore[attr-defined]
+        node = getattr(self.server, "node", None)
         try:
             while True:
                 req = _recv_msg(self.request)
                 op = req.get("op")
+                if node is not None and req.get("from"):
+                    node._learn([req["from"]])          # the caller is a serving node: remember it
+                peers = node.known_peers() if node is not None else []
                 if op == "store":
                     ok = table.store(req["key"], req["value"], req["exp"], req.get("subkey"))
-                    _send_msg(self.request, {"ok": ok})
+                    _send_msg(self.request, {"ok": ok, "peers": peers})
                 elif op == "get":
-                    _send_msg(self.request, {"r": table.get(req["key"])})
+                    _send_msg(self.request, {"r": table.get(req["key"]), "peers": peers})
                 elif op == "ping":
-                    _send_msg(self.request, {"peer_id": self.server.peer_id})  # type: ignore[attr-defined]
+                    _send_msg(self.request, {"peer_id": self.server.peer_id, "peers": peers})  # type: ignore[attr-defined]
                 else:
                     _send_msg(self.request, {"error": f"unknown op {op!r}"})
         except (ConnectionError, OSError, ValueError):
@@ -207,12 +217,16 @@ class DHT:
             h, p, _ = parse_maddr(host_maddrs[0])
             self._host, self._port = h, p
         self._peers: List[Tuple[str, int]] = []
+        self._peer_lock = threading.Lock()
+        self._dead_until: Dict[Tuple[str, int], float] = {}
+        self._fails: Dict[Tuple[str, int], int] = {}
         for m in self.initial_peers:
             h, p, _ = parse_maddr(m)
             self._peers.append((h, p))
         self.client_mode = client_mode
         if start:
             self.run_in_background()
+            self.refresh_peers()
 
     # ---- lifecycle
     def run_in_background(self) -> None:
@@ -222,6 +236,7 @@ class DHT:
         self._server = _Server((bind_host, self._port), _Handler)
         self._server.table = self._table          # type: ignore[attr-defined]
         self._server.peer_id = str(self.peer_id)  # type: ignore[attr-defined]
+        self._server.node = self                  # type: ignore[attr-defined]
         self._port = self._server.server_address[1]
         self._thread = threading.Thread(target=self._server.serve_forever, name="dht-server", daemon=True)
         self._thread.start()
@@ -245,8 +260,80 @@ class DHT:
         host = "127.0.0.1" if self._host in ("0.0.0.0", "") else self._host
         return [f"/ip4/{host}/tcp/{self._port}/p2p/{self.peer_id}"]
 
+    # ---- peer bookkeeping
+    DEAD_BACKOFF = 5.0
+    FORGET_AFTER = 8
+
+    def _listen_addr(self) -> Optional[List]:
+        """Address other nodes can dial this node's table at (None for client-mode nodes)."""
+        if self._server is None:
+            return None
+        if self._announce:
+            h, p, _ = parse_maddr(self._announce[0])
+            return [h, p]
+        host = "127.0.0.1" if self._host in ("0.0.0.0", "") else self._host
+        return [host, self._port]
+
+    def known_peers(self) -> List[List]:
+        with self._peer_lock:
+            out = [[h, p] for h, p in self._peers]
+        me = self._listen_addr()
+        if me is not None:
+            out.append(me)
+        return out
+
+    def _learn(self, peers) -> None:
+        me = self._listen_addr()
+        with self._peer_lock:
+            for hp in peers or []:
+                try:
+                    a = (str(hp[0]), int(hp[1]))
+                except (TypeError, ValueError, IndexError):
+                    continue
+                if me is not None and a == (me[0], me[1]):
+                    continue
+                if a not in self._peers:
+                    self._peers.append(a)
+
+    def _live_peers(self) -> List[Tuple[str, int]]:
+        now = time.monotonic()
+        with self._peer_lock:
+            return [a for a in self._peers if self._dead_until.get(a, 0.0) <= now]
+
+    def refresh_peers(self, rounds: int = 2) -> int:
+        """Introduce this node to every peer it knows of and collect theirs (transitive closure in `rounds`)."""
+        for _ in range(rounds):
+            before = len(self._peers)
+            for a in self._live_peers():
+                self._call(a, {"op": "ping"}, timeout=1.5)
+            if len(self._peers) == before:
+                break
+        return len(self._peers)
+
     # ---- remote plumbing
     def _call(self, addr: Tuple[str, int], req: dict, timeout: float = 3.0):
+        me = self._listen_addr()
+        if me is not None:
+            req = dict(req)
+            req["from"] = me
+        r = self._call_raw(addr, req, timeout)
+        if r is None:
+            n = self._fails.get(addr, 0) + 1
+            self._fails[addr] = n
+            self._dead_until[addr] = time.monotonic() + self.DEAD_BACKOFF
+            if n >= self.FORGET_AFTER:
+                # gone for good (or re-placed under another port): stop gossiping it
+                with self._peer_lock:
+                    if addr in self._peers and len(self._peers) > 1:
+                        self._peers.remove(addr)
+                self._fails.pop(addr, None)
+        else:
+            self._fails.pop(addr, None)
+            self._dead_until.pop(addr, None)
+            self._learn(r.get("peers"))
+        return r
+
+    def _call_raw(self, addr: Tuple[str, int], req: dict, timeout: float = 3.0):
         with self._conn_lock:
             s = self._conns.get(addr)
             try:
@@ -270,7 +357,7 @@ class DHT:
     def store(self, key: str, value, expiration_time: float, subkey: Optional[str] = None,
               return_future: bool = False, **_ignored) -> bool:
         ok = self._table.store(key, value, float(expiration_time), subkey)
-        for addr in self._peers:
+        for addr in self._live_peers():
             r = self._call(addr, {"op": "store", "key": key, "value": value, "exp": float(expiration_time),
                                   "subkey": subkey})
             ok = ok or bool(r and r.get("ok"))
@@ -278,7 +365,7 @@ class DHT:
 
     def get(self, key: str, latest: bool = True, **_ignored) -> Optional[ValueWithExpiration]:
         results = [self._table.get(key)]
-        for addr in self._peers:
+        for addr in self._live_peers():
             r = self._call(addr, {"op": "get", "key": key})
             if r is not None:
                 results.append(r.get("r"))
@@ -301,4 +388,4 @@ class DHT:
         return best_plain
 
     def ping_peers(self) -> int:
-        return sum(1 for a in self._peers if self._call(a, {"op": "ping"}) is not None)
+        return sum(1 for a in list(self._peers) if self._call(a, {"op": "ping"}) is not None)

@@ -36,7 +36,20 @@ class SampleRow(C.Structure):
                 ("recent", i32 * 50)]
 
 
+class HopArgs(C.Structure):
+    """Mirror of ``b200_hop_args``."""
+
+    _fields_ = [("x", vp), ("extra", vp), ("ring", vp), ("counter", vp),
+                ("T", i32), ("hidden", i32), ("ldx", i32), ("n_extra", i32),
+                ("depth", i32), ("t_max", i32), ("pairs_per_token", i32), ("timeout_ms", i32), ("pdl", i32)]
+
+
 PROTOTYPES = [
+    ("b200_hop_ring_bytes", [i32, i32, i32], i64),
+    ("b200_hop_send", [C.POINTER(HopArgs), vp], C.c_int),
+    ("b200_hop_recv", [C.POINTER(HopArgs), vp], C.c_int),
+    ("b200_hop_init", [], C.c_int),
+    ("b200_argmax_partial", [vp, i32, i32, i32, vp, vp, vp, vp, i32, i32, vp, vp, i32, vp], C.c_int),
     ("b200_sample_row_bytes", [], i32),
     ("b200_sample", [vp, i32, i32, i32, vp, vp, vp, vp, i32, vp], C.c_int),
     ("b200_decode_mega_plan_bytes", [i32], i64),

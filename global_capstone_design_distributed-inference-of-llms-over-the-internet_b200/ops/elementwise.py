@@ -51,11 +51,20 @@ class ArgmaxWorkspace:
         self.counters = torch.zeros(max_tokens, dtype=torch.int32, device=device)
 
 
-def argmax(logits: torch.Tensor, out_ids: torch.Tensor, ws: ArgmaxWorkspace, pdl: bool = False):
-    assert logits.dtype == torch.float32 and out_ids.dtype == torch.int64
+def argmax(logits: torch.Tensor, out_ids: Optional[torch.Tensor], ws: ArgmaxWorkspace, pdl: bool = False,
+           idx_offset: int = 0, init_pair: Optional[torch.Tensor] = None, out_pair: Optional[torch.Tensor] = None):
+    """First index of the row maximum.  For a vocabulary SHARD: ``idx_offset`` is added to the indices,
+    ``init_pair`` ([T, 2] int32: float bits, index) is another shard's winner to beat (lower index wins ties)
+    and ``out_pair`` receives this shard's winner in the same form."""
+    assert logits.dtype == torch.float32 and (out_ids is None or out_ids.dtype == torch.int64)
     T, V = logits.shape
-    rc = native.lib().b200_argmax(logits.data_ptr(), logits.stride(0), T, V, ws.part_val.data_ptr(),
-                                  ws.part_idx.data_ptr(), ws.counters.data_ptr(), out_ids.data_ptr(), ws.chunks,
-                                  1 if pdl else 0, native.current_stream_ptr())
+    for t in (init_pair, out_pair):
+        assert t is None or (t.dtype == torch.int32 and t.is_contiguous() and t.numel() >= 2 * T)
+    rc = native.lib().b200_argmax_partial(logits.data_ptr(), logits.stride(0), T, V, ws.part_val.data_ptr(),
+                                          ws.part_idx.data_ptr(), ws.counters.data_ptr(),
+                                          out_ids.data_ptr() if out_ids is not None else None, ws.chunks, idx_offset,
+                                          init_pair.data_ptr() if init_pair is not None else None,
+                                          out_pair.data_ptr() if out_pair is not None else None,
+                                          1 if pdl else 0, native.current_stream_ptr())
     native.check(rc, "b200_argmax")
     return out_ids

@@ -39,7 +39,8 @@ class PipelineEngine:
     def __init__(self, model: str, splits: Sequence[int] = (), dtype: torch.dtype = torch.float16, device=None, *,
                  backend: Optional[str] = None, kv_capacity: int = 2048, max_sessions: int = 8, max_chunk: int = 512,
                  seed: int = 0, use_graphs: bool = True, cfg: Optional[ModelConfig] = None,
-                 weight_format: str = "native", tp: int = 1, tp_mode: str = "fused"):
+                 weight_format: str = "native", tp: int = 1, tp_mode: str = "fused", hop: Optional[str] = None,
+                 head_split: Optional[bool] = None, attn_splits: int = 0):
         self.cfg = cfg or resolve_config(model)
         grank = dist.get_rank() if _dist_ready() else 0
         gworld = dist.get_world_size() if _dist_ready() else 1
@@ -74,20 +75,44 @@ class PipelineEngine:
         self.backend = backend or ("native" if self.device.type == "cuda" else "torch")
         self.kv_capacity = kv_capacity
         self.max_sessions = max_sessions
-        w = load_span(model, self.cfg, self.start, self.end, need_embed=self.is_first, need_head=self.is_last,
+        # Decode hops: "p2p" = peer stores + polling kernels captured into each stage's graph (parallel/hop.py),
+        # "nccl" = send/recv issued by the host around the graph (also the CPU/gloo path).  Prefill chunks always
+        # travel over NCCL.  B200_PIPE_HOP overrides the default.
+        import os as _os
+
+        if hop is None:
+            hop = _os.environ.get("B200_PIPE_HOP", "p2p")
+        if self.backend != "native" or self.world == 1 or not use_graphs:
+            hop = "nccl"
+        if hop not in ("p2p", "nccl"):
+            raise ValueError("hop must be 'p2p' or 'nccl'")
+        self.hop = hop
+        # Vocabulary-sharded LM head: the last stage multiplies rows [0, V0) and hands its arg-max candidate and the
+        # final hidden state to stage 0, which multiplies rows [V0, V) at the head of its next step - the head's
+        # weight stream is shared by the two ends of the chain instead of making the last stage the slow one.
+        if head_split is None:
+            head_split = _os.environ.get("B200_HEAD_SPLIT", "1") != "0"
+        self.head_split = bool(head_split) and self.hop == "p2p" and self.world > 1
+        tiles = (self.cfg.vocab + 127) // 128
+        self.v0 = (tiles // 2) * 128
+        need_head = self.is_last or (self.is_first and self.head_split)
+        head_rows = None
+        if self.head_split and need_head:
+            head_rows = (0, self.v0) if self.is_last else (self.v0, self.cfg.vocab)
+        w = load_span(model, self.cfg, self.start, self.end, need_embed=self.is_first, need_head=need_head,
                       dtype=dtype, device=self.device, seed=seed)
         if self.backend == "native" and self.tp > 1:
             from .tensor_parallel import make_tp_span
 
             self.span = make_tp_span(self.cfg, w, self.device, dtype, self.tp_group, mode=tp_mode,
                                      kv_capacity=kv_capacity, max_batch=max_sessions, max_chunk=max_chunk,
-                                     use_graphs=use_graphs)
+                                     use_graphs=use_graphs, head_rows=head_rows, attn_splits=attn_splits)
         elif self.backend == "native":
             from ..runtime.native_span import NativeSpan
 
             self.span = NativeSpan(self.cfg, w, self.device, dtype, kv_capacity=kv_capacity,
                                    max_batch=max_sessions, max_chunk=max_chunk, use_graphs=use_graphs,
-                                   weight_format=weight_format)
+                                   weight_format=weight_format, head_rows=head_rows, attn_splits=attn_splits)
         else:
             from ..models.torch_ref import TorchSpan
 
@@ -119,6 +144,139 @@ class PipelineEngine:
             self._tok_host = self._tok_host.pin_memory()
         self.h2d_bytes = 0
         self.d2h_bytes = 0
+        self.links = None
+        self._tail_pending: dict = {}
+        if self.hop == "p2p":
+            self._init_p2p()
+
+    # ------------------------------------------------------------------ in-graph hops
+    def _init_p2p(self) -> None:
+        from ..runtime.native_span import MAX_DECODE_BATCH, StepProgram
+        from .hop import HopLinks
+
+        sp = self.span
+        H = self.cfg.hidden
+        t_max = min(self.max_sessions, MAX_DECODE_BATCH)
+        self.links = hl = HopLinks(self.device, dist.group.WORLD, H, depth=self.max_sessions + 2, t_max=t_max)
+        nxt = self._g(self.rank + 1) if not self.is_last else -1
+        first = self._g(0)
+        mb = sp.max_batch
+        self._pair = torch.zeros(mb, 2, dtype=torch.int32, device=self.device)      # arg-max candidate (value bits, index)
+        self._h_tail = torch.zeros(mb, H, dtype=self.dtype, device=self.device)     # final hidden state of the chain
+        split = self.head_split
+        if split and self.is_first:
+            sp.head_only_tail = True
+        if split and self.is_last:
+            sp.head_out_pair = self._pair
+
+        def recv_h(B, dry):
+            if not dry:
+                hl.recv_hidden(sp.h_a[:B], pdl=sp.pdl)
+                sp._count()
+
+        def send_h(B, h, dry):
+            if not dry:
+                hl.send_hidden(h, nxt, pdl=sp.pdl)
+                sp._count()
+
+        def send_tail(B, h, dry):
+            if dry:
+                return
+            if split:
+                hl.send_tail(h, self._pair, 2, B, first, pdl=sp.pdl)
+            else:
+                hl.send_tail(None, sp.ids_out.view(torch.int32), 2, B, first, pdl=sp.pdl)
+            sp._count()
+
+        def recv_tail(B, dry):
+            # the new tokens of this micro-batch -> ids_in[:B]
+            if split:
+                if not dry:
+                    hl.recv_tail(self._h_tail[:B], self._pair, 2, B, pdl=sp.pdl)
+                    sp._count()
+                sp._head(self._h_tail[:B], True, out_ids=sp.ids_in[:B], init_pair=self._pair)
+            elif not dry:
+                hl.recv_tail(None, sp.ids_in.view(torch.int32), 2, B, pdl=sp.pdl)
+                sp._count()
+
+        P = StepProgram
+        if self.is_first:
+            self._prog_chain = P("p2p_first_chain", True, pre=recv_tail, post=send_h, head=False)
+            self._prog_host = P("p2p_first_host", True, post=send_h, head=False)
+            self._prog_tail = P("p2p_first_tail", False, pre=recv_tail, layers=False, head=False)
+        elif self.is_last:
+            self._prog_last = P("p2p_last", False, pre=recv_h, post=send_tail)
+            self._prog_last.out_pair = self._pair if split else None
+        else:
+            self._prog_mid = P("p2p_mid", False, pre=recv_h, post=send_h)
+
+    def _collect_slot(self, j0: int) -> None:
+        """Rank 0: receive the tokens the chain produced for the micro-batch starting at slot j0 into _tok."""
+        B = self._tail_pending.pop(j0, 0)
+        if B:
+            self.span.run_program(B, self._prog_tail)
+            self._tok[j0:j0 + B].copy_(self.span.ids_in[:B])
+
+    def _round_p2p(self, tokens, sess, to_host: bool, group: int):
+        S = len(sess)
+        g = max(1, min(int(group), self.links.t_max))
+        sp = self.span
+        for j0 in range(0, S, g):
+            j1 = min(S, j0 + g)
+            B = j1 - j0
+            kv = [self.sessions[si] for si in sess[j0:j1]]
+            if self.is_first:
+                if tokens is not None:
+                    self._collect_slot(j0)             # a token nobody asked for must still leave the ring
+                    self._tok_host[j0:j1] = torch.as_tensor(list(tokens[j0:j1]), dtype=torch.int64)
+                    sp.ids_in[:B].copy_(self._tok_host[j0:j1], non_blocking=True)
+                    self.h2d_bytes += 8 * B
+                    sp.decode(kv, prog=self._prog_host)
+                elif self._tail_pending.get(j0) == B:
+                    self._tail_pending.pop(j0)
+                    sp.decode(kv, prog=self._prog_chain)
+                else:
+                    self._collect_slot(j0)
+                    sp.ids_in[:B].copy_(self._tok[j0:j1])
+                    sp.decode(kv, prog=self._prog_host)
+                self._tail_pending[j0] = B
+            elif self.is_last:
+                sp.decode(kv, prog=self._prog_last)
+            else:
+                sp.decode(kv, prog=self._prog_mid)
+        if self.is_first and to_host:
+            for j0 in range(0, S, g):
+                self._collect_slot(j0)
+            self._tok_host[:S].copy_(self._tok[:S])
+            self.d2h_bytes += 8 * S
+            return [int(x) for x in self._tok_host[:S]]
+        return None
+
+    def _streaming_p2p(self, tokens, sess):
+        S = len(sess)
+        sp = self.span
+        out = [None] * S
+        have_prev = getattr(self, "_streaming_live", False)
+        for j, si in enumerate(sess):
+            kv = [self.sessions[si]]
+            if self.is_first:
+                if self._tail_pending.pop(j, 0):
+                    sp.run_program(1, self._prog_tail)
+                    self._tok_host[j:j + 1].copy_(sp.ids_in[:1])          # D2H of session j's result (blocks on it only)
+                    self.d2h_bytes += 8
+                    out[j] = int(self._tok_host[j])
+                else:
+                    self._tok_host[j] = int(tokens[j])
+                sp.ids_in[:1].copy_(self._tok_host[j:j + 1], non_blocking=True)   # H2D of the step's input
+                self.h2d_bytes += 8
+                sp.decode(kv, prog=self._prog_host)
+                self._tail_pending[j] = 1
+            elif self.is_last:
+                sp.decode(kv, prog=self._prog_last)
+            else:
+                sp.decode(kv, prog=self._prog_mid)
+        self._streaming_live = True
+        return out if (self.is_first and have_prev) else None
 
     # ------------------------------------------------------------------ sessions
     def open_sessions(self, n: int) -> List[int]:
@@ -235,13 +393,23 @@ class PipelineEngine:
                 pending.append((o, dist.isend(o, self._g(self.rank + 1))))
         for _, w in pending:
             w.wait()
-        if self.is_last:
-            tok.copy_(out[1].reshape(-1)[:1])
-            if not self.is_first:
-                self._send(tok, 0, self.tok_group)
-        if self.is_first:
-            if not self.is_last:
+        if self.head_split:
+            # vocabulary-sharded head: the last stage's candidate and the final hidden row go to stage 0
+            if self.is_last:
+                self._send(self.span.last_hidden.contiguous(), 0, self.tok_group)
+                self._send(self._pair[:1], 0, self.tok_group)
+            if self.is_first:
+                self._recv(self._h_tail[:1], self.world - 1, self.tok_group)
+                self._recv(self._pair[:1], self.world - 1, self.tok_group)
+                self.span._head(self._h_tail[:1], True, out_ids=tok, init_pair=self._pair)
+        else:
+            if self.is_last:
+                tok.copy_(out[1].reshape(-1)[:1])
+                if not self.is_first:
+                    self._send(tok, 0, self.tok_group)
+            if self.is_first and not self.is_last:
                 self._recv(tok, self.world - 1, self.tok_group)
+        if self.is_first:
             self.d2h_bytes += 8
             return int(tok.cpu()[0])
         return None
@@ -256,6 +424,8 @@ class PipelineEngine:
         """
         sess = list(range(len(self.sessions))) if sessions is None else list(sessions)
         S = len(sess)
+        if self.hop == "p2p":
+            return self._round_p2p(tokens, sess, to_host, group)
         if self.world == 1 and tokens is not None and to_host and self.backend == "native":
             # Single-GPU host loop, the latency path: the pinned token buffer is copied straight into the captured
             # graph's input and the result straight out of its output - no device-to-device staging in between.
@@ -344,6 +514,8 @@ class PipelineEngine:
         S = len(sess)
         if self.world == 1:
             return self.decode_round(tokens, sessions)
+        if self.hop == "p2p":
+            return self._streaming_p2p(tokens, sess)
         last = self.world - 1
         out = [None] * S
         have_prev = getattr(self, "_streaming_live", False)
@@ -391,6 +563,15 @@ class PipelineEngine:
         """Collect the tokens of the last streaming round (rank 0) and leave streaming mode."""
         S = len(self.sessions) if sessions is None else len(sessions)
         out = None
+        if self.hop == "p2p":
+            if self.is_first and getattr(self, "_streaming_live", False):
+                for j in sorted(self._tail_pending):
+                    self._collect_slot(j)
+                self._tok_host[:S].copy_(self._tok[:S])
+                self.d2h_bytes += 8 * S
+                out = [int(x) for x in self._tok_host[:S]]
+            self._streaming_live = False
+            return out
         if self.is_first and self.world > 1 and getattr(self, "_streaming_live", False):
             for j in range(S):
                 self._wait(self._tok_work[j])
@@ -403,6 +584,11 @@ class PipelineEngine:
 
     def drain(self) -> None:
         """Wait for every outstanding p2p operation (call before reading staging buffers directly)."""
+        if self.hop == "p2p":
+            if self.is_first:
+                for j in sorted(self._tail_pending):      # tokens still in the ring -> _tok
+                    self._collect_slot(j)
+            return
         for lst in (self._send_work, self._tok_work):
             for j, w in enumerate(lst):
                 self._wait(w)

@@ -71,11 +71,25 @@ def _mega_default() -> bool:
 MEGA_MAX_TOKENS = 16
 
 
+class StepProgram:
+    """What a captured decode step does AROUND the blocks (the pipeline engine's in-graph hops).
+
+    ``pre(B, dry)`` runs before the embedding / blocks (e.g. receive the hidden state into ``h_a``, or receive the
+    previous token), ``post(B, h, dry)`` after the blocks and the head (e.g. send ``h`` to the next stage).  Both
+    are called once with ``dry=True`` outside the capture (warm-up: they must not touch a link then) and once
+    inside it.  ``layers=False`` makes a step that only runs ``pre``; ``head=False`` skips the span's own head
+    after the blocks (a first stage that only holds a shard of the head for the NEXT token's arg-max)."""
+
+    def __init__(self, key, from_ids: bool, pre=None, post=None, layers: bool = True, head: bool = True):
+        self.key, self.from_ids, self.pre, self.post, self.layers, self.head = key, from_ids, pre, post, layers, head
+
+
 class NativeSpan:
     def __init__(self, cfg: ModelConfig, weights: Dict[str, object], device, dtype: torch.dtype, *,
                  kv_capacity: int = 2048, max_batch: int = 8, max_chunk: int = 512, attn_splits: int = 0,
                  use_graphs: bool = True, pdl: Optional[bool] = None, free_source_weights: bool = True,
-                 use_mega: Optional[bool] = None, mega_grid: int = 0, weight_format: str = "native"):
+                 use_mega: Optional[bool] = None, mega_grid: int = 0, weight_format: str = "native",
+                 head_rows: Optional[tuple] = None):
         assert dtype in (torch.float16, torch.bfloat16), "native path runs fp16/bf16"
         self.cfg, self.device, self.dtype = cfg, torch.device(device), dtype
         self.kv_capacity, self.max_batch, self.max_chunk = kv_capacity, min(max_batch, MAX_DECODE_BATCH), max_chunk
@@ -117,10 +131,17 @@ class NativeSpan:
                         L.pop(k, None)
             self.embed_w = weights.get("embed") if self.has_embed else None
             self.pos_embed_w = weights.get("pos_embed") if self.has_embed else None
+            # head_rows = (lo, hi): this span holds only rows [lo, hi) of the LM head (a vocabulary shard; lo must
+            # sit on a 128-row tile boundary); its arg-max reports indices with lo added.
+            self.head_lo, self.head_hi = (0, c.vocab) if head_rows is None else (int(head_rows[0]), int(head_rows[1]))
             if self.has_head:
                 self.final_norm_w = weights["final_norm_w"]
                 self.final_norm_b = weights.get("final_norm_b")
-                self.lm_head = pack_w(weights["lm_head"])  # type: ignore[arg-type]
+                assert self.head_lo % 128 == 0 and 0 <= self.head_lo < self.head_hi <= c.vocab
+                hw = weights["lm_head"]
+                if head_rows is not None:
+                    hw = hw[self.head_lo:self.head_hi]  # type: ignore[index]
+                self.lm_head = pack_w(hw)  # type: ignore[arg-type]
             self.inv_freq = (A.rope_inv_freq(c.head_dim, c.rope_theta, c.rope_scaling, self.device)
                              if c.is_llama else None)
             self.scale = 1.0 / math.sqrt(c.head_dim)
@@ -148,7 +169,7 @@ class NativeSpan:
             self._pos_ring_idx = 0
             self._ptr_tables: Dict[tuple, torch.Tensor] = {}
             if self.has_head:
-                self.logits = mk(self.max_batch, c.vocab, dt=torch.float32)
+                self.logits = mk(self.max_batch, self.head_hi - self.head_lo, dt=torch.float32)
                 self.ids_out = torch.zeros(self.max_batch, dtype=torch.int64, device=self.device)
                 self.argmax_ws = E.ArgmaxWorkspace(self.device, self.max_batch)
         self._graphs: Dict[tuple, torch.cuda.CUDAGraph] = {}
@@ -272,8 +293,11 @@ class NativeSpan:
             self._count(5)
         return h
 
-    def _head(self, h_rows: torch.Tensor, greedy: bool) -> torch.Tensor:
-        """h_rows: [B<=32, H] -> logits [B, V] fp32 (and ids_out when greedy)."""
+    def _head(self, h_rows: torch.Tensor, greedy: bool, out_ids: Optional[torch.Tensor] = None,
+              init_pair: Optional[torch.Tensor] = None, out_pair: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """h_rows: [B<=32, H] -> logits [B, V (or this span's vocabulary shard)] fp32 (and ids_out when greedy).
+
+        ``init_pair`` / ``out_pair``: arg-max candidates exchanged between vocabulary shards (see ops.elementwise.argmax)."""
         c = self.cfg
         B = h_rows.shape[0]
         logits = self.logits[:B]
@@ -281,7 +305,9 @@ class NativeSpan:
                  norm_b=self.final_norm_b, norm_eps=c.norm_eps, out_fp32=True, workspace=self.ws, pdl=self.pdl)
         self._count()
         if greedy:
-            E.argmax(logits, self.ids_out[:B], self.argmax_ws, pdl=self.pdl)
+            ids = self.ids_out[:B] if out_ids is None else out_ids
+            E.argmax(logits, ids, self.argmax_ws, pdl=self.pdl, idx_offset=self.head_lo, init_pair=init_pair,
+                     out_pair=out_pair)
             self._count()
         return logits
 
@@ -339,13 +365,20 @@ class NativeSpan:
         self._stage_ptrs(kvs)
         self._prestaged = tuple((kv.data.data_ptr(), kv.length) for kv in kvs)
 
-    def _decode_body(self, B: int, from_ids: bool, greedy: bool):
+    def _decode_body(self, B: int, from_ids: bool, greedy: bool, prog: Optional[StepProgram] = None, dry: bool = False):
+        if prog is not None and prog.pre is not None:
+            prog.pre(B, dry)
+        if prog is not None and not prog.layers:
+            return None
         h = self._embed(B, 0, True) if from_ids else self.h_a[:B]
-        if self.use_mega and B <= MEGA_MAX_TOKENS and self.tp_mode is None and self.weight_format == "native":
+        if (self.use_mega and B <= MEGA_MAX_TOKENS and self.tp_mode is None and self.weight_format == "native"
+                and prog is None):
             return self._decode_mega(B, h, greedy)
         h = self._decode_layers(B, h)
-        if self.has_head:
-            self._head(h, greedy)
+        if self.has_head and (prog is None or prog.head):
+            self._head(h, greedy, out_pair=getattr(prog, "out_pair", None) if prog is not None else None)
+        if prog is not None and prog.post is not None:
+            prog.post(B, h, dry)
         return h
 
     # ------------------------------------------------------------------ persistent decode kernel
@@ -411,7 +444,7 @@ class NativeSpan:
         return self.h_a[:B]
 
     def decode(self, kvs: Sequence[SessionKV], h_in: Optional[torch.Tensor] = None,
-               ids: Optional[torch.Tensor] = None, greedy: bool = True):
+               ids: Optional[torch.Tensor] = None, greedy: bool = True, prog: Optional[StepProgram] = None):
         """One token for each session in ``kvs``.
 
         First stage: pass ``ids`` (int64 device tensor [B]) or leave ``ids_in`` pre-filled (e.g. by
@@ -420,41 +453,54 @@ class NativeSpan:
         ``(logits [B, V] fp32, ids_out [B] int64)`` device views.
         """
         with nvtx_range("b200.decode_step"):
-            return self._decode_impl(kvs, h_in, ids, greedy)
+            return self._decode_impl(kvs, h_in, ids, greedy, prog)
 
-    def _decode_impl(self, kvs, h_in, ids, greedy):
+    def run_program(self, B: int, prog: StepProgram) -> None:
+        """Replay a step that touches no session (``prog.layers`` is False), e.g. 'receive the token of slot j'."""
+        assert not prog.layers
+        key = (B, False, True, prog.key)
+        g = self._graphs.get(key) if self.use_graphs else None
+        if g is None and self.use_graphs:
+            g = self._capture(key, prog)
+        if g is not None:
+            g.replay()
+            self.kernel_launches += self._launches_per_graph[key]
+        else:
+            self._decode_body(B, False, True, prog)
+
+    def _decode_impl(self, kvs, h_in, ids, greedy, prog=None):
         B = len(kvs)
         assert 1 <= B <= self.max_batch
-        from_ids = self.embed_w is not None and h_in is None
+        from_ids = (self.embed_w is not None and h_in is None) if prog is None else bool(prog.from_ids)
         staged = getattr(self, "_prestaged", None)
         self._prestaged = None
         if staged is None or staged != tuple((kv.data.data_ptr(), kv.length) for kv in kvs):
             self._stage_ptrs(kvs)
-        key = (B, from_ids, greedy)
+        key = (B, from_ids, greedy) if prog is None else (B, from_ids, greedy, prog.key)
         g = None
         if self.use_graphs:
             g = self._graphs.get(key)
             if g is None:
-                g = self._capture(key)   # runs the body once on whatever the buffers hold
+                g = self._capture(key, prog)   # runs the body once on whatever the buffers hold
         if from_ids and ids is not None:
             self.ids_in[:B].copy_(ids, non_blocking=True)
-        if not from_ids:
+        if not from_ids and h_in is not None:
             self.h_a[:B].copy_(h_in, non_blocking=True)
         if g is not None:
             g.replay()
             self.kernel_launches += self._launches_per_graph[key]
             out_h = self._graph_out[key]
         else:
-            out_h = self._decode_body(B, from_ids, greedy)
+            out_h = self._decode_body(B, from_ids, greedy, prog)
         for kv in kvs:
             kv.length += 1
             kv.touch()
-        if self.has_head:
+        if self.has_head and (prog is None or prog.head):
             return self.logits[:B], self.ids_out[:B]
         return out_h
 
-    def _capture(self, key) -> torch.cuda.CUDAGraph:
-        B, from_ids, greedy = key
+    def _capture(self, key, prog: Optional[StepProgram] = None) -> torch.cuda.CUDAGraph:
+        B, from_ids, greedy = key[:3]
         if not hasattr(self, "_graph_out"):
             self._graph_out = {}
         # warm-up outside capture (sets kernel attributes, loads modules)
@@ -462,13 +508,14 @@ class NativeSpan:
         s = torch.cuda.Stream(device=self.device)
         s.wait_stream(torch.cuda.current_stream(self.device))
         with torch.cuda.stream(s):
-            self._decode_body(B, from_ids, greedy)
+            self._decode_body(B, from_ids, greedy, prog, dry=True)
         torch.cuda.current_stream(self.device).wait_stream(s)
         torch.cuda.synchronize(self.device)
-        per = self.kernel_launches - before
         g = torch.cuda.CUDAGraph()
+        self.kernel_launches = before
         with torch.cuda.graph(g, stream=s):
-            out_h = self._decode_body(B, from_ids, greedy)
+            out_h = self._decode_body(B, from_ids, greedy, prog)
+        per = self.kernel_launches - before
         self.kernel_launches = before  # warm-up + capture passes touched KV slot `pos` twice; harmless: same data
         self._graphs[key] = g
         self._graph_out[key] = out_h
@@ -533,6 +580,10 @@ class NativeSpan:
         return self.hist[:n_steps, :B]
 
     # ------------------------------------------------------------------ prefill
+    head_only_tail = False # True on a first stage whose head shard serves the END of the chain (see PipelineEngine)
+    last_hidden = None     # [1, H] view: final hidden row of the latest prefill on a span with a head
+    head_out_pair = None   # [B, 2] int32: where the head's arg-max leaves its (value, index) candidate (vocabulary shards)
+
     def prefill(self, kv: SessionKV, h_in: Optional[torch.Tensor] = None, ids: Optional[torch.Tensor] = None,
                 pos0: Optional[int] = None, greedy: bool = True):
         """Append T tokens of one session (chunked to ``max_chunk``).
@@ -548,7 +599,8 @@ class NativeSpan:
             raise ValueError(f"session {kv.session_id}: {pos0}+{T} tokens exceed max_length {kv.max_len}")
         if kv.max_len != self.kv_capacity:
             raise ValueError(f"session capacity {kv.max_len} != engine kv_capacity {self.kv_capacity}")
-        out = None if self.has_head else torch.empty(T, c.hidden, dtype=self.dtype, device=self.device)
+        tail_only = self.head_only_tail     # a first stage that holds a head shard for the chain's tail
+        out = None if (self.has_head and not tail_only) else torch.empty(T, c.hidden, dtype=self.dtype, device=self.device)
         last_h = None
         for c0 in range(0, T, self.max_chunk):
             n = min(self.max_chunk, T - c0)
@@ -594,8 +646,9 @@ class NativeSpan:
             last_h = h[n - 1:n]
         kv.length = pos0 + T
         kv.touch()
-        if self.has_head:
-            self._head(last_h, greedy)
+        if self.has_head and not tail_only:
+            self.last_hidden = last_h
+            self._head(last_h, greedy, out_pair=self.head_out_pair)
             return self.logits[:1], self.ids_out[:1]
         return out
 

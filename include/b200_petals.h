@@ -243,6 +243,44 @@ int b200_norm(const void* x, const void* w, const void* b, void* out, int32_t T,
 int b200_argmax(const float* logits, int32_t ld, int32_t T, int32_t V, float* part_val, int32_t* part_idx,
                 int32_t* counters, void* out_ids, int32_t chunks, int32_t pdl, void* stream);
 
+/* Arg-max over one SHARD of the vocabulary (vocab-sharded LM head): indices are reported with `idx_offset` added,
+ * `init_pair` (T x {float bits, int32 index}, or NULL) is a candidate from another shard that the shard's own
+ * maximum has to beat (ties go to the lower index, as torch.argmax would on the whole row), and `out_pair`
+ * (T x 2 words, or NULL) receives the winning (value, index) so that the next shard can continue.  out_ids may be NULL. */
+int b200_argmax_partial(const float* logits, int32_t ld, int32_t T, int32_t V, float* part_val, int32_t* part_idx,
+                        int32_t* counters, void* out_ids, int32_t chunks, int32_t idx_offset, const void* init_pair,
+                        void* out_pair, int32_t pdl, void* stream);
+
+/* ---------------------------------------------------------- pipeline hop --
+ * Hidden-state handoff between two pipeline stages on different GPUs of one NVSwitch box, made of two small
+ * kernels that are captured into the stages' CUDA graphs: b200_hop_send (last node of the producer's graph) writes
+ * the micro-batch into a ring in the RECEIVER's memory with peer stores over NVLink, each 4-byte payload paired
+ * with the message number in one 8-byte word; b200_hop_recv (first node of the consumer's graph) polls its own
+ * memory until the whole message carries the expected number and unpacks it.  No host, no flag, no fence, no
+ * library call on the per-token path.  Replaces the reference's hop through the client:
+ * src/rpc_transport.py:736-766 (GPU -> CPU -> serialize -> libp2p -> deserialize -> GPU, twice per stage).
+ *   ring     b200_hop_ring_bytes(depth, t_max, pairs_per_token) bytes in the receiver's memory, zeroed once; the
+ *            sender passes the peer-mapped address (e.g. torch symmetric memory), the receiver its local one.
+ *            Message n uses entry n % depth: depth must exceed the number of messages the link can have in flight.
+ *   counter  one int per link END (sender and receiver each own one, both start at 0, local memory).
+ *   x        [T, hidden] 16-bit rows (send: source, recv: destination), row stride ldx elements; hidden may be 0.
+ *   extra    [T, n_extra] 32-bit words that travel with each token (token ids, arg-max partials), or NULL.
+ * A receive that sees nothing for timeout_ms (0 = 30 s) prints a message and traps instead of hanging the GPU. */
+typedef struct b200_hop_args {
+    void* x;
+    void* extra;
+    void* ring;
+    int32_t* counter;
+    int32_t T, hidden, ldx, n_extra;
+    int32_t depth, t_max, pairs_per_token;
+    int32_t timeout_ms, pdl;
+} b200_hop_args;
+int64_t b200_hop_ring_bytes(int32_t depth, int32_t t_max, int32_t pairs_per_token);
+int b200_hop_send(const b200_hop_args* args, void* stream);
+int b200_hop_recv(const b200_hop_args* args, void* stream);
+/* Loads the two kernels on the current device (call once before capturing them into a graph). */
+int b200_hop_init(void);
+
 /* Temperature / top-k / top-p / repetition-penalty sampling on the device with the reference's rules
  * (src/rpc_handler.py:327-403), one CTA per row, no sort (radix descent over float bit patterns).
  * rows: T records {float temperature, top_p, penalty; int32 top_k, n_recent; int32 recent[50]} on the

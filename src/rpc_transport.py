@@ -241,6 +241,18 @@ class RpcTransport:
                             self.push = False          # finish this session hop by hop
                             time.sleep(0.2)
                             continue
+                        if dead is None:
+                            # every server of the chain answers: the error was transient and came from some hop
+                            # at or after i, but hops [i, failing) have already appended this step.  Nobody is to
+                            # blame; rebuild the whole suffix from hop i's journal (a replayed prefill resets each
+                            # cache) and resend the step hop by hop.
+                            self._replay(session_id, route[i:], hop.key)
+                            self.recoveries += 1
+                            self.push = False
+                            metrics.emit("recovery", session=session_id, hop=hop.key, peer=hop.peer_id[:12],
+                                         error="transient downstream error: " + str(e)[:160])
+                            time.sleep(0.2)
+                            continue
                     self.failed_peers.setdefault(hop.key, set()).add(hop.peer_id)
                     logger.info("Marked peer %s as failed for %s", hop.peer_id[:12], hop.key)
                     metrics.emit("recovery", session=session_id, hop=hop.key, peer=hop.peer_id[:12], error=str(e)[:200])
@@ -293,6 +305,9 @@ class RpcTransport:
 
     # ------------------------------------------------------------------ public API (reference names)
     def send_prefill(self, L: int, hidden: torch.Tensor, session_id: str, max_length: int) -> None:
+        # a prefill starts the session over on every server (fresh cache), so the journal starts over too:
+        # a later replay must not rebuild "old session + new prompt"
+        self.client_cache.pop(session_id, None)
         self.session_max_length[session_id] = int(max_length)
         self._send(session_id, hidden, L, True, None)
 

@@ -103,3 +103,89 @@ def test_kv_length_mismatch_is_an_error_not_a_warning():
         c.close()
     finally:
         h.stop()
+
+
+def test_push_chain_transient_error_downstream_is_recovered():
+    """Three server stages, servers push to each other; the LAST one fails one request with a server-side error
+    while every server stays alive.  The stages before it have already consumed the step, so the client must
+    rebuild the whole suffix (not blame the first hop) and still produce the undisturbed tokens."""
+    from src.main import parse_splits, run_rank0
+
+    model, splits = "tiny-llama-gqa", "1,2,3"
+    cuts = parse_splits(splits)
+    dev = torch.device("cpu")
+    handles = []
+    try:
+        first = _start(model, splits, cuts, 1, "")
+        peers = first.dht.get_visible_maddrs()[0]
+        handles = [first, _start(model, splits, cuts, 2, peers), _start(model, splits, cuts, 3, peers)]
+        ref, _ = run_rank0(_args(model, splits, 0, peers, seed=11, max_new_tokens=8), dev, cuts)
+        last = handles[2]
+        assert last.handler.final_stage
+        base = last.handler.requests
+
+        def arm():                       # fail the 4th request of the next run (a decode step)
+            import time
+            while last.handler.requests < base + 3:
+                time.sleep(0.005)
+            last.handler.fail_next = 1
+
+        t = threading.Thread(target=arm, daemon=True)
+        t.start()
+        out, stats = run_rank0(_args(model, splits, 0, peers, seed=11, max_new_tokens=8, push=True,
+                                     request_timeout=5.0), dev, cuts)
+        assert stats["recoveries"] >= 1
+        assert out == ref
+    finally:
+        for h in handles:
+            try:
+                h.stop()
+            except Exception:
+                pass
+
+
+def test_registry_survives_the_bootstrap_node():
+    """Servers learn of each other through the bootstrap node; when it dies mid-generation the survivors keep
+    announcing to each other and the client (which has talked to the swarm) still finds a replacement."""
+    from src.main import parse_splits, run_rank0
+
+    model, splits = "tiny-llama-gqa", "2"
+    cuts = parse_splits(splits)
+    dev = torch.device("cpu")
+    handles = []
+    try:
+        boot = _start(model, splits, cuts, 1, "")
+        peers = boot.dht.get_visible_maddrs()[0]
+        a = _start(model, splits, cuts, 1, peers)
+        # b is bootstrapped from a (not from the bootstrap node): discovery must be transitive
+        b = _start(model, splits, cuts, 1, a.dht.get_visible_maddrs()[0])
+        handles = [boot, a, b]
+        assert len(b.dht.known_peers()) >= 3 and len(boot.dht.known_peers()) >= 3
+        ref, _ = run_rank0(_args(model, splits, 0, peers, seed=11, max_new_tokens=8), dev, cuts)
+        # the bootstrap node (DHT + stage server) dies while serving its 3rd request, whichever replica is in use
+        fired = []
+        for h in handles:
+            h.handler.die_after = h.handler.requests + 3
+            h.handler.die_guard = lambda: (not fired) and (fired.append(1) or True)
+        boot.handler.on_die = lambda: boot.stop(announce=False)
+        # the client joins through `a`, the registry's bootstrap node goes away under it
+        boot_only = boot.dht
+        out, stats = run_rank0(_args(model, splits, 0, a.dht.get_visible_maddrs()[0], seed=11, max_new_tokens=8,
+                                     request_timeout=5.0), dev, cuts)
+        assert out == ref
+        boot.stop(announce=False)
+        del boot_only
+        # with the bootstrap node gone, a fresh client that only knows `b` still sees `a`'s record
+        from petals_b200.net.dht import DHT
+        from src.dht_utils import get_stage_entries
+
+        c = DHT(start=True, initial_peers=[b.dht.get_visible_maddrs()[0]], client_mode=True)
+        ids = {str(e.get("peer_id")) for e in get_stage_entries(c, 1)}
+        assert str(a.peer_id) in ids and str(b.peer_id) in ids
+        c.shutdown()
+    finally:
+        for h in handles:
+            try:
+                h.stop()
+            except Exception:
+                pass

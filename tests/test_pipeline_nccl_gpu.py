@@ -1,4 +1,6 @@
-"""2-GPU NCCL chain (native kernels) must reproduce the single-GPU tokens exactly."""
+"""Multi-GPU pipeline chains (native kernels) must reproduce the single-GPU tokens exactly, whichever way the
+hidden state travels: host-issued NCCL send/recv, or the peer-store hops captured into the stages' graphs, with
+the LM head on the last stage or sharded over the two ends of the chain."""
 import os
 import socket
 import sys
@@ -9,6 +11,8 @@ import torch.multiprocessing as mp
 
 pytestmark = pytest.mark.gpu
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+MODES = [("nccl", False), ("p2p", False), ("p2p", True)]
 
 
 def _free_port():
@@ -21,7 +25,26 @@ def _free_port():
 
 def _prompts(vocab):
     g = torch.Generator().manual_seed(0)
-    return [torch.randint(0, vocab, (n,), generator=g) for n in (40, 9)]
+    return [torch.randint(0, vocab, (n,), generator=g) for n in (40, 9, 17, 33)]
+
+
+def _device_loop(eng, prompts, n_steps, group):
+    """Prefill, then n_steps rounds with the tokens fed back on the device; returns [steps+1][sessions] on rank 0."""
+    eng.close_sessions()
+    ids = eng.open_sessions(len(prompts))
+    first = [eng.prefill(i, p) for i, p in zip(ids, prompts)]
+    if eng.is_first:
+        eng._tok[:len(ids)].copy_(torch.tensor(first, dtype=torch.int64))
+    rows = [first]
+    for _ in range(n_steps):
+        if eng.world == 1:
+            rows.append(eng.decode_round(rows[-1]))
+        else:
+            eng.decode_round(None, to_host=False, group=group)
+            eng.drain()
+            if eng.is_first:
+                rows.append([int(x) for x in eng._tok[:len(ids)].cpu()])
+    return rows
 
 
 def _worker(rank, world, port, model, splits, q):
@@ -34,32 +57,68 @@ def _worker(rank, world, port, model, splits, q):
     torch.cuda.set_device(rank)
     dev = torch.device("cuda", rank)
     dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
-    eng = PipelineEngine(model, splits, torch.bfloat16, dev, kv_capacity=256, max_sessions=4, seed=5)
-    res = eng.generate(_prompts(eng.cfg.vocab), 10)
+    out = {}
+    for hop, split in MODES:
+        eng = PipelineEngine(model, splits, torch.bfloat16, dev, kv_capacity=256, max_sessions=4, seed=5, hop=hop,
+                             head_split=split)
+        assert eng.hop == hop and eng.head_split == split
+        prompts = _prompts(eng.cfg.vocab)
+        res = eng.generate(prompts[:2], 10)
+        res_s = eng.generate(prompts[:2], 10, streaming=True)
+        loop1 = _device_loop(eng, prompts, 6, 1)
+        loop2 = _device_loop(eng, prompts, 6, 2)
+        if rank == 0:
+            out[(hop, split)] = (res[0], res_s[0], loop1, loop2)
+        dist.barrier()
+        del eng
     if rank == 0:
-        q.put(res[0])
+        q.put(out)
     dist.barrier()
     dist.destroy_process_group()
 
 
-@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs")
-def test_two_stage_nccl_chain_token_exact():
+def _reference(model):
     sys.path.insert(0, ROOT)
     from petals_b200.parallel.pipeline import PipelineEngine
 
-    model = "tiny-llama-gqa"
     torch.cuda.set_device(0)
     eng = PipelineEngine(model, [], torch.bfloat16, torch.device("cuda", 0), kv_capacity=256, max_sessions=4, seed=5)
-    ref = eng.generate(_prompts(eng.cfg.vocab), 10)[0]
+    prompts = _prompts(eng.cfg.vocab)
+    ref = eng.generate(prompts[:2], 10)[0]
+    loop = _device_loop(eng, prompts, 6, 1)
     del eng
+    return ref, loop
+
+
+def _chain(world, model, splits):
+    ref, ref_loop = _reference(model)
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
     port = _free_port()
-    procs = [ctx.Process(target=_worker, args=(r, 2, port, model, [2], q)) for r in range(2)]
+    procs = [ctx.Process(target=_worker, args=(r, world, port, model, splits, q)) for r in range(world)]
     for p in procs:
         p.start()
-    out = q.get(timeout=300)
+    out = q.get(timeout=600)
     for p in procs:
-        p.join(timeout=60)
+        p.join(timeout=120)
         assert p.exitcode == 0
-    assert out == ref
+    for mode, (res, res_s, loop1, loop2) in out.items():
+        assert res == ref, f"{mode}: generate() differs from one GPU"
+        assert res_s == ref, f"{mode}: streaming generate() differs from one GPU"
+        assert loop1 == ref_loop, f"{mode}: device loop differs from one GPU"
+        assert loop2 == ref_loop, f"{mode}: device loop with micro-batches of 2 differs from one GPU"
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs")
+def test_two_stage_chain_token_exact():
+    _chain(2, "tiny-llama-gqa", [2])
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 4, reason="needs 4 GPUs")
+def test_four_stage_chain_token_exact():
+    _chain(4, "tiny-llama-gqa", [1, 2, 3])
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs")
+def test_two_stage_chain_gpt2_token_exact():
+    _chain(2, "tiny-gpt2", [2])
