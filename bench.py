@@ -144,7 +144,7 @@ def run_b200(args):
         cap = max(cap, max(ttft_lens) + 64)
     cap = (cap + 255) // 256 * 256
     eng = PipelineEngine(args.model, even_splits(cfg.n_layers, stages), dtype, dev, kv_capacity=cap,
-                         max_sessions=max(S, 1), max_chunk=512, seed=0, weight_format=args.weights, tp=args.tp,
+                         max_sessions=max(S, 1), max_chunk=2048 if stages == 1 else 512, seed=0, weight_format=args.weights, tp=args.tp,
                          tp_mode=args.tp_mode, hop=args.hop,
                          head_split=None if args.head_split is None else bool(args.head_split))
     sess = eng.open_sessions(S)

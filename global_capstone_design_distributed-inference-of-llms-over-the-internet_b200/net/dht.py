@@ -242,10 +242,11 @@ class DHT:
         self._thread.start()
 
     def shutdown(self) -> None:
-        if self._server is not None:
-            self._server.shutdown()
-            self._server.server_close()
-            self._server = None
+        with self._peer_lock:                      # idempotent, also when two threads stop the node at once
+            server, self._server = self._server, None
+        if server is not None:
+            server.shutdown()
+            server.server_close()
         with self._conn_lock:
             for s in self._conns.values():
                 try:

@@ -14,6 +14,12 @@ The server accepts connections on an asyncio loop in a background thread and run
 handlers on a single worker thread, so GPU work never blocks heartbeats.
 Large payloads need no separate streaming RPC on TCP; ``rpc_forward_stream`` is the same
 handler under a second name for wire-level parity.
+
+Streams: a method registered with ``add_stream_handler`` owns its connection for as long as it
+runs - the handler gets a ``stream`` object with ``recv(timeout)`` / ``send(tensors, metadata)``
+and exchanges any number of frames with the client before it returns (its return value is the
+closing frame).  This carries the per-session ``rpc_inference`` protocol of upstream Petals
+(petals/server/handler.py:132-195); the client side is ``RpcClient.open_stream``.
 """
 from __future__ import annotations
 
@@ -89,13 +95,21 @@ class RpcServer:
         self._loop: Optional[asyncio.AbstractEventLoop] = None
         self._thread: Optional[threading.Thread] = None
         self._server = None
-        self._pool = cf.ThreadPoolExecutor(max_workers=1, thread_name_prefix="rpc-compute")
+        # Handlers mostly WAIT (for the stage's task pool, for the next hop): many may be in flight at once, the
+        # compute itself is serialised - and batched - by the stage's own task pool thread.
+        self._pool = cf.ThreadPoolExecutor(max_workers=64, thread_name_prefix="rpc-handler")
+        self._stream_pool = cf.ThreadPoolExecutor(max_workers=256, thread_name_prefix="rpc-stream")
+        self.stream_handlers: Dict[str, Callable] = {}
         self._ready = threading.Event()
         self.drop_next = 0          # fault injection: close the connection instead of answering
         self.requests_served = 0
 
     def add_handler(self, name: str, fn: Handler) -> None:
         self.handlers[name] = fn
+
+    def add_stream_handler(self, name: str, fn: Callable) -> None:
+        """``fn(uid, tensors, metadata, stream) -> (tensors, metadata)``; see the module docstring."""
+        self.stream_handlers[name] = fn
 
     def start(self) -> "RpcServer":
         self._thread = threading.Thread(target=self._run, name="rpc-server", daemon=True)
@@ -133,6 +147,21 @@ class RpcServer:
                     self.drop_next -= 1
                     break
                 header, tensors = unpack_frame(hb, payload)
+                sfn = self.stream_handlers.get(header.get("method", ""))
+                if sfn is not None:
+                    stream = _ServerStream(self._loop, reader, writer, header["method"], header.get("uid", ""))
+                    try:
+                        res_t, res_md = await self._loop.run_in_executor(
+                            self._stream_pool, sfn, header.get("uid", ""), tensors, header.get("metadata") or {}, stream)
+                        out = pack_frame(header["method"], header.get("uid", ""), res_md, res_t)
+                    except Exception as e:  # noqa: BLE001
+                        out = pack_frame(header["method"], header.get("uid", ""), {}, [], error=f"{type(e).__name__}: {e}")
+                    self.requests_served += 1
+                    writer.write(out)
+                    await writer.drain()
+                    if stream.broken:
+                        break
+                    continue
                 fn = self.handlers.get(header.get("method", ""))
                 if fn is None:
                     out = pack_frame(header.get("method", ""), header.get("uid", ""), {}, [],
@@ -179,6 +208,7 @@ class RpcServer:
         if self._thread is not None:
             self._thread.join(timeout=5)
         self._pool.shutdown(wait=False, cancel_futures=True)
+        self._stream_pool.shutdown(wait=False, cancel_futures=True)
         self._loop = None
 
     @property
@@ -186,8 +216,119 @@ class RpcServer:
         return ("127.0.0.1" if self.host in ("0.0.0.0", "") else self.host), self.port
 
 
+class _ServerStream:
+    """The handler thread's view of its connection: blocking frame I/O executed on the server's event loop."""
+
+    def __init__(self, loop, reader, writer, method: str, uid: str):
+        self._loop, self._reader, self._writer, self.method, self.uid = loop, reader, writer, method, uid
+        self.broken = False
+
+    async def _read(self):
+        raw = await self._reader.readexactly(_HDR.size)
+        magic, hl, pl = _HDR.unpack(raw)
+        if magic != MAGIC or hl + pl > MAX_FRAME:
+            raise ConnectionError("bad frame")
+        hb = await self._reader.readexactly(hl)
+        payload = await self._reader.readexactly(pl) if pl else b""
+        return unpack_frame(hb, payload)
+
+    async def _write(self, frame: bytes):
+        self._writer.write(frame)
+        await self._writer.drain()
+
+    def recv(self, timeout: Optional[float] = None) -> Tuple[List[torch.Tensor], dict]:
+        fut = asyncio.run_coroutine_threadsafe(self._read(), self._loop)
+        try:
+            header, tensors = fut.result(timeout)
+        except cf.TimeoutError:
+            fut.cancel()
+            self.broken = True          # a frame may be half read: the connection cannot be reused
+            raise TimeoutError("no message on the stream") from None
+        except (asyncio.IncompleteReadError, ConnectionError, OSError, asyncio.CancelledError) as e:
+            self.broken = True
+            raise ConnectionError(f"stream closed: {e}") from None
+        return tensors, header.get("metadata") or {}
+
+    def send(self, tensors: List[torch.Tensor], metadata: dict) -> None:
+        frame = pack_frame(self.method, self.uid, metadata, tensors)
+        try:
+            asyncio.run_coroutine_threadsafe(self._write(frame), self._loop).result(30)
+        except Exception as e:  # noqa: BLE001
+            self.broken = True
+            raise ConnectionError(f"stream closed: {e}") from None
+
+
+class ClientStream:
+    """Client end of a stream method: its own connection, frames in both directions until ``close``."""
+
+    def __init__(self, sock: socket.socket, method: str, uid: str):
+        self._s, self.method, self.uid = sock, method, uid
+        self.closed = False
+
+    def send(self, tensors: List[torch.Tensor], metadata: dict) -> None:
+        self._s.sendall(pack_frame(self.method, self.uid, metadata, tensors))
+
+    def recv(self, timeout: Optional[float] = 30.0) -> Tuple[List[torch.Tensor], dict]:
+        self._s.settimeout(timeout)
+        try:
+            raw = _recv_exact(self._s, _HDR.size)
+            magic, hl, pl = _HDR.unpack(raw)
+            if magic != MAGIC:
+                raise ConnectionError("bad frame magic")
+            hb = _recv_exact(self._s, hl)
+            payload = _recv_exact(self._s, pl) if pl else b""
+        except socket.timeout as e:
+            raise TimeoutError(f"stream {self.method}: no answer in {timeout}s") from e
+        except OSError as e:
+            raise ConnectionError(f"stream {self.method} failed: {e}") from e
+        header, out = unpack_frame(hb, payload)
+        if header.get("error"):
+            raise RpcError(header["error"])
+        md = header.get("metadata") or {}
+        if md.get("error"):
+            raise RpcError(md["error"])
+        return out, md
+
+    def call(self, tensors: List[torch.Tensor], metadata: dict, timeout: float = 30.0):
+        self.send(tensors, metadata)
+        return self.recv(timeout)
+
+    def close(self, timeout: float = 5.0) -> Optional[dict]:
+        if self.closed:
+            return None
+        self.closed = True
+        md = None
+        try:
+            self.send([], {"close": True})
+            _, md = self.recv(timeout)
+        except Exception:  # noqa: BLE001 - best effort
+            pass
+        try:
+            self._s.close()
+        except OSError:
+            pass
+        return md
+
+
 class RpcClient:
     """Blocking client with one pooled connection per server address."""
+
+    def open_stream(self, addr: Tuple[str, int], method: str, uid: str, tensors: List[torch.Tensor], metadata: dict,
+                    timeout: float = 30.0) -> ClientStream:
+        """Starts a stream method on its own connection and returns after the server's opening answer."""
+        try:
+            s = socket.create_connection(addr, timeout=timeout)
+        except OSError as e:
+            raise ConnectionError(f"RPC {method} to {addr} failed: {e}") from e
+        s.setsockopt(socket.IPPROTO_TCP, socket.TCP_NODELAY, 1)
+        st = ClientStream(s, method, uid)
+        try:
+            st.send(tensors, metadata)
+            _, st.opened = st.recv(timeout)
+        except Exception:
+            s.close()
+            raise
+        return st
 
     def __init__(self):
         self._socks: Dict[Tuple[str, int], socket.socket] = {}

@@ -11,16 +11,15 @@ petals/server/block_functions.py:163-168).
 """
 from __future__ import annotations
 
+import contextlib
 import threading
 import time
 from dataclasses import dataclass, field
-from typing import Dict, Optional
+from typing import Callable, Dict, Optional
 
 import torch
 
-
-class AllocationFailed(RuntimeError):
-    """Raised when the KV token budget cannot hold a new session (memory_cache.py:26)."""
+from .memory_cache import AllocationFailed, MemoryCache, TensorDescriptor  # noqa: F401  (AllocationFailed re-exported)
 
 
 @dataclass
@@ -31,6 +30,7 @@ class SessionKV:
     length: int = 0               # tokens cached so far
     last_used: float = field(default_factory=time.monotonic)
     limit: Optional[int] = None   # request-level max_length (<= max_len), enforced by the handler
+    release: Optional[Callable[[], None]] = None   # returns the bytes to the manager's MemoryCache
 
     @property
     def n_layers(self) -> int:
@@ -53,14 +53,18 @@ class SessionKV:
 
 class KVCacheManager:
     def __init__(self, n_layers: int, n_kv_heads: int, head_dim: int, dtype: torch.dtype, device,
-                 max_tokens: Optional[int] = None, default_max_length: int = 2048, session_ttl: float = 600.0):
+                 max_tokens: Optional[int] = None, default_max_length: int = 2048, session_ttl: float = 600.0,
+                 alloc_timeout: float = 0.0):
         self.n_layers, self.n_kv, self.head_dim = n_layers, n_kv_heads, head_dim
         self.dtype, self.device = dtype, torch.device(device)
         self.max_tokens = max_tokens              # None = unlimited
         self.default_max_length = default_max_length
         self.session_ttl = session_ttl
+        self.alloc_timeout = alloc_timeout        # how long a request may wait for cache bytes (0 = fail at once)
         self.sessions: Dict[str, SessionKV] = {}
         self._lock = threading.Lock()
+        # every session buffer is carved from this byte budget; waiters are woken when a session closes
+        self.cache = MemoryCache(None if max_tokens is None else max_tokens * self.bytes_per_token(), alloc_timeout)
 
     # ---- accounting
     @property
@@ -81,26 +85,43 @@ class KVCacheManager:
             s.touch()
         return s
 
-    def allocate(self, session_id: str, max_length: Optional[int] = None) -> SessionKV:
+    def _drop(self, session_id: str) -> bool:
+        s = self.sessions.pop(session_id, None)
+        if s is None:
+            return False
+        if s.release is not None:
+            s.release()
+        return True
+
+    def allocate(self, session_id: str, max_length: Optional[int] = None, timeout: Optional[float] = None) -> SessionKV:
+        """A zeroed cache of ``max_length`` tokens for ``session_id`` (an existing, large enough one is reset and
+        reused).  When the token budget is taken the call first evicts expired / long-idle sessions and then WAITS
+        up to ``timeout`` (default: the manager's ``alloc_timeout``) for other sessions to be closed;
+        ``AllocationFailed`` after that."""
         max_length = int(max_length or self.default_max_length)
         with self._lock:
             self.evict_expired()
-            old = self.sessions.pop(session_id, None)
+            old = self.sessions.get(session_id)
             if old is not None and old.max_len >= max_length:
                 old.length = 0
                 old.touch()
-                self.sessions[session_id] = old
                 return old
+            self._drop(session_id)
             if self.max_tokens is not None and self.tokens_used + max_length > self.max_tokens:
                 self._evict_lru_until(max_length)
-                if self.tokens_used + max_length > self.max_tokens:
-                    raise AllocationFailed(
-                        f"KV budget exhausted: need {max_length} tokens, {self.tokens_left} left of {self.max_tokens}")
-            data = torch.zeros((self.n_layers, 2, self.n_kv, max_length, self.head_dim), dtype=self.dtype,
-                               device=self.device)
-            s = SessionKV(session_id, data, max_length)
+        desc = TensorDescriptor((self.n_layers, 2, self.n_kv, max_length, self.head_dim), self.dtype, self.device)
+        stack = contextlib.ExitStack()
+        try:
+            handles = stack.enter_context(self.cache.allocate_cache(desc, timeout=timeout))   # may block (no lock held)
+        except AllocationFailed as e:
+            raise AllocationFailed(f"KV budget exhausted: need {max_length} tokens, {self.tokens_left} left of "
+                                   f"{self.max_tokens} ({e})") from None
+        data = self.cache.use_cache(*handles)[0]
+        s = SessionKV(session_id, data, max_length, release=stack.close)
+        with self._lock:
+            self._drop(session_id)          # a concurrent allocate for the same id loses
             self.sessions[session_id] = s
-            return s
+        return s
 
     def reorder(self, session_ids, hypo_ids) -> None:
         """Beam-search bookkeeping: after the call, session ``session_ids[i]`` continues the hypothesis
@@ -125,13 +146,13 @@ class KVCacheManager:
 
     def close(self, session_id: str) -> bool:
         with self._lock:
-            return self.sessions.pop(session_id, None) is not None
+            return self._drop(session_id)
 
     def evict_expired(self, now: Optional[float] = None) -> int:
         now = time.monotonic() if now is None else now
         dead = [k for k, s in self.sessions.items() if now - s.last_used > self.session_ttl]
         for k in dead:
-            del self.sessions[k]
+            self._drop(k)
         return len(dead)
 
     def _evict_lru_until(self, need: int) -> None:
@@ -141,4 +162,4 @@ class KVCacheManager:
             if self.tokens_used + need <= self.max_tokens:
                 break
             if now - s.last_used > 0.1 * self.session_ttl:
-                del self.sessions[k]
+                self._drop(k)

@@ -8,6 +8,11 @@ that does not fit waits (up to a timeout) for other sessions to free memory and 
 Here there is one process per GPU, so handles map directly to device tensors, but the contract
 is the same: ``with cache.allocate_cache(descr, ..., timeout=t) as handles:`` blocks while the
 budget is exhausted, accounts ``enqueued_size`` for waiters, frees on exit.
+
+:class:`~petals_b200.runtime.kv_cache.KVCacheManager` allocates every session cache through one of
+these (budget = ``attn_cache_tokens`` x bytes per token), so a request that arrives while the budget
+is taken WAITS up to ``alloc_timeout`` for another session to close or expire, as upstream's
+``_allocate_cache`` does (petals/server/handler.py:532-547).
 """
 from __future__ import annotations
 
@@ -20,9 +25,11 @@ from typing import Dict, Iterator, Optional, Sequence, Tuple
 
 import torch
 
-from .kv_cache import AllocationFailed
-
 Handle = int
+
+
+class AllocationFailed(RuntimeError):
+    """The cache budget cannot hold the request (petals/server/memory_cache.py:26)."""
 
 
 @dataclass(frozen=True)

@@ -120,6 +120,25 @@ class _StageBase(torch.nn.Module):
             kv.rollback(pos0)                      # start_from_position semantics
         return self.span.forward(h, kv, pos0)
 
+    @torch.inference_mode()
+    def decode_batch(self, hidden: torch.Tensor, kvs) -> list:
+        """One token for each of several SESSIONS in one step: ``hidden`` [B, H] (row b belongs to ``kvs[b]``) ->
+        list of B outputs shaped like :meth:`forward`'s for a single token ([1, 1, H] hidden states, or
+        [1, 1, V] fp32 logits on the last stage).  The native engine runs the B sessions as one batched
+        kernel sequence; the torch engine falls back to a loop."""
+        B = hidden.shape[0]
+        if self.role == "stage0":
+            raise ValueError("decode_batch serves server stages (hidden-state inputs)")
+        if self.backend == "native" and B <= self.span.max_batch:
+            h = hidden.reshape(B, self.cfg.hidden).to(self.device, self.dtype)
+            if self.role == "last":
+                logits, _ = self.span.decode(list(kvs), h_in=h, greedy=True)
+                out = logits[:B].clone()
+            else:
+                out = self.span.decode(list(kvs), h_in=h).clone()
+            return [out[b].reshape(1, 1, -1) for b in range(B)]
+        return [self.forward(hidden[b:b + 1].reshape(1, 1, -1), None, None, kvs[b])[0] for b in range(B)]
+
     def parameters(self, recurse: bool = True):   # reference probes next(stage.parameters()).dtype
         yield torch.empty(0, dtype=self.dtype, device=self.device)
 

@@ -7,6 +7,13 @@ forward/backward 2.0); different-length requests are never batched together.  He
 pool per GPU plays both roles: RPC handlers submit closures with a priority, the worker runs
 them one at a time on the device stream, and a task larger than ``max_task_tokens`` is
 rejected up front (task_pool.py:103-105).
+
+Batching: upstream's pools merge queued tasks of the SAME shape into one batch
+(task_pool.py:117-131).  Here single-token decode steps of different sessions are the one
+case worth merging - the decode kernels take up to 32 sessions per launch sequence at little
+more than the cost of one - so ``submit_batch_item`` queues an item for a batch function and
+the worker, when it reaches such an item, takes every other queued item of the same function
+along (up to its ``max_batch``) and runs them in one call.
 """
 from __future__ import annotations
 
@@ -20,6 +27,10 @@ from typing import Any, Callable, Optional
 
 PRIORITY_INFERENCE = 1.0
 PRIORITY_FORWARD = 2.0
+
+
+def _BATCH():  # marker in the `fn` slot of a heap entry: args = (batch_fn, item, max_batch)
+    raise RuntimeError("batch marker is not callable")
 
 
 class TaskPrioritizerBase(ABC):
@@ -44,6 +55,8 @@ class PrioritizedTaskPool:
         self._cv = threading.Condition()
         self._stop = False
         self.completed = 0
+        self.batches = 0           # batch calls made / items they carried (rpc_info reports the mean batch)
+        self.batched_items = 0
         self._thread = threading.Thread(target=self._run, name=f"{name}-runtime", daemon=True)
         self._thread.start()
 
@@ -60,6 +73,38 @@ class PrioritizedTaskPool:
             self._cv.notify()
         return fut
 
+    def submit_batch_item(self, batch_fn: Callable[[list], list], item: Any, *, kind: str = "inference",
+                          tokens: int = 1, max_batch: int = 32, priority: Optional[float] = None) -> "cf.Future":
+        """Queue ``item`` for ``batch_fn``; the worker calls ``batch_fn([item, ...])`` with every queued item of
+        the same function (submit order, at most ``max_batch``) and resolves each future with the matching entry
+        of the returned list (an entry that is an exception instance fails only that item)."""
+        if self.max_task_tokens is not None and tokens > self.max_task_tokens:
+            raise ValueError(f"task of {tokens} tokens exceeds max_task_tokens={self.max_task_tokens}")
+        fut: cf.Future = cf.Future()
+        pr = self.prioritizer.prioritize(kind) if priority is None else priority
+        with self._cv:
+            if self._stop:
+                raise RuntimeError("pool is shut down")
+            heapq.heappush(self._heap, (pr, time.monotonic(), next(self._seq), _BATCH, (batch_fn, item, max_batch), {}, fut))
+            self._cv.notify()
+        return fut
+
+    def _take_batch(self, first) -> list:
+        """Called with the lock held: `first` plus the queued batch items of the same function."""
+        batch_fn, _, max_batch = first[4]
+        group = [first]
+        if max_batch > 1:
+            rest = []
+            for ent in sorted(self._heap):
+                if len(group) < max_batch and ent[3] is _BATCH and ent[4][0] == batch_fn:
+                    group.append(ent)
+                else:
+                    rest.append(ent)
+            if len(group) > 1:
+                self._heap[:] = rest
+                heapq.heapify(self._heap)
+        return group
+
     def _run(self) -> None:
         while True:
             with self._cv:
@@ -67,7 +112,12 @@ class PrioritizedTaskPool:
                     self._cv.wait()
                 if self._stop and not self._heap:
                     return
-                _, _, _, fn, args, kwargs, fut = heapq.heappop(self._heap)
+                ent = heapq.heappop(self._heap)
+                group = self._take_batch(ent) if ent[3] is _BATCH else None
+            if group is not None:
+                self._run_batch(group)
+                continue
+            _, _, _, fn, args, kwargs, fut = ent
             if not fut.set_running_or_notify_cancel():
                 continue
             try:
@@ -75,6 +125,26 @@ class PrioritizedTaskPool:
             except BaseException as e:  # noqa: BLE001 - delivered through the future
                 fut.set_exception(e)
             self.completed += 1
+
+    def _run_batch(self, group: list) -> None:
+        live = [e for e in group if e[6].set_running_or_notify_cancel()]
+        if not live:
+            return
+        batch_fn = live[0][4][0]
+        try:
+            results = batch_fn([e[4][1] for e in live])
+            if len(results) != len(live):
+                raise RuntimeError(f"batch function returned {len(results)} results for {len(live)} items")
+        except BaseException as e:  # noqa: BLE001
+            results = [e] * len(live)
+        for ent, r in zip(live, results):
+            if isinstance(r, BaseException):
+                ent[6].set_exception(r)
+            else:
+                ent[6].set_result(r)
+        self.completed += len(live)
+        self.batches += 1
+        self.batched_items += len(live)
 
     @property
     def queued(self) -> int:

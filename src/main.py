@@ -104,7 +104,7 @@ def run_rank0(args, device, splits, dht: Optional[DHT] = None):
                       routing=("module" if args.use_load_balancing else "stage"), model_name=args.model,
                       total_blocks=total_blocks, start_block=stage0_end, request_timeout=args.request_timeout,
                       repetition_penalty=getattr(args, "repetition_penalty", None), dht=dht,
-                      push=getattr(args, "push", False))
+                      push=getattr(args, "push", False), stream=getattr(args, "stream", False))
     session_id = str(uuid4())
     t_prefill_start = time.perf_counter()
     hidden, _ = s0(input_ids, None, None, kv0)
@@ -205,7 +205,12 @@ def start_stage_server(args, device, stage_model, final_stage: bool, stage_index
     maddrs = [f"/ip4/{ip}/tcp/{port}/p2p/{peer_id}"]
     handler = StageConnectionHandler(dht, stage_model, device, request_timeout=args.request_timeout,
                                      final_stage=final_stage, throughput=throughput,
-                                     seed=getattr(args, "seed", None))
+                                     seed=getattr(args, "seed", None),
+                                     attn_cache_tokens=_attn_cache_tokens(args, stage_model),
+                                     alloc_timeout=getattr(args, "alloc_timeout", 10.0),
+                                     session_timeout=getattr(args, "session_timeout", 30 * 60.0),
+                                     step_timeout=getattr(args, "step_timeout", 5 * 60.0),
+                                     max_batch=getattr(args, "max_batch", None))
     stop = threading.Event()
     model_name = args.model
     handler.on_die = lambda: (stop.set(), rpc.stop())   # scripted kill (tests / kill_stage.py --soft)
@@ -257,6 +262,34 @@ def start_stage_server(args, device, stage_model, final_stage: bool, stage_index
     return ServerHandle(dht, rpc, handler, peer_id, maddrs, stop, [t], lb_blocks or [], model_name)
 
 
+def _attn_cache_tokens(args, stage_model) -> Optional[int]:
+    """KV budget of a server in tokens (upstream --attn_cache_tokens, petals/server/server.py:204-209): the
+    upstream defaults, but never less than what ``max_batch`` full-length sessions need on this stage."""
+    from petals_b200.runtime.block_utils import default_limits
+
+    v = getattr(args, "attn_cache_tokens", None)
+    if v == 0:
+        return None
+    if v is None:
+        v = default_limits(stage_model.cfg)[1]
+        v = max(v, (getattr(args, "max_batch", None) or 1) * stage_model.kv_capacity)
+    return max(int(v), stage_model.kv_capacity)
+
+
+def _default_num_blocks(args, cfg, device) -> int:
+    """--num_blocks when the user gave none: as many blocks as this GPU holds next to its KV budget (upstream
+    ``_choose_num_blocks``, petals/server/server.py:275-326); 4 on a CPU-only host."""
+    from petals_b200.runtime.block_utils import choose_num_blocks, default_limits
+
+    if device.type != "cuda":
+        return min(4, cfg.n_layers)
+    tokens = getattr(args, "attn_cache_tokens", None) or default_limits(cfg)[1]
+    n = choose_num_blocks(cfg, device, args.dtype if isinstance(args.dtype, torch.dtype) else torch.bfloat16,
+                          attn_cache_tokens=tokens)
+    logger.info("num_blocks not given: this GPU holds %d of %d blocks next to a %d-token cache", n, cfg.n_layers, tokens)
+    return n
+
+
 def _build_stage(args, device, start: int, end: int, final: bool, n_layers: int):
     role = "last" if final else "segment"
     full = load_stage_model(args.model, device, role=role, start=start, end=end, dtype=args.dtype,
@@ -264,6 +297,8 @@ def _build_stage(args, device, start: int, end: int, final: bool, n_layers: int)
     kw = dict(gpu_device=device, keep_layers_on_gpu=args.keep_layers_on_gpu)
     if getattr(args, "kv_capacity", None):
         kw["kv_capacity"] = args.kv_capacity
+    if getattr(args, "max_batch", None):
+        kw["max_batch"] = args.max_batch
     return StageLast(full, start, **kw) if final else StageSegment(full, start, end, **kw)
 
 
@@ -282,12 +317,18 @@ def run_stage_server_with_load_balancing(args, device, splits, num_blocks=None, 
     """Join where the swarm is weakest, serve, re-evaluate every ~``mean_balance_check_period`` s."""
     cfg = resolve_config(args.model)
     total_blocks = total_blocks or args.total_blocks or cfg.n_layers
-    num_blocks = num_blocks or args.num_blocks or 4
+    num_blocks = num_blocks or args.num_blocks or _default_num_blocks(args, cfg, device)
+    num_blocks = min(num_blocks, total_blocks - (splits[0] if splits else 0))
     min_block = splits[0] if splits else 0
     dht = _make_dht(args)
     placements = 0
     handle = None
     while True:
+        # Servers started together (one script, one box) would all see the same empty swarm and pick the same
+        # blocks: spread their decisions over time (upstream server.py:407-411).
+        sel_delay = float(getattr(args, "mean_block_selection_delay", 0.0) or 0.0)
+        if sel_delay > 0:
+            time.sleep(random.random() * 2 * sel_delay)
         infos, delay = [], 1.0
         for _ in range(3):
             infos = get_remote_module_infos(dht, args.model, total_blocks)
@@ -303,7 +344,8 @@ def run_stage_server_with_load_balancing(args, device, splits, num_blocks=None, 
         stage_model = _build_stage(args, device, start, end, final, cfg.n_layers)
         try:
             thr = get_server_throughput(stage_model, device, args.dtype, cfg.hidden,
-                                        network_bandwidth_mbps=args.network_bandwidth_mbps, model_name=args.model)
+                                        network_bandwidth_mbps=args.network_bandwidth_mbps, model_name=args.model,
+                                        use_cache=not getattr(args, "no_throughput_cache", False))
         except Exception as e:  # noqa: BLE001
             logger.warning("throughput measurement failed (%s); using fallback 10.0 rps", e)
             thr = 10.0
@@ -320,7 +362,7 @@ def run_stage_server_with_load_balancing(args, device, splits, num_blocks=None, 
                 try:
                     h.handler.throughput = get_server_throughput(
                         sm, device, args.dtype, cfg.hidden, network_bandwidth_mbps=args.network_bandwidth_mbps,
-                        model_name=args.model)
+                        model_name=args.model, use_cache=not getattr(args, "no_throughput_cache", False))
                     mi = get_remote_module_infos(dht, args.model, total_blocks)
                     if should_choose_other_blocks(str(h.peer_id), mi, args.balance_quality, total_blocks, min_block):
                         logger.info("Swarm is imbalanced: re-placing this server")
@@ -410,11 +452,25 @@ def build_parser() -> argparse.ArgumentParser:
     p.add_argument("--balance_quality", type=float, default=0.75)
     p.add_argument("--mean_balance_check_period", type=float, default=120.0)
     p.add_argument("--network_bandwidth_mbps", type=float, default=None)
+    p.add_argument("--mean_block_selection_delay", type=float, default=5.0,
+                   help="load-balanced server: mean of the random wait before choosing blocks (join-race avoidance)")
     # additions (not in the reference)
     p.add_argument("--repetition_penalty", type=float, default=None, help="override the server default 1.5 (B8)")
     p.add_argument("--seed", type=int, default=0, help="seed of the random-init weights when no checkpoint is local")
     p.add_argument("--kv_capacity", type=int, default=None, help="per-session KV capacity in tokens")
     p.add_argument("--push", action="store_true", help="servers forward activations to the next hop themselves")
+    p.add_argument("--stream", action="store_true",
+                   help="client: one rpc_inference stream per session and server (cache allocated once per stream)")
+    p.add_argument("--attn_cache_tokens", type=int, default=None,
+                   help="server: KV budget in tokens over all sessions (default: the upstream rule, 16384 for GQA "
+                        "models and 4096 otherwise, never less than one session); 0 = unlimited")
+    p.add_argument("--alloc_timeout", type=float, default=10.0,
+                   help="server: how long a new session may wait for KV cache bytes before AllocationFailed")
+    p.add_argument("--session_timeout", type=float, default=30 * 60.0, help="server: lifetime of an inference stream")
+    p.add_argument("--step_timeout", type=float, default=5 * 60.0, help="server: idle time of an inference stream")
+    p.add_argument("--max_batch", type=int, default=16,
+                   help="server: single-token requests of different sessions merged into one decode step (1 = off)")
+    p.add_argument("--no_throughput_cache", action="store_true", help="server: re-measure the throughput on every start")
     p.add_argument("--inbox", action="store_true",
                    help="in-box mode: launch with torchrun (one process per GPU); stages hand hidden states over "
                         "NCCL p2p instead of TCP RPC; --splits gives the stage boundaries, --stage is ignored")

@@ -17,7 +17,16 @@ error instead of a warning — unless ``start_from_position`` asks for a rollbac
 can be closed and idle ones expire; no per-hop ``.item()`` range checks; compute runs on a
 priority task pool thread, never on the network loop (B11).  Extras from the upstream server
 (petals/server/handler.py): ``rpc_info``, ``rpc_close_session`` and server->server forwarding
-of the result along ``route`` (the rpc_push idea) so a chain of hosts needs one client round trip.
+of the result along ``route`` (the rpc_push idea) so a chain of hosts needs one client round trip;
+``rpc_inference`` - one stream per session with the cache allocated once, ``session_timeout`` /
+``step_timeout`` and the cache freed when the stream ends (handler.py:132-195, 532-547);
+cache admission that waits up to ``alloc_timeout`` for bytes (memory_cache.py:26-225);
+``hypo_ids`` beam re-ordering (backend.py:154-158).
+
+Concurrent sessions: single-token decode requests of different sessions that are queued at the
+same time are merged into ONE batched step of the stage (up to ``max_batch`` sessions,
+task_pool.py:17-177 / backend.py:201-235 upstream) - the decode kernels serve 16 sessions in about
+1.4x the time of one.
 """
 from __future__ import annotations
 
@@ -41,7 +50,9 @@ HANDLER_PREFIX = "StageConnectionHandler"
 class StageConnectionHandler:
     def __init__(self, dht, stage_model, device, request_timeout: float = 30.0, final_stage: bool = True,
                  attn_cache_tokens: Optional[int] = None, session_ttl: float = 600.0, start_block: Optional[int] = None,
-                 end_block: Optional[int] = None, throughput: float = 0.0, seed: Optional[int] = None):
+                 end_block: Optional[int] = None, throughput: float = 0.0, seed: Optional[int] = None,
+                 alloc_timeout: float = 10.0, session_timeout: float = 30 * 60.0, step_timeout: float = 5 * 60.0,
+                 max_batch: Optional[int] = None):
         self.dht = dht
         self.stage_model = stage_model
         self.device = torch.device(device)
@@ -51,8 +62,16 @@ class StageConnectionHandler:
         self.end_block = getattr(stage_model, "end", end_block)
         self.throughput = throughput
         cap = getattr(stage_model, "kv_capacity", 2048)
-        self.kv = stage_model.new_kv_manager(max_tokens=attn_cache_tokens, session_ttl=session_ttl)
+        self.kv = stage_model.new_kv_manager(max_tokens=attn_cache_tokens, session_ttl=session_ttl,
+                                             alloc_timeout=alloc_timeout)
         self.kv_capacity = cap
+        self.session_timeout, self.step_timeout = session_timeout, step_timeout
+        # sessions per batched decode step: what the stage's engine takes in one call (1 = never batch)
+        span = getattr(stage_model, "span", None)
+        self.max_batch = int(max_batch if max_batch is not None else getattr(span, "max_batch", 1) or 1)
+        if not hasattr(stage_model, "decode_batch"):
+            self.max_batch = 1
+        self.streams_open = 0
         self._default_temperature, self._default_top_p, self._default_top_k = 0.8, 0.9, 0
         self.pool = PrioritizedTaskPool("stage")
         self._fwd_client = RpcClient()
@@ -68,8 +87,10 @@ class StageConnectionHandler:
 
     # ------------------------------------------------------------------ registration
     def add_p2p_handlers(self, server: RpcServer) -> None:
-        for name in ("rpc_forward", "rpc_forward_stream", "rpc_info", "rpc_close_session", "rpc_push", "rpc_check"):
+        for name in ("rpc_forward", "rpc_forward_stream", "rpc_info", "rpc_close_session", "rpc_push", "rpc_check",
+                     "rpc_reorder"):
             server.add_handler(f"{HANDLER_PREFIX}.{name}", getattr(self, name))
+        server.add_stream_handler(f"{HANDLER_PREFIX}.rpc_inference", self.rpc_inference)
 
     # ------------------------------------------------------------------ core
     def _session_for(self, md: dict, T: int):
@@ -118,11 +139,16 @@ class StageConnectionHandler:
                 threading.Thread(target=self.on_die, daemon=True).start()
             raise ConnectionError("injected crash")
         T = hidden_states.shape[-2] if hidden_states.dim() >= 2 else 1
+        self._maybe_reorder(metadata)
         sid, kv = self._session_for(metadata, T)
         pos_ids = torch.arange(kv.length, kv.length + T, dtype=torch.long).unsqueeze(0)
         out, _ = self.stage_model(hidden_states, position_ids=pos_ids, attention_mask=None, past_key_values=kv,
                                   use_cache=True)
         self.requests += 1
+        return self._finish(out, metadata, sid)
+
+    def _finish(self, out: torch.Tensor, metadata: Dict, sid) -> Tuple[List[torch.Tensor], Dict]:
+        """Stage output of ONE request -> its reply (sampled token on the final stage, hidden states otherwise)."""
         if self.final_stage:
             logits = out.reshape(-1, out.shape[-1])[-1]
             params = SamplingParams(
@@ -137,6 +163,55 @@ class StageConnectionHandler:
                                      generator=self._gen if logits.device.type == "cpu" else None)
             return [torch.tensor([[token]], dtype=torch.long)], {"token_id": token, "session_id": sid}
         return [out.detach().to("cpu")], {"session_id": sid}
+
+    def _maybe_reorder(self, metadata: Dict) -> None:
+        """Beam search: ``hypo_ids[i]`` names which hypothesis of ``beam_sessions`` session i continues."""
+        hypo = metadata.get("hypo_ids")
+        if hypo is None:
+            return
+        group = metadata.get("beam_sessions")
+        if not group:
+            raise ValueError("hypo_ids needs beam_sessions (the session ids of the beam, in hypothesis order)")
+        self.kv.reorder(list(group), [int(h) for h in hypo])
+
+    def _run_decode_batch(self, items: List[Tuple[torch.Tensor, Dict]]) -> list:
+        """One batched decode step for every queued single-token request (different sessions).  Returns one
+        reply - or one exception - per request, so a bad request does not fail its neighbours."""
+        results: list = [None] * len(items)
+        ready = []
+        seen = set()
+        for i, (hidden, md) in enumerate(items):
+            try:
+                if self.fail_next > 0:
+                    self.fail_next -= 1
+                    raise RuntimeError("injected failure")
+                if self.die_after is not None and self.requests + len(ready) + 1 >= self.die_after and \
+                        (self.die_guard is None or self.die_guard()):
+                    self.die_after = None
+                    if self.on_die is not None:
+                        threading.Thread(target=self.on_die, daemon=True).start()
+                    raise ConnectionError("injected crash")
+                self._maybe_reorder(md)
+                sid, kv = self._session_for(md, 1)
+                if sid in seen:                       # two steps of ONE session cannot share a batch
+                    results[i] = self._run_forward(hidden, md)
+                    continue
+                seen.add(sid)
+                ready.append((i, hidden, md, sid, kv))
+            except BaseException as e:  # noqa: BLE001
+                results[i] = e
+        if ready:
+            try:
+                H = ready[0][1].shape[-1]
+                h = torch.cat([r[1].reshape(1, H) for r in ready], 0)
+                outs = self.stage_model.decode_batch(h, [r[4] for r in ready])
+                self.requests += len(ready)
+                for (i, _, md, sid, _), o in zip(ready, outs):
+                    results[i] = self._finish(o, md, sid)
+            except BaseException as e:  # noqa: BLE001
+                for i, *_ in ready:
+                    results[i] = e
+        return results
 
     def _device_sample(self, logits: torch.Tensor, params: SamplingParams, generated) -> int:
         from petals_b200.ops.sampling import DeviceSampler
@@ -155,7 +230,12 @@ class StageConnectionHandler:
             raise ValueError("No tensors in request")
         hidden = tensors[0]
         T = hidden.shape[-2] if hidden.dim() >= 2 else 1
-        out_t, out_md = self._submit(self._run_forward, hidden, metadata, kind="inference", tokens=T)
+        if T == 1 and self.max_batch > 1 and not metadata.get("is_prefill") and hidden.numel() == hidden.shape[-1]:
+            out_t, out_md = self.pool.submit_batch_item(self._run_decode_batch, (hidden, metadata), kind="inference",
+                                                        tokens=1, max_batch=self.max_batch).result(
+                                                            timeout=self.request_timeout)
+        else:
+            out_t, out_md = self._submit(self._run_forward, hidden, metadata, kind="inference", tokens=T)
         route = metadata.get("route") or []
         if route and not self.final_stage:
             # server->server push: hand the activations to the next hop ourselves and relay its answer
@@ -169,13 +249,76 @@ class StageConnectionHandler:
     rpc_forward_stream = rpc_forward   # TCP needs no separate streaming path; kept for name parity
     rpc_push = rpc_forward
 
+    def rpc_reorder(self, uid: str, tensors, metadata: Dict):
+        """Beam search between steps: session ``session_ids[i]`` continues hypothesis ``hypo_ids[i]``."""
+        self._submit(self.kv.reorder, list(metadata["session_ids"]), [int(h) for h in metadata["hypo_ids"]],
+                     kind="inference")
+        return [], {"reordered": len(metadata["session_ids"])}
+
+    def rpc_inference(self, uid: str, tensors: List[torch.Tensor], metadata: Dict, stream):
+        """One inference SESSION over one connection (upstream handler.py:132-195).
+
+        The opening message names ``session_id`` and ``max_length``; the cache is allocated once, right here,
+        waiting up to ``alloc_timeout`` for bytes (AllocationFailed goes back to the client).  Every further
+        message is one step - a prompt chunk or a single token - answered in order; the session ends when the
+        client says ``close``, when no step arrives for ``step_timeout`` seconds, after ``session_timeout``
+        seconds in total, or when the connection drops - and the cache is freed in every one of those cases."""
+        sid = metadata.get("session_id")
+        if sid is None:
+            raise ValueError("rpc_inference: the opening message must carry session_id")
+        max_length = int(metadata.get("max_length", self.kv_capacity))
+        if max_length > self.kv_capacity:
+            raise ValueError(f"max_length {max_length} exceeds this server's per-session capacity {self.kv_capacity}")
+        kv = self.kv.allocate(sid, self.kv_capacity, timeout=metadata.get("alloc_timeout"))
+        kv.limit = max_length
+        self.streams_open += 1
+        deadline = time.monotonic() + float(metadata.get("session_timeout", self.session_timeout))
+        step_timeout = float(metadata.get("step_timeout", self.step_timeout))
+        stream.send([], {"session_id": sid, "opened": True, "max_length": max_length})
+        steps, reason = 0, "closed by client"
+        try:
+            while True:
+                left = deadline - time.monotonic()
+                if left <= 0:
+                    reason = "session_timeout"
+                    break
+                try:
+                    t_in, md = stream.recv(min(step_timeout, left))
+                except TimeoutError:
+                    reason = "step_timeout" if step_timeout <= left else "session_timeout"
+                    break
+                except ConnectionError:
+                    reason = "connection lost"
+                    break
+                if md.get("close"):
+                    break
+                md = dict(md)
+                md.setdefault("session_id", sid)
+                md.setdefault("max_length", max_length)
+                if md.get("is_prefill") and kv.length == 0 and steps == 0:
+                    md["is_prefill"] = False          # the cache of this stream exists already: append, do not re-allocate
+                    md.setdefault("start_from_position", 0)
+                try:
+                    out_t, out_md = self.rpc_forward(uid, t_in, md)
+                    stream.send(out_t, out_md)
+                except Exception as e:  # noqa: BLE001  (a failed step is reported, the session stays usable)
+                    stream.send([], {"error": f"{type(e).__name__}: {e}"})
+                steps += 1
+        finally:
+            self.streams_open -= 1
+            self.kv.close(sid)
+            logger.info("[%s] inference stream ended after %d steps (%s)", str(sid)[:8], steps, reason)
+        return [], {"session_id": sid, "steps": steps, "ended": reason}
+
     def rpc_info(self, uid: str, tensors, metadata: Dict):
         left = self.kv.tokens_left
         return [], {"version": "0.1.0", "start_block": self.start_block, "end_block": self.end_block,
                     "final_stage": self.final_stage, "sessions": len(self.kv.sessions),
                     "cache_tokens_left": left if left is not None else -1, "kv_capacity": self.kv_capacity,
                     "throughput": self.throughput, "requests": self.requests, "queued": self.pool.queued,
-                    "uptime_s": time.time() - self.started}
+                    "max_batch": self.max_batch, "batches": self.pool.batches,
+                    "mean_batch": (self.pool.batched_items / self.pool.batches) if self.pool.batches else 0.0,
+                    "streams_open": self.streams_open, "uptime_s": time.time() - self.started}
 
     def rpc_check(self, uid: str, tensors, metadata: Dict):
         """Dial-back probe for joining servers (upstream reachability.py rpc_check)."""

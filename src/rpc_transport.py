@@ -59,7 +59,8 @@ class RpcTransport:
                  dht_port: int = 0, rpc_port: int = 0, temperature: float = 1.0, top_p: float = 0.92, top_k: int = 50,
                  stage_keys: Optional[Sequence[str]] = None, routing: str = "stage", model_name: str = "default",
                  total_blocks: int = 32, start_block: int = 0, request_timeout: float = 30.0,
-                 repetition_penalty: Optional[float] = None, dht: Optional[DHT] = None, push: bool = False):
+                 repetition_penalty: Optional[float] = None, dht: Optional[DHT] = None, push: bool = False,
+                 stream: bool = False, session_timeout: Optional[float] = None, step_timeout: Optional[float] = None):
         self.device = device
         self.temperature, self.top_p, self.top_k = temperature, top_p, top_k
         self.repetition_penalty = repetition_penalty
@@ -68,6 +69,11 @@ class RpcTransport:
         self.model_name, self.total_blocks, self.start_block = model_name, total_blocks, start_block
         self.request_timeout = request_timeout
         self.push = push
+        # stream=True: one ``rpc_inference`` stream per (session, server) instead of one unary call per step - the
+        # server allocates the session's cache once when the stream opens and frees it when the stream ends
+        self.stream = bool(stream) and not push
+        self.session_timeout, self.step_timeout = session_timeout, step_timeout
+        self._streams: Dict[Tuple[str, str], object] = {}
         peers = [p for p in (dht_initial_peers or []) if p]
         for p in peers:
             if ":" in p and "/p2p/" not in p and not p.startswith("/"):
@@ -163,8 +169,56 @@ class RpcTransport:
         return md
 
     def _call(self, hop: Hop, tensor: torch.Tensor, md: dict):
+        if self.stream:
+            return self._call_stream(hop, tensor, md)
         return self.client.call(hop.addr, f"{HANDLER_PREFIX}.rpc_forward", hop.key, [tensor], md,
                                 timeout=self.request_timeout)
+
+    def _call_stream(self, hop: Hop, tensor: torch.Tensor, md: dict):
+        sid = md["session_id"]
+        key = (sid, hop.peer_id)
+        st = self._streams.get(key)
+        try:
+            if st is None:
+                open_md = {"session_id": sid, "max_length": md.get("max_length") or self.session_max_length.get(sid)}
+                if open_md["max_length"] is None:
+                    del open_md["max_length"]
+                if self.session_timeout is not None:
+                    open_md["session_timeout"] = self.session_timeout
+                if self.step_timeout is not None:
+                    open_md["step_timeout"] = self.step_timeout
+                st = self.client.open_stream(hop.addr, f"{HANDLER_PREFIX}.rpc_inference", hop.key, [], open_md,
+                                             timeout=self.request_timeout)
+                self._streams[key] = st
+            return st.call([tensor], md, timeout=self.request_timeout)
+        except (TimeoutError, ConnectionError):
+            self._drop_stream(key)
+            raise
+
+    def _drop_stream(self, key) -> None:
+        st = self._streams.pop(key, None)
+        if st is not None:
+            try:
+                st.close(timeout=1.0)
+            except Exception:  # noqa: BLE001
+                pass
+
+    def reorder_hypotheses(self, session_ids: Sequence[str], hypo_ids: Sequence[int]) -> None:
+        """Beam search: on every server of the beam's route, session ``session_ids[i]`` continues the hypothesis
+        that ``session_ids[hypo_ids[i]]`` held (upstream ``hypo_ids``, petals/server/backend.py:154-158).  All
+        sessions of a beam share one route (the first session's)."""
+        route = self._get_route(session_ids[0])
+        for sid in session_ids[1:]:
+            self.session_routes.setdefault(sid, route)
+        for hop in route:
+            self.client.call(hop.addr, f"{HANDLER_PREFIX}.rpc_reorder", hop.key, [],
+                             {"session_ids": list(session_ids), "hypo_ids": [int(h) for h in hypo_ids]},
+                             timeout=self.request_timeout)
+        # the journals follow the hypotheses, so that a later replay rebuilds the re-ordered caches
+        snap = {sid: {k: list(v) for k, v in self.client_cache.get(sid, {}).items()} for sid in session_ids}
+        for i, h in enumerate(hypo_ids):
+            if int(h) != i:
+                self.client_cache[session_ids[i]] = {k: list(v) for k, v in snap[session_ids[int(h)]].items()}
 
     def _journal(self, session_id: str, key: str) -> List[torch.Tensor]:
         return self.client_cache.setdefault(session_id, {}).setdefault(key, [])
@@ -322,12 +376,15 @@ class RpcTransport:
         return self.last_token
 
     def close_session(self, session_id: str) -> None:
-        for hop in self.session_routes.pop(session_id, []):
+        for key in [k for k in self._streams if k[0] == session_id]:
+            self._drop_stream(key)                       # ending the stream frees the server-side cache
+        for hop in ([] if self.stream else self.session_routes.get(session_id, [])):
             try:
                 self.client.call(hop.addr, f"{HANDLER_PREFIX}.rpc_close_session", hop.key, [],
                                  {"session_id": session_id}, timeout=5.0)
             except Exception:  # noqa: BLE001 - best effort
                 pass
+        self.session_routes.pop(session_id, None)
         self.client_cache.pop(session_id, None)
         self.session_max_length.pop(session_id, None)
 
@@ -344,6 +401,8 @@ class RpcTransport:
                 "decode_mean_ms": sum(s) / len(s) * 1e3, "steps": len(s)}
 
     def shutdown(self) -> None:
+        for key in list(self._streams):
+            self._drop_stream(key)
         self.client.close()
         if self._own_dht:
             self.dht.shutdown()

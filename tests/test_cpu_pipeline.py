@@ -14,6 +14,8 @@ def _args(model, splits, stage, dht_peers="", **kw):
                                    "--dht_initial_peers", dht_peers, "--dht_port", "0", "--rpc_port", "0",
                                    "--temperature", "0", "--dtype", "fp32"])
     a.dtype = torch.float32
+    a.mean_block_selection_delay = 0.0      # tests place servers one after the other
+    a.no_throughput_cache = True
     for k, v in kw.items():
         setattr(a, k, v)
     return a

@@ -80,18 +80,39 @@ def test_throughput_estimate_and_cache(tmp_path, monkeypatch):
         class cfg:
             hidden = 4096
 
+    n = 3   # blocks of the stage
+    # measurement fails: the estimate falls back to the network bound, nothing is cached
     calls = []
     monkeypatch.setattr(tm, "measure_compute_throughput", lambda *a, **k: calls.append(1) or (_ for _ in ()).throw(RuntimeError("no")))
+    monkeypatch.setattr(tm, "measure_forward_throughput", lambda *a, **k: (_ for _ in ()).throw(RuntimeError("no")))
     thr = tm.get_server_throughput(Stage(), "cpu", torch.float16, network_bandwidth_mbps=100.0, use_cache=True, model_name="m")
     assert thr == pytest.approx(100e6 / 65536 * (1 - tm.NETWORK_OVERHEAD)) and calls == [1]
+    assert not os.path.exists(tm.CACHE_PATH)
+    # upstream model: per-block rps, (n+1)/2 blocks used on average, min with the network
+    monkeypatch.setattr(tm, "measure_compute_throughput", lambda *a, **k: calls.append(2) or 50.0)    # steps/s of the span
+    monkeypatch.setattr(tm, "measure_forward_throughput", lambda *a, **k: 4000.0)                      # tokens/s of the span
+    info = tm.get_server_throughput_info(Stage(), "cpu", torch.float16, network_bandwidth_mbps=1e6, use_cache=True,
+                                         model_name="m")
+    assert info["inference_rps"] == pytest.approx(50.0 * n) and info["forward_rps"] == pytest.approx(4000.0 * n)
+    assert info["throughput"] == pytest.approx(4000.0 * n / ((n + 1) / 2))
     stored = json.load(open(tm.CACHE_PATH))
-    assert list(stored.values()) == [pytest.approx(thr)] and "2:5" in next(iter(stored))
-    # second call is served from the file, the measurement is not run again
-    assert tm.get_server_throughput(Stage(), "cpu", torch.float16, use_cache=True, model_name="m") == pytest.approx(thr)
-    assert calls == [1]
-    # compute-bound case: min(compute, network)
-    monkeypatch.setattr(tm, "measure_compute_throughput", lambda *a, **k: 12.5)
-    assert tm.get_server_throughput(Stage(), "cpu", torch.float16, network_bandwidth_mbps=100.0) == 12.5
+    assert list(stored) == ["m|cpu|torch.float16|per_block"]
+    # second call is served from the file (the per-block numbers do not depend on the span), nothing is re-measured
+    calls.clear()
+    again = tm.get_server_throughput(Stage(), "cpu", torch.float16, network_bandwidth_mbps=1e6, use_cache=True, model_name="m")
+    assert again == pytest.approx(info["throughput"]) and calls == []
+    # network-bound case and the relay penalty
+    slow = tm.get_server_throughput_info(Stage(), "cpu", torch.float16, network_bandwidth_mbps=100.0, use_cache=True, model_name="m")
+    assert slow["throughput"] == pytest.approx(slow["network_rps"]) == pytest.approx(100e6 / 65536 * 0.8)
+    relay = tm.get_server_throughput_info(Stage(), "cpu", torch.float16, network_bandwidth_mbps=100.0, use_cache=True,
+                                          model_name="m", reachable_via_relay=True)
+    assert relay["throughput"] == pytest.approx(0.2 * slow["throughput"])
+    # no bandwidth given, no process group: the loopback RPC itself is timed (not the 100 Mbit/s constant)
+    lo = tm.get_server_throughput_info(Stage(), "cpu", torch.float16, use_cache=True, model_name="m")
+    assert lo["network_rps"] > 50            # a real measurement of this machine's loopback round trips
+    monkeypatch.setattr(tm, "measure_loopback_rpc_rps", lambda *a, **k: 7777.0)
+    lo = tm.get_server_throughput_info(Stage(), "cpu", torch.float16, use_cache=True, model_name="m")
+    assert lo["network_rps"] == 7777.0 and lo["throughput"] == pytest.approx(4000.0 * n / ((n + 1) / 2))
 
 
 def test_cache_and_position_helpers():
