@@ -164,6 +164,8 @@ __global__ void __launch_bounds__(128) attn_prefill_kernel(const AttnPrefillPara
 
 using namespace b200;
 
+B200_DEFINE_TRACE_SETTER(b200_trace_set_attn)
+
 extern "C" int64_t b200_attn_decode_scratch_bytes(int32_t T, int32_t n_heads, int32_t head_dim, int32_t splits) {
     return (int64_t)T * n_heads * splits * (head_dim + 2) * (int64_t)sizeof(float);
 }

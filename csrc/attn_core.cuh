@@ -2,6 +2,7 @@
 #pragma once
 #include "common.h"
 #include "ptx.cuh"
+#include "trace.cuh"
 
 namespace b200 {
 
@@ -366,7 +367,10 @@ __global__ void __launch_bounds__(kAttnThreads) attn_decode_kernel(const AttnDec
     const int g = bid % p.n_kv;
     const int t = bid / p.n_kv;
     pdl_launch_dependents();
-    attn_decode_body<D, GROUP>(p, t, g, s, (int)threadIdx.x, sm, [] { __syncthreads(); }, [] { pdl_wait_prior_grid(); });
+    if (threadIdx.x == 0) trace_event(2, 0);
+    attn_decode_body<D, GROUP>(p, t, g, s, (int)threadIdx.x, sm, [] { __syncthreads(); },
+                               [] { pdl_wait_prior_grid(); if (threadIdx.x == 0) trace_event(2, 1); });
+    if (threadIdx.x == 0) trace_event(2, 3);
 }
 
 }  // namespace b200

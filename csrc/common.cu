@@ -35,3 +35,13 @@ int sm_count_cached() {
 extern "C" const char* b200_last_error(void) { return b200::error_buffer(); }
 extern "C" int b200_version(void) { return 100; }
 extern "C" int b200_sm_count(void) { return b200::sm_count_cached(); }
+
+// Event trace of the decode kernels (csrc/trace.cuh): buf = device memory of 8 * (1 + 2 * cap) bytes, zeroed by the
+// caller; NULL switches the trace off again.
+extern "C" int b200_trace_set_gemm(void*, int);
+extern "C" int b200_trace_set_attn(void*, int);
+extern "C" int b200_trace_set(void* buf, int32_t cap) {
+    if (b200_trace_set_gemm(buf, cap) != 0 || b200_trace_set_attn(buf, cap) != 0)
+        return b200::fail(B200_ECUDA, "b200_trace_set: cudaMemcpyToSymbol failed");
+    return B200_OK;
+}

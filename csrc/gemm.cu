@@ -12,6 +12,7 @@
 #include <stdlib.h>
 
 #include "gemm_core.cuh"
+#include "trace.cuh"
 
 namespace b200 {
 
@@ -46,6 +47,7 @@ gemm_streamk_kernel(const GemmParams p) {
     const int cta = blockIdx.x;
 
     if (threadIdx.x == 0) {
+        trace_event(1, 0, (p.n_tiles & 0xfff) | ((p.kbpt & 0xfff) << 12));
         for (int i = 0; i < SA; ++i) { mbar_init(&a_full[i], 1); mbar_init(&a_empty[i], 1); }
         for (int i = 0; i < SB; ++i) { mbar_init(&b_full[i], 4); mbar_init(&b_empty[i], 1); }
         mbar_init(acc_full, 1);
@@ -188,6 +190,7 @@ gemm_streamk_kernel(const GemmParams p) {
         const int r0 = e >> 3;                  // first token row this thread stages
 
         pdl_wait_prior_grid();  // activations come from the previous kernel
+        if (e == 0) trace_event(1, 1, (p.n_tiles & 0xfff) | ((p.kbpt & 0xfff) << 12));
         if (p.gather_world > 1) tp_gather_prologue(p, e);   // x = residual + sum of the TP partials of the previous linear
 
         if (p.norm_mode == B200_NORM_LAYER) {
@@ -394,6 +397,7 @@ gemm_streamk_kernel(const GemmParams p) {
             float* my_partial = p.scratch + ((size_t)cta * 2 + slot) * (size_t)(APER * BN * kTileM);
             mbar_wait(acc_full, part & 1);
             tc_fence_after();
+            if (e == 0) trace_event(1, 2, (p.n_tiles & 0xfff) | ((p.kbpt & 0xfff) << 12));
             const int t_live = min(BN, p.T - t_tile * BN);  // token columns that exist in this tile
 #pragma unroll 1
             for (int c = 0; c * 16 < t_live; ++c) {
@@ -625,6 +629,7 @@ gemm_streamk_kernel(const GemmParams p) {
             q += kb1 - kb0;
             ++part;
         }
+        if (e == 0) trace_event(1, 3, (p.n_tiles & 0xfff) | ((p.kbpt & 0xfff) << 12));
         if (p.tp_world > 1 && !tp_bumped) {   // a CTA without work still counts
             named_bar_sync(1, kEpiThreads);
             if (e == 0 && atomicAdd(p.tp_exit, 1) == (int)gridDim.x - 1) {
@@ -668,6 +673,8 @@ static int pick_token_tile(int T) {
 }  // namespace b200
 
 using namespace b200;
+
+B200_DEFINE_TRACE_SETTER(b200_trace_set_gemm)
 
 extern "C" int32_t b200_gemm_token_tile(int32_t T, int32_t dual) {
     (void)dual;

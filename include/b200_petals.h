@@ -281,6 +281,13 @@ int b200_hop_recv(const b200_hop_args* args, void* stream);
 /* Loads the two kernels on the current device (call once before capturing them into a graph). */
 int b200_hop_init(void);
 
+/* Opt-in device-side event trace of the decode kernels (profiling aid, scripts/trace_decode.py): the GEMM and the
+ * decode attention stamp %globaltimer at entry / after their dependency wait / first accumulator / exit for the first
+ * and last CTA.  buf: 8 * (1 + 2 * cap) bytes of zeroed device memory ([0] = events written, then (ns, tag) pairs with
+ * tag = kernel << 56 | aux << 32 | phase << 16 | last_cta; aux of a GEMM = n_tiles | k_blocks << 12); NULL = off.  Synchronous (cudaMemcpyToSymbol); the reference's only
+ * timing aid is time.time() around forward calls (src/rpc_handler.py:190-249). */
+int b200_trace_set(void* buf, int32_t cap);
+
 /* Temperature / top-k / top-p / repetition-penalty sampling on the device with the reference's rules
  * (src/rpc_handler.py:327-403), one CTA per row, no sort (radix descent over float bit patterns).
  * rows: T records {float temperature, top_p, penalty; int32 top_k, n_recent; int32 recent[50]} on the

@@ -1,0 +1,122 @@
+"""Per-kernel timeline of one decode step from the device-side event trace (csrc/trace.cuh).
+
+    python scripts/trace_decode.py [--layers 8] [--model llama-2-7b] [--out gpurun_out/trace_decode.json]
+
+For every GEMM / attention launch of one CUDA-graph replay: when its first and last CTA entered, when the
+dependency wait ended, when the first accumulator was ready and when the CTA left - all in microseconds from
+the first event, plus the gaps between consecutive kernels.
+"""
+import argparse
+import ctypes
+import json
+import os
+import sys
+
+import torch
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--model", default="llama-2-7b")
+    ap.add_argument("--layers", type=int, default=8)
+    ap.add_argument("--prompt", type=int, default=128)
+    ap.add_argument("--out", default="gpurun_out/trace_decode.json")
+    a = ap.parse_args()
+    from petals_b200.models.config import resolve_config
+    from petals_b200.ops import native
+    from petals_b200.runtime.kv_cache import KVCacheManager
+    from petals_b200.runtime.native_span import NativeSpan
+    from petals_b200.weights.loader import load_span
+
+    dev = torch.device("cuda", 0)
+    torch.cuda.set_device(dev)
+    cfg = resolve_config(a.model)
+    dt = torch.float16
+    w = load_span(a.model, cfg, 0, a.layers, need_embed=True, need_head=True, dtype=dt, device=dev, seed=0)
+    span = NativeSpan(cfg, w, dev, dt, kv_capacity=512, max_batch=1, max_chunk=256)
+    kv = KVCacheManager(a.layers, cfg.n_kv_heads, cfg.head_dim, dt, dev).allocate("s", 512)
+    ids = torch.randint(0, cfg.vocab, (a.prompt,), device=dev)
+    _, tok = span.prefill(kv, ids=ids)
+    for _ in range(8):
+        _, tok = span.decode([kv], ids=tok.clone())
+    torch.cuda.synchronize()
+    cap = 8192
+    buf = torch.zeros(1 + 2 * cap, dtype=torch.int64, device=dev)
+    L = native.lib()
+    L.b200_trace_set.argtypes = [ctypes.c_void_p, ctypes.c_int32]
+    native.check(L.b200_trace_set(buf.data_ptr(), cap), "trace on")
+    _, tok = span.decode([kv], ids=tok.clone())
+    torch.cuda.synchronize()
+    native.check(L.b200_trace_set(None, 0), "trace off")
+    h = buf.cpu().tolist()
+    n = min(h[0], cap)
+    ev = sorted((h[1 + 2 * i], h[2 + 2 * i]) for i in range(n))
+    t0 = ev[0][0]
+    names = {}
+
+    def kname(tag):
+        kid, aux = tag >> 56, (tag >> 32) & 0xffffff
+        if kid == 2:
+            return "attn"
+        nt, kb = aux & 0xfff, aux >> 12
+        key = (nt, kb)
+        if key not in names:
+            names[key] = f"gemm[{nt}x{kb}]"
+        return names[key]
+
+    # the i-th event of a (kernel type, phase, cta) belongs to the i-th launch of that type (launches of one type
+    # never overlap each other); launches are then ordered by the time their first CTA entered
+    per = {}
+    for t, tag in ev:
+        k = (kname(tag), ["enter", "dep", "acc", "exit"][(tag >> 16) & 0xff], "L" if tag & 1 else "0")
+        per.setdefault(k, []).append((t - t0) / 1e3)
+    launches = []
+    for kn in sorted({k[0] for k in per}):
+        cnt = len(per.get((kn, "enter", "0"), []))
+        for i in range(cnt):
+            d = {"kernel": kn}
+            for ph in ("enter", "dep", "acc", "exit"):
+                for c in ("0", "L"):
+                    lst = per.get((kn, ph, c), [])
+                    # "acc" is stamped once per part; keep the first one after this launch's enter
+                    if ph == "acc":
+                        ent = per[(kn, "enter", c)][i] if i < len(per.get((kn, "enter", c), [])) else None
+                        nxt = per[(kn, "enter", c)][i + 1] if ent is not None and i + 1 < len(per[(kn, "enter", c)]) else 1e18
+                        cand = [x for x in lst if ent is not None and ent <= x < nxt]
+                        d[ph + c] = cand[0] if cand else float("nan")
+                    else:
+                        d[ph + c] = lst[i] if i < len(lst) else float("nan")
+            launches.append(d)
+    launches.sort(key=lambda d: d["enter0"])
+    print(f"{n} events, {len(launches)} launches; step = {(ev[-1][0] - t0) / 1e3:.1f} us for {a.layers} layers + head")
+    print(f"{'#':>3} {'kernel':14} {'enter0':>8} {'dep0':>8} {'acc0':>8} {'exit0':>8} | {'enterL':>8} {'depL':>8} {'accL':>8} {'exitL':>8} | prev_end->dep  dep->end")
+    summary = []
+    prev_end = 0.0
+    for i, d in enumerate(launches):
+        end_ = max(x for x in (d["exit0"], d["exitL"]) if x == x) if (d["exit0"] == d["exit0"] or d["exitL"] == d["exitL"]) else float("nan")
+        dep = max(x for x in (d["dep0"], d["depL"]) if x == x) if (d["dep0"] == d["dep0"] or d["depL"] == d["depL"]) else float("nan")
+        d["end"], d["dep"] = end_, dep
+        summary.append(d)
+        if 5 <= i < 16 or i >= len(launches) - 3:
+            print(f"{i:>3} {d['kernel']:14} " + " ".join(f"{d[k]:8.1f}" for k in ("enter0", "dep0", "acc0", "exit0")) + " | "
+                  + " ".join(f"{d[k]:8.1f}" for k in ("enterL", "depL", "accL", "exitL")) + f" | {dep - prev_end:8.1f} {end_ - dep:8.1f}")
+        prev_end = end_
+    # mean over layers per kernel type
+    print("mean per kernel type (us): wait after the previous kernel's end until the dependency is visible, then dep -> end")
+    for kn in sorted({d["kernel"] for d in summary}):
+        sel = [(j, d) for j, d in enumerate(summary) if d["kernel"] == kn and j > 0]
+        if not sel:
+            continue
+        gaps = [d["dep"] - summary[j - 1]["end"] for j, d in sel]
+        runs = [d["end"] - d["dep"] for j, d in sel]
+        pre = [d["dep"] - d["enter0"] for j, d in sel]
+        print(f"  {kn:14} n={len(sel):3d}  prev_end->dep {sum(gaps) / len(gaps):6.2f}   dep->end {sum(runs) / len(runs):6.2f}   resident before dep {sum(pre) / len(pre):6.2f}")
+    os.makedirs(os.path.dirname(a.out) or ".", exist_ok=True)
+    with open(a.out, "w") as f:
+        json.dump({"model": a.model, "layers": a.layers, "launches": summary}, f)
+
+
+if __name__ == "__main__":
+    main()
