@@ -190,6 +190,21 @@ extern "C" int b200_attn_decode(const b200_attn_decode_args* a, void* stream_) {
     p.ldqkv = a->ldqkv; p.ldo = a->ldo;
     p.scale = a->scale;
     p.is_bf16 = (a->dtype == B200_BF16) ? 1 : 0;
+    p.ch = LLChain{};
+    if (a->chain.seq) {
+        const b200_ll_chain& c = a->chain;
+        if (!c.x_ll || !c.out_ll || !a->ll_scratch || !a->pdl)
+            return fail(B200_EINVAL, "b200_attn_decode: a flag chain needs x_ll, out_ll, ll_scratch and pdl = 1");
+        if ((c.ldx_ll % 4) != 0 || (reinterpret_cast<uintptr_t>(c.x_ll) & 31) != 0 || (a->head_dim % 16) != 0)
+            return fail(B200_EINVAL, "b200_attn_decode: chain.x_ll must be 32-byte aligned with ldx_ll %% 4 == 0");
+        if (c.x_op <= 0 || c.x_op >= (1 << kLLOpBits) || c.out_op <= 0 || c.out_op >= (1 << kLLOpBits))
+            return fail(B200_EINVAL, "b200_attn_decode: chain launch ids must be in 1..%d", (1 << kLLOpBits) - 1);
+        p.ch.seq = c.seq;
+        p.ch.x = static_cast<const uint2*>(c.x_ll);
+        p.ch.out = static_cast<uint2*>(c.out_ll);
+        p.ch.ldx = c.ldx_ll; p.ch.ldo = c.ldo_ll;
+        p.ch.x_op = c.x_op; p.ch.out_op = c.out_op;
+    }
     const dim3 grid((unsigned)(a->T * a->n_kv_heads * p.splits));
     cudaStream_t stream = static_cast<cudaStream_t>(stream_);
     const bool pdl = a->pdl != 0;

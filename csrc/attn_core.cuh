@@ -3,6 +3,7 @@
 #include "common.h"
 #include "ptx.cuh"
 #include "trace.cuh"
+#include "llchain.cuh"
 
 namespace b200 {
 
@@ -18,6 +19,7 @@ struct AttnDecodeParams {
     int T, n_heads, n_kv, s_max, splits, ldqkv, ldo;
     float scale;
     int is_bf16;
+    LLChain ch;   // flag-chained decode step (ch.seq != null): qkv polled from ch.x, the output also published to ch.out
 };
 
 constexpr int kAttnThreads = 128;
@@ -139,21 +141,33 @@ __device__ __forceinline__ void attn_decode_body(const AttnDecodeParams& p, int 
         }
     }
     before_qkv();
+    const bool chain = p.ch.seq != nullptr;
+    uint32_t xtag = 0, otag = 0;
+    const uint2* row_ll = nullptr;
+    if (chain) {
+        const int seq = ll_read_seq(p.ch.seq);
+        xtag = ll_tag(seq, p.ch.x_op);
+        otag = ll_tag(seq, p.ch.out_op);
+        row_ll = p.ch.x + (size_t)t * p.ch.ldx;
+    }
+    auto load8 = [&](int off) -> uint4 {       // 8 elements of this token's qkv row starting at element `off`
+        return chain ? ll_load8(row_ll + (off >> 1), xtag) : ld_cg_v4(row + off);
+    };
     for (int item = tid; item < (GROUP + 1) * TPH; item += kAttnThreads) {
         const int h = item / TPH, c = (item % TPH) * 8;
         const bool is_k = (h == GROUP);
         if (is_k && !(pos >= r_begin && pos < r_end)) continue;
-        const uint16_t* src = row + (is_k ? k_off : q_off + h * D);
+        const int src = is_k ? k_off : q_off + h * D;
         float lo[8], hi[8];
-        unpack8(ld_cg_v4(src + c), lo, p.is_bf16);
-        unpack8(ld_cg_v4(src + c + D / 2), hi, p.is_bf16);
+        unpack8(load8(src + c), lo, p.is_bf16);
+        unpack8(load8(src + c + D / 2), hi, p.is_bf16);
         if (p.inv_freq) rope_apply8(lo, hi, rs, rc);
         if (is_k) {
             *reinterpret_cast<uint4*>(kbase + (size_t)pos * D + c) = pack8(lo, p.is_bf16);
             *reinterpret_cast<uint4*>(kbase + (size_t)pos * D + c + D / 2) = pack8(hi, p.is_bf16);
             // v is copied verbatim alongside
-            *reinterpret_cast<uint4*>(vbase + (size_t)pos * D + c) = ld_cg_v4(row + v_off + c);
-            *reinterpret_cast<uint4*>(vbase + (size_t)pos * D + c + D / 2) = ld_cg_v4(row + v_off + c + D / 2);
+            *reinterpret_cast<uint4*>(vbase + (size_t)pos * D + c) = load8(v_off + c);
+            *reinterpret_cast<uint4*>(vbase + (size_t)pos * D + c + D / 2) = load8(v_off + c + D / 2);
         } else {
 #pragma unroll
             for (int i = 0; i < 8; ++i) {
@@ -256,7 +270,9 @@ __device__ __forceinline__ void attn_decode_body(const AttnDecodeParams& p, int 
             oo += s_o[w][h][d] * c;
         }
         if (eff == 1) {
-            p.out[(size_t)t * p.ldo + (g * GROUP + h) * D + d] = float_to_h16(oo / ll, p.is_bf16);
+            const uint16_t hv = float_to_h16(oo / ll, p.is_bf16);
+            p.out[(size_t)t * p.ldo + (g * GROUP + h) * D + d] = hv;
+            if (chain) ll_store_pairwise(p.ch.out + (size_t)t * p.ch.ldo, (g * GROUP + h) * D + d, hv, true, otag);
         } else if (p.ll) {
             // ---- ticket-free merge: splits 0..eff-2 publish (value, tag) words, split eff-1 polls for them, merges
             // in split order (same arithmetic as the ticket path) and clears the words again.
@@ -313,7 +329,9 @@ __device__ __forceinline__ void attn_decode_body(const AttnDecodeParams& p, int 
                 const float cs = __expf(mm - gm);
                 gl += ll * cs;
                 go += oo * cs;
-                p.out[(size_t)t * p.ldo + (g * GROUP + h) * D + d] = float_to_h16(go / gl, p.is_bf16);
+                const uint16_t hv = float_to_h16(go / gl, p.is_bf16);
+                p.out[(size_t)t * p.ldo + (g * GROUP + h) * D + d] = hv;
+                if (chain) ll_store_pairwise(p.ch.out + (size_t)t * p.ch.ldo, (g * GROUP + h) * D + d, hv, true, otag);
             }
         } else {
             float* dst = my_part + (size_t)h * splits * (D + 2);
@@ -368,8 +386,9 @@ __global__ void __launch_bounds__(kAttnThreads) attn_decode_kernel(const AttnDec
     const int t = bid / p.n_kv;
     pdl_launch_dependents();
     if (threadIdx.x == 0) trace_event(2, 0);
+    const bool chain = p.ch.seq != nullptr;    // a link of a flag chain polls its inputs instead of waiting for the grid
     attn_decode_body<D, GROUP>(p, t, g, s, (int)threadIdx.x, sm, [] { __syncthreads(); },
-                               [] { pdl_wait_prior_grid(); if (threadIdx.x == 0) trace_event(2, 1); });
+                               [chain] { if (!chain) pdl_wait_prior_grid(); if (threadIdx.x == 0) trace_event(2, 1); });
     if (threadIdx.x == 0) trace_event(2, 3);
 }
 

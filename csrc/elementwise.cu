@@ -3,6 +3,7 @@
 // prologue), and arg-max over the vocabulary.
 #include "common.h"
 #include "ptx.cuh"
+#include "llchain.cuh"
 
 namespace b200 {
 
@@ -39,6 +40,23 @@ __global__ void __launch_bounds__(128) embed_kernel(const long long* __restrict_
             v = make_uint4(a[0], a[1], a[2], a[3]);
         }
         dst[c] = v;
+    }
+}
+
+// ------------------------------------------------------------------ head of a flag chain
+// x[T, H] (complete in stream order) -> LL words tagged (*seq << 12 | op): 8 elements = 4 words per thread step.
+__global__ void __launch_bounds__(256) ll_publish_kernel(const uint16_t* __restrict__ x, int ldx, uint2* __restrict__ out,
+                                                        int ld, int T, int H, const int* __restrict__ seq, int op) {
+    pdl_wait_prior_grid();
+    pdl_launch_dependents();
+    const uint32_t tag = ll_tag(ll_read_seq(seq), op);
+    const int per_row = H / 8;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < T * per_row; i += gridDim.x * blockDim.x) {
+        const int t = i / per_row, c = i - t * per_row;
+        const uint4 v = ld_cg_v4(x + (size_t)t * ldx + c * 8);
+        uint2* w = out + (size_t)t * ld + c * 4;
+        asm volatile("st.relaxed.gpu.global.v4.u32 [%0], {%1, %2, %3, %2};\n" ::"l"(w), "r"(v.x), "r"(tag), "r"(v.y) : "memory");
+        asm volatile("st.relaxed.gpu.global.v4.u32 [%0], {%1, %2, %3, %2};\n" ::"l"(w + 2), "r"(v.z), "r"(tag), "r"(v.w) : "memory");
     }
 }
 
@@ -196,6 +214,17 @@ extern "C" int b200_embed(const void* ids, const void* pos, int32_t pos0, const 
                            static_cast<const long long*>(ids), static_cast<const int*>(pos), pos0,
                            static_cast<const uint16_t*>(wte), static_cast<const uint16_t*>(wpe),
                            static_cast<uint16_t*>(out), T, H, vocab, max_pos, dtype == B200_BF16 ? 1 : 0));
+    return B200_OK;
+}
+
+extern "C" int b200_ll_publish(const void* x, int32_t ldx, void* out_ll, int32_t ld_ll, int32_t T, int32_t H,
+                               const int32_t* seq, int32_t op, int32_t pdl, void* stream_) {
+    if (!x || !out_ll || !seq) return fail(B200_EINVAL, "b200_ll_publish: null pointer argument");
+    if (H % 8 != 0 || ld_ll % 4 != 0 || T <= 0 || op <= 0 || op >= (1 << kLLOpBits))
+        return fail(B200_EINVAL, "b200_ll_publish: bad sizes T=%d H=%d ld=%d op=%d", T, H, ld_ll, op);
+    const int blocks = (T * (H / 8) + 255) / 256;
+    B200_CUDA_CHECK(launch(ll_publish_kernel, dim3(blocks > 64 ? 64 : blocks), dim3(256), 0, static_cast<cudaStream_t>(stream_),
+                           pdl != 0, static_cast<const uint16_t*>(x), ldx, static_cast<uint2*>(out_ll), ld_ll, T, H, seq, op));
     return B200_OK;
 }
 

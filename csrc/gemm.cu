@@ -16,10 +16,15 @@
 
 namespace b200 {
 
+constexpr int kLLMaxCtasDev = 512;   // CTAs one half of the word buffer has slots for (b200_gemm_ll_bytes)
+
 // WIDE = 1: the ticket-free fix-up for 5..16 tokens (every CTA of a tile publishes its whole partial and then
 // reduces its own share of the tile's elements).  A separate instantiation so that its registers never weigh on
 // the batch-1 kernel.
-template <int BN, int DUAL, int FP8, int WIDE = 0>
+// LLIO = 1: link of a flag-chained decode step (b200_ll_chain): no grid-dependency wait; x and the residual are polled
+// as LL words, the output is published as LL words, the stream-K exchange uses per-launch tags in alternating halves
+// of the word buffer (nothing to clear).
+template <int BN, int DUAL, int FP8, int WIDE = 0, int LLIO = 0>
 __global__ void __launch_bounds__(kThreads, GemmCfg<BN, DUAL>::kMinBlocks)
 gemm_streamk_kernel(const GemmParams p) {
     using Cfg = GemmCfg<BN, DUAL>;
@@ -189,7 +194,14 @@ gemm_streamk_kernel(const GemmParams p) {
         const int ch = e & 7;                   // 16-byte chunk of the 128 B k-row
         const int r0 = e >> 3;                  // first token row this thread stages
 
-        pdl_wait_prior_grid();  // activations come from the previous kernel
+        uint32_t xtag = 0, rtag = 0, otag = 0;
+        if (LLIO) {
+            // no grid dependency: the words this CTA needs are polled where they are used
+            const int seq = ll_read_seq(p.ch.seq);
+            xtag = ll_tag(seq, p.ch.x_op); rtag = ll_tag(seq, p.ch.res_op); otag = ll_tag(seq, p.ch.out_op);
+        } else {
+            pdl_wait_prior_grid();  // activations come from the previous kernel
+        }
         if (e == 0) trace_event(1, 1, (p.n_tiles & 0xfff) | ((p.kbpt & 0xfff) << 12));
         if (p.gather_world > 1) tp_gather_prologue(p, e);   // x = residual + sum of the TP partials of the previous linear
 
@@ -202,7 +214,7 @@ gemm_streamk_kernel(const GemmParams p) {
                 if (t < p.T) {
                     const uint16_t* xr = p.x + (size_t)t * p.ldx;
                     for (int c = lane; c < p.K / 8; c += 32) {
-                        const uint4 v = ld_cg_v4(xr + c * 8);
+                        const uint4 v = LLIO ? ll_load8(p.ch.x + (size_t)t * p.ch.ldx + c * 4, xtag) : ld_cg_v4(xr + c * 8);
                         const uint32_t w4[4] = {v.x, v.y, v.z, v.w};
 #pragma unroll
                         for (int i = 0; i < 4; ++i) {
@@ -238,6 +250,11 @@ gemm_streamk_kernel(const GemmParams p) {
         const int tp_seq = (p.tp_world > 1) ? (__ldcv(p.tp_seq) + 1) : 0;
         bool tp_bumped = false;
         constexpr int ll_seq = 1;   // tag of a published word; the consumer clears the word again (tag 0) once it has read it
+        // chain: the exchange words carry this launch's own tag and live in the half named by the caller - the
+        // previous GEMM may still be reading the other half, and nothing has to be cleared
+        const uint32_t wtag = LLIO ? otag : 1u;
+        unsigned long long* const ll_words = LLIO && p.ll_words
+            ? p.ll_words + (size_t)p.ch.half * ((size_t)kLLMaxCtasDev * 2 * 16 * kTileM) : p.ll_words;
         long long q = q_begin;
         while (q < q_end) {
             const int u = (int)(q / p.kbpt);
@@ -296,7 +313,9 @@ gemm_streamk_kernel(const GemmParams p) {
 #pragma unroll
                             for (int i = 0; i < NI; ++i) {
                                 const int t = t_tile * BN + r0 + 16 * i;
-                                v[g][i] = (t < p.T) ? ld_cg_v4(p.x + (size_t)t * p.ldx + kcol) : make_uint4(0, 0, 0, 0);
+                                if (t >= p.T) v[g][i] = make_uint4(0, 0, 0, 0);
+                                else if (LLIO) v[g][i] = ll_load8(p.ch.x + (size_t)t * p.ch.ldx + (kcol >> 1), xtag);
+                                else v[g][i] = ld_cg_v4(p.x + (size_t)t * p.ldx + kcol);
                             }
                             if (p.norm_mode != B200_NORM_NONE) {
                                 gw[g] = ld_nc_v4(p.norm_w + kcol);
@@ -387,7 +406,7 @@ gemm_streamk_kernel(const GemmParams p) {
                 rms_ready = true;
             }
             if (p.norm_mode == B200_NORM_RMS && !rms_ready) {
-                rms_stats_128(p, min(BN, p.T), e, stat_red, stat_rstd);
+                rms_stats_128<LLIO>(p, min(BN, p.T), e, stat_red, stat_rstd, xtag);
                 rms_ready = true;
             }
             const float* tok_scale = (p.norm_mode == B200_NORM_RMS || FP8) ? stat_rstd : nullptr;
@@ -421,16 +440,16 @@ gemm_streamk_kernel(const GemmParams p) {
                 if (full_tile) {
                     if (p.tp_world > 1) tp_allreduce_tile(p, n_tile, row, ncol, e, tp_seq, vg);
                     if (!(p.tp_world > 1 && p.tp_defer))
-                    epilogue_store_chunk<BN, DUAL>(p, n_tile, t_tile, row, c, vg, vu, tok_scale);
+                    epilogue_store_chunk<BN, DUAL, LLIO>(p, n_tile, t_tile, row, c, vg, vu, tok_scale, rtag, otag);
                 } else if (WIDE && p.ll_words) {
                     // ---- wide ticket-free fix-up, part 1: publish the whole partial (reduced below, after the drain)
                     constexpr int kLLStrideW = APER * 16 * kTileM;        // words per CTA
-                    uint2* mine = reinterpret_cast<uint2*>(p.ll_words) + (size_t)cta * kLLStrideW + row;
+                    uint2* mine = reinterpret_cast<uint2*>(ll_words) + (size_t)cta * kLLStrideW + row;
 #pragma unroll
                     for (int j = 0; j < 16; ++j) {
                         if (j < ncol) {
-                            ll_store(mine + j * kTileM, vg[j], 1);
-                            if (DUAL) ll_store(mine + (16 + j) * kTileM, vu[j], 1);
+                            ll_store(mine + j * kTileM, vg[j], (int)wtag);
+                            if (DUAL) ll_store(mine + (16 + j) * kTileM, vu[j], (int)wtag);
                         }
                     }
                 } else if (p.ll_words) {
@@ -528,55 +547,64 @@ gemm_streamk_kernel(const GemmParams p) {
             if (WIDE && !full_tile && p.ll_words) {
                 // ---- wide fix-up, part 2: this CTA reduces its share of the tile's 128 x T elements (column-major
                 // index j * 128 + row): polls the P words of an element together, adds them in CTA order (the order
-                // of every other path), clears them, applies the epilogue for that single element.
+                // of every other path), clears them (not in a chain: tags are per launch there), applies the epilogue
+                // for that single element.  Shares are even-sized and every lane of a warp walks the loop, so that in
+                // a chain two neighbouring lanes can publish their two 16-bit results as one LL word.
                 constexpr int kLLStrideW = APER * 16 * kTileM;
                 const int P = p.ll_parts;
                 const int first = u * P;
                 const int E = kTileM * t_live;
-                const int per = (E + P - 1) / P;
-                const int e_lo = (cta - first) * per, e_hi = min(E, e_lo + per);
-                uint2* base = reinterpret_cast<uint2*>(p.ll_words) + (size_t)first * kLLStrideW;
-                for (int idx = e_lo + e; idx < e_hi; idx += kEpiThreads) {
+                const int per = (((E + P - 1) / P) + 1) & ~1;
+                const int e_lo = min(E, (cta - first) * per), e_hi = min(E, e_lo + per);
+                uint2* base = reinterpret_cast<uint2*>(ll_words) + (size_t)first * kLLStrideW;
+                for (int idx0 = e_lo + (e & ~31); idx0 < e_hi; idx0 += kEpiThreads) {
+                    const int idx = idx0 + lane;
+                    const bool valid = idx < e_hi;
                     const int j = idx >> 7, r = idx & (kTileM - 1);
-                    uint2* w0 = base + j * kTileM + r;
-                    uint32_t vgw[9], tgw[9], vuw[9], tuw[9];
-                    long long t0 = 0;
-                    for (;;) {
-                        bool ok = true;
+                    float sg = 0.f, su = 0.f;
+                    if (valid) {
+                        uint2* w0 = base + j * kTileM + r;
+                        uint32_t vgw[9], tgw[9], vuw[9], tuw[9];
+                        long long t0 = 0;
+                        for (;;) {
+                            bool ok = true;
+#pragma unroll
+                            for (int c = 0; c < 9; ++c) {
+                                if (c < P) {
+                                    asm volatile("ld.relaxed.gpu.global.v2.u32 {%0, %1}, [%2];\n"
+                                                 : "=r"(vgw[c]), "=r"(tgw[c]) : "l"(w0 + (size_t)c * kLLStrideW) : "memory");
+                                    if (DUAL)
+                                        asm volatile("ld.relaxed.gpu.global.v2.u32 {%0, %1}, [%2];\n"
+                                                     : "=r"(vuw[c]), "=r"(tuw[c])
+                                                     : "l"(w0 + (size_t)c * kLLStrideW + 16 * kTileM) : "memory");
+                                }
+                            }
+#pragma unroll
+                            for (int c = 0; c < 9; ++c)
+                                if (c < P) ok = ok && tgw[c] == wtag && (!DUAL || tuw[c] == wtag);
+                            if (ok) break;
+                            if (t0 == 0) t0 = clock64();
+                            else if (clock64() - t0 > 8000000000LL) {
+                                printf("b200: stream-K wide exchange timed out (block %d thread %d)\n", blockIdx.x, threadIdx.x);
+                                __trap();
+                            }
+                        }
 #pragma unroll
                         for (int c = 0; c < 9; ++c) {
                             if (c < P) {
-                                asm volatile("ld.relaxed.gpu.global.v2.u32 {%0, %1}, [%2];\n"
-                                             : "=r"(vgw[c]), "=r"(tgw[c]) : "l"(w0 + (size_t)c * kLLStrideW) : "memory");
-                                if (DUAL)
-                                    asm volatile("ld.relaxed.gpu.global.v2.u32 {%0, %1}, [%2];\n"
-                                                 : "=r"(vuw[c]), "=r"(tuw[c])
-                                                 : "l"(w0 + (size_t)c * kLLStrideW + 16 * kTileM) : "memory");
-                            }
-                        }
-#pragma unroll
-                        for (int c = 0; c < 9; ++c)
-                            if (c < P) ok = ok && tgw[c] == 1u && (!DUAL || tuw[c] == 1u);
-                        if (ok) break;
-                        if (t0 == 0) t0 = clock64();
-                        else if (clock64() - t0 > 8000000000LL) {
-                            printf("b200: stream-K wide exchange timed out (block %d thread %d)\n", blockIdx.x, threadIdx.x);
-                            __trap();
-                        }
-                    }
-                    float sg = 0.f, su = 0.f;
-#pragma unroll
-                    for (int c = 0; c < 9; ++c) {
-                        if (c < P) {
-                            sg += __uint_as_float(vgw[c]);
-                            asm volatile("st.relaxed.gpu.global.v2.u32 [%0], {%1, %1};\n" ::"l"(w0 + (size_t)c * kLLStrideW), "r"(0) : "memory");
-                            if (DUAL) {
-                                su += __uint_as_float(vuw[c]);
-                                asm volatile("st.relaxed.gpu.global.v2.u32 [%0], {%1, %1};\n" ::"l"(w0 + (size_t)c * kLLStrideW + 16 * kTileM), "r"(0) : "memory");
+                                sg += __uint_as_float(vgw[c]);
+                                if (!LLIO)
+                                    asm volatile("st.relaxed.gpu.global.v2.u32 [%0], {%1, %1};\n" ::"l"(w0 + (size_t)c * kLLStrideW), "r"(0) : "memory");
+                                if (DUAL) {
+                                    su += __uint_as_float(vuw[c]);
+                                    if (!LLIO)
+                                        asm volatile("st.relaxed.gpu.global.v2.u32 [%0], {%1, %1};\n" ::"l"(w0 + (size_t)c * kLLStrideW + 16 * kTileM), "r"(0) : "memory");
+                                }
                             }
                         }
                     }
-                    epilogue_store_scalar<DUAL>(p, n_tile * kTileM + r, j, sg, su, tok_scale ? tok_scale[j] : 1.0f);
+                    epilogue_store_scalar<DUAL, LLIO>(p, n_tile * kTileM + r, valid ? j : 0, sg, su,
+                                                      (tok_scale && valid) ? tok_scale[j] : 1.0f, valid, rtag, otag);
                 }
             }
             if (!full_tile && !p.ll_words) {
@@ -621,7 +649,7 @@ gemm_streamk_kernel(const GemmParams p) {
                         }
                         if (p.tp_world > 1) tp_allreduce_tile(p, n_tile, row, ncol, e, tp_seq, vg);
                         if (!(p.tp_world > 1 && p.tp_defer))
-                        epilogue_store_chunk<BN, DUAL>(p, n_tile, t_tile, row, c, vg, vu, tok_scale);
+                        epilogue_store_chunk<BN, DUAL, LLIO>(p, n_tile, t_tile, row, c, vg, vu, tok_scale, rtag, otag);
                     }
                     if (e == 0) p.counters[u] = 0;  // leave the counters clean for the next launch
                 }
@@ -644,7 +672,7 @@ gemm_streamk_kernel(const GemmParams p) {
     if (warp == 1) tmem_dealloc<Cfg::kTmemCols>(tmem_base);
 }
 
-template <int BN, int DUAL, int FP8 = 0, int WIDE = 0>
+template <int BN, int DUAL, int FP8 = 0, int WIDE = 0, int LLIO = 0>
 static int launch_gemm(const GemmParams& p, int grid, bool pdl, cudaStream_t stream) {
     using Cfg = GemmCfg<BN, DUAL>;
     static_assert(Cfg::kSmemBytes <= 227 * 1024, "shared memory budget exceeded");
@@ -652,12 +680,12 @@ static int launch_gemm(const GemmParams& p, int grid, bool pdl, cudaStream_t str
     int dev = 0;
     B200_CUDA_CHECK(cudaGetDevice(&dev));
     if (configured_dev != dev) {
-        B200_CUDA_CHECK(cudaFuncSetAttribute(gemm_streamk_kernel<BN, DUAL, FP8, WIDE>,
+        B200_CUDA_CHECK(cudaFuncSetAttribute(gemm_streamk_kernel<BN, DUAL, FP8, WIDE, LLIO>,
                                              cudaFuncAttributeMaxDynamicSharedMemorySize,
                                              (int)Cfg::kSmemBytes));
         configured_dev = dev;
     }
-    B200_CUDA_CHECK(launch(gemm_streamk_kernel<BN, DUAL, FP8, WIDE>, dim3(grid), dim3(kThreads), Cfg::kSmemBytes,
+    B200_CUDA_CHECK(launch(gemm_streamk_kernel<BN, DUAL, FP8, WIDE, LLIO>, dim3(grid), dim3(kThreads), Cfg::kSmemBytes,
                            stream, pdl, p));
     return B200_OK;
 }
@@ -682,9 +710,10 @@ extern "C" int32_t b200_gemm_token_tile(int32_t T, int32_t dual) {
 }
 
 // ll_buf layout: [kLLHeaderBytes reserved][kLLMaxCtas x 32 KiB of (value, tag) words, all zero between launches]
-constexpr int kLLMaxCtas = 512;
+constexpr int kLLMaxCtas = kLLMaxCtasDev;
 constexpr int kLLHeaderBytes = 256;
-extern "C" int64_t b200_gemm_ll_bytes(void) { return (int64_t)kLLHeaderBytes + (int64_t)kLLMaxCtas * 2 * 16 * kTileM * 8; }
+// two halves: the launches of a flag chain alternate between them (b200_ll_chain.half)
+extern "C" int64_t b200_gemm_ll_bytes(void) { return (int64_t)kLLHeaderBytes + 2 * (int64_t)kLLMaxCtas * 2 * 16 * kTileM * 8; }
 
 extern "C" int64_t b200_gemm_scratch_bytes(int32_t max_tokens) {
     const int bn = pick_token_tile(max_tokens);
@@ -807,7 +836,11 @@ static int gemm_impl(const b200_gemm_args* a, const b200_tp_args* tp, void* stre
         // Few output tiles (o_proj, down_proj): give every tile the same whole number of CTAs so each
         // CTA writes one partial and each tile has equally many contributors (measured 17.4 -> 14.1 us
         // for 4096x4096 at 128 instead of 148 CTAs).
-        const int per_tile = grid / a->n_tiles;
+        int per_tile = grid / a->n_tiles;
+        if (a->chain.seq) {   // a flag chain needs the wide exchange: at most 9 CTAs per tile, at least one k-block each
+            if (per_tile > 9) per_tile = 9;
+            if (per_tile > a->K / kBK) per_tile = a->K / kBK;
+        }
         if (per_tile >= 2) grid = per_tile * a->n_tiles;
     }
     if ((long long)grid > p.Q) grid = (int)p.Q;
@@ -828,6 +861,29 @@ static int gemm_impl(const b200_gemm_args* a, const b200_tp_args* tp, void* stre
     }
     cudaStream_t stream = static_cast<cudaStream_t>(stream_);
     const bool pdl = a->pdl != 0;
+    p.ch = LLChain{};
+    if (a->chain.seq) {
+        const b200_ll_chain& c = a->chain;
+        if (bn != 16 || a->fp8 || tp || gather || a->rstd)
+            return fail(B200_ELIMIT, "b200_gemm: a flag chain needs T <= 16, 16-bit weights, no tensor parallelism, no rstd");
+        if (!c.x_ll || (a->residual && !c.res_ll) || (!a->out_fp32 && !c.out_ll))
+            return fail(B200_EINVAL, "b200_gemm: flag chain without x_ll / res_ll / out_ll");
+        if ((c.ldx_ll % 4) != 0 || (reinterpret_cast<uintptr_t>(c.x_ll) & 31) != 0)
+            return fail(B200_EINVAL, "b200_gemm: chain.x_ll must be 32-byte aligned with ldx_ll %% 4 == 0");
+        if (c.x_op <= 0 || c.x_op >= (1 << kLLOpBits) || c.out_op <= 0 || c.out_op >= (1 << kLLOpBits) || (c.half & ~1))
+            return fail(B200_EINVAL, "b200_gemm: chain launch ids must be in 1..%d, half 0/1", (1 << kLLOpBits) - 1);
+        if (!a->pdl) return fail(B200_EINVAL, "b200_gemm: the launches of a flag chain need pdl = 1");
+        p.ch.seq = c.seq;
+        p.ch.x = static_cast<const uint2*>(c.x_ll);
+        p.ch.res = a->residual ? static_cast<const uint2*>(c.res_ll) : nullptr;
+        p.ch.out = a->out_fp32 ? nullptr : static_cast<uint2*>(c.out_ll);
+        p.ch.ldx = c.ldx_ll; p.ch.ldr = c.ldr_ll; p.ch.ldo = c.ldo_ll;
+        p.ch.x_op = c.x_op; p.ch.res_op = c.res_op; p.ch.out_op = c.out_op; p.ch.half = c.half;
+        if (p.ll_words && !ll_wide) { p.ll_words = nullptr; p.ll_parts = 0; }   // only the wide exchange is chain-safe
+        if (p.ll_words)
+            return a->dual ? launch_gemm<16, 1, 0, 1, 1>(p, grid, pdl, stream) : launch_gemm<16, 0, 0, 1, 1>(p, grid, pdl, stream);
+        return a->dual ? launch_gemm<16, 1, 0, 0, 1>(p, grid, pdl, stream) : launch_gemm<16, 0, 0, 0, 1>(p, grid, pdl, stream);
+    }
     if (a->fp8) {   // only the decode-size tiles are instantiated for e4m3 weights
         if (bn == 16) return a->dual ? launch_gemm<16, 1, 1>(p, grid, pdl, stream) : launch_gemm<16, 0, 1>(p, grid, pdl, stream);
         return a->dual ? launch_gemm<32, 1, 1>(p, grid, pdl, stream) : launch_gemm<32, 0, 1>(p, grid, pdl, stream);

@@ -1,11 +1,11 @@
 // Shared device-side pieces of the tcgen05 GEMM: tile configuration, kernel parameters and the
-// fused epilogue.  Used by the stand-alone stream-K kernel (gemm.cu) and by the persistent
-// multi-op decode kernel (decode_mega.cu).
+// fused epilogue of the stream-K kernel (gemm.cu).
 #pragma once
 #include <cuda_fp8.h>
 
 #include "common.h"
 #include "ptx.cuh"
+#include "llchain.cuh"
 
 #ifndef B200_SA16
 #define B200_SA16 3        /* 32 KiB weight stages for the decode tile (BN = 16) */
@@ -93,6 +93,7 @@ struct GemmParams {
     const uint8_t* pf_ptr[2];   // L2 warm-up ranges for the kernels that follow (see b200_gemm_args.prefetch)
     long long pf_bytes[2];
     int debug;  // experiment switches (scripts/exp_*.py): 1 = no MMA issue, 2 = no B stage waits
+    LLChain ch; // flag-chained decode step (ch.seq != null): x / residual polled as LL words, output published as LL words
 };
 
 __device__ __forceinline__ long long range_begin(const GemmParams& p, int c) {
@@ -196,7 +197,8 @@ __device__ __forceinline__ void tp_allreduce_tile(const GemmParams& p, int tile,
 
 // Per-token 1/rms for the deferred RMSNorm: all 128 worker threads cooperate, result in rstd[0..T).
 // `red` is 4*32 floats of shared scratch; callers separate uses with their own barriers.
-__device__ __forceinline__ void rms_stats_128(const GemmParams& p, int T, int e, float* red, float* rstd) {
+template <int LLIO = 0>
+__device__ __forceinline__ void rms_stats_128(const GemmParams& p, int T, int e, float* red, float* rstd, uint32_t xtag = 0) {
     // All 128 threads on one token after the other, two tokens in flight (their loads are independent).  The
     // reduction tree of a token is the same for every T, so a token's 1/rms does not depend on how many sessions
     // share the step.  Measured alternatives: eight tokens in flight spills registers into the GEMM main loops
@@ -208,9 +210,14 @@ __device__ __forceinline__ void rms_stats_128(const GemmParams& p, int T, int e,
         const uint16_t* xa = p.x + (size_t)t0 * p.ldx;
         const uint16_t* xb = xa + (two ? p.ldx : 0);
         for (int c = e; c < p.K / 8; c += 128) {
-            const uint4 va = ld_cg_v4(xa + c * 8);
-            uint4 vb = make_uint4(0, 0, 0, 0);
-            if (two) vb = ld_cg_v4(xb + c * 8);
+            uint4 va, vb = make_uint4(0, 0, 0, 0);
+            if (LLIO) {
+                va = ll_load8(p.ch.x + (size_t)t0 * p.ch.ldx + c * 4, xtag);
+                if (two) vb = ll_load8(p.ch.x + (size_t)(t0 + 1) * p.ch.ldx + c * 4, xtag);
+            } else {
+                va = ld_cg_v4(xa + c * 8);
+                if (two) vb = ld_cg_v4(xb + c * 8);
+            }
             const uint32_t wa[4] = {va.x, va.y, va.z, va.w};
             const uint32_t wb[4] = {vb.x, vb.y, vb.z, vb.w};
 #pragma unroll
@@ -345,15 +352,19 @@ __device__ __forceinline__ float round16(float v, int is_bf16) {
     return h16_to_float(float_to_h16(v, is_bf16), is_bf16);
 }
 
-template <int BN, int DUAL>
+// LLIO: the residual is polled from LL words (tag rtag) and the 16-bit result is ALSO published as LL words (tag otag);
+// every lane of the warp must call (the lanes of a pair of rows combine their halves with a shuffle).
+template <int BN, int DUAL, int LLIO = 0>
 __device__ __forceinline__ void epilogue_store_chunk(const GemmParams& p, int n_tile, int t_tile,
                                                      int row, int chunk, const float (&vg)[16],
-                                                     const float (&vu)[16], const float* tok_scale = nullptr) {
+                                                     const float (&vu)[16], const float* tok_scale = nullptr,
+                                                     uint32_t rtag = 0, uint32_t otag = 0) {
     const int n = n_tile * kTileM + row;
-    if (n >= p.N) return;
-    const float b = p.bias ? h16_to_float(p.bias[n], p.is_bf16) : 0.0f;
-    const float ws_g = p.w_scale ? p.w_scale[n] : 1.0f;
-    const float ws_u = (DUAL && p.w_scale) ? p.w_scale[(size_t)p.n_tiles * kTileM + n] : 1.0f;
+    if (!LLIO && n >= p.N) return;
+    const bool live = n < p.N;
+    const float b = (p.bias && live) ? h16_to_float(p.bias[n], p.is_bf16) : 0.0f;
+    const float ws_g = (p.w_scale && live) ? p.w_scale[n] : 1.0f;
+    const float ws_u = (DUAL && p.w_scale && live) ? p.w_scale[(size_t)p.n_tiles * kTileM + n] : 1.0f;
 #pragma unroll
     for (int j = 0; j < 16; ++j) {
         const int t = t_tile * BN + chunk * 16 + j;
@@ -369,25 +380,33 @@ __device__ __forceinline__ void epilogue_store_chunk(const GemmParams& p, int n_
         } else if (p.epilogue == B200_EPI_GELU_TANH) {
             v = gelu_tanh(round16(v, p.is_bf16));
         }
-        if (p.residual) {
+        if (LLIO && p.ch.res) {
+            if (live) v = round16(v, p.is_bf16) + h16_to_float(ll_load1(p.ch.res + (size_t)t * p.ch.ldr, n, rtag), p.is_bf16);
+        } else if (p.residual) {
             v = round16(v, p.is_bf16) + h16_to_float(__ldcg(p.residual + (size_t)t * p.ldr + n), p.is_bf16);
         }
         if (p.out_fp32) {
-            reinterpret_cast<float*>(p.out)[(size_t)t * p.ldo + n] = v;
+            if (live) reinterpret_cast<float*>(p.out)[(size_t)t * p.ldo + n] = v;
         } else {
-            reinterpret_cast<uint16_t*>(p.out)[(size_t)t * p.ldo + n] = float_to_h16(v, p.is_bf16);
+            const uint16_t hv = float_to_h16(v, p.is_bf16);
+            if (live && p.out) reinterpret_cast<uint16_t*>(p.out)[(size_t)t * p.ldo + n] = hv;
+            if (LLIO && p.ch.out) ll_store_pairwise(p.ch.out + (size_t)t * p.ch.ldo, n, hv, live, otag);
         }
     }
 }
 
 // The same epilogue for ONE element (output feature n, token t): used by the wide ticket-free fix-up, where a thread
 // finishes elements of rows it did not accumulate.  Expression order as in epilogue_store_chunk (bit-identical).
-template <int DUAL>
-__device__ __forceinline__ void epilogue_store_scalar(const GemmParams& p, int n, int t, float g_sum, float u_sum, float ts) {
-    if (n >= p.N || t >= p.T) return;
-    const float b = p.bias ? h16_to_float(p.bias[n], p.is_bf16) : 0.0f;
-    const float ws_g = p.w_scale ? p.w_scale[n] : 1.0f;
-    const float ws_u = (DUAL && p.w_scale) ? p.w_scale[(size_t)p.n_tiles * kTileM + n] : 1.0f;
+// LLIO: as above; `valid` = this lane has an element at all (every lane of the warp calls, consecutive lanes hold
+// consecutive n of one token).
+template <int DUAL, int LLIO = 0>
+__device__ __forceinline__ void epilogue_store_scalar(const GemmParams& p, int n, int t, float g_sum, float u_sum, float ts,
+                                                      bool valid = true, uint32_t rtag = 0, uint32_t otag = 0) {
+    const bool live = valid && n < p.N && t < p.T;
+    if (!LLIO && !live) return;
+    const float b = (p.bias && live) ? h16_to_float(p.bias[n], p.is_bf16) : 0.0f;
+    const float ws_g = (p.w_scale && live) ? p.w_scale[n] : 1.0f;
+    const float ws_u = (DUAL && p.w_scale && live) ? p.w_scale[(size_t)p.n_tiles * kTileM + n] : 1.0f;
     float v = g_sum * ts * ws_g + b;
     if (DUAL) {
         const float g = round16(v, p.is_bf16);
@@ -397,9 +416,18 @@ __device__ __forceinline__ void epilogue_store_scalar(const GemmParams& p, int n
     } else if (p.epilogue == B200_EPI_GELU_TANH) {
         v = gelu_tanh(round16(v, p.is_bf16));
     }
-    if (p.residual) v = round16(v, p.is_bf16) + h16_to_float(__ldcg(p.residual + (size_t)t * p.ldr + n), p.is_bf16);
-    if (p.out_fp32) reinterpret_cast<float*>(p.out)[(size_t)t * p.ldo + n] = v;
-    else reinterpret_cast<uint16_t*>(p.out)[(size_t)t * p.ldo + n] = float_to_h16(v, p.is_bf16);
+    if (LLIO && p.ch.res) {
+        if (live) v = round16(v, p.is_bf16) + h16_to_float(ll_load1(p.ch.res + (size_t)t * p.ch.ldr, n, rtag), p.is_bf16);
+    } else if (p.residual) {
+        v = round16(v, p.is_bf16) + h16_to_float(__ldcg(p.residual + (size_t)t * p.ldr + n), p.is_bf16);
+    }
+    if (p.out_fp32) {
+        if (live) reinterpret_cast<float*>(p.out)[(size_t)t * p.ldo + n] = v;
+        return;
+    }
+    const uint16_t hv = float_to_h16(v, p.is_bf16);
+    if (live && p.out) reinterpret_cast<uint16_t*>(p.out)[(size_t)t * p.ldo + n] = hv;
+    if (LLIO && p.ch.out) ll_store_pairwise(p.ch.out + (size_t)(live ? t : 0) * p.ch.ldo, n, hv, live, otag);
 }
 
 }  // namespace b200

@@ -6,6 +6,9 @@ import ctypes as C
 vp, i32, i64, f32 = C.c_void_p, C.c_int32, C.c_int64, C.c_float
 
 
+from .native import LLChainArgs as _LLChainArgs  # noqa: E402
+
+
 class AttnDecodeArgs(C.Structure):
     """Mirror of ``b200_attn_decode_args``."""
 
@@ -14,19 +17,8 @@ class AttnDecodeArgs(C.Structure):
         ("counters", vp),
         ("T", i32), ("n_heads", i32), ("n_kv_heads", i32), ("head_dim", i32), ("s_max", i32),
         ("splits", i32), ("ldqkv", i32), ("ldo", i32),
-        ("scale", f32), ("dtype", i32), ("pdl", i32), ("ll_scratch", vp),
+        ("scale", f32), ("dtype", i32), ("pdl", i32), ("ll_scratch", vp), ("chain", _LLChainArgs),
     ]
-
-
-def _mega_op_type():
-    from .native import GemmArgs
-
-    class MegaOp(C.Structure):
-        """Mirror of ``b200_mega_op``."""
-
-        _fields_ = [("type", i32), ("reserved", i32), ("gemm", GemmArgs), ("attn", AttnDecodeArgs)]
-
-    return MegaOp
 
 
 class SampleRow(C.Structure):
@@ -49,12 +41,11 @@ PROTOTYPES = [
     ("b200_hop_send", [C.POINTER(HopArgs), vp], C.c_int),
     ("b200_hop_recv", [C.POINTER(HopArgs), vp], C.c_int),
     ("b200_hop_init", [], C.c_int),
+    ("b200_ll_publish", [vp, i32, vp, i32, i32, i32, vp, i32, i32, vp], C.c_int),
+    ("b200_trace_set", [vp, i32], C.c_int),
     ("b200_argmax_partial", [vp, i32, i32, i32, vp, vp, vp, vp, i32, i32, vp, vp, i32, vp], C.c_int),
     ("b200_sample_row_bytes", [], i32),
     ("b200_sample", [vp, i32, i32, i32, vp, vp, vp, vp, i32, vp], C.c_int),
-    ("b200_decode_mega_plan_bytes", [i32], i64),
-    ("b200_decode_mega_build", [vp, i32, vp], C.c_int),
-    ("b200_decode_mega_launch", [vp, i32, vp, i32, i32, vp], C.c_int),
     ("b200_gemm_static_scratch", [vp, vp], C.c_int),
     ("b200_attn_decode", [C.POINTER(AttnDecodeArgs), vp], C.c_int),
     ("b200_attn_decode_scratch_bytes", [i32, i32, i32, i32], i64),

@@ -44,8 +44,10 @@ class DecodeAttnWorkspace:
 
 
 def attn_decode(qkv, out, kv_ptrs, pos, inv_freq, ws: DecodeAttnWorkspace, n_heads, n_kv_heads, head_dim, s_max,
-                scale=None, pdl=False):
+                scale=None, pdl=False, chain=None):
     a = fill_decode_args(qkv, out, kv_ptrs, pos, inv_freq, ws, n_heads, n_kv_heads, head_dim, s_max, scale, pdl)
+    if chain is not None:
+        a.chain = chain
     native.check(native.lib().b200_attn_decode(ctypes.byref(a), native.current_stream_ptr()), "b200_attn_decode")
     return out
 

@@ -68,3 +68,11 @@ def argmax(logits: torch.Tensor, out_ids: Optional[torch.Tensor], ws: ArgmaxWork
                                           1 if pdl else 0, native.current_stream_ptr())
     native.check(rc, "b200_argmax")
     return out_ids
+
+
+def ll_publish(x: torch.Tensor, out_ll: torch.Tensor, seq: torch.Tensor, op: int, pdl: bool = False) -> None:
+    """Head of a flag chain: x [T, H] (16-bit) -> LL words in out_ll [T, ld] (int64) tagged (seq << 12 | op)."""
+    T, H = x.shape
+    rc = native.lib().b200_ll_publish(x.data_ptr(), x.stride(0), out_ll.data_ptr(), out_ll.stride(0), T, H,
+                                      seq.data_ptr(), op, 1 if pdl else 0, native.current_stream_ptr())
+    native.check(rc, "b200_ll_publish")

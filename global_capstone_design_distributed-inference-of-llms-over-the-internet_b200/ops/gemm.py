@@ -80,11 +80,15 @@ def linear(
     debug: int = 0,
     prefetch=None,
     rstd: Optional[torch.Tensor] = None,
+    chain=None,
 ) -> torch.Tensor:
-    """x: [T, K] (16-bit, last dim contiguous) -> [T, N]."""
+    """x: [T, K] (16-bit, last dim contiguous) -> [T, N].
+
+    ``chain``: a :class:`petals_b200.ops.native.LLChainArgs` making this launch a link of a flag-chained decode step
+    (see ``b200_ll_chain`` in the header)."""
     a, out = fill_args(x, w, out=out, residual=residual, epilogue=epilogue, norm_mode=norm_mode, norm_w=norm_w,
                        norm_b=norm_b, norm_eps=norm_eps, out_fp32=out_fp32, workspace=workspace, pdl=pdl, grid=grid,
-                       debug=debug, prefetch=prefetch, rstd=rstd)
+                       debug=debug, prefetch=prefetch, rstd=rstd, chain=chain)
     if uses_prefill_kernel(x.shape[0], w, norm_mode):
         # token-tile-filling inputs: TMA-fed kernel with the epilogue overlapped (csrc/gemm_prefill.cu)
         rc = native.lib().b200_gemm_prefill(ctypes.byref(a), native.current_stream_ptr())
@@ -116,7 +120,8 @@ def _prefill_kernel_enabled() -> bool:
 
 
 def fill_args(x, w, *, out=None, residual=None, epilogue=EPI_NONE, norm_mode=NORM_NONE, norm_w=None, norm_b=None,
-              norm_eps=1e-5, out_fp32=False, workspace=None, pdl=False, grid=0, debug=0, prefetch=None, rstd=None):
+              norm_eps=1e-5, out_fp32=False, workspace=None, pdl=False, grid=0, debug=0, prefetch=None, rstd=None,
+              chain=None):
     """Builds the ``b200_gemm_args`` for one call (also used to describe ops of the persistent kernel)."""
     assert x.dim() == 2 and x.stride(1) == 1 and x.is_cuda
     T, K = x.shape
@@ -155,6 +160,8 @@ def fill_args(x, w, *, out=None, residual=None, epilogue=EPI_NONE, norm_mode=NOR
     a.w_scale = w.scale.data_ptr() if w.scale is not None else None
     a.ll_buf = ws.ll.data_ptr() if ws.ll is not None else None
     a.rstd = rstd.data_ptr() if rstd is not None else None
+    if chain is not None:
+        a.chain = chain
     # prefetch: up to two (PackedWeight | tensor, first_byte, n_bytes) ranges to warm the L2 with
     for i, (t, off, nbytes) in enumerate(prefetch or ()):
         data = t.data if hasattr(t, "n_tiles") else t
@@ -163,3 +170,15 @@ def fill_args(x, w, *, out=None, residual=None, epilogue=EPI_NONE, norm_mode=NOR
         a.prefetch[i] = data.data_ptr() + off
         a.prefetch_bytes[i] = max(0, min(nbytes, total - off))
     return a, out
+
+
+def chain_capable(w: PackedWeight, T: int = 1) -> bool:
+    """Would b200_gemm, as a link of a flag chain, exchange the stream-K partials of this weight through the
+    per-launch-tagged wide words (the only exchange two overlapping launches may share)?  Mirrors the grid choice
+    in csrc/gemm.cu: 2..9 CTAs per output tile, each with at least one k-block."""
+    if w.fp8 or T > 16:
+        return False
+    sms = native.lib().b200_sm_count()
+    kbpt = w.k_padded // 64
+    parts = min((2 * sms) // w.n_tiles, 9, kbpt)
+    return parts >= 2 and parts * w.n_tiles <= 512

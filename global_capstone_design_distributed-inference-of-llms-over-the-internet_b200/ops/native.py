@@ -20,6 +20,15 @@ class NativeError(RuntimeError):
     pass
 
 
+class LLChainArgs(ctypes.Structure):
+    """Mirror of ``b200_ll_chain``."""
+
+    _fields_ = [("seq", ctypes.c_void_p), ("x_ll", ctypes.c_void_p), ("res_ll", ctypes.c_void_p),
+                ("out_ll", ctypes.c_void_p), ("ldx_ll", ctypes.c_int32), ("ldr_ll", ctypes.c_int32),
+                ("ldo_ll", ctypes.c_int32), ("x_op", ctypes.c_int32), ("res_op", ctypes.c_int32),
+                ("out_op", ctypes.c_int32), ("half", ctypes.c_int32), ("reserved", ctypes.c_int32)]
+
+
 class GemmArgs(ctypes.Structure):
     """Mirror of ``b200_gemm_args`` (include/b200_petals.h)."""
 
@@ -55,6 +64,7 @@ class GemmArgs(ctypes.Structure):
         ("prefetch_bytes", ctypes.c_int64 * 2),
         ("ll_buf", ctypes.c_void_p),
         ("rstd", ctypes.c_void_p),
+        ("chain", LLChainArgs),
     ]
 
 

@@ -40,6 +40,9 @@ MAX_DECODE_BATCH = 32
 
 
 RSTD_KERNEL_MIN_TOKENS = int(os.environ.get("B200_RSTD_KERNEL_MIN_TOKENS", "8"))
+# Decode steps of up to this many tokens run as a flag chain (b200_ll_chain): the kernels of the step hand their
+# activations over as self-validating words instead of waiting for each other's grids.  0 switches it off.
+CHAIN_MAX_TOKENS = int(os.environ.get("B200_LL_CHAIN_MAX_TOKENS", "4"))
 
 
 def _l2_prefetch_default():
@@ -61,16 +64,6 @@ def _pdl_default() -> bool:
     return os.environ.get("B200_PDL", "1") != "0"
 
 
-def _mega_default() -> bool:
-    # The persistent multi-op decode kernel is functionally complete and tested, but its per-op
-    # latency chain (grid barrier + stream-K fix-up) currently costs more than the launch gaps it
-    # removes (203 vs 239 tok/s on Llama-2-7B); it stays opt-in until that is fixed.
-    return os.environ.get("B200_MEGA", "0") == "1"
-
-
-MEGA_MAX_TOKENS = 16
-
-
 class StepProgram:
     """What a captured decode step does AROUND the blocks (the pipeline engine's in-graph hops).
 
@@ -88,7 +81,7 @@ class NativeSpan:
     def __init__(self, cfg: ModelConfig, weights: Dict[str, object], device, dtype: torch.dtype, *,
                  kv_capacity: int = 2048, max_batch: int = 8, max_chunk: int = 512, attn_splits: int = 0,
                  use_graphs: bool = True, pdl: Optional[bool] = None, free_source_weights: bool = True,
-                 use_mega: Optional[bool] = None, mega_grid: int = 0, weight_format: str = "native",
+                 weight_format: str = "native",
                  head_rows: Optional[tuple] = None):
         assert dtype in (torch.float16, torch.bfloat16), "native path runs fp16/bf16"
         self.cfg, self.device, self.dtype = cfg, torch.device(device), dtype
@@ -108,9 +101,6 @@ class NativeSpan:
         self.l2_prefetch_mb = _l2_prefetch_default()
         self._prefill_plans = {}
         self._planned_prefill = os.environ.get("B200_PREFILL_PLAN", "1") != "0"
-        self.use_mega = _mega_default() if use_mega is None else use_mega
-        self.mega_grid = mega_grid      # 0 = all SMs; leave a few free when NCCL kernels run concurrently
-        self._mega_plans: Dict[tuple, tuple] = {}
         self.has_embed = bool(weights.get("has_embed", False))
         self.has_head = bool(weights.get("has_head", "lm_head" in weights))
         c = cfg
@@ -163,9 +153,19 @@ class NativeSpan:
             self.attn_ws = A.DecodeAttnWorkspace(self.device, self.max_batch, c.n_heads, c.n_kv_heads, c.head_dim,
                                                  self.splits)
             self.kv_ptrs = torch.zeros(max(nl, 1), self.max_batch, 2, dtype=torch.int64, device=self.device)
-            self.pos = torch.zeros(self.max_batch, dtype=torch.int32, device=self.device)
-            self._pos_ring = [(torch.zeros(self.max_batch, dtype=torch.int32).pin_memory(), torch.cuda.Event())
+            # positions of the step's tokens, then one more int: the step number the flag chain tags its words with
+            self.pos = torch.zeros(self.max_batch + 1, dtype=torch.int32, device=self.device)
+            self.step_seq = self.pos[self.max_batch:]
+            self._seq_host = 0
+            self._pos_ring = [(torch.zeros(self.max_batch + 1, dtype=torch.int32).pin_memory(), torch.cuda.Event())
                               for _ in range(8)]
+            self.chain_tokens = 0
+            if (CHAIN_MAX_TOKENS > 0 and not fp8 and self.layers
+                    and all(G.chain_capable(P[k]) for P in self.layers for k in ("qkv", "o", "mlp_in", "down"))):
+                Tc = self.chain_tokens = min(CHAIN_MAX_TOKENS, self.max_batch, RSTD_KERNEL_MIN_TOKENS - 1)
+                ll = lambda width: torch.zeros(Tc, (width // 2 + 3) // 4 * 4, dtype=torch.int64, device=self.device)  # noqa: E731
+                self.h_a_ll, self.h_b_ll = ll(c.hidden), ll(c.hidden)
+                self.qkv_ll, self.attn_ll, self.act_ll = ll(c.qkv_size), ll(c.q_size), ll(self.act.shape[1])
             self._pos_ring_idx = 0
             self._ptr_tables: Dict[tuple, torch.Tensor] = {}
             if self.has_head:
@@ -231,6 +231,9 @@ class NativeSpan:
         mb = self.l2_prefetch_mb if T <= 32 else None
         n = len(self.layers)
         M = 1 << 20
+        chain = self._chain_on(T)
+        if chain:
+            return self._decode_layers_chain(T, h, other, mb)
         for li, P in enumerate(self.layers):
             qkv, attn, act, h2 = self.qkv[:T], self.attn[:T], self.act[:T], other[:T]
             pf = [None] * 4
@@ -258,6 +261,68 @@ class NativeSpan:
                      norm_b=P["ln2_b"], norm_eps=c.norm_eps, workspace=self.ws, pdl=pdl, prefetch=pf[2], rstd=rs)
             self._row_parallel(act, P["down"], h, h2, prefetch=pf[3])
             self._count(5)
+        return h
+
+    def _chain_on(self, T: int) -> bool:
+        return 0 < T <= self.chain_tokens and self.tp_mode is None and self.pdl
+
+    def _link(self, x_ll, x_op, out_ll, out_op, res_ll=None, res_op=0):
+        """One link of the flag chain (see b200_ll_chain): who produced the input words, where the output words go."""
+        a = native.LLChainArgs()
+        a.seq = self.step_seq.data_ptr()
+        a.x_ll, a.ldx_ll, a.x_op = x_ll.data_ptr(), x_ll.stride(0), x_op
+        if res_ll is not None:
+            a.res_ll, a.ldr_ll, a.res_op = res_ll.data_ptr(), res_ll.stride(0), res_op
+        if out_ll is not None:
+            a.out_ll, a.ldo_ll = out_ll.data_ptr(), out_ll.stride(0)
+        a.out_op = out_op
+        a.half = self._chain_half
+        return a
+
+    def _decode_layers_chain(self, T: int, h: torch.Tensor, other: torch.Tensor, mb) -> torch.Tensor:
+        """The blocks of a decode step as one flag chain: 5 launches per block as before, but no launch waits for
+        the grid before it - every kernel polls the tagged words it needs (h -> qkv -> attn -> h2 -> act -> h)."""
+        c, pdl = self.cfg, True
+        n = len(self.layers)
+        M = 1 << 20
+        h_ll = self.h_a_ll if h.data_ptr() == self.h_a.data_ptr() else self.h_b_ll
+        o_ll = self.h_b_ll if h_ll is self.h_a_ll else self.h_a_ll
+        qkv, attn, act, h2 = self.qkv[:T], self.attn[:T], self.act[:T], other[:T]
+        op = 1
+        E.ll_publish(h, h_ll, self.step_seq, op, pdl=pdl)     # head of the chain: waits for whatever produced h
+        self._count()
+        h_op = op
+        self._chain_half = 0
+
+        def gemm(x, w, x_ll, x_op, out, out_ll, res=None, res_ll=None, res_op=0, prefetch=None, **kw):
+            nonlocal op
+            op += 1
+            G.linear(x, w, out=out, residual=res, workspace=self.ws, pdl=pdl, prefetch=prefetch,
+                     chain=self._link(x_ll, x_op, out_ll, op, res_ll, res_op), **kw)
+            self._chain_half ^= 1
+            return op
+
+        for li, P in enumerate(self.layers):
+            pf = [None] * 4
+            if mb:
+                nxt = self.layers[li + 1]["qkv"] if li + 1 < n else (self.lm_head if self.has_head else None)
+                pf[0] = [(P["o"], 0, P["o"].nbytes), (P["mlp_in"], 0, mb[0] * M)]
+                pf[1] = [(P["mlp_in"], mb[0] * M, mb[1] * M)]
+                pf[2] = [(P["down"], 0, mb[2] * M)]
+                pf[3] = [(nxt, 0, mb[3] * M)] if nxt is not None else None
+            q_op = gemm(h, P["qkv"], h_ll, h_op, qkv, self.qkv_ll, prefetch=pf[0], norm_mode=self.norm_mode,
+                        norm_w=P["ln1_w"], norm_b=P["ln1_b"], norm_eps=c.norm_eps)
+            op += 1
+            a_op = op
+            A.attn_decode(qkv, attn, self.kv_ptrs[li], self.pos, self.inv_freq, self.attn_ws, c.n_heads, c.n_kv_heads,
+                          c.head_dim, self.kv_capacity, self.scale, pdl=pdl,
+                          chain=self._link(self.qkv_ll, q_op, self.attn_ll, a_op))
+            o_op = gemm(attn, P["o"], self.attn_ll, a_op, h2, o_ll, res=h, res_ll=h_ll, res_op=h_op, prefetch=pf[1])
+            m_op = gemm(h2, P["mlp_in"], o_ll, o_op, act, self.act_ll, prefetch=pf[2], epilogue=self.mlp_epi,
+                        norm_mode=self.norm_mode, norm_w=P["ln2_w"], norm_b=P["ln2_b"], norm_eps=c.norm_eps)
+            h_op = gemm(act, P["down"], self.act_ll, m_op, h, h_ll, res=h2, res_ll=o_ll, res_op=o_op, prefetch=pf[3])
+            self._count(5)
+        self._chain_tail = (h_ll, h_op)      # the head GEMM (if any) continues the chain
         return h
 
     def _decode_layers_tp_deferred(self, T: int, h: torch.Tensor, other: torch.Tensor) -> torch.Tensor:
@@ -301,8 +366,14 @@ class NativeSpan:
         c = self.cfg
         B = h_rows.shape[0]
         logits = self.logits[:B]
+        link = None
+        tail = getattr(self, "_chain_tail", None)
+        if tail is not None:       # directly behind the blocks of a flag-chained step: poll their output words
+            self._chain_tail = None
+            link = self._link(tail[0], tail[1], None, tail[1] + 1)
         G.linear(h_rows, self.lm_head, out=logits, norm_mode=self.norm_mode, norm_w=self.final_norm_w,
-                 norm_b=self.final_norm_b, norm_eps=c.norm_eps, out_fp32=True, workspace=self.ws, pdl=self.pdl)
+                 norm_b=self.final_norm_b, norm_eps=c.norm_eps, out_fp32=True, workspace=self.ws, pdl=self.pdl,
+                 chain=link)
         self._count()
         if greedy:
             ids = self.ids_out[:B] if out_ids is None else out_ids
@@ -356,7 +427,9 @@ class NativeSpan:
             if kv.length + 1 > kv.max_len:
                 raise ValueError(f"session {kv.session_id}: max_length {kv.max_len} reached")
             host[b] = kv.length
-        self.pos[:B].copy_(host[:B], non_blocking=True)
+        self._seq_host = self._seq_host % 1000000 + 1        # a new step number for every staged step (never 0)
+        host[self.max_batch] = self._seq_host
+        self.pos.copy_(host, non_blocking=True)
         ev.record(torch.cuda.current_stream(self.device))
 
     def prestage(self, kvs: Sequence[SessionKV]) -> None:
@@ -371,77 +444,14 @@ class NativeSpan:
         if prog is not None and not prog.layers:
             return None
         h = self._embed(B, 0, True) if from_ids else self.h_a[:B]
-        if (self.use_mega and B <= MEGA_MAX_TOKENS and self.tp_mode is None and self.weight_format == "native"
-                and prog is None):
-            return self._decode_mega(B, h, greedy)
+        self._chain_tail = None
         h = self._decode_layers(B, h)
         if self.has_head and (prog is None or prog.head):
             self._head(h, greedy, out_pair=getattr(prog, "out_pair", None) if prog is not None else None)
+        self._chain_tail = None
         if prog is not None and prog.post is not None:
             prog.post(B, h, dry)
         return h
-
-    # ------------------------------------------------------------------ persistent decode kernel
-    def _mega_plan(self, B: int):
-        """Op list of one decode step (all blocks [+ LM head]) for the persistent kernel."""
-        plan = self._mega_plans.get(B)
-        if plan is not None:
-            return plan
-        from ..ops import native
-        from ..ops._prototypes import _mega_op_type
-
-        MegaOp = _mega_op_type()
-        c = self.cfg
-        ops = []
-
-        def gemm_op(x, w, **kw):
-            a, _ = G.fill_args(x, w, workspace=self.ws, **kw)
-            op = MegaOp()
-            op.type = 0
-            op.gemm = a
-            ops.append(op)
-
-        h, other = self.h_a[:B], self.h_b[:B]
-        qkv, attn, act = self.qkv[:B], self.attn[:B], self.act[:B]
-        for li, P in enumerate(self.layers):
-            gemm_op(h, P["qkv"], out=qkv, norm_mode=self.norm_mode, norm_w=P["ln1_w"], norm_b=P["ln1_b"],
-                    norm_eps=c.norm_eps)
-            op = MegaOp()
-            op.type = 1
-            op.attn = A.fill_decode_args(qkv, attn, self.kv_ptrs[li], self.pos, self.inv_freq, self.attn_ws, c.n_heads,
-                                         c.n_kv_heads, c.head_dim, self.kv_capacity, self.scale)
-            ops.append(op)
-            gemm_op(attn, P["o"], out=other, residual=h)
-            gemm_op(other, P["mlp_in"], out=act, epilogue=self.mlp_epi, norm_mode=self.norm_mode, norm_w=P["ln2_w"],
-                    norm_b=P["ln2_b"], norm_eps=c.norm_eps)
-            gemm_op(act, P["down"], out=h, residual=other)
-        if self.has_head:
-            gemm_op(h, self.lm_head, out=self.logits[:B], norm_mode=self.norm_mode, norm_w=self.final_norm_w,
-                    norm_b=self.final_norm_b, norm_eps=c.norm_eps, out_fp32=True)
-        n = len(ops)
-        arr = (MegaOp * n)(*ops)
-        L = native.lib()
-        dev_plan = torch.empty(L.b200_decode_mega_plan_bytes(n), dtype=torch.uint8, device=self.device)
-        with torch.cuda.device(self.device):
-            native.check(L.b200_decode_mega_build(arr, n, dev_plan.data_ptr()), "b200_decode_mega_build")
-        if not hasattr(self, "_mega_bar"):
-            self._mega_bar = torch.zeros(1, dtype=torch.int32, device=self.device)
-        plan = (dev_plan, n)
-        self._mega_plans[B] = plan
-        return plan
-
-    def _decode_mega(self, B: int, h: torch.Tensor, greedy: bool):
-        from ..ops import native
-
-        dev_plan, n = self._mega_plan(B)
-        rc = native.lib().b200_decode_mega_launch(dev_plan.data_ptr(), n, self._mega_bar.data_ptr(), self.mega_grid, 1,
-                                                  native.current_stream_ptr())
-        native.check(rc, "b200_decode_mega_launch")
-        self._count()
-        if self.has_head and greedy:
-            E.argmax(self.logits[:B], self.ids_out[:B], self.argmax_ws, pdl=False)
-            self._count()
-        return self.h_a[:B]
 
     def decode(self, kvs: Sequence[SessionKV], h_in: Optional[torch.Tensor] = None,
                ids: Optional[torch.Tensor] = None, greedy: bool = True, prog: Optional[StepProgram] = None):
@@ -482,6 +492,7 @@ class NativeSpan:
             g = self._graphs.get(key)
             if g is None:
                 g = self._capture(key, prog)   # runs the body once on whatever the buffers hold
+                self._stage_ptrs(kvs)          # a fresh step number: the warm-up run left chain words tagged with the old one
         if from_ids and ids is not None:
             self.ids_in[:B].copy_(ids, non_blocking=True)
         if not from_ids and h_in is not None:
@@ -545,12 +556,16 @@ class NativeSpan:
                 self.hist = torch.zeros(4096, self.max_batch, dtype=torch.int64, device=self.device)
                 self.step_idx = torch.zeros(1, dtype=torch.int64, device=self.device)
 
+            pos_inc = torch.zeros_like(self.pos)
+            pos_inc[:B] = 1
+            pos_inc[self.max_batch] = 1
+
             def body():
                 self._decode_body(B, True, True)
                 self.hist.index_copy_(0, self.step_idx, self.ids_out[:B].unsqueeze(0) if B == self.max_batch
                                       else torch.nn.functional.pad(self.ids_out[:B], (0, self.max_batch - B)).unsqueeze(0))
                 self.ids_in[:B].copy_(self.ids_out[:B])
-                self.pos[:B].add_(1)
+                self.pos.add_(pos_inc)            # positions of the B sessions and the chain's step number
                 self.step_idx.add_(1)
 
             before = self.kernel_launches

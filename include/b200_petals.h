@@ -60,6 +60,30 @@ int b200_sm_count(void);
 #define B200_NORM_RMS 1
 #define B200_NORM_LAYER 2
 
+/* Flag-chained decode step ("LL chain").  Between two kernel launches the GPU needs 3-4 us to notice that the
+ * first grid is complete and to release the second one's dependency wait - five times per decoder block, with
+ * the HBM idle.  With a chain the kernels of a decode step hand their activation vectors over as "LL words"
+ * (two 16-bit values + a 32-bit tag in one 8-byte store, the scheme of the stream-K and tensor-parallel
+ * exchanges): a consumer launched with programmatic stream serialization does NOT wait for the producer grid, it
+ * polls the words it needs until they carry the tag (step number << 12 | id of the producing launch).  Words are
+ * self-validating, so no fence, flag or grid dependency is needed, and a consumer starts on the first values while
+ * the producer is still finishing others.  The caller numbers the producing launches of a step (ids 1..4095, unique
+ * within the step), advances *seq once per step BEFORE the step's first launch (stream order), launches every kernel
+ * of the step with pdl = 1 into one stream, and ends the step with an ordinary (grid-dependent) kernel.
+ * LL buffers: [T][ld] 8-byte words, word i of a row = elements 2i, 2i+1; zero-initialised once.
+ * Replaces nothing in the reference (its blocks are eager torch ops, petals/llama/block.py:200-240); it removes the
+ * launch-boundary cost that CUDA graphs alone (petals/llama/cuda_graphs.py) leave in place. */
+typedef struct b200_ll_chain {
+    const int32_t* seq;   /* device: the step number (> 0); NULL = chain off, everything below ignored */
+    const void* x_ll;     /* input vector as LL words (the kernel then never reads args->x) */
+    const void* res_ll;   /* residual as LL words, when args->residual is set */
+    void* out_ll;         /* output as LL words (16-bit outputs; args->out is still written when non-NULL) */
+    int32_t ldx_ll, ldr_ll, ldo_ll;   /* row strides in words */
+    int32_t x_op, res_op, out_op;     /* launch ids: who produced x / the residual, and this launch's own id */
+    int32_t half;         /* 0/1: half of ll_buf for this launch's stream-K exchange; alternate between consecutive GEMMs */
+    int32_t reserved;
+} b200_ll_chain;
+
 typedef struct b200_gemm_args {
     const void* w_packed; /* b200_pack layout, see ops/packing.py */
     const void* x;        /* [T, K] 16-bit, row stride ldx elements */
@@ -104,6 +128,8 @@ typedef struct b200_gemm_args {
     /* Optional with norm_mode == B200_NORM_RMS: per-token 1/rms computed beforehand (b200_rms_rstd, same bits as the
      * in-kernel statistics); the kernel then skips its own statistics pass.  Pays off from ~8 tokens per step. */
     const float* rstd;
+    /* Optional flag chain (decode sizes, 16-bit weights, b200_gemm only): see b200_ll_chain. */
+    b200_ll_chain chain;
 } b200_gemm_args;
 
 int b200_gemm(const b200_gemm_args* args, void* stream);
@@ -182,6 +208,9 @@ typedef struct b200_attn_decode_args {
      * words and the last split polls, merges and clears them: no fence / atomic ticket in the merge.  Same
      * arithmetic and order as the ticket path.  NULL = ticket path (scratch + counters). */
     void* ll_scratch;
+    /* Optional flag chain (see b200_ll_chain): qkv is read from chain.x_ll (tag of chain.x_op) instead of waiting for
+     * the producer grid, the output also goes to chain.out_ll with chain.out_op; needs ll_scratch.  res_* unused. */
+    b200_ll_chain chain;
 } b200_attn_decode_args;
 int b200_attn_decode(const b200_attn_decode_args* args, void* stream);
 int64_t b200_attn_decode_scratch_bytes(int32_t T, int32_t n_heads, int32_t head_dim, int32_t splits);
@@ -197,30 +226,6 @@ int b200_attn_prefill(const void* q, void* out, const void* kcache, const void* 
                       int32_t n_kv_heads, int32_t head_dim, int32_t s_max, int32_t ldq, int32_t ldo, int32_t pos0,
                       float scale, int32_t dtype, int32_t pdl, void* stream);
 
-/* -------------------------------------------------- persistent decode kernel --
- * One cooperative launch runs a whole chain of decode ops (all blocks of a stage, plus the LM head):
- * GEMM ops with the same semantics as b200_gemm (T <= 16) and attention ops with the semantics of
- * b200_attn_decode.  Op i may read anything op i-1 wrote (a grid-wide barrier separates them); the
- * weight loader runs ahead across op boundaries so HBM never idles.  Replaces the reference's
- * per-op torch launches inside the layer loop (src/llama_partition.py:233-297) and its 3-op CUDA
- * graphs (petals/llama/cuda_graphs.py).
- *   b200_decode_mega_build   validates the op list and writes the device-side plan (synchronous
- *                            copy into plan_device, which must hold b200_decode_mega_plan_bytes()).
- *   b200_decode_mega_launch  zeroes *grid_barrier (one int, device) on the stream and launches;
- *                            grid <= SM count (0 = all SMs); every CTA must be co-resident, so leave
- *                            SMs free for concurrently running communication kernels if there are any.
- */
-typedef struct b200_mega_op {
-    int32_t type; /* 0 = GEMM, 1 = attention */
-    int32_t reserved;
-    b200_gemm_args gemm;
-    b200_attn_decode_args attn;
-} b200_mega_op;
-int64_t b200_decode_mega_plan_bytes(int32_t n_ops);
-int b200_decode_mega_build(const b200_mega_op* ops, int32_t n_ops, void* plan_device);
-int b200_decode_mega_launch(const void* plan_device, int32_t n_ops, int32_t* grid_barrier, int32_t grid,
-                            int32_t cooperative, void* stream);
-
 /* Same contract on the tensor cores: 128-query x 128-key tiles, S = QK^T and O = PV by tcgen05.mma
  * (V consumed in place as an MN-major operand), online softmax between them, accumulators in TMEM. */
 int b200_attn_prefill_tc(const void* q, void* out, const void* kcache, const void* vcache, int32_t T, int32_t n_heads,
@@ -232,6 +237,10 @@ int b200_attn_prefill_tc(const void* q, void* out, const void* kcache, const voi
  * ids are int64 on the device (the last stage writes them there). */
 int b200_embed(const void* ids, const void* pos, int32_t pos0, const void* wte, const void* wpe, void* out, int32_t T,
                int32_t H, int32_t vocab, int32_t max_pos, int32_t dtype, int32_t pdl, void* stream);
+/* Head of a flag chain: the 16-bit rows x[T, H] (already complete in stream order) re-published as LL words tagged
+ * (*seq << 12 | op), so that the chain's first GEMM can poll them like any other link of the chain. */
+int b200_ll_publish(const void* x, int32_t ldx, void* out_ll, int32_t ld_ll, int32_t T, int32_t H, const int32_t* seq,
+                    int32_t op, int32_t pdl, void* stream);
 /* Standalone RMSNorm (layer_norm=0) / LayerNorm (1) for prefill-size inputs: block.py:208-213. */
 /* rstd[t] = 1/sqrt(mean(x[t]^2) + eps), one block per token; see b200_gemm_args.rstd. */
 int b200_rms_rstd(const void* x, float* rstd, int32_t T, int32_t K, int32_t ldx, float eps, int32_t dtype, int32_t pdl,

@@ -2,7 +2,7 @@
 Writes profiles/sass_tcgen05_evidence.txt."""
 import collections, os, re, subprocess, sys, tempfile
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-SRC = ["gemm.cu", "gemm_prefill.cu", "attn_prefill_tc.cu", "attention.cu", "decode_mega.cu", "elementwise.cu", "sampling.cu"]
+SRC = ["gemm.cu", "gemm_prefill.cu", "attn_prefill_tc.cu", "attention.cu", "p2p.cu", "elementwise.cu", "sampling.cu"]
 WANT = ["UTCHMMA", "UTCQMMA", "UBLKCP", "UTMALDG", "LDTM", "STTM", "UTCBAR", "SYNCS", "USETMAXREG", "UTMAPF", "UBLKPF"]
 out = ["# cuobjdump -sass of the sm_100a objects: count of tensor-core / TMEM / TMA mnemonics per kernel",
        "# UTCHMMA/UTCQMMA = tcgen05.mma (f16 / f8f6f4), LDTM/STTM = tcgen05.ld/st, UBLKCP = cp.async.bulk,",

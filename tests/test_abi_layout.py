@@ -16,12 +16,13 @@ PROG = r"""
 #include <stddef.h>
 #include "b200_petals.h"
 int main(void) {
-    printf("gemm %zu %zu %zu %zu\n", sizeof(b200_gemm_args), offsetof(b200_gemm_args, w_scale),
-           offsetof(b200_gemm_args, ll_buf), offsetof(b200_gemm_args, rstd));
+    printf("gemm %zu %zu %zu %zu %zu\n", sizeof(b200_gemm_args), offsetof(b200_gemm_args, w_scale),
+           offsetof(b200_gemm_args, ll_buf), offsetof(b200_gemm_args, rstd), offsetof(b200_gemm_args, chain));
+    printf("chain %zu %zu %zu\n", sizeof(b200_ll_chain), offsetof(b200_ll_chain, ldx_ll), offsetof(b200_ll_chain, half));
     printf("tp %zu %zu %zu\n", sizeof(b200_tp_args), offsetof(b200_tp_args, seq), offsetof(b200_tp_args, mode));
-    printf("attn %zu %zu %zu\n", sizeof(b200_attn_decode_args), offsetof(b200_attn_decode_args, scale),
-           offsetof(b200_attn_decode_args, ll_scratch));
-    printf("mega %zu %zu %zu\n", sizeof(b200_mega_op), offsetof(b200_mega_op, gemm), offsetof(b200_mega_op, attn));
+    printf("attn %zu %zu %zu %zu\n", sizeof(b200_attn_decode_args), offsetof(b200_attn_decode_args, scale),
+           offsetof(b200_attn_decode_args, ll_scratch), offsetof(b200_attn_decode_args, chain));
+    printf("hop %zu %zu %zu\n", sizeof(b200_hop_args), offsetof(b200_hop_args, counter), offsetof(b200_hop_args, pdl));
     return 0;
 }
 """
@@ -29,8 +30,8 @@ int main(void) {
 
 @pytest.mark.skipif(shutil.which("gcc") is None, reason="needs a host C compiler")
 def test_ctypes_structs_match_the_header(tmp_path):
-    from petals_b200.ops._prototypes import AttnDecodeArgs, _mega_op_type
-    from petals_b200.ops.native import GemmArgs
+    from petals_b200.ops._prototypes import AttnDecodeArgs, HopArgs
+    from petals_b200.ops.native import GemmArgs, LLChainArgs
     from petals_b200.parallel.tensor_parallel import TpArgs
 
     src = tmp_path / "abi.c"
@@ -39,8 +40,10 @@ def test_ctypes_structs_match_the_header(tmp_path):
     subprocess.check_call(["gcc", "-I", os.path.join(ROOT, "include"), str(src), "-o", str(exe)])
     out = dict((ln.split()[0], [int(v) for v in ln.split()[1:]])
                for ln in subprocess.check_output([str(exe)], text=True).strip().splitlines())
-    MegaOp = _mega_op_type()
-    assert out["gemm"] == [ctypes.sizeof(GemmArgs), GemmArgs.w_scale.offset, GemmArgs.ll_buf.offset, GemmArgs.rstd.offset]
+    assert out["gemm"] == [ctypes.sizeof(GemmArgs), GemmArgs.w_scale.offset, GemmArgs.ll_buf.offset, GemmArgs.rstd.offset,
+                           GemmArgs.chain.offset]
+    assert out["chain"] == [ctypes.sizeof(LLChainArgs), LLChainArgs.ldx_ll.offset, LLChainArgs.half.offset]
     assert out["tp"] == [ctypes.sizeof(TpArgs), TpArgs.seq.offset, TpArgs.mode.offset]
-    assert out["attn"] == [ctypes.sizeof(AttnDecodeArgs), AttnDecodeArgs.scale.offset, AttnDecodeArgs.ll_scratch.offset]
-    assert out["mega"] == [ctypes.sizeof(MegaOp), MegaOp.gemm.offset, MegaOp.attn.offset]
+    assert out["attn"] == [ctypes.sizeof(AttnDecodeArgs), AttnDecodeArgs.scale.offset, AttnDecodeArgs.ll_scratch.offset,
+                           AttnDecodeArgs.chain.offset]
+    assert out["hop"] == [ctypes.sizeof(HopArgs), HopArgs.counter.offset, HopArgs.pdl.offset]

@@ -51,22 +51,6 @@ def test_prefill_then_decode_matches_oracle(name, dtype, graphs):
     assert kn.length == L + 12
 
 
-def test_persistent_decode_kernel_matches_multi_kernel_path():
-    """The one-launch persistent decode kernel must be bit-identical to the per-op launches."""
-    cfg, ref, nat, mref, mnat = _build("tiny-llama-gqa", torch.bfloat16, use_mega=False)
-    _, _, nat2, _, mnat2 = _build("tiny-llama-gqa", torch.bfloat16, use_mega=True)
-    torch.manual_seed(2)
-    ids = torch.randint(0, cfg.vocab, (30,), device="cuda")
-    ka, kb = mnat.allocate("a", 256), mnat2.allocate("a", 256)
-    _, ta = nat.prefill(ka, ids=ids)
-    _, tb = nat2.prefill(kb, ids=ids)
-    assert torch.equal(ta, tb)
-    for _ in range(6):
-        la, ta = nat.decode([ka], ids=ta.clone())
-        lb, tb = nat2.decode([kb], ids=tb.clone())
-        assert torch.equal(la, lb) and torch.equal(ta, tb)
-
-
 def test_batched_decode_equals_single(monkeypatch):
     cfg, ref, nat, mref, mnat = _build("tiny-llama-gqa", torch.bfloat16)
     torch.manual_seed(1)
@@ -103,3 +87,39 @@ def test_fp8_weight_span_tracks_the_oracle():
         assert (ln - lr).abs().max().item() < 0.15 * scale
     w16 = sum(P[k].nbytes for P in nat.layers for k in ("qkv", "o", "mlp_in", "down"))
     assert w16 == cfg.n_layers * (cfg.qkv_size * cfg.hidden + cfg.hidden * cfg.q_size + 3 * cfg.hidden * cfg.intermediate)
+
+
+@pytest.mark.parametrize("name", ["tiny-llama", "tiny-llama-gqa", "tiny-gpt2"])
+@pytest.mark.parametrize("graphs", [True, False])
+def test_flag_chained_decode_is_bit_identical(name, graphs):
+    """A decode step run as a flag chain (kernels poll tagged words instead of waiting for each other's grids) must
+    give exactly the logits of the grid-ordered step: same arithmetic, same summation order - for 1..4 sessions per
+    step, over several steps (stale words of an earlier step must never be taken for new ones)."""
+    cfg, _, chain, _, m1 = _build(name, torch.bfloat16, use_graphs=graphs)
+    _, _, plain, _, m2 = _build(name, torch.bfloat16, use_graphs=graphs)
+    assert chain.chain_tokens >= 4, "the tiny presets must qualify for the chain"
+    plain.chain_tokens = 0
+    torch.manual_seed(5)
+    prompts = [torch.randint(0, cfg.vocab, (n,), device="cuda") for n in (33, 7, 50, 12)]
+    ka = [m1.allocate(f"a{i}", 256) for i in range(4)]
+    kb = [m2.allocate(f"b{i}", 256) for i in range(4)]
+    toks = []
+    for p, x, y in zip(prompts, ka, kb):
+        _, t1 = chain.prefill(x, ids=p)
+        _, t2 = plain.prefill(y, ids=p)
+        assert torch.equal(t1, t2)
+        toks.append(t1.clone())
+    ids = torch.cat(toks)
+    launches0 = chain.kernel_launches
+    for step in range(6):
+        for B in (1, 2, 4, 3):                      # alternating batch sizes share the word buffers
+            la, ta = chain.decode(ka[:B], ids=ids[:B].clone())
+            lb, tb = plain.decode(kb[:B], ids=ids[:B].clone())
+            assert torch.equal(la, lb), f"step {step} batch {B}: chained logits differ"
+            assert torch.equal(ta, tb)
+            ids[:B] = ta
+    assert chain.kernel_launches > launches0
+    # the device-resident greedy loop (positions and the step number advance inside the graph)
+    ha = chain.decode_loop(ka[:2], ids[:2].clone(), 5).clone()
+    hb = plain.decode_loop(kb[:2], ids[:2].clone(), 5).clone()
+    assert torch.equal(ha, hb)
