@@ -150,6 +150,15 @@ __device__ __forceinline__ void attn_decode_body(const AttnDecodeParams& p, int 
         otag = ll_tag(seq, p.ch.out_op);
         row_ll = p.ch.x + (size_t)t * p.ch.ldx;
     }
+    if (chain) {   // cheap wait for this item's q heads, k and v (see ll_wait_range), then everybody loads
+        constexpr int kSent = D / 16;           // sentinels per head vector
+        for (int i = tid; i < (GROUP + 2) * kSent; i += kAttnThreads) {
+            const int hv = i / kSent, k = i - hv * kSent;
+            const int off = (hv < GROUP) ? q_off + hv * D : (hv == GROUP ? k_off : v_off);
+            ll_wait_range(row_ll + (off >> 1) + (k << 3), 0, 1, 0, 1, xtag, 0, 1, -1);
+        }
+        sync();
+    }
     auto load8 = [&](int off) -> uint4 {       // 8 elements of this token's qkv row starting at element `off`
         return chain ? ll_load8(row_ll + (off >> 1), xtag) : ld_cg_v4(row + off);
     };

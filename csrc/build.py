@@ -56,17 +56,22 @@ def _newer(target: str, deps: list[str]) -> bool:
     return any(os.path.getmtime(d) > t for d in deps)
 
 
-def build(force: bool = False, verbose: bool = False) -> str:
-    os.makedirs(OBJ_DIR, exist_ok=True)
+def build(force: bool = False, verbose: bool = False, trace: bool = False) -> str:
+    """trace=True builds the variant with the device-side event trace compiled in (csrc/trace.cuh) as
+    ops/libb200petals_trace.so; select it with B200_LIB (scripts/trace_decode.py does)."""
+    obj_dir = OBJ_DIR + ("_trace" if trace else "")
+    out_lib = OUT_LIB.replace(".so", "_trace.so") if trace else OUT_LIB
+    extra = ["-DB200_TRACE"] if trace else []
+    os.makedirs(obj_dir, exist_ok=True)
     nvcc = _nvcc()
     headers = _headers()
     jobs = []
     objs = []
     for src in _sources():
-        obj = os.path.join(OBJ_DIR, os.path.basename(src)[:-3] + ".o")
+        obj = os.path.join(obj_dir, os.path.basename(src)[:-3] + ".o")
         objs.append(obj)
         if force or _newer(obj, [src] + headers):
-            cmd = [nvcc, *NVCC_FLAGS, "-I", os.path.join(ROOT, "include"), "-c", src, "-o", obj]
+            cmd = [nvcc, *NVCC_FLAGS, *extra, "-I", os.path.join(ROOT, "include"), "-c", src, "-o", obj]
             if verbose:
                 cmd.insert(1, "-Xptxas=-v")
             jobs.append(cmd)
@@ -82,18 +87,19 @@ def build(force: bool = False, verbose: bool = False) -> str:
                     sys.stderr.write(" ".join(cmd) + "\n" + r.stdout + r.stderr)
                 if r.returncode != 0:
                     raise RuntimeError(f"nvcc failed for {cmd[-3]}")
-    if jobs or force or _newer(OUT_LIB, objs):
-        cmd = [nvcc, "-shared", "-o", OUT_LIB, *objs]
+    if jobs or force or _newer(out_lib, objs):
+        cmd = [nvcc, "-shared", "-o", out_lib, *objs]
         r = subprocess.run(cmd, capture_output=True, text=True)
         if r.returncode != 0:
             sys.stderr.write(r.stdout + r.stderr)
             raise RuntimeError("link failed")
-    return OUT_LIB
+    return out_lib
 
 
 if __name__ == "__main__":
     ap = argparse.ArgumentParser()
     ap.add_argument("--force", action="store_true")
     ap.add_argument("--verbose", action="store_true")
+    ap.add_argument("--trace", action="store_true", help="build the event-trace variant (libb200petals_trace.so)")
     a = ap.parse_args()
-    print(build(force=a.force, verbose=a.verbose))
+    print(build(force=a.force, verbose=a.verbose, trace=a.trace))

@@ -202,6 +202,17 @@ gemm_streamk_kernel(const GemmParams p) {
         } else {
             pdl_wait_prior_grid();  // activations come from the previous kernel
         }
+        if (LLIO) {
+            // wait (cheaply) until the input words exist: the whole vector when a norm needs its statistics anyway,
+            // else the k-range this CTA multiplies
+            int w0 = 0, w1 = p.K >> 1;
+            if (p.norm_mode == B200_NORM_NONE) {
+                const int kb_lo = (int)(q_begin % p.kbpt);
+                const long long span = q_end - q_begin;
+                if (kb_lo + span <= p.kbpt) { w0 = kb_lo * (kBK / 2); w1 = (kb_lo + (int)span) * (kBK / 2); }
+            }
+            ll_wait_range(p.ch.x, p.ch.ldx, min(BN, p.T), w0, w1, xtag, e, kEpiThreads, 1);
+        }
         if (e == 0) trace_event(1, 1, (p.n_tiles & 0xfff) | ((p.kbpt & 0xfff) << 12));
         if (p.gather_world > 1) tp_gather_prologue(p, e);   // x = residual + sum of the TP partials of the previous linear
 
@@ -703,6 +714,18 @@ static int pick_token_tile(int T) {
 using namespace b200;
 
 B200_DEFINE_TRACE_SETTER(b200_trace_set_gemm)
+
+extern "C" int b200_gemm_debug_occupancy(void) {
+    using Cfg = GemmCfg<16, 0>;
+    cudaFuncSetAttribute(gemm_streamk_kernel<16, 0, 0, 1, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg::kSmemBytes);
+    cudaFuncAttributes fa;
+    cudaFuncGetAttributes(&fa, gemm_streamk_kernel<16, 0, 0, 1, 0>);
+    int n = 0;
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, gemm_streamk_kernel<16, 0, 0, 1, 0>, kThreads, Cfg::kSmemBytes);
+    printf("gemm<16,0,0,1,0>: regs %d static %zu local %zu dyn %zu -> %d blocks/SM\n", fa.numRegs, fa.sharedSizeBytes,
+           fa.localSizeBytes, (size_t)Cfg::kSmemBytes, n);
+    return n;
+}
 
 extern "C" int32_t b200_gemm_token_tile(int32_t T, int32_t dual) {
     (void)dual;

@@ -42,9 +42,33 @@ __device__ __forceinline__ uint4 ll_load8(const uint2* w, uint32_t tag) {
         asm volatile("ld.relaxed.gpu.global.v4.u32 {%0, %1, %2, %3}, [%4];\n"
                      : "=r"(a2), "=r"(t2_), "=r"(a3), "=r"(t3_) : "l"(w + 2) : "memory");
         if (t0_ == tag && t1_ == tag && t2_ == tag && t3_ == tag) break;
+        __nanosleep(64);    // back off: thousands of threads polling flat out starve the producers and the weight stream
         ll_timeout(t0, "ll_load8", tag);
     }
     return make_uint4(a0, a1, a2, a3);
+}
+
+// Cheap wait for a range of words of T rows before the real loads: every 32nd word of [w_begin, w_end) is polled by one
+// thread with a back-off, then the `nthreads` callers meet at named barrier `bar`.  The loads that follow still check
+// every word's tag (a producer's stores may land in any order), but they normally succeed at once - without this,
+// every thread of every waiting CTA hammers the L2 with 32-byte polls while the producers and the weight stream need it.
+__device__ __forceinline__ void ll_wait_range(const uint2* x, int ld, int T, int w_begin, int w_end, uint32_t tag, int tid,
+                                              int nthreads, int bar) {
+    constexpr int kShift = 5;   // one sentinel per 32 words (64 elements)
+    const int n_sent = (w_end - w_begin + (1 << kShift) - 1) >> kShift;
+    for (int i = tid; i < n_sent * T; i += nthreads) {
+        const int t = i / n_sent, k = i - t * n_sent;
+        const uint2* w = x + (size_t)t * ld + w_begin + (k << kShift);
+        uint32_t a, tg;
+        long long t0 = 0;
+        for (;;) {
+            asm volatile("ld.relaxed.gpu.global.v2.u32 {%0, %1}, [%2];\n" : "=r"(a), "=r"(tg) : "l"(w) : "memory");
+            if (tg == tag) break;
+            __nanosleep(100);
+            ll_timeout(t0, "ll_wait_range", tag);
+        }
+    }
+    if (bar >= 0) named_bar_sync(bar, nthreads);
 }
 
 // One word = elements 2i, 2i+1.
@@ -54,6 +78,7 @@ __device__ __forceinline__ uint32_t ll_load2(const uint2* w, uint32_t tag) {
     for (;;) {
         asm volatile("ld.relaxed.gpu.global.v2.u32 {%0, %1}, [%2];\n" : "=r"(a), "=r"(t_) : "l"(w) : "memory");
         if (t_ == tag) break;
+        __nanosleep(64);
         ll_timeout(t0, "ll_load2", tag);
     }
     return a;

@@ -14,7 +14,11 @@ import sys
 
 import torch
 
-sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+# the stamps are compiled in only in the trace variant of the library (python csrc/build.py --trace)
+os.environ.setdefault("B200_LIB", os.path.join(
+    ROOT, "global_capstone_design_distributed-inference-of-llms-over-the-internet_b200", "ops", "libb200petals_trace.so"))
 
 
 def main():
@@ -42,7 +46,7 @@ def main():
     for _ in range(8):
         _, tok = span.decode([kv], ids=tok.clone())
     torch.cuda.synchronize()
-    cap = 8192
+    cap = 1 << 17
     buf = torch.zeros(1 + 2 * cap, dtype=torch.int64, device=dev)
     L = native.lib()
     L.b200_trace_set.argtypes = [ctypes.c_void_p, ctypes.c_int32]
@@ -70,7 +74,13 @@ def main():
     # never overlap each other); launches are then ordered by the time their first CTA entered
     per = {}
     for t, tag in ev:
-        k = (kname(tag), ["enter", "dep", "acc", "exit"][(tag >> 16) & 0xff], "L" if tag & 1 else "0")
+        which = tag & 3
+        ph = ["enter", "dep", "acc", "exit"][(tag >> 16) & 0xff]
+        if ph == "exit":                      # every CTA stamps its exit: keep them all for the true end of the launch
+            per.setdefault((kname(tag), "exit_all", "*"), []).append((t - t0) / 1e3)
+        if which == 2:
+            continue
+        k = (kname(tag), ph, "L" if which == 1 else "0")
         per.setdefault(k, []).append((t - t0) / 1e3)
     launches = []
     for kn in sorted({k[0] for k in per}):
@@ -88,6 +98,13 @@ def main():
                         d[ph + c] = cand[0] if cand else float("nan")
                     else:
                         d[ph + c] = lst[i] if i < len(lst) else float("nan")
+            # true end: the last exit of any CTA between this launch's entry and the next launch of the same type
+            ent = per[(kn, "enter", "0")][i]
+            nxt = per[(kn, "enter", "0")][i + 1] if i + 1 < cnt else 1e18
+            ex = [x for x in per.get((kn, "exit_all", "*"), []) if ent <= x < nxt]
+            d["exit_max"] = max(ex) if ex else float("nan")
+            d["exit_med"] = sorted(ex)[len(ex) // 2] if ex else float("nan")
+            d["n_exit"] = len(ex)
             launches.append(d)
     launches.sort(key=lambda d: d["enter0"])
     print(f"{n} events, {len(launches)} launches; step = {(ev[-1][0] - t0) / 1e3:.1f} us for {a.layers} layers + head")
@@ -95,13 +112,14 @@ def main():
     summary = []
     prev_end = 0.0
     for i, d in enumerate(launches):
-        end_ = max(x for x in (d["exit0"], d["exitL"]) if x == x) if (d["exit0"] == d["exit0"] or d["exitL"] == d["exitL"]) else float("nan")
+        end_ = d["exit_max"]
         dep = max(x for x in (d["dep0"], d["depL"]) if x == x) if (d["dep0"] == d["dep0"] or d["depL"] == d["depL"]) else float("nan")
         d["end"], d["dep"] = end_, dep
         summary.append(d)
         if 5 <= i < 16 or i >= len(launches) - 3:
             print(f"{i:>3} {d['kernel']:14} " + " ".join(f"{d[k]:8.1f}" for k in ("enter0", "dep0", "acc0", "exit0")) + " | "
-                  + " ".join(f"{d[k]:8.1f}" for k in ("enterL", "depL", "accL", "exitL")) + f" | {dep - prev_end:8.1f} {end_ - dep:8.1f}")
+                  + " ".join(f"{d[k]:8.1f}" for k in ("enterL", "depL", "accL", "exitL"))
+                  + f" | {dep - prev_end:8.1f} {end_ - dep:8.1f}  end(all {d['n_exit']} CTAs) {end_:8.1f} med {d['exit_med']:8.1f}")
         prev_end = end_
     # mean over layers per kernel type
     print("mean per kernel type (us): wait after the previous kernel's end until the dependency is visible, then dep -> end")
