@@ -150,17 +150,15 @@ __device__ __forceinline__ void attn_decode_body(const AttnDecodeParams& p, int 
         otag = ll_tag(seq, p.ch.out_op);
         row_ll = p.ch.x + (size_t)t * p.ch.ldx;
     }
-    if (chain) {   // cheap wait for this item's q heads, k and v (see ll_wait_range), then everybody loads
-        constexpr int kSent = D / 16;           // sentinels per head vector
-        for (int i = tid; i < (GROUP + 2) * kSent; i += kAttnThreads) {
-            const int hv = i / kSent, k = i - hv * kSent;
+    if (chain) {   // validate this item's q heads, k and v once (see ll_validate_range); the loads below are then plain
+        for (int hv = 0; hv < GROUP + 2; ++hv) {
             const int off = (hv < GROUP) ? q_off + hv * D : (hv == GROUP ? k_off : v_off);
-            ll_wait_range(row_ll + (off >> 1) + (k << 3), 0, 1, 0, 1, xtag, 0, 1, -1);
+            ll_validate_range(row_ll, 0, 1, off >> 1, (off + D) >> 1, xtag, tid, kAttnThreads, -1);
         }
         sync();
     }
     auto load8 = [&](int off) -> uint4 {       // 8 elements of this token's qkv row starting at element `off`
-        return chain ? ll_load8(row_ll + (off >> 1), xtag) : ld_cg_v4(row + off);
+        return chain ? ll_load8_valid(row_ll + (off >> 1)) : ld_cg_v4(row + off);
     };
     for (int item = tid; item < (GROUP + 1) * TPH; item += kAttnThreads) {
         const int h = item / TPH, c = (item % TPH) * 8;

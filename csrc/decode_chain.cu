@@ -20,10 +20,12 @@
 //
 // Same arithmetic, summation order and rounding as the per-launch kernels: bit-identical results
 // (tests/test_native_span_gpu.py).  Replaces the reference's eager per-op loop (src/llama_partition.py:233-297).
+#include <stdlib.h>
 #include <string.h>
 
 #include "attn_core.cuh"
 #include "gemm_core.cuh"
+#include "trace.cuh"
 
 namespace b200 {
 
@@ -70,7 +72,7 @@ __device__ __forceinline__ bool chain_unit(const ChainOp& op, int cta, int G, in
 }
 
 template <int D, int GROUP>
-__device__ __noinline__ void chain_attn(const AttnDecodeParams& A, uint8_t* smem, int e) {
+__device__ __forceinline__ void chain_attn(const AttnDecodeParams& A, uint8_t* smem, int e) {
     auto& sm = *reinterpret_cast<AttnDecodeSmem<D, GROUP>*>(smem);
     const int items = A.T * A.n_kv * A.splits;
     for (int item = blockIdx.x; item < items; item += gridDim.x) {   // increasing order: see the deadlock note above
@@ -84,7 +86,7 @@ __device__ __noinline__ void chain_attn(const AttnDecodeParams& A, uint8_t* smem
 }
 
 template <int DUAL>
-__device__ __noinline__ void chain_gemm_unit_epilogue(const GemmParams& p, int parts, int cta, int u, bool split,
+__device__ __forceinline__ void chain_gemm_unit_epilogue(const GemmParams& p, int parts, int cta, int u, bool split,
                                                          const float (&vg)[16], const float (&vu)[16],
                                                          const float* tok_scale, int row, int lane, int e,
                                                          uint32_t rtag, uint32_t otag) {
@@ -153,8 +155,11 @@ __device__ __noinline__ void chain_gemm_unit_epilogue(const GemmParams& p, int p
 #ifndef B200_CHAIN_BOUND_THREADS
 #define B200_CHAIN_BOUND_THREADS 192   /* register budget of the chain kernel: 65536 / (2 x this) per thread */
 #endif
+// One instantiation per attention shape (head_dim, GQA group): every op of a plan has the same one, and a single
+// inlined attention body keeps the kernel's live state in registers (six bodies behind calls put it in local memory).
+template <int D, int GROUP>
 __global__ void __launch_bounds__(B200_CHAIN_BOUND_THREADS, 2)
-decode_chain_kernel(const ChainOp* __restrict__ ops, int n_ops) {
+decode_chain_kernel(const ChainOp* __restrict__ ops, int n_ops, int debug) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     uint8_t* smem_a = smem;
@@ -198,6 +203,7 @@ decode_chain_kernel(const ChainOp* __restrict__ ops, int n_ops) {
             const int block_a = op.dual ? 2 * kABytes : kABytes;
             const int kps = op.dual ? 1 : 2;
             int u, kb0, kb1;
+            if (lane == 0) trace_event(3, 4, oi);
             for (int j = 0; chain_unit(op, cta, G, j, u, kb0, kb1); ++j) {
                 const uint8_t* tile_base = op.g.w + (size_t)u * op.g.kbpt * block_a;
                 for (int kb = kb0; kb < kb1;) {
@@ -205,14 +211,18 @@ decode_chain_kernel(const ChainOp* __restrict__ ops, int n_ops) {
                     mbar_wait(&a_empty[s], ph ^ 1);
                     const uint32_t bytes = (uint32_t)n * block_a;
                     if (elect_one()) {
-                        mbar_arrive_expect_tx(&a_full[s], bytes);
-                        bulk_g2s_hint(smem_a + (size_t)s * kCStageA, tile_base + (size_t)kb * block_a, bytes, &a_full[s], policy);
+                        if (debug & 4) mbar_arrive(&a_full[s]);       // experiment: no weight traffic at all
+                        else {
+                            mbar_arrive_expect_tx(&a_full[s], bytes);
+                            bulk_g2s_hint(smem_a + (size_t)s * kCStageA, tile_base + (size_t)kb * block_a, bytes, &a_full[s], policy);
+                        }
                     }
                     __syncwarp();
                     if (++s == kCSA) { s = 0; ph ^= 1; }
                     kb += n;
                 }
             }
+            if (lane == 0) trace_event(3, 5, oi);
         }
     } else if (warp == 1) {
         // ------------------------------------------------------------ MMA issuer (whole warp, elected lane issues)
@@ -229,6 +239,7 @@ decode_chain_kernel(const ChainOp* __restrict__ ops, int n_ops) {
             int u, kb0, kb1;
             for (int j = 0; chain_unit(op, cta, G, j, u, kb0, kb1); ++j) {
                 const int nk = kb1 - kb0;
+                if (lane == 0) trace_event(3, 6, oi);
                 mbar_wait(acc_empty, php ^ 1);
                 tc_fence_after();
                 uint32_t acc = 0;
@@ -240,7 +251,7 @@ decode_chain_kernel(const ChainOp* __restrict__ ops, int n_ops) {
                         if (bofs == 0) mbar_wait(&b_full[sb], phb);
                         tc_fence_after();
                         const uint64_t bdesc = umma_desc_kmajor_sw128(b_base + sb * kCStageB + bofs * kCSubB, 1024);
-                        if (elect_one()) {
+                        if (!(debug & 2) && elect_one()) {
                             for (int a = 0; a < aper; ++a) {
                                 const uint64_t adesc =
                                     umma_desc_kmajor_sw128(a_base + sa * kCStageA + jj * block_a + a * kABytes, 1024);
@@ -267,6 +278,7 @@ decode_chain_kernel(const ChainOp* __restrict__ ops, int n_ops) {
                 }
                 if (elect_one()) umma_commit(acc_full);
                 __syncwarp();
+                if (lane == 0) trace_event(3, 7, oi);
                 php ^= 1;
             }
         }
@@ -285,15 +297,10 @@ decode_chain_kernel(const ChainOp* __restrict__ ops, int n_ops) {
         for (int oi = 0; oi < n_ops; ++oi) {
             const ChainOp& op = ops[oi];
             if (oi == 0) seq = ll_read_seq(op.type == 0 ? op.g.ch.seq : op.a.ch.seq);
+            if (e == 0) trace_event(3, 0, oi);
             if (op.type == 1) {
-                const AttnDecodeParams& A = op.a;
-                const int D = op.attn_d, GR = op.attn_group;
-                if (D == 128 && GR == 1) chain_attn<128, 1>(A, smem_b, e);
-                else if (D == 128 && GR == 2) chain_attn<128, 2>(A, smem_b, e);
-                else if (D == 128 && GR == 4) chain_attn<128, 4>(A, smem_b, e);
-                else if (D == 64 && GR == 1) chain_attn<64, 1>(A, smem_b, e);
-                else if (D == 64 && GR == 2) chain_attn<64, 2>(A, smem_b, e);
-                else if (D == 64 && GR == 4) chain_attn<64, 4>(A, smem_b, e);
+                chain_attn<D, GROUP>(op.a, smem_b, e);
+                if (e == 0) trace_event(3, 3, oi);
                 continue;
             }
             const GemmParams& p = op.g;
@@ -301,14 +308,23 @@ decode_chain_kernel(const ChainOp* __restrict__ ops, int n_ops) {
             const int T = min(kCBN, p.T);
             bool stats_ready = p.norm_mode == B200_NORM_NONE;
             int u, kb0, kb1;
+            bool validated = false;
             for (int j = 0; chain_unit(op, cta, G, j, u, kb0, kb1); ++j) {
+                if (!validated) {
+                    // wait until the input words exist - the whole vector when a norm needs its statistics (or this CTA
+                    // works on whole tiles), else the k-range of this CTA's unit; afterwards plain pipelined loads
+                    int w0 = 0, w1 = p.K >> 1;
+                    if (p.norm_mode == B200_NORM_NONE && op.parts >= 2) { w0 = kb0 * (kBK / 2); w1 = kb1 * (kBK / 2); }
+                    ll_validate_range(p.ch.x, p.ch.ldx, T, w0, w1, xtag, e, kEpiThreads, 1);
+                    validated = true;
+                }
                 if (p.norm_mode == B200_NORM_LAYER && !stats_ready) {
                     // LayerNorm needs its statistics before the staging (RMSNorm defers 1/rms to the epilogue)
                     const int pw = warp - 2;
                     for (int tt = pw; tt < T; tt += 4) {
                         float s1 = 0.f, s2 = 0.f;
                         for (int c = lane; c < p.K / 8; c += 32) {
-                            const uint4 v = ll_load8(p.ch.x + (size_t)tt * p.ch.ldx + c * 4, xtag);
+                            const uint4 v = ll_load8_valid(p.ch.x + (size_t)tt * p.ch.ldx + c * 4);
                             const uint32_t w4[4] = {v.x, v.y, v.z, v.w};
 #pragma unroll
                             for (int i = 0; i < 4; ++i) {
@@ -338,9 +354,9 @@ decode_chain_kernel(const ChainOp* __restrict__ ops, int n_ops) {
                         for (int g = 0; g < kCGroup; ++g) {
                             if (kb + g < kb1) {
                                 const int kcol = (kb + g) * kBK + ch * 8;
-                                v[g] = (t < p.T) ? ll_load8(p.ch.x + (size_t)t * p.ch.ldx + (kcol >> 1), xtag)
-                                                 : make_uint4(0, 0, 0, 0);
-                                if (p.norm_mode != B200_NORM_NONE) {
+                                v[g] = (t < p.T && !(debug & 1)) ? ll_load8_valid(p.ch.x + (size_t)t * p.ch.ldx + (kcol >> 1))
+                                                                 : make_uint4(0, 0, 0, 0);
+                                if (p.norm_mode != B200_NORM_NONE && !(debug & 1)) {
                                     gw[g] = ld_nc_v4(p.norm_w + kcol);
                                     gb[g] = p.norm_b ? ld_nc_v4(p.norm_b + kcol) : make_uint4(0, 0, 0, 0);
                                 }
@@ -397,8 +413,10 @@ decode_chain_kernel(const ChainOp* __restrict__ ops, int n_ops) {
                 }
                 const float* tok_scale = (p.norm_mode == B200_NORM_RMS) ? stat_rstd : nullptr;
                 // ---- drain the accumulators of this unit
+                if (e == 0) trace_event(3, 1, oi);
                 mbar_wait(acc_full, part & 1);
                 tc_fence_after();
+                if (e == 0) trace_event(3, 2, oi);
                 float vg[16], vu[16];
 #pragma unroll
                 for (int jj = 0; jj < 16; ++jj) { vg[jj] = 0.f; vu[jj] = 0.f; }
@@ -425,6 +443,7 @@ decode_chain_kernel(const ChainOp* __restrict__ ops, int n_ops) {
                 if (op.dual) chain_gemm_unit_epilogue<1>(p, op.parts, cta, u, split, vg, vu, tok_scale, row, lane, e, rtag, otag);
                 else chain_gemm_unit_epilogue<0>(p, op.parts, cta, u, split, vg, vu, tok_scale, row, lane, e, rtag, otag);
             }
+            if (e == 0) trace_event(3, 3, oi);
         }
     }
 
@@ -436,6 +455,8 @@ decode_chain_kernel(const ChainOp* __restrict__ ops, int n_ops) {
 }  // namespace b200
 
 using namespace b200;
+
+B200_DEFINE_TRACE_SETTER(b200_trace_set_chain)
 
 extern "C" int64_t b200_decode_chain_plan_bytes(int32_t n_ops) { return (int64_t)n_ops * (int64_t)sizeof(ChainOp); }
 extern "C" int32_t b200_decode_chain_max_attn_group(void) { return kCMaxAttnGroup; }
@@ -543,40 +564,37 @@ extern "C" int b200_decode_chain_build(const b200_chain_op* ops, int32_t n_ops, 
     return B200_OK;
 }
 
-extern "C" int b200_decode_chain_debug(void) {
-    cudaFuncAttributes fa;
-    B200_CUDA_CHECK(cudaFuncSetAttribute(decode_chain_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kCSmemBytes));
-    B200_CUDA_CHECK(cudaFuncGetAttributes(&fa, decode_chain_kernel));
-    printf("chain kernel: regs %d static smem %zu local %zu maxdyn %d maxthreads %d\n", fa.numRegs, fa.sharedSizeBytes,
-           fa.localSizeBytes, fa.maxDynamicSharedSizeBytes, fa.maxThreadsPerBlock);
-    for (size_t dyn : {kCSmemBytes, (size_t)100000, (size_t)65536, (size_t)32768}) {
-        int n = 0;
-        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, decode_chain_kernel, kThreads, dyn);
-        printf("  dyn %zu -> %d blocks/SM\n", dyn, n);
-    }
-    cudaDeviceProp pr;
-    cudaGetDeviceProperties(&pr, 0);
-    printf("device: smem/SM %zu optin/block %zu reserved %zu regs/SM %d\n", pr.sharedMemPerMultiprocessor,
-           pr.sharedMemPerBlockOptin, pr.reservedSharedMemPerBlock, pr.regsPerMultiprocessor);
-    return 0;
-}
-
-extern "C" int b200_decode_chain_launch(const void* plan_device, int32_t n_ops, int32_t grid, int32_t pdl, void* stream_) {
-    if (!plan_device || n_ops <= 0) return fail(B200_EINVAL, "b200_decode_chain_launch: null plan");
-    const int max_grid = 2 * sm_count_cached();
-    if (grid <= 0 || grid > max_grid) return fail(B200_EINVAL, "b200_decode_chain_launch: grid %d outside 1..%d", grid, max_grid);
+template <int D, int GROUP>
+static int launch_chain(const void* plan_device, int n_ops, int grid, bool pdl, int dbg, cudaStream_t stream) {
     static thread_local int configured_dev = -1;
     int dev = 0;
     B200_CUDA_CHECK(cudaGetDevice(&dev));
     if (configured_dev != dev) {
-        B200_CUDA_CHECK(cudaFuncSetAttribute(decode_chain_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kCSmemBytes));
-        B200_CUDA_CHECK(cudaFuncSetAttribute(decode_chain_kernel, cudaFuncAttributePreferredSharedMemoryCarveout,
-                                             (int)cudaSharedmemCarveoutMaxShared));
         // (cudaOccupancyMaxActiveBlocksPerMultiprocessor answers 1 for every tcgen05 kernel of this library, whatever its
         // registers and shared memory; the hardware runs two of these CTAs per SM - scripts/exp_residency.py stamps SM ids.)
+        B200_CUDA_CHECK(cudaFuncSetAttribute(decode_chain_kernel<D, GROUP>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             (int)kCSmemBytes));
+        B200_CUDA_CHECK(cudaFuncSetAttribute(decode_chain_kernel<D, GROUP>, cudaFuncAttributePreferredSharedMemoryCarveout,
+                                             (int)cudaSharedmemCarveoutMaxShared));
         configured_dev = dev;
     }
-    B200_CUDA_CHECK(launch(decode_chain_kernel, dim3(grid), dim3(kThreads), kCSmemBytes, static_cast<cudaStream_t>(stream_),
-                           pdl != 0, static_cast<const ChainOp*>(plan_device), (int)n_ops));
+    B200_CUDA_CHECK(launch(decode_chain_kernel<D, GROUP>, dim3(grid), dim3(kThreads), kCSmemBytes, stream, pdl,
+                           static_cast<const ChainOp*>(plan_device), n_ops, dbg));
     return B200_OK;
+}
+
+// head_dim / gqa_group: the attention shape of the plan's ops (all ops of a plan share it).
+extern "C" int b200_decode_chain_launch(const void* plan_device, int32_t n_ops, int32_t grid, int32_t head_dim,
+                                        int32_t gqa_group, int32_t pdl, void* stream_) {
+    if (!plan_device || n_ops <= 0) return fail(B200_EINVAL, "b200_decode_chain_launch: null plan");
+    const int max_grid = 2 * sm_count_cached();
+    if (grid <= 0 || grid > max_grid) return fail(B200_EINVAL, "b200_decode_chain_launch: grid %d outside 1..%d", grid, max_grid);
+    static const int dbg = [] { const char* e = getenv("B200_CHAIN_DEBUG"); return e ? atoi(e) : 0; }();
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+#define B200_CHAIN_CASE(D_, G_) \
+    if (head_dim == D_ && gqa_group == G_) return launch_chain<D_, G_>(plan_device, n_ops, grid, pdl != 0, dbg, stream);
+    B200_CHAIN_CASE(128, 1) B200_CHAIN_CASE(128, 2) B200_CHAIN_CASE(128, 4)
+    B200_CHAIN_CASE(64, 1) B200_CHAIN_CASE(64, 2) B200_CHAIN_CASE(64, 4)
+#undef B200_CHAIN_CASE
+    return fail(B200_ELIMIT, "b200_decode_chain_launch: unsupported attention shape head_dim=%d group=%d", head_dim, gqa_group);
 }

@@ -203,15 +203,15 @@ gemm_streamk_kernel(const GemmParams p) {
             pdl_wait_prior_grid();  // activations come from the previous kernel
         }
         if (LLIO) {
-            // wait (cheaply) until the input words exist: the whole vector when a norm needs its statistics anyway,
-            // else the k-range this CTA multiplies
+            // wait until the input words exist - the whole vector when a norm needs its statistics anyway, else the
+            // k-range this CTA multiplies; afterwards they are read with plain pipelined loads
             int w0 = 0, w1 = p.K >> 1;
             if (p.norm_mode == B200_NORM_NONE) {
                 const int kb_lo = (int)(q_begin % p.kbpt);
                 const long long span = q_end - q_begin;
                 if (kb_lo + span <= p.kbpt) { w0 = kb_lo * (kBK / 2); w1 = (kb_lo + (int)span) * (kBK / 2); }
             }
-            ll_wait_range(p.ch.x, p.ch.ldx, min(BN, p.T), w0, w1, xtag, e, kEpiThreads, 1);
+            ll_validate_range(p.ch.x, p.ch.ldx, min(BN, p.T), w0, w1, xtag, e, kEpiThreads, 1);
         }
         if (e == 0) trace_event(1, 1, (p.n_tiles & 0xfff) | ((p.kbpt & 0xfff) << 12));
         if (p.gather_world > 1) tp_gather_prologue(p, e);   // x = residual + sum of the TP partials of the previous linear
@@ -225,7 +225,7 @@ gemm_streamk_kernel(const GemmParams p) {
                 if (t < p.T) {
                     const uint16_t* xr = p.x + (size_t)t * p.ldx;
                     for (int c = lane; c < p.K / 8; c += 32) {
-                        const uint4 v = LLIO ? ll_load8(p.ch.x + (size_t)t * p.ch.ldx + c * 4, xtag) : ld_cg_v4(xr + c * 8);
+                        const uint4 v = LLIO ? ll_load8_valid(p.ch.x + (size_t)t * p.ch.ldx + c * 4) : ld_cg_v4(xr + c * 8);
                         const uint32_t w4[4] = {v.x, v.y, v.z, v.w};
 #pragma unroll
                         for (int i = 0; i < 4; ++i) {
@@ -325,7 +325,7 @@ gemm_streamk_kernel(const GemmParams p) {
                             for (int i = 0; i < NI; ++i) {
                                 const int t = t_tile * BN + r0 + 16 * i;
                                 if (t >= p.T) v[g][i] = make_uint4(0, 0, 0, 0);
-                                else if (LLIO) v[g][i] = ll_load8(p.ch.x + (size_t)t * p.ch.ldx + (kcol >> 1), xtag);
+                                else if (LLIO) v[g][i] = ll_load8_valid(p.ch.x + (size_t)t * p.ch.ldx + (kcol >> 1));
                                 else v[g][i] = ld_cg_v4(p.x + (size_t)t * p.ldx + kcol);
                             }
                             if (p.norm_mode != B200_NORM_NONE) {

@@ -211,9 +211,9 @@ __device__ __forceinline__ void rms_stats_128(const GemmParams& p, int T, int e,
         const uint16_t* xb = xa + (two ? p.ldx : 0);
         for (int c = e; c < p.K / 8; c += 128) {
             uint4 va, vb = make_uint4(0, 0, 0, 0);
-            if (LLIO) {
-                va = ll_load8(p.ch.x + (size_t)t0 * p.ch.ldx + c * 4, xtag);
-                if (two) vb = ll_load8(p.ch.x + (size_t)(t0 + 1) * p.ch.ldx + c * 4, xtag);
+            if (LLIO) {   // the caller has validated the whole vector (ll_validate_range)
+                va = ll_load8_valid(p.ch.x + (size_t)t0 * p.ch.ldx + c * 4);
+                if (two) vb = ll_load8_valid(p.ch.x + (size_t)(t0 + 1) * p.ch.ldx + c * 4);
             } else {
                 va = ld_cg_v4(xa + c * 8);
                 if (two) vb = ld_cg_v4(xb + c * 8);

@@ -48,27 +48,49 @@ __device__ __forceinline__ uint4 ll_load8(const uint2* w, uint32_t tag) {
     return make_uint4(a0, a1, a2, a3);
 }
 
-// Cheap wait for a range of words of T rows before the real loads: every 32nd word of [w_begin, w_end) is polled by one
-// thread with a back-off, then the `nthreads` callers meet at named barrier `bar`.  The loads that follow still check
-// every word's tag (a producer's stores may land in any order), but they normally succeed at once - without this,
-// every thread of every waiting CTA hammers the L2 with 32-byte polls while the producers and the weight stream need it.
-__device__ __forceinline__ void ll_wait_range(const uint2* x, int ld, int T, int w_begin, int w_end, uint32_t tag, int tid,
-                                              int nthreads, int bar) {
-    constexpr int kShift = 5;   // one sentinel per 32 words (64 elements)
-    const int n_sent = (w_end - w_begin + (1 << kShift) - 1) >> kShift;
-    for (int i = tid; i < n_sent * T; i += nthreads) {
-        const int t = i / n_sent, k = i - t * n_sent;
-        const uint2* w = x + (size_t)t * ld + w_begin + (k << kShift);
-        uint32_t a, tg;
+// Validation of a range of words before they are read WITHOUT checks: every word of [w_begin, w_end) (both multiples
+// of 2) of T rows is polled by exactly one of the `nthreads` callers - four 16-byte loads in flight per round, a back-off
+// between rounds - until it carries `tag`; then the callers meet at named barrier `bar` (bar < 0: the caller
+// synchronises).  A producer writes each word once per step, so a word that carries the tag is final and the loads that
+// follow can be plain, pipelined loads (ll_load8_valid) instead of one blocking poll per load - which would put an L2
+// round trip on the critical path of every k-block - and the L2 is not hammered by thousands of spinning threads.
+__device__ __forceinline__ void ll_validate_range(const uint2* x, int ld, int T, int w_begin, int w_end, uint32_t tag,
+                                                  int tid, int nthreads, int bar) {
+    const int pairs = (w_end - w_begin) >> 1;          // 16-byte cells per row
+    const int total = pairs * T;
+    for (int i0 = tid; i0 < total; i0 += 4 * nthreads) {
         long long t0 = 0;
         for (;;) {
-            asm volatile("ld.relaxed.gpu.global.v2.u32 {%0, %1}, [%2];\n" : "=r"(a), "=r"(tg) : "l"(w) : "memory");
-            if (tg == tag) break;
+            uint32_t tg[8];
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const int i = i0 + k * nthreads;
+                tg[2 * k] = tag; tg[2 * k + 1] = tag;
+                if (i < total) {
+                    const int t = i / pairs, c = i - t * pairs;
+                    uint32_t a, b;
+                    asm volatile("ld.relaxed.gpu.global.v4.u32 {%0, %1, %2, %3}, [%4];\n"
+                                 : "=r"(a), "=r"(tg[2 * k]), "=r"(b), "=r"(tg[2 * k + 1])
+                                 : "l"(x + (size_t)t * ld + w_begin + 2 * c) : "memory");
+                }
+            }
+            bool ok = true;
+#pragma unroll
+            for (int k = 0; k < 8; ++k) ok = ok && tg[k] == tag;
+            if (ok) break;
             __nanosleep(100);
-            ll_timeout(t0, "ll_wait_range", tag);
+            ll_timeout(t0, "ll_validate_range", tag);
         }
     }
     if (bar >= 0) named_bar_sync(bar, nthreads);
+}
+
+// 8 consecutive elements of a VALIDATED range: two plain 16-byte loads, no poll.
+__device__ __forceinline__ uint4 ll_load8_valid(const uint2* w) {
+    uint32_t a0, t0_, a1, t1_, a2, t2_, a3, t3_;
+    asm volatile("ld.relaxed.gpu.global.v4.u32 {%0, %1, %2, %3}, [%4];\n" : "=r"(a0), "=r"(t0_), "=r"(a1), "=r"(t1_) : "l"(w));
+    asm volatile("ld.relaxed.gpu.global.v4.u32 {%0, %1, %2, %3}, [%4];\n" : "=r"(a2), "=r"(t2_), "=r"(a3), "=r"(t3_) : "l"(w + 2));
+    return make_uint4(a0, a1, a2, a3);
 }
 
 // One word = elements 2i, 2i+1.

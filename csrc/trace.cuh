@@ -19,7 +19,8 @@ __device__ __forceinline__ void trace_event(int kernel_id, int phase, int aux = 
 #endif
     unsigned long long* b = t_trace_buf;
     if (b == nullptr) return;
-    if (phase != 3 && phase != 0 && blockIdx.x != 0 && blockIdx.x != gridDim.x - 1) return;   // entries and exits: every CTA
+    const bool edge = blockIdx.x == 0 || blockIdx.x == gridDim.x - 1;
+    if (!edge && (kernel_id == 3 || (phase != 3 && phase != 0))) return;   // per-launch kernels: entries and exits of every CTA
     unsigned long long t;
     asm volatile("mov.u64 %0, %%globaltimer;\n" : "=l"(t));
     const unsigned long long slot = atomicAdd(b, 1ULL);

@@ -55,7 +55,7 @@ PROTOTYPES = [
     ("b200_decode_chain_plan_bytes", [i32], i64),
     ("b200_decode_chain_max_attn_group", [], i32),
     ("b200_decode_chain_build", [vp, i32, i32, vp], C.c_int),
-    ("b200_decode_chain_launch", [vp, i32, i32, i32, vp], C.c_int),
+    ("b200_decode_chain_launch", [vp, i32, i32, i32, i32, i32, vp], C.c_int),
     ("b200_ll_publish", [vp, i32, vp, i32, i32, i32, vp, i32, i32, vp], C.c_int),
     ("b200_trace_set", [vp, i32], C.c_int),
     ("b200_argmax_partial", [vp, i32, i32, i32, vp, vp, vp, vp, i32, i32, vp, vp, i32, vp], C.c_int),

@@ -41,8 +41,13 @@ MAX_DECODE_BATCH = 32
 
 RSTD_KERNEL_MIN_TOKENS = int(os.environ.get("B200_RSTD_KERNEL_MIN_TOKENS", "8"))
 # Decode steps of up to this many tokens run as a flag chain (b200_ll_chain): the kernels of the step hand their
-# activations over as self-validating words instead of waiting for each other's grids.  0 switches it off.
-CHAIN_MAX_TOKENS = int(os.environ.get("B200_LL_CHAIN_MAX_TOKENS", "4"))
+# activations over as self-validating words instead of waiting for each other's grids.  Bit-identical to the
+# grid-ordered step, but measured SLOWER on Llama-2-7B batch-1 decode (1xB200): 352 tok/s as one launch per op
+# (B200_CHAIN_KERNEL=0), 259 tok/s as one persistent launch (csrc/decode_chain.cu), against 361 tok/s grid-ordered -
+# the per-launch timeline (profiles/decode_timeline_r2_*.txt) shows that what a launch boundary costs is not the
+# grid-completion signal but the start-up of the next kernel's CTAs, which cannot be resident before the previous
+# kernel's CTAs leave.  So the chain is OFF by default (0); set B200_LL_CHAIN_MAX_TOKENS=4 to experiment.
+CHAIN_MAX_TOKENS = int(os.environ.get("B200_LL_CHAIN_MAX_TOKENS", "0"))
 # 1: the chained blocks of a step run as ONE persistent launch (csrc/decode_chain.cu); 0: one launch per op, chained
 CHAIN_KERNEL = os.environ.get("B200_CHAIN_KERNEL", "1") != "0"
 
@@ -337,7 +342,8 @@ class NativeSpan:
             plans[key] = plan
         dev_plan, n, grid, h_op = plan
         E.ll_publish(h, h_ll, self.step_seq, 1, pdl=True)      # head of the chain: waits for whatever produced h
-        native.check(L.b200_decode_chain_launch(dev_plan.data_ptr(), n, grid, 1, native.current_stream_ptr()),
+        native.check(L.b200_decode_chain_launch(dev_plan.data_ptr(), n, grid, c.head_dim, c.n_heads // c.n_kv_heads, 1,
+                                                native.current_stream_ptr()),
                      "b200_decode_chain_launch")
         self._count(2)
         self._head_done = key[2]

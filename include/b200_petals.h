@@ -237,7 +237,8 @@ int b200_attn_prefill(const void* q, void* out, const void* kcache, const void* 
  * .chain filled).  Replaces the reference's eager per-op block loop (src/llama_partition.py:233-297).
  *   b200_decode_chain_build   validates the ops and writes the device plan (synchronous copy; plan_device holds
  *                             b200_decode_chain_plan_bytes(n_ops) bytes); grid = the grid of the later launches.
- *   b200_decode_chain_launch  grid <= 2 x SM count; every CTA must be co-resident (nothing else may fill the GPU). */
+ *   b200_decode_chain_launch  grid <= 2 x SM count; every CTA must be co-resident (nothing else may fill the GPU);
+ *                             head_dim / gqa_group = the attention shape of the plan's ops. */
 typedef struct b200_chain_op {
     int32_t type; /* 0 = GEMM, 1 = attention */
     int32_t reserved;
@@ -247,7 +248,8 @@ typedef struct b200_chain_op {
 int64_t b200_decode_chain_plan_bytes(int32_t n_ops);
 int32_t b200_decode_chain_max_attn_group(void);
 int b200_decode_chain_build(const b200_chain_op* ops, int32_t n_ops, int32_t grid, void* plan_device);
-int b200_decode_chain_launch(const void* plan_device, int32_t n_ops, int32_t grid, int32_t pdl, void* stream);
+int b200_decode_chain_launch(const void* plan_device, int32_t n_ops, int32_t grid, int32_t head_dim, int32_t gqa_group,
+                             int32_t pdl, void* stream);
 
 /* Same contract on the tensor cores: 128-query x 128-key tiles, S = QK^T and O = PV by tcgen05.mma
  * (V consumed in place as an MN-major operand), online softmax between them, accumulators in TMEM. */

@@ -58,6 +58,22 @@ def main():
     n = min(h[0], cap)
     ev = sorted((h[1 + 2 * i], h[2 + 2 * i]) for i in range(n))
     t0 = ev[0][0]
+    chain_ev = [(t, tag) for t, tag in ev if (tag >> 56) == 3]
+    if chain_ev:
+        # persistent chain kernel: per op and CTA (first / last): begin, staged (inputs consumed), accumulator ready, end
+        rows = {}
+        for t, tag in chain_ev:
+            oi, ph, which = (tag >> 32) & 0xffffff, (tag >> 16) & 0xff, tag & 3
+            rows.setdefault((oi, which), {})[ph] = (t - t0) / 1e3
+        print(f"persistent chain kernel: {len(chain_ev)} events; step = {(ev[-1][0] - t0) / 1e3:.1f} us")
+        print(f"{'op':>4} | CTA 0 workers: {'begin':>8} {'staged':>8} {'acc':>8} {'end':>8} | loader {'begin':>8} {'issued':>8} | mma {'begin':>8} {'commit':>8}")
+        nops = max(k[0] for k in rows) + 1
+        for oi in list(range(min(nops, 14))) + list(range(max(14, nops - 3), nops)):
+            a, b = rows.get((oi, 0), {}), rows.get((oi, 1), {})
+            f = lambda d, k: f"{d[k]:8.1f}" if k in d else "       -"   # noqa: E731
+            print(f"{oi:>4} |                " + " ".join(f(a, k) for k in range(4)) + " |        " + " ".join(f(a, k) for k in (4, 5))
+                  + " |     " + " ".join(f(a, k) for k in (6, 7)))
+        ev = [(t, tag) for t, tag in ev if (tag >> 56) != 3]
     names = {}
 
     def kname(tag):

@@ -100,6 +100,7 @@ def test_flag_chained_decode_is_bit_identical(name, graphs, persistent, monkeypa
     from petals_b200.runtime import native_span
 
     monkeypatch.setattr(native_span, "CHAIN_KERNEL", persistent)
+    monkeypatch.setattr(native_span, "CHAIN_MAX_TOKENS", 4)      # off by default (measured slower); tested all the same
     cfg, _, chain, _, m1 = _build(name, torch.bfloat16, use_graphs=graphs)
     _, _, plain, _, m2 = _build(name, torch.bfloat16, use_graphs=graphs)
     assert chain.chain_tokens >= 4, "the tiny presets must qualify for the chain"
