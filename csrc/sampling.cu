@@ -22,6 +22,34 @@ struct SampleRow {
     int recent[kMaxRecent];
 };
 
+// Device-resident generator state of one session (b200_sample_stateful): the uniform number of a draw is
+// Philox4x32-10(key = seed, counter = draws made so far), so a session's random stream depends on nothing but its
+// seed - not on the batch it is sampled in, the GPU it runs on or how many pipeline stages there are.
+struct SampleState {
+    unsigned long long seed;
+    unsigned long long offset;
+};
+
+__device__ __forceinline__ void philox_round(uint32_t (&c)[4], uint32_t k0, uint32_t k1) {
+    const unsigned long long p0 = (unsigned long long)0xD2511F53u * c[0];
+    const unsigned long long p1 = (unsigned long long)0xCD9E8D57u * c[2];
+    const uint32_t n0 = (uint32_t)(p1 >> 32) ^ c[1] ^ k0;
+    const uint32_t n2 = (uint32_t)(p0 >> 32) ^ c[3] ^ k1;
+    c[0] = n0; c[1] = (uint32_t)p1; c[2] = n2; c[3] = (uint32_t)p0;
+}
+// First word of Philox4x32-10 as a float in [0, 1) with 24 random bits.
+__device__ __forceinline__ float philox_uniform(unsigned long long seed, unsigned long long offset) {
+    uint32_t c[4] = {(uint32_t)offset, (uint32_t)(offset >> 32), 0u, 0u};
+    uint32_t k0 = (uint32_t)seed, k1 = (uint32_t)(seed >> 32);
+#pragma unroll
+    for (int r = 0; r < 10; ++r) {
+        philox_round(c, k0, k1);
+        k0 += 0x9E3779B9u;
+        k1 += 0xBB67AE85u;
+    }
+    return (float)(c[0] >> 8) * (1.0f / 16777216.0f);
+}
+
 __device__ __forceinline__ float block_reduce_max(float v, float* red) {
     v = warp_max(v);
     if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = v;
@@ -51,10 +79,15 @@ __device__ __forceinline__ double block_reduce_sum(double v, double* red) {
     return r;
 }
 
+// Stateless: rows[t] + uniforms[t].  Stateful (states != null): row / state of CTA t = rows / states[row_index ?
+// row_index[t] : t]; the uniform comes from the session's Philox stream, and after the draw the CTA appends the token to
+// the row's recent-token window and advances the stream - nothing of a session's sampling state lives on the host.
 __global__ void __launch_bounds__(kSampThreads) sample_kernel(const float* __restrict__ logits, int ld, int V,
-                                                             const SampleRow* __restrict__ rows,
+                                                             SampleRow* __restrict__ rows_all,
                                                              const float* __restrict__ uniforms, float* __restrict__ probs,
-                                                             long long* __restrict__ out_ids) {
+                                                             long long* __restrict__ out_ids,
+                                                             SampleState* __restrict__ states,
+                                                             const int* __restrict__ row_index) {
     __shared__ float s_redf[32];
     __shared__ double s_redd[32];
     __shared__ unsigned long long s_hist[256];
@@ -69,7 +102,9 @@ __global__ void __launch_bounds__(kSampThreads) sample_kernel(const float* __res
     pdl_wait_prior_grid();
     pdl_launch_dependents();
     const int t = blockIdx.x, tid = threadIdx.x;
-    const SampleRow& R = rows[t];
+    const int ri = (states && row_index) ? row_index[t] : t;
+    SampleRow& R = rows_all[ri];
+    const float u01 = states ? philox_uniform(states[ri].seed, states[ri].offset) : uniforms[t];
     const float* x = logits + (size_t)t * ld;
     float* p = probs + (size_t)t * V;
 
@@ -221,7 +256,7 @@ __global__ void __launch_bounds__(kSampThreads) sample_kernel(const float* __res
     }
     __syncthreads();
     const double total = s_redd[0];
-    const double want = (double)uniforms[t] * total;
+    const double want = (double)u01 * total;
     const double start = s_seg[tid];
     if (want >= start && (want < start + seg || (tid == kSampThreads - 1))) {
         double run = start;
@@ -241,7 +276,18 @@ __global__ void __launch_bounds__(kSampThreads) sample_kernel(const float* __res
         if (pick < 0) {   // numerical corner (want == total): take the last kept element
             for (int i = V - 1; i >= 0; --i) if (p[i] > 0.f) { pick = i; break; }
         }
-        out_ids[t] = pick < 0 ? 0 : pick;
+        pick = pick < 0 ? 0 : pick;
+        out_ids[t] = pick;
+        if (states) {     // the session's window of recent tokens and its random stream move on
+            int n = R.n_recent;
+            if (n >= kMaxRecent) {
+                for (int j = 1; j < kMaxRecent; ++j) R.recent[j - 1] = R.recent[j];
+                n = kMaxRecent - 1;
+            }
+            R.recent[n] = pick;
+            R.n_recent = n + 1;
+            states[ri].offset += 1;
+        }
     }
 }
 
@@ -258,7 +304,23 @@ extern "C" int b200_sample(const float* logits, int32_t ld, int32_t T, int32_t V
     if (!logits || !rows || !uniforms || !probs || !out_ids) return fail(B200_EINVAL, "b200_sample: null pointer argument");
     if (T <= 0 || V <= 0) return fail(B200_EINVAL, "b200_sample: bad sizes T=%d V=%d", T, V);
     B200_CUDA_CHECK(launch(sample_kernel, dim3(T), dim3(kSampThreads), 0, static_cast<cudaStream_t>(stream_), pdl != 0,
-                           logits, ld, V, static_cast<const SampleRow*>(rows), uniforms, probs,
-                           static_cast<long long*>(out_ids)));
+                           logits, ld, V, static_cast<SampleRow*>(const_cast<void*>(rows)), uniforms, probs,
+                           static_cast<long long*>(out_ids), static_cast<SampleState*>(nullptr),
+                           static_cast<const int*>(nullptr)));
+    return B200_OK;
+}
+
+extern "C" int32_t b200_sample_state_bytes(void) { return (int32_t)sizeof(SampleState); }
+
+// Sampling with device-resident session state: rows / states are arrays indexed by row_index[t] (or t when row_index
+// is NULL); each draw takes its uniform number from the session's Philox4x32-10 stream (seed, draws so far), appends
+// the token to the row's recent-token window and advances the stream.  No host data per step: capturable in a graph.
+extern "C" int b200_sample_stateful(const float* logits, int32_t ld, int32_t T, int32_t V, void* rows, void* states,
+                                    const int32_t* row_index, float* probs, void* out_ids, int32_t pdl, void* stream_) {
+    if (!logits || !rows || !states || !probs || !out_ids) return fail(B200_EINVAL, "b200_sample_stateful: null pointer argument");
+    if (T <= 0 || V <= 0) return fail(B200_EINVAL, "b200_sample_stateful: bad sizes T=%d V=%d", T, V);
+    B200_CUDA_CHECK(launch(sample_kernel, dim3(T), dim3(kSampThreads), 0, static_cast<cudaStream_t>(stream_), pdl != 0,
+                           logits, ld, V, static_cast<SampleRow*>(rows), static_cast<const float*>(nullptr), probs,
+                           static_cast<long long*>(out_ids), static_cast<SampleState*>(states), row_index));
     return B200_OK;
 }

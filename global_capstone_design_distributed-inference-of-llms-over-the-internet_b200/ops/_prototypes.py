@@ -61,6 +61,8 @@ PROTOTYPES = [
     ("b200_argmax_partial", [vp, i32, i32, i32, vp, vp, vp, vp, i32, i32, vp, vp, i32, vp], C.c_int),
     ("b200_sample_row_bytes", [], i32),
     ("b200_sample", [vp, i32, i32, i32, vp, vp, vp, vp, i32, vp], C.c_int),
+    ("b200_sample_state_bytes", [], i32),
+    ("b200_sample_stateful", [vp, i32, i32, i32, vp, vp, vp, vp, vp, i32, vp], C.c_int),
     ("b200_gemm_static_scratch", [vp, vp], C.c_int),
     ("b200_attn_decode", [C.POINTER(AttnDecodeArgs), vp], C.c_int),
     ("b200_attn_decode_scratch_bytes", [i32, i32, i32, i32], i64),

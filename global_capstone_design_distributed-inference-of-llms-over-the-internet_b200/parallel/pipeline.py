@@ -145,6 +145,7 @@ class PipelineEngine:
         self.h2d_bytes = 0
         self.d2h_bytes = 0
         self.links = None
+        self._greedy = True          # True, or "sample": the last stage samples on the device (see generate)
         self._tail_pending: dict = {}
         if self.hop == "p2p":
             self._init_p2p()
@@ -241,7 +242,7 @@ class PipelineEngine:
                     sp.decode(kv, prog=self._prog_host)
                 self._tail_pending[j0] = B
             elif self.is_last:
-                sp.decode(kv, prog=self._prog_last)
+                sp.decode(kv, prog=self._prog_last, greedy=self._greedy)
             else:
                 sp.decode(kv, prog=self._prog_mid)
         if self.is_first and to_host:
@@ -272,7 +273,7 @@ class PipelineEngine:
                 sp.decode(kv, prog=self._prog_host)
                 self._tail_pending[j] = 1
             elif self.is_last:
-                sp.decode(kv, prog=self._prog_last)
+                sp.decode(kv, prog=self._prog_last, greedy=self._greedy)
             else:
                 sp.decode(kv, prog=self._prog_mid)
         self._streaming_live = True
@@ -330,7 +331,7 @@ class PipelineEngine:
     def _stage_prefill(self, kv: SessionKV, ids: Optional[torch.Tensor], h: Optional[torch.Tensor]):
         sp = self.span
         if self.backend == "native":
-            return sp.prefill(kv, h_in=h, ids=ids)
+            return sp.prefill(kv, h_in=h, ids=ids, greedy=self._greedy)
         if self.is_first:
             h = sp.embed(ids, kv.length)
         h = sp.forward(h, kv)
@@ -342,7 +343,7 @@ class PipelineEngine:
     def _stage_decode(self, kvs: Sequence[SessionKV], ids: Optional[torch.Tensor], h: Optional[torch.Tensor]):
         sp = self.span
         if self.backend == "native":
-            return sp.decode(kvs, h_in=h, ids=ids)
+            return sp.decode(kvs, h_in=h, ids=ids, greedy=self._greedy)
         outs = []
         for b, kv in enumerate(kvs):
             hb = sp.embed(ids[b:b + 1], kv.length) if self.is_first else h[b:b + 1]
@@ -434,7 +435,7 @@ class PipelineEngine:
                 self._tok_host[j] = int(t)
             self.span.ids_in[:S].copy_(self._tok_host[:S], non_blocking=True)
             self.h2d_bytes += 8 * S
-            out = self.span.decode(kvs, ids=None)
+            out = self.span.decode(kvs, ids=None, greedy=self._greedy)
             self.span.prestage(kvs)                                   # next step's positions, off the critical path
             self._tok_host[:S].copy_(out[1].reshape(-1)[:S])          # blocking D2H
             self.d2h_bytes += 8 * S
@@ -595,12 +596,30 @@ class PipelineEngine:
                 lst[j] = None
 
     def generate(self, prompts: Sequence[torch.Tensor], max_new_tokens: int, eos_token_id: Optional[int] = None,
-                 streaming: bool = False):
-        """Greedy generation for a batch of prompts (one session each).  Returns, on rank 0,
-        ``(tokens per prompt, stats)`` with TTFT / decode timings like the reference client prints
-        (src/main.py:213-225); None elsewhere."""
+                 streaming: bool = False, sampling=None, seed: int = 0, eos_check_every: int = 8):
+        """Generation for a batch of prompts (one session each).  Returns, on rank 0, ``(tokens per prompt, stats)``
+        with TTFT / decode timings like the reference client prints (src/main.py:213-225); None elsewhere.
+
+        ``sampling``: a :class:`~petals_b200.runtime.sampler.SamplingParams`; with ``temperature > 0`` the LAST stage
+        samples on the device (``b200_sample_stateful``: repetition penalty, temperature, top-k, top-p with the
+        reference's rules, src/rpc_handler.py:327-403) from a per-session Philox stream seeded with ``seed`` +
+        session index, so the tokens do not depend on the number of stages.  Otherwise greedy.
+        ``eos_token_id``: generation stops once every session has produced it; the decision is rank 0's and is
+        shared with the other ranks every ``eos_check_every`` rounds (they run ahead in between)."""
         self.close_sessions()
         ids = self.open_sessions(len(prompts))
+        sample = sampling is not None and sampling.temperature > 0.0
+        if sample:
+            if self.backend != "native":
+                raise NotImplementedError("device-side sampling runs on the native backend")
+            if self.head_split:
+                raise ValueError("sampling needs the whole vocabulary on the last stage: build the engine with "
+                                 "head_split=False")
+            if self.is_last:
+                pool = self.span.enable_sampling(4 * self.max_sessions)
+                for i in ids:
+                    self.sessions[i].sampler_row = pool.open(sampling, seed + i)
+        self._greedy = "sample" if sample else True
         t0 = time.perf_counter()
         first = [self.prefill(i, p) for i, p in zip(ids, prompts)]
         ttft = time.perf_counter() - t0
@@ -617,15 +636,27 @@ class PipelineEngine:
             if self.is_first and got:
                 for o, t in zip(outs, got):
                     o.append(t)
-        for _ in range(0 if (streaming and self.world > 1) else max_new_tokens - 1):
+        for step in range(0 if (streaming and self.world > 1) else max_new_tokens - 1):
             cur = self.decode_round(cur)
             if self.is_first:
                 for o, t in zip(outs, cur):
                     o.append(t)
-                if eos_token_id is not None and all(eos_token_id in o for o in outs):
-                    # the stop decision is made on rank 0; other ranks learn it via the flag below
-                    pass
+            if eos_token_id is not None:
+                done = self.is_first and all(eos_token_id in o for o in outs)
+                if self.world == 1:
+                    if done:
+                        break
+                elif (step + 1) % max(1, eos_check_every) == 0:
+                    # rank 0 decides, everybody learns it at the same round (the chain stays in lock step)
+                    flag = torch.tensor([1 if done else 0], dtype=torch.int32, device=self.device)
+                    dist.broadcast(flag, src=0)
+                    if int(flag.item()):
+                        break
         dec = time.perf_counter() - t1
+        if sample and self.is_last:
+            for i in ids:
+                self.span.sampler.close(self.sessions[i].sampler_row)
+        self._greedy = True
         if self.is_first:
             if eos_token_id is not None:
                 outs = [o[: o.index(eos_token_id) + 1] if eos_token_id in o else o for o in outs]

@@ -159,12 +159,23 @@ class NativeSpan:
             self.splits = attn_splits or int(os.environ.get("B200_ATTN_SPLITS", "0")) or max(1, min(16, kv_capacity // 64))
             self.attn_ws = A.DecodeAttnWorkspace(self.device, self.max_batch, c.n_heads, c.n_kv_heads, c.head_dim,
                                                  self.splits)
-            self.kv_ptrs = torch.zeros(max(nl, 1), self.max_batch, 2, dtype=torch.int64, device=self.device)
-            # positions of the step's tokens, then one more int: the step number the flag chain tags its words with
-            self.pos = torch.zeros(self.max_batch + 1, dtype=torch.int32, device=self.device)
-            self.step_seq = self.pos[self.max_batch:]
+            # What a captured step reads about "its" sessions lives in ONE device buffer, so that pointing the graph at
+            # the sessions of the next step is one host-to-device copy: positions of the step's tokens, the step number
+            # the flag chain tags its words with, the sampler rows of the sessions (device-side sampling, see
+            # enable_sampling) and, behind them, the table of cache pointers [layer][token][K, V].
+            mb = self.max_batch
+            self._n_pos = 2 * mb + 1
+            n_head = (self._n_pos + 1) // 2 * 2                     # the int64 table starts 8-byte aligned
+            n_tab = max(nl, 1) * mb * 2
+            self._stage_dev = torch.zeros(n_head + 2 * n_tab, dtype=torch.int32, device=self.device)
+            self._n_stage_head = n_head
+            self.pos = self._stage_dev[:self._n_pos]
+            self.kv_ptrs = self._stage_dev[n_head:].view(torch.int64).view(max(nl, 1), mb, 2)
+            self.step_seq = self.pos[mb:mb + 1]
+            self.samp_idx = self.pos[mb + 1:]
+            self.sampler = None
             self._seq_host = 0
-            self._pos_ring = [(torch.zeros(self.max_batch + 1, dtype=torch.int32).pin_memory(), torch.cuda.Event())
+            self._pos_ring = [(torch.zeros(n_head + 2 * n_tab, dtype=torch.int32).pin_memory(), torch.cuda.Event())
                               for _ in range(8)]
             self.chain_tokens = 0
             if (CHAIN_MAX_TOKENS > 0 and not fp8 and self.layers
@@ -447,7 +458,7 @@ class NativeSpan:
 
     def _head(self, h_rows: torch.Tensor, greedy: bool, out_ids: Optional[torch.Tensor] = None,
               init_pair: Optional[torch.Tensor] = None, out_pair: Optional[torch.Tensor] = None,
-              gemm_done: bool = False) -> torch.Tensor:
+              gemm_done: bool = False, row_index: Optional[torch.Tensor] = None) -> torch.Tensor:
         """h_rows: [B<=32, H] -> logits [B, V (or this span's vocabulary shard)] fp32 (and ids_out when greedy).
 
         ``init_pair`` / ``out_pair``: arg-max candidates exchanged between vocabulary shards (see ops.elementwise.argmax)."""
@@ -464,12 +475,28 @@ class NativeSpan:
                      norm_b=self.final_norm_b, norm_eps=c.norm_eps, out_fp32=True, workspace=self.ws, pdl=self.pdl,
                      chain=link)
             self._count()
-        if greedy:
+        if greedy == "sample":
+            # device-side sampling: parameters, recent tokens and the Philox stream of every session live on the GPU
+            assert self.sampler is not None and self.head_lo == 0 and self.head_hi == c.vocab, \
+                "sampling needs enable_sampling() and the whole vocabulary on this span"
+            idx = self.samp_idx[:B] if row_index is None else row_index
+            self.sampler.sample(logits, idx, self.ids_out[:B] if out_ids is None else out_ids, pdl=self.pdl)
+            self._count()
+        elif greedy:
             ids = self.ids_out[:B] if out_ids is None else out_ids
             E.argmax(logits, ids, self.argmax_ws, pdl=self.pdl, idx_offset=self.head_lo, init_pair=init_pair,
                      out_pair=out_pair)
             self._count()
         return logits
+
+    def enable_sampling(self, n_rows: int):
+        """Device-resident sampling state for up to ``n_rows`` sessions (``decode(..., greedy="sample")``): open a
+        row per session with ``span.sampler.open(params, seed)`` and store its index in ``kv.sampler_row``."""
+        from ..ops.sampling import SamplerPool
+
+        if self.sampler is None:
+            self.sampler = SamplerPool(self.device, n_rows, self.cfg.vocab, self.max_batch)
+        return self.sampler
 
     def _embed(self, T: int, pos0: int, use_pos_buffer: bool) -> torch.Tensor:
         h = self.h_a[:T]
@@ -489,10 +516,15 @@ class NativeSpan:
         """
         B = len(kvs)
         key = tuple(kv.data.data_ptr() for kv in kvs)
+        slot = self._pos_ring_idx
+        self._pos_ring_idx = (slot + 1) % len(self._pos_ring)
+        host, ev = self._pos_ring[slot]
+        ev.synchronize()
+        n_copy = self._n_pos
         if key != self._ptr_key:
-            tab = self._ptr_tables.get(key)
+            tab = self._ptr_tables.get(key)       # host-side table per session tuple (the addresses determine it)
             if tab is None:
-                host = torch.zeros(max(self.n_layers, 1), B, 2, dtype=torch.int64)
+                tab = torch.zeros(max(self.n_layers, 1), self.max_batch, 2, dtype=torch.int64)
                 for b, kv in enumerate(kvs):
                     if kv.max_len != self.kv_capacity:
                         raise ValueError(f"session capacity {kv.max_len} != engine kv_capacity {self.kv_capacity}")
@@ -500,25 +532,22 @@ class NativeSpan:
                     per_layer = kv.data.stride(0) * kv.data.element_size()
                     half = kv.data.stride(1) * kv.data.element_size()
                     for li in range(self.n_layers):
-                        host[li, b, 0] = base + li * per_layer
-                        host[li, b, 1] = base + li * per_layer + half
-                tab = host.to(self.device)
+                        tab[li, b, 0] = base + li * per_layer
+                        tab[li, b, 1] = base + li * per_layer + half
                 if len(self._ptr_tables) > 256:
                     self._ptr_tables.clear()
                 self._ptr_tables[key] = tab
-            self.kv_ptrs[:, :B].copy_(tab)
+            host[self._n_stage_head:].view(torch.int64).view_as(tab).copy_(tab)
             self._ptr_key = key
-        slot = self._pos_ring_idx
-        self._pos_ring_idx = (slot + 1) % len(self._pos_ring)
-        host, ev = self._pos_ring[slot]
-        ev.synchronize()
+            n_copy = host.numel()                 # positions and pointers travel in the same copy
         for b, kv in enumerate(kvs):
             if kv.length + 1 > kv.max_len:
                 raise ValueError(f"session {kv.session_id}: max_length {kv.max_len} reached")
             host[b] = kv.length
+            host[self.max_batch + 1 + b] = getattr(kv, "sampler_row", 0) or 0
         self._seq_host = self._seq_host % 1000000 + 1        # a new step number for every staged step (never 0)
         host[self.max_batch] = self._seq_host
-        self.pos.copy_(host, non_blocking=True)
+        self._stage_dev[:n_copy].copy_(host[:n_copy], non_blocking=True)
         ev.record(torch.cuda.current_stream(self.device))
 
     def prestage(self, kvs: Sequence[SessionKV]) -> None:
@@ -649,7 +678,7 @@ class NativeSpan:
 
             pos_inc = torch.zeros_like(self.pos)
             pos_inc[:B] = 1
-            pos_inc[self.max_batch] = 1
+            pos_inc[self.max_batch] = 1          # (the sampler rows behind it stay as they are)
 
             def body():
                 self._decode_body(B, True, True)
@@ -754,7 +783,10 @@ class NativeSpan:
         kv.touch()
         if self.has_head and not tail_only:
             self.last_hidden = last_h
-            self._head(last_h, greedy, out_pair=self.head_out_pair)
+            ri = None
+            if greedy == "sample":
+                ri = torch.tensor([getattr(kv, "sampler_row", 0) or 0], dtype=torch.int32, device=self.device)
+            self._head(last_h, greedy, out_pair=self.head_out_pair, row_index=ri)
             return self.logits[:1], self.ids_out[:1]
         return out
 

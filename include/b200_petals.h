@@ -330,6 +330,16 @@ int b200_trace_set(void* buf, int32_t cap);
 int32_t b200_sample_row_bytes(void);
 int b200_sample(const float* logits, int32_t ld, int32_t T, int32_t V, const void* rows, const float* uniforms,
                 float* probs, void* out_ids, int32_t pdl, void* stream);
+/* The same with the sessions' sampling state on the device: rows[row_index[t]] (row_index NULL: rows[t]) holds the
+ * parameters and the window of recent tokens, states[..] = {uint64 seed, uint64 draws so far}
+ * (b200_sample_state_bytes() each).  The uniform number of a draw is the first word of
+ * Philox4x32-10(key = seed, counter = draws so far); after the draw the kernel appends the token to the window and
+ * advances the stream.  Nothing comes from the host per step, so the call can sit in a captured graph, and a session's
+ * tokens depend only on its seed (the reference draws from torch's global generator on whichever server samples,
+ * src/rpc_handler.py:396-403). */
+int32_t b200_sample_state_bytes(void);
+int b200_sample_stateful(const float* logits, int32_t ld, int32_t T, int32_t V, void* rows, void* states,
+                         const int32_t* row_index, float* probs, void* out_ids, int32_t pdl, void* stream);
 
 #ifdef __cplusplus
 }

@@ -299,13 +299,44 @@ def _build_stage(args, device, start: int, end: int, final: bool, n_layers: int)
         kw["kv_capacity"] = args.kv_capacity
     if getattr(args, "max_batch", None):
         kw["max_batch"] = args.max_batch
+    if _tp_width(args) > 1:
+        # a span wider than one GPU: this process holds one tensor-parallel shard of it (runtime/tp_stage.py)
+        import torch.distributed as dist
+
+        from petals_b200.runtime.tp_stage import TPStage
+
+        kw.pop("keep_layers_on_gpu", None)
+        return TPStage(full, start, end, dist.group.WORLD, final=final, **kw)
     return StageLast(full, start, **kw) if final else StageSegment(full, start, end, **kw)
+
+
+def _tp_width(args) -> int:
+    return int(getattr(args, "tp", 1) or 1) if not getattr(args, "inbox", False) else 1
+
+
+def _tp_setup(args, device) -> int:
+    """Served stage with --tp k: one process per GPU (torchrun), rank 0 serves, the others follow.  Returns the rank."""
+    import torch.distributed as dist
+
+    if not dist.is_initialized():
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=device)
+    if dist.get_world_size() != _tp_width(args):
+        raise SystemExit(f"--tp {args.tp} needs exactly {args.tp} processes (torchrun --nproc-per-node {args.tp}); "
+                         f"got {dist.get_world_size()}")
+    return dist.get_rank()
 
 
 def run_stage_server_fixed(args, device, splits, block: bool = True):
     cfg = resolve_config(args.model)
     start, end, final = stage_span(splits, args.stage, cfg.n_layers)
+    tp_rank = _tp_setup(args, device) if _tp_width(args) > 1 else 0
     stage_model = _build_stage(args, device, start, end, final, cfg.n_layers)
+    if tp_rank > 0:
+        from petals_b200.runtime.tp_stage import serve_follower
+
+        serve_follower(stage_model)        # returns when the leader stops
+        return None
     handle = start_stage_server(args, device, stage_model, final, stage_index=args.stage)
     if block:
         handle.wait()
@@ -320,6 +351,22 @@ def run_stage_server_with_load_balancing(args, device, splits, num_blocks=None, 
     num_blocks = num_blocks or args.num_blocks or _default_num_blocks(args, cfg, device)
     num_blocks = min(num_blocks, total_blocks - (splits[0] if splits else 0))
     min_block = splits[0] if splits else 0
+    tp = _tp_width(args)
+    tp_rank = _tp_setup(args, device) if tp > 1 else 0
+    if tp > 1:
+        import torch.distributed as dist
+
+        # the leader looks at the swarm and decides; the followers take its word (one placement: re-placing a
+        # tensor-parallel server would mean reloading every shard, so it keeps its blocks)
+        max_placements = 1
+        span = [0, 0]
+        if tp_rank > 0:
+            dist.broadcast_object_list(span, src=0)
+            from petals_b200.runtime.tp_stage import serve_follower
+
+            stage_model = _build_stage(args, device, span[0], span[1], span[1] >= total_blocks, cfg.n_layers)
+            serve_follower(stage_model)
+            return None
     dht = _make_dht(args)
     placements = 0
     handle = None
@@ -341,6 +388,10 @@ def run_stage_server_with_load_balancing(args, device, splits, num_blocks=None, 
         blocks = list(range(start, end))
         final = end >= total_blocks
         logger.info("Selected blocks [%d:%d) (final_stage=%s)", start, end, final)
+        if tp > 1:
+            import torch.distributed as dist
+
+            dist.broadcast_object_list([start, end], src=0)
         stage_model = _build_stage(args, device, start, end, final, cfg.n_layers)
         try:
             thr = get_server_throughput(stage_model, device, args.dtype, cfg.hidden,
@@ -411,9 +462,16 @@ def run_inbox(args, device, splits):
     tok = load_tokenizer(args.model, cfg)
     ids = torch.tensor(tok.encode(args.prompt), dtype=torch.long)
     cap = max(getattr(args, "kv_capacity", None) or 0, ((ids.numel() + args.max_new_tokens + 255) // 256) * 256)
+    from petals_b200.runtime.sampler import SamplingParams
+
+    sampling = None
+    if args.temperature > 0:      # same knobs as the TCP path; the last stage samples on the device
+        rp = getattr(args, "repetition_penalty", None)
+        sampling = SamplingParams(args.temperature, args.top_p, args.top_k, 1.5 if rp is None else rp)
     eng = PipelineEngine(args.model, splits, args.dtype, device, kv_capacity=cap, max_sessions=1,
-                         seed=getattr(args, "seed", 0), tp=args.tp)
-    res = eng.generate([ids], args.max_new_tokens, eos_token_id=tok.eos_token_id)
+                         seed=getattr(args, "seed", 0), tp=args.tp, head_split=False if sampling else None)
+    res = eng.generate([ids], args.max_new_tokens, eos_token_id=tok.eos_token_id, sampling=sampling,
+                       seed=getattr(args, "seed", 0))
     if dist.get_rank() == 0:
         outs, stats = res
         print(f"\n{'=' * 80}\nPROMPT: {args.prompt}\nGENERATED: {tok.decode(outs[0])}\n{'=' * 80}\n")
@@ -474,7 +532,10 @@ def build_parser() -> argparse.ArgumentParser:
     p.add_argument("--inbox", action="store_true",
                    help="in-box mode: launch with torchrun (one process per GPU); stages hand hidden states over "
                         "NCCL p2p instead of TCP RPC; --splits gives the stage boundaries, --stage is ignored")
-    p.add_argument("--tp", type=int, default=1, help="--inbox: tensor-parallel width of every stage")
+    p.add_argument("--tp", type=int, default=1,
+                   help="tensor-parallel width: with --inbox of every pipeline stage; for a served stage (--stage k or "
+                        "--use_load_balancing) the span runs on this many GPUs - launch with torchrun "
+                        "--nproc-per-node <tp>, rank 0 serves, the other ranks hold the other shards")
     return p
 
 

@@ -327,9 +327,25 @@ class StageConnectionHandler:
         ok, rtt = check_direct_reachability(metadata["maddr"], float(metadata.get("timeout", 2.0)))
         return [], {"reachable": ok, "rtt_s": rtt}
 
+    def _close(self, sid: str) -> bool:
+        closed = self.kv.close(sid)
+        mirror = getattr(self.stage_model, "close_session", None)     # tensor-parallel stage: the followers' shards
+        if closed and mirror is not None:
+            mirror(sid)
+        return closed
+
     def rpc_close_session(self, uid: str, tensors, metadata: Dict):
-        return [], {"closed": self.kv.close(metadata.get("session_id", ""))}
+        sid = metadata.get("session_id", "")
+        if getattr(self.stage_model, "close_session", None) is not None:
+            return [], {"closed": self._submit(self._close, sid, kind="inference")}    # serialised with the steps
+        return [], {"closed": self.kv.close(sid)}
 
     def shutdown(self) -> None:
+        stop = getattr(self.stage_model, "stop_followers", None)
+        if stop is not None:
+            try:
+                self._submit(stop, kind="inference")
+            except Exception:  # noqa: BLE001
+                pass
         self.pool.shutdown()
         self._fwd_client.close()

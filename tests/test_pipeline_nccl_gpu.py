@@ -47,6 +47,29 @@ def _device_loop(eng, prompts, n_steps, group):
     return rows
 
 
+def _sampled(eng, prompts):
+    """Sampled generation (device-side sampler on the last stage, per-session Philox streams) and an EOS stop."""
+    from petals_b200.runtime.sampler import SamplingParams
+
+    sp = SamplingParams(0.9, 0.92, 50, 1.3)
+    a = eng.generate(prompts[:2], 12, sampling=sp, seed=42)
+    b = eng.generate(prompts[:2], 12, sampling=sp, seed=42)
+    g = eng.generate(prompts[:2], 24, eos_token_id=None)
+    eos = None
+    if eng.is_first:
+        assert a[0] == b[0], "same seed, same tokens"
+        eos = g[0][0][5]                       # a token the greedy run is known to produce
+    import torch.distributed as dist
+    if dist.is_initialized():
+        t = torch.tensor([eos if eos is not None else 0], device=eng.device)
+        dist.broadcast(t, 0)
+        eos = int(t.item())
+    e = eng.generate(prompts[:2], 24, eos_token_id=eos, eos_check_every=2)
+    if eng.is_first:
+        return a[0], e[0][0], eos
+    return None
+
+
 def _worker(rank, world, port, model, splits, q):
     sys.path.insert(0, ROOT)
     import torch.distributed as dist
@@ -67,8 +90,11 @@ def _worker(rank, world, port, model, splits, q):
         res_s = eng.generate(prompts[:2], 10, streaming=True)
         loop1 = _device_loop(eng, prompts, 6, 1)
         loop2 = _device_loop(eng, prompts, 6, 2)
+        samp = None
+        if not split:      # sampling needs the whole vocabulary on the last stage
+            samp = _sampled(eng, prompts)
         if rank == 0:
-            out[(hop, split)] = (res[0], res_s[0], loop1, loop2)
+            out[(hop, split)] = (res[0], res_s[0], loop1, loop2, samp)
         dist.barrier()
         del eng
     if rank == 0:
@@ -86,12 +112,14 @@ def _reference(model):
     prompts = _prompts(eng.cfg.vocab)
     ref = eng.generate(prompts[:2], 10)[0]
     loop = _device_loop(eng, prompts, 6, 1)
+    samp = _sampled(eng, prompts)
     del eng
-    return ref, loop
+    return ref, loop, samp
 
 
 def _chain(world, model, splits):
-    ref, ref_loop = _reference(model)
+    ref, ref_loop, ref_samp = _reference(model)
+    assert ref_samp[1][-1] == ref_samp[2] or ref_samp[2] not in ref_samp[1], "an EOS in the output ends it"
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
     port = _free_port()
@@ -102,7 +130,10 @@ def _chain(world, model, splits):
     for p in procs:
         p.join(timeout=120)
         assert p.exitcode == 0
-    for mode, (res, res_s, loop1, loop2) in out.items():
+    for mode, (res, res_s, loop1, loop2, samp) in out.items():
+        if samp is not None:
+            assert samp[0] == ref_samp[0], f"{mode}: sampled tokens differ from one GPU (same seed)"
+            assert samp[1] == ref_samp[1], f"{mode}: EOS-stopped generation differs from one GPU"
         assert res == ref, f"{mode}: generate() differs from one GPU"
         assert res_s == ref, f"{mode}: streaming generate() differs from one GPU"
         assert loop1 == ref_loop, f"{mode}: device loop differs from one GPU"

@@ -50,3 +50,31 @@ def test_sampling_statistics():
         counts += torch.bincount(ids.cpu(), minlength=V).float()
     ref = filtered_probs(row.clone(), params, []).cpu()
     assert (counts / counts.sum() - ref).abs().max().item() < 0.03
+
+
+def test_stateful_sampler_matches_stateless_with_philox_uniforms():
+    """b200_sample_stateful keeps parameters, recent tokens and the Philox stream on the device; fed the same
+    uniform numbers (host restatement of Philox4x32-10) the stateless kernel must pick the same tokens, step by step."""
+    from petals_b200.ops.sampling import DeviceSampler, SamplerPool, philox_uniform
+    from petals_b200.runtime.sampler import SamplingParams
+
+    dev = torch.device("cuda")
+    V = 4096
+    g = torch.Generator(device="cuda").manual_seed(7)
+    params = [SamplingParams(0.9, 0.92, 40, 1.3), SamplingParams(1.2, 0.8, 0, 1.5)]
+    seeds = [1234, 99]
+    pool = SamplerPool(dev, 8, V, max_batch=4)
+    rows = [pool.open(p, s, recent=[5, 5, 5] if i == 0 else []) for i, (p, s) in enumerate(zip(params, seeds))]
+    idx = torch.tensor(rows, dtype=torch.int32, device=dev)
+    ref = DeviceSampler(dev, 2, V)
+    hist = [[5, 5, 5], []]
+    out = torch.zeros(2, dtype=torch.int64, device=dev)
+    for step in range(12):
+        logits = torch.randn(2, V, device=dev, generator=g) * 3.0
+        pool.sample(logits, idx, out)
+        u = torch.tensor([philox_uniform(seeds[i], step) for i in range(2)], dtype=torch.float32, device=dev)
+        want = ref.sample(logits, params, hist, uniforms=u).clone()
+        assert torch.equal(out, want), f"step {step}: {out.tolist()} vs {want.tolist()}"
+        for i in range(2):
+            hist[i].append(int(want[i]))
+    assert pool.states[rows[0], 1].item() == 12 and pool.states[rows[1], 1].item() == 12   # draws made
