@@ -19,6 +19,7 @@ Every rank computes bit-identical hidden states (partials are added in rank orde
 from __future__ import annotations
 
 import ctypes
+import os
 from typing import Dict, List, Optional
 
 import torch
@@ -38,6 +39,75 @@ class TpArgs(ctypes.Structure):
     _fields_ = [("world", ctypes.c_int32), ("rank", ctypes.c_int32), ("n_max", ctypes.c_int32),
                 ("tiles_max", ctypes.c_int32), ("stage", ctypes.c_void_p * 8), ("flags", ctypes.c_void_p * 8),
                 ("seq", ctypes.c_void_p), ("exit_counter", ctypes.c_void_p), ("mode", ctypes.c_int32)]
+
+
+class NvlsArgs(ctypes.Structure):
+    """Mirror of ``b200_nvls_args``."""
+
+    _fields_ = [("mc_partial", ctypes.c_void_p), ("mc_out", ctypes.c_void_p), ("residual", ctypes.c_void_p),
+                ("bias", ctypes.c_void_p), ("T", ctypes.c_int32), ("N", ctypes.c_int32), ("ldp", ctypes.c_int32),
+                ("ldo", ctypes.c_int32), ("ldr", ctypes.c_int32), ("dtype", ctypes.c_int32), ("world", ctypes.c_int32),
+                ("rank", ctypes.c_int32), ("flags_local", ctypes.c_void_p), ("flags_peer", ctypes.c_void_p * 8),
+                ("seq", ctypes.c_void_p), ("cta_done", ctypes.c_void_p), ("pdl", ctypes.c_int32),
+                ("reserved", ctypes.c_int32)]
+
+
+class NvlsWorkspace:
+    """Symmetric, multicast-mapped buffers for the NVLS all-reduce of prefill-size row-parallel outputs
+    (``b200_tp_allreduce_nvls``): the partial-output buffer and the two hidden-state buffers of the span."""
+
+    def __init__(self, group: dist.ProcessGroup, device, rows: int, hidden: int, dtype: torch.dtype):
+        import torch.distributed._symmetric_memory as symm
+
+        self.world, self.rank = dist.get_world_size(group), dist.get_rank(group)
+        self.partial = symm.empty(rows, hidden, dtype=dtype, device=device)
+        self.h = [symm.empty(rows, hidden, dtype=dtype, device=device) for _ in range(2)]
+        self.flags = symm.empty(16, dtype=torch.int32, device=device)
+        for t in (self.partial, *self.h, self.flags):
+            t.zero_()
+        hs = [symm.rendezvous(t, group.group_name) for t in (self.partial, *self.h, self.flags)]
+        self.ok = all(int(getattr(h, "multicast_ptr", 0) or 0) != 0 for h in hs[:3])
+        off = [int(getattr(h, "offset", 0) or 0) for h in hs]
+        # multicast address of each buffer's STORAGE base (views are addressed relative to it, see mc_ptr)
+        self.mc = {}
+        if self.ok:
+            for t, h, o in zip((self.partial, *self.h), hs[:3], off[:3]):
+                sp = t.untyped_storage().data_ptr()
+                self.mc[sp] = int(h.multicast_ptr) + o - (t.data_ptr() - sp)
+        self.flag_ptrs = [int(hs[3].buffer_ptrs[r]) + off[3] for r in range(self.world)]
+        self.local = torch.zeros(2, dtype=torch.int32, device=device)      # [launches, CTAs done]
+        self._handles = hs
+        torch.cuda.synchronize(device)
+        dist.barrier(group)
+        L = native.lib()
+        L.b200_tp_allreduce_nvls.argtypes = [ctypes.POINTER(NvlsArgs), ctypes.c_void_p]
+        L.b200_tp_allreduce_nvls.restype = ctypes.c_int
+
+    def mc_ptr(self, t: torch.Tensor) -> int:
+        """Multicast address of a view into one of the symmetric buffers (rows from the top)."""
+        base = t.untyped_storage().data_ptr()
+        return self.mc[base] + (t.data_ptr() - base)
+
+    def allreduce(self, T: int, N: int, out: torch.Tensor, residual: Optional[torch.Tensor],
+                  bias: Optional[torch.Tensor], pdl: bool = False) -> None:
+        a = NvlsArgs()
+        a.mc_partial = self.mc_ptr(self.partial)
+        a.mc_out = self.mc_ptr(out)
+        a.residual = residual.data_ptr() if residual is not None else None
+        a.bias = bias.data_ptr() if bias is not None else None
+        a.T, a.N = T, N
+        a.ldp, a.ldo = self.partial.stride(0), out.stride(0)
+        a.ldr = residual.stride(0) if residual is not None else 0
+        a.dtype = G.dtype_code(out.dtype)
+        a.world, a.rank = self.world, self.rank
+        a.flags_local = self.flags.data_ptr()
+        for r in range(self.world):
+            a.flags_peer[r] = self.flag_ptrs[r]
+        a.seq = self.local.data_ptr()
+        a.cta_done = self.local.data_ptr() + 4
+        a.pdl = 1 if pdl else 0
+        native.check(native.lib().b200_tp_allreduce_nvls(ctypes.byref(a), native.current_stream_ptr()),
+                     "b200_tp_allreduce_nvls")
 
 
 class TPWorkspace:
@@ -174,4 +244,17 @@ def make_tp_span(cfg: ModelConfig, weights: Dict[str, object], device, dtype, gr
     span.tp_mode = mode
     span.tp_group = group
     span.tp = TPWorkspace(group, device, cfg.hidden) if mode == "fused" else None
+    span.nvls = None
+    if mode == "fused" and os.environ.get("B200_TP_NVLS", "1") != "0":
+        # prefill-size row-parallel outputs are reduced through the switch: the span's hidden-state buffers move into
+        # symmetric, multicast-mapped memory so that the reducing rank can write every rank's copy with multimem.st
+        try:
+            nv = NvlsWorkspace(group, device, span.h_a.shape[0], cfg.hidden, dtype)
+            if nv.ok:
+                span.h_a, span.h_b = nv.h
+                span.nvls = nv
+        except Exception as e:  # noqa: BLE001  (no multicast support: the NCCL path stays)
+            import logging
+
+            logging.getLogger(__name__).warning("NVLS workspace unavailable (%s): prefill all-reduce stays on NCCL", e)
     return span

@@ -221,6 +221,19 @@ class NativeSpan:
             from ..parallel.tensor_parallel import linear_allreduce
 
             linear_allreduce(x, w, self.tp, out=out, residual=residual, workspace=self.ws, pdl=self.pdl)
+        elif self.tp_mode == "fused" and getattr(self, "nvls", None) is not None and x.shape[0] <= self.nvls.partial.shape[0] \
+                and out.untyped_storage().data_ptr() in self.nvls.mc:
+            # prefill sizes: this rank's partial goes into the symmetric buffer, then ONE kernel reduces the ranks'
+            # partials through the switch (multimem.ld_reduce), adds bias / residual and writes every rank's output
+            # (multimem.st) - see csrc/tp_nvls.cu
+            T = x.shape[0]
+            bias, w.bias = w.bias, None
+            try:
+                G.linear(x, w, out=self.nvls.partial[:T], workspace=self.ws, pdl=self.pdl)
+            finally:
+                w.bias = bias
+            self.nvls.allreduce(T, w.n, out, residual, bias, pdl=self.pdl)
+            self._count()
         else:
             # library baseline: GEMM without bias/residual, NCCL all-reduce, then the epilogue in torch
             import torch.distributed as dist
@@ -566,8 +579,9 @@ class NativeSpan:
         want_head = self.has_head and (prog is None or prog.head)
         h = self._decode_layers(B, h, with_head=want_head)
         if want_head:
-            self._head(h, greedy, out_pair=getattr(prog, "out_pair", None) if prog is not None else None,
-                       gemm_done=self._head_done)
+            # (the warm-up pass before a capture must not draw: a draw advances the session's random stream)
+            self._head(h, False if (dry and greedy == "sample") else greedy,
+                       out_pair=getattr(prog, "out_pair", None) if prog is not None else None, gemm_done=self._head_done)
         self._chain_tail = None
         if prog is not None and prog.post is not None:
             prog.post(B, h, dry)

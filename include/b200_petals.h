@@ -172,6 +172,32 @@ int b200_gemm_allreduce(const b200_gemm_args* args, const b200_tp_args* tp, void
 int b200_gemm_gather(const b200_gemm_args* args, const b200_tp_args* tp, const void* residual, int32_t ldr,
                      const void* bias, void* stream);
 
+/* Row-parallel linear of a tensor-parallel span at PREFILL sizes: all-reduce of the ranks' partial outputs through
+ * the NVSwitch (NVLS) with the linear's epilogue in the same kernel: out = sum_r partial_r + bias + residual on every
+ * rank.  Each rank reads its slice of the elements through the multicast address with multimem.ld_reduce (the switch
+ * adds the ranks' values, fp32 accumulation), applies bias / residual, and writes the slice through the multicast
+ * address of the output with multimem.st (replicated into every rank's memory): reduce-scatter by load, all-gather by
+ * store, no rank polls its peers in turn.  The reference's dead TP path: NCCL all-reduce + separate torch adds
+ * (petals/server/backend.py:134-136).
+ *   mc_partial / mc_out  MULTICAST addresses (e.g. torch symmetric memory, handle.multicast_ptr + offset) of two
+ *                        symmetric buffers; every rank's GEMM wrote its [T, N] partial into its own copy of the first.
+ *   flags_local / flags_peer[r]  16 ints of symmetric memory per rank (zeroed once): this rank's copy and every rank's.
+ *   seq, cta_done        one int each, local, zeroed once.  All ranks must issue the same sequence of calls. */
+typedef struct b200_nvls_args {
+    const void* mc_partial;
+    void* mc_out;
+    const void* residual;  /* local [T, ldr] 16-bit, or NULL */
+    const void* bias;      /* [N] 16-bit, or NULL */
+    int32_t T, N, ldp, ldo, ldr, dtype;
+    int32_t world, rank;
+    int32_t* flags_local;
+    void* flags_peer[8];
+    int32_t* seq;
+    int32_t* cta_done;
+    int32_t pdl, reserved;
+} b200_nvls_args;
+int b200_tp_allreduce_nvls(const b200_nvls_args* args, void* stream);
+
 /* b200_gemm for callers that cannot allocate device memory (no counterpart in the reference, which
  * has no native code and lets torch allocate freely).  Same arguments and result as b200_gemm, but
  * args->scratch and args->counters are ignored: the workspace is a fixed ~5 MiB array inside the

@@ -56,6 +56,8 @@ def _run(rank, world, port, q, preset="tiny-llama-gqa"):
             outs.append(logits.float().clone())
         torch.cuda.synchronize()
         res[mode] = torch.cat(outs).cpu()
+        if mode == "fused":
+            res["nvls_used"] = torch.tensor(float(getattr(span, "nvls", None) is not None))
         dist.barrier()
     # every rank must hold identical logits in the fused mode
     mine = res["fused"].to(dev)
@@ -83,6 +85,7 @@ def test_tp_fused_allreduce_matches_single_gpu_and_nccl(world, preset):
         p.join(timeout=60)
         assert p.exitcode == 0
     assert same, "fused all-reduce must leave bit-identical results on every rank"
+    assert res.pop("nvls_used").item() == 1.0, "the 40-token prefill chunk should have been reduced through the switch (NVLS)"
     scale = res["single"].abs().max().item()
     assert (res["fused"] - res["single"]).abs().max().item() < 0.05 * scale
     assert (res["nccl"] - res["single"]).abs().max().item() < 0.05 * scale
