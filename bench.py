@@ -47,8 +47,8 @@ def parse_args():
     ap.add_argument("--tp-mode", default="fused", choices=["fused", "nccl"])
     ap.add_argument("--group", type=int, default=1,
                     help="sessions per micro-batch travelling through the chain together (serving-throughput mode)")
-    ap.add_argument("--weights", default="native", choices=["native", "fp8"],
-                    help="fp8 = opt-in e4m3 weights (NOT the headline configuration)")
+    ap.add_argument("--weights", default="native", choices=["native", "fp8", "mxfp8"],
+                    help="fp8 / mxfp8 = opt-in e4m3 weights with per-row / OCP-MX block scales (NOT the headline configuration)")
     ap.add_argument("--hop", default=None, choices=["p2p", "nccl"],
                     help="decode hop between stages: in-graph peer stores (default) or host-issued NCCL send/recv")
     ap.add_argument("--head-split", type=int, default=None, help="1/0: shard the LM head over the last and first stage")
@@ -259,7 +259,7 @@ def run_b200(args):
                       + ("Llama-2-7B" if args.model == "llama-2-7b" else args.model) + " N-stage pipeline",
             "value": round(tok_s, 2), "unit": "tokens/s", "n_gpus": world, "steps": K, "warmup": W,
             "ms_per_step": round(dev_ms / K, 4), "higher_is_better": True, "scaling": "weak",
-            "vs_baseline": None, "dtype": args.dtype if args.weights == "native" else f"{args.dtype} activations, fp8(e4m3) weights (opt-in)",
+            "vs_baseline": None, "dtype": args.dtype if args.weights == "native" else f"{args.dtype} activations, {args.weights} (e4m3) weights (opt-in)",
             "data": "synthetic prompts, random-init weights",
             "impl": "b200",
             "config": {"model": args.model, "global_batch": S, "seq_len": L, "parallelism": f"pp{stages}" + (f"tp{args.tp}({args.tp_mode})" if args.tp > 1 else ""),

@@ -27,7 +27,8 @@ constexpr int kLLMaxCtasDev = 512;   // CTAs one half of the word buffer has slo
 template <int BN, int DUAL, int FP8, int WIDE = 0, int LLIO = 0>
 __global__ void __launch_bounds__(kThreads, GemmCfg<BN, DUAL>::kMinBlocks)
 gemm_streamk_kernel(const GemmParams p) {
-    using Cfg = GemmCfg<BN, DUAL>;
+    constexpr int MX = (FP8 == 2) ? 1 : 0;      // FP8: 0 = 16-bit weights, 1 = e4m3 with one scale per row, 2 = MX block scales
+    using Cfg = GemmCfg<BN, DUAL, MX>;
     constexpr int SA = Cfg::kSA, SB = Cfg::kSB, APER = Cfg::kAPer;
 
     extern __shared__ uint8_t smem_raw[];
@@ -46,6 +47,7 @@ gemm_streamk_kernel(const GemmParams p) {
     float* stat_mean = reinterpret_cast<float*>(tmem_slot + 4);               // [32]
     float* stat_rstd = stat_mean + 32;                                        // [32]
     float* stat_red = stat_rstd + 32;                                         // [2][4][32]
+    uint8_t* smem_sfb = smem + Cfg::kSmemData + 1024;                         // MX: activation scale factors, 512 B per k-block
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
@@ -127,6 +129,9 @@ gemm_streamk_kernel(const GemmParams p) {
         {
             const uint32_t idesc = FP8 ? umma_idesc(kTileM, BN, 0, 0, 0, 0)   // e4m3 x e4m3
                                             : umma_idesc(kTileM, BN, p.is_bf16, p.is_bf16, 0, 0);
+            const uint32_t sf_base = tmem_base + BN * APER * Cfg::kNAcc;      // MX: scale-factor columns behind the accumulators
+            const uint32_t sfb_smem = smem_u32(smem_sfb);
+            uint32_t sf_slot = 0;
             int u = (int)(q_begin / p.kbpt);
             int kb0 = (int)(q_begin - (long long)u * p.kbpt);
             long long left = q_end - q_begin;
@@ -148,7 +153,29 @@ gemm_streamk_kernel(const GemmParams p) {
                         if (bofs == 0 && !(p.debug & 2)) mbar_wait(&b_full[sb], phb);
                         tc_fence_after();
                         const uint64_t bdesc = umma_desc_kmajor_sw128(b_base + sb * Cfg::kStageB + bofs * Cfg::kSubB, 1024);
-                        if (!(p.debug & 1) && elect_one()) {
+                        if (MX && !(p.debug & 1) && elect_one()) {
+                            // scale factors of this k-block: smem -> tensor memory (in order with the MMAs that use them)
+                            const uint32_t cols = sf_base + sf_slot * (APER * 4 + 4);
+                            const uint32_t sfa_smem = a_base + sa * Cfg::kStageA + j * Cfg::kBlockA + APER * kABytes;
+#pragma unroll
+                            for (int a = 0; a < APER; ++a)
+                                tmem_cp_32x128b(cols + a * 4, umma_desc_kmajor_noswizzle(sfa_smem + a * kMxSfBytes, 128, 128));
+                            tmem_cp_32x128b(cols + APER * 4,
+                                            umma_desc_kmajor_noswizzle(sfb_smem + (sb * Cfg::kGroup + bofs) * kMxSfBytes, 128, 128));
+#pragma unroll
+                            for (int a = 0; a < APER; ++a) {
+                                const uint64_t adesc = umma_desc_kmajor_sw128(
+                                    a_base + sa * Cfg::kStageA + j * Cfg::kBlockA + a * kABytes, 1024);
+#pragma unroll
+                                for (int k = 0; k < kBK / 16; ++k) {    // four 32-element steps, one scale byte each
+                                    const uint32_t d_tmem = tmem_base + (a * Cfg::kNAcc + (k % Cfg::kNAcc)) * BN;
+                                    umma_mxf8(d_tmem, adesc + (uint64_t)(k * 2), bdesc + (uint64_t)(k * 2),
+                                              umma_idesc_mxf8(kTileM, BN, k, k), acc, cols + a * 4, cols + APER * 4);
+                                }
+                            }
+                        }
+                        if (MX) sf_slot = (sf_slot + 1) % kMxSfSlots;
+                        if (!MX && !(p.debug & 1) && elect_one()) {
 #pragma unroll
                             for (int a = 0; a < APER; ++a) {
                                 const uint64_t adesc = umma_desc_kmajor_sw128(
@@ -254,10 +281,10 @@ gemm_streamk_kernel(const GemmParams p) {
             named_bar_sync(1, kEpiThreads);
         }
 
-        if (FP8) fp8_stats_128(p, min(BN, p.T), e, stat_red, stat_mean, stat_rstd);   // qmul, epilogue scale
+        if (FP8 == 1) fp8_stats_128(p, min(BN, p.T), e, stat_red, stat_mean, stat_rstd);   // qmul, epilogue scale
         uint32_t part = 0, phb = 0;
         int sb = 0;
-        bool rms_ready = (FP8 != 0);   // fp8: the 1/rms is already folded into stat_rstd
+        bool rms_ready = (FP8 == 1);   // per-row fp8: the 1/rms is already folded into stat_rstd
         const int tp_seq = (p.tp_world > 1) ? (__ldcv(p.tp_seq) + 1) : 0;
         bool tp_bumped = false;
         constexpr int ll_seq = 1;   // tag of a published word; the consumer clears the word again (tag 0) once it has read it
@@ -300,7 +327,7 @@ gemm_streamk_kernel(const GemmParams p) {
                                         gl = ld_nc_v4(p.norm_w + kcol8);
                                         gh = ld_nc_v4(p.norm_w + kcol8 + 8);
                                     }
-                                    const float qm = (t < p.T) ? stat_mean[r0 + 16 * i] : 0.f;
+                                    const float qm = MX ? 1.0f : ((t < p.T) ? stat_mean[r0 + 16 * i] : 0.f);
                                     const uint32_t xs[8] = {lo.x, lo.y, lo.z, lo.w, hi.x, hi.y, hi.z, hi.w};
                                     const uint32_t gs[8] = {gl.x, gl.y, gl.z, gl.w, gh.x, gh.y, gh.z, gh.w};
                                     float f[16];
@@ -314,6 +341,25 @@ gemm_streamk_kernel(const GemmParams p) {
                                         }
                                         f[2 * w] = a * qm;
                                         f[2 * w + 1] = b * qm;
+                                    }
+                                    if (MX) {
+                                        // one UE8M0 scale per 32 elements = this thread's 16 and its neighbour's (ch ^ 1):
+                                        // 2^e with e = ceil(log2(amax / 448)), so that every value fits e4m3
+                                        float am = 0.f;
+#pragma unroll
+                                        for (int w = 0; w < 16; ++w) am = fmaxf(am, fabsf(f[w]));
+                                        am = fmaxf(am, __shfl_xor_sync(0xffffffffu, am, 1));
+                                        int ex = -127;
+                                        if (am > 0.f) {
+                                            const float m = frexpf(am * (1.0f / 448.0f), &ex);     // am/448 = m * 2^ex, m in [0.5, 1)
+                                            if (m == 0.5f) --ex;
+                                            ex = max(-127, min(126, ex));
+                                        }
+                                        const float inv = __uint_as_float((uint32_t)(127 - ex) << 23);   // 2^-ex
+#pragma unroll
+                                        for (int w = 0; w < 16; ++w) f[w] *= inv;
+                                        const uint32_t sfb = (uint32_t)(ex + 127) << (8 * i);
+                                        if (i == 0) gw[g].x = sfb; else gw[g].x |= sfb;
                                     }
                                     v[g][i] = make_uint4(pack_e4m3x4(f[0], f[1], f[2], f[3]), pack_e4m3x4(f[4], f[5], f[6], f[7]),
                                                          pack_e4m3x4(f[8], f[9], f[10], f[11]), pack_e4m3x4(f[12], f[13], f[14], f[15]));
@@ -377,6 +423,10 @@ gemm_streamk_kernel(const GemmParams p) {
                                     }
                                 }
                                 st_shared_v4(base + r * 128 + ((ch ^ (r & 7)) << 4), val);
+                                if (MX && !(ch & 1)) {   // the pair's scale byte: atom position (row % 32) * 16 + (row / 32) * 4 + group
+                                    const uint32_t sfa = smem_u32(smem_sfb) + (sb * G + g) * kMxSfBytes + (r & 31) * 16 + (r >> 5) * 4 + (ch >> 1);
+                                    asm volatile("st.shared.u8 [%0], %1;\n" ::"r"(sfa), "r"((cgw[g].x >> (8 * i)) & 0xffu) : "memory");
+                                }
                             }
                         }
                     }
@@ -420,7 +470,7 @@ gemm_streamk_kernel(const GemmParams p) {
                 rms_stats_128<LLIO>(p, min(BN, p.T), e, stat_red, stat_rstd, xtag);
                 rms_ready = true;
             }
-            const float* tok_scale = (p.norm_mode == B200_NORM_RMS || FP8) ? stat_rstd : nullptr;
+            const float* tok_scale = (p.norm_mode == B200_NORM_RMS || FP8 == 1) ? stat_rstd : nullptr;
             // ---- drain the accumulator of this part
             const bool full_tile = (kb0 == 0) && (kb1 == p.kbpt);
             const int slot = (part == 0) ? 0 : 1;
@@ -685,7 +735,7 @@ gemm_streamk_kernel(const GemmParams p) {
 
 template <int BN, int DUAL, int FP8 = 0, int WIDE = 0, int LLIO = 0>
 static int launch_gemm(const GemmParams& p, int grid, bool pdl, cudaStream_t stream) {
-    using Cfg = GemmCfg<BN, DUAL>;
+    using Cfg = GemmCfg<BN, DUAL, (FP8 == 2) ? 1 : 0>;
     static_assert(Cfg::kSmemBytes <= 227 * 1024, "shared memory budget exceeded");
     static thread_local int configured_dev = -1;
     int dev = 0;
@@ -792,7 +842,8 @@ static int gemm_impl(const b200_gemm_args* a, const b200_tp_args* tp, void* stre
     if (a->fp8) {
         if (t_tiles != 1 || bn > 32) return fail(B200_ELIMIT, "b200_gemm: fp8 weights support T <= 32 per call (got %d)", a->T);
         if (a->K % 128 != 0) return fail(B200_EINVAL, "b200_gemm: fp8 weights need K %% 128 == 0 (got %d)", a->K);
-        if (!a->w_scale) return fail(B200_EINVAL, "b200_gemm: fp8 weights need w_scale");
+        if (a->fp8 == 1 && !a->w_scale) return fail(B200_EINVAL, "b200_gemm: fp8 weights need w_scale");
+        if (a->fp8 != 1 && a->fp8 != 2) return fail(B200_EINVAL, "b200_gemm: fp8 must be 0, 1 (per-row scales) or 2 (MX block scales)");
         if (a->norm_mode == B200_NORM_LAYER) return fail(B200_EINVAL, "b200_gemm: fp8 + LayerNorm prologue is not supported");
     }
     if (a->norm_mode != B200_NORM_NONE) {
@@ -814,7 +865,7 @@ static int gemm_impl(const b200_gemm_args* a, const b200_tp_args* tp, void* stre
     p.ldx = a->ldx; p.ldo = a->ldo; p.ldr = a->ldr;
     p.n_tiles = a->n_tiles; p.t_tiles = t_tiles; p.kbpt = a->fp8 ? a->K / 128 : a->K / kBK;
     p.is_fp8 = a->fp8 ? 1 : 0;
-    p.w_scale = a->fp8 ? a->w_scale : nullptr;
+    p.w_scale = a->fp8 == 1 ? a->w_scale : nullptr;
     p.Q = (long long)a->n_tiles * t_tiles * p.kbpt;
     p.epilogue = a->epilogue; p.norm_mode = a->norm_mode; p.norm_eps = a->norm_eps;
     p.is_bf16 = (a->dtype == B200_BF16) ? 1 : 0;
@@ -852,7 +903,7 @@ static int gemm_impl(const b200_gemm_args* a, const b200_tp_args* tp, void* stre
     // loader / MMA-issue threads per SM (measured 280 -> 297 tok/s on Llama-2-7B) and the next
     // kernel's CTAs can start under PDL while this kernel drains.  B200_GEMM_CTAS_PER_SM=1 restores one.
     static const int ctas_per_sm = [] { const char* e = getenv("B200_GEMM_CTAS_PER_SM"); return (e && atoi(e) == 1) ? 1 : 2; }();
-    const int max_grid = sm_count_cached() * ((bn == 16 && !a->fp8) ? ctas_per_sm : 1);
+    const int max_grid = sm_count_cached() * ((bn == 16 && a->fp8 != 1) ? ctas_per_sm : 1);
     int grid = a->grid > 0 ? a->grid : max_grid;
     if (grid > max_grid) grid = max_grid;
     if (a->grid <= 0 && t_tiles == 1) {
@@ -874,7 +925,7 @@ static int gemm_impl(const b200_gemm_args* a, const b200_tp_args* tp, void* stre
     // T=4: 93.7 -> 82.5, T=16: 138 -> 108; T=1: 359.1 -> 362.2 tok/s end of the decode bench).  With tensor parallelism or
     // fp8 weights (T <= 4) the tile's last CTA collects.
     static const int wide_min = [] { const char* e = getenv("B200_LL_WIDE_MIN"); return e ? atoi(e) : 1; }();
-    const bool ll_wide = a->T >= wide_min && a->T <= 16 && !tp && !gather && !a->fp8;
+    const bool ll_wide = a->T >= wide_min && a->T <= 16 && !tp && !gather && a->fp8 != 1;
     if (a->ll_buf && bn == 16 && t_tiles == 1 && (a->T <= 4 || ll_wide) && grid % a->n_tiles == 0 && grid <= kLLMaxCtas) {
         const int parts = grid / a->n_tiles;
         if (parts >= 2 && p.kbpt >= parts && (!ll_wide || parts <= 9)) {
@@ -906,6 +957,13 @@ static int gemm_impl(const b200_gemm_args* a, const b200_tp_args* tp, void* stre
         if (p.ll_words)
             return a->dual ? launch_gemm<16, 1, 0, 1, 1>(p, grid, pdl, stream) : launch_gemm<16, 0, 0, 1, 1>(p, grid, pdl, stream);
         return a->dual ? launch_gemm<16, 1, 0, 0, 1>(p, grid, pdl, stream) : launch_gemm<16, 0, 0, 0, 1>(p, grid, pdl, stream);
+    }
+    if (a->fp8 == 2) {   // MX block-scaled e4m3: the decode-size tiles; split tiles meet through the wide exchange
+        if (bn == 16 && p.ll_words && ll_wide)
+            return a->dual ? launch_gemm<16, 1, 2, 1>(p, grid, pdl, stream) : launch_gemm<16, 0, 2, 1>(p, grid, pdl, stream);
+        if (p.ll_words) { p.ll_words = nullptr; p.ll_parts = 0; }
+        if (bn == 16) return a->dual ? launch_gemm<16, 1, 2>(p, grid, pdl, stream) : launch_gemm<16, 0, 2>(p, grid, pdl, stream);
+        return a->dual ? launch_gemm<32, 1, 2>(p, grid, pdl, stream) : launch_gemm<32, 0, 2>(p, grid, pdl, stream);
     }
     if (a->fp8) {   // only the decode-size tiles are instantiated for e4m3 weights
         if (bn == 16) return a->dual ? launch_gemm<16, 1, 1>(p, grid, pdl, stream) : launch_gemm<16, 0, 1>(p, grid, pdl, stream);

@@ -25,29 +25,41 @@ constexpr int kABytes = kTileM * 128;  // bytes of one packed weight block
 constexpr int kThreads = 192;
 constexpr int kEpiThreads = 128;
 
-template <int BN, int DUAL>
+// MX = 1: block-scaled e4m3 weights (OCP MX: one UE8M0 scale per 32 elements along k).  A k-block is then 128
+// elements (one 128-byte swizzle row) and carries its scale factors behind the weights: 512 bytes per matrix in the
+// order tcgen05.cp expects ((row % 32) * 16 + (row / 32) * 4 + 32-element group), padded to 1 KiB per k-block so that
+// every block stays 1024-byte aligned - weights and scales of a k-block still arrive in ONE bulk copy.
+constexpr int kMxSfBytes = 512;        // scale factors of one 128-row matrix for one k-block
+constexpr int kMxSfPad = 1024;         // scale-factor area of a k-block (1 or 2 matrices)
+constexpr int kMxSfSlots = 4;          // k-blocks whose scale factors can sit in tensor memory at once
+
+template <int BN, int DUAL, int MX = 0>
 struct GemmCfg {
     static constexpr int kAPer = DUAL ? 2 : 1;
-    static constexpr int kBlockA = kABytes * kAPer;       // weight bytes of one k-block
+    static constexpr int kBlockA = kABytes * kAPer + (MX ? kMxSfPad : 0);   // bytes of one k-block of the weight stream
     // One weight-ring stage = one 32 KiB bulk copy.  The single-thread loader and
     // MMA loops pay ~100+ ns of barrier latency per stage, so stages must be big.
     static constexpr int kKps = DUAL ? 1 : 2;              // k-blocks per weight stage
     static constexpr int kStageA = kBlockA * kKps;         // 32768
     static constexpr int kSA = (BN <= 16) ? B200_SA16 : (BN == 256) ? 3 : 4;
-    static constexpr int kGroup = (BN == 16) ? B200_GROUP16 : (BN == 32) ? 2 : 1;  // k-blocks per activation stage
+    static constexpr int kGroup = MX ? 1 : (BN == 16) ? B200_GROUP16 : (BN == 32) ? 2 : 1;  // k-blocks per activation stage
     static constexpr int kSubB = BN * 128;                 // one k-block of activations
     static constexpr int kStageB = kSubB * kGroup;
-    static constexpr int kSB = (BN == 16) ? 3 : (BN == 32) ? 4 : (BN == 64) ? 6 : (BN == 128) ? 4 : 3;
+    static constexpr int kSB = MX ? 3 : (BN == 16) ? 3 : (BN == 32) ? 4 : (BN == 64) ? 6 : (BN == 128) ? 4 : 3;
     static constexpr bool kPrefetch = BN <= 32;            // register double-buffering of the next B stage
     // Back-to-back tcgen05.mma into ONE accumulator serialise on the tensor-pipe latency
     // (~180 cycles each when N is tiny), so narrow tiles rotate the four k-steps of a
     // k-block over independent accumulators that the epilogue adds up.
     static constexpr int kNAcc = (BN <= 32) ? 4 : (BN == 64) ? 2 : 1;
-    static constexpr int kTmemColsRaw = BN * kAPer * kNAcc;
+    // MX: behind the accumulators, kMxSfSlots sets of scale-factor columns (4 per weight matrix + 4 for the activations)
+    static constexpr int kSfCols = MX ? kMxSfSlots * (kAPer * 4 + 4) : 0;
+    static constexpr int kTmemColsRaw = BN * kAPer * kNAcc + kSfCols;
     static constexpr int kTmemCols = kTmemColsRaw <= 32 ? 32 : kTmemColsRaw <= 64 ? 64 : kTmemColsRaw <= 128 ? 128 : kTmemColsRaw <= 256 ? 256 : 512;
     static constexpr int kMinBlocks = (BN <= 16) ? B200_MINBLK16 : 1;
     static constexpr size_t kSmemData = (size_t)kSA * kStageA + (size_t)kSB * kStageB;
-    static constexpr size_t kSmemBytes = kSmemData + 1024 /*align*/ + 1024 /*barriers, stats*/;
+    // MX: + the activations' scale factors of every activation stage (one 512-byte atom per k-block in flight)
+    static constexpr size_t kSfbBytes = MX ? (size_t)kSB * kGroup * kMxSfBytes : 0;
+    static constexpr size_t kSmemBytes = kSmemData + 1024 /*align*/ + 1024 /*barriers, stats*/ + kSfbBytes;
 };
 
 struct GemmParams {

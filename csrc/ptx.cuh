@@ -166,6 +166,45 @@ __device__ __forceinline__ void umma_f8f6f4(uint32_t tmem_d, uint64_t desc_a, ui
         "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
         : "memory");
 }
+// Block-scaled e4m3 x e4m3 -> fp32 (OCP MX): every 32 elements along k carry one UE8M0 scale for A and one for B;
+// the scales sit in tensor memory (tcgen05.cp) and the instruction descriptor names the byte of the 4-byte column
+// that belongs to this k-step.
+__device__ __forceinline__ void umma_mxf8(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc,
+                                          uint32_t accumulate, uint32_t tmem_sfa, uint32_t tmem_sfb) {
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::mxf8f6f4.block_scale.scale_vec::1X [%0], %1, %2, %3, [%5], [%6], p;\n\t"
+        "}\n" ::"r"(tmem_d),
+        "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate), "r"(tmem_sfa), "r"(tmem_sfb)
+        : "memory");
+}
+// 32 rows x 16 bytes of shared memory -> tensor memory lanes 0..31 (replicated into the four lane quarters), four
+// 32-bit columns from `tmem_dst`: the scale-factor copy (SASS UTCCP).
+__device__ __forceinline__ void tmem_cp_32x128b(uint32_t tmem_dst, uint64_t smem_desc) {
+    asm volatile("tcgen05.cp.cta_group::1.32x128b.warpx4 [%0], %1;\n" ::"r"(tmem_dst), "l"(smem_desc) : "memory");
+}
+// Shared-memory matrix descriptor without swizzle, K-major: 8-row x 16-byte core matrices, SBO apart along rows.
+__device__ __forceinline__ uint64_t umma_desc_kmajor_noswizzle(uint32_t smem_addr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+    uint64_t d = 0;
+    d |= (uint64_t)((smem_addr & 0x3FFFF) >> 4);
+    d |= (uint64_t)((lbo_bytes >> 4) & 0x3FFF) << 16;
+    d |= (uint64_t)((sbo_bytes >> 4) & 0x3FFF) << 32;
+    d |= (uint64_t)1 << 46;
+    return d;
+}
+// Instruction descriptor of kind::mxf8f6f4.block_scale, e4m3 operands, UE8M0 scales, K-major A and B.
+__host__ __device__ __forceinline__ uint32_t umma_idesc_mxf8(uint32_t M, uint32_t N, uint32_t a_sf_id, uint32_t b_sf_id) {
+    uint32_t d = 0;
+    d |= (b_sf_id & 3u) << 4;
+    d |= ((N >> 3) & 63u) << 17;
+    d |= 1u << 23;                 // scale format: UE8M0
+    d |= ((M >> 4) & 31u) << 24;
+    d |= (a_sf_id & 3u) << 29;
+    return d;
+}
+
 // Arrive on an mbarrier when all previously issued tcgen05.mma of this thread retire.
 __device__ __forceinline__ void umma_commit(uint64_t* bar) {
     asm volatile(

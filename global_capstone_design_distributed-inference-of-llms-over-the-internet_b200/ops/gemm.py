@@ -156,7 +156,7 @@ def fill_args(x, w, *, out=None, residual=None, epilogue=EPI_NONE, norm_mode=NOR
     a.grid = grid
     a.pdl = 1 if pdl else 0
     a.debug = debug
-    a.fp8 = 1 if w.fp8 else 0
+    a.fp8 = (2 if getattr(w, "mx", False) else 1) if w.fp8 else 0
     a.w_scale = w.scale.data_ptr() if w.scale is not None else None
     a.ll_buf = ws.ll.data_ptr() if ws.ll is not None else None
     a.rstd = rstd.data_ptr() if rstd is not None else None

@@ -39,6 +39,7 @@ class PackedWeight:
     bias: Optional[torch.Tensor] = None
     fp8: bool = False
     scale: Optional[torch.Tensor] = None   # fp8: fp32 [n_tiles*128] (dual: [2 * n_tiles*128], gate then up)
+    mx: bool = False                       # fp8 with OCP-MX block scales (UE8M0 per 32 elements) packed behind each k-block
 
     @property
     def kb_per_tile(self) -> int:
@@ -157,3 +158,72 @@ def dequantize_fp8(w: torch.Tensor) -> torch.Tensor:
     """What the fp8 GEMM effectively multiplies by (tests): per-row quantise -> dequantise."""
     q, scale = _quantize_rows(w)
     return q.float() * scale[:, None]
+
+
+# ----------------------------------------------------------------------------- MX fp8 (opt-in, block-scaled)
+MX_BLOCK = 32            # elements that share one UE8M0 scale
+MX_SF_PAD = 1024         # bytes of scale factors (+ padding) behind the weights of a k-block
+
+
+def _mx_quantize(w: torch.Tensor):
+    """[N, K] (K % 32 == 0) -> (e4m3 values, UE8M0 scale bytes [N, K/32]).  scale = 2^ceil(log2(amax / 448))."""
+    n, k = w.shape
+    blk = w.float().view(n, k // MX_BLOCK, MX_BLOCK)
+    amax = blk.abs().amax(dim=2)
+    m, ex = torch.frexp(amax / FP8_MAX)                     # amax/448 = m * 2^ex, m in [0.5, 1)
+    ex = torch.where(m == 0.5, ex - 1, ex)
+    ex = torch.where(amax > 0, ex, torch.full_like(ex, -127)).clamp(-127, 126)
+    q = (blk * torch.exp2(-ex.float())[:, :, None]).to(torch.float8_e4m3fn).view(n, k)
+    return q, (ex + 127).to(torch.uint8)
+
+
+def mx_dequantize(w: torch.Tensor) -> torch.Tensor:
+    """What the MX GEMM effectively multiplies by (tests): block-quantise -> dequantise, fp32."""
+    n, k = w.shape
+    k_pad = (k + BLOCK_K8 - 1) // BLOCK_K8 * BLOCK_K8
+    wp = w.new_zeros((n, k_pad))
+    wp[:, :k] = w
+    q, sf = _mx_quantize(wp)
+    return (q.float().view(n, k_pad // MX_BLOCK, MX_BLOCK) * torch.exp2(sf.float() - 127)[:, :, None]).view(n, k_pad)[:, :k]
+
+
+def _mx_tiles(w: torch.Tensor):
+    """-> (weights [nt, kb, 128, 128] uint8 swizzled, scale atoms [nt, kb, 512] uint8)."""
+    n, k = w.shape
+    n_pad = (n + TILE_N - 1) // TILE_N * TILE_N
+    k_pad = (k + BLOCK_K8 - 1) // BLOCK_K8 * BLOCK_K8
+    wp = w.new_zeros((n_pad, k_pad))
+    wp[:n, :k] = w
+    q, sf = _mx_quantize(wp)
+    t = _tile8(q)                                                   # [nt, kb, 128, 128]
+    nt, kb = t.shape[0], t.shape[1]
+    # scale atom of a (tile, k-block): byte (row % 32) * 16 + (row / 32) * 4 + group  <- sf[row, kb*4 + group]
+    a = sf.view(nt, 4, 32, kb, 4)                                   # [tile, row/32, row%32, kb, group]
+    atom = torch.zeros(nt, kb, 32, 16, dtype=torch.uint8, device=w.device)
+    atom.view(nt, kb, 32, 4, 4).copy_(a.permute(0, 3, 2, 1, 4))     # [tile, kb, row%32, row/32, group]
+    return t, atom.view(nt, kb, 512)
+
+
+def _mx_assemble(mats, atoms) -> torch.Tensor:
+    """k-block stream: [weights of each matrix (16 KiB)] [512 B of scales per matrix] [pad to 1 KiB]."""
+    nt, kb = mats[0].shape[0], mats[0].shape[1]
+    w = torch.stack([m.reshape(nt, kb, TILE_N * BLOCK_K8) for m in mats], dim=2).reshape(nt, kb, -1)
+    sf = torch.zeros(nt, kb, MX_SF_PAD, dtype=torch.uint8, device=w.device)
+    for i, a in enumerate(atoms):
+        sf[:, :, i * 512:(i + 1) * 512] = a
+    return torch.cat((w, sf), dim=2).contiguous().reshape(-1)
+
+
+def pack_weight_mx(w: torch.Tensor, bias: Optional[torch.Tensor] = None) -> PackedWeight:
+    """Block-scaled (OCP MX) e4m3 copy of ``w`` for ``tcgen05.mma.kind::mxf8f6f4.block_scale``."""
+    n, k = w.shape
+    t, atom = _mx_tiles(w)
+    return PackedWeight(_mx_assemble([t], [atom]), n, k, t.shape[1] * BLOCK_K8, t.shape[0], False,
+                        None if bias is None else bias.contiguous(), True, None, True)
+
+
+def pack_dual_mx(w_gate: torch.Tensor, w_up: torch.Tensor) -> PackedWeight:
+    n, k = w_gate.shape
+    g, ag = _mx_tiles(w_gate)
+    u, au = _mx_tiles(w_up)
+    return PackedWeight(_mx_assemble([g, u], [ag, au]), n, k, g.shape[1] * BLOCK_K8, g.shape[0], True, None, True, None, True)

@@ -94,16 +94,17 @@ class NativeSpan:
         self.cfg, self.device, self.dtype = cfg, torch.device(device), dtype
         self.kv_capacity, self.max_batch, self.max_chunk = kv_capacity, min(max_batch, MAX_DECODE_BATCH), max_chunk
         self.use_graphs = use_graphs
-        if weight_format not in ("native", "fp8"):
-            raise ValueError("weight_format must be 'native' (fp16/bf16) or 'fp8'")
-        if weight_format == "fp8" and not cfg.is_llama:
+        if weight_format not in ("native", "fp8", "mxfp8"):
+            raise ValueError("weight_format must be 'native' (fp16/bf16), 'fp8' (e4m3, one scale per row) or "
+                             "'mxfp8' (e4m3 with OCP-MX block scales)")
+        if weight_format != "native" and not cfg.is_llama:
             raise ValueError("fp8 weights are implemented for RMSNorm (Llama-family) models")
         self.weight_format = weight_format
-        fp8 = weight_format == "fp8"
+        fp8 = weight_format != "native"
         if fp8:
             self.max_chunk = max_chunk = min(max_chunk, G.MAX_FUSED_NORM_TOKENS)   # fp8 GEMM quantises <= 32 tokens per call
-        pack_w = packing.pack_weight_fp8 if fp8 else packing.pack_weight
-        pack_d = packing.pack_dual_fp8 if fp8 else packing.pack_dual
+        pack_w = {"native": packing.pack_weight, "fp8": packing.pack_weight_fp8, "mxfp8": packing.pack_weight_mx}[weight_format]
+        pack_d = {"native": packing.pack_dual, "fp8": packing.pack_dual_fp8, "mxfp8": packing.pack_dual_mx}[weight_format]
         self.pdl = _pdl_default() if pdl is None else pdl
         self.l2_prefetch_mb = _l2_prefetch_default()
         self._prefill_plans = {}

@@ -106,7 +106,10 @@ typedef struct b200_gemm_args {
     int32_t grid;         /* 0 = one CTA per SM */
     int32_t pdl;          /* 1 = launch with programmatic stream serialization */
     int32_t debug;        /* 0 in production; experiment switches, see csrc/gemm.cu */
-    int32_t fp8;          /* 1 = w_packed holds e4m3 weights (pack_weight_fp8), T <= 32, K % 128 == 0 */
+    int32_t fp8;          /* 1 = e4m3 weights with one scale per output row (pack_weight_fp8, needs w_scale);
+                             2 = OCP-MX: e4m3 weights with one UE8M0 scale per 32 elements along k packed behind every
+                             k-block (pack_weight_mx), activations block-quantised on the fly,
+                             tcgen05.mma.kind::mxf8f6f4.block_scale with the scales in tensor memory.  T <= 32, K % 128 == 0 */
     const float* w_scale; /* fp8: per-output-row dequantisation scale, [n_tiles*128] (dual: gate rows then up rows) */
     /* Optional L2 warm-up for the kernels that follow in the stream (b200_gemm only): once a CTA has issued
      * its last weight load it asks the L2 for its share of up to two byte ranges (cp.async.bulk.prefetch.L2),

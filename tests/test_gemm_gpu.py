@@ -182,6 +182,70 @@ def test_gemm_fp8_swiglu_dual():
     _close(out, ref, dtype)
 
 
+def _mx_emulate_act(xn):
+    """OCP-MX round trip of activations: one power-of-two scale per 32 elements, e4m3 values (the kernel's rule)."""
+    from petals_b200.ops import packing
+
+    return packing.mx_dequantize(xn)
+
+
+@pytest.mark.parametrize("T", [1, 3, 16, 27])
+@pytest.mark.parametrize("norm", [False, True])
+def test_gemm_mxfp8_block_scaled(T, norm):
+    """tcgen05.mma.kind::mxf8f6f4.block_scale: e4m3 weights and activations, UE8M0 scales per 32 elements in tensor
+    memory.  Checked against an fp32 matmul of the block-quantised operands (same quantisation rule), and against the
+    unquantised product within the quantisation error."""
+    from petals_b200.ops import gemm, packing
+
+    dtype = torch.bfloat16
+    torch.manual_seed(31 + T)
+    N, K = 1024, 2048
+    x = (torch.randn(T, K, device="cuda") * 1.5).to(dtype)
+    x[:, ::7] *= 8.0                                               # outliers: what block scales are for
+    w = (torch.randn(N, K, device="cuda") / K ** 0.5).to(dtype)
+    w[::5] *= 4.0
+    g = (1 + 0.1 * torch.randn(K, device="cuda")).to(dtype)
+    res = torch.randn(T, N, device="cuda").to(dtype)
+    pw = packing.pack_weight_mx(w)
+    assert pw.mx and pw.nbytes == (N // 128) * (K // 128) * (16384 + 1024)
+    xf = x.float()
+    if norm:
+        rstd = torch.rsqrt(xf.pow(2).mean(-1, keepdim=True) + 1e-5)
+        xa = _mx_emulate_act(xf * g.float()) * rstd
+        out = gemm.linear(x, pw, norm_mode=gemm.NORM_RMS, norm_w=g, norm_eps=1e-5, residual=res)
+    else:
+        xa = _mx_emulate_act(xf)
+        out = gemm.linear(x, pw, residual=res)
+    torch.cuda.synchronize()
+    ref = (xa @ packing.mx_dequantize(w).t()).to(dtype).float() + res.float()
+    _close(out, ref, dtype)
+    exact = ((xf * g.float() * rstd if norm else xf) @ w.float().t()) + res.float()
+    rel = (out.float() - exact).abs().max().item() / exact.abs().max().item()
+    assert rel < 0.06, f"MX quantisation error {rel:.3f} out of range"
+    out2 = gemm.linear(x, pw, norm_mode=gemm.NORM_RMS, norm_w=g, norm_eps=1e-5, residual=res) if norm else gemm.linear(x, pw, residual=res)
+    torch.cuda.synchronize()
+    assert torch.equal(out, out2)
+
+
+def test_gemm_mxfp8_swiglu_dual():
+    from petals_b200.ops import gemm, packing
+
+    dtype = torch.float16
+    torch.manual_seed(34)
+    N, K, T = 1408, 1024, 3
+    x = (torch.randn(T, K, device="cuda")).to(dtype)
+    wg = (torch.randn(N, K, device="cuda") / K ** 0.5).to(dtype)
+    wu = (torch.randn(N, K, device="cuda") / K ** 0.5).to(dtype)
+    pw = packing.pack_dual_mx(wg, wu)
+    out = gemm.linear(x, pw)
+    torch.cuda.synchronize()
+    xa = _mx_emulate_act(x.float())
+    gq = (xa @ packing.mx_dequantize(wg).t()).to(dtype).float()
+    uq = (xa @ packing.mx_dequantize(wu).t()).to(dtype).float()
+    ref = torch.nn.functional.silu(gq).to(dtype).float() * uq
+    _close(out, ref, dtype)
+
+
 def test_gemm_l2_prefetch_hint_changes_nothing():
     """The optional L2 warm-up ranges are a pure hint: same bits out, odd sizes and offsets accepted."""
     from petals_b200.ops import gemm, packing
