@@ -1054,6 +1054,14 @@ extern "C" int b200_gemm_static_scratch(const b200_gemm_args* a, void* stream_) 
     if (sm_count_cached() > kStaticMaxCtas)
         return fail(B200_ELIMIT, "b200_gemm_static_scratch: %d SMs exceed the %d CTAs the built-in workspace holds",
                     sm_count_cached(), kStaticMaxCtas);
+    // Argument errors are reported before anything is put on the stream (the checks b200_gemm would make).
+    if (!a->w_packed || !a->x || !a->out) return fail(B200_EINVAL, "b200_gemm_static_scratch: null pointer argument");
+    if (a->T <= 0 || a->N <= 0 || a->K <= 0 || (a->K % kBK) != 0)
+        return fail(B200_EINVAL, "b200_gemm_static_scratch: bad sizes T=%d N=%d K=%d (K must be a multiple of 64)", a->T, a->N, a->K);
+    if (a->n_tiles * kTileM < a->N) return fail(B200_EINVAL, "b200_gemm_static_scratch: n_tiles=%d does not cover N=%d", a->n_tiles, a->N);
+    if ((a->ldx % 8) != 0 || (reinterpret_cast<uintptr_t>(a->x) & 15) != 0)
+        return fail(B200_EINVAL, "b200_gemm_static_scratch: x must be 16-byte aligned with ldx %% 8 == 0");
+    if (a->chain.seq) return fail(B200_EINVAL, "b200_gemm_static_scratch: flag chains need the caller's own buffers (b200_gemm)");
     void* ws = nullptr;
     const int rc = static_ws_for_current_device(&ws);
     if (rc != B200_OK) return rc;
@@ -1063,6 +1071,8 @@ extern "C" int b200_gemm_static_scratch(const b200_gemm_args* a, void* stream_) 
     B200_CUDA_CHECK(cudaMemsetAsync(ws, 0, (size_t)n_units * sizeof(int), stream));
     b200_gemm_args local = *a;
     local.grid = sm_count_cached();   // one CTA per SM: the built-in workspace has slots for kStaticMaxCtas CTAs
+    local.pdl = 0;                    // the node before the kernel is the memset above: nothing to overlap with
+    local.ll_buf = nullptr;           // the partial tiles meet in the built-in array only
     local.counters = static_cast<int32_t*>(ws);
     local.scratch = reinterpret_cast<float*>(static_cast<unsigned char*>(ws) + kStaticCounterBytes);
     return b200_gemm(&local, stream_);

@@ -87,12 +87,13 @@ def _name_seed(name: str, seed: int) -> int:
 
 
 class RandomSource:
-    """Deterministic random tensors keyed by (seed, HF tensor name).
+    """Deterministic random tensors keyed by (seed, HF tensor name), the SAME values on every device.
 
-    Values are generated on the CPU generator in fp32 for small tensors (identical
-    on every machine) and directly on the target CUDA device for big ones
-    (identical on every GPU of the same architecture, which is what a pipeline of
-    B200 stages needs; a 7B model would take minutes on the CPU generator).
+    Small tensors come from the CPU generator.  Big ones (a 7B model would take minutes there) are produced on the
+    target device from a counter-based generator written with integer tensor ops only (a 32-bit mixing hash of the
+    element index and the name seed, four uniforms summed per element), so a CPU oracle, a ``--use_cpu_offload`` stage
+    and GPU stages of one pipeline agree on the model bit for bit without exchanging files (torch's own CUDA and CPU
+    generators do not produce the same stream).
     """
 
     CPU_LIMIT = 1 << 22
@@ -105,22 +106,48 @@ class RandomSource:
     def has(self, name: str) -> bool:
         return name in self.shapes
 
+    @staticmethod
+    def _hash32(x: torch.Tensor) -> torch.Tensor:
+        """lowbias32-style integer mix on int64 tensors holding 32-bit values."""
+        M = 0xFFFFFFFF
+        x = (x ^ (x >> 16)) & M
+        x = (x * 0x7FEB352D) & M
+        x = (x ^ (x >> 15)) & M
+        x = (x * 0x846CA68B) & M
+        return (x ^ (x >> 16)) & M
+
+    def _counter_randn(self, numel: int, key: int, device) -> torch.Tensor:
+        """Approximately normal values from integer arithmetic only (bit-identical on every device): four 24-bit
+        uniforms per element from a mixing hash of (element index, key), summed (Irwin-Hall), centred and scaled to
+        unit variance.  No transcendental function, so no device-dependent rounding."""
+        out = torch.empty(numel, dtype=torch.float32, device=device)
+        step = 1 << 24
+        k1, k2 = key & 0xFFFFFFFF, (key >> 32) & 0x7FFFFF
+        for lo in range(0, numel, step):
+            idx = torch.arange(lo, min(numel, lo + step), dtype=torch.int64, device=device)
+            h = self._hash32((idx & 0xFFFFFFFF) ^ k1 ^ (((idx >> 32) * 0x9E3779B1) & 0xFFFFFFFF))
+            total = torch.zeros_like(idx)
+            for j in range(4):
+                h = self._hash32((h + 0x6A09E667 + k2 + j) & 0xFFFFFFFF)
+                total += h >> 8                                   # 24 random bits
+            # sum of four U[0, 2^24): mean 2 * 2^24, variance 4 * 2^48 / 12
+            out[lo:lo + idx.numel()] = (total - (2 << 24)).to(torch.float32) * (3.0 ** 0.5 / float(1 << 24))
+        return out
+
     def get(self, name: str) -> torch.Tensor:
         shape = self.shapes[name]
         numel = 1
         for s in shape:
             numel *= s
         is_norm_w = name.endswith(("layernorm.weight", "norm.weight", "ln_1.weight", "ln_2.weight", "ln_f.weight"))
-        is_bias = name.endswith(".bias")
-        use_cuda = self.device.type == "cuda" and numel > self.CPU_LIMIT
-        dev = self.device if use_cuda else torch.device("cpu")
-        g = torch.Generator(device=dev)
-        g.manual_seed(_name_seed(name, self.seed))
-        t = torch.randn(shape, generator=g, device=dev, dtype=torch.float32)
+        if numel > self.CPU_LIMIT:
+            t = self._counter_randn(numel, _name_seed(name, self.seed), self.device).view(shape)
+        else:
+            g = torch.Generator(device="cpu")
+            g.manual_seed(_name_seed(name, self.seed))
+            t = torch.randn(shape, generator=g, dtype=torch.float32)
         if is_norm_w:
             t = 1.0 + 0.05 * t
-        elif is_bias:
-            t = 0.02 * t
         else:
             t = 0.02 * t
         return t

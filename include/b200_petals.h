@@ -207,7 +207,8 @@ int b200_tp_allreduce_nvls(const b200_nvls_args* args, void* stream);
  * library image, resolved per device on the first call made on that device (make that call before
  * starting a stream capture).  Limits: T <= 16 tokens, <= 2048 output tiles, <= 160 CTAs; beyond
  * them the call returns B200_ELIMIT.  Calls share the one array: keep them on one stream — kernels
- * from two calls that overlap on the GPU race on it.  Performs no cudaMalloc/cudaFree. */
+ * from two calls that overlap on the GPU race on it.  args->pdl and args->ll_buf are ignored.
+ * Performs no cudaMalloc/cudaFree. */
 #define B200_GEMM_STATIC_MAX_TOKENS 16
 int b200_gemm_static_scratch(const b200_gemm_args* args, void* stream);
 

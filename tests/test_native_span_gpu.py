@@ -132,3 +132,50 @@ def test_flag_chained_decode_is_bit_identical(name, graphs, persistent, monkeypa
     ha = chain.decode_loop(ka[:2], ids[:2].clone(), 5).clone()
     hb = plain.decode_loop(kb[:2], ids[:2].clone(), 5).clone()
     assert torch.equal(ha, hb)
+
+
+def test_real_shape_layer_elementwise_against_fp32_oracle():
+    """One decoder block with Llama-2-7B's real shapes (H = 4096, 32 heads of 128, I = 11008): the native kernels'
+    hidden states against the fp32 torch restatement on the same (16-bit rounded) weights, ELEMENT BY ELEMENT
+    (rtol / atol, not a max-normalised error) - prefill of a chunk, then single-token steps."""
+    from dataclasses import replace
+
+    from petals_b200.models.config import resolve_config
+    from petals_b200.models.torch_ref import TorchSpan
+    from petals_b200.runtime.kv_cache import KVCacheManager
+    from petals_b200.runtime.native_span import NativeSpan
+    from petals_b200.weights.loader import load_span
+
+    dtype = torch.float16
+    cfg = replace(resolve_config("llama-2-7b"), n_layers=1)
+    dev = torch.device("cuda")
+    w16 = load_span("llama-2-7b", cfg, 0, 1, need_embed=False, need_head=False, dtype=dtype, device=dev, seed=1)
+    w32 = {k: (v.float() if torch.is_tensor(v) else v) for k, v in w16.items() if k != "layers"}
+    w32["layers"] = [{k: v.float() for k, v in L.items()} for L in w16["layers"]]
+    ref = TorchSpan(cfg, w32, dev, torch.float32)
+    nat = NativeSpan(cfg, w16, dev, dtype, kv_capacity=256, max_batch=2, max_chunk=128, free_source_weights=False)
+    kr = KVCacheManager(1, cfg.n_kv_heads, cfg.head_dim, torch.float32, dev).allocate("a", 256)
+    kn = KVCacheManager(1, cfg.n_kv_heads, cfg.head_dim, dtype, dev).allocate("a", 256)
+    torch.manual_seed(3)
+    x = (torch.randn(100, cfg.hidden, device=dev) * 0.7).to(dtype)
+    want = ref.forward(x[:96].float(), kr)
+    got = nat.prefill(kn, h_in=x[:96])
+    atol = 0.02 * want.abs().mean().item()
+    torch.testing.assert_close(got.float(), want, rtol=2e-2, atol=atol)
+    for t in range(96, 100):
+        want = ref.forward(x[t:t + 1].float(), kr)
+        got = nat.decode([kn], h_in=x[t:t + 1])
+        torch.testing.assert_close(got.float(), want, rtol=2e-2, atol=atol)
+
+
+def test_random_weights_are_the_same_on_cpu_and_gpu():
+    """Large random-init tensors come from an integer-only counter generator: bit-identical wherever they are made."""
+    from petals_b200.models.config import resolve_config
+    from petals_b200.weights.loader import RandomSource
+
+    cfg = resolve_config("llama-2-7b")
+    name = "model.layers.0.self_attn.q_proj.weight"            # 16.8M elements: beyond the CPU-generator limit
+    a = RandomSource(cfg, 7, "cpu").get(name)
+    b = RandomSource(cfg, 7, "cuda").get(name)
+    assert b.is_cuda and torch.equal(a, b.cpu())
+    assert abs(a.std().item() - 0.02) < 2e-4

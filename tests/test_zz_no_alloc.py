@@ -68,6 +68,11 @@ def test_static_scratch_matches_regular_entry_point(T, N, K, dual):
     for out in outs:
         err = (out.float() - ref.float()).abs().max().item()
         assert err / scale < 2e-2, f"rel err {err / scale:.3g}"
+    if not dual:   # and against plain torch in fp32, so that the oracle is not only this library's other entry point
+        w = packing.unpack_weight(pw).float()
+        want = (x.float() @ w.t()).to(dtype).float() + res.float()
+        err = (outs[1].float() - want).abs().max().item()
+        assert err / (want.abs().max().item() + 1e-6) < 2e-2
 
 
 def test_static_scratch_rejects_oversize():
