@@ -10,8 +10,15 @@
 // Persistent grid, tiles assigned round-robin; tiles that share a weight block run on neighbouring
 // CTAs at the same time, so the weight block is read from HBM once and from L2 afterwards.
 // The decode-size kernel (gemm.cu) stages activations with the worker warps instead (fused norm,
-// fp8 quantisation) and splits K across CTAs; neither is needed once T fills the tile.
+// fp8 quantisation) and splits K across CTAs stream-K style.
+//
+// Short prompts (few token tiles): a Llama-2-7B GEMM then has only 32-96 output tiles for 148 SMs and every CTA
+// would stream a whole tile's weights alone (~1-3 MB at the ~90 GB/s one CTA reaches).  Such launches split K:
+// every tile is worked on by `ksplit` units (k-ranges), each unit leaves its fp32 partial tile in the scratch
+// buffer and takes a ticket; the unit that takes the tile's last ticket adds the partials in k order (bit-reproducible)
+// and runs the epilogue.  Nobody waits for anybody.
 #include <cuda.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include "gemm_core.cuh"
@@ -69,7 +76,9 @@ gemm_prefill_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap
     const uint32_t tmem_base = *tmem_slot;
     pdl_launch_dependents();
 
-    const int units = p.n_tiles * p.t_tiles;
+    const int P = p.ll_parts > 1 ? p.ll_parts : 1;            // k-splits per tile (host: prefill_ksplit)
+    const int units = p.n_tiles * p.t_tiles * P;
+    volatile int* s_last = reinterpret_cast<volatile int*>(tmem_slot + 1);
 
     if (warp == 0) {
         // ------------------------------------------------------------ TMA producer
@@ -77,9 +86,11 @@ gemm_prefill_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap
         int s = 0;
         uint32_t ph = 0;
         for (int u = blockIdx.x; u < units; u += gridDim.x) {
-            const int n_tile = u / p.t_tiles, t_tile = u - n_tile * p.t_tiles;
+            const int tu = u / P, part = u - tu * P;
+            const int n_tile = tu / p.t_tiles, t_tile = tu - n_tile * p.t_tiles;
             const uint8_t* wt = p.w + (size_t)n_tile * p.kbpt * Cfg::kBytesA;
-            for (int kb = 0; kb < p.kbpt; ++kb) {
+            const int kb0 = part * p.kbpt / P, kb1 = (part + 1) * p.kbpt / P;
+            for (int kb = kb0; kb < kb1; ++kb) {
                 mbar_wait(&empty[s], ph ^ 1);
                 if (elect_one()) {
                     uint8_t* st = smem + (size_t)s * Cfg::kStage;
@@ -102,7 +113,9 @@ gemm_prefill_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap
             mbar_wait(&acc_empty[buf], ((it >> 1) & 1) ^ 1);
             tc_fence_after();
             const uint32_t d0 = tmem_base + buf * Cfg::kAccCols;
-            for (int kb = 0; kb < p.kbpt; ++kb) {
+            const int part = u % P;
+            const int kb0 = part * p.kbpt / P, kb1 = (part + 1) * p.kbpt / P;
+            for (int kb = kb0; kb < kb1; ++kb) {
                 mbar_wait(&full[s], ph);
                 tc_fence_after();
                 if (elect_one()) {
@@ -114,7 +127,7 @@ gemm_prefill_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap
 #pragma unroll
                         for (int k = 0; k < kBK / 16; ++k)
                             umma_f16(d0 + a * BN, adesc + (uint64_t)(k * 2), bdesc + (uint64_t)(k * 2), idesc,
-                                     (kb > 0 || k > 0) ? 1u : 0u);
+                                     (kb > kb0 || k > 0) ? 1u : 0u);
                     }
                     umma_commit(&empty[s]);
                 }
@@ -131,13 +144,65 @@ gemm_prefill_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap
         const bool vec_ok = !p.out_fp32 && (p.N % 8 == 0) && (p.ldo % 8 == 0) && (!p.residual || p.ldr % 8 == 0);
         float* my_smem = epi_smem + (warp - 2) * 512;
         uint32_t it = 0;
+        const int e = threadIdx.x - 64;
         for (int u = blockIdx.x; u < units; u += gridDim.x, ++it) {
-            const int n_tile = u / p.t_tiles, t_tile = u - n_tile * p.t_tiles;
+            const int tu = u / P;
+            const int n_tile = tu / p.t_tiles, t_tile = tu - n_tile * p.t_tiles;
             const int buf = it & 1;
             mbar_wait(&acc_full[buf], (it >> 1) & 1);
             tc_fence_after();
             const int t_live = min(BN, p.T - t_tile * BN);
             const uint32_t taddr0 = tmem_base + buf * Cfg::kAccCols + ((uint32_t)(lg * 32) << 16);
+            if (P > 1) {
+                // ---- split K: leave the fp32 partial of this unit in the scratch buffer, take a ticket
+                constexpr size_t kTileFloats = (size_t)APER * BN * kTileM;
+                float* mine = p.scratch + (size_t)u * kTileFloats;
+#pragma unroll 1
+                for (int c = 0; c * 16 < t_live; ++c) {
+                    uint32_t rg[16], ru[16];
+                    tmem_ld16(taddr0 + c * 16, rg);
+                    if (DUAL) tmem_ld16(taddr0 + BN + c * 16, ru);
+                    tmem_ld_wait();
+#pragma unroll
+                    for (int j = 0; j < 16; ++j) {
+                        mine[(size_t)(c * 16 + j) * kTileM + row] = __uint_as_float(rg[j]);
+                        if (DUAL) mine[(size_t)(BN + c * 16 + j) * kTileM + row] = __uint_as_float(ru[j]);
+                    }
+                }
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&acc_empty[buf]);     // the tensor core may have the buffer back
+                named_bar_sync(1, kEpiThreads);
+                if (e == 0) {
+                    int old;
+                    asm volatile("atom.acq_rel.gpu.global.add.s32 %0, [%1], %2;\n" : "=r"(old) : "l"(&p.counters[tu]), "r"(1) : "memory");
+                    *s_last = (old + 1 == P) ? 1 : 0;
+                }
+                named_bar_sync(1, kEpiThreads);
+                if (*s_last) {
+                    // last unit of the tile: add the partials in k order and finish the tile
+                    const float* base = p.scratch + (size_t)tu * P * kTileFloats;
+#pragma unroll 1
+                    for (int c = 0; c * 16 < t_live; ++c) {
+                        float vg[16], vu[16];
+#pragma unroll
+                        for (int j = 0; j < 16; ++j) { vg[j] = 0.f; vu[j] = 0.f; }
+                        for (int q = 0; q < P; ++q) {
+                            const float* src = base + (size_t)q * kTileFloats;
+#pragma unroll
+                            for (int j = 0; j < 16; ++j) {
+                                vg[j] += __ldcg(src + (size_t)(c * 16 + j) * kTileM + row);
+                                if (DUAL) vu[j] += __ldcg(src + (size_t)(BN + c * 16 + j) * kTileM + row);
+                            }
+                        }
+                        if (vec_ok) epilogue_store_chunk_vec<BN, DUAL>(p, n_tile, t_tile, lane, lg, c, vg, vu, my_smem);
+                        else epilogue_store_chunk<BN, DUAL>(p, n_tile, t_tile, row, c, vg, vu, nullptr);
+                    }
+                    if (e == 0) p.counters[tu] = 0;      // clean for the next launch
+                }
+                named_bar_sync(1, kEpiThreads);           // s_last is rewritten by the next unit
+                continue;
+            }
 #pragma unroll 1
             for (int c = 0; c * 16 < t_live; ++c) {
                 uint32_t rg[16], ru[16];
@@ -223,9 +288,27 @@ extern "C" int b200_gemm_prefill(const b200_gemm_args* a, void* stream_) {
                            CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) return fail(B200_ECUDA, "b200_gemm_prefill: cuTensorMapEncodeTiled failed (%d)", (int)r);
 
-    const int units = p.n_tiles * p.t_tiles;
     int grid = a->grid > 0 ? a->grid : sm_count_cached();
     if (grid > sm_count_cached()) grid = sm_count_cached();
+    // Few tiles for the SMs (short prompts): split K over up to 4 units per tile when that fills the grid better
+    // (see the kernel comment); needs the caller's scratch buffer and zeroed counters like b200_gemm.
+    const int tiles = p.n_tiles * p.t_tiles;
+    int ksplit = 1;
+    static const int split_on = [] { const char* e = getenv("B200_PREFILL_KSPLIT"); return e ? atoi(e) : 1; }();
+    if (split_on && a->scratch && a->counters && tiles < grid) {
+        double best = (double)tiles / (double)(((tiles + grid - 1) / grid) * grid);
+        for (int q = 2; q <= 4; ++q) {
+            if (p.kbpt / q < 8) break;
+            const int un = tiles * q;
+            const double eff = (double)un / (double)(((un + grid - 1) / grid) * grid);
+            const size_t need = (size_t)un * (a->dual ? 2 : 1) * bn * kTileM * sizeof(float);
+            if (eff > best + 0.05 && need <= (size_t)b200_gemm_scratch_bytes(a->T)) { best = eff; ksplit = q; }
+        }
+    }
+    p.ll_parts = ksplit;
+    p.scratch = a->scratch;
+    p.counters = a->counters;
+    const int units = tiles * ksplit;
     if (grid > units) grid = units;
     cudaStream_t stream = static_cast<cudaStream_t>(stream_);
     if (a->dual) return launch_prefill<128, 1>(p, tmap, grid, a->pdl != 0, stream);

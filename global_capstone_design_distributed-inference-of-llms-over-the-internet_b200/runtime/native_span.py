@@ -89,7 +89,7 @@ class NativeSpan:
                  kv_capacity: int = 2048, max_batch: int = 8, max_chunk: int = 512, attn_splits: int = 0,
                  use_graphs: bool = True, pdl: Optional[bool] = None, free_source_weights: bool = True,
                  weight_format: str = "native",
-                 head_rows: Optional[tuple] = None):
+                 head_rows: Optional[tuple] = None, streamed_layers: int = 0):
         assert dtype in (torch.float16, torch.bfloat16), "native path runs fp16/bf16"
         self.cfg, self.device, self.dtype = cfg, torch.device(device), dtype
         self.kv_capacity, self.max_batch, self.max_chunk = kv_capacity, min(max_batch, MAX_DECODE_BATCH), max_chunk
@@ -145,7 +145,9 @@ class NativeSpan:
             self.scale = 1.0 / math.sqrt(c.head_dim)
             self.norm_mode = G.NORM_RMS if c.is_llama else G.NORM_LAYER
             self.mlp_epi = G.EPI_SWIGLU if c.is_llama else G.EPI_GELU_TANH
-            nl = len(self.layers)
+            # streamed_layers: blocks that are NOT resident (runtime/offload.py streams them through two device slots)
+            self.streamed_layers = int(streamed_layers)
+            nl = len(self.layers) + self.streamed_layers
             Tm = max(self.max_chunk, self.max_batch)
             mk = lambda *s, dt=dtype: torch.empty(*s, dtype=dt, device=self.device)  # noqa: E731
             self.h_a, self.h_b, self.xn = mk(Tm, c.hidden), mk(Tm, c.hidden), mk(Tm, c.hidden)
@@ -199,7 +201,11 @@ class NativeSpan:
     # ------------------------------------------------------------------ pieces
     @property
     def n_layers(self) -> int:
-        return len(self.layers)
+        return len(self.layers) + self.streamed_layers
+
+    def _iter_layers(self):
+        """(index, packed weights) of every block in order; a span that streams blocks from the host overrides this."""
+        return enumerate(self.layers)
 
     def weight_bytes(self) -> int:
         n = sum(P[k].nbytes for P in self.layers for k in ("qkv", "o", "mlp_in", "down"))
@@ -267,12 +273,14 @@ class NativeSpan:
         mb = self.l2_prefetch_mb if T <= 32 else None
         n = len(self.layers)
         M = 1 << 20
-        chain = self._chain_on(T)
+        chain = self._chain_on(T) and not self.streamed_layers
+        if self.streamed_layers:
+            mb = None                       # the next block's weights are not where a prefetch hint could point
         if chain and CHAIN_KERNEL and self._chain_kernel_ok():
             return self._decode_layers_chain_kernel(T, h, other, with_head)
         if chain:
             return self._decode_layers_chain(T, h, other, mb)
-        for li, P in enumerate(self.layers):
+        for li, P in self._iter_layers():
             qkv, attn, act, h2 = self.qkv[:T], self.attn[:T], self.act[:T], other[:T]
             pf = [None] * 4
             if mb:
@@ -764,13 +772,14 @@ class NativeSpan:
             other = self.h_b
             fused = n <= G.MAX_FUSED_NORM_TOKENS
             ln = not c.is_llama
-            if not fused and self.tp_mode is None and self.weight_format == "native" and self._planned_prefill:
+            if (not fused and self.tp_mode is None and self.weight_format == "native" and self._planned_prefill
+                    and not self.streamed_layers):
                 self._prefill_chunk_planned(kv, n, p0)
                 if out is not None:
                     out[c0:c0 + n].copy_(h, non_blocking=True)
                 last_h = h[n - 1:n]
                 continue
-            for li, P in enumerate(self.layers):
+            for li, P in self._iter_layers():
                 qkv, attn, act, h2 = self.qkv[:n], self.attn[:n], self.act[:n], other[:n]
                 if fused:
                     G.linear(h, P["qkv"], out=qkv, norm_mode=self.norm_mode, norm_w=P["ln1_w"], norm_b=P["ln1_b"],

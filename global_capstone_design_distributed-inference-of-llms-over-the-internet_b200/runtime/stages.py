@@ -85,10 +85,16 @@ class _StageBase(torch.nn.Module):
         self.keep_layers_on_gpu = keep_layers_on_gpu
         self.use_cpu_offload = full.use_cpu_offload
         self.kv_capacity = kv_capacity
-        native_ok = self.device.type == "cuda" and self.dtype in (torch.float16, torch.bfloat16) \
-            and not full.use_cpu_offload
+        native_ok = self.device.type == "cuda" and self.dtype in (torch.float16, torch.bfloat16)
         self.backend = backend or ("native" if native_ok else "torch")
-        if self.backend == "native":
+        if self.backend == "native" and full.use_cpu_offload:
+            # weights stay in pinned host memory (packed), two device slots stream them under the sm_100a kernels
+            from .offload import make_offloaded_native_span
+
+            self.span = make_offloaded_native_span(self.cfg, full.weights, self.device, self.dtype,
+                                                   keep_layers_on_gpu=keep_layers_on_gpu, kv_capacity=kv_capacity,
+                                                   max_batch=max_batch)
+        elif self.backend == "native":
             from .native_span import NativeSpan
 
             self.span = NativeSpan(self.cfg, full.weights, self.device, self.dtype, kv_capacity=kv_capacity,

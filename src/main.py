@@ -104,7 +104,8 @@ def run_rank0(args, device, splits, dht: Optional[DHT] = None):
                       routing=("module" if args.use_load_balancing else "stage"), model_name=args.model,
                       total_blocks=total_blocks, start_block=stage0_end, request_timeout=args.request_timeout,
                       repetition_penalty=getattr(args, "repetition_penalty", None), dht=dht,
-                      push=getattr(args, "push", False), stream=getattr(args, "stream", False))
+                      push=getattr(args, "push", False), stream=getattr(args, "stream", False),
+                      device_handoff=getattr(args, "device_handoff", False))
     session_id = str(uuid4())
     t_prefill_start = time.perf_counter()
     hidden, _ = s0(input_ids, None, None, kv0)
@@ -529,6 +530,10 @@ def build_parser() -> argparse.ArgumentParser:
     p.add_argument("--max_batch", type=int, default=16,
                    help="server: single-token requests of different sessions merged into one decode step (1 = off)")
     p.add_argument("--no_throughput_cache", action="store_true", help="server: re-measure the throughput on every start")
+    p.add_argument("--device_handoff", action="store_true",
+                   help="client: servers on GPUs of this machine exchange hidden states device to device (CUDA IPC + "
+                        "NVLink peer copies); the RPC messages to them carry a descriptor instead of the tensor")
+    p.add_argument("--gpu", type=int, default=None, help="CUDA device index of this process (default: LOCAL_RANK or 0)")
     p.add_argument("--inbox", action="store_true",
                    help="in-box mode: launch with torchrun (one process per GPU); stages hand hidden states over "
                         "NCCL p2p instead of TCP RPC; --splits gives the stage boundaries, --stage is ignored")
@@ -541,7 +546,7 @@ def build_parser() -> argparse.ArgumentParser:
 
 def main(argv=None):
     args = build_parser().parse_args(argv)
-    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0")) if args.gpu is None else args.gpu
     if torch.cuda.is_available():
         torch.cuda.set_device(local_rank)
         device = torch.device("cuda", local_rank)

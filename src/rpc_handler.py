@@ -84,6 +84,11 @@ class StageConnectionHandler:
         self.die_after: Optional[int] = None   # fault injection: "crash" while serving request number N
         self.on_die = None                     # callable that tears the server down (set by the launcher)
         self.die_guard = None                  # optional callable -> bool, consulted right before crashing
+        # device-to-device hand-off inside one box (petals_b200/net/devshare.py): built on first use
+        self._exporter = None
+        self._importer = None
+        self._box = None
+        self.handoff_out = self.handoff_in = 0
 
     # ------------------------------------------------------------------ registration
     def add_p2p_handlers(self, server: RpcServer) -> None:
@@ -147,6 +152,27 @@ class StageConnectionHandler:
         self.requests += 1
         return self._finish(out, metadata, sid)
 
+    def box(self) -> Optional[str]:
+        """The machine id this server hands device tensors off in (None on CPU)."""
+        if self._box is None and self.device.type == "cuda":
+            from petals_b200.net.devshare import box_id
+            self._box = box_id()
+        return self._box
+
+    def _export(self, out: torch.Tensor) -> dict:
+        if self._exporter is None:
+            from petals_b200.net.devshare import DeviceExporter
+            self._exporter = DeviceExporter(self.device)
+        self.handoff_out += 1
+        return self._exporter.export(out)
+
+    def _import(self, desc: dict) -> torch.Tensor:
+        if self._importer is None:
+            from petals_b200.net.devshare import DeviceImporter
+            self._importer = DeviceImporter(self.device)
+        self.handoff_in += 1
+        return self._importer.pull(desc)
+
     def _finish(self, out: torch.Tensor, metadata: Dict, sid) -> Tuple[List[torch.Tensor], Dict]:
         """Stage output of ONE request -> its reply (sampled token on the final stage, hidden states otherwise)."""
         if self.final_stage:
@@ -162,6 +188,9 @@ class StageConnectionHandler:
                 token = sample_token(logits, params, generated,
                                      generator=self._gen if logits.device.type == "cpu" else None)
             return [torch.tensor([[token]], dtype=torch.long)], {"token_id": token, "session_id": sid}
+        if out.is_cuda and metadata.get("device_handoff") and metadata["device_handoff"] == self.box():
+            # the consumer shares this box: the reply names a slot of this GPU's exported arena, no payload
+            return [], {"session_id": sid, "device_tensor": self._export(out)}
         return [out.detach().to("cpu")], {"session_id": sid}
 
     def _maybe_reorder(self, metadata: Dict) -> None:
@@ -226,9 +255,14 @@ class StageConnectionHandler:
 
     # ------------------------------------------------------------------ RPC methods
     def rpc_forward(self, uid: str, tensors: List[torch.Tensor], metadata: Dict):
-        if not tensors:
+        desc = metadata.get("device_tensor")
+        if desc is not None:
+            hidden = self._import(desc)              # one peer copy over NVLink from the producer's arena
+            metadata = {k: v for k, v in metadata.items() if k != "device_tensor"}
+        elif not tensors:
             raise ValueError("No tensors in request")
-        hidden = tensors[0]
+        else:
+            hidden = tensors[0]
         T = hidden.shape[-2] if hidden.dim() >= 2 else 1
         if T == 1 and self.max_batch > 1 and not metadata.get("is_prefill") and hidden.numel() == hidden.shape[-1]:
             out_t, out_md = self.pool.submit_batch_item(self._run_decode_batch, (hidden, metadata), kind="inference",
@@ -242,6 +276,8 @@ class StageConnectionHandler:
             (host, port, next_uid), rest = route[0], route[1:]
             md = dict(metadata)
             md["route"] = rest
+            if "device_tensor" in out_md:
+                md["device_tensor"] = out_md["device_tensor"]
             return self._fwd_client.call((host, int(port)), f"{HANDLER_PREFIX}.rpc_forward", next_uid, out_t, md,
                                          timeout=self.request_timeout)
         return out_t, out_md
@@ -318,7 +354,8 @@ class StageConnectionHandler:
                     "throughput": self.throughput, "requests": self.requests, "queued": self.pool.queued,
                     "max_batch": self.max_batch, "batches": self.pool.batches,
                     "mean_batch": (self.pool.batched_items / self.pool.batches) if self.pool.batches else 0.0,
-                    "streams_open": self.streams_open, "uptime_s": time.time() - self.started}
+                    "streams_open": self.streams_open, "uptime_s": time.time() - self.started,
+                    "box": self.box(), "handoff_out": self.handoff_out, "handoff_in": self.handoff_in}
 
     def rpc_check(self, uid: str, tensors, metadata: Dict):
         """Dial-back probe for joining servers (upstream reachability.py rpc_check)."""

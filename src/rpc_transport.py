@@ -52,6 +52,7 @@ class Hop:
         host, port, _ = parse_maddr((entry.get("p2p_maddrs") or [""])[0])
         self.addr = (host, port)
         self.start_block, self.end_block = start_block, end_block
+        self.box: Optional[str] = None        # machine id of the server, asked on first use (device hand-off)
 
 
 class RpcTransport:
@@ -60,8 +61,18 @@ class RpcTransport:
                  stage_keys: Optional[Sequence[str]] = None, routing: str = "stage", model_name: str = "default",
                  total_blocks: int = 32, start_block: int = 0, request_timeout: float = 30.0,
                  repetition_penalty: Optional[float] = None, dht: Optional[DHT] = None, push: bool = False,
-                 stream: bool = False, session_timeout: Optional[float] = None, step_timeout: Optional[float] = None):
+                 stream: bool = False, session_timeout: Optional[float] = None, step_timeout: Optional[float] = None,
+                 device_handoff: bool = False):
         self.device = device
+        # device_handoff: hops that live in this box exchange hidden states GPU to GPU (net/devshare.py); the TCP
+        # messages to and from them carry a descriptor instead of the tensor
+        self.device_handoff = bool(device_handoff) and device is not None and torch.device(device).type == "cuda"
+        self._exporter = self._importer = None
+        self._box = None
+        self.handoff_hops = 0
+        if self.device_handoff:
+            from petals_b200.net.devshare import DeviceExporter, DeviceImporter, box_id
+            self._exporter, self._importer, self._box = DeviceExporter(device), DeviceImporter(device), box_id()
         self.temperature, self.top_p, self.top_k = temperature, top_p, top_k
         self.repetition_penalty = repetition_penalty
         self.stage_keys = list(stage_keys or [])
@@ -168,13 +179,42 @@ class RpcTransport:
             md["repetition_penalty"] = float(self.repetition_penalty)
         return md
 
-    def _call(self, hop: Hop, tensor: torch.Tensor, md: dict):
-        if self.stream:
-            return self._call_stream(hop, tensor, md)
-        return self.client.call(hop.addr, f"{HANDLER_PREFIX}.rpc_forward", hop.key, [tensor], md,
-                                timeout=self.request_timeout)
+    def _in_box(self, hop: Hop) -> bool:
+        """Does this hop's server run on a GPU of the client's own machine (asked once per server)?"""
+        if not self.device_handoff:
+            return False
+        if hop.box is None:
+            try:
+                _, info = self.client.call(hop.addr, f"{HANDLER_PREFIX}.rpc_info", hop.key, [], {}, timeout=5.0)
+                hop.box = info.get("box") or ""
+            except Exception:  # noqa: BLE001
+                hop.box = ""
+        return hop.box == self._box
 
-    def _call_stream(self, hop: Hop, tensor: torch.Tensor, md: dict):
+    def _call(self, hop: Hop, tensor: torch.Tensor, md: dict, desc: Optional[dict] = None,
+              consumer_in_box: bool = False):
+        """One step on one hop.  ``desc``: the producer's hand-off descriptor of ``tensor`` (passed through untouched
+        when the hop can pull it itself); ``consumer_in_box``: whoever reads this hop's output shares the box."""
+        tensors = [tensor]
+        if tensor.is_cuda:
+            if self._in_box(hop):
+                md = dict(md)
+                md["device_tensor"] = desc if desc is not None else self._exporter.export(tensor)
+                tensors = []
+                self.handoff_hops += 1
+            else:
+                tensors = [tensor.to("cpu")]
+        if consumer_in_box and self._in_box(hop):
+            md = dict(md)
+            md["device_handoff"] = self._box
+        if self.stream:
+            out, omd = self._call_stream(hop, tensors, md)
+        else:
+            out, omd = self.client.call(hop.addr, f"{HANDLER_PREFIX}.rpc_forward", hop.key, tensors, md,
+                                        timeout=self.request_timeout)
+        return out, omd
+
+    def _call_stream(self, hop: Hop, tensors: List[torch.Tensor], md: dict):
         sid = md["session_id"]
         key = (sid, hop.peer_id)
         st = self._streams.get(key)
@@ -190,7 +230,7 @@ class RpcTransport:
                 st = self.client.open_stream(hop.addr, f"{HANDLER_PREFIX}.rpc_inference", hop.key, [], open_md,
                                              timeout=self.request_timeout)
                 self._streams[key] = st
-            return st.call([tensor], md, timeout=self.request_timeout)
+            return st.call(tensors, md, timeout=self.request_timeout)
         except (TimeoutError, ConnectionError):
             self._drop_stream(key)
             raise
@@ -245,12 +285,21 @@ class RpcTransport:
                 if j > 0:
                     self._journal(session_id, hop.key).append(x.clone())
                 md = self._metadata(session_id, T, cur_len, i == 0, None, is_replay=True)
-                out, _ = self._call(hop, x, md)
-                x = out[0]
+                out, omd = self._call(hop, x, md, consumer_in_box=j + 1 < len(hops) and self._in_box(hops[j + 1]))
+                x, _ = self._take(out, omd)
+
+    def _take(self, out, omd) -> Tuple[torch.Tensor, Optional[dict]]:
+        """A hop's output: the tensor of the reply, or - handed off on the device - this GPU's pull of the slot the
+        reply names (that copy is what gets journaled; the descriptor itself travels on to the next hop)."""
+        desc = omd.get("device_tensor") if isinstance(omd, dict) else None
+        if desc is not None:
+            return self._importer.pull(desc), desc
+        return out[0], None
 
     def _send(self, session_id: str, hidden: torch.Tensor, cur_len: int, is_prefill: bool,
               generated: Optional[Sequence[int]]) -> int:
-        cur = hidden.detach().to("cpu")
+        cur = hidden.detach() if self.device_handoff and hidden.is_cuda else hidden.detach().to("cpu")
+        cur_desc = None
         T = cur.shape[-2]
         route = self._get_route(session_id)
         t_all = time.perf_counter()
@@ -264,7 +313,12 @@ class RpcTransport:
             while True:
                 t0 = time.perf_counter()
                 try:
-                    out, omd = self._call(hop, cur, md)
+                    if self.push:
+                        chained = not hop.final and all(self._in_box(h) for h in route[i:])
+                    else:
+                        chained = i + 1 < len(route) and self._in_box(route[i + 1])
+                    out, omd = self._call(hop, cur, md, desc=cur_desc if attempt == 0 else None,
+                                          consumer_in_box=chained)
                     break
                 except (TimeoutError, ConnectionError, RpcError, RuntimeError, ValueError) as e:
                     attempt += 1
@@ -322,7 +376,7 @@ class RpcTransport:
             if "token_id" in omd or hop.final or (self.push and "token_id" in omd):
                 self.last_token = int(omd.get("token_id", out[0].reshape(-1)[0].item()))
                 break
-            cur = out[0]
+            cur, cur_desc = self._take(out, omd)
             i += 1
         total = time.perf_counter() - t_all
         if is_prefill:

@@ -314,3 +314,36 @@ def test_rms_rstd_kernel_matches_in_kernel_statistics(T):
     b = gemm.linear(x, pw, norm_mode=gemm.NORM_RMS, norm_w=g, rstd=rstd)
     torch.cuda.synchronize()
     assert torch.equal(a, b)
+
+
+@pytest.mark.parametrize("T,N,K,dual", [(100, 4096, 4096, False), (128, 4096, 11008, False), (128, 2048, 4096, True),
+                                        (200, 4096, 4096, False)])
+def test_prefill_gemm_split_k_for_short_prompts(T, N, K, dual, monkeypatch):
+    """Few output tiles for 148 SMs: the prefill GEMM splits K over several units per tile and the unit with the
+    tile's last ticket adds the partials in k order.  Same result as the unsplit kernel up to fp32 summation order,
+    bit-reproducible from launch to launch, counters left clean."""
+    from petals_b200.ops import gemm, packing
+
+    dtype = torch.bfloat16
+    torch.manual_seed(T + N)
+    dev = "cuda"
+    x = (torch.randn(T, K, device=dev) * 0.5).to(dtype)
+    mk = lambda: (torch.randn(N, K, device=dev) / K ** 0.5).to(dtype)  # noqa: E731
+    ws = gemm.GemmWorkspace.create(dev, 256)
+    if dual:
+        wg, wu = mk(), mk()
+        pw = packing.pack_dual(wg, wu)
+        out = gemm.linear(x, pw, workspace=ws)
+        ref = _ref(x, wg, epi="swiglu", up=wu, dtype=dtype)
+    else:
+        w = mk()
+        res = torch.randn(T, N, device=dev).to(dtype)
+        pw = packing.pack_weight(w)
+        out = gemm.linear(x, pw, residual=res, workspace=ws)
+        ref = _ref(x, w, residual=res, dtype=dtype)
+    torch.cuda.synchronize()
+    _close(out, ref, dtype)
+    assert int(ws.counters.abs().sum()) == 0, "tickets must be handed back"
+    out2 = gemm.linear(x, pw, workspace=ws) if dual else gemm.linear(x, pw, residual=res, workspace=ws)
+    torch.cuda.synchronize()
+    assert torch.equal(out, out2)

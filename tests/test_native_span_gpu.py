@@ -179,3 +179,36 @@ def test_random_weights_are_the_same_on_cpu_and_gpu():
     b = RandomSource(cfg, 7, "cuda").get(name)
     assert b.is_cuda and torch.equal(a, b.cpu())
     assert abs(a.std().item() - 0.02) < 2e-4
+
+
+@pytest.mark.parametrize("name", ["tiny-llama-gqa", "tiny-gpt2"])
+@pytest.mark.parametrize("keep", [0, 1])
+def test_offloaded_native_span_equals_resident_span(name, keep):
+    """--use_cpu_offload on a B200: packed blocks stream from pinned host memory through two device slots under the
+    same sm_100a kernels - bit-identical to the resident span."""
+    from petals_b200.models.config import PRESETS
+    from petals_b200.runtime.kv_cache import KVCacheManager
+    from petals_b200.runtime.native_span import NativeSpan
+    from petals_b200.runtime.offload import OffloadedNativeSpan, make_offloaded_native_span
+    from petals_b200.weights.loader import load_span
+
+    cfg = PRESETS[name]
+    dev = torch.device("cuda")
+    dtype = torch.bfloat16
+    load = lambda d: load_span(name, cfg, 0, cfg.n_layers, need_embed=True, need_head=True, dtype=dtype, device=d, seed=3)  # noqa: E731
+    res = NativeSpan(cfg, load(dev), dev, dtype, kv_capacity=256, max_batch=2, max_chunk=64, use_graphs=False)
+    off = make_offloaded_native_span(cfg, load("cpu"), dev, dtype, keep_layers_on_gpu=keep, kv_capacity=256, max_batch=2,
+                                     max_chunk=64)
+    assert isinstance(off, OffloadedNativeSpan) and off.n_layers == cfg.n_layers and len(off.layers) == keep
+    ka = KVCacheManager(cfg.n_layers, cfg.n_kv_heads, cfg.head_dim, dtype, dev).allocate("a", 256)
+    kb = KVCacheManager(cfg.n_layers, cfg.n_kv_heads, cfg.head_dim, dtype, dev).allocate("b", 256)
+    torch.manual_seed(0)
+    ids = torch.randint(0, cfg.vocab, (90,), device=dev)
+    la, ta = res.prefill(ka, ids=ids[:80])
+    lb, tb = off.prefill(kb, ids=ids[:80])
+    assert torch.equal(la, lb) and torch.equal(ta, tb)
+    for t in range(80, 86):
+        la, ta = res.decode([ka], ids=ids[t:t + 1])
+        lb, tb = off.decode([kb], ids=ids[t:t + 1])
+        assert torch.equal(la, lb) and torch.equal(ta, tb)
+    assert off.bytes_streamed > 0
