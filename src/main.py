@@ -112,6 +112,9 @@ def run_rank0(args, device, splits, dht: Optional[DHT] = None):
     tx.send_prefill(L, hidden, session_id=session_id, max_length=max_length)
     next_id = tx.recv_token()
     generated = [next_id]
+    on_token = getattr(args, "on_token", None)        # optional observer (benchmarks / fault injection scripts)
+    if on_token is not None:
+        on_token(0, next_id)
     prefill_time = time.perf_counter() - t_prefill_start
     logger.info("Prefill completed in %.3fs", prefill_time)
     logger.info("Generated token: %d (%s)", next_id, tok.decode([next_id]))
@@ -123,12 +126,14 @@ def run_rank0(args, device, splits, dht: Optional[DHT] = None):
         hidden, _ = s0(torch.tensor([[next_id]], dtype=torch.long), None, None, kv0)
         tx.send_decode_step(cur_len, hidden, session_id=session_id, max_length=max_length, generated_tokens=generated)
         next_id = tx.recv_token()
+        if on_token is not None:
+            on_token(len(generated), next_id)
         if eos is not None and next_id == eos:
             logger.info("EOS token generated, stopping generation")
             break
         if next_id == last:
             repeat += 1
-            if repeat >= 5:
+            if repeat >= 5 and not getattr(args, "no_repeat_stop", False):
                 logger.warning("Consecutive repetition detected (token %d), stopping generation", next_id)
                 break
         else:
@@ -533,6 +538,8 @@ def build_parser() -> argparse.ArgumentParser:
     p.add_argument("--device_handoff", action="store_true",
                    help="client: servers on GPUs of this machine exchange hidden states device to device (CUDA IPC + "
                         "NVLink peer copies); the RPC messages to them carry a descriptor instead of the tensor")
+    p.add_argument("--no_repeat_stop", action="store_true",
+                   help="client: keep generating when one token repeats 5 times (random-weight benchmarks)")
     p.add_argument("--gpu", type=int, default=None, help="CUDA device index of this process (default: LOCAL_RANK or 0)")
     p.add_argument("--inbox", action="store_true",
                    help="in-box mode: launch with torchrun (one process per GPU); stages hand hidden states over "
