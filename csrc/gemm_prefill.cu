@@ -296,13 +296,14 @@ extern "C" int b200_gemm_prefill(const b200_gemm_args* a, void* stream_) {
     int ksplit = 1;
     static const int split_on = [] { const char* e = getenv("B200_PREFILL_KSPLIT"); return e ? atoi(e) : 1; }();
     if (split_on && a->scratch && a->counters && tiles < grid) {
-        double best = (double)tiles / (double)(((tiles + grid - 1) / grid) * grid);
+        // One wave only: a short-prompt GEMM is a weight stream, ~90 GB/s per CTA, so what a split buys is more SMs
+        // streaming at once.  From ~75 streaming CTAs the HBM is the limit and a second wave of units only adds
+        // their fixed costs (measured: 3-way split of the 96-tile qkv GEMM made a 128-token prefill slower).
         for (int q = 2; q <= 4; ++q) {
             if (p.kbpt / q < 8) break;
             const int un = tiles * q;
-            const double eff = (double)un / (double)(((un + grid - 1) / grid) * grid);
             const size_t need = (size_t)un * (a->dual ? 2 : 1) * bn * kTileM * sizeof(float);
-            if (eff > best + 0.05 && need <= (size_t)b200_gemm_scratch_bytes(a->T)) { best = eff; ksplit = q; }
+            if (tiles * (q - 1) < 75 && un <= grid && need <= (size_t)b200_gemm_scratch_bytes(a->T)) ksplit = q;
         }
     }
     p.ll_parts = ksplit;

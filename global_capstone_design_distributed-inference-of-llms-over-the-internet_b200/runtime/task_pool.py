@@ -13,7 +13,11 @@ Batching: upstream's pools merge queued tasks of the SAME shape into one batch
 case worth merging - the decode kernels take up to 32 sessions per launch sequence at little
 more than the cost of one - so ``submit_batch_item`` queues an item for a batch function and
 the worker, when it reaches such an item, takes every other queued item of the same function
-along (up to its ``max_batch``) and runs them in one call.
+along (up to its ``max_batch``) and runs them in one call.  Clients that step in lockstep send their
+requests within a few hundred microseconds of each other, so the worker may *linger*: when it reaches a
+batch item and fewer items are queued than the caller expects (``expect()``: the number of sessions
+that have been stepping lately), it waits up to ``batch_linger`` seconds for the rest before it runs
+the step - one short wait instead of a step for the early bird and a second step for everybody else.
 """
 from __future__ import annotations
 
@@ -46,8 +50,11 @@ class DummyTaskPrioritizer(TaskPrioritizerBase):
 
 class PrioritizedTaskPool:
     def __init__(self, name: str = "pool", max_task_tokens: Optional[int] = None,
-                 prioritizer: Optional[TaskPrioritizerBase] = None):
+                 prioritizer: Optional[TaskPrioritizerBase] = None, batch_linger: float = 0.0,
+                 expect: Optional[Callable[[], int]] = None):
         self.name = name
+        self.batch_linger = float(batch_linger)
+        self.expect = expect
         self.max_task_tokens = max_task_tokens
         self.prioritizer = prioritizer or DummyTaskPrioritizer()
         self._heap: list = []
@@ -105,6 +112,19 @@ class PrioritizedTaskPool:
                 heapq.heapify(self._heap)
         return group
 
+    def _linger(self, first) -> None:
+        """Lock held: wait (releasing the lock) until as many items of ``first``'s function are queued as the caller
+        expects, at most ``batch_linger`` seconds."""
+        batch_fn, _, max_batch = first[4]
+        deadline = time.monotonic() + self.batch_linger
+        while not self._stop:
+            want = min(int(self.expect()), max_batch)
+            have = 1 + sum(1 for e in self._heap if e[3] is _BATCH and e[4][0] == batch_fn)
+            left = deadline - time.monotonic()
+            if have >= want or left <= 0:
+                return
+            self._cv.wait(left)
+
     def _run(self) -> None:
         while True:
             with self._cv:
@@ -113,6 +133,8 @@ class PrioritizedTaskPool:
                 if self._stop and not self._heap:
                     return
                 ent = heapq.heappop(self._heap)
+                if ent[3] is _BATCH and self.batch_linger > 0.0 and self.expect is not None:
+                    self._linger(ent)
                 group = self._take_batch(ent) if ent[3] is _BATCH else None
             if group is not None:
                 self._run_batch(group)

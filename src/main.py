@@ -216,7 +216,8 @@ def start_stage_server(args, device, stage_model, final_stage: bool, stage_index
                                      alloc_timeout=getattr(args, "alloc_timeout", 10.0),
                                      session_timeout=getattr(args, "session_timeout", 30 * 60.0),
                                      step_timeout=getattr(args, "step_timeout", 5 * 60.0),
-                                     max_batch=getattr(args, "max_batch", None))
+                                     max_batch=getattr(args, "max_batch", None),
+                                     batch_linger=getattr(args, "batch_linger_ms", 0.5) * 1e-3)
     stop = threading.Event()
     model_name = args.model
     handler.on_die = lambda: (stop.set(), rpc.stop())   # scripted kill (tests / kill_stage.py --soft)
@@ -534,6 +535,9 @@ def build_parser() -> argparse.ArgumentParser:
     p.add_argument("--step_timeout", type=float, default=5 * 60.0, help="server: idle time of an inference stream")
     p.add_argument("--max_batch", type=int, default=16,
                    help="server: single-token requests of different sessions merged into one decode step (1 = off)")
+    p.add_argument("--batch_linger_ms", type=float, default=0.5,
+                   help="server: how long a batched decode step waits for the other sessions that have been stepping "
+                        "lately (0 = take what is queued)")
     p.add_argument("--no_throughput_cache", action="store_true", help="server: re-measure the throughput on every start")
     p.add_argument("--device_handoff", action="store_true",
                    help="client: servers on GPUs of this machine exchange hidden states device to device (CUDA IPC + "

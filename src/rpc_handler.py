@@ -52,7 +52,7 @@ class StageConnectionHandler:
                  attn_cache_tokens: Optional[int] = None, session_ttl: float = 600.0, start_block: Optional[int] = None,
                  end_block: Optional[int] = None, throughput: float = 0.0, seed: Optional[int] = None,
                  alloc_timeout: float = 10.0, session_timeout: float = 30 * 60.0, step_timeout: float = 5 * 60.0,
-                 max_batch: Optional[int] = None):
+                 max_batch: Optional[int] = None, batch_linger: float = 0.0005):
         self.dht = dht
         self.stage_model = stage_model
         self.device = torch.device(device)
@@ -73,7 +73,12 @@ class StageConnectionHandler:
             self.max_batch = 1
         self.streams_open = 0
         self._default_temperature, self._default_top_p, self._default_top_k = 0.8, 0.9, 0
-        self.pool = PrioritizedTaskPool("stage")
+        # sessions that made a decode step in the last 50 ms are expected to make the next one together: the pool
+        # waits up to batch_linger for them before it runs a batched step (0 = never wait)
+        self._stepping: Dict[str, float] = {}
+        self.batch_linger = float(batch_linger)
+        self.pool = PrioritizedTaskPool("stage", batch_linger=self.batch_linger if self.max_batch > 1 else 0.0,
+                                        expect=self._expected_batch)
         self._fwd_client = RpcClient()
         self._gen = torch.Generator(device="cpu")
         if seed is not None:
@@ -89,6 +94,10 @@ class StageConnectionHandler:
         self._importer = None
         self._box = None
         self.handoff_out = self.handoff_in = 0
+
+    def _expected_batch(self) -> int:
+        now = time.monotonic()
+        return sum(1 for t in self._stepping.values() if now - t < 0.05)
 
     # ------------------------------------------------------------------ registration
     def add_p2p_handlers(self, server: RpcServer) -> None:
@@ -265,6 +274,7 @@ class StageConnectionHandler:
             hidden = tensors[0]
         T = hidden.shape[-2] if hidden.dim() >= 2 else 1
         if T == 1 and self.max_batch > 1 and not metadata.get("is_prefill") and hidden.numel() == hidden.shape[-1]:
+            self._stepping[metadata.get("session_id")] = time.monotonic()
             out_t, out_md = self.pool.submit_batch_item(self._run_decode_batch, (hidden, metadata), kind="inference",
                                                         tokens=1, max_batch=self.max_batch).result(
                                                             timeout=self.request_timeout)
@@ -365,6 +375,7 @@ class StageConnectionHandler:
         return [], {"reachable": ok, "rtt_s": rtt}
 
     def _close(self, sid: str) -> bool:
+        self._stepping.pop(sid, None)
         closed = self.kv.close(sid)
         mirror = getattr(self.stage_model, "close_session", None)     # tensor-parallel stage: the followers' shards
         if closed and mirror is not None:
@@ -375,6 +386,7 @@ class StageConnectionHandler:
         sid = metadata.get("session_id", "")
         if getattr(self.stage_model, "close_session", None) is not None:
             return [], {"closed": self._submit(self._close, sid, kind="inference")}    # serialised with the steps
+        self._stepping.pop(sid, None)
         return [], {"closed": self.kv.close(sid)}
 
     def shutdown(self) -> None:

@@ -143,6 +143,43 @@ def test_task_pool_priorities():
     pool.shutdown()
 
 
+def test_task_pool_batches_and_lingers_for_expected_items():
+    """Queued items of one batch function run in one call; with a linger the worker waits for the items the caller
+    expects (lockstep clients) instead of running the early bird alone; an exception entry fails only its item."""
+    from petals_b200.runtime.task_pool import PrioritizedTaskPool
+
+    calls = []
+
+    def fn(items):
+        calls.append(list(items))
+        return [ValueError("odd") if i % 2 else i * 10 for i in items]
+
+    pool = PrioritizedTaskPool("t")
+    gate = pool.submit(lambda: time.sleep(0.1))
+    futs = [pool.submit_batch_item(fn, i, max_batch=3) for i in range(5)]
+    gate.result(2)
+    assert futs[0].result(2) == 0 and futs[2].result(2) == 20 and futs[4].result(2) == 40
+    with pytest.raises(ValueError):
+        futs[1].result(2)
+    assert calls == [[0, 1, 2], [3, 4]] and pool.batches == 2 and pool.batched_items == 5
+    pool.shutdown()
+
+    calls.clear()
+    pool = PrioritizedTaskPool("t", batch_linger=0.5, expect=lambda: 3)
+    a = pool.submit_batch_item(fn, 0, max_batch=8)
+    time.sleep(0.05)                                   # the worker is lingering on item 0 by now
+    b = pool.submit_batch_item(fn, 2, max_batch=8)
+    c = pool.submit_batch_item(fn, 4, max_batch=8)
+    t0 = time.monotonic()
+    assert (a.result(2), b.result(2), c.result(2)) == (0, 20, 40)
+    assert calls == [[0, 2, 4]], "one step for the three expected items"
+    assert time.monotonic() - t0 < 0.3, "the step starts as soon as the expected items are there, not at the deadline"
+    calls.clear()
+    d = pool.submit_batch_item(fn, 6, max_batch=8)     # the others never come: the linger bounds the wait
+    assert d.result(2) == 60 and calls == [[6]]
+    pool.shutdown()
+
+
 def test_rope_llama3_scaling_matches_hf():
     import transformers
     from petals_b200.models.config import PRESETS
