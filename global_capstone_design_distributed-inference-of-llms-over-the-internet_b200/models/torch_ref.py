@@ -67,6 +67,16 @@ class TorchSpan:
         self.inv_freq = rope_inv_freq(cfg.head_dim, cfg.rope_theta, cfg.rope_scaling, self.device) if cfg.is_llama else None
         self.scale = 1.0 / math.sqrt(cfg.head_dim)
 
+    def subspan(self, a: int, b: int) -> "TorchSpan":
+        """View over blocks [a, b) of this span (shared weights)."""
+        import copy
+
+        if not (0 <= a < b <= len(self.layers)):
+            raise ValueError(f"blocks [{a},{b}) are not inside this span of {len(self.layers)} blocks")
+        v = copy.copy(self)
+        v.layers = self.layers[a:b]
+        return v
+
     # ---- stage-0 / last-stage pieces
     def embed(self, ids: torch.Tensor, pos0: int) -> torch.Tensor:
         h = self.w["embed"][ids]                                               # type: ignore[index]

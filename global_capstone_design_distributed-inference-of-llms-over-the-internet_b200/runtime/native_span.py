@@ -203,6 +203,25 @@ class NativeSpan:
     def n_layers(self) -> int:
         return len(self.layers) + self.streamed_layers
 
+    def subspan(self, a: int, b: int) -> "NativeSpan":
+        """A view that runs only blocks [a, b) of this span: same packed weights and work buffers, its own graphs and
+        plans.  Lets a client enter (or leave) a server's span at any block - upstream addresses blocks one by one
+        (chained module uids, petals/server/handler.py) - without a second copy of the weights.  Calls on a span and
+        its views must not overlap in time (the stage's task pool runs them one at a time)."""
+        import copy
+
+        if not (0 <= a < b <= len(self.layers)):
+            raise ValueError(f"blocks [{a},{b}) are not inside this span of {len(self.layers)} blocks")
+        if self.streamed_layers or self.tp_mode is not None:
+            raise NotImplementedError("sub-spans of offloaded or tensor-parallel spans")
+        v = copy.copy(self)
+        v.layers = self.layers[a:b]
+        v.has_embed = self.has_embed and a == 0
+        v.has_head = self.has_head and b == len(self.layers)
+        v._graphs, v._launches_per_graph, v._prefill_plans, v._ptr_tables = {}, {}, {}, {}
+        v._ptr_key = None
+        return v
+
     def _iter_layers(self):
         """(index, packed weights) of every block in order; a span that streams blocks from the host overrides this."""
         return enumerate(self.layers)

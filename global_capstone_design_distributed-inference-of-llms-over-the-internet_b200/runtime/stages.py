@@ -110,6 +110,22 @@ class _StageBase(torch.nn.Module):
                 w = _to_device(w, self.device)
             self.span = TorchSpan(self.cfg, w, self.device, self.dtype)
 
+    def subspan(self, start: int, end: int) -> "_StageBase":
+        """Stage object over blocks [start, end) of THIS server's span (absolute block numbers): the same weights, own
+        graphs; a view that stops before the model's last block is a segment even on a last-stage server."""
+        import copy
+
+        if (start, end) == (self.start, self.end):
+            return self
+        if not (self.start <= start < end <= self.end) or self.role == "stage0":
+            raise ValueError(f"blocks [{start},{end}) are not inside this server's span [{self.start},{self.end})")
+        v = copy.copy(self)
+        v.span = self.span.subspan(start - self.start, end - self.start)
+        v.start, v.end = start, end
+        if self.role == "last" and end != self.end:
+            v.__class__ = StageSegment
+        return v
+
     # ---- KV helpers (the handler owns the manager; tests may let the stage own one)
     def new_kv_manager(self, **kw) -> KVCacheManager:
         return KVCacheManager(self.end - self.start, self.cfg.n_kv_heads, self.cfg.head_dim, self.dtype,
@@ -127,7 +143,7 @@ class _StageBase(torch.nn.Module):
         return self.span.forward(h, kv, pos0)
 
     @torch.inference_mode()
-    def decode_batch(self, hidden: torch.Tensor, kvs) -> list:
+    def decode_batch(self, hidden: torch.Tensor, kvs, to_cpu: bool = False) -> list:
         """One token for each of several SESSIONS in one step: ``hidden`` [B, H] (row b belongs to ``kvs[b]``) ->
         list of B outputs shaped like :meth:`forward`'s for a single token ([1, 1, H] hidden states, or
         [1, 1, V] fp32 logits on the last stage).  The native engine runs the B sessions as one batched
@@ -135,13 +151,19 @@ class _StageBase(torch.nn.Module):
         B = hidden.shape[0]
         if self.role == "stage0":
             raise ValueError("decode_batch serves server stages (hidden-state inputs)")
+        self.last_greedy_ids = None
         if self.backend == "native" and B <= self.span.max_batch:
             h = hidden.reshape(B, self.cfg.hidden).to(self.device, self.dtype)
             if self.role == "last":
-                logits, _ = self.span.decode(list(kvs), h_in=h, greedy=True)
+                logits, ids = self.span.decode(list(kvs), h_in=h, greedy=True)
                 out = logits[:B].clone()
+                # the step's graph already took the arg-max of every row: one copy for the whole batch instead of one
+                # arg-max + sync per request in the handler
+                self.last_greedy_ids = [int(t) for t in ids[:B].tolist()]
             else:
                 out = self.span.decode(list(kvs), h_in=h).clone()
+                if to_cpu:
+                    out = out.cpu()                    # one device-to-host copy for the whole batch
             return [out[b].reshape(1, 1, -1) for b in range(B)]
         return [self.forward(hidden[b:b + 1].reshape(1, 1, -1), None, None, kvs[b])[0] for b in range(B)]
 

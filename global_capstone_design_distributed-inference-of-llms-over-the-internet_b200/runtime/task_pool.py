@@ -18,6 +18,9 @@ requests within a few hundred microseconds of each other, so the worker may *lin
 batch item and fewer items are queued than the caller expects (``expect()``: the number of sessions
 that have been stepping lately), it waits up to ``batch_linger`` seconds for the rest before it runs
 the step - one short wait instead of a step for the early bird and a second step for everybody else.
+It only waits when FEW items are missing (``linger_max_missing``): with many sessions the arrivals spread
+over more than a step's time, and the better steady state is the one greedy batching falls into by
+itself - two groups that alternate, one computing while the other one is on the wire.
 """
 from __future__ import annotations
 
@@ -51,10 +54,11 @@ class DummyTaskPrioritizer(TaskPrioritizerBase):
 class PrioritizedTaskPool:
     def __init__(self, name: str = "pool", max_task_tokens: Optional[int] = None,
                  prioritizer: Optional[TaskPrioritizerBase] = None, batch_linger: float = 0.0,
-                 expect: Optional[Callable[[], int]] = None):
+                 expect: Optional[Callable[[], int]] = None, linger_max_missing: int = 3):
         self.name = name
         self.batch_linger = float(batch_linger)
         self.expect = expect
+        self.linger_max_missing = int(linger_max_missing)
         self.max_task_tokens = max_task_tokens
         self.prioritizer = prioritizer or DummyTaskPrioritizer()
         self._heap: list = []
@@ -121,7 +125,7 @@ class PrioritizedTaskPool:
             want = min(int(self.expect()), max_batch)
             have = 1 + sum(1 for e in self._heap if e[3] is _BATCH and e[4][0] == batch_fn)
             left = deadline - time.monotonic()
-            if have >= want or left <= 0:
+            if have >= want or left <= 0 or want - have > self.linger_max_missing:
                 return
             self._cv.wait(left)
 

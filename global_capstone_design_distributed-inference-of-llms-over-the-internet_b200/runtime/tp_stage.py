@@ -99,17 +99,21 @@ class TPStage(_StageBase):
         return out.unsqueeze(0), kv
 
     @torch.inference_mode()
-    def decode_batch(self, hidden: torch.Tensor, kvs) -> list:
+    def decode_batch(self, hidden: torch.Tensor, kvs, to_cpu: bool = False) -> list:
         B = hidden.shape[0]
+        self.last_greedy_ids = None
         h = hidden.reshape(B, self.cfg.hidden).to(self.device, self.dtype).contiguous()
         if B > self.span.max_batch:
             return [self.forward(h[b:b + 1], None, None, kvs[b])[0] for b in range(B)]
         self._send_cmd(CMD_BATCH, [kv.session_id for kv in kvs], B, 0, h)
         if self.role == "last":
-            logits, _ = self.span.decode(list(kvs), h_in=h, greedy=True)
+            logits, ids = self.span.decode(list(kvs), h_in=h, greedy=True)
             out = logits[:B].clone()
+            self.last_greedy_ids = [int(t) for t in ids[:B].tolist()]
         else:
             out = self.span.decode(list(kvs), h_in=h).clone()
+            if to_cpu:
+                out = out.cpu()
         return [out[b].reshape(1, 1, -1) for b in range(B)]
 
     def close_session(self, session_id: str) -> None:

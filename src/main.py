@@ -21,6 +21,7 @@ from __future__ import annotations
 import argparse
 import logging
 import os
+import sys
 import random
 import threading
 import time
@@ -218,6 +219,7 @@ def start_stage_server(args, device, stage_model, final_stage: bool, stage_index
                                      step_timeout=getattr(args, "step_timeout", 5 * 60.0),
                                      max_batch=getattr(args, "max_batch", None),
                                      batch_linger=getattr(args, "batch_linger_ms", 0.5) * 1e-3)
+    sys.setswitchinterval(2e-4)   # many handler threads + one compute thread: hand the GIL over faster than every 5 ms
     stop = threading.Event()
     model_name = args.model
     handler.on_die = lambda: (stop.set(), rpc.stop())   # scripted kill (tests / kill_stage.py --soft)

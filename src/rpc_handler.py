@@ -62,8 +62,10 @@ class StageConnectionHandler:
         self.end_block = getattr(stage_model, "end", end_block)
         self.throughput = throughput
         cap = getattr(stage_model, "kv_capacity", 2048)
-        self.kv = stage_model.new_kv_manager(max_tokens=attn_cache_tokens, session_ttl=session_ttl,
-                                             alloc_timeout=alloc_timeout)
+        self._kv_kw = dict(max_tokens=attn_cache_tokens, session_ttl=session_ttl, alloc_timeout=alloc_timeout)
+        self.kv = stage_model.new_kv_manager(**self._kv_kw)
+        self._views: Dict[tuple, tuple] = {}
+        self._views_lock = threading.Lock()
         self.kv_capacity = cap
         self.session_timeout, self.step_timeout = session_timeout, step_timeout
         # sessions per batched decode step: what the stage's engine takes in one call (1 = never batch)
@@ -95,6 +97,26 @@ class StageConnectionHandler:
         self._box = None
         self.handoff_out = self.handoff_in = 0
 
+    def _view(self, md: dict):
+        """(stage, cache manager, is_final) a request runs on: the whole span, or - ``blocks = [b, e)`` in the request,
+        a client entering this server's span at a block other than its first - a view over those blocks with its own
+        per-session caches (same weights; runtime/stages.py:subspan)."""
+        blocks = md.get("blocks")
+        if not blocks or (int(blocks[0]), int(blocks[1])) == (self.start_block, self.end_block):
+            return self.stage_model, self.kv, self.final_stage
+        key = (int(blocks[0]), int(blocks[1]))
+        with self._views_lock:
+            v = self._views.get(key)
+            if v is None:
+                if not hasattr(self.stage_model, "subspan"):
+                    raise ValueError("this server only serves its whole span")
+                stage = self.stage_model.subspan(*key)
+                v = self._views[key] = (stage, stage.new_kv_manager(**self._kv_kw),
+                                        self.final_stage and key[1] == self.end_block)
+                logger.info("serving a sub-span: blocks [%d:%d) of [%s:%s)", key[0], key[1], self.start_block,
+                            self.end_block)
+        return v
+
     def _expected_batch(self) -> int:
         now = time.monotonic()
         return sum(1 for t in self._stepping.values() if now - t < 0.05)
@@ -107,7 +129,8 @@ class StageConnectionHandler:
         server.add_stream_handler(f"{HANDLER_PREFIX}.rpc_inference", self.rpc_inference)
 
     # ------------------------------------------------------------------ core
-    def _session_for(self, md: dict, T: int):
+    def _session_for(self, md: dict, T: int, mgr=None):
+        mgr = mgr or self.kv
         sid = md.get("session_id")
         if sid is None:
             raise ValueError("request.metadata must contain session_id")
@@ -117,18 +140,18 @@ class StageConnectionHandler:
         max_length = int(md.get("max_length", self.kv_capacity))
         if max_length > self.kv_capacity:
             raise ValueError(f"max_length {max_length} exceeds this server's per-session capacity {self.kv_capacity}")
-        kv = self.kv.get(sid)
+        kv = mgr.get(sid)
         if is_prefill:
             if is_replay:
                 logger.info("[%s] REPLAY MODE: restoring KV cache (prefill)", str(sid)[:8])
-            kv = self.kv.allocate(sid, self.kv_capacity)
+            kv = mgr.allocate(sid, self.kv_capacity)
             kv.limit = max_length
         elif kv is None:
             if not is_replay:
                 raise ValueError(f"Missing past_key_values for session_id={sid}: server restart or cache loss; "
                                  "replay the session with is_replay=True")
             logger.warning("[%s] REPLAY: no cache for a decode step, starting a fresh session", str(sid)[:8])
-            kv = self.kv.allocate(sid, self.kv_capacity)
+            kv = mgr.allocate(sid, self.kv_capacity)
             kv.limit = max_length
         start = md.get("start_from_position")
         if start is not None:
@@ -154,12 +177,12 @@ class StageConnectionHandler:
             raise ConnectionError("injected crash")
         T = hidden_states.shape[-2] if hidden_states.dim() >= 2 else 1
         self._maybe_reorder(metadata)
-        sid, kv = self._session_for(metadata, T)
+        stage, mgr, final = self._view(metadata)
+        sid, kv = self._session_for(metadata, T, mgr)
         pos_ids = torch.arange(kv.length, kv.length + T, dtype=torch.long).unsqueeze(0)
-        out, _ = self.stage_model(hidden_states, position_ids=pos_ids, attention_mask=None, past_key_values=kv,
-                                  use_cache=True)
+        out, _ = stage(hidden_states, position_ids=pos_ids, attention_mask=None, past_key_values=kv, use_cache=True)
         self.requests += 1
-        return self._finish(out, metadata, sid)
+        return self._finish(out, metadata, sid, final)
 
     def box(self) -> Optional[str]:
         """The machine id this server hands device tensors off in (None on CPU)."""
@@ -182,9 +205,9 @@ class StageConnectionHandler:
         self.handoff_in += 1
         return self._importer.pull(desc)
 
-    def _finish(self, out: torch.Tensor, metadata: Dict, sid) -> Tuple[List[torch.Tensor], Dict]:
+    def _finish(self, out: torch.Tensor, metadata: Dict, sid, final: Optional[bool] = None) -> Tuple[List[torch.Tensor], Dict]:
         """Stage output of ONE request -> its reply (sampled token on the final stage, hidden states otherwise)."""
-        if self.final_stage:
+        if self.final_stage if final is None else final:
             logits = out.reshape(-1, out.shape[-1])[-1]
             params = SamplingParams(
                 float(metadata.get("temperature", self._default_temperature)),
@@ -200,7 +223,7 @@ class StageConnectionHandler:
         if out.is_cuda and metadata.get("device_handoff") and metadata["device_handoff"] == self.box():
             # the consumer shares this box: the reply names a slot of this GPU's exported arena, no payload
             return [], {"session_id": sid, "device_tensor": self._export(out)}
-        return [out.detach().to("cpu")], {"session_id": sid}
+        return [out.detach() if out.device.type == "cpu" else out.detach().to("cpu")], {"session_id": sid}
 
     def _maybe_reorder(self, metadata: Dict) -> None:
         """Beam search: ``hypo_ids[i]`` names which hypothesis of ``beam_sessions`` session i continues."""
@@ -242,10 +265,15 @@ class StageConnectionHandler:
             try:
                 H = ready[0][1].shape[-1]
                 h = torch.cat([r[1].reshape(1, H) for r in ready], 0)
-                outs = self.stage_model.decode_batch(h, [r[4] for r in ready])
+                to_cpu = not self.final_stage and not any(r[2].get("device_handoff") for r in ready)
+                outs = self.stage_model.decode_batch(h, [r[4] for r in ready], to_cpu=to_cpu)
+                ids = getattr(self.stage_model, "last_greedy_ids", None)
                 self.requests += len(ready)
-                for (i, _, md, sid, _), o in zip(ready, outs):
-                    results[i] = self._finish(o, md, sid)
+                for b, ((i, _, md, sid, _), o) in enumerate(zip(ready, outs)):
+                    if ids is not None and float(md.get("temperature", self._default_temperature)) <= 0.0:
+                        results[i] = ([torch.tensor([[ids[b]]], dtype=torch.long)], {"token_id": ids[b], "session_id": sid})
+                    else:
+                        results[i] = self._finish(o, md, sid)
             except BaseException as e:  # noqa: BLE001
                 for i, *_ in ready:
                     results[i] = e
@@ -273,7 +301,8 @@ class StageConnectionHandler:
         else:
             hidden = tensors[0]
         T = hidden.shape[-2] if hidden.dim() >= 2 else 1
-        if T == 1 and self.max_batch > 1 and not metadata.get("is_prefill") and hidden.numel() == hidden.shape[-1]:
+        whole = self._view(metadata)[0] is self.stage_model        # sub-span views run unbatched
+        if whole and T == 1 and self.max_batch > 1 and not metadata.get("is_prefill") and hidden.numel() == hidden.shape[-1]:
             self._stepping[metadata.get("session_id")] = time.monotonic()
             out_t, out_md = self.pool.submit_batch_item(self._run_decode_batch, (hidden, metadata), kind="inference",
                                                         tokens=1, max_batch=self.max_batch).result(
@@ -281,7 +310,7 @@ class StageConnectionHandler:
         else:
             out_t, out_md = self._submit(self._run_forward, hidden, metadata, kind="inference", tokens=T)
         route = metadata.get("route") or []
-        if route and not self.final_stage:
+        if route and "token_id" not in out_md:
             # server->server push: hand the activations to the next hop ourselves and relay its answer
             (host, port, next_uid), rest = route[0], route[1:]
             md = dict(metadata)
@@ -315,7 +344,8 @@ class StageConnectionHandler:
         max_length = int(metadata.get("max_length", self.kv_capacity))
         if max_length > self.kv_capacity:
             raise ValueError(f"max_length {max_length} exceeds this server's per-session capacity {self.kv_capacity}")
-        kv = self.kv.allocate(sid, self.kv_capacity, timeout=metadata.get("alloc_timeout"))
+        mgr = self._view(metadata)[1]
+        kv = mgr.allocate(sid, self.kv_capacity, timeout=metadata.get("alloc_timeout"))
         kv.limit = max_length
         self.streams_open += 1
         deadline = time.monotonic() + float(metadata.get("session_timeout", self.session_timeout))
@@ -341,6 +371,8 @@ class StageConnectionHandler:
                 md = dict(md)
                 md.setdefault("session_id", sid)
                 md.setdefault("max_length", max_length)
+                if metadata.get("blocks"):
+                    md.setdefault("blocks", metadata["blocks"])
                 if md.get("is_prefill") and kv.length == 0 and steps == 0:
                     md["is_prefill"] = False          # the cache of this stream exists already: append, do not re-allocate
                     md.setdefault("start_from_position", 0)
@@ -352,7 +384,7 @@ class StageConnectionHandler:
                 steps += 1
         finally:
             self.streams_open -= 1
-            self.kv.close(sid)
+            mgr.close(sid)
             logger.info("[%s] inference stream ended after %d steps (%s)", str(sid)[:8], steps, reason)
         return [], {"session_id": sid, "steps": steps, "ended": reason}
 
@@ -374,9 +406,15 @@ class StageConnectionHandler:
         ok, rtt = check_direct_reachability(metadata["maddr"], float(metadata.get("timeout", 2.0)))
         return [], {"reachable": ok, "rtt_s": rtt}
 
+    def _close_everywhere(self, sid: str) -> bool:
+        closed = self.kv.close(sid)
+        for _, mgr, _ in self._views.values():
+            closed = mgr.close(sid) or closed
+        return closed
+
     def _close(self, sid: str) -> bool:
         self._stepping.pop(sid, None)
-        closed = self.kv.close(sid)
+        closed = self._close_everywhere(sid)
         mirror = getattr(self.stage_model, "close_session", None)     # tensor-parallel stage: the followers' shards
         if closed and mirror is not None:
             mirror(sid)
@@ -387,7 +425,7 @@ class StageConnectionHandler:
         if getattr(self.stage_model, "close_session", None) is not None:
             return [], {"closed": self._submit(self._close, sid, kind="inference")}    # serialised with the steps
         self._stepping.pop(sid, None)
-        return [], {"closed": self.kv.close(sid)}
+        return [], {"closed": self._close_everywhere(sid)}
 
     def shutdown(self) -> None:
         stop = getattr(self.stage_model, "stop_followers", None)

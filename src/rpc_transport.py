@@ -53,6 +53,7 @@ class Hop:
         self.addr = (host, port)
         self.start_block, self.end_block = start_block, end_block
         self.box: Optional[str] = None        # machine id of the server, asked on first use (device hand-off)
+        self.partial = False                  # module routing: the session enters this server's span mid-way
 
 
 class RpcTransport:
@@ -139,14 +140,18 @@ class RpcTransport:
                      if str(e.get("peer_id")) not in exclude and e.get("p2p_maddrs")
                      and e.get("state", "online") != "offline"
                      and e.get("start_block") is not None and int(e["start_block"]) <= b < int(e["end_block"])]
-            # a replacement must START at b: its cache holds nothing for blocks before b otherwise
+            if not cands:
+                raise ConnectionError(f"no live server holds block {b} of {self.model_name}")
+            # prefer a server whose span STARTS at b (it runs its whole span: batched steps, one graph); any server
+            # that covers b will do otherwise - it is asked for blocks [b, its end) only (md["blocks"], served from
+            # a view over its span with caches of its own)
             aligned = [e for e in cands if int(e["start_block"]) == b]
-            if not aligned:
-                raise ConnectionError(f"no live server starts at block {b} of {self.model_name}")
-            best = max(aligned, key=lambda e: (int(e["end_block"]), float(e.get("throughput") or 0.0)))
+            best = max(aligned or cands, key=lambda e: (int(e["end_block"]), float(e.get("throughput") or 0.0)))
             end = int(best["end_block"])
-            hops.append(Hop(f"block_{b}", best, final=bool(best.get("final_stage")) or end >= self.total_blocks,
-                            start_block=b, end_block=end))
+            hop = Hop(f"block_{b}", best, final=bool(best.get("final_stage")) or end >= self.total_blocks,
+                      start_block=b, end_block=end)
+            hop.partial = int(best["start_block"]) != b
+            hops.append(hop)
             b = end
         return hops
 
@@ -196,6 +201,9 @@ class RpcTransport:
         """One step on one hop.  ``desc``: the producer's hand-off descriptor of ``tensor`` (passed through untouched
         when the hop can pull it itself); ``consumer_in_box``: whoever reads this hop's output shares the box."""
         tensors = [tensor]
+        if hop.partial:
+            md = dict(md)
+            md["blocks"] = [int(hop.start_block), int(hop.end_block)]
         if tensor.is_cuda:
             if self._in_box(hop):
                 md = dict(md)
@@ -223,6 +231,8 @@ class RpcTransport:
                 open_md = {"session_id": sid, "max_length": md.get("max_length") or self.session_max_length.get(sid)}
                 if open_md["max_length"] is None:
                     del open_md["max_length"]
+                if md.get("blocks"):
+                    open_md["blocks"] = md["blocks"]
                 if self.session_timeout is not None:
                     open_md["session_timeout"] = self.session_timeout
                 if self.step_timeout is not None:

@@ -212,3 +212,37 @@ def test_offloaded_native_span_equals_resident_span(name, keep):
         lb, tb = off.decode([kb], ids=ids[t:t + 1])
         assert torch.equal(la, lb) and torch.equal(ta, tb)
     assert off.bytes_streamed > 0
+
+
+@pytest.mark.parametrize("name", ["tiny-llama-gqa", "tiny-gpt2"])
+def test_subspan_views_chain_to_the_whole_span(name):
+    """Views over blocks [0,a) and [a,n) of one span (shared packed weights, own graphs and caches) run back to back
+    give bit-identical hidden states and logits to the whole span - the server side of a client that enters a span
+    mid-way."""
+    from petals_b200.runtime.kv_cache import KVCacheManager
+
+    dtype = torch.bfloat16
+    cfg, _, nat, _, mnat = _build(name, dtype)
+    n = cfg.n_layers
+    a = n // 2
+    lo, hi = nat.subspan(0, a), nat.subspan(a, n)
+    assert lo.has_embed and not lo.has_head and hi.has_head and not hi.has_embed
+    assert lo.layers[0] is nat.layers[0] and hi.layers[-1] is nat.layers[-1], "views share the packed weights"
+    dev = torch.device("cuda")
+    m_lo = KVCacheManager(a, cfg.n_kv_heads, cfg.head_dim, dtype, dev)
+    m_hi = KVCacheManager(n - a, cfg.n_kv_heads, cfg.head_dim, dtype, dev)
+    torch.manual_seed(5)
+    ids = torch.randint(0, cfg.vocab, (60,), device="cuda")
+    L = 40
+    kw, kl, kh = mnat.allocate("w", 256), m_lo.allocate("w", 256), m_hi.allocate("w", 256)
+    ref_logits, ref_tok = nat.prefill(kw, ids=ids[:L])
+    ref_logits, ref_tok = ref_logits.clone(), ref_tok.clone()
+    h = lo.prefill(kl, ids=ids[:L]).clone()
+    logits, tok = hi.prefill(kh, h_in=h)
+    assert torch.equal(logits, ref_logits) and torch.equal(tok, ref_tok)
+    for t in range(L, L + 8):
+        ref_logits, ref_tok = (x.clone() for x in nat.decode([kw], ids=ids[t:t + 1]))
+        h = lo.decode([kl], ids=ids[t:t + 1]).clone()
+        logits, tok = hi.decode([kh], h_in=h)
+        assert torch.equal(logits, ref_logits) and torch.equal(tok, ref_tok), f"step {t}"
+    assert kl.length == kh.length == kw.length == L + 8
