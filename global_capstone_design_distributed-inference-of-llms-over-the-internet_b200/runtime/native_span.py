@@ -166,20 +166,9 @@ class NativeSpan:
             # the sessions of the next step is one host-to-device copy: positions of the step's tokens, the step number
             # the flag chain tags its words with, the sampler rows of the sessions (device-side sampling, see
             # enable_sampling) and, behind them, the table of cache pointers [layer][token][K, V].
-            mb = self.max_batch
-            self._n_pos = 2 * mb + 1
-            n_head = (self._n_pos + 1) // 2 * 2                     # the int64 table starts 8-byte aligned
-            n_tab = max(nl, 1) * mb * 2
-            self._stage_dev = torch.zeros(n_head + 2 * n_tab, dtype=torch.int32, device=self.device)
-            self._n_stage_head = n_head
-            self.pos = self._stage_dev[:self._n_pos]
-            self.kv_ptrs = self._stage_dev[n_head:].view(torch.int64).view(max(nl, 1), mb, 2)
-            self.step_seq = self.pos[mb:mb + 1]
-            self.samp_idx = self.pos[mb + 1:]
+            self._make_stage_buffers(nl)
             self.sampler = None
             self._seq_host = 0
-            self._pos_ring = [(torch.zeros(n_head + 2 * n_tab, dtype=torch.int32).pin_memory(), torch.cuda.Event())
-                              for _ in range(8)]
             self.chain_tokens = 0
             if (CHAIN_MAX_TOKENS > 0 and not fp8 and self.layers
                     and all(G.chain_capable(P[k]) for P in self.layers for k in ("qkv", "o", "mlp_in", "down"))):
@@ -203,6 +192,23 @@ class NativeSpan:
     def n_layers(self) -> int:
         return len(self.layers) + self.streamed_layers
 
+    def _make_stage_buffers(self, nl: int) -> None:
+        """The per-step staging buffer (positions | step number | sampler rows | cache pointer table) and its pinned
+        host ring, for a span of ``nl`` blocks."""
+        mb = self.max_batch
+        self._n_pos = 2 * mb + 1
+        n_head = (self._n_pos + 1) // 2 * 2                     # the int64 table starts 8-byte aligned
+        n_tab = max(nl, 1) * mb * 2
+        self._stage_dev = torch.zeros(n_head + 2 * n_tab, dtype=torch.int32, device=self.device)
+        self._n_stage_head = n_head
+        self.pos = self._stage_dev[:self._n_pos]
+        self.kv_ptrs = self._stage_dev[n_head:].view(torch.int64).view(max(nl, 1), mb, 2)
+        self.step_seq = self.pos[mb:mb + 1]
+        self.samp_idx = self.pos[mb + 1:]
+        self._pos_ring = [(torch.zeros(n_head + 2 * n_tab, dtype=torch.int32).pin_memory(), torch.cuda.Event())
+                          for _ in range(8)]
+        self._pos_ring_idx = 0
+
     def subspan(self, a: int, b: int) -> "NativeSpan":
         """A view that runs only blocks [a, b) of this span: same packed weights and work buffers, its own graphs and
         plans.  Lets a client enter (or leave) a server's span at any block - upstream addresses blocks one by one
@@ -220,6 +226,9 @@ class NativeSpan:
         v.has_head = self.has_head and b == len(self.layers)
         v._graphs, v._launches_per_graph, v._prefill_plans, v._ptr_tables = {}, {}, {}, {}
         v._ptr_key = None
+        v.__dict__.pop("_graph_out", None)
+        with torch.cuda.device(self.device):
+            v._make_stage_buffers(b - a)       # its graphs read its own positions and cache pointers
         return v
 
     def _iter_layers(self):
@@ -565,16 +574,22 @@ class NativeSpan:
         if key != self._ptr_key:
             tab = self._ptr_tables.get(key)       # host-side table per session tuple (the addresses determine it)
             if tab is None:
-                tab = torch.zeros(max(self.n_layers, 1), self.max_batch, 2, dtype=torch.int64)
+                # (a served stage batches whatever sessions are queued, so new tuples are the common case there: the
+                # table is assembled from one cached [layers, 2] column per session, not element by element)
+                nl = self.n_layers
+                tab = torch.zeros(max(nl, 1), self.max_batch, 2, dtype=torch.int64)
                 for b, kv in enumerate(kvs):
                     if kv.max_len != self.kv_capacity:
                         raise ValueError(f"session capacity {kv.max_len} != engine kv_capacity {self.kv_capacity}")
-                    base = kv.data.data_ptr()
-                    per_layer = kv.data.stride(0) * kv.data.element_size()
-                    half = kv.data.stride(1) * kv.data.element_size()
-                    for li in range(self.n_layers):
-                        tab[li, b, 0] = base + li * per_layer
-                        tab[li, b, 1] = base + li * per_layer + half
+                    col = getattr(kv, "_ptr_col", None)
+                    if col is None or col.shape[0] != nl or int(col[0, 0]) != kv.data.data_ptr():
+                        base = kv.data.data_ptr()
+                        per_layer = kv.data.stride(0) * kv.data.element_size()
+                        half = kv.data.stride(1) * kv.data.element_size()
+                        k_ptr = base + torch.arange(max(nl, 1), dtype=torch.int64) * per_layer
+                        col = kv._ptr_col = torch.stack([k_ptr, k_ptr + half], 1)
+                    if nl:
+                        tab[:, b] = col
                 if len(self._ptr_tables) > 256:
                     self._ptr_tables.clear()
                 self._ptr_tables[key] = tab

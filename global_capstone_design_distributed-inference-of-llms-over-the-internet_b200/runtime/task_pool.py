@@ -118,16 +118,22 @@ class PrioritizedTaskPool:
 
     def _linger(self, first) -> None:
         """Lock held: wait (releasing the lock) until as many items of ``first``'s function are queued as the caller
-        expects, at most ``batch_linger`` seconds."""
+        expects - at most ``batch_linger`` seconds in total, and only while items keep coming (a quiet gap of a
+        quarter of the linger ends the wait: the missing sessions are in the other phase, not on their way)."""
         batch_fn, _, max_batch = first[4]
         deadline = time.monotonic() + self.batch_linger
+        gap = self.batch_linger / 4
+        seen = -1
         while not self._stop:
             want = min(int(self.expect()), max_batch)
             have = 1 + sum(1 for e in self._heap if e[3] is _BATCH and e[4][0] == batch_fn)
             left = deadline - time.monotonic()
             if have >= want or left <= 0 or want - have > self.linger_max_missing:
                 return
-            self._cv.wait(left)
+            if have == seen:
+                return                              # a whole gap without a new arrival
+            seen = have
+            self._cv.wait(min(left, gap))
 
     def _run(self) -> None:
         while True:

@@ -52,7 +52,7 @@ class StageConnectionHandler:
                  attn_cache_tokens: Optional[int] = None, session_ttl: float = 600.0, start_block: Optional[int] = None,
                  end_block: Optional[int] = None, throughput: float = 0.0, seed: Optional[int] = None,
                  alloc_timeout: float = 10.0, session_timeout: float = 30 * 60.0, step_timeout: float = 5 * 60.0,
-                 max_batch: Optional[int] = None, batch_linger: float = 0.0005):
+                 max_batch: Optional[int] = None, batch_linger: float = 0.001):
         self.dht = dht
         self.stage_model = stage_model
         self.device = torch.device(device)
