@@ -219,7 +219,8 @@ def start_stage_server(args, device, stage_model, final_stage: bool, stage_index
                                      step_timeout=getattr(args, "step_timeout", 5 * 60.0),
                                      max_batch=getattr(args, "max_batch", None),
                                      batch_linger=getattr(args, "batch_linger_ms", 1.0) * 1e-3)
-    sys.setswitchinterval(2e-4)   # many handler threads + one compute thread: hand the GIL over faster than every 5 ms
+    # many handler threads + one compute thread: hand the GIL over faster than CPython's 5 ms default
+    sys.setswitchinterval(float(os.environ.get("B200_GIL_SWITCH_US", "200")) * 1e-6)
     stop = threading.Event()
     model_name = args.model
     handler.on_die = lambda: (stop.set(), rpc.stop())   # scripted kill (tests / kill_stage.py --soft)
