@@ -21,17 +21,6 @@ class AttnDecodeArgs(C.Structure):
     ]
 
 
-def chain_op_type():
-    from .native import GemmArgs
-
-    class ChainOpArgs(C.Structure):
-        """Mirror of ``b200_chain_op``."""
-
-        _fields_ = [("type", i32), ("reserved", i32), ("gemm", GemmArgs), ("attn", AttnDecodeArgs)]
-
-    return ChainOpArgs
-
-
 class SampleRow(C.Structure):
     """Mirror of ``b200::SampleRow`` (csrc/sampling.cu)."""
 
@@ -52,10 +41,6 @@ PROTOTYPES = [
     ("b200_hop_send", [C.POINTER(HopArgs), vp], C.c_int),
     ("b200_hop_recv", [C.POINTER(HopArgs), vp], C.c_int),
     ("b200_hop_init", [], C.c_int),
-    ("b200_decode_chain_plan_bytes", [i32], i64),
-    ("b200_decode_chain_max_attn_group", [], i32),
-    ("b200_decode_chain_build", [vp, i32, i32, vp], C.c_int),
-    ("b200_decode_chain_launch", [vp, i32, i32, i32, i32, i32, vp], C.c_int),
     ("b200_ll_publish", [vp, i32, vp, i32, i32, i32, vp, i32, i32, vp], C.c_int),
     ("b200_trace_set", [vp, i32], C.c_int),
     ("b200_argmax_partial", [vp, i32, i32, i32, vp, vp, vp, vp, i32, i32, vp, vp, i32, vp], C.c_int),

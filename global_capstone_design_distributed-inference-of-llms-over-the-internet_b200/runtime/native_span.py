@@ -42,14 +42,12 @@ MAX_DECODE_BATCH = 32
 RSTD_KERNEL_MIN_TOKENS = int(os.environ.get("B200_RSTD_KERNEL_MIN_TOKENS", "8"))
 # Decode steps of up to this many tokens run as a flag chain (b200_ll_chain): the kernels of the step hand their
 # activations over as self-validating words instead of waiting for each other's grids.  Bit-identical to the
-# grid-ordered step, but measured SLOWER on Llama-2-7B batch-1 decode (1xB200): 352 tok/s as one launch per op
-# (B200_CHAIN_KERNEL=0), 259 tok/s as one persistent launch (csrc/decode_chain.cu), against 361 tok/s grid-ordered -
-# the per-launch timeline (profiles/decode_timeline_r2_*.txt) shows that what a launch boundary costs is not the
+# grid-ordered step, but measured SLOWER on Llama-2-7B batch-1 decode (1xB200): 352 tok/s against 361 tok/s
+# grid-ordered (a persistent single-launch variant of the chain reached 259 tok/s and was removed again, see DESIGN
+# 2.2) - the per-launch timeline (profiles/decode_timeline_r2_*.txt) shows that what a launch boundary costs is not the
 # grid-completion signal but the start-up of the next kernel's CTAs, which cannot be resident before the previous
 # kernel's CTAs leave.  So the chain is OFF by default (0); set B200_LL_CHAIN_MAX_TOKENS=4 to experiment.
 CHAIN_MAX_TOKENS = int(os.environ.get("B200_LL_CHAIN_MAX_TOKENS", "0"))
-# 1: the chained blocks of a step run as ONE persistent launch (csrc/decode_chain.cu); 0: one launch per op, chained
-CHAIN_KERNEL = os.environ.get("B200_CHAIN_KERNEL", "1") != "0"
 
 
 def _l2_prefetch_default():
@@ -286,8 +284,7 @@ class NativeSpan:
     def _decode_layers(self, T: int, h: torch.Tensor, with_head: bool = False) -> torch.Tensor:
         """h: [T, H] view of a static buffer; returns the buffer view holding the result.
 
-        ``with_head``: the caller will run the LM head on the result next; a persistent chain launch then takes the
-        head GEMM along (``self._head_done`` tells the caller)."""
+        ``with_head``: the caller will run the LM head on the result next."""
         self._head_done = False
         c, pdl = self.cfg, self.pdl
         other = self.h_b if h.data_ptr() == self.h_a.data_ptr() else self.h_a
@@ -304,8 +301,6 @@ class NativeSpan:
         chain = self._chain_on(T) and not self.streamed_layers
         if self.streamed_layers:
             mb = None                       # the next block's weights are not where a prefetch hint could point
-        if chain and CHAIN_KERNEL and self._chain_kernel_ok():
-            return self._decode_layers_chain_kernel(T, h, other, with_head)
         if chain:
             return self._decode_layers_chain(T, h, other, mb)
         for li, P in self._iter_layers():
@@ -335,80 +330,6 @@ class NativeSpan:
                      norm_b=P["ln2_b"], norm_eps=c.norm_eps, workspace=self.ws, pdl=pdl, prefetch=pf[2], rstd=rs)
             self._row_parallel(act, P["down"], h, h2, prefetch=pf[3])
             self._count(5)
-        return h
-
-    def _chain_kernel_ok(self) -> bool:
-        c = self.cfg
-        return (c.n_heads // c.n_kv_heads) <= native.lib().b200_decode_chain_max_attn_group() and c.head_dim in (64, 128)
-
-    def _decode_layers_chain_kernel(self, T: int, h: torch.Tensor, other: torch.Tensor, with_head: bool) -> torch.Tensor:
-        """All blocks of the step (and the head GEMM when it follows) as ONE persistent launch walking a plan of
-        chained ops (csrc/decode_chain.cu); the plan is built once per (tokens, input buffer, head) combination."""
-        import ctypes as C
-
-        from ..ops._prototypes import chain_op_type
-
-        L = native.lib()
-        key = (T, h.data_ptr(), bool(with_head and self.has_head))
-        plans = self.__dict__.setdefault("_chain_plans", {})
-        plan = plans.get(key)
-        c = self.cfg
-        h_ll = self.h_a_ll if h.data_ptr() == self.h_a.data_ptr() else self.h_b_ll
-        if plan is None:
-            Op = chain_op_type()
-            ops = []
-            o_ll = self.h_b_ll if h_ll is self.h_a_ll else self.h_a_ll
-            qkv, attn, act, h2 = self.qkv[:T], self.attn[:T], self.act[:T], other[:T]
-            state = {"op": 1, "half": 0}
-
-            def gemm(x, w, x_ll, x_op, out, out_ll, res=None, res_ll=None, res_op=0, **kw):
-                state["op"] += 1
-                self._chain_half = state["half"]
-                a, _ = G.fill_args(x, w, out=out, residual=res, workspace=self.ws, pdl=True,
-                                   chain=self._link(x_ll, x_op, out_ll, state["op"], res_ll, res_op), **kw)
-                state["half"] ^= 1
-                o = Op()
-                o.type = 0
-                o.gemm = a
-                ops.append(o)
-                return state["op"]
-
-            h_op = 1
-            for li, P in enumerate(self.layers):
-                q_op = gemm(h, P["qkv"], h_ll, h_op, qkv, self.qkv_ll, norm_mode=self.norm_mode, norm_w=P["ln1_w"],
-                            norm_b=P["ln1_b"], norm_eps=c.norm_eps)
-                state["op"] += 1
-                a_op = state["op"]
-                aa = A.fill_decode_args(qkv, attn, self.kv_ptrs[li], self.pos, self.inv_freq, self.attn_ws, c.n_heads,
-                                        c.n_kv_heads, c.head_dim, self.kv_capacity, self.scale, True)
-                aa.chain = self._link(self.qkv_ll, q_op, self.attn_ll, a_op)
-                o = Op()
-                o.type = 1
-                o.attn = aa
-                ops.append(o)
-                o_op = gemm(attn, P["o"], self.attn_ll, a_op, h2, o_ll, res=h, res_ll=h_ll, res_op=h_op)
-                m_op = gemm(h2, P["mlp_in"], o_ll, o_op, act, self.act_ll, epilogue=self.mlp_epi,
-                            norm_mode=self.norm_mode, norm_w=P["ln2_w"], norm_b=P["ln2_b"], norm_eps=c.norm_eps)
-                h_op = gemm(act, P["down"], self.act_ll, m_op, h, h_ll, res=h2, res_ll=o_ll, res_op=o_op)
-            if key[2]:
-                gemm(h, self.lm_head, h_ll, h_op, self.logits[:T], None, norm_mode=self.norm_mode,
-                     norm_w=self.final_norm_w, norm_b=self.final_norm_b, norm_eps=c.norm_eps, out_fp32=True)
-            n = len(ops)
-            arr = (Op * n)(*ops)
-            grid = 2 * L.b200_sm_count()
-            dev_plan = torch.empty(L.b200_decode_chain_plan_bytes(n), dtype=torch.uint8, device=self.device)
-            with torch.cuda.device(self.device):
-                native.check(L.b200_decode_chain_build(arr, n, grid, dev_plan.data_ptr()), "b200_decode_chain_build")
-            plan = (dev_plan, n, grid, h_op)
-            plans[key] = plan
-        dev_plan, n, grid, h_op = plan
-        E.ll_publish(h, h_ll, self.step_seq, 1, pdl=True)      # head of the chain: waits for whatever produced h
-        native.check(L.b200_decode_chain_launch(dev_plan.data_ptr(), n, grid, c.head_dim, c.n_heads // c.n_kv_heads, 1,
-                                                native.current_stream_ptr()),
-                     "b200_decode_chain_launch")
-        self._count(2)
-        self._head_done = key[2]
-        self._chain_tail = None
         return h
 
     def _chain_on(self, T: int) -> bool:

@@ -256,31 +256,6 @@ int b200_attn_prefill(const void* q, void* out, const void* kcache, const void* 
                       int32_t n_kv_heads, int32_t head_dim, int32_t s_max, int32_t ldq, int32_t ldo, int32_t pos0,
                       float scale, int32_t dtype, int32_t pdl, void* stream);
 
-/* --------------------------------------------------- persistent decode chain --
- * ONE launch for all blocks of a decode step (and the LM head): the grid - two CTAs per SM - stays resident and walks a
- * list of GEMM and attention ops whose inputs and outputs are flag-chain words (b200_ll_chain).  There is no grid
- * barrier and no launch boundary between ops: an op starts on a CTA as soon as the words that CTA needs carry the
- * producing op's tag, the weight loader streams ahead across op boundaries.  Results are bit-identical to the
- * per-launch kernels.  The op before the first one must have published its output with b200_ll_publish (or be a
- * chain link itself); launch with pdl = 1 right behind it.  Ops: b200_gemm_args (T <= 16, 16-bit weights, ll_buf,
- * .chain filled; scratch / counters unused) or b200_attn_decode_args (head_dim 64/128, GQA group 1/2/4, ll_scratch,
- * .chain filled).  Replaces the reference's eager per-op block loop (src/llama_partition.py:233-297).
- *   b200_decode_chain_build   validates the ops and writes the device plan (synchronous copy; plan_device holds
- *                             b200_decode_chain_plan_bytes(n_ops) bytes); grid = the grid of the later launches.
- *   b200_decode_chain_launch  grid <= 2 x SM count; every CTA must be co-resident (nothing else may fill the GPU);
- *                             head_dim / gqa_group = the attention shape of the plan's ops. */
-typedef struct b200_chain_op {
-    int32_t type; /* 0 = GEMM, 1 = attention */
-    int32_t reserved;
-    b200_gemm_args gemm;
-    b200_attn_decode_args attn;
-} b200_chain_op;
-int64_t b200_decode_chain_plan_bytes(int32_t n_ops);
-int32_t b200_decode_chain_max_attn_group(void);
-int b200_decode_chain_build(const b200_chain_op* ops, int32_t n_ops, int32_t grid, void* plan_device);
-int b200_decode_chain_launch(const void* plan_device, int32_t n_ops, int32_t grid, int32_t head_dim, int32_t gqa_group,
-                             int32_t pdl, void* stream);
-
 /* Same contract on the tensor cores: 128-query x 128-key tiles, S = QK^T and O = PV by tcgen05.mma
  * (V consumed in place as an MN-major operand), online softmax between them, accumulators in TMEM. */
 int b200_attn_prefill_tc(const void* q, void* out, const void* kcache, const void* vcache, int32_t T, int32_t n_heads,

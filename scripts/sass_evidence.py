@@ -2,7 +2,7 @@
 Writes profiles/sass_tcgen05_evidence.txt."""
 import collections, os, re, subprocess, sys, tempfile
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-SRC = ["gemm.cu", "gemm_prefill.cu", "attn_prefill_tc.cu", "attention.cu", "decode_chain.cu", "tp_nvls.cu", "p2p.cu",
+SRC = ["gemm.cu", "gemm_prefill.cu", "attn_prefill_tc.cu", "attention.cu", "tp_nvls.cu", "p2p.cu",
        "elementwise.cu", "sampling.cu"]
 WANT = ["UTCHMMA", "UTCQMMA", "UTCCP", "UBLKCP", "UTMALDG", "LDTM", "STTM", "UTCBAR", "SYNCS", "USETMAXREG", "UTMAPF", "UBLKPF",
         "LDGMC", "STGMC"]

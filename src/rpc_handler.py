@@ -78,6 +78,7 @@ class StageConnectionHandler:
         # sessions that made a decode step in the last 50 ms are expected to make the next one together: the pool
         # waits up to batch_linger for them before it runs a batched step (0 = never wait)
         self._stepping: Dict[str, float] = {}
+        self.batch_seconds: Dict[str, float] = {}
         self.batch_linger = float(batch_linger)
         self.pool = PrioritizedTaskPool("stage", batch_linger=self.batch_linger if self.max_batch > 1 else 0.0,
                                         expect=self._expected_batch)
@@ -239,6 +240,7 @@ class StageConnectionHandler:
         """One batched decode step for every queued single-token request (different sessions).  Returns one
         reply - or one exception - per request, so a bad request does not fail its neighbours."""
         results: list = [None] * len(items)
+        t0 = time.perf_counter()
         ready = []
         seen = set()
         for i, (hidden, md) in enumerate(items):
@@ -265,15 +267,21 @@ class StageConnectionHandler:
             try:
                 H = ready[0][1].shape[-1]
                 h = torch.cat([r[1].reshape(1, H) for r in ready], 0)
+                t1 = time.perf_counter()
                 to_cpu = not self.final_stage and not any(r[2].get("device_handoff") for r in ready)
                 outs = self.stage_model.decode_batch(h, [r[4] for r in ready], to_cpu=to_cpu)
                 ids = getattr(self.stage_model, "last_greedy_ids", None)
+                t2 = time.perf_counter()
                 self.requests += len(ready)
                 for b, ((i, _, md, sid, _), o) in enumerate(zip(ready, outs)):
                     if ids is not None and float(md.get("temperature", self._default_temperature)) <= 0.0:
                         results[i] = ([torch.tensor([[ids[b]]], dtype=torch.long)], {"token_id": ids[b], "session_id": sid})
                     else:
                         results[i] = self._finish(o, md, sid)
+                t3 = time.perf_counter()
+                # where a batched step's wall time goes (rpc_info: batch_ms) - prepare / engine step / replies
+                for k, v in (("prepare", t1 - t0), ("step", t2 - t1), ("finish", t3 - t2)):
+                    self.batch_seconds[k] = self.batch_seconds.get(k, 0.0) + v
             except BaseException as e:  # noqa: BLE001
                 for i, *_ in ready:
                     results[i] = e
@@ -397,6 +405,7 @@ class StageConnectionHandler:
                     "max_batch": self.max_batch, "batches": self.pool.batches,
                     "mean_batch": (self.pool.batched_items / self.pool.batches) if self.pool.batches else 0.0,
                     "streams_open": self.streams_open, "uptime_s": time.time() - self.started,
+                    "batch_ms": {k: round(v * 1e3 / max(self.pool.batches, 1), 3) for k, v in self.batch_seconds.items()},
                     "box": self.box(), "handoff_out": self.handoff_out, "handoff_in": self.handoff_in}
 
     def rpc_check(self, uid: str, tensors, metadata: Dict):

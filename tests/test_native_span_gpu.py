@@ -94,15 +94,12 @@ def test_fp8_weight_span_tracks_the_oracle(fmt):
 
 @pytest.mark.parametrize("name", ["tiny-llama", "tiny-llama-gqa", "tiny-gpt2"])
 @pytest.mark.parametrize("graphs", [True, False])
-@pytest.mark.parametrize("persistent", [True, False])
-def test_flag_chained_decode_is_bit_identical(name, graphs, persistent, monkeypatch):
-    """A decode step run as a flag chain (ops poll tagged words instead of waiting for each other's grids) - as one
-    persistent launch walking an op list, or as one launch per op - must give exactly the logits of the grid-ordered
-    step: same arithmetic, same summation order - for 1..4 sessions per step, over several steps (stale words of an
+def test_flag_chained_decode_is_bit_identical(name, graphs, monkeypatch):
+    """A decode step run as a flag chain (ops poll tagged words instead of waiting for each other's grids) must give
+    exactly the logits of the grid-ordered step: same arithmetic, same summation order - for 1..4 sessions per step, over several steps (stale words of an
     earlier step must never be taken for new ones)."""
     from petals_b200.runtime import native_span
 
-    monkeypatch.setattr(native_span, "CHAIN_KERNEL", persistent)
     monkeypatch.setattr(native_span, "CHAIN_MAX_TOKENS", 4)      # off by default (measured slower); tested all the same
     cfg, _, chain, _, m1 = _build(name, torch.bfloat16, use_graphs=graphs)
     _, _, plain, _, m2 = _build(name, torch.bfloat16, use_graphs=graphs)
