@@ -40,9 +40,8 @@ extern "C" int b200_sm_count(void) { return b200::sm_count_cached(); }
 // caller; NULL switches the trace off again.
 extern "C" int b200_trace_set_gemm(void*, int);
 extern "C" int b200_trace_set_attn(void*, int);
-extern "C" int b200_trace_set_chain(void*, int);
 extern "C" int b200_trace_set(void* buf, int32_t cap) {
-    if (b200_trace_set_gemm(buf, cap) != 0 || b200_trace_set_attn(buf, cap) != 0 || b200_trace_set_chain(buf, cap) != 0)
+    if (b200_trace_set_gemm(buf, cap) != 0 || b200_trace_set_attn(buf, cap) != 0)
         return b200::fail(B200_ECUDA, "b200_trace_set: cudaMemcpyToSymbol failed");
     return B200_OK;
 }

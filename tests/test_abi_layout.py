@@ -47,3 +47,20 @@ def test_ctypes_structs_match_the_header(tmp_path):
     assert out["attn"] == [ctypes.sizeof(AttnDecodeArgs), AttnDecodeArgs.scale.offset, AttnDecodeArgs.ll_scratch.offset,
                            AttnDecodeArgs.chain.offset]
     assert out["hop"] == [ctypes.sizeof(HopArgs), HopArgs.counter.offset, HopArgs.pdl.offset]
+
+
+def test_library_loads_with_every_symbol_resolved():
+    """The in-tree library must dlopen with immediate binding (a dangling reference between translation units only
+    shows at load time) and export every entry point the Python layer registers; no GPU needed for either."""
+    import ctypes
+    import os
+
+    from petals_b200.ops import native
+
+    if not os.path.exists(native.LIB_PATH):
+        import pytest
+
+        pytest.skip("library not built (python csrc/build.py)")
+    ctypes.CDLL(native.LIB_PATH, mode=os.RTLD_NOW)
+    L = native.lib()                       # registers all prototypes: a missing export raises AttributeError
+    assert L.b200_version() > 0

@@ -95,10 +95,10 @@ def test_served_chain_device_handoff_token_exact(push):
     procs = [ctx.Process(target=_server, args=(1, 1 % n_gpu, p1, "", model, splits, r1), daemon=True)]
     procs[0].start()
     try:
-        assert r1.wait(300)
+        assert r1.wait(120)
         procs.append(ctx.Process(target=_server, args=(2, 2 % n_gpu, p2, peers, model, splits, r2), daemon=True))
         procs[1].start()
-        assert r2.wait(300)
+        assert r2.wait(120)
 
         def client(handoff):
             a = _args(model, splits, 0, 0, dht_initial_peers=peers, max_new_tokens=12, prompt="the quick brown fox jumps",
@@ -156,7 +156,7 @@ def test_killed_replica_is_recovered_from_the_device_journal(tmp_path):
             p.start()
             procs.append(p)
             events.append(ev)
-            assert ev.wait(300)
+            assert ev.wait(120)
 
         def client(handoff):
             a = _args(model, splits, 0, 0, dht_initial_peers=peers, max_new_tokens=14, prompt="one two three four five",
