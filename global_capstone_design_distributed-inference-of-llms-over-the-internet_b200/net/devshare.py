@@ -105,7 +105,7 @@ class DeviceImporter:
     def __init__(self, device: torch.device):
         self.device = torch.device(device)
         self.box = box_id()
-        self._open: Dict[Tuple[int, bytes], torch.Tensor] = {}
+        self._open: Dict[Tuple[int, bytes], int] = {}
         self.lock = threading.Lock()
         self.pulled_bytes = 0
         self.pulls = 0
@@ -113,7 +113,8 @@ class DeviceImporter:
     def accepts(self, desc: Optional[dict]) -> bool:
         return bool(desc) and desc.get("box") == self.box and self.device.type == "cuda"
 
-    def _arena(self, desc: dict) -> torch.Tensor:
+    def _arena(self, desc: dict) -> int:
+        """Base address of the exporter's arena in THIS process (opened once per exporter)."""
         key = (int(desc["pid"]), bytes(desc["handle"]))
         with self.lock:
             a = self._open.get(key)
@@ -123,11 +124,14 @@ class DeviceImporter:
                 driver, runtime = _rt()
                 h = runtime.cudaIpcMemHandle_t()
                 h.reserved = bytes(desc["handle"])
+                # The mapping belongs to the context that opens it: open it under the CONSUMER's device (peer access to
+                # the exporter's GPU is enabled on the way) and copy with a plain cudaMemcpyAsync from that same
+                # context.  (Wrapping the pointer in a torch tensor would make torch issue the copy from the exporting
+                # GPU's context of this process, where the mapping does not exist: illegal address across GPUs.)
                 with torch.cuda.device(self.device):
                     err, ptr = runtime.cudaIpcOpenMemHandle(h, runtime.cudaIpcMemLazyEnablePeerAccess)
                     _check(err, "cudaIpcOpenMemHandle")
-                a = _wrap(int(ptr), int(desc["arena_bytes"]), None)
-                self._open[key] = a
+                a = self._open[key] = int(ptr)
             return a
 
     def pull(self, desc: dict, local: Optional[torch.Tensor] = None) -> torch.Tensor:
@@ -136,12 +140,20 @@ class DeviceImporter:
             raise RuntimeError("device descriptor from another machine")
         n, off = int(desc["nbytes"]), int(desc["offset"])
         tail = _HDR + ((n + 15) // 16) * 16
+        total = tail + _HDR
+        if off < 0 or off + total > int(desc["arena_bytes"]):
+            raise ValueError("hand-off descriptor points outside its arena")
+        buf = torch.empty(total, dtype=torch.uint8, device=self.device)
         if local is not None and int(desc["pid"]) == os.getpid():
-            src = local[off:off + tail + _HDR]                      # producer and consumer in one process (tests)
+            buf.copy_(local[off:off + total])                       # producer and consumer in one process (tests)
         else:
-            src = self._arena(desc)[off:off + tail + _HDR]
-        buf = torch.empty(tail + _HDR, dtype=torch.uint8, device=self.device)
-        buf.copy_(src)
+            base = self._arena(desc)
+            _, runtime = _rt()
+            with torch.cuda.device(self.device):
+                err, = runtime.cudaMemcpyAsync(buf.data_ptr(), base + off, total,
+                                               runtime.cudaMemcpyKind.cudaMemcpyDeviceToDevice,
+                                               torch.cuda.current_stream(self.device).cuda_stream)
+                _check(err, "cudaMemcpyAsync(peer slot)")
         seqs = torch.stack([buf[:8].view(torch.int64)[0], buf[tail:tail + 8].view(torch.int64)[0]]).tolist()
         if seqs[0] != int(desc["seq"]) or seqs[1] != int(desc["seq"]):
             raise StaleDeviceTensor(f"hand-off slot holds seq {seqs}, descriptor says {desc['seq']}")

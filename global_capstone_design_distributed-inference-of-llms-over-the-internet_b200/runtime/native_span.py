@@ -622,7 +622,8 @@ class NativeSpan:
         torch.cuda.synchronize(self.device)
         g = torch.cuda.CUDAGraph()
         self.kernel_launches = before
-        with torch.cuda.graph(g, stream=s):
+        # (thread_local: other threads of a server or client process keep making CUDA calls while this one captures)
+        with torch.cuda.graph(g, stream=s, capture_error_mode="thread_local"):
             out_h = self._decode_body(B, from_ids, greedy, prog)
         per = self.kernel_launches - before
         self.kernel_launches = before  # warm-up + capture passes touched KV slot `pos` twice; harmless: same data
@@ -675,7 +676,7 @@ class NativeSpan:
             torch.cuda.synchronize(self.device)
             per = self.kernel_launches - before
             g = torch.cuda.CUDAGraph()
-            with torch.cuda.graph(g, stream=s):
+            with torch.cuda.graph(g, stream=s, capture_error_mode="thread_local"):
                 body()
             self.kernel_launches = before
             self._graphs[key] = g
