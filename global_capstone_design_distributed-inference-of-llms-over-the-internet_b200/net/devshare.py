@@ -105,7 +105,7 @@ class DeviceImporter:
     def __init__(self, device: torch.device):
         self.device = torch.device(device)
         self.box = box_id()
-        self._open: Dict[Tuple[int, bytes], int] = {}
+        self._open: Dict[Tuple[int, bytes], Tuple[int, int]] = {}
         self.lock = threading.Lock()
         self.pulled_bytes = 0
         self.pulls = 0
@@ -113,8 +113,8 @@ class DeviceImporter:
     def accepts(self, desc: Optional[dict]) -> bool:
         return bool(desc) and desc.get("box") == self.box and self.device.type == "cuda"
 
-    def _arena(self, desc: dict) -> int:
-        """Base address of the exporter's arena in THIS process (opened once per exporter)."""
+    def _arena(self, desc: dict) -> Tuple[int, int]:
+        """(base address of the exporter's arena in THIS process, its device index here); opened once per exporter."""
         key = (int(desc["pid"]), bytes(desc["handle"]))
         with self.lock:
             a = self._open.get(key)
@@ -124,14 +124,14 @@ class DeviceImporter:
                 driver, runtime = _rt()
                 h = runtime.cudaIpcMemHandle_t()
                 h.reserved = bytes(desc["handle"])
-                # The mapping belongs to the context that opens it: open it under the CONSUMER's device (peer access to
-                # the exporter's GPU is enabled on the way) and copy with a plain cudaMemcpyAsync from that same
-                # context.  (Wrapping the pointer in a torch tensor would make torch issue the copy from the exporting
-                # GPU's context of this process, where the mapping does not exist: illegal address across GPUs.)
-                with torch.cuda.device(self.device):
+                # CUDA IPC maps the allocation into the context of the device it physically lives on: open it with THAT
+                # device current (as torch's own CUDA IPC does), then copy across with cudaMemcpyPeerAsync.  (Opened
+                # under the consumer's device instead, every access to the mapping is an illegal address.)
+                src = local_index(int(desc["gpu"]))
+                with torch.cuda.device(src):
                     err, ptr = runtime.cudaIpcOpenMemHandle(h, runtime.cudaIpcMemLazyEnablePeerAccess)
                     _check(err, "cudaIpcOpenMemHandle")
-                a = self._open[key] = int(ptr)
+                a = self._open[key] = (int(ptr), src)
             return a
 
     def pull(self, desc: dict, local: Optional[torch.Tensor] = None) -> torch.Tensor:
@@ -147,13 +147,13 @@ class DeviceImporter:
         if local is not None and int(desc["pid"]) == os.getpid():
             buf.copy_(local[off:off + total])                       # producer and consumer in one process (tests)
         else:
-            base = self._arena(desc)
+            base, src = self._arena(desc)
             _, runtime = _rt()
+            dst = self.device.index if self.device.index is not None else torch.cuda.current_device()
             with torch.cuda.device(self.device):
-                err, = runtime.cudaMemcpyAsync(buf.data_ptr(), base + off, total,
-                                               runtime.cudaMemcpyKind.cudaMemcpyDeviceToDevice,
-                                               torch.cuda.current_stream(self.device).cuda_stream)
-                _check(err, "cudaMemcpyAsync(peer slot)")
+                err, = runtime.cudaMemcpyPeerAsync(buf.data_ptr(), dst, base + off, src, total,
+                                                   torch.cuda.current_stream(self.device).cuda_stream)
+                _check(err, "cudaMemcpyPeerAsync(hand-off slot)")
         seqs = torch.stack([buf[:8].view(torch.int64)[0], buf[tail:tail + 8].view(torch.int64)[0]]).tolist()
         if seqs[0] != int(desc["seq"]) or seqs[1] != int(desc["seq"]):
             raise StaleDeviceTensor(f"hand-off slot holds seq {seqs}, descriptor says {desc['seq']}")
@@ -162,15 +162,29 @@ class DeviceImporter:
         return buf[_HDR:_HDR + n].view(_DTYPES[desc["dtype"]]).reshape(desc["shape"])
 
 
-def _physical_index(device: torch.device) -> int:
-    idx = device.index if device.index is not None else torch.cuda.current_device()
+def visible_gpus() -> list:
+    """Physical indices of the GPUs this process can address, in its own numbering order."""
     vis = os.environ.get("CUDA_VISIBLE_DEVICES")
     if vis:
         try:
-            return int(vis.split(",")[idx])
-        except (ValueError, IndexError):
+            return [int(v) for v in vis.split(",") if v.strip() != ""]
+        except ValueError:
             pass
-    return idx
+    return list(range(torch.cuda.device_count()))
+
+
+def local_index(physical: int) -> int:
+    """This process's device index of the GPU with the given physical index (raises when it is not visible here)."""
+    vis = visible_gpus()
+    if physical not in vis:
+        raise RuntimeError(f"GPU {physical} of the exporting process is not visible here (CUDA_VISIBLE_DEVICES)")
+    return vis.index(physical)
+
+
+def _physical_index(device: torch.device) -> int:
+    idx = device.index if device.index is not None else torch.cuda.current_device()
+    vis = visible_gpus()
+    return vis[idx] if idx < len(vis) else idx
 
 
 class _RawCuda:

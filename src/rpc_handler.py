@@ -192,6 +192,14 @@ class StageConnectionHandler:
             self._box = box_id()
         return self._box
 
+    def _gpu_ids(self):
+        """(physical index of this server's GPU, physical indices of the GPUs it can address) - what a client needs
+        to know before it offers device hand-off."""
+        if self.device.type != "cuda":
+            return None, []
+        from petals_b200.net.devshare import _physical_index, visible_gpus
+        return _physical_index(self.device), visible_gpus()
+
     def _export(self, out: torch.Tensor) -> dict:
         if self._exporter is None:
             from petals_b200.net.devshare import DeviceExporter
@@ -406,7 +414,7 @@ class StageConnectionHandler:
                     "mean_batch": (self.pool.batched_items / self.pool.batches) if self.pool.batches else 0.0,
                     "streams_open": self.streams_open, "uptime_s": time.time() - self.started,
                     "batch_ms": {k: round(v * 1e3 / max(self.pool.batches, 1), 3) for k, v in self.batch_seconds.items()},
-                    "box": self.box(), "handoff_out": self.handoff_out, "handoff_in": self.handoff_in}
+                    "box": self.box(), "gpu": self._gpu_ids()[0], "visible_gpus": self._gpu_ids()[1], "handoff_out": self.handoff_out, "handoff_in": self.handoff_in}
 
     def rpc_check(self, uid: str, tensors, metadata: Dict):
         """Dial-back probe for joining servers (upstream reachability.py rpc_check)."""

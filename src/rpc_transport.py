@@ -185,13 +185,18 @@ class RpcTransport:
         return md
 
     def _in_box(self, hop: Hop) -> bool:
-        """Does this hop's server run on a GPU of the client's own machine (asked once per server)?"""
+        """Can this hop's server and the client hand tensors over device to device: same machine, and each side can
+        address the other's GPU (asked once per server)?"""
         if not self.device_handoff:
             return False
         if hop.box is None:
             try:
+                from petals_b200.net.devshare import _physical_index, visible_gpus
                 _, info = self.client.call(hop.addr, f"{HANDLER_PREFIX}.rpc_info", hop.key, [], {}, timeout=5.0)
-                hop.box = info.get("box") or ""
+                mine = _physical_index(torch.device(self.device))
+                ok = (info.get("box") == self._box and mine in (info.get("visible_gpus") or [])
+                      and info.get("gpu") in visible_gpus())
+                hop.box = self._box if ok else ""
             except Exception:  # noqa: BLE001
                 hop.box = ""
         return hop.box == self._box
