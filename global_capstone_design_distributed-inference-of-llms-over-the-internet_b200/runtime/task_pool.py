@@ -54,11 +54,13 @@ class DummyTaskPrioritizer(TaskPrioritizerBase):
 class PrioritizedTaskPool:
     def __init__(self, name: str = "pool", max_task_tokens: Optional[int] = None,
                  prioritizer: Optional[TaskPrioritizerBase] = None, batch_linger: float = 0.0,
-                 expect: Optional[Callable[[], int]] = None, linger_max_missing: int = 3):
+                 expect: Optional[Callable[[], int]] = None, linger_max_missing: int = 3,
+                 thread_init: Optional[Callable[[], None]] = None):
         self.name = name
         self.batch_linger = float(batch_linger)
         self.expect = expect
         self.linger_max_missing = int(linger_max_missing)
+        self.thread_init = thread_init          # runs first on the worker thread (e.g. select the stage's GPU)
         self.max_task_tokens = max_task_tokens
         self.prioritizer = prioritizer or DummyTaskPrioritizer()
         self._heap: list = []
@@ -136,6 +138,8 @@ class PrioritizedTaskPool:
             self._cv.wait(min(left, gap))
 
     def _run(self) -> None:
+        if self.thread_init is not None:
+            self.thread_init()
         while True:
             with self._cv:
                 while not self._heap and not self._stop:

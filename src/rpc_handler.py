@@ -81,7 +81,7 @@ class StageConnectionHandler:
         self.batch_seconds: Dict[str, float] = {}
         self.batch_linger = float(batch_linger)
         self.pool = PrioritizedTaskPool("stage", batch_linger=self.batch_linger if self.max_batch > 1 else 0.0,
-                                        expect=self._expected_batch)
+                                        expect=self._expected_batch, thread_init=self._bind_device)
         self._fwd_client = RpcClient()
         self._gen = torch.Generator(device="cpu")
         if seed is not None:
@@ -166,7 +166,14 @@ class StageConnectionHandler:
             raise ValueError(f"session {str(sid)[:8]} would exceed max_length={limit} ({kv.length}+{T})")
         return sid, kv
 
+    def _bind_device(self) -> None:
+        """CUDA's current device is per host thread and starts at 0: the compute thread of a server on another GPU
+        must select its own before it launches anything (kernels take the current stream of the current device)."""
+        if self.device.type == "cuda":
+            torch.cuda.set_device(self.device)
+
     def _run_forward(self, hidden_states: torch.Tensor, metadata: Dict) -> Tuple[List[torch.Tensor], Dict]:
+        self._bind_device()
         if self.fail_next > 0:
             self.fail_next -= 1
             raise RuntimeError("injected failure")
@@ -247,6 +254,7 @@ class StageConnectionHandler:
     def _run_decode_batch(self, items: List[Tuple[torch.Tensor, Dict]]) -> list:
         """One batched decode step for every queued single-token request (different sessions).  Returns one
         reply - or one exception - per request, so a bad request does not fail its neighbours."""
+        self._bind_device()
         results: list = [None] * len(items)
         t0 = time.perf_counter()
         ready = []
