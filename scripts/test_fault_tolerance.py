@@ -42,6 +42,8 @@ def main():
     ap.add_argument("--device_handoff", action="store_true")
     ap.add_argument("--kv_capacity", type=int, default=0)
     ap.add_argument("--out", default="")
+    ap.add_argument("--port_base", type=int, default=18000)
+    ap.add_argument("--request_timeout", type=float, default=5.0)
     a = ap.parse_args()
     import torch
 
@@ -52,7 +54,7 @@ def main():
     n = len(cuts)
     kill_stage = a.kill_stage or n
     procs, logs, peers = {}, {}, ""
-    port = 18000
+    port = a.port_base
     try:
         for rep in range(2):
             for st in range(1, n + 1):
@@ -79,7 +81,7 @@ def main():
             stamps.clear()
             args = build_parser().parse_args(["--model", a.model, "--splits", a.splits, "--stage", "0", "--dtype", a.dtype,
                                               "--dht_initial_peers", peers, "--temperature", "0",
-                                              "--max_new_tokens", str(a.max_new_tokens), "--request_timeout", "5"])
+                                              "--max_new_tokens", str(a.max_new_tokens), "--request_timeout", str(a.request_timeout)])
             args.dtype = {"fp16": torch.float16, "bf16": torch.bfloat16, "fp32": torch.float32}[a.dtype]
             dev = torch.device("cuda", 0) if torch.cuda.is_available() and a.dtype != "fp32" else torch.device("cpu")
             args.device_handoff = a.device_handoff
