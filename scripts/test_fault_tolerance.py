@@ -40,6 +40,8 @@ def main():
     ap.add_argument("--hard", action="store_true", help="SIGKILL instead of SIGTERM")
     ap.add_argument("--gpus", type=int, default=0, help="spread the servers over GPUs 1..gpus-1 (client on GPU 0)")
     ap.add_argument("--device_handoff", action="store_true")
+    ap.add_argument("--device_handoff_min_kb", type=int, default=128)
+    ap.add_argument("--prompt", default="")
     ap.add_argument("--kv_capacity", type=int, default=0)
     ap.add_argument("--out", default="")
     ap.add_argument("--port_base", type=int, default=18000)
@@ -85,6 +87,9 @@ def main():
             args.dtype = {"fp16": torch.float16, "bf16": torch.bfloat16, "fp32": torch.float32}[a.dtype]
             dev = torch.device("cuda", 0) if torch.cuda.is_available() and a.dtype != "fp32" else torch.device("cpu")
             args.device_handoff = a.device_handoff
+            args.device_handoff_min_kb = a.device_handoff_min_kb
+            if a.prompt:
+                args.prompt = a.prompt
             args.no_repeat_stop = bool(a.kill_at_token)
             if a.kv_capacity:
                 args.kv_capacity = a.kv_capacity

@@ -106,7 +106,8 @@ def run_rank0(args, device, splits, dht: Optional[DHT] = None):
                       total_blocks=total_blocks, start_block=stage0_end, request_timeout=args.request_timeout,
                       repetition_penalty=getattr(args, "repetition_penalty", None), dht=dht,
                       push=getattr(args, "push", False), stream=getattr(args, "stream", False),
-                      device_handoff=getattr(args, "device_handoff", False))
+                      device_handoff=getattr(args, "device_handoff", False),
+                      device_handoff_min_bytes=int(getattr(args, "device_handoff_min_kb", 128)) << 10)
     session_id = str(uuid4())
     t_prefill_start = time.perf_counter()
     hidden, _ = s0(input_ids, None, None, kv0)
@@ -545,6 +546,8 @@ def build_parser() -> argparse.ArgumentParser:
     p.add_argument("--device_handoff", action="store_true",
                    help="client: servers on GPUs of this machine exchange hidden states device to device (CUDA IPC + "
                         "NVLink peer copies); the RPC messages to them carry a descriptor instead of the tensor")
+    p.add_argument("--device_handoff_min_kb", type=int, default=128,
+                   help="client: smallest payload that goes device to device (single tokens are cheaper in the frame)")
     p.add_argument("--no_repeat_stop", action="store_true",
                    help="client: keep generating when one token repeats 5 times (random-weight benchmarks)")
     p.add_argument("--gpu", type=int, default=None, help="CUDA device index of this process (default: LOCAL_RANK or 0)")

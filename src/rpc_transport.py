@@ -63,8 +63,12 @@ class RpcTransport:
                  total_blocks: int = 32, start_block: int = 0, request_timeout: float = 30.0,
                  repetition_penalty: Optional[float] = None, dht: Optional[DHT] = None, push: bool = False,
                  stream: bool = False, session_timeout: Optional[float] = None, step_timeout: Optional[float] = None,
-                 device_handoff: bool = False):
+                 device_handoff: bool = False, device_handoff_min_bytes: int = 128 << 10):
         self.device = device
+        # (measured on Llama-2-13B, 4xB200: for a single token's 10 KB the arena copy, the peer copy and their
+        # synchronisations cost more than the frame bytes they replace - 6.0 vs 4.7 ms per token - so only payloads
+        # from device_handoff_min_bytes upwards, i.e. prompts, go device to device)
+        self.device_handoff_min_bytes = int(device_handoff_min_bytes)
         # device_handoff: hops that live in this box exchange hidden states GPU to GPU (net/devshare.py); the TCP
         # messages to and from them carry a descriptor instead of the tensor
         self.device_handoff = bool(device_handoff) and device is not None and torch.device(device).type == "cuda"
@@ -209,8 +213,10 @@ class RpcTransport:
         if hop.partial:
             md = dict(md)
             md["blocks"] = [int(hop.start_block), int(hop.end_block)]
+        big = tensor.numel() * tensor.element_size() >= self.device_handoff_min_bytes
+        consumer_in_box = consumer_in_box and big          # a hop's output has its input's shape
         if tensor.is_cuda:
-            if self._in_box(hop):
+            if big and self._in_box(hop):
                 md = dict(md)
                 md["device_tensor"] = desc if desc is not None else self._exporter.export(tensor)
                 tensors = []
@@ -313,7 +319,8 @@ class RpcTransport:
 
     def _send(self, session_id: str, hidden: torch.Tensor, cur_len: int, is_prefill: bool,
               generated: Optional[Sequence[int]]) -> int:
-        cur = hidden.detach() if self.device_handoff and hidden.is_cuda else hidden.detach().to("cpu")
+        big = hidden.numel() * hidden.element_size() >= self.device_handoff_min_bytes
+        cur = hidden.detach() if self.device_handoff and hidden.is_cuda and big else hidden.detach().to("cpu")
         cur_desc = None
         T = cur.shape[-2]
         route = self._get_route(session_id)

@@ -102,7 +102,8 @@ def test_served_chain_device_handoff_token_exact(push):
 
         def client(handoff):
             a = _args(model, splits, 0, 0, dht_initial_peers=peers, max_new_tokens=12, prompt="the quick brown fox jumps",
-                      request_timeout=60.0, device_handoff=handoff, push=push, no_repeat_stop=True)
+                      request_timeout=60.0, device_handoff=handoff, push=push, no_repeat_stop=True,
+                      device_handoff_min_kb=0)      # every tensor, single tokens included (default: prompts only)
             return run_rank0(a, dev, cuts)
 
         ref, _ = client(False)
@@ -160,7 +161,7 @@ def test_killed_replica_is_recovered_from_the_device_journal(tmp_path):
 
         def client(handoff):
             a = _args(model, splits, 0, 0, dht_initial_peers=peers, max_new_tokens=14, prompt="one two three four five",
-                      request_timeout=20.0, device_handoff=handoff, no_repeat_stop=True)
+                      request_timeout=20.0, device_handoff=handoff, no_repeat_stop=True, device_handoff_min_kb=0)
             return run_rank0(a, dev, cuts)
 
         out, stats = client(True)
