@@ -149,7 +149,9 @@ def main():
             run = {"clients": n, "tokens_per_s": round(n * args.steps / dt, 1), "ms_per_round": round(dt / args.steps * 1e3, 3),
                    "server_mean_batch": round((info.get("mean_batch", 0.0) * info.get("batches", 0) - seen_i)
                                               / max(info.get("batches", 0) - seen_b, 1), 2),
-                   "server_batch_ms_cumulative_mean": info.get("batch_ms"), "tokens_equal_to_solo_runs": same}
+                   "server_batch_ms_cumulative_mean": info.get("batch_ms"),
+                   "server_mean_service_ms_cumulative": info.get("mean_service_ms"),
+                   "session_turnaround_ms_cumulative": info.get("mean_turnaround_ms"), "client_cpus": os.cpu_count(), "tokens_equal_to_solo_runs": same}
             print(json.dumps(run), flush=True)
             result["runs"].append(run)
     finally:

@@ -31,6 +31,7 @@ task_pool.py:17-177 / backend.py:201-235 upstream) - the decode kernels serve 16
 from __future__ import annotations
 
 import logging
+import os
 import threading
 import time
 from typing import Dict, List, Optional, Tuple
@@ -79,9 +80,15 @@ class StageConnectionHandler:
         # waits up to batch_linger for them before it runs a batched step (0 = never wait)
         self._stepping: Dict[str, float] = {}
         self.batch_seconds: Dict[str, float] = {}
+        # request-level timing (rpc_info): time inside the server per request, and how long a session takes to come
+        # back with its next step after a reply (network + client)
+        self._last_reply: Dict[str, float] = {}
+        self.think_seconds = self.service_seconds = 0.0
+        self.think_count = self.service_count = 0
         self.batch_linger = float(batch_linger)
         self.pool = PrioritizedTaskPool("stage", batch_linger=self.batch_linger if self.max_batch > 1 else 0.0,
-                                        expect=self._expected_batch, thread_init=self._bind_device)
+                                        expect=self._expected_batch, thread_init=self._bind_device,
+                                        linger_max_missing=int(os.environ.get("B200_LINGER_MAX_MISSING", "3")))
         self._fwd_client = RpcClient()
         self._gen = torch.Generator(device="cpu")
         if seed is not None:
@@ -325,6 +332,12 @@ class StageConnectionHandler:
         else:
             hidden = tensors[0]
         T = hidden.shape[-2] if hidden.dim() >= 2 else 1
+        t_in = time.perf_counter()
+        sid_ = metadata.get("session_id")
+        last = self._last_reply.get(sid_)
+        if last is not None and T == 1:
+            self.think_seconds += t_in - last          # reply sent -> next step of the session received
+            self.think_count += 1
         whole = self._view(metadata)[0] is self.stage_model        # sub-span views run unbatched
         if whole and T == 1 and self.max_batch > 1 and not metadata.get("is_prefill") and hidden.numel() == hidden.shape[-1]:
             self._stepping[metadata.get("session_id")] = time.monotonic()
@@ -333,6 +346,11 @@ class StageConnectionHandler:
                                                             timeout=self.request_timeout)
         else:
             out_t, out_md = self._submit(self._run_forward, hidden, metadata, kind="inference", tokens=T)
+        t_out = time.perf_counter()
+        if T == 1:                                      # (decode steps only: a prompt is followed by client-side work)
+            self._last_reply[sid_] = t_out
+            self.service_seconds += t_out - t_in
+            self.service_count += 1
         route = metadata.get("route") or []
         if route and "token_id" not in out_md:
             # server->server push: hand the activations to the next hop ourselves and relay its answer
@@ -422,6 +440,8 @@ class StageConnectionHandler:
                     "mean_batch": (self.pool.batched_items / self.pool.batches) if self.pool.batches else 0.0,
                     "streams_open": self.streams_open, "uptime_s": time.time() - self.started,
                     "batch_ms": {k: round(v * 1e3 / max(self.pool.batches, 1), 3) for k, v in self.batch_seconds.items()},
+                    "mean_service_ms": round(self.service_seconds * 1e3 / max(self.service_count, 1), 3),
+                    "mean_turnaround_ms": round(self.think_seconds * 1e3 / max(self.think_count, 1), 3),
                     "box": self.box(), "gpu": self._gpu_ids()[0], "visible_gpus": self._gpu_ids()[1], "handoff_out": self.handoff_out, "handoff_in": self.handoff_in}
 
     def rpc_check(self, uid: str, tensors, metadata: Dict):
@@ -432,6 +452,7 @@ class StageConnectionHandler:
         return [], {"reachable": ok, "rtt_s": rtt}
 
     def _close_everywhere(self, sid: str) -> bool:
+        self._last_reply.pop(sid, None)
         closed = self.kv.close(sid)
         for _, mgr, _ in self._views.values():
             closed = mgr.close(sid) or closed
