@@ -101,7 +101,7 @@ def main():
     ap.add_argument("--clients", default="1,4,16")
     ap.add_argument("--steps", type=int, default=64)
     ap.add_argument("--prompt", type=int, default=64)
-    ap.add_argument("--linger_ms", type=float, default=1.0)
+    ap.add_argument("--linger_ms", type=float, default=2.0)
     ap.add_argument("--out", default="gpurun_out/bench_served.json")
     args = ap.parse_args()
     from petals_b200.models.config import resolve_config

@@ -219,7 +219,7 @@ def start_stage_server(args, device, stage_model, final_stage: bool, stage_index
                                      session_timeout=getattr(args, "session_timeout", 30 * 60.0),
                                      step_timeout=getattr(args, "step_timeout", 5 * 60.0),
                                      max_batch=getattr(args, "max_batch", None),
-                                     batch_linger=getattr(args, "batch_linger_ms", 1.0) * 1e-3)
+                                     batch_linger=getattr(args, "batch_linger_ms", 2.0) * 1e-3)
     # many handler threads + one compute thread: hand the GIL over faster than CPython's 5 ms default
     sys.setswitchinterval(float(os.environ.get("B200_GIL_SWITCH_US", "200")) * 1e-6)
     stop = threading.Event()
@@ -539,7 +539,7 @@ def build_parser() -> argparse.ArgumentParser:
     p.add_argument("--step_timeout", type=float, default=5 * 60.0, help="server: idle time of an inference stream")
     p.add_argument("--max_batch", type=int, default=16,
                    help="server: single-token requests of different sessions merged into one decode step (1 = off)")
-    p.add_argument("--batch_linger_ms", type=float, default=1.0,
+    p.add_argument("--batch_linger_ms", type=float, default=2.0,
                    help="server: how long a batched decode step waits for the other sessions that have been stepping "
                         "lately (0 = take what is queued)")
     p.add_argument("--no_throughput_cache", action="store_true", help="server: re-measure the throughput on every start")

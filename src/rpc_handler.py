@@ -53,7 +53,7 @@ class StageConnectionHandler:
                  attn_cache_tokens: Optional[int] = None, session_ttl: float = 600.0, start_block: Optional[int] = None,
                  end_block: Optional[int] = None, throughput: float = 0.0, seed: Optional[int] = None,
                  alloc_timeout: float = 10.0, session_timeout: float = 30 * 60.0, step_timeout: float = 5 * 60.0,
-                 max_batch: Optional[int] = None, batch_linger: float = 0.001):
+                 max_batch: Optional[int] = None, batch_linger: float = 0.002):
         self.dht = dht
         self.stage_model = stage_model
         self.device = torch.device(device)
@@ -88,7 +88,7 @@ class StageConnectionHandler:
         self.batch_linger = float(batch_linger)
         self.pool = PrioritizedTaskPool("stage", batch_linger=self.batch_linger if self.max_batch > 1 else 0.0,
                                         expect=self._expected_batch, thread_init=self._bind_device,
-                                        linger_max_missing=int(os.environ.get("B200_LINGER_MAX_MISSING", "3")))
+                                        linger_max_missing=int(os.environ.get("B200_LINGER_MAX_MISSING", "32")))
         self._fwd_client = RpcClient()
         self._gen = torch.Generator(device="cpu")
         if seed is not None:
