@@ -261,23 +261,10 @@ __device__ __forceinline__ void rms_stats_128(const GemmParams& p, int T, int e,
 // shared-memory transpose so that every global access is a 16-byte vector along n (one 64-byte segment per
 // token row per warp) instead of 2-byte accesses 2*ld bytes apart.  Same arithmetic as above.
 // Requirements (checked by the caller): 16-bit output, N, ldo, ldr multiples of 8.
-// The residual words one thread adds in epilogue_store_chunk_vec for `chunk` (its two 8-wide n segments).  They do not
-// depend on the accumulator, so a caller may fetch them one or two chunks ahead and pass them in as `pre`.
-template <int BN>
-__device__ __forceinline__ void epilogue_load_residual(const GemmParams& p, int n_tile, int t_tile, int lane, int lg,
-                                                       int chunk, uint4 (&r)[2]) {
-    const int n0 = n_tile * kTileM + lg * 32 + (lane & 3) * 8;
-#pragma unroll
-    for (int i = 0; i < 2; ++i) {
-        const int t = t_tile * BN + chunk * 16 + (lane >> 2) + 8 * i;
-        r[i] = (p.residual && t < p.T && n0 < p.N) ? ld_cg_v4(p.residual + (size_t)t * p.ldr + n0) : make_uint4(0, 0, 0, 0);
-    }
-}
-
 template <int BN, int DUAL>
 __device__ __forceinline__ void epilogue_store_chunk_vec(const GemmParams& p, int n_tile, int t_tile, int lane, int lg,
                                                          int chunk, const float (&vg)[16], const float (&vu)[16],
-                                                         float* warp_smem /* [16][32] */, const uint4* pre = nullptr) {
+                                                         float* warp_smem /* [16][32] */) {
     const int n_row = n_tile * kTileM + lg * 32 + lane;
     const float b = (p.bias && n_row < p.N) ? h16_to_float(p.bias[n_row], p.is_bf16) : 0.0f;
 #pragma unroll
@@ -305,7 +292,7 @@ __device__ __forceinline__ void epilogue_store_chunk_vec(const GemmParams& p, in
             const float4 hi = *reinterpret_cast<const float4*>(warp_smem + j * 32 + q * 8 + 4);
             float f[8] = {lo.x, lo.y, lo.z, lo.w, hi.x, hi.y, hi.z, hi.w};
             if (p.residual) {
-                const uint4 r4 = pre ? pre[i] : ld_cg_v4(p.residual + (size_t)t * p.ldr + n0);
+                const uint4 r4 = ld_cg_v4(p.residual + (size_t)t * p.ldr + n0);
                 const uint32_t rw[4] = {r4.x, r4.y, r4.z, r4.w};
 #pragma unroll
                 for (int k = 0; k < 4; ++k) {

@@ -203,17 +203,8 @@ gemm_prefill_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap
                 named_bar_sync(1, kEpiThreads);           // s_last is rewritten by the next unit
                 continue;
             }
-            // The residual a chunk adds does not depend on the accumulator: it is fetched two chunks ahead (the first
-            // two before the accumulator is even waited for would need the tile index earlier; here they overlap the
-            // TMEM read of chunk 0), so its L2 latency no longer sits between every TMEM read and its store - that
-            // latency, 16 times per tile, was what kept o_proj / down at 42 / 67 % tensor-pipe activity.
-            const bool pre_ok = vec_ok && p.residual != nullptr;
-            uint4 ra[2], rb[2];
-            if (pre_ok) {
-                epilogue_load_residual<BN>(p, n_tile, t_tile, lane, lg, 0, ra);
-                epilogue_load_residual<BN>(p, n_tile, t_tile, lane, lg, 1, rb);
-            }
-            auto chunk = [&](int c, uint4 (&r)[2]) {
+#pragma unroll 1
+            for (int c = 0; c * 16 < t_live; ++c) {
                 uint32_t rg[16], ru[16];
                 tmem_ld16(taddr0 + c * 16, rg);
                 if (DUAL) tmem_ld16(taddr0 + BN + c * 16, ru);
@@ -224,14 +215,8 @@ gemm_prefill_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap
                     vg[j] = __uint_as_float(rg[j]);
                     vu[j] = DUAL ? __uint_as_float(ru[j]) : 0.f;
                 }
-                if (vec_ok) epilogue_store_chunk_vec<BN, DUAL>(p, n_tile, t_tile, lane, lg, c, vg, vu, my_smem, pre_ok ? r : nullptr);
+                if (vec_ok) epilogue_store_chunk_vec<BN, DUAL>(p, n_tile, t_tile, lane, lg, c, vg, vu, my_smem);
                 else epilogue_store_chunk<BN, DUAL>(p, n_tile, t_tile, row, c, vg, vu, nullptr);
-                if (pre_ok && (c + 2) * 16 < t_live) epilogue_load_residual<BN>(p, n_tile, t_tile, lane, lg, c + 2, r);
-            };
-#pragma unroll 1
-            for (int c = 0; c * 16 < t_live; c += 2) {
-                chunk(c, ra);
-                if ((c + 1) * 16 < t_live) chunk(c + 1, rb);
             }
             tc_fence_before();
             __syncwarp();
