@@ -208,9 +208,25 @@ extern "C" int b200_attn_decode(const b200_attn_decode_args* a, void* stream_) {
     const dim3 grid((unsigned)(a->T * a->n_kv_heads * p.splits));
     cudaStream_t stream = static_cast<cudaStream_t>(stream_);
     const bool pdl = a->pdl != 0;
+    // B200_ATTN_BULK=0: cache rows by plain 16-byte loads (+ an L2 prefetch above the PDL wait) instead of bulk copies
+    static const bool bulk = [] { const char* e = getenv("B200_ATTN_BULK"); return !(e && e[0] == '0'); }();
 #define B200_ATTN_CASE(D_, G_)                                                                     \
     if (a->head_dim == D_ && group == G_) {                                                        \
-        B200_CUDA_CHECK(launch(attn_decode_kernel<D_, G_>, grid, dim3(kAttnThreads), 0, stream, pdl, p)); \
+        if (bulk) {                                                                                \
+            static int configured_dev = -1;                                                        \
+            int dev = 0;                                                                           \
+            B200_CUDA_CHECK(cudaGetDevice(&dev));                                                  \
+            if (configured_dev != dev) {                                                           \
+                B200_CUDA_CHECK(cudaFuncSetAttribute(attn_decode_kernel<D_, G_, 1>,                \
+                                                     cudaFuncAttributeMaxDynamicSharedMemorySize,  \
+                                                     (int)sizeof(AttnBulkTiles<D_>)));             \
+                configured_dev = dev;                                                              \
+            }                                                                                      \
+            B200_CUDA_CHECK(launch(attn_decode_kernel<D_, G_, 1>, grid, dim3(kAttnThreads),        \
+                                   sizeof(AttnBulkTiles<D_>), stream, pdl, p));                    \
+        } else {                                                                                   \
+            B200_CUDA_CHECK(launch(attn_decode_kernel<D_, G_, 0>, grid, dim3(kAttnThreads), 0, stream, pdl, p)); \
+        }                                                                                          \
         return B200_OK;                                                                            \
     }
     B200_ATTN_CASE(128, 1) B200_ATTN_CASE(128, 2) B200_ATTN_CASE(128, 4) B200_ATTN_CASE(128, 8)

@@ -91,6 +91,21 @@ struct AttnDecodeSmem {
     int last;
 };
 
+// Cache rows of a split staged through shared memory by bulk async copies (cp.async.bulk, SASS UBLKCP): one pass of
+// the CTA = kAttnRowsPerPass<D> rows = 8 KiB of K and 8 KiB of V, two passes in flight.  The rows of earlier tokens do
+// not depend on the previous kernel, so the first two passes are requested above the programmatic-launch wait and are
+// in shared memory when the new q arrives; later passes are copied while the current one is being reduced.
+template <int D>
+constexpr int kAttnRowsPerPass = (kAttnThreads / 32) * (32 / (D / 8)) * 4;   // warps x rows per warp step x unroll
+template <int D>
+struct AttnBulkTiles {
+    alignas(128) uint16_t k[2][kAttnRowsPerPass<D> * D];
+    alignas(128) uint16_t v[2][kAttnRowsPerPass<D> * D];
+    alignas(16) uint16_t newk[D];      // the new token's own row (RoPE'd k, v): its owner split has it in registers
+    alignas(16) uint16_t newv[D];
+    alignas(8) uint64_t full[2];
+};
+
 // One work item = (token t, kv head g, split s), executed by kAttnThreads threads that share
 // `sm` and synchronise through `sync()` (a __syncthreads() or a named barrier).
 // `before_qkv()` runs right before the first access to p.qkv (the only input the previous kernel produces):
@@ -99,10 +114,14 @@ struct AttnDecodeSmem {
 struct AttnNoHook { __device__ __forceinline__ void operator()() const {} };
 template <int D, int GROUP, typename Sync, typename Hook = AttnNoHook>
 __device__ __forceinline__ void attn_decode_body(const AttnDecodeParams& p, int t, int g, int s, int tid,
-                                                 AttnDecodeSmem<D, GROUP>& sm, Sync sync, Hook before_qkv = Hook()) {
+                                                 AttnDecodeSmem<D, GROUP>& sm, Sync sync, Hook before_qkv = Hook(),
+                                                 AttnBulkTiles<D>* tiles = nullptr) {
     constexpr int LPR = D / 8;          // lanes per row: 16 (D=128) or 8 (D=64)
     constexpr int RPW = 32 / LPR;       // rows per warp per step: 2 or 4
     constexpr int NW = kAttnThreads / 32;
+    constexpr int UNROLL = 4;
+    constexpr int ROWS = NW * RPW * UNROLL;     // rows per pass of the CTA
+    static_assert(ROWS == kAttnRowsPerPass<D>, "tile size");
     auto& s_q = sm.q;
     auto& s_m = sm.m;
     auto& s_l = sm.l;
@@ -133,9 +152,24 @@ __device__ __forceinline__ void attn_decode_body(const AttnDecodeParams& p, int 
     static_assert((GROUP + 1) * TPH <= kAttnThreads, "one RoPE item per thread");
     float rs[8], rc[8];
     if (p.inv_freq && tid < (GROUP + 1) * TPH) rope_sincos8((tid % TPH) * 8, pos, p.inv_freq, p.is_bf16, rs, rc);
-    if (tid == 0) {   // cache rows of earlier tokens do not depend on the previous kernel: start pulling them into L2
-        const int n_old = min(r_end, pos) - r_begin;
-        if (n_old > 0) {
+    const bool bulk = tiles != nullptr;
+    const int n_old = max(0, min(r_end, pos) - r_begin);      // rows written by earlier steps
+    const int n_pass = bulk ? (n_old + ROWS - 1) / ROWS : 0;
+    auto issue = [&](int pass, int st) {                       // one thread: request pass `pass` into stage `st`
+        const int rows = min(ROWS, n_old - pass * ROWS);
+        const uint32_t bytes = (uint32_t)(rows * D * 2);
+        mbar_arrive_expect_tx(&tiles->full[st], 2 * bytes);
+        bulk_g2s(tiles->k[st], kbase + (size_t)(r_begin + pass * ROWS) * D, bytes, &tiles->full[st]);
+        bulk_g2s(tiles->v[st], vbase + (size_t)(r_begin + pass * ROWS) * D, bytes, &tiles->full[st]);
+    };
+    if (tid == 0) {   // cache rows of earlier tokens do not depend on the previous kernel: start fetching them
+        if (bulk) {
+            mbar_init(&tiles->full[0], 1);
+            mbar_init(&tiles->full[1], 1);
+            fence_mbar_init();
+            if (n_pass > 0) issue(0, 0);
+            if (n_pass > 1) issue(1, 1);
+        } else if (n_old > 0) {
             bulk_prefetch_l2(kbase + (size_t)r_begin * D, (uint32_t)(n_old * D * 2));
             bulk_prefetch_l2(vbase + (size_t)r_begin * D, (uint32_t)(n_old * D * 2));
         }
@@ -173,8 +207,15 @@ __device__ __forceinline__ void attn_decode_body(const AttnDecodeParams& p, int 
             *reinterpret_cast<uint4*>(kbase + (size_t)pos * D + c) = pack8(lo, p.is_bf16);
             *reinterpret_cast<uint4*>(kbase + (size_t)pos * D + c + D / 2) = pack8(hi, p.is_bf16);
             // v is copied verbatim alongside
-            *reinterpret_cast<uint4*>(vbase + (size_t)pos * D + c) = load8(v_off + c);
-            *reinterpret_cast<uint4*>(vbase + (size_t)pos * D + c + D / 2) = load8(v_off + c + D / 2);
+            const uint4 v_lo = load8(v_off + c), v_hi = load8(v_off + c + D / 2);
+            *reinterpret_cast<uint4*>(vbase + (size_t)pos * D + c) = v_lo;
+            *reinterpret_cast<uint4*>(vbase + (size_t)pos * D + c + D / 2) = v_hi;
+            if (bulk) {
+                *reinterpret_cast<uint4*>(tiles->newk + c) = pack8(lo, p.is_bf16);
+                *reinterpret_cast<uint4*>(tiles->newk + c + D / 2) = pack8(hi, p.is_bf16);
+                *reinterpret_cast<uint4*>(tiles->newv + c) = v_lo;
+                *reinterpret_cast<uint4*>(tiles->newv + c + D / 2) = v_hi;
+            }
         } else {
 #pragma unroll
             for (int i = 0; i < 8; ++i) {
@@ -197,44 +238,76 @@ __device__ __forceinline__ void attn_decode_body(const AttnDecodeParams& p, int 
 #pragma unroll
         for (int i = 0; i < 8; ++i) { q[h][i] = s_q[h][dl + i]; acc[h][i] = 0.f; }
     }
-    constexpr int UNROLL = 4;
-    for (int r0 = r_begin + warp * RPW * UNROLL; r0 < r_end; r0 += NW * RPW * UNROLL) {
-        uint4 kraw[UNROLL], vraw[UNROLL];
+    // one row (this lane's 8 dims of it) into the running (m, l, acc) of every q head of the group
+    auto accumulate = [&](const uint4& kr, const uint4& vr, bool valid) {
+        float kf[8], vf[8];
+        unpack8(kr, kf, p.is_bf16);
+        unpack8(vr, vf, p.is_bf16);
 #pragma unroll
-        for (int j = 0; j < UNROLL; ++j) {
-            const int r = r0 + j * RPW + sub;
-            if (r < r_end) {
-                kraw[j] = *reinterpret_cast<const uint4*>(kbase + (size_t)r * D + dl);
-                vraw[j] = *reinterpret_cast<const uint4*>(vbase + (size_t)r * D + dl);
-            } else {
-                kraw[j] = make_uint4(0, 0, 0, 0);
-                vraw[j] = make_uint4(0, 0, 0, 0);
+        for (int h = 0; h < GROUP; ++h) {
+            float sc = 0.f;
+#pragma unroll
+            for (int i = 0; i < 8; ++i) sc += q[h][i] * kf[i];
+#pragma unroll
+            for (int o = LPR / 2; o > 0; o >>= 1) sc += __shfl_xor_sync(0xffffffffu, sc, o);
+            if (valid) {
+                const float mn = fmaxf(m[h], sc);
+                const float corr = __expf(m[h] - mn);
+                const float pr = __expf(sc - mn);
+                l[h] = l[h] * corr + pr;
+#pragma unroll
+                for (int i = 0; i < 8; ++i) acc[h][i] = acc[h][i] * corr + pr * vf[i];
+                m[h] = mn;
             }
         }
+    };
+    if (bulk) {
+        const int old_end = r_begin + n_old;
+        for (int pi = 0; pi < n_pass; ++pi) {
+            const int st = pi & 1;
+            mbar_wait(&tiles->full[st], (uint32_t)((pi >> 1) & 1));
+            const int base = r_begin + pi * ROWS;
+            uint4 kraw[UNROLL], vraw[UNROLL];
 #pragma unroll
-        for (int j = 0; j < UNROLL; ++j) {
-            const int r = r0 + j * RPW + sub;
-            const bool valid = r < r_end;
-            float kf[8], vf[8];
-            unpack8(kraw[j], kf, p.is_bf16);
-            unpack8(vraw[j], vf, p.is_bf16);
-#pragma unroll
-            for (int h = 0; h < GROUP; ++h) {
-                float sc = 0.f;
-#pragma unroll
-                for (int i = 0; i < 8; ++i) sc += q[h][i] * kf[i];
-#pragma unroll
-                for (int o = LPR / 2; o > 0; o >>= 1) sc += __shfl_xor_sync(0xffffffffu, sc, o);
-                if (valid) {
-                    const float mn = fmaxf(m[h], sc);
-                    const float corr = __expf(m[h] - mn);
-                    const float pr = __expf(sc - mn);
-                    l[h] = l[h] * corr + pr;
-#pragma unroll
-                    for (int i = 0; i < 8; ++i) acc[h][i] = acc[h][i] * corr + pr * vf[i];
-                    m[h] = mn;
+            for (int j = 0; j < UNROLL; ++j) {
+                const int r = base + warp * RPW * UNROLL + j * RPW + sub;
+                if (r < old_end) {
+                    kraw[j] = *reinterpret_cast<const uint4*>(tiles->k[st] + (size_t)(r - base) * D + dl);
+                    vraw[j] = *reinterpret_cast<const uint4*>(tiles->v[st] + (size_t)(r - base) * D + dl);
+                } else {
+                    kraw[j] = make_uint4(0, 0, 0, 0);
+                    vraw[j] = make_uint4(0, 0, 0, 0);
                 }
             }
+#pragma unroll
+            for (int j = 0; j < UNROLL; ++j)
+                accumulate(kraw[j], vraw[j], base + warp * RPW * UNROLL + j * RPW + sub < old_end);
+            if (pi + 2 < n_pass) {
+                sync();                                   // every thread is done with stage st
+                if (tid == 0) issue(pi + 2, st);
+            }
+        }
+        if (pos >= r_begin && pos < r_end && warp == 0) {  // the new token's own row, from shared memory
+            const uint4 kr = *reinterpret_cast<const uint4*>(tiles->newk + dl);
+            const uint4 vr = *reinterpret_cast<const uint4*>(tiles->newv + dl);
+            accumulate(kr, vr, sub == 0);
+        }
+    } else {
+        for (int r0 = r_begin + warp * RPW * UNROLL; r0 < r_end; r0 += NW * RPW * UNROLL) {
+            uint4 kraw[UNROLL], vraw[UNROLL];
+#pragma unroll
+            for (int j = 0; j < UNROLL; ++j) {
+                const int r = r0 + j * RPW + sub;
+                if (r < r_end) {
+                    kraw[j] = *reinterpret_cast<const uint4*>(kbase + (size_t)r * D + dl);
+                    vraw[j] = *reinterpret_cast<const uint4*>(vbase + (size_t)r * D + dl);
+                } else {
+                    kraw[j] = make_uint4(0, 0, 0, 0);
+                    vraw[j] = make_uint4(0, 0, 0, 0);
+                }
+            }
+#pragma unroll
+            for (int j = 0; j < UNROLL; ++j) accumulate(kraw[j], vraw[j], r0 + j * RPW + sub < r_end);
         }
     }
     // ---- merge the RPW row-groups of a warp, then the warps, then the splits
@@ -384,9 +457,11 @@ __device__ __forceinline__ void attn_decode_body(const AttnDecodeParams& p, int 
 }
 
 
-template <int D, int GROUP>
+template <int D, int GROUP, int BULK = 0>
 __global__ void __launch_bounds__(kAttnThreads) attn_decode_kernel(const AttnDecodeParams p) {
     __shared__ AttnDecodeSmem<D, GROUP> sm;
+    extern __shared__ __align__(128) unsigned char attn_dyn_smem[];      // BULK: the K/V tiles
+    AttnBulkTiles<D>* tiles = BULK ? reinterpret_cast<AttnBulkTiles<D>*>(attn_dyn_smem) : nullptr;
     int bid = blockIdx.x;
     const int s = bid % p.splits; bid /= p.splits;
     const int g = bid % p.n_kv;
@@ -395,7 +470,8 @@ __global__ void __launch_bounds__(kAttnThreads) attn_decode_kernel(const AttnDec
     if (threadIdx.x == 0) trace_event(2, 0);
     const bool chain = p.ch.seq != nullptr;    // a link of a flag chain polls its inputs instead of waiting for the grid
     attn_decode_body<D, GROUP>(p, t, g, s, (int)threadIdx.x, sm, [] { __syncthreads(); },
-                               [chain] { if (!chain) pdl_wait_prior_grid(); if (threadIdx.x == 0) trace_event(2, 1); });
+                               [chain] { if (!chain) pdl_wait_prior_grid(); if (threadIdx.x == 0) trace_event(2, 1); },
+                               tiles);
     if (threadIdx.x == 0) trace_event(2, 3);
 }
 
