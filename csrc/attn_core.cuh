@@ -92,18 +92,22 @@ struct AttnDecodeSmem {
 };
 
 // Cache rows of a split staged through shared memory by bulk async copies (cp.async.bulk, SASS UBLKCP): one pass of
-// the CTA = kAttnRowsPerPass<D> rows = 8 KiB of K and 8 KiB of V, two passes in flight.  The rows of earlier tokens do
-// not depend on the previous kernel, so the first two passes are requested above the programmatic-launch wait and are
+// the CTA = kAttnRowsPerPass<D> rows = 8 KiB of K and 8 KiB of V, kAttnStages passes in flight.  The rows of earlier tokens do
+// not depend on the previous kernel, so the first passes are requested above the programmatic-launch wait and are
 // in shared memory when the new q arrives; later passes are copied while the current one is being reduced.
 template <int D>
 constexpr int kAttnRowsPerPass = (kAttnThreads / 32) * (32 / (D / 8)) * 4;   // warps x rows per warp step x unroll
+#ifndef B200_ATTN_BULK_STAGES
+#define B200_ATTN_BULK_STAGES 3   /* 48 KiB of tiles per CTA: four CTAs per SM stay resident (>= 512 at batch 1) */
+#endif
+constexpr int kAttnStages = B200_ATTN_BULK_STAGES;
 template <int D>
 struct AttnBulkTiles {
-    alignas(128) uint16_t k[2][kAttnRowsPerPass<D> * D];
-    alignas(128) uint16_t v[2][kAttnRowsPerPass<D> * D];
+    alignas(128) uint16_t k[kAttnStages][kAttnRowsPerPass<D> * D];
+    alignas(128) uint16_t v[kAttnStages][kAttnRowsPerPass<D> * D];
     alignas(16) uint16_t newk[D];      // the new token's own row (RoPE'd k, v): its owner split has it in registers
     alignas(16) uint16_t newv[D];
-    alignas(8) uint64_t full[2];
+    alignas(8) uint64_t full[kAttnStages];
 };
 
 // One work item = (token t, kv head g, split s), executed by kAttnThreads threads that share
@@ -164,11 +168,12 @@ __device__ __forceinline__ void attn_decode_body(const AttnDecodeParams& p, int 
     };
     if (tid == 0) {   // cache rows of earlier tokens do not depend on the previous kernel: start fetching them
         if (bulk) {
-            mbar_init(&tiles->full[0], 1);
-            mbar_init(&tiles->full[1], 1);
+#pragma unroll
+            for (int st = 0; st < kAttnStages; ++st) mbar_init(&tiles->full[st], 1);
             fence_mbar_init();
-            if (n_pass > 0) issue(0, 0);
-            if (n_pass > 1) issue(1, 1);
+#pragma unroll
+            for (int st = 0; st < kAttnStages; ++st)
+                if (st < n_pass) issue(st, st);
         } else if (n_old > 0) {
             bulk_prefetch_l2(kbase + (size_t)r_begin * D, (uint32_t)(n_old * D * 2));
             bulk_prefetch_l2(vbase + (size_t)r_begin * D, (uint32_t)(n_old * D * 2));
@@ -264,8 +269,8 @@ __device__ __forceinline__ void attn_decode_body(const AttnDecodeParams& p, int 
     if (bulk) {
         const int old_end = r_begin + n_old;
         for (int pi = 0; pi < n_pass; ++pi) {
-            const int st = pi & 1;
-            mbar_wait(&tiles->full[st], (uint32_t)((pi >> 1) & 1));
+            const int st = pi % kAttnStages;
+            mbar_wait(&tiles->full[st], (uint32_t)((pi / kAttnStages) & 1));
             const int base = r_begin + pi * ROWS;
             uint4 kraw[UNROLL], vraw[UNROLL];
 #pragma unroll
@@ -282,9 +287,9 @@ __device__ __forceinline__ void attn_decode_body(const AttnDecodeParams& p, int 
 #pragma unroll
             for (int j = 0; j < UNROLL; ++j)
                 accumulate(kraw[j], vraw[j], base + warp * RPW * UNROLL + j * RPW + sub < old_end);
-            if (pi + 2 < n_pass) {
+            if (pi + kAttnStages < n_pass) {
                 sync();                                   // every thread is done with stage st
-                if (tid == 0) issue(pi + 2, st);
+                if (tid == 0) issue(pi + kAttnStages, st);
             }
         }
         if (pos >= r_begin && pos < r_end && warp == 0) {  // the new token's own row, from shared memory
