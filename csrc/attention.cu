@@ -208,8 +208,14 @@ extern "C" int b200_attn_decode(const b200_attn_decode_args* a, void* stream_) {
     const dim3 grid((unsigned)(a->T * a->n_kv_heads * p.splits));
     cudaStream_t stream = static_cast<cudaStream_t>(stream_);
     const bool pdl = a->pdl != 0;
-    // B200_ATTN_BULK=0: cache rows by plain 16-byte loads (+ an L2 prefetch above the PDL wait) instead of bulk copies
-    static const bool bulk = [] { const char* e = getenv("B200_ATTN_BULK"); return !(e && e[0] == '0'); }();
+    // Cache rows reach the SM either by plain 16-byte loads (+ an L2 prefetch above the PDL wait) or through shared
+    // memory by bulk async copies.  Measured per layer (32 kv heads, d = 128, 1xB200, scripts/exp_attn.py): with 512
+    // CTAs (16 splits) the loads win, 11.4 vs 12.3 us at 1500 cached tokens - 3.5 CTAs per SM hide their latency and
+    // the copies' fixed cost shows; with 128 CTAs (4 splits, or a GQA model with 8 kv heads) the copies win, 16.8 vs
+    // 20.8 us - one CTA per SM has nothing but its own prefetch depth.  So: bulk copies when the grid leaves at most
+    // two CTAs per SM; B200_ATTN_BULK=0/1 forces one or the other.
+    static const int bulk_env = [] { const char* e = getenv("B200_ATTN_BULK"); return e ? (e[0] == '0' ? 0 : 1) : -1; }();
+    const bool bulk = bulk_env >= 0 ? bulk_env == 1 : (int)grid.x <= 2 * sm_count_cached();
 #define B200_ATTN_CASE(D_, G_)                                                                     \
     if (a->head_dim == D_ && group == G_) {                                                        \
         if (bulk) {                                                                                \

@@ -26,7 +26,8 @@ def _attn_ref(q, k, v, n_rep):
 
 @pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
 @pytest.mark.parametrize("nh,nkv,D,rope", [(8, 8, 128, True), (8, 2, 128, True), (16, 2, 128, True),
-                                           (4, 4, 64, False), (8, 1, 128, True)])
+                                           (4, 4, 64, False), (8, 1, 128, True),
+                                           (32, 32, 128, True)])   # 768 CTAs: the plain-load path (small grids: bulk copies)
 @pytest.mark.parametrize("past", [0, 5, 63, 64, 300, 1500])
 def test_attn_decode(nh, nkv, D, rope, past, dtype):
     from petals_b200.ops import attention as A
