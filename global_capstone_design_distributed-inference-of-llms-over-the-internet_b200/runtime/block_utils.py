@@ -28,6 +28,8 @@ def get_block_size(cfg: ModelConfig, dtype: torch.dtype = torch.bfloat16, weight
     if weight_format == "fp8":
         rows = cfg.qkv_size + cfg.hidden + (2 if cfg.is_llama else 1) * cfg.intermediate + cfg.hidden
         return params + 4 * rows
+    if weight_format == "mxfp8":
+        return params + params // 32          # one UE8M0 byte per 32 elements of K (OCP MX)
     return params * torch.empty((), dtype=dtype).element_size()
 
 

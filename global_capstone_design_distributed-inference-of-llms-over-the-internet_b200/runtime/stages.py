@@ -74,7 +74,8 @@ class _StageBase(torch.nn.Module):
     role = "segment"
 
     def __init__(self, full: StageWeights, start: int, end: int, gpu_device=None, keep_layers_on_gpu: int = 0,
-                 kv_capacity: int = 2048, max_batch: int = 8, backend: Optional[str] = None):
+                 kv_capacity: int = 2048, max_batch: int = 8, backend: Optional[str] = None,
+                 weight_format: str = "native"):
         super().__init__()
         if (start, end) != (full.start, full.end):
             raise ValueError(f"stage span [{start},{end}) does not match loaded weights [{full.start},{full.end})")
@@ -98,7 +99,7 @@ class _StageBase(torch.nn.Module):
             from .native_span import NativeSpan
 
             self.span = NativeSpan(self.cfg, full.weights, self.device, self.dtype, kv_capacity=kv_capacity,
-                                   max_batch=max_batch)
+                                   max_batch=max_batch, weight_format=weight_format)
         elif full.use_cpu_offload and self.device.type == "cuda":
             from .offload import OffloadedSpan
 

@@ -296,7 +296,7 @@ def _default_num_blocks(args, cfg, device) -> int:
         return min(4, cfg.n_layers)
     tokens = getattr(args, "attn_cache_tokens", None) or default_limits(cfg)[1]
     n = choose_num_blocks(cfg, device, args.dtype if isinstance(args.dtype, torch.dtype) else torch.bfloat16,
-                          attn_cache_tokens=tokens)
+                          weight_format=getattr(args, "weight_format", "native") or "native", attn_cache_tokens=tokens)
     logger.info("num_blocks not given: this GPU holds %d of %d blocks next to a %d-token cache", n, cfg.n_layers, tokens)
     return n
 
@@ -310,6 +310,11 @@ def _build_stage(args, device, start: int, end: int, final: bool, n_layers: int)
         kw["kv_capacity"] = args.kv_capacity
     if getattr(args, "max_batch", None):
         kw["max_batch"] = args.max_batch
+    wf = getattr(args, "weight_format", "native") or "native"
+    if wf != "native":
+        if device.type != "cuda" or _tp_width(args) > 1 or args.use_cpu_offload:
+            raise ValueError("--weight_format fp8/mxfp8 needs a resident single-GPU span on CUDA")
+        kw["weight_format"] = wf
     if _tp_width(args) > 1:
         # a span wider than one GPU: this process holds one tensor-parallel shard of it (runtime/tp_stage.py)
         import torch.distributed as dist
@@ -539,6 +544,9 @@ def build_parser() -> argparse.ArgumentParser:
     p.add_argument("--step_timeout", type=float, default=5 * 60.0, help="server: idle time of an inference stream")
     p.add_argument("--max_batch", type=int, default=16,
                    help="server: single-token requests of different sessions merged into one decode step (1 = off)")
+    p.add_argument("--weight_format", type=str, default="native", choices=["native", "fp8", "mxfp8"],
+                   help="server: weights of the span as loaded (fp16/bf16), e4m3 with one scale per output row, or "
+                        "OCP-MX e4m3 with one UE8M0 scale per 32 elements (upstream: --quant_type)")
     p.add_argument("--batch_linger_ms", type=float, default=2.0,
                    help="server: how long a batched decode step waits for the other sessions that have been stepping "
                         "lately (0 = take what is queued)")

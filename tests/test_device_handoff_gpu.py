@@ -174,3 +174,33 @@ def test_killed_replica_is_recovered_from_the_device_journal(tmp_path):
             p.terminate()
         for p in procs:
             p.join(10)
+
+
+def test_served_stage_with_mx_fp8_weights():
+    """`--weight_format mxfp8` (upstream: --quant_type): the served span holds block-scaled e4m3 weights - about half
+    the bytes - and serves a deterministic greedy continuation over the TCP path."""
+    sys.path.insert(0, ROOT)
+    from src.main import parse_splits, run_rank0, run_stage_server_fixed
+
+    model, splits = "tiny-llama-gqa", "1"
+    cuts = parse_splits(splits)
+    dev = torch.device("cuda", 0)
+    handles, sizes, outs = [], {}, {}
+    try:
+        for wf in ("native", "mxfp8"):
+            h = run_stage_server_fixed(_args(model, splits, 1, 0, weight_format=wf), dev, cuts, block=False)
+            handles.append(h)
+            span = h.handler.stage_model.span
+            assert span.weight_format == wf
+            sizes[wf] = sum(P[k].nbytes for P in span.layers for k in ("qkv", "o", "mlp_in", "down"))
+            peers = h.dht.get_visible_maddrs()[0]
+            runs = [run_rank0(_args(model, splits, 0, 0, dht_initial_peers=peers, max_new_tokens=10, prompt="a b c d e f",
+                                    request_timeout=60.0, no_repeat_stop=True), dev, cuts)[0] for _ in range(2)]
+            assert runs[0] == runs[1] and len(runs[0]) == 10
+            outs[wf] = runs[0]
+            h.stop()
+            handles.remove(h)
+        assert sizes["mxfp8"] < 0.6 * sizes["native"]
+    finally:
+        for h in handles:
+            h.stop()
