@@ -285,3 +285,79 @@ def test_metrics_jsonl_and_percentiles(tmp_path, monkeypatch):
     assert s["n"] == 5 and s["p50"] == 3 and s["max"] == 100 and sum(h.counts) == 5
     with metrics.nvtx_range("noop"):
         pass
+
+
+def test_rpc_server_threads_errors_and_stop():
+    """Thread-per-connection server: concurrent connections are served in parallel, a handler's exception travels back
+    as RpcError, an unknown method is reported, and stop() unblocks clients that wait for an answer."""
+    import threading
+
+    from petals_b200.net.rpc import RpcClient, RpcError, RpcServer
+
+    gate = threading.Event()
+
+    def slow(uid, tensors, md):
+        gate.wait(5)
+        return [tensors[0] * 2], {"uid": uid}
+
+    def boom(uid, tensors, md):
+        raise ValueError("nope")
+
+    def hang(uid, tensors, md):
+        time.sleep(30)
+        return [], {}
+
+    srv = RpcServer().start()
+    for name, fn in (("t.slow", slow), ("t.boom", boom), ("t.hang", hang)):
+        srv.add_handler(name, fn)
+    addr = srv.address
+    res = {}
+
+    def call(i):
+        c = RpcClient()
+        res[i] = c.call(addr, "t.slow", f"u{i}", [torch.full((4,), float(i))], {}, timeout=10)
+        c.close()
+
+    ts = [threading.Thread(target=call, args=(i,)) for i in range(4)]
+    for t in ts:
+        t.start()
+    time.sleep(0.2)
+    gate.set()                      # all four were waiting inside the handler at the same time
+    for t in ts:
+        t.join(5)
+    assert sorted(res) == [0, 1, 2, 3] and all(torch.equal(res[i][0][0], torch.full((4,), 2.0 * i)) for i in res)
+    assert all(res[i][1]["uid"] == f"u{i}" for i in res)
+    c = RpcClient()
+    with pytest.raises(RpcError, match="ValueError: nope"):
+        c.call(addr, "t.boom", "u", [], {})
+    with pytest.raises(RpcError, match="no handler"):
+        c.call(addr, "t.missing", "u", [], {})
+    failed = []
+
+    def waiter():
+        try:
+            RpcClient().call(addr, "t.hang", "u", [], {}, timeout=20)
+        except (ConnectionError, TimeoutError) as e:
+            failed.append(e)
+
+    w = threading.Thread(target=waiter)
+    w.start()
+    time.sleep(0.2)
+    t0 = time.monotonic()
+    srv.stop()
+    w.join(5)
+    assert failed and time.monotonic() - t0 < 5, "a stopped server must not leave its clients waiting"
+    with pytest.raises(ConnectionError):
+        c.call(addr, "t.boom", "u", [], {}, timeout=2)
+    c.close()
+
+
+def test_handoff_gpu_numbering(monkeypatch):
+    from petals_b200.net import devshare
+
+    monkeypatch.setenv("CUDA_VISIBLE_DEVICES", "3,5")
+    assert devshare.visible_gpus() == [3, 5]
+    assert devshare.local_index(5) == 1
+    with pytest.raises(RuntimeError):
+        devshare.local_index(0)
+    assert devshare._physical_index(torch.device("cuda", 1)) == 5
