@@ -72,6 +72,16 @@ class DeviceExporter:
         self.lock = threading.Lock()
         self.box = box_id()
 
+    def close(self) -> None:
+        """Free the arena (importers that still hold it open keep their mapping until they close it)."""
+        if self.base:
+            _, runtime = _rt()
+            self.arena = None
+            with torch.cuda.device(self.device):
+                torch.cuda.synchronize(self.device)
+                runtime.cudaFree(self.base)
+            self.base = 0
+
     def export(self, t: torch.Tensor) -> dict:
         """Copy ``t`` into the next slot and describe it.  Returns after the copy has completed on the device."""
         if not t.is_cuda:
@@ -110,6 +120,15 @@ class DeviceImporter:
         self.pulled_bytes = 0
         self.pulls = 0
 
+    def close(self) -> None:
+        """Unmap every arena this process opened."""
+        _, runtime = _rt()
+        with self.lock:
+            for ptr, src in self._open.values():
+                with torch.cuda.device(src):
+                    runtime.cudaIpcCloseMemHandle(ptr)
+            self._open.clear()
+
     def accepts(self, desc: Optional[dict]) -> bool:
         return bool(desc) and desc.get("box") == self.box and self.device.type == "cuda"
 
@@ -132,6 +151,10 @@ class DeviceImporter:
                     err, ptr = runtime.cudaIpcOpenMemHandle(h, runtime.cudaIpcMemLazyEnablePeerAccess)
                     _check(err, "cudaIpcOpenMemHandle")
                 a = self._open[key] = (int(ptr), src)
+                if len(self._open) > 64:            # exporters come and go (client processes): unmap the oldest
+                    old_ptr, old_src = self._open.pop(next(iter(self._open)))
+                    with torch.cuda.device(old_src):
+                        runtime.cudaIpcCloseMemHandle(old_ptr)
             return a
 
     def pull(self, desc: dict, local: Optional[torch.Tensor] = None) -> torch.Tensor:

@@ -127,7 +127,11 @@ class StageConnectionHandler:
 
     def _expected_batch(self) -> int:
         now = time.monotonic()
-        return sum(1 for t in self._stepping.values() if now - t < 0.05)
+        if len(self._stepping) > 4 * self.max_batch:       # sessions that ended without a close (TTL eviction)
+            for sid in [s for s, t in list(self._stepping.items()) if now - t > 60.0]:
+                self._stepping.pop(sid, None)
+                self._last_reply.pop(sid, None)
+        return sum(1 for t in list(self._stepping.values()) if now - t < 0.05)
 
     # ------------------------------------------------------------------ registration
     def add_p2p_handlers(self, server: RpcServer) -> None:
@@ -482,3 +486,10 @@ class StageConnectionHandler:
                 pass
         self.pool.shutdown()
         self._fwd_client.close()
+        for side in (self._importer, self._exporter):
+            if side is not None:
+                try:
+                    side.close()
+                except Exception:  # noqa: BLE001
+                    pass
+        self._importer = self._exporter = None

@@ -480,5 +480,12 @@ class RpcTransport:
         for key in list(self._streams):
             self._drop_stream(key)
         self.client.close()
+        for side in (self._importer, self._exporter):
+            if side is not None:
+                try:
+                    side.close()
+                except Exception:  # noqa: BLE001
+                    pass
+        self._importer = self._exporter = None
         if self._own_dht:
             self.dht.shutdown()
