@@ -94,7 +94,10 @@ class PipelineEngine:
             head_split = _os.environ.get("B200_HEAD_SPLIT", "1") != "0"
         self.head_split = bool(head_split) and self.hop == "p2p" and self.world > 1
         tiles = (self.cfg.vocab + 127) // 128
-        self.v0 = (tiles // 2) * 128
+        # share of the vocabulary the LAST stage multiplies (the first stage also embeds and merges the candidates,
+        # so an even split leaves it the slower of the two; B200_HEAD_SPLIT_LAST_FRAC to measure other splits)
+        frac = float(_os.environ.get("B200_HEAD_SPLIT_LAST_FRAC", "0.5"))
+        self.v0 = max(1, min(tiles - 1, int(round(tiles * frac)))) * 128
         need_head = self.is_last or (self.is_first and self.head_split)
         head_rows = None
         if self.head_split and need_head:
