@@ -24,7 +24,7 @@ mgr = KVCacheManager(layers, 32, 128, torch.float16, dev)
 kvs = [mgr.allocate(f"p{i}", 1024) for i in range(batch)]
 toks = []
 for kv in kvs:
-    ids = torch.randint(0, 32000, (128 if batch > 1 else 512,), device=dev)
+    ids = torch.randint(0, 32000, (int(os.environ.get("PROMPT", "128" if batch > 1 else "512")),), device=dev)
     _, tok = span.prefill(kv, ids=ids)
     toks.append(tok.clone())
 tok = torch.cat(toks)
