@@ -58,6 +58,25 @@ def attention_with_cache(q, k_new, v_new, kv: SessionKV, layer: int, pos0: int, 
     return torch.matmul(probs, vf).transpose(0, 1).reshape(T, nh * D)
 
 
+class _ScratchKV:
+    """Cache stand-in for a forward pass that keeps nothing: fresh K/V buffers per block, sized to the sequence."""
+
+    def __init__(self, n_kv: int, length: int, head_dim: int, dtype, device):
+        self._shape, self._dtype, self._device = (n_kv, length, head_dim), dtype, device
+        self._bufs: Dict[tuple, torch.Tensor] = {}
+
+    def _buf(self, key):
+        if key not in self._bufs:
+            self._bufs[key] = torch.zeros(self._shape, dtype=self._dtype, device=self._device)
+        return self._bufs[key]
+
+    def k(self, layer: int) -> torch.Tensor:
+        return self._buf((layer, 0))
+
+    def v(self, layer: int) -> torch.Tensor:
+        return self._buf((layer, 1))
+
+
 class TorchSpan:
     """Runs decoder blocks [start, end) of a model from canonical weights with torch ops."""
 
@@ -122,6 +141,23 @@ class TorchSpan:
         x = F.layer_norm(h, (c.hidden,), L["ln2_w"], L["ln2_b"], c.norm_eps)
         m = F.linear(F.gelu(F.linear(x, L["fc_w"], L["fc_b"]), approximate="tanh"), L["down_w"], L["down_b"])
         return h + m
+
+    def block_stateless(self, h: torch.Tensor, L: Dict[str, torch.Tensor]) -> torch.Tensor:
+        """One block over whole sequences ``h`` [B, T, H] from position 0, causal, nothing cached.  Differentiable:
+        this is what the training-side RPCs run (upstream ``run_rpc_forward`` / ``run_rpc_backward``,
+        petals/server/block_functions.py:32-139)."""
+        fn = self._llama_layer if self.cfg.is_llama else self._gpt2_layer
+        outs = []
+        for b in range(h.shape[0]):
+            kv = _ScratchKV(self.cfg.n_kv_heads, h.shape[1], self.cfg.head_dim, h.dtype, h.device)
+            outs.append(fn(h[b], L, kv, 0, 0))
+        return torch.stack(outs)
+
+    def forward_stateless(self, h: torch.Tensor) -> torch.Tensor:
+        """All blocks of the span over ``h`` [B, T, H], no session (autograd-friendly)."""
+        for L in self.layers:
+            h = self.block_stateless(h, L)
+        return h
 
     @torch.inference_mode()
     def forward(self, h: torch.Tensor, kv: SessionKV, pos0: Optional[int] = None) -> torch.Tensor:

@@ -127,6 +127,63 @@ class _StageBase(torch.nn.Module):
             v.__class__ = StageSegment
         return v
 
+    # ---- training-side passes: whole sequences, no session cache (upstream rpc_forward / rpc_backward)
+    def _dense_block(self, li: int):
+        """(helper TorchSpan, dense weight dict) of block ``li``.  A native span keeps only its packed tiles, so the
+        block is un-tiled for the moment it is needed - one block's worth of extra memory, never the span's."""
+        if self.role == "stage0":
+            raise ValueError("stateless passes are served by server stages")
+        if isinstance(self.span, TorchSpan):
+            return self.span, self.span.layers[li]
+        from ..ops import packing
+
+        span = self.span
+        if getattr(span, "weight_format", "native") != "native" or getattr(span, "streamed_layers", 0) or \
+                getattr(span, "tp_mode", None) is not None:
+            raise NotImplementedError("stateless forward / backward need a resident 16-bit single-GPU span")
+        if getattr(self, "_dense_helper", None) is None:
+            self._dense_helper = TorchSpan(self.cfg, {"layers": []}, self.device, self.dtype)
+        P = span.layers[li]
+        L = {"ln1_w": P["ln1_w"], "ln2_w": P["ln2_w"], "qkv_w": packing.unpack_weight(P["qkv"]),
+             "o_w": packing.unpack_weight(P["o"]), "down_w": packing.unpack_weight(P["down"])}
+        if self.cfg.is_llama:
+            gu = packing.unpack_weight(P["mlp_in"])
+            L["gate_w"], L["up_w"] = gu[0], gu[1]
+        else:
+            L.update(ln1_b=P["ln1_b"], ln2_b=P["ln2_b"], qkv_b=P["qkv"].bias, o_b=P["o"].bias,
+                     fc_w=packing.unpack_weight(P["mlp_in"]), fc_b=P["mlp_in"].bias, down_b=P["down"].bias)
+        return self._dense_helper, L
+
+    def _dense_blocks(self):
+        for li in range(len(self.span.layers)):
+            yield self._dense_block(li)
+
+    def forward_stateless(self, hidden: torch.Tensor) -> torch.Tensor:
+        """hidden [B, T, H] -> the span's output [B, T, H]; every sequence starts at position 0, nothing is cached."""
+        h = hidden.reshape(-1, hidden.shape[-2], self.cfg.hidden).to(self.device, self.dtype)
+        with torch.no_grad():
+            for helper, L in self._dense_blocks():
+                h = helper.block_stateless(h, L)
+        return h
+
+    def backward(self, hidden: torch.Tensor, grad_out: torch.Tensor) -> torch.Tensor:
+        """Gradient of the span's output w.r.t. its input: re-runs the forward block by block (inputs kept, weights
+        un-tiled per block) and back-propagates ``grad_out`` [B, T, H] through it."""
+        h = hidden.reshape(-1, hidden.shape[-2], self.cfg.hidden).to(self.device, self.dtype)
+        g = grad_out.reshape(h.shape).to(self.device, self.dtype)
+        inputs = []
+        with torch.no_grad():
+            for helper, L in self._dense_blocks():
+                inputs.append(h)
+                h = helper.block_stateless(h, L)
+        for li in reversed(range(len(inputs))):
+            helper, L = self._dense_block(li)         # (native span: un-tiled again, only this block)
+            x = inputs[li].detach().requires_grad_(True)
+            with torch.enable_grad():
+                y = helper.block_stateless(x, L)
+            (g,) = torch.autograd.grad(y, x, g)
+        return g
+
     # ---- KV helpers (the handler owns the manager; tests may let the stage own one)
     def new_kv_manager(self, **kw) -> KVCacheManager:
         return KVCacheManager(self.end - self.start, self.cfg.n_kv_heads, self.cfg.head_dim, self.dtype,

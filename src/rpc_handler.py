@@ -136,7 +136,7 @@ class StageConnectionHandler:
     # ------------------------------------------------------------------ registration
     def add_p2p_handlers(self, server: RpcServer) -> None:
         for name in ("rpc_forward", "rpc_forward_stream", "rpc_info", "rpc_close_session", "rpc_push", "rpc_check",
-                     "rpc_reorder"):
+                     "rpc_reorder", "rpc_backward", "rpc_backward_stream"):
             server.add_handler(f"{HANDLER_PREFIX}.{name}", getattr(self, name))
         server.add_stream_handler(f"{HANDLER_PREFIX}.rpc_inference", self.rpc_inference)
 
@@ -335,6 +335,10 @@ class StageConnectionHandler:
             raise ValueError("No tensors in request")
         else:
             hidden = tensors[0]
+        if metadata.get("stateless") or (metadata.get("session_id") is None and "cur_len" not in metadata
+                                         and "is_prefill" not in metadata):
+            # no session: upstream's rpc_forward - whole sequences through the span, nothing cached
+            return self._stateless(hidden, None, metadata)
         T = hidden.shape[-2] if hidden.dim() >= 2 else 1
         t_in = time.perf_counter()
         sid_ = metadata.get("session_id")
@@ -367,6 +371,34 @@ class StageConnectionHandler:
                                          timeout=self.request_timeout)
         return out_t, out_md
 
+    def _stateless(self, hidden: torch.Tensor, grad_out: Optional[torch.Tensor], metadata: Dict):
+        stage = self._view(metadata)[0]
+        if not hasattr(stage, "forward_stateless"):
+            raise ValueError("this server only serves inference sessions")
+        tokens = int(hidden.numel() // hidden.shape[-1])
+
+        def run():
+            self._bind_device()
+            if grad_out is None:
+                return stage.forward_stateless(hidden)
+            return stage.backward(hidden, grad_out)
+
+        out = self._submit(run, kind="forward" if grad_out is None else "backward", tokens=tokens)
+        self.requests += 1
+        return [out.detach().to("cpu")], {"stateless": True}
+
+    def rpc_backward(self, uid: str, tensors: List[torch.Tensor], metadata: Dict):
+        """Upstream ``rpc_backward`` (petals/server/handler.py, block_functions.run_rpc_backward): ``tensors`` =
+        [inputs, grad_outputs] of this span, both [B, T, H]; the answer is the gradient w.r.t. the inputs.  The
+        forward is recomputed here (nothing is kept between the two calls), at forward priority - inference steps of
+        other sessions go first."""
+        if len(tensors) < 2:
+            raise ValueError("rpc_backward needs [inputs, grad_outputs]")
+        if tensors[0].shape != tensors[1].shape:
+            raise ValueError(f"inputs {tuple(tensors[0].shape)} and grad_outputs {tuple(tensors[1].shape)} differ in shape")
+        return self._stateless(tensors[0], tensors[1], metadata)
+
+    rpc_backward_stream = rpc_backward
     rpc_forward_stream = rpc_forward   # TCP needs no separate streaming path; kept for name parity
     rpc_push = rpc_forward
 
