@@ -433,6 +433,53 @@ class RpcTransport:
             self._replay(session_id, [new] if not new.final else [new], new.key)
         return route, route[i]
 
+    # ------------------------------------------------------------------ training-side passes (no sessions)
+    def _stateless_hop(self, route: List[Hop], i: int, method: str, tensors: List[torch.Tensor]):
+        """One stateless call on hop i; a dead server is replaced and the call repeated (nothing to replay)."""
+        for attempt in range(MAX_ATTEMPTS):
+            hop = route[i]
+            md = {"stateless": True}
+            if hop.partial:
+                md["blocks"] = [int(hop.start_block), int(hop.end_block)]
+            try:
+                out, _ = self.client.call(hop.addr, f"{HANDLER_PREFIX}.{method}", hop.key, tensors, md,
+                                          timeout=self.request_timeout)
+                return out[0]
+            except (TimeoutError, ConnectionError, RpcError) as e:
+                if attempt == MAX_ATTEMPTS - 1:
+                    raise
+                logger.warning("stateless %s on %s (%s) failed: %s", method, hop.key, hop.peer_id[:12], e)
+                self.failed_peers.setdefault(hop.key, set()).add(hop.peer_id)
+                self.recoveries += 1
+                if self.routing == "module":
+                    excl = set().union(*self.failed_peers.values())
+                    route[i:] = self._module_route(hop.start_block, excl)
+                else:
+                    route[i] = Hop(hop.key, self._discover_stage(hop.key, self.failed_peers[hop.key], tries=5), hop.final)
+
+    def forward_stateless(self, hidden: torch.Tensor) -> Tuple[torch.Tensor, list]:
+        """Whole sequences ``hidden`` [B, T, H] through every server span of a fresh route (upstream
+        ``sequential_forward``): returns the last span's output and what :meth:`backward_stateless` needs."""
+        route = list(self._get_route(f"stateless-{time.time_ns()}"))
+        x = hidden.detach().to("cpu")
+        saved = []
+        i = 0
+        while i < len(route):
+            y = self._stateless_hop(route, i, "rpc_forward", [x])
+            saved.append(x)
+            x = y
+            i += 1
+        return x, [route, saved]
+
+    def backward_stateless(self, ctx: list, grad_out: torch.Tensor) -> torch.Tensor:
+        """Gradient w.r.t. the input of :meth:`forward_stateless` (upstream ``sequential_backward``): every span
+        recomputes its forward from the saved input and back-propagates."""
+        route, saved = ctx
+        g = grad_out.detach().to("cpu")
+        for i in reversed(range(len(saved))):
+            g = self._stateless_hop(route, i, "rpc_backward", [saved[i], g])
+        return g
+
     # ------------------------------------------------------------------ public API (reference names)
     def send_prefill(self, L: int, hidden: torch.Tensor, session_id: str, max_length: int) -> None:
         # a prefill starts the session over on every server (fresh cache), so the journal starts over too:

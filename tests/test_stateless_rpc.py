@@ -11,6 +11,7 @@ def _oracle(model, start, end, seed):
     from petals_b200.weights.loader import load_span
 
     cfg = resolve_config(model)
+    end = cfg.n_layers if end is None else end
     w = load_span(model, cfg, start, end, need_embed=False, need_head=False, dtype=torch.float32, device="cpu", seed=seed)
     return cfg, TorchSpan(cfg, w, torch.device("cpu"), torch.float32)
 
@@ -96,3 +97,35 @@ def test_native_stage_untiles_blocks_for_stateless_passes(model):
     g = stage.backward(x, gy)
     assert g.shape == x.shape
     assert (g.float() - g_ref).abs().max().item() < 0.05 * g_ref.abs().max().item()
+
+
+def test_client_chains_stateless_passes_over_two_servers():
+    """RpcTransport.forward_stateless / backward_stateless: the route's spans one after the other, gradients flow back
+    in reverse; equal to autograd through the oracle over all served blocks."""
+    from src.main import parse_splits, run_stage_server_fixed
+    from src.rpc_transport import RpcTransport
+
+    model, splits = "tiny-llama-gqa", "1,3"
+    cuts = parse_splits(splits)
+    handles = []
+    try:
+        h1 = run_stage_server_fixed(_args(model, splits, 1, "", seed=9), torch.device("cpu"), cuts, block=False)
+        handles.append(h1)
+        peers = h1.dht.get_visible_maddrs()[0]
+        handles.append(run_stage_server_fixed(_args(model, splits, 2, peers, seed=9), torch.device("cpu"), cuts, block=False))
+        cfg, ref = _oracle(model, 1, None, 9)
+        tx = RpcTransport(device=torch.device("cpu"), dht_initial_peers=[peers],
+                          stage_keys=["mini_petals:stage1", "mini_petals:stage2"], request_timeout=30.0)
+        torch.manual_seed(3)
+        x, gy = torch.randn(1, 6, cfg.hidden), torch.randn(1, 6, cfg.hidden)
+        y, ctx = tx.forward_stateless(x)
+        gx = tx.backward_stateless(ctx, gy)
+        tx.shutdown()
+        xr = x.clone().requires_grad_(True)
+        y_ref = ref.forward_stateless(xr)
+        (gx_ref,) = torch.autograd.grad(y_ref, xr, gy)
+        assert torch.allclose(y, y_ref.detach(), atol=1e-5, rtol=1e-5)
+        assert torch.allclose(gx, gx_ref, atol=1e-5, rtol=1e-4)
+    finally:
+        for h in handles:
+            h.stop()
