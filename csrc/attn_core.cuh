@@ -93,8 +93,8 @@ struct AttnDecodeSmem {
 
 // Cache rows of a split staged through shared memory by bulk async copies (cp.async.bulk, SASS UBLKCP): one pass of
 // the CTA = kAttnRowsPerPass<D> rows = 8 KiB of K and 8 KiB of V, kAttnStages passes in flight.  The rows of earlier tokens do
-// not depend on the previous kernel, so the first passes are requested above the programmatic-launch wait and are
-// in shared memory when the new q arrives; later passes are copied while the current one is being reduced.
+// are requested as soon as the previous kernels are known to be complete (their L2 prefetch is issued above the
+// programmatic-launch wait) and land while q is rotated; later passes are copied while the current one is reduced.
 template <int D>
 constexpr int kAttnRowsPerPass = (kAttnThreads / 32) * (32 / (D / 8)) * 4;   // warps x rows per warp step x unroll
 #ifndef B200_ATTN_BULK_STAGES
@@ -171,10 +171,8 @@ __device__ __forceinline__ void attn_decode_body(const AttnDecodeParams& p, int 
 #pragma unroll
             for (int st = 0; st < kAttnStages; ++st) mbar_init(&tiles->full[st], 1);
             fence_mbar_init();
-#pragma unroll
-            for (int st = 0; st < kAttnStages; ++st)
-                if (st < n_pass) issue(st, st);
-        } else if (n_old > 0) {
+        }
+        if (n_old > 0) {   // (a hint only: the copies themselves wait for the previous kernels, see below)
             bulk_prefetch_l2(kbase + (size_t)r_begin * D, (uint32_t)(n_old * D * 2));
             bulk_prefetch_l2(vbase + (size_t)r_begin * D, (uint32_t)(n_old * D * 2));
         }
@@ -195,6 +193,13 @@ __device__ __forceinline__ void attn_decode_body(const AttnDecodeParams& p, int 
             ll_validate_range(row_ll, 0, 1, off >> 1, (off + D) >> 1, xtag, tid, kAttnThreads, -1);
         }
         sync();
+    }
+    // The rows are READ only now: the newest of them was written by this layer's launch of the previous step, and a
+    // chain of programmatic launches (or a flag chain) may let this kernel's prologue run before that one has finished.
+    if (bulk && tid == 0) {
+#pragma unroll
+        for (int st = 0; st < kAttnStages; ++st)
+            if (st < n_pass) issue(st, st);
     }
     auto load8 = [&](int off) -> uint4 {       // 8 elements of this token's qkv row starting at element `off`
         return chain ? ll_load8_valid(row_ll + (off >> 1)) : ld_cg_v4(row + off);
