@@ -21,6 +21,8 @@ Replaces src/llama_partition.py:99-137,222-297,391-474 (Stage forward loops).
 """
 from __future__ import annotations
 
+import contextlib
+import gc
 import math
 import os
 from typing import Dict, List, Optional, Sequence
@@ -37,6 +39,22 @@ from ..utils.metrics import nvtx_range
 from .kv_cache import SessionKV
 
 MAX_DECODE_BATCH = 32
+
+
+@contextlib.contextmanager
+def _capture_guard():
+    """No cyclic garbage collection while a stream is capturing: a collection that happens to run inside the capture
+    may finalise dead objects of this thread that own CUDA resources (graphs, streams, raw allocations) - their
+    destructors make calls that are illegal during capture and invalidate it ("operation failed due to a previous error
+    during capture"; seen when a test suite had left such garbage behind).  Collect first, then hold the collector."""
+    gc.collect()
+    was = gc.isenabled()
+    gc.disable()
+    try:
+        yield
+    finally:
+        if was:
+            gc.enable()
 
 
 RSTD_KERNEL_MIN_TOKENS = int(os.environ.get("B200_RSTD_KERNEL_MIN_TOKENS", "8"))
@@ -623,7 +641,7 @@ class NativeSpan:
         g = torch.cuda.CUDAGraph()
         self.kernel_launches = before
         # (thread_local: other threads of a server or client process keep making CUDA calls while this one captures)
-        with torch.cuda.graph(g, stream=s, capture_error_mode="thread_local"):
+        with _capture_guard(), torch.cuda.graph(g, stream=s, capture_error_mode="thread_local"):
             out_h = self._decode_body(B, from_ids, greedy, prog)
         per = self.kernel_launches - before
         self.kernel_launches = before  # warm-up + capture passes touched KV slot `pos` twice; harmless: same data
@@ -676,7 +694,7 @@ class NativeSpan:
             torch.cuda.synchronize(self.device)
             per = self.kernel_launches - before
             g = torch.cuda.CUDAGraph()
-            with torch.cuda.graph(g, stream=s, capture_error_mode="thread_local"):
+            with _capture_guard(), torch.cuda.graph(g, stream=s, capture_error_mode="thread_local"):
                 body()
             self.kernel_launches = before
             self._graphs[key] = g
