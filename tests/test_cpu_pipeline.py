@@ -90,3 +90,25 @@ def test_push_chain_matches_star():
     finally:
         for h in handles:
             h.stop()
+
+
+def test_generate_api_equals_the_cli_client():
+    """src.client.generate(): the CLI client's loop as a call (same tokens; unknown flags are refused)."""
+    import pytest
+
+    from src.client import generate
+    from src.main import parse_splits, run_rank0, run_stage_server_fixed
+
+    model, splits = "tiny-llama-gqa", "2"
+    h = run_stage_server_fixed(_args(model, splits, 1, "", seed=7), torch.device("cpu"), parse_splits(splits), block=False)
+    try:
+        peers = h.dht.get_visible_maddrs()[0]
+        ref, _ = run_rank0(_args(model, splits, 0, peers, seed=7, max_new_tokens=6), torch.device("cpu"), parse_splits(splits))
+        seen = []
+        out, stats = generate(model, splits, "Hello, how are you?", peers, max_new_tokens=6, temperature=0.0, seed=7,
+                              device=torch.device("cpu"), on_token=lambda i, t: seen.append(t))
+        assert out == ref and seen[:len(out)] == out and "ttft_s" in stats
+        with pytest.raises(TypeError):
+            generate(model, splits, "x", peers, no_such_flag=1)
+    finally:
+        h.stop()
