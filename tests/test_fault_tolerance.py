@@ -189,3 +189,59 @@ def test_registry_survives_the_bootstrap_node():
                 h.stop()
             except Exception:
                 pass
+
+
+@pytest.mark.parametrize("push", [False, True])
+def test_concurrent_sessions_survive_a_replica_kill(push):
+    """Six client sessions step concurrently against batching servers (two replicas per stage); one replica "crashes"
+    mid-generation.  Every session - the ones that were on the dead replica and the ones batched next to them on the
+    survivors - must end with exactly the tokens it produces alone."""
+    import threading
+
+    from src.main import parse_splits, run_rank0
+
+    model, splits = "tiny-llama-gqa", "1,3"
+    cuts = parse_splits(splits)
+    dev = torch.device("cpu")
+    prompts = ["alpha beta", "one two three four", "x", "the quick brown fox", "a b c d e f g", "hello there"]
+    handles = []
+    try:
+        first = _start(model, splits, cuts, 1, "")
+        peers = first.dht.get_visible_maddrs()[0]
+        handles = [first, _start(model, splits, cuts, 2, peers), _start(model, splits, cuts, 1, peers),
+                   _start(model, splits, cuts, 2, peers)]
+        n_new = 12
+
+        def client(i):
+            return run_rank0(_args(model, splits, 0, peers, seed=11, max_new_tokens=n_new, prompt=prompts[i],
+                                   request_timeout=10.0, no_repeat_stop=True, push=push and armed), dev, cuts)
+
+        armed = False
+        ref = [client(i)[0] for i in range(len(prompts))]
+        armed = True
+        fired = []
+        for h in handles:
+            h.handler.die_after = h.handler.requests + 20          # somewhere in the middle of the concurrent run
+            h.handler.die_guard = lambda: (not fired) and (fired.append(1) or True)   # only one server dies
+        out, rec = [None] * len(prompts), [0] * len(prompts)
+
+        def run(i):
+            out[i], st = client(i)
+            rec[i] = st["recoveries"]
+
+        ts = [threading.Thread(target=run, args=(i,)) for i in range(len(prompts))]
+        for t in ts:
+            t.start()
+        for t in ts:
+            t.join(120)
+        assert fired, "the fault was never injected"
+        assert sum(rec) >= 1, "somebody must have had to recover"
+        assert out == ref, "every concurrent session continues token-exact"
+        batched = any(h.handler.pool.batches and h.handler.pool.batched_items > h.handler.pool.batches for h in handles)
+        assert batched, "the servers did batch concurrent steps"
+    finally:
+        for h in handles:
+            try:
+                h.stop()
+            except Exception:
+                pass
