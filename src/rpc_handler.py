@@ -246,7 +246,15 @@ class StageConnectionHandler:
             else:
                 token = sample_token(logits, params, generated,
                                      generator=self._gen if logits.device.type == "cpu" else None)
-            return [torch.tensor([[token]], dtype=torch.long)], {"token_id": token, "session_id": sid}
+            reply = {"token_id": token, "session_id": sid}
+            k = int(metadata.get("return_logprobs") or 0)
+            if k > 0:
+                # beam search on the client: the k most likely next tokens with their log-probabilities
+                lp = torch.log_softmax(logits.float(), dim=-1)
+                top = torch.topk(lp, min(k, lp.numel()))
+                reply["topk_ids"] = [int(i) for i in top.indices.tolist()]
+                reply["topk_logprobs"] = [float(v) for v in top.values.tolist()]
+            return [torch.tensor([[token]], dtype=torch.long)], reply
         if out.is_cuda and metadata.get("device_handoff") and metadata["device_handoff"] == self.box():
             # the consumer shares this box: the reply names a slot of this GPU's exported arena, no payload
             return [], {"session_id": sid, "device_tensor": self._export(out)}
@@ -301,7 +309,8 @@ class StageConnectionHandler:
                 t2 = time.perf_counter()
                 self.requests += len(ready)
                 for b, ((i, _, md, sid, _), o) in enumerate(zip(ready, outs)):
-                    if ids is not None and float(md.get("temperature", self._default_temperature)) <= 0.0:
+                    if ids is not None and float(md.get("temperature", self._default_temperature)) <= 0.0 \
+                            and not md.get("return_logprobs"):
                         results[i] = ([torch.tensor([[ids[b]]], dtype=torch.long)], {"token_id": ids[b], "session_id": sid})
                     else:
                         results[i] = self._finish(o, md, sid)

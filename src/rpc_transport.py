@@ -103,6 +103,8 @@ class RpcTransport:
         self.client_cache: Dict[str, Dict[str, List[torch.Tensor]]] = {}
         self.session_max_length: Dict[str, int] = {}
         self.last_token: Optional[int] = None
+        self.last_reply: dict = {}            # metadata of the final stage's latest answer (token, top-k log-probs ...)
+        self.extra_metadata: dict = {}        # merged into every step's request (e.g. return_logprobs for beam search)
         self.hop_times: List[Tuple[str, float]] = []
         self.last_prefill_total: Optional[float] = None
         self.last_decode_total: Optional[float] = None
@@ -186,6 +188,8 @@ class RpcTransport:
             md["is_replay"] = True
         if self.repetition_penalty is not None:
             md["repetition_penalty"] = float(self.repetition_penalty)
+        if self.extra_metadata and not is_replay:
+            md.update(self.extra_metadata)
         return md
 
     def _in_box(self, hop: Hop) -> bool:
@@ -397,6 +401,7 @@ class RpcTransport:
                          tokens=int(T), prefill=bool(is_prefill))
             if "token_id" in omd or hop.final or (self.push and "token_id" in omd):
                 self.last_token = int(omd.get("token_id", out[0].reshape(-1)[0].item()))
+                self.last_reply = dict(omd)
                 break
             cur, cur_desc = self._take(out, omd)
             i += 1
