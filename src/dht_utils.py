@@ -89,6 +89,31 @@ def register_blocks_on_dht(dht: DHT, peer_id, block_indices: Sequence[int], mode
     return ok
 
 
+MODELS_KEY = "_petals.models"
+
+
+def declare_model(dht: DHT, model_name: str, peer_id, info: Dict[str, Any],
+                  expiration_time: Optional[float] = None) -> bool:
+    """The swarm-wide list of served models (upstream ``_petals.models``, petals/server/server.py:738-744): every
+    server adds ``{model -> {peer -> info}}`` so that a monitor can discover what a swarm serves without knowing
+    model names in advance.  ``info``: architecture facts a client needs before it asks for blocks."""
+    rec = {"peer_id": str(peer_id), "model": model_name, "timestamp": get_dht_time(), **info}
+    return dht.store(MODELS_KEY, rec, _exp(expiration_time), subkey=f"{model_name}|{peer_id}")
+
+
+def get_models(dht: DHT) -> Dict[str, List[Dict[str, Any]]]:
+    """{model name: [live server records]} from the ``_petals.models`` key."""
+    out: Dict[str, List[Dict[str, Any]]] = {}
+    rec = dht.get(MODELS_KEY, latest=True)
+    if rec is None or not isinstance(rec.value, dict):
+        return out
+    for x in rec.value.values():
+        v = getattr(x, "value", None)
+        if isinstance(v, dict) and v.get("model"):
+            out.setdefault(str(v["model"]), []).append(v)
+    return out
+
+
 def _live_entries(record) -> Dict[str, Dict[str, Any]]:
     """{subkey: value dict} of a sub-keyed record (tolerates plain records)."""
     if record is None:

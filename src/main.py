@@ -35,8 +35,8 @@ from petals_b200.net.dht import DHT, PeerID, get_dht_time
 from petals_b200.net.rpc import RpcServer
 from petals_b200.utils.tokenizer import load_tokenizer
 
-from .dht_utils import (announce_offline, get_remote_module_infos, register_blocks_on_dht, register_server_on_dht,
-                        register_stage_on_dht)
+from .dht_utils import (announce_offline, declare_model, get_remote_module_infos, register_blocks_on_dht,
+                        register_server_on_dht, register_stage_on_dht)
 from .load_balancing import choose_best_blocks, should_choose_other_blocks
 from .partition import Stage0, StageLast, StageSegment, load_stage_model
 from .rpc_handler import StageConnectionHandler
@@ -243,6 +243,12 @@ def start_stage_server(args, device, stage_model, final_stage: bool, stage_index
 
     def publish():
         exp = get_dht_time() + RECORD_TTL
+        cfg_ = getattr(stage_model, "cfg", None)
+        declare_model(dht, model_name, peer_id, {
+            "n_layers": getattr(cfg_, "n_layers", None), "hidden": getattr(cfg_, "hidden", None),
+            "blocks": [handler.start_block, handler.end_block], "final_stage": final_stage,
+            "dtype": str(getattr(stage_model, "dtype", "")).replace("torch.", ""), "p2p_maddrs": maddrs,
+            "stage": stage_index, "throughput": handler.throughput}, expiration_time=exp)
         if stage_index is not None:
             extra = {}
             if lb_blocks:

@@ -361,3 +361,31 @@ def test_handoff_gpu_numbering(monkeypatch):
     with pytest.raises(RuntimeError):
         devshare.local_index(0)
     assert devshare._physical_index(torch.device("cuda", 1)) == 5
+
+
+def test_models_registry_and_swarm_status():
+    """Servers declare their model under `_petals.models`; scripts/swarm_status.py finds models, spans and gaps from a
+    registry address alone."""
+    from scripts.swarm_status import collect
+    from src.main import parse_splits, run_stage_server_fixed
+    from tests.test_cpu_pipeline import _args
+
+    model, splits = "tiny-llama-gqa", "1,3"
+    cuts = parse_splits(splits)
+    h1 = run_stage_server_fixed(_args(model, splits, 1, "", seed=1), torch.device("cpu"), cuts, block=False)
+    try:
+        peers = h1.dht.get_visible_maddrs()[0]
+        st = collect(peers)
+        assert list(st) == [model]
+        m = st[model]
+        assert m["n_layers"] == 4 and m["served_blocks"] == [1, 3] and m["gaps"] == [3], m
+        assert m["servers"][0]["alive"] and m["servers"][0]["blocks"] == [1, 3] and m["servers"][0]["stage"] == 1
+        h2 = run_stage_server_fixed(_args(model, splits, 2, peers, seed=1), torch.device("cpu"), cuts, block=False)
+        try:
+            m = collect(peers)[model]
+            assert m["served_blocks"] == [1, 4] and m["gaps"] == [] and len(m["servers"]) == 2
+            assert [s["final"] for s in m["servers"]] == [False, True]
+        finally:
+            h2.stop()
+    finally:
+        h1.stop()
