@@ -33,7 +33,7 @@ def collect(peers: str) -> dict:
                 try:
                     host, port, _ = parse_maddr((s.get("p2p_maddrs") or [""])[0])
                     _, info = client.call((host, port), "StageConnectionHandler.rpc_info", "status", [], {}, timeout=3.0)
-                    row.update(alive=True, sessions=info.get("sessions"), cache_tokens_left=info.get("cache_tokens_left"),
+                    row.update(alive=bool(info.get("healthy", True)), sessions=info.get("sessions"), cache_tokens_left=info.get("cache_tokens_left"),
                                queued=info.get("queued"), mean_batch=round(info.get("mean_batch", 0.0), 2),
                                requests=info.get("requests"), uptime_s=round(info.get("uptime_s", 0.0), 1))
                 except Exception as e:  # noqa: BLE001

@@ -487,6 +487,7 @@ class StageConnectionHandler:
                     "batch_ms": {k: round(v * 1e3 / max(self.pool.batches, 1), 3) for k, v in self.batch_seconds.items()},
                     "mean_service_ms": round(self.service_seconds * 1e3 / max(self.service_count, 1), 3),
                     "mean_turnaround_ms": round(self.think_seconds * 1e3 / max(self.think_count, 1), 3),
+                    "healthy": bool(self.pool._thread.is_alive()) and not self.pool._stop,
                     "box": self.box(), "gpu": self._gpu_ids()[0], "visible_gpus": self._gpu_ids()[1], "handoff_out": self.handoff_out, "handoff_in": self.handoff_in}
 
     def rpc_check(self, uid: str, tensors, metadata: Dict):
