@@ -32,6 +32,7 @@ def _reference_modules():
         import importlib
 
         lp = importlib.import_module("src.llama_partition")
+        lp.ReferenceHandler = importlib.import_module("src.rpc_handler").StageConnectionHandler
     finally:
         sys.path.remove(REF)
         for k in [k for k in sys.modules if k == "src" or k.startswith("src.") or k == "petals" or k.startswith("petals.")]:
@@ -102,3 +103,57 @@ def test_reference_stages_and_ours_agree_token_by_token():
             lo = out_our.reshape(-1, cfg.vocab)[-1].float()
             assert torch.allclose(lo, lr, atol=5e-5, rtol=1e-4), f"logits, token {t}"
             assert int(lo.argmax()) == int(lr.argmax())
+
+
+def test_reference_handler_and_ours_answer_the_same_requests():
+    """The reference's StageConnectionHandler._run_forward (+ its _sample_token, greedy) and our handler, fed the same
+    session - a one-token prefill, then single-token steps with the reference's metadata keys - must return the same
+    tokens from the same hidden states."""
+    import transformers
+
+    from petals_b200.models.config import resolve_config
+    from petals_b200.runtime.stages import StageLast, StageWeights
+    from petals_b200.weights.loader import full_hf_state_dict, load_span
+    from src.rpc_handler import StageConnectionHandler
+
+    lp, H = _reference_modules()
+    _, _, mser = H._install_stubs()
+    model, seed, cut = "tiny-llama-gqa", 23, 1
+    cfg = resolve_config(model)
+    sd = full_hf_state_dict(cfg, seed)
+    c = transformers.LlamaConfig(**{k: v for k, v in cfg.to_hf_dict().items() if k not in ("model_type", "architectures")})
+    c.num_hidden_layers = cfg.n_layers - cut
+    c.pretraining_tp = 1
+    c._attn_implementation = "eager"
+    m = transformers.LlamaForCausalLM(c).float().eval()
+    part = {}
+    for k, v in sd.items():
+        if k.startswith("model.layers."):
+            li = int(k.split(".")[2])
+            if li >= cut:
+                part[k.replace(f"model.layers.{li}.", f"model.layers.{li - cut}.")] = v.float()
+        else:
+            part[k] = v.float()
+    m.load_state_dict(part, strict=False)
+    dev = torch.device("cpu")
+    ref_stage = lp.StageLast(m, cut, gpu_device=dev, keep_layers_on_gpu=cfg.n_layers - cut)
+    H._shim(ref_stage, c)
+    ref = lp.ReferenceHandler(None, ref_stage, dev, request_timeout=30.0, final_stage=True)
+
+    w = load_span(model, cfg, cut, cfg.n_layers, need_embed=False, need_head=True, dtype=torch.float32, device=dev, seed=seed)
+    ours = StageConnectionHandler(None, StageLast(StageWeights(cfg, w, "last", cut, cfg.n_layers, dev, torch.float32), cut,
+                                                  kv_capacity=64), dev, final_stage=True)
+    try:
+        g = torch.Generator().manual_seed(5)
+        generated = []
+        for t in range(10):
+            hidden = torch.randn(1, 1, cfg.hidden, generator=g) * 0.5
+            md = dict(session_id="parity", seq_len=1, cur_len=t + 1, is_prefill=(t == 0), max_length=64, temperature=0.0,
+                      top_p=0.92, top_k=50, generated_tokens=generated[-50:])
+            r = ref._run_forward(hidden.clone(), dict(md))
+            tok_ref = int(mser.loads(r.metadata)["token_id"])
+            _, omd = ours.rpc_forward("k", [hidden.clone()], dict(md))
+            assert omd["token_id"] == tok_ref, f"step {t}: ours {omd['token_id']} vs reference {tok_ref}"
+            generated.append(tok_ref)
+    finally:
+        ours.shutdown()
