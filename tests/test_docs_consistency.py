@@ -5,7 +5,7 @@ import re
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 DOCS = ["README.md", "DESIGN.md", "INTEGRATION.md", "BASELINE.md", "docs/DEPLOY.md", "docs/LOAD_BALANCING.md",
-        "docs/FAULT_TOLERANCE.md", "docs/TROUBLESHOOTING.md", "docs/BENCHMARKS.md", "profiles/README.md"]
+        "docs/FAULT_TOLERANCE.md", "docs/TROUBLESHOOTING.md", "docs/BENCHMARKS.md", "docs/ARCHITECTURE.md", "profiles/README.md"]
 
 
 def _read(rel):
