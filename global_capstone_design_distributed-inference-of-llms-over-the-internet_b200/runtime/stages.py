@@ -158,30 +158,59 @@ class _StageBase(torch.nn.Module):
         for li in range(len(self.span.layers)):
             yield self._dense_block(li)
 
-    def forward_stateless(self, hidden: torch.Tensor) -> torch.Tensor:
-        """hidden [B, T, H] -> the span's output [B, T, H]; every sequence starts at position 0, nothing is cached."""
+    @staticmethod
+    def _add_prompts(h: torch.Tensor, prompts: Optional[torch.Tensor], li: int) -> torch.Tensor:
+        """Deep prompt tuning (upstream block_functions.py:55-61): the client's trainable prefix of block ``li`` is
+        ADDED to the first ``prefix_len`` positions of that block's input."""
+        if prompts is None:
+            return h
+        p = prompts[li].to(h.device, h.dtype)
+        pre = p.shape[-2]
+        return torch.cat([h[:, :pre] + p, h[:, pre:]], dim=1)
+
+    def _check_prompts(self, prompts: Optional[torch.Tensor], h: torch.Tensor) -> Optional[torch.Tensor]:
+        if prompts is None:
+            return None
+        n = len(self.span.layers)
+        if prompts.dim() != 4 or prompts.shape[0] != n or prompts.shape[1] != h.shape[0] or \
+                prompts.shape[2] > h.shape[1] or prompts.shape[3] != h.shape[2]:
+            raise ValueError(f"prompts must be [blocks={n}, batch={h.shape[0]}, prefix<={h.shape[1]}, {h.shape[2]}], "
+                             f"got {tuple(prompts.shape)}")
+        return prompts
+
+    def forward_stateless(self, hidden: torch.Tensor, prompts: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """hidden [B, T, H] -> the span's output [B, T, H]; every sequence starts at position 0, nothing is cached.
+        ``prompts`` [blocks, B, prefix, H]: deep prompts, one per block of the span."""
         h = hidden.reshape(-1, hidden.shape[-2], self.cfg.hidden).to(self.device, self.dtype)
+        prompts = self._check_prompts(prompts, h)
         with torch.no_grad():
-            for helper, L in self._dense_blocks():
-                h = helper.block_stateless(h, L)
+            for li, (helper, L) in enumerate(self._dense_blocks()):
+                h = helper.block_stateless(self._add_prompts(h, prompts, li), L)
         return h
 
-    def backward(self, hidden: torch.Tensor, grad_out: torch.Tensor) -> torch.Tensor:
+    def backward(self, hidden: torch.Tensor, grad_out: torch.Tensor, prompts: Optional[torch.Tensor] = None):
         """Gradient of the span's output w.r.t. its input: re-runs the forward block by block (inputs kept, weights
-        un-tiled per block) and back-propagates ``grad_out`` [B, T, H] through it."""
+        un-tiled per block) and back-propagates ``grad_out`` [B, T, H] through it.  With ``prompts`` the result is
+        ``(grad_input, grad_prompts)``."""
         h = hidden.reshape(-1, hidden.shape[-2], self.cfg.hidden).to(self.device, self.dtype)
         g = grad_out.reshape(h.shape).to(self.device, self.dtype)
+        prompts = self._check_prompts(prompts, h)
         inputs = []
         with torch.no_grad():
-            for helper, L in self._dense_blocks():
+            for li, (helper, L) in enumerate(self._dense_blocks()):
                 inputs.append(h)
-                h = helper.block_stateless(h, L)
+                h = helper.block_stateless(self._add_prompts(h, prompts, li), L)
+        grad_prompts = [] if prompts is not None else None
         for li in reversed(range(len(inputs))):
             helper, L = self._dense_block(li)         # (native span: un-tiled again, only this block)
             x = inputs[li].detach().requires_grad_(True)
             with torch.enable_grad():
-                y = helper.block_stateless(x, L)
+                y = helper.block_stateless(self._add_prompts(x, prompts, li), L)
             (g,) = torch.autograd.grad(y, x, g)
+            if prompts is not None:
+                grad_prompts.append(g[:, : prompts.shape[2]].clone())      # d/d(prompt) = d/d(input) on the prefix
+        if prompts is not None:
+            return g, torch.stack(grad_prompts[::-1])
         return g
 
     # ---- KV helpers (the handler owns the manager; tests may let the stage own one)

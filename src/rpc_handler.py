@@ -347,7 +347,7 @@ class StageConnectionHandler:
         if metadata.get("stateless") or (metadata.get("session_id") is None and "cur_len" not in metadata
                                          and "is_prefill" not in metadata):
             # no session: upstream's rpc_forward - whole sequences through the span, nothing cached
-            return self._stateless(hidden, None, metadata)
+            return self._stateless(hidden, None, metadata, tensors[1] if len(tensors) > 1 else None)
         T = hidden.shape[-2] if hidden.dim() >= 2 else 1
         t_in = time.perf_counter()
         sid_ = metadata.get("session_id")
@@ -380,7 +380,8 @@ class StageConnectionHandler:
                                          timeout=self.request_timeout)
         return out_t, out_md
 
-    def _stateless(self, hidden: torch.Tensor, grad_out: Optional[torch.Tensor], metadata: Dict):
+    def _stateless(self, hidden: torch.Tensor, grad_out: Optional[torch.Tensor], metadata: Dict,
+                   prompts: Optional[torch.Tensor] = None):
         stage = self._view(metadata)[0]
         if not hasattr(stage, "forward_stateless"):
             raise ValueError("this server only serves inference sessions")
@@ -389,23 +390,25 @@ class StageConnectionHandler:
         def run():
             self._bind_device()
             if grad_out is None:
-                return stage.forward_stateless(hidden)
-            return stage.backward(hidden, grad_out)
+                return stage.forward_stateless(hidden, prompts) if prompts is not None else stage.forward_stateless(hidden)
+            return stage.backward(hidden, grad_out, prompts) if prompts is not None else stage.backward(hidden, grad_out)
 
         out = self._submit(run, kind="forward" if grad_out is None else "backward", tokens=tokens)
         self.requests += 1
-        return [out.detach().to("cpu")], {"stateless": True}
+        outs = list(out) if isinstance(out, tuple) else [out]
+        return [o.detach().to("cpu") for o in outs], {"stateless": True}
 
     def rpc_backward(self, uid: str, tensors: List[torch.Tensor], metadata: Dict):
         """Upstream ``rpc_backward`` (petals/server/handler.py, block_functions.run_rpc_backward): ``tensors`` =
-        [inputs, grad_outputs] of this span, both [B, T, H]; the answer is the gradient w.r.t. the inputs.  The
+        [inputs, grad_outputs] of this span, both [B, T, H] (+ optional deep prompts [blocks, B, prefix, H]); the answer is
+        the gradient w.r.t. the inputs (+ the gradient w.r.t. the prompts).  The
         forward is recomputed here (nothing is kept between the two calls), at forward priority - inference steps of
         other sessions go first."""
         if len(tensors) < 2:
             raise ValueError("rpc_backward needs [inputs, grad_outputs]")
         if tensors[0].shape != tensors[1].shape:
             raise ValueError(f"inputs {tuple(tensors[0].shape)} and grad_outputs {tuple(tensors[1].shape)} differ in shape")
-        return self._stateless(tensors[0], tensors[1], metadata)
+        return self._stateless(tensors[0], tensors[1], metadata, tensors[2] if len(tensors) > 2 else None)
 
     rpc_backward_stream = rpc_backward
     rpc_forward_stream = rpc_forward   # TCP needs no separate streaming path; kept for name parity

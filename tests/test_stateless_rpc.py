@@ -129,3 +129,37 @@ def test_client_chains_stateless_passes_over_two_servers():
     finally:
         for h in handles:
             h.stop()
+
+
+def test_deep_prompts_forward_and_gradients():
+    """Deep prompt tuning over the wire: per-block prefixes are added to the block inputs; rpc_backward returns the
+    gradients w.r.t. the input AND the prompts - equal to autograd through the oracle."""
+    from petals_b200.net.rpc import RpcClient
+    from src.main import parse_splits, run_stage_server_fixed
+
+    model, splits = "tiny-llama-gqa", "1,3"
+    h = run_stage_server_fixed(_args(model, splits, 1, "", seed=9), torch.device("cpu"), parse_splits(splits), block=False)
+    try:
+        cfg, ref = _oracle(model, 1, 3, 9)
+        torch.manual_seed(2)
+        x, gy = torch.randn(2, 6, cfg.hidden), torch.randn(2, 6, cfg.hidden)
+        prompts = torch.randn(2, 2, 3, cfg.hidden) * 0.1                 # [blocks, batch, prefix, H]
+        xr, pr = x.clone().requires_grad_(True), prompts.clone().requires_grad_(True)
+        hcur = xr
+        for li, L in enumerate(ref.layers):
+            hcur = ref.block_stateless(torch.cat([hcur[:, :3] + pr[li], hcur[:, 3:]], 1), L)
+        gx_ref, gp_ref = torch.autograd.grad(hcur, (xr, pr), gy)
+        c = RpcClient()
+        addr = h.rpc.address
+        (y,), _ = c.call(addr, "StageConnectionHandler.rpc_forward", "k", [x, prompts], {})
+        assert torch.allclose(y, hcur.detach(), atol=1e-5, rtol=1e-5)
+        (gx, gp), _ = c.call(addr, "StageConnectionHandler.rpc_backward", "k", [x, gy, prompts], {})
+        assert torch.allclose(gx, gx_ref, atol=1e-5, rtol=1e-4) and torch.allclose(gp, gp_ref, atol=1e-5, rtol=1e-4)
+        try:
+            c.call(addr, "StageConnectionHandler.rpc_forward", "k", [x, prompts[:1]], {})
+            raise AssertionError("a prompt tensor for the wrong number of blocks must be refused")
+        except Exception as e:  # noqa: BLE001
+            assert "prompts must be" in str(e)
+        c.close()
+    finally:
+        h.stop()
